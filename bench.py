@@ -1,0 +1,368 @@
+#!/usr/bin/env python
+"""bench.py -- grid-point updates/s of the shallow-water step over fd_lib fields on B200.
+
+    python bench.py --gpus N --steps K --warmup W              (our arm)
+    python bench.py --impl reference --gpus N --steps K --warmup W   (reference arm: CPU)
+
+Workload (BASELINE.json metric/config): FP64 shallow-water C-grid step, double periodic,
+GO_OFFSET_SW, 16384^2 points PER GPU (weak scaling: the global domain grows with the
+go_decompose tile grid 1x1, 1x2, 2x2, 2x4), DL_ESM_ALIGNMENT=64, synthetic classic "shallow"
+initial state.  One bench step = one model time step of the fused sweep + halo fill /
+exchange.  One JSON line on stdout (rank 0).
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "grid-point updates/s per shallow-water step"
+UNIT = "points/s"
+BYTES_PER_POINT = 96.0          # 6 FP64 reads + 6 FP64 writes per internal point
+FALLBACK_HBM_GBS = 6650.0       # B200_PROFILING.md fallback when MEASURED_PEAKS.json is absent
+
+
+def env_int(name, default):
+    try:
+        return int(os.environ.get(name, default))
+    except ValueError:
+        return default
+
+
+# ---------------------------------------------------------------------------------------------
+# clocks sampler (NVML) during the timed region
+# ---------------------------------------------------------------------------------------------
+class ClockSampler(threading.Thread):
+    def __init__(self, device_index, period=0.02):
+        super().__init__(daemon=True)
+        self.samples, self.period, self.stop_flag = [], period, False
+        self.ok = False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(device_index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception:
+            self.max_mhz = None
+
+    def run(self):
+        if not self.ok:
+            return
+        nv = self.nv
+        while not self.stop_flag:
+            try:
+                mhz = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
+                try:
+                    reasons = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    reasons = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                self.samples.append((time.time(), mhz, reasons))
+            except Exception:
+                pass
+            time.sleep(self.period)
+
+    def summary(self, t0, t1):
+        if not self.ok:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvml unavailable"]}
+        inside = [s for s in self.samples if t0 <= s[0] <= t1] or self.samples[-3:]
+        mhz = sorted(s[1] for s in inside)
+        bits = 0
+        for s in inside:
+            bits |= s[2]
+        names = {0x1: "gpu_idle", 0x2: "applications_clocks_setting", 0x4: "sw_power_cap", 0x8: "hw_slowdown",
+                 0x10: "sync_boost", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+                 0x80: "hw_power_brake_slowdown", 0x100: "display_clock_setting"}
+        reasons = [n for b, n in names.items() if bits & b and n != "gpu_idle"]
+        return {"sm_mhz": mhz[len(mhz) // 2] if mhz else None, "sm_max_mhz": self.max_mhz,
+                "reasons": reasons, "samples": len(inside)}
+
+
+def measured_hbm_peak():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(path) as fh:
+            return float(json.load(fh)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return FALLBACK_HBM_GBS, "fallback (B200_PROFILING.md)"
+
+
+# ---------------------------------------------------------------------------------------------
+# reference arm / cpu baseline: the oracle port of the reference's CPU formulation
+# ---------------------------------------------------------------------------------------------
+def cpu_run(global_n, nthreads, steps, warmup):
+    from oracle import oracle as O
+    secs, cks = O.sw_run_threads(global_n, global_n, nthreads, steps, warmup)
+    return global_n * global_n * steps / secs, secs, cks
+
+
+def pick_cpu_sample(nthreads, steps, warmup, budget_s):
+    """largest square sample whose (steps+warmup) steps fit the time budget"""
+    rate, _, _ = cpu_run(1024, nthreads, 3, 1)          # calibration: points/s
+    best = 1024
+    for n in (2048, 4096, 8192, 16384):
+        est = n * n * (steps + warmup) / rate * 1.3 + 13 * n * n * 8 / 4e9   # + first-touch init
+        try:
+            avail = os.sysconf("SC_AVPHYS_PAGES") * os.sysconf("SC_PAGE_SIZE")
+        except (ValueError, OSError):
+            avail = 1 << 62
+        if est <= budget_s and 13 * n * n * 8 * 1.2 < avail:
+            best = n
+    return best
+
+
+def run_reference_arm(args):
+    rank = env_int("RANK", 0)
+    if rank != 0:
+        return 0        # rank 0 alone runs the CPU arm
+    ncores = os.cpu_count() or 1
+    n = pick_cpu_sample(ncores, args.steps, args.warmup, budget_s=90.0)
+    value, secs, cks = cpu_run(n, ncores, args.steps, args.warmup)
+    sample = ("%dx%d double-periodic sample of the 16384^2-per-GPU workload, %d timed steps, %d threads "
+              "(one go_decompose sub-domain each, exchange_generic-style pack/copy/unpack)"
+              % (n, n, args.steps, ncores))
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1000.0 * secs / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic",
+        "config": {"workload": "shallow-water C-grid step, 16384^2 points per GPU, double periodic, FP64 "
+                               "(CPU arm: bounded sample, see cpu_baseline.sample)",
+                   "reference_build": "oracle port of the reference's Fortran loops (no Fortran/MPI toolchain "
+                                      "in this image: oracle/_ref cannot be built)"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": ncores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+        "checksums_p_u_v": list(cks),
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# ---------------------------------------------------------------------------------------------
+# our arm
+# ---------------------------------------------------------------------------------------------
+def run_ours(args):
+    os.environ["DL_ESM_ALIGNMENT"] = str(args.alignment)
+    rank, world, local_rank = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
+    if world != args.gpus and world > 1:
+        raise SystemExit("--gpus %d but WORLD_SIZE=%d" % (args.gpus, world))
+    import numpy as np
+    import torch
+
+    import dl_esm_inf_b200 as fd
+    from dl_esm_inf_b200 import _lib
+
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    L = _lib.lib()
+    fd.gocean_initialise(rank + 1, world, device=local_rank)
+    if world > 1:
+        # ship rank 1's NCCL id to everyone through torch.distributed (plumbing only)
+        idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            idt = torch.frombuffer(bytearray(fd.comm_unique_id()), dtype=torch.uint8).cuda()
+        dist.broadcast(idt, 0)
+        fd.gocean_initialise(rank + 1, world, device=local_rank, comm_id=bytes(idt.cpu().numpy().tobytes()))
+        fd.set_extensions(fd.EXT_PERIODIC_DISTMEM)   # periodic wrap across ranks (SURVEY F4 extension)
+
+    def barrier():
+        fd.dev_sync()
+        if dist is not None:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    # weak scaling: args.size^2 points per GPU; the tile grid is go_decompose's own choice
+    n = args.size
+    probe = fd.go_decompose(n, n)                       # tile grid for `world` ranks on a square domain
+    gx, gy = n * probe.nx, n * probe.ny
+    bcs = (fd.GO_BC_PERIODIC, fd.GO_BC_PERIODIC, fd.GO_BC_NONE)
+    grid = fd.grid_type(fd.GO_ARAKAWA_C, bcs, fd.GO_OFFSET_SW)
+    grid.decompose(gx, gy)
+    fd.grid_init(grid, 1.0e5, 1.0e5)
+    sub = grid.subdomain
+    local_points = sub.internal.nx * sub.internal.ny
+    total_points = gx * gy
+
+    sw = fd.shallow_water(grid, dt=90.0, alpha=0.001, mode=fd.SW_FUSED if args.mode == "fused" else fd.SW_UNFUSED)
+    sw.set_variant(args.variant)
+    sw.init_device()
+    mass0 = fd.field_checksum(sw.field("p"))
+
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    sw.step(max(args.warmup, 3))
+    L.dlesm_profile_enable(1)
+    L.dlesm_profile_read(None, None, 1)
+    barrier()
+    launches0 = fd.kernel_launch_count()
+    t_wall0 = time.time()
+    L.dlesm_event_record(0)
+    sw.step(args.steps)
+    L.dlesm_event_record(1)
+    ms = C.c_double(0.0)
+    assert L.dlesm_event_elapsed_ms(0, 1, C.byref(ms)) == 0
+    barrier()
+    t_wall1 = time.time()
+    launches = fd.kernel_launch_count() - launches0
+    kms, kn = C.c_double(0.0), C.c_longlong(0)
+    L.dlesm_profile_read(C.byref(kms), C.byref(kn), 1)
+    L.dlesm_profile_enable(0)
+    clocks = sampler.summary(t_wall0, t_wall1)
+
+    elapsed_ms = ms.value
+    if dist is not None:
+        t = torch.tensor([elapsed_ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        elapsed_ms = float(t.item())
+    value = total_points * args.steps / (elapsed_ms * 1e-3)
+
+    # parity guards on the timed state: mass conservation and finite checksums
+    cks = sw.checksums()
+    mass1 = cks[0]
+    assert all(np.isfinite(c) for c in cks), cks
+    assert abs(mass1 - mass0) <= 1e-11 * abs(mass0), (mass0, mass1)
+
+    # ---- roofline of the dominant kernel (fused sweep), timed live with CUDA events ----
+    peak, peak_src = measured_hbm_peak()
+    roofline = None
+    if kn.value > 0:
+        k_ms = kms.value / kn.value
+        achieved = BYTES_PER_POINT * local_points / (k_ms * 1e-3) / 1e9
+        roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                    "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                    "kernel": "fused shallow-water sweep (variant %d)" % args.variant,
+                    "kernel_ms": k_ms, "kernel_share_of_step": kms.value / elapsed_ms,
+                    "algorithmic_bytes_per_launch": BYTES_PER_POINT * local_points,
+                    "frac_of_nominal_8TBs": achieved / 8000.0}
+        prof = os.path.join(ROOT, "profiles", "fused_traffic.json")
+        try:
+            with open(prof) as fh:
+                roofline["traffic"] = json.load(fh).get("dram_bytes_per_launch")
+        except Exception:
+            pass
+
+    # ---- e2e: the same step driven with HOST buffers through the field hooks ----
+    e2e = run_e2e(args, fd, L, sw, grid, total_points, dist, torch) if args.e2e_steps > 0 else None
+    sampler.stop_flag = True
+
+    # ---- cpu baseline (rank 0, N=1 only): bounded sample on the box's host cores ----
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        ncores = os.cpu_count() or 1
+        ncpu = pick_cpu_sample(ncores, 6, 1, budget_s=20.0)
+        cval, csecs, _ = cpu_run(ncpu, ncores, 6, 1)
+        cpu = {"value": cval, "unit": UNIT, "cores": ncores, "kind": "port",
+               "sample": "%dx%d double-periodic sample, 6 timed steps, %d threads (oracle port of the "
+                         "reference's un-fused loops + exchange_generic-style halo exchange)" % (ncpu, ncpu, ncores)}
+        c1, _, _ = cpu_run(1024, 1, 6, 1)
+        cpu["serial_fd_lib_1core_1024sq"] = c1
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "shallow-water C-grid step %dx%d per GPU (global %dx%d, tiles %dx%d), "
+                                   "double periodic, GO_OFFSET_SW, FP64, DL_ESM_ALIGNMENT=%d, mode=%s"
+                                   % (n, n, gx, gy, probe.nx, probe.ny, args.alignment, args.mode),
+                       "l2": "inputs larger than L2 (9 fields x %.2f GB per GPU)" % (grid.nx * grid.ny * 8 / 1e9),
+                       "fused_variant": args.variant, "parallelism": "tile-per-GPU %dx%d" % (probe.nx, probe.ny)},
+            "clocks": clocks, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
+            "e2e": e2e, "checksums_p_u_v": list(cks),
+            "hbm_frac_of_measured_whole_step": (BYTES_PER_POINT * local_points * args.steps /
+                                                (elapsed_ms * 1e-3) / 1e9) / peak,
+        }
+        print(json.dumps(line), flush=True)
+    sw.free()
+    if dist is not None:
+        dist.barrier()
+        fd.gocean_finalise()
+        dist.destroy_process_group()
+    return 0
+
+
+def run_e2e(args, fd, L, sw, grid, total_points, dist, torch):
+    """Every step: write_to_device of the six prognostic fields from pinned host memory, one
+    model step, read_from_device of the six results (the fields' host mirrors own the data
+    between steps, as with the reference's data_on_device hooks when the host touches
+    fld%data each step)."""
+    import numpy as np
+    names = ("u", "v", "p", "uold", "vold", "pold")
+    nx, ny = grid.nx, grid.ny
+    nbytes = nx * ny * 8
+    flds = [sw.field(nm) for nm in names]
+    host = []
+    for f in flds:
+        p = C.c_void_p()
+        assert L.dlesm_host_alloc(nbytes, C.byref(p)) == 0, L.dlesm_last_error()
+        a = np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_double)), shape=(nx * ny,)).reshape((nx, ny), order="F")
+        host.append((p, a))
+        assert L.dlesm_field_read_from_device(f._h, a.ctypes.data_as(C.POINTER(C.c_double)), 1, 1, nx, ny, True) == 0
+
+    def one_step():
+        fl = [sw.field(nm) for nm in names]          # handles follow the buffer rotation
+        for f, (p, a) in zip(fl, host):
+            L.dlesm_write_to_device_c(p, f.device_ptr, 1, 1, nx, ny, False)
+        sw.step(1)
+        fl = [sw.field(nm) for nm in names]
+        for k, (f, (p, a)) in enumerate(zip(fl, host)):
+            L.dlesm_read_from_device_c(f.device_ptr, p, 1, 1, nx, ny, k == len(fl) - 1)
+
+    one_step()                                        # warm-up
+    fd.dev_sync()
+    if dist is not None:
+        dist.barrier()
+    L.dlesm_event_record(2)
+    for _ in range(args.e2e_steps):
+        one_step()
+    L.dlesm_event_record(3)
+    ms = C.c_double(0.0)
+    assert L.dlesm_event_elapsed_ms(2, 3, C.byref(ms)) == 0
+    el = ms.value
+    if dist is not None:
+        t = torch.tensor([el], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        el = float(t.item())
+    out = {"value": total_points * args.e2e_steps / (el * 1e-3), "unit": UNIT,
+           "h2d_bytes_per_step": 6 * nbytes, "d2h_bytes_per_step": 6 * nbytes, "steps": args.e2e_steps,
+           "ms_per_step": el / args.e2e_steps,
+           "what": "per step: H2D of u,v,p,uold,vold,pold from pinned host memory through write_to_device_c, "
+                   "one model step, D2H of the six results through read_from_device_c"}
+    for p, _ in host:
+        L.dlesm_host_free(p)
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--size", type=int, default=16384, help="points per GPU in each dimension")
+    ap.add_argument("--alignment", type=int, default=64)
+    ap.add_argument("--variant", type=int, default=0)
+    ap.add_argument("--mode", default="fused", choices=["fused", "unfused"])
+    ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference_arm(args)
+    return run_ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

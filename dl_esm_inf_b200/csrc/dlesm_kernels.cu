@@ -1,0 +1,553 @@
+// dlesm_kernels.cu -- hand-written sm_100a FP64 kernels for the field_mod operations, the
+// halo pack/unpack, and the un-fused shallow-water sweeps.  Everything here is HBM-bound
+// byte shuffling or low-intensity FP64 arithmetic: coalesced along the contiguous i
+// dimension, 16-byte vectors where alignment allows, grids sized in multiples of 148 SMs,
+// no tensor cores.  Compiled with -fmad=false so that each arithmetic operation rounds once,
+// like the reference's Fortran loops built without FMA (compiler_setup/gnu.sh:7-8) and like
+// the CPU oracle: stencil results are bit-identical, not merely within 1e-12.
+#include "dlesm_kernels.cuh"
+
+#include <atomic>
+
+namespace dlesm {
+namespace k {
+
+namespace {
+std::atomic<long long> g_launches{0};
+inline void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+constexpr int kSMs = 148;
+
+__host__ __device__ inline size_t idx(int pitch, int i, int j)
+{
+    return (static_cast<size_t>(j) - 1) * static_cast<size_t>(pitch) + (static_cast<size_t>(i) - 1);
+}
+inline unsigned cdiv(long long a, long long b) { return static_cast<unsigned>((a + b - 1) / b); }
+}  // namespace
+
+long long launch_count() { return g_launches.load(); }
+void note_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+// ---------------------------------------------------------------------------------------
+// copy_field (src/field_mod.f90:1152-1159): out(:,:) = in(:,:), padding included.
+// 16 B/point.  Grid-stride, 2 x 16-byte loads in flight per thread.
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) copy_kernel(const double2 *__restrict__ in,
+                                                   double2 *__restrict__ out, size_t n2,
+                                                   const double *__restrict__ in_tail,
+                                                   double *__restrict__ out_tail, int tail)
+{
+    const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+    size_t t = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    for (; t + stride < n2; t += 2 * stride) {
+        const double2 a = __ldcs(in + t);
+        const double2 b = __ldcs(in + t + stride);
+        __stcs(out + t, a);
+        __stcs(out + t + stride, b);
+    }
+    if (t < n2) __stcs(out + t, __ldcs(in + t));
+    if (blockIdx.x == 0 && static_cast<int>(threadIdx.x) < tail) out_tail[threadIdx.x] = in_tail[threadIdx.x];
+}
+
+cudaError_t copy_field(const double *in, double *out, size_t n, cudaStream_t s)
+{
+    if (n == 0) return cudaSuccess;
+    const size_t n2 = n / 2;
+    const int tail = static_cast<int>(n - 2 * n2);
+    const unsigned blocks = static_cast<unsigned>(
+        n2 / 512 + 1 < static_cast<size_t>(kSMs) * 16 ? n2 / 512 + 1 : static_cast<size_t>(kSMs) * 16);
+    copy_kernel<<<blocks, 256, 0, s>>>(reinterpret_cast<const double2 *>(in),
+                                       reinterpret_cast<double2 *>(out), n2, in + 2 * n2,
+                                       out + 2 * n2, tail);
+    count_launch();
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------
+// set_field (src/field_mod.f90:1191-1202): fld%data = val.  8 B/point.
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) set_kernel(double2 *__restrict__ out, size_t n2, double val,
+                                                  double *__restrict__ out_tail, int tail)
+{
+    const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+    const double2 v2 = make_double2(val, val);
+    for (size_t t = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; t < n2; t += stride)
+        __stcs(out + t, v2);
+    if (blockIdx.x == 0 && static_cast<int>(threadIdx.x) < tail) out_tail[threadIdx.x] = val;
+}
+
+cudaError_t set_field(double *f, size_t n, double val, cudaStream_t s)
+{
+    if (n == 0) return cudaSuccess;
+    const size_t n2 = n / 2;
+    const unsigned blocks = static_cast<unsigned>(
+        n2 / 256 + 1 < static_cast<size_t>(kSMs) * 16 ? n2 / 256 + 1 : static_cast<size_t>(kSMs) * 16);
+    set_kernel<<<blocks, 256, 0, s>>>(reinterpret_cast<double2 *>(f), n2, val, f + 2 * n2,
+                                      static_cast<int>(n - 2 * n2));
+    count_launch();
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------
+// copy_field patch (src/field_mod.f90:1179-1187): f(dest box) = f(src box) inside one array.
+// Fortran array assignment evaluates the right-hand side first, so overlapping boxes go
+// through a scratch buffer; halo patches never overlap and are copied directly.
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) patch_kernel(const double *__restrict__ src, int spitch,
+                                                    int si0, int sj0, double *__restrict__ dst,
+                                                    int dpitch, int di0, int dj0, int w, int h)
+{
+    const long long n = static_cast<long long>(w) * h;
+    for (long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; t < n;
+         t += static_cast<long long>(gridDim.x) * blockDim.x) {
+        const int jj = static_cast<int>(t / w), ii = static_cast<int>(t - static_cast<long long>(jj) * w);
+        dst[idx(dpitch, di0 + ii, dj0 + jj)] = src[idx(spitch, si0 + ii, sj0 + jj)];
+    }
+}
+
+cudaError_t copy_patch(double *f, int pitch, Box src, Box dst, double *scratch, cudaStream_t s)
+{
+    const int w = src.xe - src.xs + 1, h = src.ye - src.ys + 1;
+    if (w <= 0 || h <= 0) return cudaSuccess;
+    const long long n = static_cast<long long>(w) * h;
+    const unsigned blocks = n / 256 + 1 < kSMs * 8 ? static_cast<unsigned>(n / 256 + 1) : kSMs * 8;
+    const bool overlap = !(src.xe < dst.xs || dst.xs + w - 1 < src.xs || src.ye < dst.ys ||
+                           dst.ys + h - 1 < src.ys);
+    if (overlap) {
+        if (!scratch) return cudaErrorInvalidValue;
+        patch_kernel<<<blocks, 256, 0, s>>>(f, pitch, src.xs, src.ys, scratch, w, 1, 1, w, h);
+        patch_kernel<<<blocks, 256, 0, s>>>(scratch, w, 1, 1, f, pitch, dst.xs, dst.ys, w, h);
+        count_launch();
+    } else {
+        patch_kernel<<<blocks, 256, 0, s>>>(f, pitch, src.xs, src.ys, f, pitch, dst.xs, dst.ys, w, h);
+    }
+    count_launch();
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------
+// field_checksum (src/field_mod.f90:1289-1302): SUM(ABS(f(box))).  8 B/point.
+// Deterministic two-pass tree: pass 1 gives every block a fixed set of rows, four
+// accumulators per thread, warp-shuffle then shared-memory tree; pass 2 folds the
+// kChecksumBlocks partials in a fixed order.  No floating-point atomics, so the result does
+// not depend on scheduling.
+// ---------------------------------------------------------------------------------------
+__device__ inline double warp_sum(double v)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+__device__ inline double block_sum_256(double v)
+{
+    __shared__ double sh[8];
+    v = warp_sum(v);
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    if (lane == 0) sh[wid] = v;
+    __syncthreads();
+    double r = 0.0;
+    if (wid == 0) {
+        r = lane < 8 ? sh[lane] : 0.0;
+        r = warp_sum(r);
+    }
+    return r;  // valid in warp 0
+}
+
+__global__ void __launch_bounds__(256) abs_sum_rows_kernel(const double *__restrict__ f, int pitch,
+                                                           Box b, double *__restrict__ partials)
+{
+    const int w = b.xe - b.xs + 1;
+    double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+    for (int j = b.ys + blockIdx.x; j <= b.ye; j += gridDim.x) {
+        const double *row = f + idx(pitch, b.xs, j);
+        int i = threadIdx.x;
+        for (; i + 768 < w; i += 1024) {
+            const double v0 = __ldcs(row + i), v1 = __ldcs(row + i + 256);
+            const double v2 = __ldcs(row + i + 512), v3 = __ldcs(row + i + 768);
+            a0 += fabs(v0); a1 += fabs(v1); a2 += fabs(v2); a3 += fabs(v3);
+        }
+        for (; i < w; i += 256) a0 += fabs(__ldcs(row + i));
+    }
+    const double r = block_sum_256((a0 + a1) + (a2 + a3));
+    if (threadIdx.x == 0) partials[blockIdx.x] = r;
+}
+
+__global__ void __launch_bounds__(256) fold_partials_kernel(const double *__restrict__ partials,
+                                                            int n, double *__restrict__ result)
+{
+    double a = 0.0;
+    for (int t = threadIdx.x; t < n; t += 256) a += partials[t];
+    const double r = block_sum_256(a);
+    if (threadIdx.x == 0) *result = r;
+}
+
+cudaError_t checksum(const double *f, int pitch, Box b, double *partials, double *result,
+                     cudaStream_t s)
+{
+    if (b.xe < b.xs || b.ye < b.ys) return cudaMemsetAsync(result, 0, sizeof(double), s);
+    abs_sum_rows_kernel<<<kChecksumBlocks, 256, 0, s>>>(f, pitch, b, partials);
+    fold_partials_kernel<<<1, 256, 0, s>>>(partials, kChecksumBlocks, result);
+    count_launch();
+    count_launch();
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------
+// Periodic halo fill: the copy_field(fld, halo%source, halo%dest) sequence of SURVEY CS-6
+// (E, W columns, then N, S rows over xstart-1:xstop+1) for up to 8 fields in one launch.
+// Every destination reads its final source directly (the N/S rows take the wrapped
+// column for their two end cells), so there is no ordering between the four strips and
+// the bits equal those of the sequential list.
+// ---------------------------------------------------------------------------------------
+struct HaloArgs {
+    double *f[kMaxExchangeFields];
+    int nfields, pitch;
+    Box in;
+    int px, py;
+};
+
+__global__ void __launch_bounds__(256) periodic_halo_kernel(HaloArgs a)
+{
+    const int w = a.in.xe - a.in.xs + 1, h = a.in.ye - a.in.ys + 1;
+    const int ncol = a.px ? 2 * h : 0;          // E then W column cells
+    const int nrow = a.py ? 2 * (w + 2) : 0;    // N then S row cells
+    const int per_field = ncol + nrow;
+    const long long total = static_cast<long long>(per_field) * a.nfields;
+    for (long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; t < total;
+         t += static_cast<long long>(gridDim.x) * blockDim.x) {
+        const int kf = static_cast<int>(t / per_field);
+        int c = static_cast<int>(t - static_cast<long long>(kf) * per_field);
+        int di, dj, si, sj;
+        if (c < ncol) {
+            const bool east = c < h;
+            const int jj = east ? c : c - h;
+            dj = sj = a.in.ys + jj;
+            di = east ? a.in.xe + 1 : a.in.xs - 1;
+            si = east ? a.in.xs : a.in.xe;
+        } else {
+            c -= ncol;
+            const bool north = c < w + 2;
+            const int ii = north ? c : c - (w + 2);
+            di = a.in.xs - 1 + ii;
+            dj = north ? a.in.ye + 1 : a.in.ys - 1;
+            sj = north ? a.in.ys : a.in.ye;
+            si = di;
+            if (a.px) {  // the end cells were themselves filled by the E/W copies
+                if (di == a.in.xs - 1) si = a.in.xe;
+                if (di == a.in.xe + 1) si = a.in.xs;
+            }
+        }
+        double *f = a.f[kf];
+        f[idx(a.pitch, di, dj)] = f[idx(a.pitch, si, sj)];
+    }
+}
+
+cudaError_t periodic_halos(double *const *fields, int nfields, int pitch, Box in, bool px, bool py,
+                           cudaStream_t s)
+{
+    if (nfields <= 0 || (!px && !py)) return cudaSuccess;
+    if (nfields > kMaxExchangeFields) return cudaErrorInvalidValue;
+    HaloArgs a;
+    for (int q = 0; q < nfields; ++q) a.f[q] = fields[q];
+    a.nfields = nfields; a.pitch = pitch; a.in = in; a.px = px; a.py = py;
+    const long long total = static_cast<long long>(nfields) *
+                            ((px ? 2LL * (in.ye - in.ys + 1) : 0) + (py ? 2LL * (in.xe - in.xs + 3) : 0));
+    const unsigned blocks = total / 256 + 1 < kSMs * 4 ? static_cast<unsigned>(total / 256 + 1) : kSMs * 4;
+    periodic_halo_kernel<<<blocks, 256, 0, s>>>(a);
+    count_launch();
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------
+// Halo pack / unpack (src/parallel_comms_mod.f90:1678-1683, 1788-1793): every patch of every
+// field in one launch; within a patch j is the outer and i the inner index, as the
+// reference packs.  blockIdx.y = segment * nfields + field.
+// ---------------------------------------------------------------------------------------
+template <bool kPack>
+__global__ void __launch_bounds__(256) pack_kernel(PackPlan plan, double *__restrict__ buffer)
+{
+    const int sidx = blockIdx.y / plan.nfields, kf = blockIdx.y - sidx * plan.nfields;
+    const Segment sg = plan.seg[sidx];
+    const long long n = static_cast<long long>(sg.nx) * sg.ny;
+    double *buf = buffer + sg.offset + static_cast<long long>(kf) * n;
+    double *f = plan.fields[kf];
+    for (long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; t < n;
+         t += static_cast<long long>(gridDim.x) * blockDim.x) {
+        const int jj = static_cast<int>(t / sg.nx), ii = static_cast<int>(t - static_cast<long long>(jj) * sg.nx);
+        const size_t q = idx(plan.pitch, sg.i0 + ii, sg.j0 + jj);
+        if (kPack) buf[t] = f[q];
+        else f[q] = buf[t];
+    }
+}
+
+static cudaError_t pack_launch(const PackPlan &plan, double *buffer, bool do_pack, cudaStream_t s)
+{
+    if (plan.nseg <= 0 || plan.nfields <= 0) return cudaSuccess;
+    long long nmax = 1;
+    for (int q = 0; q < plan.nseg; ++q) {
+        const long long n = static_cast<long long>(plan.seg[q].nx) * plan.seg[q].ny;
+        if (n > nmax) nmax = n;
+    }
+    dim3 grid(nmax / 256 + 1 < 64 ? static_cast<unsigned>(nmax / 256 + 1) : 64u,
+              static_cast<unsigned>(plan.nseg * plan.nfields));
+    if (do_pack) pack_kernel<true><<<grid, 256, 0, s>>>(plan, buffer);
+    else pack_kernel<false><<<grid, 256, 0, s>>>(plan, buffer);
+    count_launch();
+    return cudaGetLastError();
+}
+cudaError_t pack(const PackPlan &plan, double *buffer, cudaStream_t s) { return pack_launch(plan, buffer, true, s); }
+cudaError_t unpack(const PackPlan &plan, const double *buffer, cudaStream_t s)
+{
+    return pack_launch(plan, const_cast<double *>(buffer), false, s);
+}
+
+// ---------------------------------------------------------------------------------------
+// grid metrics: broadcast a 1-D coordinate vector over the 2-D array (xt(ji,:) / yt(:,jj))
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) broadcast_kernel(double *__restrict__ out, int nx, int ny,
+                                                        const double *__restrict__ vec, int along_y)
+{
+    const size_t n = static_cast<size_t>(nx) * ny;
+    for (size_t t = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; t < n;
+         t += static_cast<size_t>(gridDim.x) * blockDim.x) {
+        const size_t j = t / nx, i = t - j * nx;
+        out[t] = vec[along_y ? j : i];
+    }
+}
+cudaError_t broadcast_x(double *out, int nx, int ny, const double *xvec, cudaStream_t s)
+{
+    broadcast_kernel<<<kSMs * 8, 256, 0, s>>>(out, nx, ny, xvec, 0);
+    count_launch();
+    return cudaGetLastError();
+}
+cudaError_t broadcast_y(double *out, int nx, int ny, const double *yvec, cudaStream_t s)
+{
+    broadcast_kernel<<<kSMs * 8, 256, 0, s>>>(out, nx, ny, yvec, 1);
+    count_launch();
+    return cudaGetLastError();
+}
+
+// r2d_field(init_global_data=...) scatter (src/field_mod.f90:378-389) from a device copy of
+// the replicated global array
+__global__ void __launch_bounds__(256) scatter_kernel(double *__restrict__ f, int pitch, Box b,
+                                                      const double *__restrict__ g, int gnx, int dx, int dy)
+{
+    const int w = b.xe - b.xs + 1, h = b.ye - b.ys + 1;
+    const long long n = static_cast<long long>(w) * h;
+    for (long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; t < n;
+         t += static_cast<long long>(gridDim.x) * blockDim.x) {
+        const int jj = static_cast<int>(t / w), ii = static_cast<int>(t - static_cast<long long>(jj) * w);
+        const int i = b.xs + ii, j = b.ys + jj;
+        f[idx(pitch, i, j)] = g[idx(gnx, i + dx, j + dy)];
+    }
+}
+cudaError_t scatter_global(double *f, int pitch, Box b, const double *g, int gnx, int dx, int dy,
+                           cudaStream_t s)
+{
+    if (b.xe < b.xs || b.ye < b.ys) return cudaSuccess;
+    scatter_kernel<<<kSMs * 4, 256, 0, s>>>(f, pitch, b, g, gnx, dx, dy);
+    count_launch();
+    return cudaGetLastError();
+}
+// gather_inner_data pack (src/field_mod.f90:1361-1368): box -> contiguous, i fastest
+cudaError_t gather_box(const double *f, int pitch, Box b, double *packed, cudaStream_t s)
+{
+    const int w = b.xe - b.xs + 1, h = b.ye - b.ys + 1;
+    if (w <= 0 || h <= 0) return cudaSuccess;
+    patch_kernel<<<kSMs * 4, 256, 0, s>>>(f, pitch, b.xs, b.ys, packed, w, 1, 1, w, h);
+    count_launch();
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------
+// Un-fused shallow-water sweeps.  One launch per reference-style kernel; the loop nest of
+// SURVEY CS-3 (jj outer, ji inner over the output field's internal region) becomes a 2-D
+// grid with i along threadIdx.x; the per-point functor is the "kernel code".
+// Formulas: SURVEY.md a-S, identical expression trees to oracle/dlesm_oracle_sw.c.
+// ---------------------------------------------------------------------------------------
+constexpr int kSweepRows = 4;
+
+template <class Op>
+__global__ void __launch_bounds__(256) sweep_kernel(Op op, Box b)
+{
+    const int i = b.xs + blockIdx.x * 256 + threadIdx.x;
+    if (i > b.xe) return;
+    const int j0 = b.ys + blockIdx.y * kSweepRows;
+#pragma unroll
+    for (int r = 0; r < kSweepRows; ++r) {
+        const int j = j0 + r;
+        if (j <= b.ye) op(i, j);
+    }
+}
+
+template <class Op>
+static cudaError_t sweep(const Op &op, Box b, cudaStream_t s)
+{
+    if (b.xe < b.xs || b.ye < b.ys) return cudaSuccess;
+    dim3 grid(cdiv(b.xe - b.xs + 1, 256), cdiv(b.ye - b.ys + 1, kSweepRows));
+    sweep_kernel<Op><<<grid, 256, 0, s>>>(op, b);
+    count_launch();
+    return cudaGetLastError();
+}
+
+struct Mask {
+    const int *t;
+    int pitch;
+    __device__ bool at(int i, int j) const { return t[idx(pitch, i, j)] == 1; }
+    __device__ bool wet_t(int i, int j) const { return !t || at(i, j); }
+    __device__ bool wet_u(int i, int j) const { return !t || (at(i, j) && at(i - 1, j)); }
+    __device__ bool wet_v(int i, int j) const { return !t || (at(i, j) && at(i, j - 1)); }
+    __device__ bool wet_f(int i, int j) const
+    {
+        return !t || (at(i, j) && at(i - 1, j) && at(i, j - 1) && at(i - 1, j - 1));
+    }
+};
+
+struct CuOp {
+    double *cu; const double *p, *u; int n; Mask m;
+    __device__ void operator()(int i, int j) const
+    {
+        const size_t q = idx(n, i, j);
+        cu[q] = m.wet_u(i, j) ? 0.5 * (p[q] + p[q - 1]) * u[q] : 0.0;
+    }
+};
+struct CvOp {
+    double *cv; const double *p, *v; int n; Mask m;
+    __device__ void operator()(int i, int j) const
+    {
+        const size_t q = idx(n, i, j);
+        cv[q] = m.wet_v(i, j) ? 0.5 * (p[q] + p[q - n]) * v[q] : 0.0;
+    }
+};
+struct ZOp {
+    double *z; const double *p, *u, *v; int n; double fsdx, fsdy; Mask m;
+    __device__ void operator()(int i, int j) const
+    {
+        const size_t q = idx(n, i, j);
+        z[q] = m.wet_f(i, j) ? (fsdx * (v[q] - v[q - 1]) - fsdy * (u[q] - u[q - n])) /
+                                   (p[q - n - 1] + p[q - n] + p[q] + p[q - 1])
+                             : 0.0;
+    }
+};
+struct HOp {
+    double *h; const double *p, *u, *v; int n; Mask m;
+    __device__ void operator()(int i, int j) const
+    {
+        const size_t q = idx(n, i, j);
+        h[q] = m.wet_t(i, j) ? p[q] + 0.25 * (u[q + 1] * u[q + 1] + u[q] * u[q] + v[q + n] * v[q + n] + v[q] * v[q])
+                             : 0.0;
+    }
+};
+struct UnewOp {
+    double *unew; const double *uold, *z, *cv, *h, *ucur; int n; double tdts8, tdtsdx; Mask m;
+    __device__ void operator()(int i, int j) const
+    {
+        const size_t q = idx(n, i, j);
+        unew[q] = m.wet_u(i, j)
+                      ? uold[q] + tdts8 * (z[q + n] + z[q]) * (cv[q + n] + cv[q + n - 1] + cv[q - 1] + cv[q]) -
+                            tdtsdx * (h[q] - h[q - 1])
+                      : ucur[q];
+    }
+};
+struct VnewOp {
+    double *vnew; const double *vold, *z, *cu, *h, *vcur; int n; double tdts8, tdtsdy; Mask m;
+    __device__ void operator()(int i, int j) const
+    {
+        const size_t q = idx(n, i, j);
+        vnew[q] = m.wet_v(i, j)
+                      ? vold[q] - tdts8 * (z[q + 1] + z[q]) * (cu[q + 1] + cu[q] + cu[q - n] + cu[q - n + 1]) -
+                            tdtsdy * (h[q] - h[q - n])
+                      : vcur[q];
+    }
+};
+struct PnewOp {
+    double *pnew; const double *pold, *cu, *cv, *pcur; int n; double tdtsdx, tdtsdy; Mask m;
+    __device__ void operator()(int i, int j) const
+    {
+        const size_t q = idx(n, i, j);
+        pnew[q] = m.wet_t(i, j) ? pold[q] - tdtsdx * (cu[q + 1] - cu[q]) - tdtsdy * (cv[q + n] - cv[q])
+                                : pcur[q];
+    }
+};
+struct SmoothOp {
+    const double *f, *fnew; double *fold; int n; double alpha; Mask m; int points;
+    __device__ void operator()(int i, int j) const
+    {
+        const bool wet = points == 0 ? m.wet_u(i, j) : points == 1 ? m.wet_v(i, j) : m.wet_t(i, j);
+        if (!wet) return;
+        const size_t q = idx(n, i, j);
+        fold[q] = f[q] + alpha * (fnew[q] - 2.0 * f[q] + fold[q]);
+    }
+};
+
+cudaError_t compute_cu(double *cu, const double *p, const double *u, int n, Box b, const int *t, cudaStream_t s)
+{
+    return sweep(CuOp{cu, p, u, n, Mask{t, n}}, b, s);
+}
+cudaError_t compute_cv(double *cv, const double *p, const double *v, int n, Box b, const int *t, cudaStream_t s)
+{
+    return sweep(CvOp{cv, p, v, n, Mask{t, n}}, b, s);
+}
+cudaError_t compute_z(double *z, const double *p, const double *u, const double *v, int n, Box b,
+                      double fsdx, double fsdy, const int *t, cudaStream_t s)
+{
+    return sweep(ZOp{z, p, u, v, n, fsdx, fsdy, Mask{t, n}}, b, s);
+}
+cudaError_t compute_h(double *h, const double *p, const double *u, const double *v, int n, Box b,
+                      const int *t, cudaStream_t s)
+{
+    return sweep(HOp{h, p, u, v, n, Mask{t, n}}, b, s);
+}
+cudaError_t compute_unew(double *unew, const double *uold, const double *z, const double *cv,
+                         const double *h, int n, Box b, double tdts8, double tdtsdx, const int *t,
+                         const double *ucur, cudaStream_t s)
+{
+    return sweep(UnewOp{unew, uold, z, cv, h, ucur, n, tdts8, tdtsdx, Mask{t, n}}, b, s);
+}
+cudaError_t compute_vnew(double *vnew, const double *vold, const double *z, const double *cu,
+                         const double *h, int n, Box b, double tdts8, double tdtsdy, const int *t,
+                         const double *vcur, cudaStream_t s)
+{
+    return sweep(VnewOp{vnew, vold, z, cu, h, vcur, n, tdts8, tdtsdy, Mask{t, n}}, b, s);
+}
+cudaError_t compute_pnew(double *pnew, const double *pold, const double *cu, const double *cv, int n,
+                         Box b, double tdtsdx, double tdtsdy, const int *t, const double *pcur,
+                         cudaStream_t s)
+{
+    return sweep(PnewOp{pnew, pold, cu, cv, pcur, n, tdtsdx, tdtsdy, Mask{t, n}}, b, s);
+}
+cudaError_t time_smooth(const double *f, const double *fnew, double *fold, int n, Box b, double alpha,
+                        const int *t, int points, cudaStream_t s)
+{
+    return sweep(SmoothOp{f, fnew, fold, n, alpha, Mask{t, n}, points}, b, s);
+}
+
+// ---------------------------------------------------------------------------------------
+// synthetic initial conditions (classic "shallow"), device sin/cos
+// ---------------------------------------------------------------------------------------
+struct InitOp {
+    double *u, *v, *p; int n; Box b; int gx0, gy0, M, N; double dx, dy;
+    __device__ void operator()(int i, int j) const
+    {
+        const double a = 1.0e6, pi = 3.14159265358979323846;
+        const double di = 2.0 * pi / static_cast<double>(M), dj = 2.0 * pi / static_cast<double>(N);
+        const double el = static_cast<double>(N) * dx;
+        const double pcf = pi * pi * a * a / (el * el);
+        const int gi = gx0 + (i - b.xs), gj = gy0 + (j - b.ys);
+        const double s_i = sin((gi - 0.5) * di), s_i1 = sin((gi + 0.5) * di);
+        const double s_j = sin((gj - 0.5) * dj), s_j1 = sin((gj + 0.5) * dj);
+        const double psi_ij = a * s_i * s_j, psi_ij1 = a * s_i * s_j1, psi_i1j = a * s_i1 * s_j;
+        const size_t q = idx(n, i, j);
+        p[q] = pcf * (cos(2.0 * (gi - 1.0) * di) + cos(2.0 * (gj - 1.0) * dj)) + 50000.0;
+        u[q] = -(psi_ij1 - psi_ij) / dy;
+        v[q] = (psi_i1j - psi_ij) / dx;
+    }
+};
+cudaError_t sw_init(double *u, double *v, double *p, int n, Box b, int gx0, int gy0, int M, int N,
+                    double dx, double dy, cudaStream_t s)
+{
+    return sweep(InitOp{u, v, p, n, b, gx0, gy0, M, N, dx, dy}, b, s);
+}
+
+}  // namespace k
+}  // namespace dlesm

@@ -1,0 +1,101 @@
+// dlesm_kernels.cuh -- launchers of the hand-written sm_100a kernels (FP64, HBM-bound).
+// All fields are column-major (i fastest) with pitch = grid%nx; boxes are 1-based inclusive.
+#pragma once
+
+#include <cuda_runtime.h>
+
+#include <cstddef>
+
+namespace dlesm {
+namespace k {
+
+struct Box {
+    int xs, xe, ys, ye;
+};
+
+constexpr int kMaxExchangeFields = 8;
+constexpr int kMaxSegments = 16;
+
+// one rectangular patch of every field <-> one contiguous slice of a message buffer
+struct Segment {
+    int i0, j0;          // 1-based start in the field
+    int nx, ny;          // extent
+    long long offset;    // element offset of this segment's first field in the buffer
+};
+struct PackPlan {
+    int nseg;
+    int nfields;
+    int pitch;
+    Segment seg[kMaxSegments];
+    double *fields[kMaxExchangeFields];
+};
+
+struct SwScalars {
+    double fsdx, fsdy;       // 4/dx, 4/dy
+    double tdts8, tdtsdx, tdtsdy;
+    double alpha;
+    int first;               // 1 => no time filter
+};
+
+// ---- field_mod operations ----
+cudaError_t copy_field(const double *in, double *out, size_t n, cudaStream_t s);
+cudaError_t set_field(double *f, size_t n, double val, cudaStream_t s);
+cudaError_t copy_patch(double *f, int pitch, Box src, Box dst, double *scratch, cudaStream_t s);
+// partials: >= kChecksumBlocks doubles of scratch; result: 1 double (device)
+constexpr int kChecksumBlocks = 1184;  // 148 SMs x 8
+cudaError_t checksum(const double *f, int pitch, Box b, double *partials, double *result,
+                     cudaStream_t s);
+cudaError_t periodic_halos(double *const *fields, int nfields, int pitch, Box internal,
+                           bool periodic_x, bool periodic_y, cudaStream_t s);
+cudaError_t pack(const PackPlan &plan, double *buffer, cudaStream_t s);
+cudaError_t unpack(const PackPlan &plan, const double *buffer, cudaStream_t s);
+cudaError_t broadcast_x(double *out, int nx, int ny, const double *xvec, cudaStream_t s);
+cudaError_t broadcast_y(double *out, int nx, int ny, const double *yvec, cudaStream_t s);
+cudaError_t scatter_global(double *f, int pitch, Box box, const double *global, int gnx, int dx,
+                           int dy, cudaStream_t s);
+cudaError_t gather_box(const double *f, int pitch, Box box, double *packed, cudaStream_t s);
+
+// ---- shallow-water sweeps, un-fused (one launch per reference-style kernel) ----
+cudaError_t compute_cu(double *cu, const double *p, const double *u, int pitch, Box b,
+                       const int *tmask, cudaStream_t s);
+cudaError_t compute_cv(double *cv, const double *p, const double *v, int pitch, Box b,
+                       const int *tmask, cudaStream_t s);
+cudaError_t compute_z(double *z, const double *p, const double *u, const double *v, int pitch,
+                      Box b, double fsdx, double fsdy, const int *tmask, cudaStream_t s);
+cudaError_t compute_h(double *h, const double *p, const double *u, const double *v, int pitch,
+                      Box b, const int *tmask, cudaStream_t s);
+cudaError_t compute_unew(double *unew, const double *uold, const double *z, const double *cv,
+                         const double *h, int pitch, Box b, double tdts8, double tdtsdx,
+                         const int *tmask, const double *ucur, cudaStream_t s);
+cudaError_t compute_vnew(double *vnew, const double *vold, const double *z, const double *cu,
+                         const double *h, int pitch, Box b, double tdts8, double tdtsdy,
+                         const int *tmask, const double *vcur, cudaStream_t s);
+cudaError_t compute_pnew(double *pnew, const double *pold, const double *cu, const double *cv,
+                         int pitch, Box b, double tdtsdx, double tdtsdy, const int *tmask,
+                         const double *pcur, cudaStream_t s);
+cudaError_t time_smooth(const double *f, const double *fnew, double *fold, int pitch, Box b,
+                        double alpha, const int *tmask, int points, cudaStream_t s);
+
+// ---- the fused step ----
+struct FusedArgs {
+    const double *u, *v, *p;
+    double *uold, *vold, *pold;
+    double *unew, *vnew, *pnew;
+    const int *tmask;   // may be null
+    int pitch, ny;
+    Box b;              // internal region (identical for U,V,T,F under SW periodic)
+    SwScalars sc;
+};
+constexpr int kNumFusedVariants = 6;
+cudaError_t sw_step_fused(const FusedArgs &a, int variant, cudaStream_t s);
+const char *fused_variant_name(int variant);
+
+// classic initial conditions, synthetic (device sin/cos)
+cudaError_t sw_init(double *u, double *v, double *p, int pitch, Box b, int gx0, int gy0, int M,
+                    int N, double dx, double dy, cudaStream_t s);
+
+long long launch_count();
+void note_launch(int n = 1);
+
+}  // namespace k
+}  // namespace dlesm

@@ -1,0 +1,1519 @@
+// dlesm_runtime.cu -- runtime context (device, stream, scratch, NCCL communicator, field
+// registry) and the C ABI of include/dlesm_b200.h.  There is no CPU fallback anywhere in
+// this file: a device entry point either runs its CUDA kernel or fails with DLESM_ERR_CUDA.
+#include <cuda_runtime.h>
+#include <nccl.h>
+
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "../../include/dlesm_b200.h"
+#include "dlesm_host.hpp"
+#include "dlesm_kernels.cuh"
+
+using namespace dlesm;
+
+// =========================================================================================
+// context
+// =========================================================================================
+namespace {
+
+struct FieldRec {
+    int nx, ny;
+};
+
+struct PeerGroup {
+    int peer0;                 // 0-based rank; == my rank for self messages
+    std::vector<int> sends;    // indices into comms lists, ordered by direction tag
+    std::vector<int> recvs;
+    long long send_off = 0, recv_off = 0;  // element offsets for ONE field
+    long long send_n = 0, recv_n = 0;
+};
+
+struct Context {
+    std::mutex mu;
+    bool device_ready = false;
+    int device = -1;
+    cudaStream_t stream = nullptr;
+    double *partials = nullptr;   // checksum partials + result
+    double *result = nullptr;
+    double *host_result = nullptr;  // pinned
+    double *scratch = nullptr;      // patch scratch
+    size_t scratch_n = 0;
+    double *sendbuf = nullptr, *recvbuf = nullptr;
+    size_t xbuf_n = 0;
+    std::unordered_map<const void *, FieldRec> registry;
+    // communication
+    bool comm_ready = false;
+    ncclComm_t comm = nullptr;
+    bool have_comms = false;
+    dlesm_comms comms{};
+    std::vector<PeerGroup> groups;
+    long long send_total = 0, recv_total = 0;  // per field
+    // profiling of the dominant kernel
+    bool profile = false;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events;
+    size_t prof_used = 0;
+};
+
+Context &ctx()
+{
+    static Context c;
+    return c;
+}
+
+int fail_cuda(cudaError_t e, const char *what)
+{
+    set_error(DLESM_ERR_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
+    return DLESM_ERR_CUDA;
+}
+int fail_nccl(ncclResult_t r, const char *what)
+{
+    set_error(DLESM_ERR_NCCL, std::string(what) + ": " + ncclGetErrorString(r));
+    return DLESM_ERR_NCCL;
+}
+#define CU(call)                                               \
+    do {                                                       \
+        cudaError_t e_ = (call);                               \
+        if (e_ != cudaSuccess) return fail_cuda(e_, #call);    \
+    } while (0)
+#define NC(call)                                               \
+    do {                                                       \
+        ncclResult_t r_ = (call);                              \
+        if (r_ != ncclSuccess) return fail_nccl(r_, #call);    \
+    } while (0)
+
+int ensure_device()
+{
+    Context &c = ctx();
+    if (c.device_ready) return DLESM_OK;
+    return dlesm_device_init(-1);
+}
+
+int lookup(const void *p, FieldRec &out)
+{
+    Context &c = ctx();
+    std::lock_guard<std::mutex> lock(c.mu);
+    auto it = c.registry.find(p);
+    if (it == c.registry.end()) {
+        set_error(DLESM_ERR_UNKNOWN_PTR, "device pointer was not allocated by dlesm_dev_field_alloc");
+        return DLESM_ERR_UNKNOWN_PTR;
+    }
+    out = it->second;
+    return DLESM_OK;
+}
+
+int ensure_scratch(size_t n)
+{
+    Context &c = ctx();
+    if (c.scratch_n >= n) return DLESM_OK;
+    if (c.scratch) cudaFree(c.scratch);
+    c.scratch = nullptr;
+    c.scratch_n = 0;
+    CU(cudaMalloc(&c.scratch, n * sizeof(double)));
+    c.scratch_n = n;
+    return DLESM_OK;
+}
+
+int ensure_xbuf(size_t n)
+{
+    Context &c = ctx();
+    if (c.xbuf_n >= n) return DLESM_OK;
+    if (c.sendbuf) cudaFree(c.sendbuf);
+    if (c.recvbuf) cudaFree(c.recvbuf);
+    c.sendbuf = c.recvbuf = nullptr;
+    c.xbuf_n = 0;
+    CU(cudaMalloc(&c.sendbuf, n * sizeof(double)));
+    CU(cudaMalloc(&c.recvbuf, n * sizeof(double)));
+    c.xbuf_n = n;
+    return DLESM_OK;
+}
+
+k::Box box_of(const dlesm_region &r) { return k::Box{r.xstart, r.xstop, r.ystart, r.ystop}; }
+
+}  // namespace
+
+// =========================================================================================
+// errors, lifecycle
+// =========================================================================================
+extern "C" const char *dlesm_last_error(void) { return last_error_cstr(); }
+extern "C" int dlesm_last_status(void) { return last_status(); }
+extern "C" const char *dlesm_version(void) { return "dlesm_b200 0.1 (sm_100a, FP64, fmad=false)"; }
+
+extern "C" int dlesm_parallel_init(int rank1, int nranks)
+{
+    if (nranks < 1 || rank1 < 1 || rank1 > nranks) {
+        set_error(DLESM_ERR_NRANKS, "dlesm_parallel_init: need 1 <= rank <= nranks");
+        return DLESM_ERR_NRANKS;
+    }
+    pstate().rank = rank1;
+    pstate().nranks = nranks;
+    return DLESM_OK;
+}
+
+extern "C" int dlesm_device_init(int device)
+{
+    Context &c = ctx();
+    if (c.device_ready && (device < 0 || device == c.device)) return DLESM_OK;
+    if (c.device_ready) {
+        set_error(DLESM_ERR_STATE, "dlesm_device_init: already bound to another device");
+        return DLESM_ERR_STATE;
+    }
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0) {
+        set_error(DLESM_ERR_CUDA, std::string("no usable CUDA device (") +
+                                      (e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0") +
+                                      "); this library has no CPU fallback");
+        return DLESM_ERR_CUDA;
+    }
+    if (device < 0) {
+        const char *lr = std::getenv("LOCAL_RANK");
+        device = lr ? std::atoi(lr) % count : 0;
+    }
+    CU(cudaSetDevice(device));
+    CU(cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
+    CU(cudaMalloc(&c.partials, (k::kChecksumBlocks + 8) * sizeof(double)));
+    c.result = c.partials + k::kChecksumBlocks;
+    CU(cudaMallocHost(&c.host_result, 8 * sizeof(double)));
+    c.device = device;
+    c.device_ready = true;
+    return DLESM_OK;
+}
+
+extern "C" int dlesm_comm_unique_id(void *id128)
+{
+    static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is expected to be 128 bytes");
+    ncclUniqueId id;
+    NC(ncclGetUniqueId(&id));
+    std::memcpy(id128, &id, sizeof(id));
+    return DLESM_OK;
+}
+
+extern "C" int dlesm_comm_init(const void *id128)
+{
+    Context &c = ctx();
+    if (c.comm_ready) return DLESM_OK;
+    int rc = ensure_device();
+    if (rc != DLESM_OK) return rc;
+    ncclUniqueId id;
+    std::memcpy(&id, id128, sizeof(id));
+    NC(ncclCommInitRank(&c.comm, pstate().nranks, id, pstate().rank - 1));
+    c.comm_ready = true;
+    return DLESM_OK;
+}
+
+extern "C" int dlesm_parallel_finalise(void)
+{
+    Context &c = ctx();
+    if (c.device_ready) cudaStreamSynchronize(c.stream);
+    if (c.comm_ready) {
+        ncclCommDestroy(c.comm);
+        c.comm = nullptr;
+        c.comm_ready = false;
+    }
+    return DLESM_OK;
+}
+
+extern "C" void dlesm_parallel_abort(const char *msg)
+{
+    std::fprintf(stderr, " %s\n", msg ? msg : "");
+    Context &c = ctx();
+    if (c.comm_ready) ncclCommAbort(c.comm);
+    std::exit(1);
+}
+
+extern "C" int dlesm_get_rank(void) { return pstate().rank; }
+extern "C" int dlesm_get_num_ranks(void) { return pstate().nranks; }
+extern "C" int dlesm_on_master(void) { return pstate().rank == 1; }
+extern "C" void dlesm_reset_saved_state(void) { reset_saved_state(); }
+extern "C" int dlesm_set_extensions(int flags)
+{
+    pstate().extensions = flags;
+    return DLESM_OK;
+}
+
+extern "C" int dlesm_global_sum(double *var)
+{
+    if (pstate().nranks == 1) return DLESM_OK;  // stub behaviour
+    Context &c = ctx();
+    if (!c.comm_ready) {
+        set_error(DLESM_ERR_STATE, "global_sum: communicator not initialised (dlesm_comm_init)");
+        return DLESM_ERR_STATE;
+    }
+    c.host_result[1] = *var;
+    CU(cudaMemcpyAsync(c.result + 1, c.host_result + 1, sizeof(double), cudaMemcpyHostToDevice, c.stream));
+    NC(ncclAllReduce(c.result + 1, c.result + 2, 1, ncclDouble, ncclSum, c.comm, c.stream));
+    CU(cudaMemcpyAsync(c.host_result + 2, c.result + 2, sizeof(double), cudaMemcpyDeviceToHost, c.stream));
+    CU(cudaStreamSynchronize(c.stream));
+    *var = c.host_result[2];
+    return DLESM_OK;
+}
+
+// =========================================================================================
+// decomposition / comm tables (host only)
+// =========================================================================================
+struct dlesm_decomp {
+    Decomposition d;
+};
+
+extern "C" dlesm_decomp_t *dlesm_go_decompose(int domainx, int domainy, int ndomains, int ndomainx,
+                                               int ndomainy, int halo_width)
+{
+    clear_error();
+    auto *h = new dlesm_decomp;
+    if (go_decompose(domainx, domainy, ndomains, ndomainx, ndomainy, halo_width, pstate().nranks, h->d) !=
+        DLESM_OK) {
+        delete h;
+        return nullptr;
+    }
+    return h;
+}
+extern "C" int dlesm_decomp_info(const dlesm_decomp_t *h, int info[8])
+{
+    const Decomposition &d = h->d;
+    const int v[8] = {d.global_nx, d.global_ny, d.nx, d.ny, d.ndomains, d.max_width, d.max_height, d.domperrank};
+    std::memcpy(info, v, sizeof(v));
+    return DLESM_OK;
+}
+extern "C" int dlesm_decomp_subdomain(const dlesm_decomp_t *h, int id1, dlesm_subdomain *out)
+{
+    if (id1 < 1 || id1 > h->d.ndomains) {
+        set_error(DLESM_ERR_ARGS, "subdomain index out of range");
+        return DLESM_ERR_ARGS;
+    }
+    *out = h->d.subdomains[id1 - 1];
+    return DLESM_OK;
+}
+extern "C" int dlesm_decomp_proc_subdomain(const dlesm_decomp_t *h, int islot1, int irank1)
+{
+    const Decomposition &d = h->d;
+    if (islot1 < 1 || islot1 > d.domperrank || irank1 < 1 || irank1 > d.nranks) return -1;
+    return d.proc_subdomains[static_cast<size_t>(irank1 - 1) * d.domperrank + (islot1 - 1)];
+}
+extern "C" void dlesm_decomp_free(dlesm_decomp_t *h) { delete h; }
+
+extern "C" int dlesm_map_comms(const dlesm_decomp_t *h, int irank1, int nranks, int pbc_x, int pbc_y,
+                               int hdx, int hdy, dlesm_comms *out)
+{
+    clear_error();
+    return build_comms(h->d, irank1, nranks, pbc_x != 0, pbc_y != 0, hdx, hdy, *out);
+}
+extern "C" int dlesm_iprocmap(const dlesm_decomp_t *h, int nranks, int ia, int ja)
+{
+    return owner_of(h->d, nranks, ia, ja);
+}
+
+// =========================================================================================
+// device layer: storage + hooks
+// =========================================================================================
+extern "C" int dlesm_dev_field_alloc(int nx, int ny, void **device_ptr)
+{
+    clear_error();
+    int rc = ensure_device();
+    if (rc != DLESM_OK) return rc;
+    if (nx < 1 || ny < 1) {
+        set_error(DLESM_ERR_ARGS, "dlesm_dev_field_alloc: extents must be positive");
+        return DLESM_ERR_ARGS;
+    }
+    Context &c = ctx();
+    void *p = nullptr;
+    const size_t bytes = static_cast<size_t>(nx) * ny * sizeof(double);
+    CU(cudaMalloc(&p, bytes));
+    cudaError_t e = cudaMemsetAsync(p, 0, bytes, c.stream);  // self%data(:,:) = 0 (field_mod.f90:375)
+    if (e != cudaSuccess) {
+        cudaFree(p);
+        return fail_cuda(e, "cudaMemsetAsync");
+    }
+    {
+        std::lock_guard<std::mutex> lock(c.mu);
+        c.registry[p] = FieldRec{nx, ny};
+    }
+    *device_ptr = p;
+    return DLESM_OK;
+}
+
+extern "C" int dlesm_dev_field_free(void *p)
+{
+    if (!p) return DLESM_OK;
+    Context &c = ctx();
+    {
+        std::lock_guard<std::mutex> lock(c.mu);
+        if (c.registry.erase(p) == 0) {
+            set_error(DLESM_ERR_UNKNOWN_PTR, "dlesm_dev_field_free: unknown pointer");
+            return DLESM_ERR_UNKNOWN_PTR;
+        }
+    }
+    CU(cudaStreamSynchronize(c.stream));
+    CU(cudaFree(p));
+    return DLESM_OK;
+}
+
+namespace {
+// shared by both hooks: 1-based sub-rectangle of the padded array, offset (j-1)*pitch+(i-1)
+int hook_copy(void *device, void *host, bool to_device, int startx, int starty, int nx, int ny, bool blocking)
+{
+    FieldRec r;
+    int rc = lookup(device, r);
+    if (rc != DLESM_OK) return rc;
+    if (startx < 1 || starty < 1 || nx < 0 || ny < 0 || startx + nx - 1 > r.nx || starty + ny - 1 > r.ny) {
+        set_error(DLESM_ERR_ARGS, "device hook: sub-rectangle outside the field allocation");
+        return DLESM_ERR_ARGS;
+    }
+    Context &c = ctx();
+    const size_t off = (static_cast<size_t>(starty) - 1) * r.nx + (static_cast<size_t>(startx) - 1);
+    double *d = static_cast<double *>(device) + off;
+    double *h = static_cast<double *>(host) + off;
+    const size_t pitch_b = static_cast<size_t>(r.nx) * sizeof(double);
+    if (nx > 0 && ny > 0) {
+        const cudaMemcpyKind kind = to_device ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToHost;
+        if (nx == r.nx)  // full rows: one contiguous transfer
+            CU(cudaMemcpyAsync(to_device ? d : h, to_device ? h : d, pitch_b * ny, kind, c.stream));
+        else
+            CU(cudaMemcpy2DAsync(to_device ? d : h, pitch_b, to_device ? h : d, pitch_b,
+                                 static_cast<size_t>(nx) * sizeof(double), ny, kind, c.stream));
+    }
+    if (blocking) CU(cudaStreamSynchronize(c.stream));
+    return DLESM_OK;
+}
+}  // namespace
+
+extern "C" void dlesm_read_from_device_c(void *from, void *to, int startx, int starty, int nx, int ny, bool blocking)
+{
+    if (hook_copy(from, to, false, startx, starty, nx, ny, blocking) != DLESM_OK)
+        dlesm_parallel_abort(dlesm_last_error());  // the hook signature has no status: fail loudly
+}
+extern "C" void dlesm_write_to_device_c(void *from, void *to, int startx, int starty, int nx, int ny, bool blocking)
+{
+    if (hook_copy(to, from, true, startx, starty, nx, ny, blocking) != DLESM_OK)
+        dlesm_parallel_abort(dlesm_last_error());
+}
+extern "C" int dlesm_dev_sync(void)
+{
+    int rc = ensure_device();
+    if (rc != DLESM_OK) return rc;
+    CU(cudaStreamSynchronize(ctx().stream));
+    return DLESM_OK;
+}
+
+extern "C" int dlesm_host_alloc(size_t bytes, void **host_ptr)
+{
+    int rc = ensure_device();
+    if (rc != DLESM_OK) return rc;
+    CU(cudaMallocHost(host_ptr, bytes));
+    return DLESM_OK;
+}
+extern "C" int dlesm_host_free(void *host_ptr)
+{
+    CU(cudaFreeHost(host_ptr));
+    return DLESM_OK;
+}
+extern "C" int dlesm_host_register(void *host_ptr, size_t bytes)
+{
+    int rc = ensure_device();
+    if (rc != DLESM_OK) return rc;
+    CU(cudaHostRegister(host_ptr, bytes, cudaHostRegisterDefault));
+    return DLESM_OK;
+}
+extern "C" int dlesm_host_unregister(void *host_ptr)
+{
+    CU(cudaHostUnregister(host_ptr));
+    return DLESM_OK;
+}
+
+namespace {
+cudaEvent_t g_events[16] = {nullptr};
+}
+extern "C" int dlesm_event_record(int slot)
+{
+    int rc = ensure_device();
+    if (rc != DLESM_OK) return rc;
+    if (slot < 0 || slot >= 16) {
+        set_error(DLESM_ERR_ARGS, "event slot out of range");
+        return DLESM_ERR_ARGS;
+    }
+    if (!g_events[slot]) CU(cudaEventCreate(&g_events[slot]));
+    CU(cudaEventRecord(g_events[slot], ctx().stream));
+    return DLESM_OK;
+}
+extern "C" int dlesm_event_elapsed_ms(int a, int b, double *ms)
+{
+    if (a < 0 || a >= 16 || b < 0 || b >= 16 || !g_events[a] || !g_events[b]) {
+        set_error(DLESM_ERR_ARGS, "event slot not recorded");
+        return DLESM_ERR_ARGS;
+    }
+    CU(cudaEventSynchronize(g_events[b]));
+    float f = 0.f;
+    CU(cudaEventElapsedTime(&f, g_events[a], g_events[b]));
+    *ms = f;
+    return DLESM_OK;
+}
+
+// =========================================================================================
+// device layer: field operations
+// =========================================================================================
+extern "C" int dlesm_dev_copy_field(const void *in, void *out)
+{
+    FieldRec a, b;
+    int rc = lookup(in, a);
+    if (rc == DLESM_OK) rc = lookup(out, b);
+    if (rc != DLESM_OK) return rc;
+    if (a.nx != b.nx || a.ny != b.ny) {
+        set_error(DLESM_ERR_ARGS, "copy_field: fields have different shapes");
+        return DLESM_ERR_ARGS;
+    }
+    CU(k::copy_field(static_cast<const double *>(in), static_cast<double *>(out),
+                     static_cast<size_t>(a.nx) * a.ny, ctx().stream));
+    return DLESM_OK;
+}
+
+extern "C" int dlesm_dev_copy_patch(void *f, int sxs, int sxe, int sys, int sye, int dxs, int dxe, int dys, int dye)
+{
+    FieldRec r;
+    int rc = lookup(f, r);
+    if (rc != DLESM_OK) return rc;
+    const int w = sxe - sxs + 1, h = sye - sys + 1;
+    if (w != dxe - dxs + 1 || h != dye - dys + 1) {
+        set_error(DLESM_ERR_ARGS, "copy_field: source and destination patches differ in shape");
+        return DLESM_ERR_ARGS;
+    }
+    if (w <= 0 || h <= 0) return DLESM_OK;
+    if (sxs < 1 || sys < 1 || dxs < 1 || dys < 1 || sxe > r.nx || dxe > r.nx || sye > r.ny || dye > r.ny) {
+        set_error(DLESM_ERR_ARGS, "copy_field: patch outside the field allocation");
+        return DLESM_ERR_ARGS;
+    }
+    rc = ensure_scratch(static_cast<size_t>(w) * h);
+    if (rc != DLESM_OK) return rc;
+    CU(k::copy_patch(static_cast<double *>(f), r.nx, k::Box{sxs, sxe, sys, sye}, k::Box{dxs, dxe, dys, dye},
+                     ctx().scratch, ctx().stream));
+    return DLESM_OK;
+}
+
+extern "C" int dlesm_dev_set_field(void *f, double val)
+{
+    FieldRec r;
+    int rc = lookup(f, r);
+    if (rc != DLESM_OK) return rc;
+    CU(k::set_field(static_cast<double *>(f), static_cast<size_t>(r.nx) * r.ny, val, ctx().stream));
+    return DLESM_OK;
+}
+
+extern "C" int dlesm_dev_checksum(const void *f, int xs, int xe, int ys, int ye, double *val)
+{
+    FieldRec r;
+    int rc = lookup(f, r);
+    if (rc != DLESM_OK) return rc;
+    if (xs < 1 || ys < 1 || xe > r.nx || ye > r.ny) {
+        set_error(DLESM_ERR_ARGS, "field_checksum: box outside the field allocation");
+        return DLESM_ERR_ARGS;
+    }
+    Context &c = ctx();
+    CU(k::checksum(static_cast<const double *>(f), r.nx, k::Box{xs, xe, ys, ye}, c.partials, c.result, c.stream));
+    CU(cudaMemcpyAsync(c.host_result, c.result, sizeof(double), cudaMemcpyDeviceToHost, c.stream));
+    CU(cudaStreamSynchronize(c.stream));
+    *val = c.host_result[0];
+    return DLESM_OK;
+}
+
+extern "C" int dlesm_dev_periodic_halos(void *f, int xs, int xe, int ys, int ye, int px, int py)
+{
+    FieldRec r;
+    int rc = lookup(f, r);
+    if (rc != DLESM_OK) return rc;
+    if (xs < 2 || ys < 2 || xe + 1 > r.nx || ye + 1 > r.ny) {
+        set_error(DLESM_ERR_ARGS, "periodic halos: internal region leaves no halo inside the allocation");
+        return DLESM_ERR_ARGS;
+    }
+    double *fl[1] = {static_cast<double *>(f)};
+    CU(k::periodic_halos(fl, 1, r.nx, k::Box{xs, xe, ys, ye}, px != 0, py != 0, ctx().stream));
+    return DLESM_OK;
+}
+
+// =========================================================================================
+// halo exchange
+// =========================================================================================
+extern "C" int dlesm_dev_set_comms(const dlesm_comms *t)
+{
+    Context &c = ctx();
+    c.comms = *t;
+    c.groups.clear();
+    const int me0 = pstate().rank - 1;
+    auto group_of = [&](int peer0) -> PeerGroup & {
+        for (auto &g : c.groups)
+            if (g.peer0 == peer0) return g;
+        c.groups.push_back(PeerGroup());
+        c.groups.back().peer0 = peer0;
+        return c.groups.back();
+    };
+    if (t->nsend > DLESM_MAXCOMM || t->nrecv > DLESM_MAXCOMM || t->nsend < 0 || t->nrecv < 0) {
+        set_error(DLESM_ERR_MAXCOMM, "set_comms: list longer than MaxComm");
+        return DLESM_ERR_MAXCOMM;
+    }
+    for (int s = 0; s < t->nsend; ++s)
+        if (t->destination[s] >= 0 && t->nxsend[s] > 0) group_of(t->destination[s]).sends.push_back(s);
+    for (int r = 0; r < t->nrecv; ++r)
+        if (t->source[r] >= 0 && t->nxrecv[r] > 0) group_of(t->source[r]).recvs.push_back(r);
+    std::sort(c.groups.begin(), c.groups.end(),
+              [](const PeerGroup &a, const PeerGroup &b) { return a.peer0 < b.peer0; });
+    // Between two ranks the reference matches messages by tag = direction
+    // (src/parallel_comms_mod.f90:1606,1647); NCCL has no tags, so both sides walk their
+    // messages for a peer in direction order and they travel as one buffer per peer.
+    long long so = 0, ro = 0;
+    for (auto &g : c.groups) {
+        std::sort(g.sends.begin(), g.sends.end(), [&](int a, int b) { return t->dirsend[a] < t->dirsend[b]; });
+        std::sort(g.recvs.begin(), g.recvs.end(), [&](int a, int b) { return t->dirrecv[a] < t->dirrecv[b]; });
+        g.send_off = so;
+        g.recv_off = ro;
+        g.send_n = g.recv_n = 0;
+        for (int s : g.sends) g.send_n += static_cast<long long>(t->nxsend[s]) * t->nysend[s];
+        for (int r : g.recvs) g.recv_n += static_cast<long long>(t->nxrecv[r]) * t->nyrecv[r];
+        if (g.peer0 == me0 && g.send_n != g.recv_n) {
+            set_error(DLESM_ERR_ARGS, "set_comms: self-messages do not pair up");
+            return DLESM_ERR_ARGS;
+        }
+        so += g.send_n;
+        ro += g.recv_n;
+    }
+    c.send_total = so;
+    c.recv_total = ro;
+    c.have_comms = true;
+    return DLESM_OK;
+}
+
+extern "C" int dlesm_dev_halo_exchange(void *const *fields, int nfields)
+{
+    Context &c = ctx();
+    if (!c.have_comms || (c.comms.nsend == 0 && c.comms.nrecv == 0)) return DLESM_OK;  // nothing to do
+    if (nfields < 1 || nfields > k::kMaxExchangeFields) {
+        set_error(DLESM_ERR_ARGS, "halo_exchange: between 1 and 8 fields per call");
+        return DLESM_ERR_ARGS;
+    }
+    int rc = ensure_device();
+    if (rc != DLESM_OK) return rc;
+    FieldRec r0;
+    rc = lookup(fields[0], r0);
+    if (rc != DLESM_OK) return rc;
+    for (int q = 1; q < nfields; ++q) {
+        FieldRec rq;
+        rc = lookup(fields[q], rq);
+        if (rc != DLESM_OK) return rc;
+        if (rq.nx != r0.nx || rq.ny != r0.ny) {
+            set_error(DLESM_ERR_ARGS, "halo_exchange: fields have different shapes");
+            return DLESM_ERR_ARGS;
+        }
+    }
+    const long long tot = std::max(c.send_total, c.recv_total) * nfields;
+    rc = ensure_xbuf(static_cast<size_t>(tot) + 1);
+    if (rc != DLESM_OK) return rc;
+    const int me0 = pstate().rank - 1;
+    const dlesm_comms &t = c.comms;
+
+    k::PackPlan sp{}, rp{};
+    sp.nfields = rp.nfields = nfields;
+    sp.pitch = rp.pitch = r0.nx;
+    for (int q = 0; q < nfields; ++q) sp.fields[q] = rp.fields[q] = static_cast<double *>(fields[q]);
+    bool remote = false;
+    for (const auto &g : c.groups) {
+        long long off = g.send_off * nfields;
+        for (int s : g.sends) {
+            k::Segment &sg = sp.seg[sp.nseg++];
+            sg.i0 = t.isrcsend[s]; sg.j0 = t.jsrcsend[s]; sg.nx = t.nxsend[s]; sg.ny = t.nysend[s];
+            sg.offset = off;
+            off += static_cast<long long>(sg.nx) * sg.ny * nfields;
+        }
+        off = g.recv_off * nfields;
+        for (int r : g.recvs) {
+            k::Segment &sg = rp.seg[rp.nseg++];
+            sg.i0 = t.idesrecv[r]; sg.j0 = t.jdesrecv[r]; sg.nx = t.nxrecv[r]; sg.ny = t.nyrecv[r];
+            sg.offset = off;
+            off += static_cast<long long>(sg.nx) * sg.ny * nfields;
+        }
+        if (g.peer0 != me0) remote = true;
+    }
+    if (remote && !c.comm_ready) {
+        set_error(DLESM_ERR_STATE, "halo_exchange: communicator not initialised (dlesm_comm_init)");
+        return DLESM_ERR_STATE;
+    }
+    CU(k::pack(sp, c.sendbuf, c.stream));
+    if (remote) NC(ncclGroupStart());
+    for (const auto &g : c.groups) {
+        if (g.peer0 == me0) {
+            // wrap-around neighbour is this rank itself: the "message" never leaves the device
+            if (g.send_n > 0)
+                CU(cudaMemcpyAsync(c.recvbuf + g.recv_off * nfields, c.sendbuf + g.send_off * nfields,
+                                   static_cast<size_t>(g.send_n) * nfields * sizeof(double),
+                                   cudaMemcpyDeviceToDevice, c.stream));
+            continue;
+        }
+        if (g.send_n > 0)
+            NC(ncclSend(c.sendbuf + g.send_off * nfields, static_cast<size_t>(g.send_n) * nfields, ncclDouble,
+                        g.peer0, c.comm, c.stream));
+        if (g.recv_n > 0)
+            NC(ncclRecv(c.recvbuf + g.recv_off * nfields, static_cast<size_t>(g.recv_n) * nfields, ncclDouble,
+                        g.peer0, c.comm, c.stream));
+    }
+    if (remote) NC(ncclGroupEnd());
+    CU(k::unpack(rp, c.recvbuf, c.stream));
+    return DLESM_OK;
+}
+
+extern "C" int dlesm_dev_grid_upload(int nx, int ny, const int *tmask, const double *const metrics[16],
+                                     void *device_ptrs[17])
+{
+    int rc = ensure_device();
+    if (rc != DLESM_OK) return rc;
+    Context &c = ctx();
+    const size_t n = static_cast<size_t>(nx) * ny;
+    for (int q = 0; q < 17; ++q) device_ptrs[q] = nullptr;
+    if (tmask) {
+        CU(cudaMalloc(&device_ptrs[0], n * sizeof(int)));
+        CU(cudaMemcpyAsync(device_ptrs[0], tmask, n * sizeof(int), cudaMemcpyHostToDevice, c.stream));
+    }
+    for (int q = 0; q < 16; ++q) {
+        if (!metrics || !metrics[q]) continue;
+        rc = dlesm_dev_field_alloc(nx, ny, &device_ptrs[q + 1]);
+        if (rc != DLESM_OK) return rc;
+        CU(cudaMemcpyAsync(device_ptrs[q + 1], metrics[q], n * sizeof(double), cudaMemcpyHostToDevice, c.stream));
+    }
+    CU(cudaStreamSynchronize(c.stream));
+    return DLESM_OK;
+}
+
+// =========================================================================================
+// device layer: stencils
+// =========================================================================================
+namespace {
+int pitch_of(const void *any, int &pitch, int &ny)
+{
+    FieldRec r;
+    int rc = lookup(any, r);
+    if (rc != DLESM_OK) return rc;
+    pitch = r.nx;
+    ny = r.ny;
+    return DLESM_OK;
+}
+int check_box(int pitch, int ny, int xs, int xe, int ys, int ye)
+{
+    // every stencil reaches one cell beyond the swept region
+    if (xs < 2 || ys < 2 || xe + 1 > pitch || ye + 1 > ny) {
+        set_error(DLESM_ERR_ARGS, "stencil sweep: region needs a one-cell rim inside the allocation");
+        return DLESM_ERR_ARGS;
+    }
+    return DLESM_OK;
+}
+#define D(p) static_cast<double *>(p)
+#define CD(p) static_cast<const double *>(p)
+#define SWEEP_PROLOGUE(outptr)                                   \
+    int pitch, ny_;                                              \
+    int rc = pitch_of(outptr, pitch, ny_);                       \
+    if (rc == DLESM_OK) rc = check_box(pitch, ny_, xs, xe, ys, ye); \
+    if (rc != DLESM_OK) return rc;                               \
+    const k::Box b{xs, xe, ys, ye};                              \
+    cudaStream_t st = ctx().stream;
+}  // namespace
+
+extern "C" int dlesm_compute_cu(void *cu, const void *p, const void *u, int xs, int xe, int ys, int ye, const void *tm)
+{
+    SWEEP_PROLOGUE(cu)
+    CU(k::compute_cu(D(cu), CD(p), CD(u), pitch, b, static_cast<const int *>(tm), st));
+    return DLESM_OK;
+}
+extern "C" int dlesm_compute_cv(void *cv, const void *p, const void *v, int xs, int xe, int ys, int ye, const void *tm)
+{
+    SWEEP_PROLOGUE(cv)
+    CU(k::compute_cv(D(cv), CD(p), CD(v), pitch, b, static_cast<const int *>(tm), st));
+    return DLESM_OK;
+}
+extern "C" int dlesm_compute_z(void *z, const void *p, const void *u, const void *v, double dx, double dy, int xs,
+                               int xe, int ys, int ye, const void *tm)
+{
+    SWEEP_PROLOGUE(z)
+    CU(k::compute_z(D(z), CD(p), CD(u), CD(v), pitch, b, 4.0 / dx, 4.0 / dy, static_cast<const int *>(tm), st));
+    return DLESM_OK;
+}
+extern "C" int dlesm_compute_h(void *h, const void *p, const void *u, const void *v, int xs, int xe, int ys, int ye,
+                               const void *tm)
+{
+    SWEEP_PROLOGUE(h)
+    CU(k::compute_h(D(h), CD(p), CD(u), CD(v), pitch, b, static_cast<const int *>(tm), st));
+    return DLESM_OK;
+}
+extern "C" int dlesm_compute_unew(void *unew, const void *uold, const void *z, const void *cv, const void *h,
+                                  double tdt, double dx, int xs, int xe, int ys, int ye, const void *tm,
+                                  const void *ucur)
+{
+    SWEEP_PROLOGUE(unew)
+    if (tm && !ucur) {
+        set_error(DLESM_ERR_ARGS, "compute_unew: masked sweep needs the current field");
+        return DLESM_ERR_ARGS;
+    }
+    CU(k::compute_unew(D(unew), CD(uold), CD(z), CD(cv), CD(h), pitch, b, tdt / 8.0, tdt / dx,
+                       static_cast<const int *>(tm), CD(ucur), st));
+    return DLESM_OK;
+}
+extern "C" int dlesm_compute_vnew(void *vnew, const void *vold, const void *z, const void *cu, const void *h,
+                                  double tdt, double dy, int xs, int xe, int ys, int ye, const void *tm,
+                                  const void *vcur)
+{
+    SWEEP_PROLOGUE(vnew)
+    if (tm && !vcur) {
+        set_error(DLESM_ERR_ARGS, "compute_vnew: masked sweep needs the current field");
+        return DLESM_ERR_ARGS;
+    }
+    CU(k::compute_vnew(D(vnew), CD(vold), CD(z), CD(cu), CD(h), pitch, b, tdt / 8.0, tdt / dy,
+                       static_cast<const int *>(tm), CD(vcur), st));
+    return DLESM_OK;
+}
+extern "C" int dlesm_compute_pnew(void *pnew, const void *pold, const void *cu, const void *cv, double tdt,
+                                  double dx, double dy, int xs, int xe, int ys, int ye, const void *tm,
+                                  const void *pcur)
+{
+    SWEEP_PROLOGUE(pnew)
+    if (tm && !pcur) {
+        set_error(DLESM_ERR_ARGS, "compute_pnew: masked sweep needs the current field");
+        return DLESM_ERR_ARGS;
+    }
+    CU(k::compute_pnew(D(pnew), CD(pold), CD(cu), CD(cv), pitch, b, tdt / dx, tdt / dy,
+                       static_cast<const int *>(tm), CD(pcur), st));
+    return DLESM_OK;
+}
+extern "C" int dlesm_time_smooth(const void *f, const void *fnew, void *fold, double alpha, int xs, int xe, int ys,
+                                 int ye, const void *tm, int points)
+{
+    SWEEP_PROLOGUE(fold)
+    if (points != DLESM_GO_U_POINTS && points != DLESM_GO_V_POINTS && points != DLESM_GO_T_POINTS) {
+        set_error(DLESM_ERR_POINTS, "time_smooth: points must be U, V or T");
+        return DLESM_ERR_POINTS;
+    }
+    CU(k::time_smooth(CD(f), CD(fnew), D(fold), pitch, b, alpha, static_cast<const int *>(tm), points, st));
+    return DLESM_OK;
+}
+
+extern "C" int dlesm_sw_step_fused(const void *u, const void *v, const void *p, void *uold, void *vold, void *pold,
+                                   void *unew, void *vnew, void *pnew, double dx, double dy, double tdt,
+                                   double alpha, int first, int xs, int xe, int ys, int ye, const void *tm,
+                                   int variant)
+{
+    SWEEP_PROLOGUE(unew)
+    (void)b;
+    const void *all[] = {u, v, p, uold, vold, pold, vnew, pnew};
+    for (const void *q : all) {
+        FieldRec r;
+        rc = lookup(q, r);
+        if (rc != DLESM_OK) return rc;
+        if (r.nx != pitch || r.ny != ny_) {
+            set_error(DLESM_ERR_ARGS, "sw_step_fused: fields have different shapes");
+            return DLESM_ERR_ARGS;
+        }
+    }
+    k::FusedArgs a;
+    a.u = CD(u); a.v = CD(v); a.p = CD(p);
+    a.uold = D(uold); a.vold = D(vold); a.pold = D(pold);
+    a.unew = D(unew); a.vnew = D(vnew); a.pnew = D(pnew);
+    a.tmask = static_cast<const int *>(tm);
+    a.pitch = pitch; a.ny = ny_;
+    a.b = k::Box{xs, xe, ys, ye};
+    a.sc.fsdx = 4.0 / dx; a.sc.fsdy = 4.0 / dy;
+    a.sc.tdts8 = tdt / 8.0; a.sc.tdtsdx = tdt / dx; a.sc.tdtsdy = tdt / dy;
+    a.sc.alpha = alpha; a.sc.first = first;
+    Context &c = ctx();
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    if (c.profile) {
+        if (c.prof_used == c.prof_events.size()) {
+            cudaEvent_t x, y;
+            CU(cudaEventCreate(&x));
+            CU(cudaEventCreate(&y));
+            c.prof_events.emplace_back(x, y);
+        }
+        e0 = c.prof_events[c.prof_used].first;
+        e1 = c.prof_events[c.prof_used].second;
+        ++c.prof_used;
+        CU(cudaEventRecord(e0, st));
+    }
+    cudaError_t e = k::sw_step_fused(a, variant, st);
+    if (e == cudaErrorNotSupported) {
+        set_error(DLESM_ERR_ARGS, "sw_step_fused: variant not available for this pitch / mask (see DESIGN.md)");
+        return DLESM_ERR_ARGS;
+    }
+    if (e != cudaSuccess) return fail_cuda(e, "sw_step_fused");
+    if (c.profile) CU(cudaEventRecord(e1, st));
+    return DLESM_OK;
+}
+
+extern "C" long long dlesm_kernel_launch_count(void) { return k::launch_count(); }
+extern "C" int dlesm_profile_enable(int on)
+{
+    ctx().profile = on != 0;
+    return DLESM_OK;
+}
+extern "C" int dlesm_profile_read(double *ms_total, long long *nlaunches, int reset)
+{
+    Context &c = ctx();
+    double tot = 0.0;
+    if (c.device_ready) CU(cudaStreamSynchronize(c.stream));
+    for (size_t q = 0; q < c.prof_used; ++q) {
+        float ms = 0.f;
+        CU(cudaEventElapsedTime(&ms, c.prof_events[q].first, c.prof_events[q].second));
+        tot += ms;
+    }
+    if (ms_total) *ms_total = tot;
+    if (nlaunches) *nlaunches = static_cast<long long>(c.prof_used);
+    if (reset) c.prof_used = 0;
+    return DLESM_OK;
+}
+
+// =========================================================================================
+// HOST MIRROR: grid_type
+// =========================================================================================
+struct dlesm_grid {
+    dlesm_grid_info info{};
+    dlesm_decomp dh;                  // handed out by dlesm_grid_decomp
+    Decomposition &decomp = dh.d;
+    bool decomposed = false;
+    bool user_tmask = false;
+    std::vector<int> tmask;           // materialised lazily when no mask was supplied
+    std::vector<double> xt, yt;       // 1-D coordinate vectors (xt(ji,:) and yt(:,jj))
+    dlesm_comms comms{};
+    bool have_comms = false;
+    bool pbc_x = false, pbc_y = false;
+    void *dev[17] = {nullptr};
+};
+
+extern "C" dlesm_grid_t *dlesm_grid_create(int grid_name, const int bcs[3], int grid_offsets)
+{
+    clear_error();
+    if (grid_offsets < 0) {
+        set_error(DLESM_ERR_GRID_OFFSET, "ERROR: grid offset not specified in call to grid_constructor.");
+        return nullptr;
+    }
+    if (grid_name != DLESM_GO_ARAKAWA_C && grid_name != DLESM_GO_ARAKAWA_B) {
+        set_error(DLESM_ERR_GRID_NAME, "grid_constructor: ERROR: unsupported grid type");
+        return nullptr;
+    }
+    if (grid_offsets != DLESM_GO_OFFSET_NE && grid_offsets != DLESM_GO_OFFSET_NW &&
+        grid_offsets != DLESM_GO_OFFSET_SE && grid_offsets != DLESM_GO_OFFSET_SW) {
+        set_error(DLESM_ERR_GRID_OFFSET, "grid_constructor: ERROR: unsupported relative offsets of grid types");
+        return nullptr;
+    }
+    auto *g = new dlesm_grid;
+    g->info.name = grid_name;
+    g->info.offset = grid_offsets;
+    for (int q = 0; q < 3; ++q) g->info.boundary_conditions[q] = bcs[q];
+    return g;
+}
+
+extern "C" int dlesm_grid_decompose(dlesm_grid_t *g, int domainx, int domainy, int ndomains, int ndomainx,
+                                    int ndomainy, int halo_width)
+{
+    clear_error();
+    int rc = go_decompose(domainx, domainy, ndomains, ndomainx, ndomainy, halo_width, pstate().nranks, g->decomp);
+    if (rc != DLESM_OK) return rc;
+    if (pstate().rank > g->decomp.ndomains) {
+        set_error(DLESM_ERR_ARGS, "grid%decompose: this rank has no sub-domain");
+        return DLESM_ERR_ARGS;
+    }
+    g->info.subdomain = g->decomp.subdomains[pstate().rank - 1];  // src/grid_mod.f90:207
+    g->info.global_nx = g->decomp.global_nx;
+    g->info.global_ny = g->decomp.global_ny;
+    g->decomposed = true;
+    return DLESM_OK;
+}
+
+extern "C" int dlesm_grid_init(dlesm_grid_t *g, double dxarg, double dyarg, const int *tmask, int tmask_nx,
+                               int tmask_ny)
+{
+    clear_error();
+    if (!g->decomposed) {
+        set_error(DLESM_ERR_STATE, "grid_init: grid%decompose must be called first");
+        return DLESM_ERR_STATE;
+    }
+    int alignment = 1;
+    int rc = parse_alignment(std::getenv("DL_ESM_ALIGNMENT"), alignment);
+    if (rc != DLESM_OK) return rc;
+    GridDims gd;
+    rc = grid_dims(g->info.subdomain, alignment, gd);
+    if (rc != DLESM_OK) return rc;
+    const dlesm_subdomain &sub = g->info.subdomain;
+    const bool px = g->info.boundary_conditions[0] == DLESM_GO_BC_PERIODIC;
+    const bool py = g->info.boundary_conditions[1] == DLESM_GO_BC_PERIODIC;
+    const bool dist = pstate().nranks > 1;
+    const bool ext = (pstate().extensions & DLESM_EXT_PERIODIC_DISTMEM) != 0;
+    if (dist && (px || py) && !ext) {
+        // src/grid_mod.f90:437-442 and :559-564
+        set_error(DLESM_ERR_PBC_DISTMEM, "grid_init: ERROR: Periodic boundary conditions are not yet supported.");
+        return DLESM_ERR_PBC_DISTMEM;
+    }
+    if (tmask) {
+        if (tmask_nx < sub.internal.xstop + 1 || tmask_ny < sub.internal.ystop + 1) {
+            set_error(DLESM_ERR_ARGS, "grid_init: tmask smaller than the sub-domain it must cover");
+            return DLESM_ERR_ARGS;
+        }
+        fill_tmask(sub, gd.nx, gd.ny, tmask, tmask_nx, g->tmask);
+        g->user_tmask = true;
+    }
+    g->info.nx = gd.nx;
+    g->info.ny = gd.ny;
+    g->info.alignment = alignment;
+    g->info.padding = gd.padding;
+    g->info.dx = dxarg;
+    g->info.dy = dyarg;
+    coord_vectors(sub, gd.nx, gd.ny, dxarg, dyarg, g->xt, g->yt);
+    g->pbc_x = px && dist;
+    g->pbc_y = py && dist;
+    if (dist) {
+        // map_comms(decomp, tmask, .false., (/1,1/), ierr) -- src/grid_mod.f90:566
+        rc = build_comms(g->decomp, pstate().rank, pstate().nranks, g->pbc_x, g->pbc_y, 1, 1, g->comms);
+        if (rc != DLESM_OK) {
+            set_error(rc, "Set-up of communication tables (call to map_comms()) failed.");
+            return rc;
+        }
+        g->have_comms = true;
+        rc = dlesm_dev_set_comms(&g->comms);  // module-level state, as in parallel_comms_mod
+        if (rc != DLESM_OK) return rc;
+    }
+    g->info.initialised = 1;
+    return DLESM_OK;
+}
+
+extern "C" int dlesm_grid_get_info(const dlesm_grid_t *g, dlesm_grid_info *out)
+{
+    *out = g->info;
+    return DLESM_OK;
+}
+extern "C" const dlesm_decomp_t *dlesm_grid_decomp(const dlesm_grid_t *g)
+{
+    return &g->dh;
+}
+extern "C" int dlesm_grid_comms(const dlesm_grid_t *g, dlesm_comms *out)
+{
+    if (!g->have_comms) {
+        dlesm_comms empty;
+        std::memset(&empty, 0, sizeof(empty));
+        *out = empty;
+        return DLESM_OK;
+    }
+    *out = g->comms;
+    return DLESM_OK;
+}
+
+namespace {
+double metric_constant(const dlesm_grid &g, int which, bool &is_const)
+{
+    is_const = true;
+    switch (which) {
+    case DLESM_GRID_DX_T: case DLESM_GRID_DX_U: case DLESM_GRID_DX_V: case DLESM_GRID_DX_F: return g.info.dx;
+    case DLESM_GRID_DY_T: case DLESM_GRID_DY_U: case DLESM_GRID_DY_V: case DLESM_GRID_DY_F: return g.info.dy;
+    case DLESM_GRID_AREA_T: case DLESM_GRID_AREA_U: case DLESM_GRID_AREA_V: return g.info.dx * g.info.dy;
+    case DLESM_GRID_GPHIU: case DLESM_GRID_GPHIV: case DLESM_GRID_GPHIF: return 50.0;
+    default: is_const = false; return 0.0;
+    }
+}
+void ensure_tmask(dlesm_grid &g)
+{
+    if (g.tmask.empty()) fill_tmask(g.info.subdomain, g.info.nx, g.info.ny, nullptr, 0, g.tmask);
+}
+}  // namespace
+
+extern "C" int dlesm_grid_host_array(dlesm_grid_t *g, int which, void *out)
+{
+    clear_error();
+    if (!g->info.initialised) {
+        set_error(DLESM_ERR_STATE, "grid arrays exist only after grid_init");
+        return DLESM_ERR_STATE;
+    }
+    const int nx = g->info.nx, ny = g->info.ny;
+    const size_t n = static_cast<size_t>(nx) * ny;
+    if (which == DLESM_GRID_TMASK) {
+        ensure_tmask(*g);
+        std::memcpy(out, g->tmask.data(), n * sizeof(int));
+        return DLESM_OK;
+    }
+    double *o = static_cast<double *>(out);
+    bool is_const;
+    const double cval = metric_constant(*g, which, is_const);
+    if (is_const) {
+        std::fill(o, o + n, cval);
+    } else if (which == DLESM_GRID_XT) {
+        for (int j = 0; j < ny; ++j) std::copy(g->xt.begin(), g->xt.end(), o + static_cast<size_t>(j) * nx);
+    } else if (which == DLESM_GRID_YT) {
+        for (int j = 0; j < ny; ++j) std::fill(o + static_cast<size_t>(j) * nx, o + static_cast<size_t>(j + 1) * nx, g->yt[j]);
+    } else {
+        set_error(DLESM_ERR_ARGS, "unknown grid array id");
+        return DLESM_ERR_ARGS;
+    }
+    return DLESM_OK;
+}
+
+extern "C" int dlesm_grid_device_array(dlesm_grid_t *g, int which, void **device_ptr)
+{
+    clear_error();
+    if (!g->info.initialised || which < 0 || which > 16) {
+        set_error(DLESM_ERR_STATE, "grid device arrays exist only after grid_init");
+        return DLESM_ERR_STATE;
+    }
+    if (g->dev[which]) {
+        *device_ptr = g->dev[which];
+        return DLESM_OK;
+    }
+    int rc = ensure_device();
+    if (rc != DLESM_OK) return rc;
+    Context &c = ctx();
+    const int nx = g->info.nx, ny = g->info.ny;
+    const size_t n = static_cast<size_t>(nx) * ny;
+    if (which == DLESM_GRID_TMASK) {
+        ensure_tmask(*g);
+        void *p = nullptr;
+        CU(cudaMalloc(&p, n * sizeof(int)));
+        CU(cudaMemcpyAsync(p, g->tmask.data(), n * sizeof(int), cudaMemcpyHostToDevice, c.stream));
+        CU(cudaStreamSynchronize(c.stream));
+        g->dev[which] = p;
+    } else {
+        void *p = nullptr;
+        rc = dlesm_dev_field_alloc(nx, ny, &p);
+        if (rc != DLESM_OK) return rc;
+        bool is_const;
+        const double cval = metric_constant(*g, which, is_const);
+        if (is_const) {
+            CU(k::set_field(static_cast<double *>(p), n, cval, c.stream));
+        } else {
+            const std::vector<double> &vec = which == DLESM_GRID_XT ? g->xt : g->yt;
+            double *dv = nullptr;
+            CU(cudaMalloc(&dv, vec.size() * sizeof(double)));
+            CU(cudaMemcpyAsync(dv, vec.data(), vec.size() * sizeof(double), cudaMemcpyHostToDevice, c.stream));
+            if (which == DLESM_GRID_XT) CU(k::broadcast_x(static_cast<double *>(p), nx, ny, dv, c.stream));
+            else CU(k::broadcast_y(static_cast<double *>(p), nx, ny, dv, c.stream));
+            CU(cudaStreamSynchronize(c.stream));
+            CU(cudaFree(dv));
+        }
+        g->dev[which] = p;
+    }
+    *device_ptr = g->dev[which];
+    return DLESM_OK;
+}
+
+extern "C" void dlesm_grid_free(dlesm_grid_t *g)
+{
+    if (!g) return;
+    if (g->dev[0]) cudaFree(g->dev[0]);
+    for (int q = 1; q < 17; ++q)
+        if (g->dev[q]) dlesm_dev_field_free(g->dev[q]);
+    delete g;
+}
+
+// =========================================================================================
+// HOST MIRROR: r2d_field
+// =========================================================================================
+struct dlesm_field {
+    dlesm_grid *grid = nullptr;
+    FieldBounds fb;
+    int nx = 0, ny = 0;
+    int ntiles = 0;
+    void *dptr = nullptr;
+};
+
+extern "C" dlesm_field_t *dlesm_r2d_field_create(dlesm_grid_t *g, int grid_points, int do_tile,
+                                                 const double *init_global_data, int gnx, int gny)
+{
+    clear_error();
+    if (!g || !g->info.initialised) {
+        set_error(DLESM_ERR_STATE, "r2d_field: the grid must be initialised (grid_init) first");
+        return nullptr;
+    }
+    auto *f = new dlesm_field;
+    f->grid = g;
+    f->nx = g->info.nx;
+    f->ny = g->info.ny;
+    if (field_bounds(g->info.subdomain, g->info.nx, g->info.ny, g->info.offset, g->info.boundary_conditions,
+                     grid_points, f->fb) != DLESM_OK) {
+        delete f;
+        return nullptr;
+    }
+    // do_tile: OpenMP thread tiling of the host loops (src/field_mod.f90:300-325); the CUDA
+    // grid takes its place, so the request is accepted and ntiles stays 0
+    (void)do_tile;
+    f->ntiles = 0;
+    if (dlesm_dev_field_alloc(f->nx, f->ny, &f->dptr) != DLESM_OK) {
+        delete f;
+        return nullptr;
+    }
+    if (init_global_data) {
+        // src/field_mod.f90:378-389: data(ji,jj) = init_global_data(ji+dx, jj+dy) over the GRID's
+        // internal region
+        const dlesm_subdomain &sub = g->info.subdomain;
+        if (gnx < sub.global.xstop || gny < sub.global.ystop) {
+            set_error(DLESM_ERR_ARGS, "r2d_field: init_global_data smaller than the global domain");
+            dlesm_free_field(f);
+            return nullptr;
+        }
+        Context &c = ctx();
+        double *dg = nullptr;
+        const size_t gn = static_cast<size_t>(gnx) * gny;
+        cudaError_t e = cudaMalloc(&dg, gn * sizeof(double));
+        if (e == cudaSuccess) e = cudaMemcpyAsync(dg, init_global_data, gn * sizeof(double), cudaMemcpyHostToDevice, c.stream);
+        if (e == cudaSuccess)
+            e = k::scatter_global(static_cast<double *>(f->dptr), f->nx, box_of(sub.internal), dg, gnx,
+                                  sub.global.xstart - f->fb.internal.xstart,
+                                  sub.global.ystart - f->fb.internal.ystart, c.stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(c.stream);
+        if (dg) cudaFree(dg);
+        if (e != cudaSuccess) {
+            fail_cuda(e, "r2d_field scatter");
+            dlesm_free_field(f);
+            return nullptr;
+        }
+    }
+    return f;
+}
+
+extern "C" int dlesm_field_get_info(const dlesm_field_t *f, dlesm_field_info *out)
+{
+    out->defined_on = f->fb.defined_on;
+    out->internal = f->fb.internal;
+    out->whole = f->fb.whole;
+    out->num_halos = f->fb.num_halos;
+    for (int q = 0; q < 4; ++q) out->halo[q] = f->fb.halo[q];
+    out->nx = f->nx;
+    out->ny = f->ny;
+    out->ntiles = f->ntiles;
+    out->data_on_device = 1;
+    out->device_ptr = f->dptr;
+    return DLESM_OK;
+}
+
+extern "C" int dlesm_grid_field_bounds(const dlesm_grid_t *g, int grid_points, dlesm_field_info *out)
+{
+    clear_error();
+    if (!g || !g->info.initialised) {
+        set_error(DLESM_ERR_STATE, "r2d_field: the grid must be initialised (grid_init) first");
+        return DLESM_ERR_STATE;
+    }
+    FieldBounds fb;
+    int rc = field_bounds(g->info.subdomain, g->info.nx, g->info.ny, g->info.offset,
+                          g->info.boundary_conditions, grid_points, fb);
+    if (rc != DLESM_OK) return rc;
+    out->defined_on = fb.defined_on;
+    out->internal = fb.internal;
+    out->whole = fb.whole;
+    out->num_halos = fb.num_halos;
+    for (int q = 0; q < 4; ++q) out->halo[q] = fb.halo[q];
+    out->nx = g->info.nx;
+    out->ny = g->info.ny;
+    out->ntiles = 0;
+    out->data_on_device = 0;
+    out->device_ptr = nullptr;
+    return DLESM_OK;
+}
+
+extern "C" int dlesm_field_write_to_device(dlesm_field_t *f, const double *host, int startx, int starty, int nx,
+                                           int ny, bool blocking)
+{
+    clear_error();
+    return hook_copy(f->dptr, const_cast<double *>(host), true, startx, starty, nx, ny, blocking);
+}
+extern "C" int dlesm_field_read_from_device(dlesm_field_t *f, double *host, int startx, int starty, int nx, int ny,
+                                            bool blocking)
+{
+    clear_error();
+    return hook_copy(f->dptr, host, false, startx, starty, nx, ny, blocking);
+}
+extern "C" int dlesm_field_set_data(dlesm_field_t *f, const double *host)
+{
+    return dlesm_field_write_to_device(f, host, 1, 1, f->nx, f->ny, true);
+}
+extern "C" int dlesm_field_get_data(dlesm_field_t *f, double *host)
+{
+    return dlesm_field_read_from_device(f, host, 1, 1, f->nx, f->ny, true);
+}
+
+extern "C" int dlesm_fields_halo_exchange(dlesm_field_t *const *f, int nfields, int depth)
+{
+    clear_error();
+    (void)depth;  // "currently ignored and hardwired to 1" -- src/field_mod.f90:1226-1229
+    if (nfields < 1 || nfields > k::kMaxExchangeFields) {
+        set_error(DLESM_ERR_ARGS, "halo_exchange: between 1 and 8 fields per call");
+        return DLESM_ERR_ARGS;
+    }
+    void *ptrs[k::kMaxExchangeFields];
+    for (int q = 0; q < nfields; ++q) ptrs[q] = f[q]->dptr;
+    return dlesm_dev_halo_exchange(ptrs, nfields);
+}
+extern "C" int dlesm_field_halo_exchange(dlesm_field_t *f, int depth)
+{
+    dlesm_field_t *one[1] = {f};
+    return dlesm_fields_halo_exchange(one, 1, depth);
+}
+
+extern "C" int dlesm_field_apply_periodic_halos(dlesm_field_t *f)
+{
+    clear_error();
+    if (f->fb.num_halos <= 0) return DLESM_OK;
+    const int *bcs = f->grid->info.boundary_conditions;
+    double *fl[1] = {static_cast<double *>(f->dptr)};
+    CU(k::periodic_halos(fl, 1, f->nx, box_of(f->fb.internal), bcs[0] == DLESM_GO_BC_PERIODIC,
+                         bcs[1] == DLESM_GO_BC_PERIODIC, ctx().stream));
+    return DLESM_OK;
+}
+
+extern "C" int dlesm_field_gather_inner_data(dlesm_field_t *f, double *global_data)
+{
+    clear_error();
+    Context &c = ctx();
+    const Decomposition &d = f->grid->decomp;
+    const dlesm_region &in = f->fb.internal;
+    const int nranks = pstate().nranks, me = pstate().rank;
+    if (nranks == 1) {
+        // src/field_mod.f90:1333-1343
+        CU(cudaMemcpy2DAsync(global_data, static_cast<size_t>(d.global_nx) * sizeof(double),
+                             static_cast<const double *>(f->dptr) + (static_cast<size_t>(in.ystart) - 1) * f->nx +
+                                 (in.xstart - 1),
+                             static_cast<size_t>(f->nx) * sizeof(double), static_cast<size_t>(in.nx) * sizeof(double),
+                             in.ny, cudaMemcpyDeviceToHost, c.stream));
+        CU(cudaStreamSynchronize(c.stream));
+        return DLESM_OK;
+    }
+    if (!c.comm_ready) {
+        set_error(DLESM_ERR_STATE, "gather_inner_data: communicator not initialised (dlesm_comm_init)");
+        return DLESM_ERR_STATE;
+    }
+    // :1348-1351: every rank contributes a fixed-size slot
+    const int halo_x = in.xstart - 1, halo_y = in.ystart - 1;
+    const size_t n = static_cast<size_t>(d.max_width - 2 * halo_x) * (d.max_height - 2 * halo_y);
+    int rc = ensure_scratch(n * (me == 1 ? nranks : 1));
+    if (rc != DLESM_OK) return rc;
+    CU(k::gather_box(static_cast<const double *>(f->dptr), f->nx, box_of(in), c.scratch, c.stream));
+    NC(ncclGroupStart());
+    if (me == 1) {
+        for (int r = 1; r < nranks; ++r)
+            NC(ncclRecv(c.scratch + static_cast<size_t>(r) * n, n, ncclDouble, r, c.comm, c.stream));
+    } else {
+        NC(ncclSend(c.scratch, n, ncclDouble, 0, c.comm, c.stream));
+    }
+    NC(ncclGroupEnd());
+    if (me == 1) {
+        std::vector<double> recv(n * nranks);
+        CU(cudaMemcpyAsync(recv.data(), c.scratch, recv.size() * sizeof(double), cudaMemcpyDeviceToHost, c.stream));
+        CU(cudaStreamSynchronize(c.stream));
+        // :1373-1388
+        for (int r = 1; r <= nranks; ++r) {
+            const dlesm_region &gr = d.subdomains[r - 1].global;
+            size_t q = static_cast<size_t>(r - 1) * n;
+            for (int jj = gr.ystart; jj <= gr.ystop; ++jj)
+                for (int ji = gr.xstart; ji <= gr.xstop; ++ji)
+                    global_data[(static_cast<size_t>(jj) - 1) * d.global_nx + (ji - 1)] = recv[q++];
+        }
+    } else {
+        CU(cudaStreamSynchronize(c.stream));
+    }
+    return DLESM_OK;
+}
+
+extern "C" int dlesm_copy_field(const dlesm_field_t *in, dlesm_field_t *out)
+{
+    clear_error();
+    return dlesm_dev_copy_field(in->dptr, out->dptr);
+}
+extern "C" int dlesm_copy_field_patch(dlesm_field_t *f, const dlesm_region *src, const dlesm_region *dest)
+{
+    clear_error();
+    return dlesm_dev_copy_patch(f->dptr, src->xstart, src->xstop, src->ystart, src->ystop, dest->xstart,
+                                dest->xstop, dest->ystart, dest->ystop);
+}
+extern "C" int dlesm_set_field(dlesm_field_t *f, double val)
+{
+    clear_error();
+    return dlesm_dev_set_field(f->dptr, val);
+}
+extern "C" int dlesm_field_checksum(dlesm_field_t *f, double *val)
+{
+    clear_error();
+    const dlesm_region &in = f->fb.internal;
+    int rc = dlesm_dev_checksum(f->dptr, in.xstart, in.xstop, in.ystart, in.ystop, val);
+    if (rc != DLESM_OK) return rc;
+    return dlesm_global_sum(val);
+}
+extern "C" int dlesm_free_field(dlesm_field_t *f)
+{
+    if (!f) return DLESM_OK;
+    int rc = f->dptr ? dlesm_dev_field_free(f->dptr) : DLESM_OK;
+    delete f;
+    return rc;
+}
+
+// =========================================================================================
+// HOST MIRROR: shallow-water application layer
+// =========================================================================================
+struct dlesm_sw {
+    dlesm_grid *grid = nullptr;
+    dlesm_field *f[DLESM_SW_NFIELDS] = {nullptr};
+    double dt = 0, tdt = 0, alpha = 0;
+    int mode = DLESM_SW_FUSED;
+    int variant = 0;
+    long long ncycle = 0;
+    const int *tmask_dev = nullptr;
+    bool periodic_local = true;  // halos by local copies (1 rank) or by exchange (several)
+};
+
+extern "C" dlesm_sw_t *dlesm_sw_create(dlesm_grid_t *g, double dt, double alpha, int mode, int use_tmask)
+{
+    clear_error();
+    if (!g || !g->info.initialised) {
+        set_error(DLESM_ERR_STATE, "sw_create: the grid must be initialised first");
+        return nullptr;
+    }
+    const int *bcs = g->info.boundary_conditions;
+    if (g->info.offset != DLESM_GO_OFFSET_SW || bcs[0] != DLESM_GO_BC_PERIODIC || bcs[1] != DLESM_GO_BC_PERIODIC) {
+        set_error(DLESM_ERR_ARGS, "sw_create: the shallow-water layer needs GO_OFFSET_SW and periodic BCs in x and y");
+        return nullptr;
+    }
+    auto *s = new dlesm_sw;
+    s->grid = g;
+    s->dt = s->tdt = dt;
+    s->alpha = alpha;
+    s->mode = mode;
+    s->periodic_local = pstate().nranks == 1;
+    static const int pts[DLESM_SW_NFIELDS] = {
+        DLESM_GO_U_POINTS, DLESM_GO_V_POINTS, DLESM_GO_T_POINTS, DLESM_GO_U_POINTS, DLESM_GO_V_POINTS,
+        DLESM_GO_T_POINTS, DLESM_GO_U_POINTS, DLESM_GO_V_POINTS, DLESM_GO_T_POINTS, DLESM_GO_U_POINTS,
+        DLESM_GO_V_POINTS, DLESM_GO_F_POINTS, DLESM_GO_T_POINTS};
+    const int nf = mode == DLESM_SW_FUSED ? DLESM_SW_CU : DLESM_SW_NFIELDS;  // cu,cv,z,h only un-fused
+    for (int q = 0; q < nf; ++q) {
+        s->f[q] = dlesm_r2d_field_create(g, pts[q], 0, nullptr, 0, 0);
+        if (!s->f[q]) {
+            dlesm_sw_free(s);
+            return nullptr;
+        }
+    }
+    if (use_tmask) {
+        void *p = nullptr;
+        if (dlesm_grid_device_array(g, DLESM_GRID_TMASK, &p) != DLESM_OK) {
+            dlesm_sw_free(s);
+            return nullptr;
+        }
+        s->tmask_dev = static_cast<const int *>(p);
+    }
+    return s;
+}
+
+namespace {
+int sw_fill_halos(dlesm_sw *s, int first_field, int count)
+{
+    if (s->periodic_local) {
+        double *fl[k::kMaxExchangeFields];
+        for (int q = 0; q < count; ++q) fl[q] = static_cast<double *>(s->f[first_field + q]->dptr);
+        // every SW periodic field shares the T-point internal region
+        CU(k::periodic_halos(fl, count, s->f[first_field]->nx, box_of(s->f[first_field]->fb.internal), true, true,
+                             ctx().stream));
+        return DLESM_OK;
+    }
+    return dlesm_fields_halo_exchange(&s->f[first_field], count, 1);
+}
+}  // namespace
+
+extern "C" int dlesm_sw_init_device(dlesm_sw_t *s)
+{
+    clear_error();
+    const dlesm_subdomain &sub = s->grid->info.subdomain;
+    const dlesm_region &in = s->f[DLESM_SW_P]->fb.internal;
+    const int n = s->f[0]->nx;
+    CU(k::sw_init(static_cast<double *>(s->f[DLESM_SW_U]->dptr), static_cast<double *>(s->f[DLESM_SW_V]->dptr),
+                  static_cast<double *>(s->f[DLESM_SW_P]->dptr), n, box_of(in), sub.global.xstart,
+                  sub.global.ystart, s->grid->info.global_nx, s->grid->info.global_ny, s->grid->info.dx,
+                  s->grid->info.dy, ctx().stream));
+    int rc = sw_fill_halos(s, DLESM_SW_U, 3);
+    if (rc != DLESM_OK) return rc;
+    for (int q = 0; q < 3; ++q) {
+        rc = dlesm_copy_field(s->f[DLESM_SW_U + q], s->f[DLESM_SW_UOLD + q]);
+        if (rc != DLESM_OK) return rc;
+    }
+    s->ncycle = 0;
+    s->tdt = s->dt;
+    return DLESM_OK;
+}
+
+extern "C" int dlesm_sw_set_state(dlesm_sw_t *s, const double *u, const double *v, const double *p)
+{
+    clear_error();
+    const double *src[3] = {u, v, p};
+    for (int q = 0; q < 3; ++q) {
+        int rc = dlesm_field_set_data(s->f[DLESM_SW_U + q], src[q]);
+        if (rc != DLESM_OK) return rc;
+        rc = dlesm_copy_field(s->f[DLESM_SW_U + q], s->f[DLESM_SW_UOLD + q]);
+        if (rc != DLESM_OK) return rc;
+    }
+    s->ncycle = 0;
+    s->tdt = s->dt;
+    return DLESM_OK;
+}
+
+extern "C" int dlesm_sw_step(dlesm_sw_t *s, int nsteps)
+{
+    clear_error();
+    dlesm_grid &g = *s->grid;
+    const double dx = g.info.dx, dy = g.info.dy;
+    for (int it = 0; it < nsteps; ++it) {
+        const int first = s->ncycle == 0;
+        dlesm_field **f = s->f;
+        const dlesm_region &ru = f[DLESM_SW_U]->fb.internal, &rv = f[DLESM_SW_V]->fb.internal;
+        const dlesm_region &rt = f[DLESM_SW_P]->fb.internal;
+        int rc;
+#define P(q) f[q]->dptr
+        if (s->mode == DLESM_SW_FUSED) {
+            rc = dlesm_sw_step_fused(P(DLESM_SW_U), P(DLESM_SW_V), P(DLESM_SW_P), P(DLESM_SW_UOLD), P(DLESM_SW_VOLD),
+                                     P(DLESM_SW_POLD), P(DLESM_SW_UNEW), P(DLESM_SW_VNEW), P(DLESM_SW_PNEW), dx, dy,
+                                     s->tdt, s->alpha, first, rt.xstart, rt.xstop, rt.ystart, rt.ystop,
+                                     s->tmask_dev, s->variant);
+            if (rc != DLESM_OK) return rc;
+            rc = sw_fill_halos(s, DLESM_SW_UNEW, 3);
+            if (rc != DLESM_OK) return rc;
+            // u <- unew by rotating the device buffers (copy_field semantics without the copy)
+            for (int q = 0; q < 3; ++q) std::swap(f[DLESM_SW_U + q]->dptr, f[DLESM_SW_UNEW + q]->dptr);
+        } else {
+            const dlesm_region &rf = f[DLESM_SW_Z]->fb.internal;
+            const void *tm = s->tmask_dev;
+            rc = dlesm_compute_cu(P(DLESM_SW_CU), P(DLESM_SW_P), P(DLESM_SW_U), ru.xstart, ru.xstop, ru.ystart, ru.ystop, tm);
+            if (rc == DLESM_OK) rc = dlesm_compute_cv(P(DLESM_SW_CV), P(DLESM_SW_P), P(DLESM_SW_V), rv.xstart, rv.xstop, rv.ystart, rv.ystop, tm);
+            if (rc == DLESM_OK) rc = dlesm_compute_z(P(DLESM_SW_Z), P(DLESM_SW_P), P(DLESM_SW_U), P(DLESM_SW_V), dx, dy, rf.xstart, rf.xstop, rf.ystart, rf.ystop, tm);
+            if (rc == DLESM_OK) rc = dlesm_compute_h(P(DLESM_SW_H), P(DLESM_SW_P), P(DLESM_SW_U), P(DLESM_SW_V), rt.xstart, rt.xstop, rt.ystart, rt.ystop, tm);
+            if (rc == DLESM_OK) rc = sw_fill_halos(s, DLESM_SW_CU, 4);
+            if (rc == DLESM_OK) rc = dlesm_compute_unew(P(DLESM_SW_UNEW), P(DLESM_SW_UOLD), P(DLESM_SW_Z), P(DLESM_SW_CV), P(DLESM_SW_H), s->tdt, dx, ru.xstart, ru.xstop, ru.ystart, ru.ystop, tm, P(DLESM_SW_U));
+            if (rc == DLESM_OK) rc = dlesm_compute_vnew(P(DLESM_SW_VNEW), P(DLESM_SW_VOLD), P(DLESM_SW_Z), P(DLESM_SW_CU), P(DLESM_SW_H), s->tdt, dy, rv.xstart, rv.xstop, rv.ystart, rv.ystop, tm, P(DLESM_SW_V));
+            if (rc == DLESM_OK) rc = dlesm_compute_pnew(P(DLESM_SW_PNEW), P(DLESM_SW_POLD), P(DLESM_SW_CU), P(DLESM_SW_CV), s->tdt, dx, dy, rt.xstart, rt.xstop, rt.ystart, rt.ystop, tm, P(DLESM_SW_P));
+            if (rc == DLESM_OK) rc = sw_fill_halos(s, DLESM_SW_UNEW, 3);
+            if (rc == DLESM_OK && !first) {
+                rc = dlesm_time_smooth(P(DLESM_SW_U), P(DLESM_SW_UNEW), P(DLESM_SW_UOLD), s->alpha, ru.xstart, ru.xstop, ru.ystart, ru.ystop, tm, DLESM_GO_U_POINTS);
+                if (rc == DLESM_OK) rc = dlesm_time_smooth(P(DLESM_SW_V), P(DLESM_SW_VNEW), P(DLESM_SW_VOLD), s->alpha, rv.xstart, rv.xstop, rv.ystart, rv.ystop, tm, DLESM_GO_V_POINTS);
+                if (rc == DLESM_OK) rc = dlesm_time_smooth(P(DLESM_SW_P), P(DLESM_SW_PNEW), P(DLESM_SW_POLD), s->alpha, rt.xstart, rt.xstop, rt.ystart, rt.ystop, tm, DLESM_GO_T_POINTS);
+            }
+            for (int q = 0; q < 3 && rc == DLESM_OK; ++q) rc = dlesm_copy_field(f[DLESM_SW_UNEW + q], f[DLESM_SW_U + q]);
+            if (rc != DLESM_OK) return rc;
+        }
+#undef P
+        if (first) s->tdt = s->tdt + s->tdt;
+        ++s->ncycle;
+    }
+    return DLESM_OK;
+}
+
+extern "C" dlesm_field_t *dlesm_sw_field(dlesm_sw_t *s, int which)
+{
+    if (which < 0 || which >= DLESM_SW_NFIELDS) return nullptr;
+    return s->f[which];
+}
+extern "C" int dlesm_sw_set_variant(dlesm_sw_t *s, int variant)
+{
+    s->variant = variant;
+    return DLESM_OK;
+}
+extern "C" void dlesm_sw_free(dlesm_sw_t *s)
+{
+    if (!s) return;
+    for (auto *fl : s->f)
+        if (fl) dlesm_free_field(fl);
+    delete s;
+}

@@ -1,0 +1,416 @@
+/*
+ * dlesm_b200.h -- C ABI of libdlesm_b200.so, the B200-native drop-in for the hot path of
+ * stfc/dl_esm_inf's fd_lib / dm_fd_lib: finite-difference stencil sweeps over r2d_field
+ * data on an Arakawa C-grid grid_type, and the halo exchange between them.
+ *
+ * Two layers, both plain C (pointers, ints, doubles; no C++/torch types):
+ *
+ *   1. DEVICE LAYER (dlesm_dev_*, dlesm_read_from_device_c, ...): what a Fortran build of
+ *      the reference binds through ISO_C_BINDING.  The Fortran side keeps its own
+ *      grid_type / r2d_field bookkeeping; these entry points own device storage, copies,
+ *      reductions, the exchange and the stencils.  INTEGRATION.md shows the bind(C) stubs.
+ *
+ *   2. HOST MIRROR (dlesm_grid_*, dlesm_field_*, dlesm_sw_*): the same public API as the
+ *      reference's grid_mod / field_mod / parallel_mod, implemented in C++ above layer 1,
+ *      for hosts without a Fortran toolchain (this image).  Same names, argument meaning,
+ *      1-based inclusive regions and error behaviour as the Fortran.
+ *
+ * Every int-returning function returns DLESM_OK (0) or a negative DLESM_ERR_* code and
+ * records a message for dlesm_last_error(); a Fortran shim turns non-zero into
+ * gocean_stop(msg) (reference: src/gocean_mod.F90:50-57 has no status returns).
+ * There is NO CPU fallback: device entry points fail with DLESM_ERR_CUDA when no GPU
+ * is usable.
+ *
+ * Citations "src/X:a-b" are to /root/reference/finite_difference/src/X.
+ */
+#ifndef DLESM_B200_H
+#define DLESM_B200_H
+
+#include <stdbool.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ------------------------------------------------------------------------------------ */
+/* constants (values identical to the reference's Fortran parameters)                   */
+/* ------------------------------------------------------------------------------------ */
+/* src/grid_mod.f90:45-69 */
+#define DLESM_GO_ARAKAWA_C 0
+#define DLESM_GO_ARAKAWA_B 1
+#define DLESM_GO_OFFSET_SW 0
+#define DLESM_GO_OFFSET_SE 1
+#define DLESM_GO_OFFSET_NW 2
+#define DLESM_GO_OFFSET_NE 3
+#define DLESM_GO_OFFSET_ANY 4
+#define DLESM_GO_BC_PERIODIC 0
+#define DLESM_GO_BC_EXTERNAL 1
+#define DLESM_GO_BC_NONE 2
+/* src/field_mod.f90:47-52 */
+#define DLESM_GO_U_POINTS 0
+#define DLESM_GO_V_POINTS 1
+#define DLESM_GO_T_POINTS 2
+#define DLESM_GO_F_POINTS 3
+#define DLESM_GO_ALL_POINTS 4
+/* src/parallel_comms_mod.f90:70,101-110 */
+#define DLESM_MAXCOMM 16
+#define DLESM_IPLUS 1
+#define DLESM_IMINUS 2
+#define DLESM_JPLUS 3
+#define DLESM_JMINUS 4
+#define DLESM_IPLUSJPLUS 5
+#define DLESM_IMINUSJMINUS 6
+#define DLESM_IPLUSJMINUS 7
+#define DLESM_IMINUSJPLUS 8
+
+#define DLESM_OK 0
+#define DLESM_ERR_ARGS (-1)         /* go_decompose: invalid arguments supplied        */
+#define DLESM_ERR_NRANKS (-2)
+#define DLESM_ERR_HALO_WIDTH (-3)
+#define DLESM_ERR_ALIGN_DIGITS (-4) /* DL_ESM_ALIGNMENT longer than 3 characters       */
+#define DLESM_ERR_ALIGN_VALUE (-5)  /* DL_ESM_ALIGNMENT not a positive integer         */
+#define DLESM_ERR_PBC_DISTMEM (-6)  /* periodic BCs with >1 rank and extension not on  */
+#define DLESM_ERR_GRID_NAME (-7)
+#define DLESM_ERR_GRID_OFFSET (-8)
+#define DLESM_ERR_FIELD_STOP (-9)   /* a c?_{sw,ne}_init gocean_stop branch            */
+#define DLESM_ERR_POINTS (-10)
+#define DLESM_ERR_MAXCOMM (-12)     /* map_comms list overflow (reference ierr = -12)  */
+#define DLESM_ERR_HALO_DEPTH (-13)
+#define DLESM_ERR_CUDA (-20)        /* no device / CUDA failure: fail loudly           */
+#define DLESM_ERR_NCCL (-21)
+#define DLESM_ERR_STATE (-22)       /* call order (e.g. field before grid_init)        */
+#define DLESM_ERR_UNKNOWN_PTR (-23) /* device pointer not allocated by this library    */
+
+/* last error message of the calling thread ("" if none) */
+const char *dlesm_last_error(void);
+/* library version string, e.g. "dlesm_b200 0.1 (sm_100a)" */
+const char *dlesm_version(void);
+
+/* ------------------------------------------------------------------------------------ */
+/* index boxes -- src/region_mod.f90:7-12, src/decomposition_mod.f90:44-50,              */
+/*                src/halo_mod.f90:9-25.  1-based, inclusive, exactly as in Fortran.     */
+/* ------------------------------------------------------------------------------------ */
+typedef struct {
+    int nx, ny;
+    int xstart, xstop;
+    int ystart, ystop;
+} dlesm_region;
+
+typedef struct {
+    dlesm_region global;   /* where the internal part sits in the global domain; nx,ny =
+                              full extent incl. halos (src/parallel_mod.f90:272-290) */
+    dlesm_region internal; /* internal region in local indices */
+} dlesm_subdomain;
+
+typedef struct {
+    int needs_update;
+    dlesm_region source;
+    dlesm_region dest;
+} dlesm_halo;
+
+/* ------------------------------------------------------------------------------------ */
+/* lifecycle -- replaces parallel_utils_mod / parallel_utils_stub_mod                    */
+/* (src/parallel/parallel_utils_mod.f90:77-125, gocean_initialise src/gocean_mod.F90:22) */
+/* ------------------------------------------------------------------------------------ */
+/* Set this process's 1-based rank and the number of ranks.  Host only: touches neither
+ * CUDA nor NCCL, so decomposition / bookkeeping entry points work on a CPU-only box.
+ * A process that never calls it is rank 1 of 1 (the serial stub's behaviour). */
+int dlesm_parallel_init(int rank1, int nranks);
+/* Bind the process to a GPU (cudaSetDevice, streams, scratch).  device < 0 => LOCAL_RANK
+ * env or 0.  Called implicitly (device 0 / LOCAL_RANK) by the first device operation. */
+int dlesm_device_init(int device);
+/* Multi-rank bring-up without MPI: rank 1 creates a 128-byte id, the launcher ships it to
+ * all ranks (torch.distributed, a file, ...), every rank calls dlesm_comm_init. */
+int dlesm_comm_unique_id(void *id128);
+int dlesm_comm_init(const void *id128);
+/* parallel_finalise (parallel_utils_mod.f90:94-98): destroys communicator, frees pools */
+int dlesm_parallel_finalise(void);
+/* parallel_abort (:104-111): message to stderr, abort communicator, exit(1) */
+void dlesm_parallel_abort(const char *msg);
+int dlesm_get_rank(void);      /* 1-based, parallel_utils_mod.f90:115-118 */
+int dlesm_get_num_ranks(void); /* :122-125 */
+int dlesm_on_master(void);     /* src/parallel_mod.f90:337-340 */
+/* global_sum (parallel_utils_mod.f90:230-238): in-place sum over ranks of one double
+ * (no-op for one rank, as the stub :148-150) */
+int dlesm_global_sum(double *var);
+/* go_decompose keeps halo_width between calls (SAVEd local, src/parallel_mod.f90:103-105);
+ * this resets it to 1 as at program start. */
+void dlesm_reset_saved_state(void);
+/* Extensions the reference marks TODO.  bit 0: allow periodic BCs with
+ * more than one rank (wrap-around neighbours); default 0 = refuse as the reference. */
+int dlesm_set_extensions(int flags);
+#define DLESM_EXT_PERIODIC_DISTMEM 1
+
+/* ------------------------------------------------------------------------------------ */
+/* HOST MIRROR: decomposition -- src/parallel_mod.f90:70-332, decomposition_mod.f90      */
+/* ------------------------------------------------------------------------------------ */
+typedef struct dlesm_decomp dlesm_decomp_t;
+
+/* Optional Fortran arguments: pass a negative value for "not present".  nranks comes from
+ * dlesm_parallel_init.  Returns NULL on error (see dlesm_last_error / dlesm_last_status). */
+dlesm_decomp_t *dlesm_go_decompose(int domainx, int domainy, int ndomains, int ndomainx,
+                                   int ndomainy, int halo_width);
+int dlesm_last_status(void);
+/* info[8] = global_nx, global_ny, nx, ny, ndomains, max_width, max_height, domperrank */
+int dlesm_decomp_info(const dlesm_decomp_t *d, int info[8]);
+int dlesm_decomp_subdomain(const dlesm_decomp_t *d, int idomain1, dlesm_subdomain *out);
+/* proc_subdomains(islot1, irank1), -1 where empty */
+int dlesm_decomp_proc_subdomain(const dlesm_decomp_t *d, int islot1, int irank1);
+void dlesm_decomp_free(dlesm_decomp_t *d);
+
+/* map_comms tables -- module variables of src/parallel_comms_mod.f90:70-83 */
+typedef struct {
+    int nsend, nrecv;
+    int dirsend[DLESM_MAXCOMM], destination[DLESM_MAXCOMM];
+    int isrcsend[DLESM_MAXCOMM], jsrcsend[DLESM_MAXCOMM];
+    int idessend[DLESM_MAXCOMM], jdessend[DLESM_MAXCOMM];
+    int nxsend[DLESM_MAXCOMM], nysend[DLESM_MAXCOMM], nsendp[DLESM_MAXCOMM];
+    int dirrecv[DLESM_MAXCOMM], source[DLESM_MAXCOMM];
+    int isrcrecv[DLESM_MAXCOMM], jsrcrecv[DLESM_MAXCOMM];
+    int idesrecv[DLESM_MAXCOMM], jdesrecv[DLESM_MAXCOMM];
+    int nxrecv[DLESM_MAXCOMM], nyrecv[DLESM_MAXCOMM], nrecvp[DLESM_MAXCOMM];
+} dlesm_comms;
+
+/* map_comms (src/parallel_comms_mod.f90:178-1172) for rank `irank1` of `nranks`.
+ * pbc_x / pbc_y: wrap-around neighbours (extension; the reference aborts if pbc).
+ * Unused slots hold -999 like the reference's initialisation (:246-261). */
+int dlesm_map_comms(const dlesm_decomp_t *d, int irank1, int nranks, int pbc_x, int pbc_y,
+                    int halo_depth_x, int halo_depth_y, dlesm_comms *out);
+/* iprocmap (:1365-1398): owner (1-based) of global point (ia, ja) or 0 */
+int dlesm_iprocmap(const dlesm_decomp_t *d, int nranks, int ia, int ja);
+
+/* ------------------------------------------------------------------------------------ */
+/* HOST MIRROR: grid_type -- src/grid_mod.f90:75-157                                     */
+/* ------------------------------------------------------------------------------------ */
+typedef struct dlesm_grid dlesm_grid_t;
+
+typedef struct {
+    int name, offset;
+    int global_nx, global_ny;
+    int nx, ny;                 /* padded local allocation (src/grid_mod.f90:368-385) */
+    double dx, dy;
+    int boundary_conditions[3];
+    dlesm_subdomain subdomain;
+    int alignment, padding;     /* DL_ESM_ALIGNMENT value used and columns added */
+    int initialised;            /* grid_init done */
+} dlesm_grid_info;
+
+/* grid_constructor (src/grid_mod.f90:217-304).  grid_offsets < 0 means "not present",
+ * which is an error exactly as in the reference (:241-246). */
+dlesm_grid_t *dlesm_grid_create(int grid_name, const int boundary_conditions[3], int grid_offsets);
+/* grid%decompose (src/grid_mod.f90:183-211) */
+int dlesm_grid_decompose(dlesm_grid_t *g, int domainx, int domainy, int ndomains, int ndomainx,
+                         int ndomainy, int halo_width);
+/* grid_init (src/grid_mod.f90:330-570).  tmask may be NULL (all-wet); otherwise column-major
+ * tmask(tmask_nx, tmask_ny), indexed with the LOCAL indices of the subdomain like the
+ * Fortran dummy.  Reads DL_ESM_ALIGNMENT from the environment like the reference. */
+int dlesm_grid_init(dlesm_grid_t *g, double dxarg, double dyarg, const int *tmask, int tmask_nx,
+                    int tmask_ny);
+int dlesm_grid_get_info(const dlesm_grid_t *g, dlesm_grid_info *out);
+const dlesm_decomp_t *dlesm_grid_decomp(const dlesm_grid_t *g);
+int dlesm_grid_comms(const dlesm_grid_t *g, dlesm_comms *out);
+/* Grid arrays.  `which` is one of DLESM_GRID_*.  Host copies are written into caller
+ * memory (column-major nx*ny); device copies are materialised on first request and cached
+ * (the reference leaves the 17 *_device c_ptr slots NULL for the user to fill,
+ * src/grid_mod.f90:286-302). */
+#define DLESM_GRID_TMASK 0
+#define DLESM_GRID_DX_T 1
+#define DLESM_GRID_DY_T 2
+#define DLESM_GRID_DX_U 3
+#define DLESM_GRID_DY_U 4
+#define DLESM_GRID_DX_V 5
+#define DLESM_GRID_DY_V 6
+#define DLESM_GRID_DX_F 7
+#define DLESM_GRID_DY_F 8
+#define DLESM_GRID_AREA_T 9
+#define DLESM_GRID_AREA_U 10
+#define DLESM_GRID_AREA_V 11
+#define DLESM_GRID_GPHIU 12
+#define DLESM_GRID_GPHIV 13
+#define DLESM_GRID_GPHIF 14
+#define DLESM_GRID_XT 15
+#define DLESM_GRID_YT 16
+int dlesm_grid_host_array(dlesm_grid_t *g, int which, void *out /* int32 or double nx*ny */);
+int dlesm_grid_device_array(dlesm_grid_t *g, int which, void **device_ptr);
+void dlesm_grid_free(dlesm_grid_t *g);
+
+/* ------------------------------------------------------------------------------------ */
+/* HOST MIRROR: r2d_field -- src/field_mod.f90:110-166                                   */
+/* ------------------------------------------------------------------------------------ */
+typedef struct dlesm_field dlesm_field_t;
+
+typedef struct {
+    int defined_on;
+    dlesm_region internal;
+    dlesm_region whole;
+    int num_halos;        /* -1 where the reference leaves it unset (cv/ct/cf_ne_init) */
+    dlesm_halo halo[4];
+    int nx, ny;           /* allocation = grid%nx, grid%ny (src/field_mod.f90:327-333) */
+    int ntiles;
+    int data_on_device;   /* always 1: storage is device-resident */
+    void *device_ptr;
+} dlesm_field_info;
+
+/* r2d_field(grid, grid_points [, do_tile] [, init_global_data]) -- src/field_mod.f90:242-390.
+ * Device storage is allocated and zero-filled; init_global_data (column-major
+ * (gnx, gny), may be NULL) is scattered as :378-389. */
+dlesm_field_t *dlesm_r2d_field_create(dlesm_grid_t *g, int grid_points, int do_tile,
+                                      const double *init_global_data, int gnx, int gny);
+int dlesm_field_get_info(const dlesm_field_t *f, dlesm_field_info *out);
+/* set_field_bounds only (src/field_mod.f90:563-624): the regions and halo list a field of
+ * this point type would get; no storage is allocated, so it works without a GPU
+ * (device_ptr = NULL, data_on_device = 0 in the result). */
+int dlesm_grid_field_bounds(const dlesm_grid_t *g, int grid_points, dlesm_field_info *out);
+/* set_data / get_data (:530-559): whole-array host <-> device */
+int dlesm_field_set_data(dlesm_field_t *f, const double *host_array);
+int dlesm_field_get_data(dlesm_field_t *f, double *host_array);
+/* write_to_device / read_from_device (:407-525): 1-based sub-rectangle of the padded array;
+ * `host_array` is the full (nx, ny) host array.  Pass 1,1,nx,ny for the defaults. */
+int dlesm_field_write_to_device(dlesm_field_t *f, const double *host_array, int startx, int starty,
+                                int nx, int ny, bool blocking);
+int dlesm_field_read_from_device(dlesm_field_t *f, double *host_array, int startx, int starty,
+                                 int nx, int ny, bool blocking);
+/* fld%halo_exchange(depth) (:1231-1256): device-resident, all 8 directions */
+int dlesm_field_halo_exchange(dlesm_field_t *f, int depth);
+/* several fields in one grouped exchange (one message per neighbour) */
+int dlesm_fields_halo_exchange(dlesm_field_t *const *f, int nfields, int depth);
+/* serial periodic BCs: copy_field(fld, halo%source, halo%dest) for ihalo = 1..num_halos */
+int dlesm_field_apply_periodic_halos(dlesm_field_t *f);
+/* gather_inner_data (:1313-1390): global_data (global_nx, global_ny) filled on the master */
+int dlesm_field_gather_inner_data(dlesm_field_t *f, double *global_data);
+/* copy_field overloads (:1126-1187) */
+int dlesm_copy_field(const dlesm_field_t *field_in, dlesm_field_t *field_out);
+int dlesm_copy_field_patch(dlesm_field_t *field, const dlesm_region *src, const dlesm_region *dest);
+/* set_field (:1191-1202) */
+int dlesm_set_field(dlesm_field_t *fld, double val);
+/* field_checksum (:1209-1219): SUM(ABS(internal region)) then global_sum */
+int dlesm_field_checksum(dlesm_field_t *field, double *val);
+/* free_field (:395-403); also releases the device storage */
+int dlesm_free_field(dlesm_field_t *fld);
+
+/* ------------------------------------------------------------------------------------ */
+/* DEVICE LAYER: storage and the data_on_device hooks                                    */
+/* ------------------------------------------------------------------------------------ */
+/* Allocate a zero-filled (nx, ny) FP64 device array; registers its pitch so that the
+ * hook signature below (which carries no pitch) can address sub-rectangles. */
+int dlesm_dev_field_alloc(int nx, int ny, void **device_ptr);
+int dlesm_dev_field_free(void *device_ptr);
+/* EXACTLY the reference's C-flavoured hook signature (src/field_mod.f90:66-72, 87-93):
+ * read:  from = device_ptr, to = C_LOC(data);  write: from = C_LOC(data), to = device_ptr.
+ * (startx, starty, nx, ny) is a 1-based sub-rectangle of the padded array; element (i,j)
+ * lives at (j-1)*size(data,1)+(i-1).  Non-blocking copies are ordered on one stream; a
+ * blocking call synchronises it (the reference only blocks on the last of four). */
+void dlesm_read_from_device_c(void *from, void *to, int startx, int starty, int nx, int ny,
+                              bool blocking);
+void dlesm_write_to_device_c(void *from, void *to, int startx, int starty, int nx, int ny,
+                             bool blocking);
+int dlesm_dev_sync(void);
+/* Page-locked host memory for the host mirror of fld%data (fast, truly asynchronous hook
+ * copies); or pin an existing allocation (a Fortran allocatable) in place. */
+int dlesm_host_alloc(size_t bytes, void **host_ptr);
+int dlesm_host_free(void *host_ptr);
+int dlesm_host_register(void *host_ptr, size_t bytes);
+int dlesm_host_unregister(void *host_ptr);
+/* CUDA-event stopwatch on the library's stream (slots 0..15): record, then read the
+ * elapsed milliseconds between two recorded slots (synchronises on the later one). */
+int dlesm_event_record(int slot);
+int dlesm_event_elapsed_ms(int slot_start, int slot_stop, double *ms);
+
+/* ------------------------------------------------------------------------------------ */
+/* DEVICE LAYER: field operations on device pointers from dlesm_dev_field_alloc          */
+/* ------------------------------------------------------------------------------------ */
+int dlesm_dev_copy_field(const void *field_in, void *field_out);                  /* :1152 */
+int dlesm_dev_copy_patch(void *field, int sxstart, int sxstop, int systart, int systop,
+                         int dxstart, int dxstop, int dystart, int dystop);       /* :1179 */
+int dlesm_dev_set_field(void *field, double val);                                 /* :1191 */
+/* local SUM(ABS(field(xstart:xstop, ystart:ystop))) -- :1289-1302; deterministic two-pass
+ * tree (no atomics).  Follow with dlesm_global_sum for :1305. */
+int dlesm_dev_checksum(const void *field, int xstart, int xstop, int ystart, int ystop,
+                       double *val);
+/* periodic halo fill for a field whose internal region is the given box: E, W columns then
+ * N, S rows over xstart-1:xstop+1 (src/field_mod.f90:1394-1464) */
+int dlesm_dev_periodic_halos(void *field, int xstart, int xstop, int ystart, int ystop,
+                             int periodic_x, int periodic_y);
+/* Install the comm tables computed by the (unchanged Fortran or mirrored) map_comms for this
+ * rank; later dlesm_dev_halo_exchange calls use them. */
+int dlesm_dev_set_comms(const dlesm_comms *tables);
+/* exchange_generic (src/parallel_comms_mod.f90:1501-1855) on device-resident fields: fused
+ * pack kernel -> grouped NCCL send/recv (self-neighbours: on-device) -> fused unpack kernel */
+int dlesm_dev_halo_exchange(void *const *fields, int nfields);
+/* Upload grid arrays once (grid_mod would call this at the end of grid_init): tmask int32
+ * (nx,ny) and 16 FP64 metric arrays in the DLESM_GRID_* order (NULL entries are skipped);
+ * device_ptrs[17] receives the 17 *_device values of src/grid_mod.f90:104-150. */
+int dlesm_dev_grid_upload(int nx, int ny, const int *tmask, const double *const metrics[16],
+                          void *device_ptrs[17]);
+
+/* ------------------------------------------------------------------------------------ */
+/* DEVICE LAYER: shallow-water stencils (SURVEY.md a-S).  One launcher per kernel of the  */
+/* un-fused formulation; each sweeps the OUTPUT field's internal region                  */
+/* (xstart:xstop, ystart:ystop), like the PSy-layer loop nest of SURVEY CS-3.            */
+/* tmask: device int32 (nx,ny) or NULL (all wet); masked rule in DESIGN.md.              */
+/* ------------------------------------------------------------------------------------ */
+int dlesm_compute_cu(void *cu, const void *p, const void *u, int xstart, int xstop, int ystart,
+                     int ystop, const void *tmask);
+int dlesm_compute_cv(void *cv, const void *p, const void *v, int xstart, int xstop, int ystart,
+                     int ystop, const void *tmask);
+int dlesm_compute_z(void *z, const void *p, const void *u, const void *v, double dx, double dy,
+                    int xstart, int xstop, int ystart, int ystop, const void *tmask);
+int dlesm_compute_h(void *h, const void *p, const void *u, const void *v, int xstart, int xstop,
+                    int ystart, int ystop, const void *tmask);
+int dlesm_compute_unew(void *unew, const void *uold, const void *z, const void *cv, const void *h,
+                       double tdt, double dx, int xstart, int xstop, int ystart, int ystop,
+                       const void *tmask, const void *ucur);
+int dlesm_compute_vnew(void *vnew, const void *vold, const void *z, const void *cu, const void *h,
+                       double tdt, double dy, int xstart, int xstop, int ystart, int ystop,
+                       const void *tmask, const void *vcur);
+int dlesm_compute_pnew(void *pnew, const void *pold, const void *cu, const void *cv, double tdt,
+                       double dx, double dy, int xstart, int xstop, int ystart, int ystop,
+                       const void *tmask, const void *pcur);
+/* points = DLESM_GO_U/V/T_POINTS selects the cells the mask rule looks at */
+int dlesm_time_smooth(const void *f, const void *fnew, void *fold, double alpha, int xstart,
+                      int xstop, int ystart, int ystop, const void *tmask, int points);
+/* The whole step fused into one sweep: reads u,v,p (with valid depth-1 halos) and
+ * uold,vold,pold; writes unew,vnew,pnew on the internal region and, unless `first`, the
+ * time-filtered uold,vold,pold in place.  96 B / point.  Halos of the new fields are NOT
+ * filled (follow with dlesm_dev_periodic_halos or dlesm_dev_halo_exchange).  `variant`
+ * selects the kernel (0 = default/best; others documented in DESIGN.md, for benchmarking). */
+int dlesm_sw_step_fused(const void *u, const void *v, const void *p, void *uold, void *vold,
+                        void *pold, void *unew, void *vnew, void *pnew, double dx, double dy,
+                        double tdt, double alpha, int first, int xstart, int xstop, int ystart,
+                        int ystop, const void *tmask, int variant);
+
+/* ------------------------------------------------------------------------------------ */
+/* HOST MIRROR: the application ("PSy") layer for the shallow-water model -- not part of  */
+/* the reference library; provided so that tests/bench drive the fields the way a GOcean   */
+/* application would.                                                                     */
+/* ------------------------------------------------------------------------------------ */
+typedef struct dlesm_sw dlesm_sw_t;
+#define DLESM_SW_UNFUSED 0 /* one launch per reference-style kernel, copy_field rotation */
+#define DLESM_SW_FUSED 1   /* single fused sweep, pointer rotation                       */
+/* field ids for dlesm_sw_field */
+enum { DLESM_SW_U = 0, DLESM_SW_V, DLESM_SW_P, DLESM_SW_UOLD, DLESM_SW_VOLD, DLESM_SW_POLD,
+       DLESM_SW_UNEW, DLESM_SW_VNEW, DLESM_SW_PNEW, DLESM_SW_CU, DLESM_SW_CV, DLESM_SW_Z,
+       DLESM_SW_H, DLESM_SW_NFIELDS };
+
+dlesm_sw_t *dlesm_sw_create(dlesm_grid_t *g, double dt, double alpha, int mode, int use_tmask);
+/* classic "shallow" initial conditions computed on the device (synthetic data) */
+int dlesm_sw_init_device(dlesm_sw_t *s);
+/* initial u,v,p from host arrays (nx,ny) incl. valid halos; uold,vold,pold <- copies */
+int dlesm_sw_set_state(dlesm_sw_t *s, const double *u, const double *v, const double *p);
+int dlesm_sw_step(dlesm_sw_t *s, int nsteps);
+dlesm_field_t *dlesm_sw_field(dlesm_sw_t *s, int which);
+int dlesm_sw_set_variant(dlesm_sw_t *s, int variant);
+/* kernels launched by this library since process start (all streams) */
+long long dlesm_kernel_launch_count(void);
+/* CUDA-event time (ms) spent in dominant-kernel launches since the last call with reset=1,
+ * and their count; enabled by dlesm_profile_enable(1) (adds event records around each
+ * fused-step launch; used by bench.py for the roofline figure) */
+int dlesm_profile_enable(int on);
+int dlesm_profile_read(double *ms_total, long long *nlaunches, int reset);
+void dlesm_sw_free(dlesm_sw_t *s);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DLESM_B200_H */

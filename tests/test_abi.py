@@ -1,0 +1,109 @@
+"""CPU tests of the drop-in boundary: the C-ABI library loads without a GPU, exports every
+symbol include/dlesm_b200.h declares (and nothing undeclared under the dlesm_ prefix), the
+Python binding covers all of them, and device entry points fail loudly -- never fall back."""
+import ctypes as C
+import os
+import re
+import subprocess
+
+import pytest
+
+import dl_esm_inf_b200 as fd
+from dl_esm_inf_b200 import _lib
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HEADER = os.path.join(ROOT, "include", "dlesm_b200.h")
+
+
+def declared_symbols():
+    text = open(HEADER).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return set(re.findall(r"\b(dlesm_[a-z0-9_]+)\s*\(", text))
+
+
+def exported_symbols():
+    out = subprocess.run(["nm", "-D", "--defined-only", _lib.LIB_PATH], capture_output=True, text=True,
+                         check=True).stdout
+    return {ln.split()[-1] for ln in out.splitlines() if " T " in ln and ln.split()[-1].startswith("dlesm_")}
+
+
+def test_header_library_and_binding_agree():
+    decl, exp, bound = declared_symbols(), exported_symbols(), set(_lib.SIGNATURES)
+    assert decl == exp, (sorted(decl - exp), sorted(exp - decl))
+    assert decl == bound, (sorted(decl - bound), sorted(bound - decl))
+    L = _lib.lib()
+    for name in decl:
+        assert hasattr(L, name)
+
+
+def test_no_torch_or_cxx_types_in_the_abi():
+    text = re.sub(r"/\*.*?\*/", "", open(HEADER).read(), flags=re.S)   # code only
+    assert "torch" not in text and "std::" not in text and "template" not in text
+    assert 'extern "C"' in text
+
+
+def test_product_never_touches_the_oracle():
+    """the oracle is test infrastructure: nothing under dl_esm_inf_b200/ may import, link or
+    load it (a product path through the oracle would void every parity claim)"""
+    pkg = os.path.join(ROOT, "dl_esm_inf_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for fn in files:
+            if fn.endswith((".py", ".cu", ".cuh", ".cpp", ".hpp", ".h", ".f90", ".F90")):
+                src = open(os.path.join(dirpath, fn), errors="ignore").read()
+                assert "liboracle" not in src and "from oracle" not in src and "import oracle" not in src, fn
+    ldd = subprocess.run(["ldd", _lib.LIB_PATH], capture_output=True, text=True).stdout
+    assert "oracle" not in ldd
+
+
+def test_device_entry_points_fail_loudly_without_gpu():
+    L = _lib.lib()
+    p = C.c_void_p()
+    rc = L.dlesm_dev_field_alloc(8, 8, C.byref(p))
+    if rc == 0:   # a GPU is present (running on the B200 box): nothing to check here
+        L.dlesm_dev_field_free(p)
+        pytest.skip("GPU present")
+    assert rc == -20 and b"no CPU fallback" in L.dlesm_last_error()
+    fd.gocean_initialise(1, 1)
+    g = fd.grid_type(fd.GO_ARAKAWA_C, (fd.GO_BC_EXTERNAL, fd.GO_BC_EXTERNAL, fd.GO_BC_NONE), fd.GO_OFFSET_NE)
+    g.decompose(4, 10)
+    fd.grid_init(g, 1.0, 1.0)
+    with pytest.raises(fd.GoceanStop) as e:
+        fd.r2d_field(g, fd.GO_T_POINTS)
+    assert e.value.code == -20
+
+
+def test_grid_constructor_validation():
+    """src/grid_mod.f90:241-278"""
+    fd.gocean_initialise(1, 1)
+    bcs = (fd.GO_BC_EXTERNAL, fd.GO_BC_EXTERNAL, fd.GO_BC_NONE)
+    with pytest.raises(fd.GoceanStop) as e:
+        fd.grid_type(fd.GO_ARAKAWA_C, bcs)                    # offset is "optional" but required
+    assert e.value.code == -8
+    with pytest.raises(fd.GoceanStop) as e:
+        fd.grid_type(7, bcs, fd.GO_OFFSET_NE)
+    assert e.value.code == -7
+    with pytest.raises(fd.GoceanStop) as e:
+        fd.grid_type(fd.GO_ARAKAWA_C, bcs, fd.GO_OFFSET_ANY)
+    assert e.value.code == -8
+    g = fd.grid_type(fd.GO_ARAKAWA_B, bcs, fd.GO_OFFSET_SE)
+    assert g.name == fd.GO_ARAKAWA_B and g.offset == fd.GO_OFFSET_SE
+
+
+def test_periodic_with_several_ranks_is_refused_like_the_reference():
+    """src/grid_mod.f90:437-442, 559-564; allowed only with the explicit extension flag"""
+    bcs = (fd.GO_BC_PERIODIC, fd.GO_BC_PERIODIC, fd.GO_BC_NONE)
+    fd.gocean_initialise(1, 4)
+    fd.set_extensions(0)
+    g = fd.grid_type(fd.GO_ARAKAWA_C, bcs, fd.GO_OFFSET_SW)
+    g.decompose(16, 16)
+    with pytest.raises(fd.GoceanStop) as e:
+        fd.grid_init(g, 1.0, 1.0)
+    assert e.value.code == -6
+    fd.set_extensions(fd.EXT_PERIODIC_DISTMEM)
+    try:
+        fd.grid_init(g, 1.0, 1.0)
+        c = g.comms
+        assert c.nsend == 8 and c.nrecv == 8      # wrap-around: every tile has 8 neighbours
+    finally:
+        fd.set_extensions(0)
+        fd.gocean_initialise(1, 1)

@@ -1,0 +1,223 @@
+"""CPU tests: the product's host-side bookkeeping (C++ behind the C ABI, no GPU needed)
+against the oracle, bit-exact, over the reference's own configurations and many more."""
+import itertools
+import os
+
+import numpy as np
+import pytest
+
+import dl_esm_inf_b200 as fd
+from oracle import oracle as O
+
+BCS_EXT = (fd.GO_BC_EXTERNAL, fd.GO_BC_EXTERNAL, fd.GO_BC_NONE)
+BCS_PER = (fd.GO_BC_PERIODIC, fd.GO_BC_PERIODIC, fd.GO_BC_NONE)
+
+
+def region_eq(a, b):
+    return a.astuple() == b.astuple()
+
+
+def box_eq(a, b):
+    return a.box() == b.box()
+
+
+DECOMP_CASES = [
+    # (domainx, domainy, nranks, kwargs)
+    (4, 10, 1, {}), (4, 10, 2, {}), (10, 4, 2, {}), (4, 10, 4, {}), (4, 10, 6, {}),
+    (10, 10, 4, {}), (10, 10, 6, {}), (10, 10, 3, {}), (10, 10, 7, {}), (10, 10, 8, {}),
+    (16384, 16384, 2, {}), (16384, 16384, 4, {}), (16384, 16384, 8, {}),
+    (16384, 32768, 2, {}), (32768, 32768, 4, {}), (32768, 65536, 8, {}),
+    (33, 17, 5, {}), (17, 33, 12, {}), (100, 7, 9, {}), (1, 1, 1, {}), (5, 3, 16, {}),
+    (64, 64, 1, dict(ndomains=4)), (64, 48, 1, dict(ndomainx=3, ndomainy=2)),
+    (64, 48, 6, dict(ndomainx=2, ndomainy=3)), (50, 50, 4, dict(halo_width=2)),
+    (50, 50, 1, dict(halo_width=0)), (1024, 1024, 1, {}),
+]
+
+
+@pytest.mark.parametrize("dx_,dy_,nranks,kw", DECOMP_CASES)
+def test_go_decompose_matches_oracle(dx_, dy_, nranks, kw):
+    O.reset_saved_state()
+    fd.gocean_initialise(1, nranks)
+    want = O.go_decompose(dx_, dy_, nranks=nranks, **kw)
+    got = fd.go_decompose(dx_, dy_, **kw)
+    assert (got.global_nx, got.global_ny, got.nx, got.ny, got.ndomains, got.max_width,
+            got.max_height, got.domperrank) == (
+        want.global_nx, want.global_ny, want.nx, want.ny, want.ndomains, want.max_width,
+        want.max_height, want.domperrank)
+    subs = got.subdomains
+    for k in range(want.ndomains):
+        assert region_eq(subs[k].glob, want.subdomains[k].glob), k
+        assert region_eq(subs[k].internal, want.subdomains[k].internal), k
+    for r in range(1, nranks + 1):
+        for s in range(1, want.domperrank + 1):
+            assert got.proc_subdomains(s, r) == want.proc_subdomains[(r - 1) * want.domperrank + (s - 1)]
+
+
+def test_go_decompose_saved_halo_width():
+    """halo_width sticks between calls (SAVEd local, src/parallel_mod.f90:103-105)."""
+    O.reset_saved_state()
+    fd.gocean_initialise(1, 1)
+    for kw in (dict(halo_width=3), {}):
+        want = O.go_decompose(20, 20, nranks=1, **kw)
+        got = fd.go_decompose(20, 20, **kw)
+        assert got.subdomains[0].internal.xstart == want.subdomains[0].internal.xstart == 4
+
+
+def test_go_decompose_errors():
+    fd.gocean_initialise(1, 2)
+    with pytest.raises(fd.GoceanStop) as e:
+        fd.go_decompose(10, 10, ndomainx=2)
+    assert e.value.code == O.ERR_ARGS
+    with pytest.raises(O.OracleStop) as eo:
+        O.go_decompose(10, 10, ndomainx=2, nranks=2)
+    assert eo.value.code == e.value.code
+    with pytest.raises(fd.GoceanStop) as e:
+        fd.go_decompose(10, 10, halo_width=0)
+    with pytest.raises(O.OracleStop) as eo:
+        O.go_decompose(10, 10, halo_width=0, nranks=2)
+    assert e.value.code == eo.value.code == O.ERR_HALO_WIDTH
+
+
+@pytest.mark.parametrize("dx_,dy_,nranks", [(4, 10, 2), (10, 4, 2), (10, 10, 4), (10, 10, 6),
+                                             (4, 10, 4), (4, 10, 6), (64, 48, 12), (33, 17, 5),
+                                             (16384, 16384, 8), (100, 7, 9), (5, 3, 15), (9, 9, 9)])
+def test_map_comms_matches_oracle_on_every_rank(dx_, dy_, nranks):
+    O.reset_saved_state()
+    fd.gocean_initialise(1, nranks)
+    want_d = O.go_decompose(dx_, dy_, nranks=nranks)
+    got_d = fd.go_decompose(dx_, dy_)
+    names = [n for n, _ in fd.Comms._fields_ if n not in ("nsend", "nrecv")]
+    for rank in range(1, nranks + 1):
+        want = O.map_comms(want_d, rank, nranks)
+        got = fd.map_comms(got_d, rank, nranks)
+        assert (got.nsend, got.nrecv) == (want.nsend, want.nrecv)
+        for n in names:
+            cnt = want.nsend if n in ("dirsend", "destination", "isrcsend", "jsrcsend", "idessend",
+                                      "jdessend", "nxsend", "nysend", "nsendp") else want.nrecv
+            assert list(getattr(got, n))[:cnt] == list(getattr(want, n))[:cnt], (rank, n)
+            # unused slots keep the reference's -999 initialisation
+            assert all(v == -999 for v in list(getattr(got, n))[cnt:]), (rank, n)
+        for ia, ja in itertools.product((0, 1, dx_ // 2 + 1, dx_, dx_ + 1), (0, 1, dy_ // 2 + 1, dy_, dy_ + 1)):
+            assert fd.iprocmap(got_d, ia, ja, nranks) == O.lib().orc_iprocmap(want_d, nranks, ia, ja)
+
+
+def test_map_comms_maxcomm_and_depth_errors():
+    fd.gocean_initialise(1, 4)
+    d = fd.go_decompose(10, 10)
+    with pytest.raises(fd.GoceanStop) as e:
+        fd.map_comms(d, 1, 4, halo_depths=(2, 2))
+    assert e.value.code == O.ERR_HALO_DEPTH
+    with pytest.raises(O.OracleStop) as eo:
+        O.map_comms(O.go_decompose(10, 10, nranks=4), 1, 4, halo_depths=(2, 2))
+    assert eo.value.code == O.ERR_HALO_DEPTH
+
+
+@pytest.mark.parametrize("env,ok", [(None, 1), ("1", 1), ("64", 64), ("8", 8), ("128", 128), (" 16", 16),
+                                    ("999", 999), ("1000", O.ERR_ALIGN_DIGITS), ("0", O.ERR_ALIGN_VALUE),
+                                    ("-4", O.ERR_ALIGN_VALUE), ("abc", O.ERR_ALIGN_VALUE),
+                                    ("4x", O.ERR_ALIGN_VALUE)])
+def test_alignment_env_matches_oracle(env, ok, monkeypatch):
+    if env is None:
+        monkeypatch.delenv("DL_ESM_ALIGNMENT", raising=False)
+    else:
+        monkeypatch.setenv("DL_ESM_ALIGNMENT", env)
+    fd.gocean_initialise(1, 1)
+    g = fd.grid_type(fd.GO_ARAKAWA_C, BCS_EXT, fd.GO_OFFSET_NE)
+    g.decompose(5, 5)
+    if ok > 0:
+        assert O.parse_alignment(env) == ok
+        fd.grid_init(g, 1.0, 1.0)
+        gd = O.GridDims()
+        sub = O.go_decompose(5, 5).subdomains[0]
+        O.lib().orc_grid_dims_compute(sub, ok, gd)
+        assert (g.nx, g.ny, g.info.padding, g.info.alignment) == (gd.nx, gd.ny, gd.padding, ok)
+        assert g.nx % ok == 0 and g.nx > sub.glob.nx
+    else:
+        with pytest.raises(O.OracleStop) as eo:
+            O.parse_alignment(env)
+        with pytest.raises(fd.GoceanStop) as e:
+            fd.grid_init(g, 1.0, 1.0)
+        assert e.value.code == eo.value.code == ok
+
+
+GRID_CASES = [
+    # (nx, ny, nranks, offset, bcs, alignment, with_tmask, dx, dy)
+    (4, 10, 1, fd.GO_OFFSET_NE, BCS_EXT, 1, True, 1.0, 1.0),
+    (4, 10, 2, fd.GO_OFFSET_NE, BCS_EXT, 1, True, 1.0, 1.0),
+    (10, 10, 6, fd.GO_OFFSET_NE, BCS_EXT, 1, True, 1.0, 1.0),
+    (10, 10, 4, fd.GO_OFFSET_NE, BCS_EXT, 1, False, 1.0, 1.0),
+    (5, 5, 1, fd.GO_OFFSET_NE, BCS_EXT, 64, True, 1.0, 1.0),
+    (37, 23, 6, fd.GO_OFFSET_NE, BCS_EXT, 8, True, 0.1, 0.3),
+    (64, 48, 1, fd.GO_OFFSET_SW, BCS_PER, 1, False, 1.0e5, 1.0e5),
+    (64, 48, 1, fd.GO_OFFSET_SW, BCS_PER, 64, True, 1000.0, 2000.0),
+    (30, 30, 1, fd.GO_OFFSET_SW, (fd.GO_BC_EXTERNAL, fd.GO_BC_PERIODIC, fd.GO_BC_NONE), 1, True, 1.0, 1.0),
+    (1024, 1024, 1, fd.GO_OFFSET_SW, BCS_PER, 1, False, 1.0e5, 1.0e5),
+]
+
+
+def _random_tmask(sub, seed):
+    rng = np.random.default_rng(seed)
+    return np.asfortranarray(rng.integers(-1, 2, size=(sub.glob.nx, sub.glob.ny)).astype(np.int32))
+
+
+@pytest.mark.parametrize("nx_,ny_,nranks,offset,bcs,align,with_tmask,dx,dy", GRID_CASES)
+def test_grid_init_and_field_bounds_match_oracle(nx_, ny_, nranks, offset, bcs, align, with_tmask,
+                                                 dx, dy, monkeypatch):
+    monkeypatch.setenv("DL_ESM_ALIGNMENT", str(align))
+    for rank in range(1, nranks + 1):
+        O.reset_saved_state()
+        fd.gocean_initialise(rank, nranks)
+        og = O.Grid(O.GO_ARAKAWA_C, bcs, offset)
+        og.decompose(nx_, ny_, rank=rank, nranks=nranks)
+        tm = _random_tmask(og.subdomain, 100 * rank + nx_) if with_tmask else None
+        og.init(dx, dy, tmask=tm, alignment=align)
+        g = fd.grid_type(fd.GO_ARAKAWA_C, bcs, offset)
+        g.decompose(nx_, ny_)
+        fd.grid_init(g, dx, dy, tmask=tm)
+        assert (g.nx, g.ny, g.global_nx, g.global_ny) == (og.nx, og.ny, og.global_nx, og.global_ny)
+        assert region_eq(g.subdomain.glob, og.subdomain.glob)
+        assert region_eq(g.subdomain.internal, og.subdomain.internal)
+        assert (g.dx, g.dy) == (og.dx, og.dy)
+        # tmask: everywhere when a mask was supplied; inside the initialised box otherwise
+        got_t = g.get_tmask()
+        if with_tmask:
+            assert np.array_equal(got_t, og.tmask)
+        else:
+            defined = og.tmask != O.TMASK_UNSET
+            assert defined.any() and np.array_equal(got_t[defined], og.tmask[defined])
+        # metrics: bit-exact, including the running-sum coordinates
+        if nx_ <= 64:
+            for name in O.METRIC_NAMES:
+                assert np.array_equal(getattr(g, name), og.metrics[name]), name
+        else:
+            for name in ("xt", "yt", "area_t"):
+                assert np.array_equal(getattr(g, name), og.metrics[name]), name
+        # comm tables installed by grid_init (only with more than one rank)
+        if nranks > 1:
+            assert list(g.comms.nxsend)[:g.comms.nsend] == list(og.comms.nxsend)[:og.comms.nsend]
+        # field bounds for every point type (device storage is not touched: bounds only)
+        for pts in (fd.GO_U_POINTS, fd.GO_V_POINTS, fd.GO_T_POINTS, fd.GO_F_POINTS, fd.GO_ALL_POINTS):
+            try:
+                want = O.field_bounds(og, pts)
+                want_err = None
+            except O.OracleStop as e:
+                want, want_err = None, e.code
+            fb = _product_bounds(g, pts)
+            if want_err is not None:
+                assert fb == want_err, pts
+                continue
+            assert not isinstance(fb, int), (pts, fb)
+            assert fb.defined_on == want.defined_on
+            assert region_eq(fb.internal, want.internal) and region_eq(fb.whole, want.whole)
+            assert fb.num_halos == want.num_halos
+            for k in range(max(want.num_halos, 0)):
+                assert box_eq(fb.halo[k].source, want.halo[k].source)
+                assert box_eq(fb.halo[k].dest, want.halo[k].dest)
+
+
+def _product_bounds(g, pts):
+    """set_field_bounds through the C ABI (host only); gocean_stop branches give their code"""
+    try:
+        return g.field_bounds(pts)
+    except fd.GoceanStop as e:
+        return e.code
