@@ -212,18 +212,23 @@ struct TmaStepParams {
     int pitch;
     Box b;
     int seg_rows;
+    int i_origin;   // first output column (1-based) of strip 0: b.xs, or lower to align strips to 128 B
     SwScalars sc;
 };
 
+constexpr int kDefaultTmaVariant = 25;
 constexpr int align128(int v) { return (v + 127) & ~127; }
 
 template <int TX, int RY, int STAGES>
 struct TmaCfg {
-    static constexpr int BW = TX + 2;
-    static constexpr int A = align128(BW * RY * 8);  // p,u,v tiles (with halo columns)
-    static constexpr int B = align128(TX * RY * 8);  // uold,vold,pold tiles
-    static constexpr int STAGE_BYTES = 3 * A + 3 * B;
-    static constexpr int TX_BYTES = 3 * BW * RY * 8 + 3 * TX * RY * 8;
+    // TMA needs the first element of a box 16-byte aligned (even FP64 column; measured with
+    // tools/tma_probe.cu: an odd start column raises "illegal instruction").  Every tile
+    // therefore starts at the even column at or below the strip's west halo column and is
+    // TX + 4 wide, which covers west halo + TX + east halo for either parity.
+    static constexpr int BW = TX + 4;
+    static constexpr int A = align128(BW * RY * 8);
+    static constexpr int STAGE_BYTES = 6 * A;
+    static constexpr int TX_BYTES = 6 * BW * RY * 8;
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 2 * STAGES * 8 + 128;
     static constexpr int THREADS = TX + 32;
 };
@@ -249,7 +254,7 @@ fused_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_constant
     const int j1 = min(j0 + prm.seg_rows - 1, prm.b.ye);
     const int nsteps = (j1 - j0 + 1) + 2;            // raw rows j0-1 .. j1+1
     const int nchunks = (nsteps + RY - 1) / RY;
-    const int i_first = prm.b.xs + blockIdx.x * TX;   // first output column of this strip
+    const int i_first = prm.i_origin + blockIdx.x * TX;   // first output column of this strip
 
     if (tid == 0) {
         for (int s = 0; s < STAGES; ++s) {
@@ -264,8 +269,7 @@ fused_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_constant
     if (warp == TX / 32) {
         // ---- producer warp: one lane feeds the ring ----
         if (lane == 0) {
-            const int x_raw = i_first - 2;   // 0-based element column of the west halo column
-            const int x_old = i_first - 1;
+            const int x_box = (i_first - 2) & ~1;   // even 0-based column at/below the west halo column
             for (int c = 0; c < nchunks; ++c) {
                 const int s = c % STAGES;
                 if (c >= STAGES) mbar_wait(&empty[s], ((c / STAGES) - 1) & 1);
@@ -273,12 +277,12 @@ fused_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_constant
                 const int y_raw = (j0 - 1) + c * RY - 1;   // 0-based row of the chunk's first raw row
                 const int y_old = y_raw - 1;               // outputs trail the raw rows by one
                 mbar_expect_tx(&full[s], Cfg::TX_BYTES);
-                tma_load_2d(st + 0 * Cfg::A, &tm_p, x_raw, y_raw, &full[s]);
-                tma_load_2d(st + 1 * Cfg::A, &tm_u, x_raw, y_raw, &full[s]);
-                tma_load_2d(st + 2 * Cfg::A, &tm_v, x_raw, y_raw, &full[s]);
-                tma_load_2d(st + 3 * Cfg::A + 0 * Cfg::B, &tm_uo, x_old, y_old, &full[s]);
-                tma_load_2d(st + 3 * Cfg::A + 1 * Cfg::B, &tm_vo, x_old, y_old, &full[s]);
-                tma_load_2d(st + 3 * Cfg::A + 2 * Cfg::B, &tm_po, x_old, y_old, &full[s]);
+                tma_load_2d(st + 0 * Cfg::A, &tm_p, x_box, y_raw, &full[s]);
+                tma_load_2d(st + 1 * Cfg::A, &tm_u, x_box, y_raw, &full[s]);
+                tma_load_2d(st + 2 * Cfg::A, &tm_v, x_box, y_raw, &full[s]);
+                tma_load_2d(st + 3 * Cfg::A, &tm_uo, x_box, y_old, &full[s]);
+                tma_load_2d(st + 4 * Cfg::A, &tm_vo, x_box, y_old, &full[s]);
+                tma_load_2d(st + 5 * Cfg::A, &tm_po, x_box, y_old, &full[s]);
             }
         }
         return;
@@ -286,7 +290,8 @@ fused_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_constant
 
     // ---- consumer warps ----
     const int i = i_first + tid;
-    const bool active = i <= prm.b.xe;
+    const bool active = i <= prm.b.xe && i >= prm.b.xs;
+    const int xoff = (i_first - 2) & 1;
     const SwScalars sc = prm.sc;
     Carry<false> cr;
     carry_init(cr);
@@ -299,18 +304,18 @@ fused_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_constant
         const double *sp = reinterpret_cast<const double *>(st + 0 * Cfg::A);
         const double *su = reinterpret_cast<const double *>(st + 1 * Cfg::A);
         const double *sv = reinterpret_cast<const double *>(st + 2 * Cfg::A);
-        const double *suo = reinterpret_cast<const double *>(st + 3 * Cfg::A + 0 * Cfg::B);
-        const double *svo = reinterpret_cast<const double *>(st + 3 * Cfg::A + 1 * Cfg::B);
-        const double *spo = reinterpret_cast<const double *>(st + 3 * Cfg::A + 2 * Cfg::B);
+        const double *suo = reinterpret_cast<const double *>(st + 3 * Cfg::A);
+        const double *svo = reinterpret_cast<const double *>(st + 4 * Cfg::A);
+        const double *spo = reinterpret_cast<const double *>(st + 5 * Cfg::A);
 #pragma unroll
         for (int r = 0; r < RY; ++r) {
             if (t < nsteps) {
                 Raw<false> N;
-                const int o = r * BW + tid;
+                const int o = r * BW + tid + xoff;   // west neighbour's column inside the tile
                 N.pW = sp[o]; N.pC = sp[o + 1]; N.pE = sp[o + 2];
                 N.uW = su[o]; N.uC = su[o + 1]; N.uE = su[o + 2];
                 N.vW = sv[o]; N.vC = sv[o + 1]; N.vE = sv[o + 2];
-                const double uo = suo[r * TX + tid], vo = svo[r * TX + tid], po = spo[r * TX + tid];
+                const double uo = suo[o + 1], vo = svo[o + 1], po = spo[o + 1];
                 Outs out;
                 ingest<false>(cr, N, sc, uo, vo, po, out);
                 if (t >= 2 && active) {
@@ -380,32 +385,6 @@ bool get_map(const double *base, int nx, int ny, int boxw, int boxh, CUtensorMap
     return true;
 }
 
-template <int TX, int RY, int STAGES, int MINB>
-cudaError_t launch_tma(const FusedArgs &a, int seg_rows, cudaStream_t s)
-{
-    using Cfg = TmaCfg<TX, RY, STAGES>;
-    CUtensorMap mu, mv, mp, muo, mvo, mpo;
-    if (!get_map(a.u, a.pitch, a.ny, Cfg::BW, RY, mu) || !get_map(a.v, a.pitch, a.ny, Cfg::BW, RY, mv) ||
-        !get_map(a.p, a.pitch, a.ny, Cfg::BW, RY, mp) || !get_map(a.uold, a.pitch, a.ny, TX, RY, muo) ||
-        !get_map(a.vold, a.pitch, a.ny, TX, RY, mvo) || !get_map(a.pold, a.pitch, a.ny, TX, RY, mpo))
-        return cudaErrorNotSupported;
-    TmaStepParams prm;
-    prm.unew = a.unew; prm.vnew = a.vnew; prm.pnew = a.pnew;
-    prm.uold = a.uold; prm.vold = a.vold; prm.pold = a.pold;
-    prm.pitch = a.pitch; prm.b = a.b; prm.seg_rows = seg_rows; prm.sc = a.sc;
-    auto kern = fused_tma_kernel<TX, RY, STAGES, MINB>;
-    static bool attr_done = false;
-    if (!attr_done) {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
-        if (e != cudaSuccess) return e;
-        attr_done = true;
-    }
-    const int w = a.b.xe - a.b.xs + 1, h = a.b.ye - a.b.ys + 1;
-    dim3 grid((w + TX - 1) / TX, (h + seg_rows - 1) / seg_rows);
-    kern<<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, s>>>(mu, mv, mp, muo, mvo, mpo, prm);
-    return cudaGetLastError();
-}
-
 // pick the segment height so that the grid is a whole number of waves of `slots` resident CTAs
 int pick_seg_rows(int w, int h, int tx, int slots)
 {
@@ -421,52 +400,88 @@ int pick_seg_rows(int w, int h, int tx, int slots)
     return (h + nseg - 1) / nseg;
 }
 
+template <int TX, int RY, int STAGES, int MINB>
+cudaError_t launch_tma(const FusedArgs &a, bool aligned_origin, cudaStream_t s)
+{
+    using Cfg = TmaCfg<TX, RY, STAGES>;
+    CUtensorMap mu, mv, mp, muo, mvo, mpo;
+    if (!get_map(a.u, a.pitch, a.ny, Cfg::BW, RY, mu) || !get_map(a.v, a.pitch, a.ny, Cfg::BW, RY, mv) ||
+        !get_map(a.p, a.pitch, a.ny, Cfg::BW, RY, mp) || !get_map(a.uold, a.pitch, a.ny, Cfg::BW, RY, muo) ||
+        !get_map(a.vold, a.pitch, a.ny, Cfg::BW, RY, mvo) || !get_map(a.pold, a.pitch, a.ny, Cfg::BW, RY, mpo))
+        return cudaErrorNotSupported;
+    TmaStepParams prm;
+    prm.unew = a.unew; prm.vnew = a.vnew; prm.pnew = a.pnew;
+    prm.uold = a.uold; prm.vold = a.vold; prm.pold = a.pold;
+    // aligned origin: strips start on 128-byte lines of the row (1-based column 1 + 16k), the
+    // columns below xs are masked; otherwise strips start at xs
+    const int i_origin = aligned_origin ? ((a.b.xs - 1) / 16) * 16 + 1 : a.b.xs;
+    const int w = a.b.xe - i_origin + 1, h = a.b.ye - a.b.ys + 1;
+    const int seg_rows = pick_seg_rows(w, h, TX, 148 * MINB);
+    prm.pitch = a.pitch; prm.b = a.b; prm.seg_rows = seg_rows; prm.i_origin = i_origin; prm.sc = a.sc;
+    auto kern = fused_tma_kernel<TX, RY, STAGES, MINB>;
+    static bool attr_done = false;
+    if (!attr_done) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
+        if (e != cudaSuccess) return e;
+        attr_done = true;
+    }
+    dim3 grid((w + TX - 1) / TX, (h + seg_rows - 1) / seg_rows);
+    kern<<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, s>>>(mu, mv, mp, muo, mvo, mpo, prm);
+    return cudaGetLastError();
+}
+
+}  // namespace
+
+namespace {
+struct TmaVariant {
+    int id;
+    const char *name;
+    cudaError_t (*launch)(const FusedArgs &, bool, cudaStream_t);
+};
+// {rows per chunk, stages, resident CTAs per SM}; ids + 20 use the 128-byte aligned strip origin
+const TmaVariant kTmaVariants[] = {
+    {2, "tma-128x4x2-occ3", launch_tma<128, 4, 2, 3>},  {3, "tma-128x8x2-occ2", launch_tma<128, 8, 2, 2>},
+    {4, "tma-128x4x2-occ4", launch_tma<128, 4, 2, 4>},  {5, "tma-128x4x3-occ2", launch_tma<128, 4, 3, 2>},
+    {6, "tma-128x4x4-occ2", launch_tma<128, 4, 4, 2>},  {7, "tma-128x2x6-occ2", launch_tma<128, 2, 6, 2>},
+    {8, "tma-128x8x3-occ1", launch_tma<128, 8, 3, 1>},  {9, "tma-128x4x6-occ1", launch_tma<128, 4, 6, 1>},
+    {10, "tma-128x2x4-occ3", launch_tma<128, 2, 4, 3>}, {11, "tma-128x16x2-occ1", launch_tma<128, 16, 2, 1>},
+    {12, "tma-128x2x8-occ2", launch_tma<128, 2, 8, 2>}, {13, "tma-128x1x12-occ2", launch_tma<128, 1, 12, 2>},
+};
+const TmaVariant *find_tma(int id)
+{
+    for (const auto &v : kTmaVariants)
+        if (v.id == id) return &v;
+    return nullptr;
+}
 }  // namespace
 
 const char *fused_variant_name(int variant)
 {
-    switch (variant) {
-    case 0: return "auto";
-    case 1: return "direct-128x64";
-    case 2: return "tma-128x4x2-occ3";
-    case 3: return "tma-128x8x2-occ2";
-    case 4: return "tma-128x4x2-occ4";
-    case 5: return "tma-128x4x3-occ2";
-    default: return "unknown";
-    }
+    if (variant == 0) return "auto";
+    if (variant == 1) return "direct-128x64";
+    const TmaVariant *v = find_tma(variant >= 20 ? variant - 20 : variant);
+    return v ? v->name : "unknown";
 }
 
 cudaError_t sw_step_fused(const FusedArgs &a, int variant, cudaStream_t s)
 {
     if (a.b.xe < a.b.xs || a.b.ye < a.b.ys) return cudaSuccess;
     const bool tma_ok = a.tmask == nullptr && (a.pitch % 2 == 0) && encode_fn() != nullptr;
-    if (variant == 0) variant = tma_ok ? 2 : 1;
+    if (variant == 0) variant = tma_ok ? kDefaultTmaVariant : 1;
     if (variant >= 2 && !tma_ok) return cudaErrorNotSupported;
-    const int w = a.b.xe - a.b.xs + 1, h = a.b.ye - a.b.ys + 1;
     cudaError_t e;
-    switch (variant) {
-    case 1: {
+    if (variant == 1) {
         constexpr int ROWS = 64;
+        const int w = a.b.xe - a.b.xs + 1, h = a.b.ye - a.b.ys + 1;
         dim3 grid((w + 127) / 128, (h + ROWS - 1) / ROWS);
         if (a.tmask) fused_direct_kernel<true, ROWS><<<grid, 128, 0, s>>>(a);
         else fused_direct_kernel<false, ROWS><<<grid, 128, 0, s>>>(a);
         e = cudaGetLastError();
-        break;
-    }
-    case 2:
-        e = launch_tma<128, 4, 2, 3>(a, pick_seg_rows(w, h, 128, 148 * 3), s);
-        break;
-    case 3:
-        e = launch_tma<128, 8, 2, 2>(a, pick_seg_rows(w, h, 128, 148 * 2), s);
-        break;
-    case 4:
-        e = launch_tma<128, 4, 2, 4>(a, pick_seg_rows(w, h, 128, 148 * 4), s);
-        break;
-    case 5:
-        e = launch_tma<128, 4, 3, 2>(a, pick_seg_rows(w, h, 128, 148 * 2), s);
-        break;
-    default:
-        return cudaErrorInvalidValue;
+    } else {
+        const bool aligned = variant >= 20;
+        const TmaVariant *v = find_tma(aligned ? variant - 20 : variant);
+        if (!v) return cudaErrorInvalidValue;
+        e = v->launch(a, aligned, s);
     }
     note_launch();
     return e;
