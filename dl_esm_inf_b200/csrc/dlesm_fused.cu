@@ -22,6 +22,7 @@
 #include <cuda.h>
 
 #include <cstdint>
+#include <cstdlib>
 #include <map>
 #include <mutex>
 #include <tuple>
@@ -219,34 +220,48 @@ struct TmaStepParams {
 constexpr int kDefaultTmaVariant = 25;
 constexpr int align128(int v) { return (v + 127) & ~127; }
 
-template <int TX, int RY, int STAGES>
+template <int TX, int RY, int STAGES, bool M, bool ALN>
 struct TmaCfg {
     // TMA needs the first element of a box 16-byte aligned (even FP64 column; measured with
     // tools/tma_probe.cu: an odd start column raises "illegal instruction").  Every tile
     // therefore starts at the even column at or below the strip's west halo column and is
-    // TX + 4 wide, which covers west halo + TX + east halo for either parity.
+    // TX + 4 wide, which covers west halo + TX + east halo for either parity.  The int32
+    // tmask tile starts at a multiple of four columns and is TX + 8 wide for the same reason.
+    // uold/vold/pold need no halo columns: with the 128-byte aligned strip origin (ALN) their
+    // tiles are exactly the TX output columns (whole 32-byte sectors, nothing shared with the
+    // neighbouring strip); otherwise they start at the even column at or below the first one.
     static constexpr int BW = TX + 4;
+    static constexpr int BWO = ALN ? TX : TX + 2;
+    static constexpr int BWM = TX + 8;
     static constexpr int A = align128(BW * RY * 8);
-    static constexpr int STAGE_BYTES = 6 * A;
-    static constexpr int TX_BYTES = 6 * BW * RY * 8;
-    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 2 * STAGES * 8 + 128;
+    static constexpr int AO = align128(BWO * RY * 8);
+    static constexpr int AM = M ? align128(BWM * RY * 4) : 0;
+    static constexpr int OFF_OLD = 3 * A;
+    static constexpr int OFF_MASK = 3 * A + 3 * AO;
+    static constexpr int STAGE_BYTES = 3 * A + 3 * AO + AM;
+    static constexpr int TX_BYTES = 3 * BW * RY * 8 + 3 * BWO * RY * 8 + (M ? BWM * RY * 4 : 0);
+    static constexpr int BAR_OFFSET = STAGES * STAGE_BYTES;
+    static constexpr int SMEM_BYTES = BAR_OFFSET + 2 * STAGES * 8;
     static constexpr int THREADS = TX + 32;
 };
 
-template <int TX, int RY, int STAGES, int MINB>
+// Dynamic shared memory, addressed straight off this symbol so that the compiler keeps the
+// shared state space (LDS, not generic LD).  No static shared memory exists in this kernel,
+// so the window starts at offset 0 of the CTA's allocation, which satisfies the 128-byte
+// alignment of TMA destinations; the kernel traps if that ever stops being true.
+template <int TX, int RY, int STAGES, int MINB, bool M, bool FIRST, bool ALN>
 __global__ void __launch_bounds__(TX + 32, MINB)
 fused_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_constant__ CUtensorMap tm_v,
                  const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUtensorMap tm_uo,
                  const __grid_constant__ CUtensorMap tm_vo, const __grid_constant__ CUtensorMap tm_po,
-                 const TmaStepParams prm)
+                 const __grid_constant__ CUtensorMap tm_mask, const TmaStepParams prm)
 {
-    using Cfg = TmaCfg<TX, RY, STAGES>;
+    using Cfg = TmaCfg<TX, RY, STAGES, M, ALN>;
     constexpr int BW = Cfg::BW;
-    extern __shared__ unsigned char smem_raw[];
-    // 128-byte alignment for the TMA destinations
-    unsigned char *smem = reinterpret_cast<unsigned char *>(
-        (reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~static_cast<uintptr_t>(127));
-    uint64_t *full = reinterpret_cast<uint64_t *>(smem + STAGES * Cfg::STAGE_BYTES);
+    constexpr int BWO = Cfg::BWO;
+    constexpr int BWM = Cfg::BWM;
+    extern __shared__ __align__(1024) unsigned char fused_smem[];
+    uint64_t *full = reinterpret_cast<uint64_t *>(fused_smem + Cfg::BAR_OFFSET);
     uint64_t *empty = full + STAGES;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -257,6 +272,7 @@ fused_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_constant
     const int i_first = prm.i_origin + blockIdx.x * TX;   // first output column of this strip
 
     if (tid == 0) {
+        if (smem_u32(fused_smem) & 127u) __trap();
         for (int s = 0; s < STAGES; ++s) {
             mbar_init(&full[s], 1);
             mbar_init(&empty[s], TX / 32);
@@ -270,68 +286,81 @@ fused_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_constant
         // ---- producer warp: one lane feeds the ring ----
         if (lane == 0) {
             const int x_box = (i_first - 2) & ~1;   // even 0-based column at/below the west halo column
+            const int x_box_m = (i_first - 2) & ~3;
+            const int x_old = (i_first - 1) & ~1;   // == i_first - 1 when ALN
             for (int c = 0; c < nchunks; ++c) {
                 const int s = c % STAGES;
                 if (c >= STAGES) mbar_wait(&empty[s], ((c / STAGES) - 1) & 1);
-                unsigned char *st = smem + s * Cfg::STAGE_BYTES;
+                unsigned char *st = fused_smem + s * Cfg::STAGE_BYTES;
                 const int y_raw = (j0 - 1) + c * RY - 1;   // 0-based row of the chunk's first raw row
                 const int y_old = y_raw - 1;               // outputs trail the raw rows by one
                 mbar_expect_tx(&full[s], Cfg::TX_BYTES);
                 tma_load_2d(st + 0 * Cfg::A, &tm_p, x_box, y_raw, &full[s]);
                 tma_load_2d(st + 1 * Cfg::A, &tm_u, x_box, y_raw, &full[s]);
                 tma_load_2d(st + 2 * Cfg::A, &tm_v, x_box, y_raw, &full[s]);
-                tma_load_2d(st + 3 * Cfg::A, &tm_uo, x_box, y_old, &full[s]);
-                tma_load_2d(st + 4 * Cfg::A, &tm_vo, x_box, y_old, &full[s]);
-                tma_load_2d(st + 5 * Cfg::A, &tm_po, x_box, y_old, &full[s]);
+                tma_load_2d(st + Cfg::OFF_OLD + 0 * Cfg::AO, &tm_uo, x_old, y_old, &full[s]);
+                tma_load_2d(st + Cfg::OFF_OLD + 1 * Cfg::AO, &tm_vo, x_old, y_old, &full[s]);
+                tma_load_2d(st + Cfg::OFF_OLD + 2 * Cfg::AO, &tm_po, x_old, y_old, &full[s]);
+                if (M) tma_load_2d(st + Cfg::OFF_MASK, &tm_mask, x_box_m, y_raw, &full[s]);
             }
         }
         return;
     }
 
     // ---- consumer warps ----
+    // Every chunk is processed in full (rows past the segment's last raw row hold the next
+    // rows of the array, or TMA's zero fill outside it); only the stores are predicated, so
+    // the unrolled row loop is straight-line code.
     const int i = i_first + tid;
     const bool active = i <= prm.b.xe && i >= prm.b.xs;
-    const int xoff = (i_first - 2) & 1;
+    const int col = tid + ((i_first - 2) & 1);        // west neighbour's column inside the tile
+    const int colm = tid + ((i_first - 2) & 3);
+    const int colo = tid + ((i_first - 1) & 1);       // own column inside the old-field tile
     const SwScalars sc = prm.sc;
-    Carry<false> cr;
+    Carry<M> cr;
     carry_init(cr);
-    size_t qo = idx(prm.pitch, i, j0 - 2);  // output row trails: step t writes row j0-2+t
-    int t = 0;
+    // output row trails the raw row by one: raw step t produces row j0-2+t
+    size_t qo = idx(prm.pitch, i, j0 - 2);
+    const size_t pitch = static_cast<size_t>(prm.pitch);
+    // steps whose outputs are stored: 2 <= t < nsteps
+    int t_lo = active ? 2 : (1 << 30), t_hi = nsteps;
     for (int c = 0; c < nchunks; ++c) {
         const int s = c % STAGES;
         mbar_wait(&full[s], (c / STAGES) & 1);
-        const unsigned char *st = smem + s * Cfg::STAGE_BYTES;
-        const double *sp = reinterpret_cast<const double *>(st + 0 * Cfg::A);
-        const double *su = reinterpret_cast<const double *>(st + 1 * Cfg::A);
-        const double *sv = reinterpret_cast<const double *>(st + 2 * Cfg::A);
-        const double *suo = reinterpret_cast<const double *>(st + 3 * Cfg::A);
-        const double *svo = reinterpret_cast<const double *>(st + 4 * Cfg::A);
-        const double *spo = reinterpret_cast<const double *>(st + 5 * Cfg::A);
+        const unsigned char *st = fused_smem + s * Cfg::STAGE_BYTES;
+        const double *sp = reinterpret_cast<const double *>(st + 0 * Cfg::A) + col;
+        const double *su = reinterpret_cast<const double *>(st + 1 * Cfg::A) + col;
+        const double *sv = reinterpret_cast<const double *>(st + 2 * Cfg::A) + col;
+        const double *suo = reinterpret_cast<const double *>(st + Cfg::OFF_OLD + 0 * Cfg::AO) + colo;
+        const double *svo = reinterpret_cast<const double *>(st + Cfg::OFF_OLD + 1 * Cfg::AO) + colo;
+        const double *spo = reinterpret_cast<const double *>(st + Cfg::OFF_OLD + 2 * Cfg::AO) + colo;
+        const int *sm = reinterpret_cast<const int *>(st + Cfg::OFF_MASK) + colm;
 #pragma unroll
         for (int r = 0; r < RY; ++r) {
-            if (t < nsteps) {
-                Raw<false> N;
-                const int o = r * BW + tid + xoff;   // west neighbour's column inside the tile
-                N.pW = sp[o]; N.pC = sp[o + 1]; N.pE = sp[o + 2];
-                N.uW = su[o]; N.uC = su[o + 1]; N.uE = su[o + 2];
-                N.vW = sv[o]; N.vC = sv[o + 1]; N.vE = sv[o + 2];
-                const double uo = suo[o + 1], vo = svo[o + 1], po = spo[o + 1];
-                Outs out;
-                ingest<false>(cr, N, sc, uo, vo, po, out);
-                if (t >= 2 && active) {
-                    __stcs(prm.unew + qo, out.unew);
-                    __stcs(prm.vnew + qo, out.vnew);
-                    __stcs(prm.pnew + qo, out.pnew);
-                    if (!sc.first) {
-                        __stcs(prm.uold + qo, out.uold);
-                        __stcs(prm.vold + qo, out.vold);
-                        __stcs(prm.pold + qo, out.pold);
-                    }
+            Raw<M> N;
+            N.pW = sp[r * BW]; N.pC = sp[r * BW + 1]; N.pE = sp[r * BW + 2];
+            N.uW = su[r * BW]; N.uC = su[r * BW + 1]; N.uE = su[r * BW + 2];
+            N.vW = sv[r * BW]; N.vC = sv[r * BW + 1]; N.vE = sv[r * BW + 2];
+            if (M) {
+                N.tW = sm[r * BWM] == 1; N.tC = sm[r * BWM + 1] == 1; N.tE = sm[r * BWM + 2] == 1;
+            }
+            const double uo = suo[r * BWO], vo = svo[r * BWO], po = spo[r * BWO];
+            Outs out;
+            ingest<M>(cr, N, sc, uo, vo, po, out);
+            if (r >= t_lo && r < t_hi) {
+                __stcs(prm.unew + qo, out.unew);
+                __stcs(prm.vnew + qo, out.vnew);
+                __stcs(prm.pnew + qo, out.pnew);
+                if (!FIRST) {
+                    if (!M || out.wu) __stcs(prm.uold + qo, out.uold);
+                    if (!M || out.wv) __stcs(prm.vold + qo, out.vold);
+                    if (!M || out.wt) __stcs(prm.pold + qo, out.pold);
                 }
             }
-            ++t;
-            qo += prm.pitch;
+            qo += pitch;
         }
+        t_lo -= RY;
+        t_hi -= RY;
         __syncwarp();
         if (lane == 0) mbar_arrive(&empty[s]);
     }
@@ -357,12 +386,13 @@ EncodeTiledFn encode_fn()
 }
 
 std::mutex g_map_mutex;
-std::map<std::tuple<const void *, int, int, int, int>, CUtensorMap> g_maps;
+std::map<std::tuple<const void *, int, int, int, int, int>, CUtensorMap> g_maps;
 
-bool get_map(const double *base, int nx, int ny, int boxw, int boxh, CUtensorMap &out)
+// 2-D tiled tensor map over a column-major (nx, ny) array of FP64 (elem_bytes 8) or int32 (4)
+bool get_map(const void *base, int elem_bytes, int nx, int ny, int boxw, int boxh, CUtensorMap &out)
 {
     std::lock_guard<std::mutex> lock(g_map_mutex);
-    auto key = std::make_tuple(static_cast<const void *>(base), nx, ny, boxw, boxh);
+    auto key = std::make_tuple(base, elem_bytes, nx, ny, boxw, boxh);
     auto it = g_maps.find(key);
     if (it != g_maps.end()) {
         out = it->second;
@@ -371,13 +401,23 @@ bool get_map(const double *base, int nx, int ny, int boxw, int boxh, CUtensorMap
     EncodeTiledFn fn = encode_fn();
     if (!fn) return false;
     cuuint64_t gdim[2] = {static_cast<cuuint64_t>(nx), static_cast<cuuint64_t>(ny)};
-    cuuint64_t gstride[1] = {static_cast<cuuint64_t>(nx) * sizeof(double)};
+    cuuint64_t gstride[1] = {static_cast<cuuint64_t>(nx) * elem_bytes};
     cuuint32_t box[2] = {static_cast<cuuint32_t>(boxw), static_cast<cuuint32_t>(boxh)};
     cuuint32_t estr[2] = {1, 1};
+    // L2 promotion of the TMA reads; DLESM_TMA_L2PROMO=0..3 (none, 64 B, 128 B, 256 B) overrides
+    // the default for the experiments recorded in DESIGN.md
+    static const int promo = [] {
+        const char *e = std::getenv("DLESM_TMA_L2PROMO");
+        const int v = e ? std::atoi(e) : 3;
+        return v < 0 || v > 3 ? 3 : v;
+    }();
+    const CUtensorMapL2promotion promos[4] = {CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_64B,
+                                              CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                                              CU_TENSOR_MAP_L2_PROMOTION_L2_256B};
     CUtensorMap m;
-    CUresult r = fn(&m, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, const_cast<double *>(base), gdim, gstride, box,
-                    estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
-                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    CUresult r = fn(&m, elem_bytes == 8 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT64 : CU_TENSOR_MAP_DATA_TYPE_INT32, 2,
+                    const_cast<void *>(base), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    CU_TENSOR_MAP_SWIZZLE_NONE, promos[promo], CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return false;
     if (g_maps.size() > 256) g_maps.clear();
     g_maps[key] = m;
@@ -400,15 +440,21 @@ int pick_seg_rows(int w, int h, int tx, int slots)
     return (h + nseg - 1) / nseg;
 }
 
-template <int TX, int RY, int STAGES, int MINB>
-cudaError_t launch_tma(const FusedArgs &a, bool aligned_origin, cudaStream_t s)
+template <int TX, int RY, int STAGES, int MINB, bool M, bool FIRST, bool ALN>
+cudaError_t launch_tma_mf(const FusedArgs &a, cudaStream_t s)
 {
-    using Cfg = TmaCfg<TX, RY, STAGES>;
-    CUtensorMap mu, mv, mp, muo, mvo, mpo;
-    if (!get_map(a.u, a.pitch, a.ny, Cfg::BW, RY, mu) || !get_map(a.v, a.pitch, a.ny, Cfg::BW, RY, mv) ||
-        !get_map(a.p, a.pitch, a.ny, Cfg::BW, RY, mp) || !get_map(a.uold, a.pitch, a.ny, Cfg::BW, RY, muo) ||
-        !get_map(a.vold, a.pitch, a.ny, Cfg::BW, RY, mvo) || !get_map(a.pold, a.pitch, a.ny, Cfg::BW, RY, mpo))
+    using Cfg = TmaCfg<TX, RY, STAGES, M, ALN>;
+    constexpr bool aligned_origin = ALN;
+    CUtensorMap mu, mv, mp, muo, mvo, mpo, mm;
+    if (!get_map(a.u, 8, a.pitch, a.ny, Cfg::BW, RY, mu) || !get_map(a.v, 8, a.pitch, a.ny, Cfg::BW, RY, mv) ||
+        !get_map(a.p, 8, a.pitch, a.ny, Cfg::BW, RY, mp) || !get_map(a.uold, 8, a.pitch, a.ny, Cfg::BWO, RY, muo) ||
+        !get_map(a.vold, 8, a.pitch, a.ny, Cfg::BWO, RY, mvo) || !get_map(a.pold, 8, a.pitch, a.ny, Cfg::BWO, RY, mpo))
         return cudaErrorNotSupported;
+    if (M) {
+        if (!get_map(a.tmask, 4, a.pitch, a.ny, Cfg::BWM, RY, mm)) return cudaErrorNotSupported;
+    } else {
+        mm = mp;  // unused by the unmasked kernel
+    }
     TmaStepParams prm;
     prm.unew = a.unew; prm.vnew = a.vnew; prm.pnew = a.pnew;
     prm.uold = a.uold; prm.vold = a.vold; prm.pold = a.pold;
@@ -418,7 +464,7 @@ cudaError_t launch_tma(const FusedArgs &a, bool aligned_origin, cudaStream_t s)
     const int w = a.b.xe - i_origin + 1, h = a.b.ye - a.b.ys + 1;
     const int seg_rows = pick_seg_rows(w, h, TX, 148 * MINB);
     prm.pitch = a.pitch; prm.b = a.b; prm.seg_rows = seg_rows; prm.i_origin = i_origin; prm.sc = a.sc;
-    auto kern = fused_tma_kernel<TX, RY, STAGES, MINB>;
+    auto kern = fused_tma_kernel<TX, RY, STAGES, MINB, M, FIRST, ALN>;
     static bool attr_done = false;
     if (!attr_done) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
@@ -426,8 +472,19 @@ cudaError_t launch_tma(const FusedArgs &a, bool aligned_origin, cudaStream_t s)
         attr_done = true;
     }
     dim3 grid((w + TX - 1) / TX, (h + seg_rows - 1) / seg_rows);
-    kern<<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, s>>>(mu, mv, mp, muo, mvo, mpo, prm);
+    kern<<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, s>>>(mu, mv, mp, muo, mvo, mpo, mm, prm);
     return cudaGetLastError();
+}
+
+template <int TX, int RY, int STAGES, int MINB, bool ALN>
+cudaError_t launch_tma(const FusedArgs &a, cudaStream_t s)
+{
+    const bool first = a.sc.first != 0;
+    if (a.tmask)
+        return first ? launch_tma_mf<TX, RY, STAGES, MINB, true, true, ALN>(a, s)
+                     : launch_tma_mf<TX, RY, STAGES, MINB, true, false, ALN>(a, s);
+    return first ? launch_tma_mf<TX, RY, STAGES, MINB, false, true, ALN>(a, s)
+                 : launch_tma_mf<TX, RY, STAGES, MINB, false, false, ALN>(a, s);
 }
 
 }  // namespace
@@ -436,16 +493,23 @@ namespace {
 struct TmaVariant {
     int id;
     const char *name;
-    cudaError_t (*launch)(const FusedArgs &, bool, cudaStream_t);
+    cudaError_t (*launch)(const FusedArgs &, cudaStream_t);
 };
-// {rows per chunk, stages, resident CTAs per SM}; ids + 20 use the 128-byte aligned strip origin
+// {columns, rows per chunk, stages, resident CTAs per SM}.  ids >= 20 start every strip on a
+// 128-byte line of the row (aligned origin); ids < 20 start strips at xstart (kept for the
+// comparison in DESIGN.md).
 const TmaVariant kTmaVariants[] = {
-    {2, "tma-128x4x2-occ3", launch_tma<128, 4, 2, 3>},  {3, "tma-128x8x2-occ2", launch_tma<128, 8, 2, 2>},
-    {4, "tma-128x4x2-occ4", launch_tma<128, 4, 2, 4>},  {5, "tma-128x4x3-occ2", launch_tma<128, 4, 3, 2>},
-    {6, "tma-128x4x4-occ2", launch_tma<128, 4, 4, 2>},  {7, "tma-128x2x6-occ2", launch_tma<128, 2, 6, 2>},
-    {8, "tma-128x8x3-occ1", launch_tma<128, 8, 3, 1>},  {9, "tma-128x4x6-occ1", launch_tma<128, 4, 6, 1>},
-    {10, "tma-128x2x4-occ3", launch_tma<128, 2, 4, 3>}, {11, "tma-128x16x2-occ1", launch_tma<128, 16, 2, 1>},
-    {12, "tma-128x2x8-occ2", launch_tma<128, 2, 8, 2>}, {13, "tma-128x1x12-occ2", launch_tma<128, 1, 12, 2>},
+    {2, "tma-128x4x2-occ3-unaligned", launch_tma<128, 4, 2, 3, false>},
+    {5, "tma-128x4x3-occ2-unaligned", launch_tma<128, 4, 3, 2, false>},
+    {22, "tma-128x4x2-occ3", launch_tma<128, 4, 2, 3, true>},
+    {23, "tma-128x8x2-occ2", launch_tma<128, 8, 2, 2, true>},
+    {24, "tma-128x4x3-occ3", launch_tma<128, 4, 3, 3, true>},
+    {25, "tma-128x4x3-occ2", launch_tma<128, 4, 3, 2, true>},
+    {26, "tma-128x4x4-occ2", launch_tma<128, 4, 4, 2, true>},
+    {27, "tma-128x2x6-occ2", launch_tma<128, 2, 6, 2, true>},
+    {28, "tma-128x8x3-occ1", launch_tma<128, 8, 3, 1, true>},
+    {29, "tma-128x2x8-occ2", launch_tma<128, 2, 8, 2, true>},
+    {30, "tma-128x2x4-occ3", launch_tma<128, 2, 4, 3, true>},
 };
 const TmaVariant *find_tma(int id)
 {
@@ -459,14 +523,15 @@ const char *fused_variant_name(int variant)
 {
     if (variant == 0) return "auto";
     if (variant == 1) return "direct-128x64";
-    const TmaVariant *v = find_tma(variant >= 20 ? variant - 20 : variant);
+    const TmaVariant *v = find_tma(variant);
     return v ? v->name : "unknown";
 }
 
 cudaError_t sw_step_fused(const FusedArgs &a, int variant, cudaStream_t s)
 {
     if (a.b.xe < a.b.xs || a.b.ye < a.b.ys) return cudaSuccess;
-    const bool tma_ok = a.tmask == nullptr && (a.pitch % 2 == 0) && encode_fn() != nullptr;
+    // FP64 rows must start 16-byte aligned (even pitch); int32 tmask rows need pitch % 4 == 0
+    const bool tma_ok = (a.pitch % 2 == 0) && (a.tmask == nullptr || a.pitch % 4 == 0) && encode_fn() != nullptr;
     if (variant == 0) variant = tma_ok ? kDefaultTmaVariant : 1;
     if (variant >= 2 && !tma_ok) return cudaErrorNotSupported;
     cudaError_t e;
@@ -478,10 +543,9 @@ cudaError_t sw_step_fused(const FusedArgs &a, int variant, cudaStream_t s)
         else fused_direct_kernel<false, ROWS><<<grid, 128, 0, s>>>(a);
         e = cudaGetLastError();
     } else {
-        const bool aligned = variant >= 20;
-        const TmaVariant *v = find_tma(aligned ? variant - 20 : variant);
+        const TmaVariant *v = find_tma(variant);
         if (!v) return cudaErrorInvalidValue;
-        e = v->launch(a, aligned, s);
+        e = v->launch(a, s);
     }
     note_launch();
     return e;

@@ -387,7 +387,10 @@ def test_sw_steps_match_oracle(n_x, n_y, align, mode, monkeypatch):
         assert abs(a - b) <= RTOL * abs(b)
 
 
-@pytest.mark.parametrize("variant", [1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 23, 25, 29])
+FUSED_VARIANTS = [1, 2, 5, 22, 23, 24, 25, 26, 27, 28, 29, 30]
+
+
+@pytest.mark.parametrize("variant", FUSED_VARIANTS)
 @pytest.mark.parametrize("n_x,n_y,align", [(128, 64, 2), (129, 70, 2), (300, 523, 64), (1024, 1024, 64)])
 def test_fused_variants_match_oracle(variant, n_x, n_y, align, monkeypatch):
     osw, sw = sw_pair(n_x, n_y, fd.SW_FUSED, alignment=align, monkeypatch=monkeypatch)
@@ -441,6 +444,73 @@ def test_sw_with_tmask_land_points(mode, n_x, n_y, align, seed, monkeypatch):
         osw.step()
     sw.step(4)
     assert_state_equal(osw, sw, internal_only=("uold", "vold", "pold"))
+
+
+@pytest.mark.parametrize("variant", [1, 2, 5, 22, 25, 28])
+@pytest.mark.parametrize("n_x,n_y,align,seed", [(70, 51, 64, 12345), (300, 523, 4, None), (512, 512, 64, None)])
+def test_fused_variants_with_tmask(variant, n_x, n_y, align, seed, monkeypatch):
+    """the masked fused sweep on the TMA ring (tmask tile streamed as int32) and the direct
+    kernel against the oracle's un-fused masked run"""
+    tm = periodic_island_mask(n_x + 2, n_y + 2, seed)
+    osw, sw = sw_pair(n_x, n_y, fd.SW_FUSED, alignment=align, tmask=tm, monkeypatch=monkeypatch)
+    sw.set_variant(variant)
+    for _ in range(4):
+        osw.step()
+    sw.step(4)
+    assert_state_equal(osw, sw, internal_only=("uold", "vold", "pold"))
+
+
+def test_masked_tma_needs_pitch_multiple_of_four(monkeypatch):
+    """int32 tmask rows must start 16-byte aligned for TMA: pitch % 4 != 0 => explicit TMA
+    variants refuse, auto (0) takes the direct kernel and still matches the oracle"""
+    tm = periodic_island_mask(68, 42, None)
+    osw, sw = sw_pair(66, 40, fd.SW_FUSED, alignment=2, tmask=tm, monkeypatch=monkeypatch)   # pitch 70
+    assert sw.field("p").info.nx % 4 == 2
+    sw.set_variant(5)
+    with pytest.raises(fd.GoceanStop):
+        sw.step(1)
+    sw.set_variant(0)
+    osw.step()
+    sw.step(1)
+    assert_state_equal(osw, sw, internal_only=("uold", "vold", "pold"))
+
+
+def test_config3_4096_tmask_alignment64_fused_equals_unfused(monkeypatch):
+    """BASELINE config 3 at full size: 4096^2, DL_ESM_ALIGNMENT=64 (alloc 4160x4099), tmask with
+    64x64 islands where mod(i,512) in [200,263] and mod(j,512) in [300,363].
+    The oracle would take minutes, so the check is the size-independent one: the fused masked
+    TMA sweep equals the un-fused per-kernel sequence bit for bit, land points never change,
+    and mass over wet points is conserved."""
+    n = 4096
+    monkeypatch.setenv("DL_ESM_ALIGNMENT", "64")
+    i = np.arange(1, n + 1)[:, None]
+    j = np.arange(1, n + 1)[None, :]
+    land = ((i % 512 >= 200) & (i % 512 <= 263)) & ((j % 512 >= 300) & (j % 512 <= 363))
+    inner = np.where(land, 0, 1).astype(np.int32)
+    tm = np.ones((n + 2, n + 2), dtype=np.int32, order="F")
+    tm[1:-1, 1:-1] = inner
+    tm[0, 1:-1], tm[-1, 1:-1] = inner[-1, :], inner[0, :]
+    tm[:, 0], tm[:, -1] = tm[:, -2], tm[:, 1]
+    g = make_grid(n, n, offset=fd.GO_OFFSET_SW, bcs=BCS_PER, tmask=tm, dx=1.0e5, dy=1.0e5)
+    assert (g.nx, g.ny) == (4160, 4099)
+    a = fd.shallow_water(g, mode=fd.SW_FUSED, use_tmask=True)
+    a.init_device()
+    ii = a.field("p").internal
+    sl = (slice(ii.xstart - 1, ii.xstop), slice(ii.ystart - 1, ii.ystop))
+    init = {k: a.field(k).get_data().copy(order="F") for k in ("u", "v", "p")}
+    a.step(5)
+    res_a = {k: a.field(k).get_data()[sl].copy() for k in ("u", "v", "p", "uold", "vold", "pold")}
+    a.free()
+    assert np.array_equal(res_a["p"][land], init["p"][sl][land])          # land points untouched
+    wet = ~land
+    m0, m1 = init["p"][sl][wet].sum(), res_a["p"][wet].sum()
+    assert abs(m1 - m0) <= 1e-11 * abs(m0)
+    b = fd.shallow_water(g, mode=fd.SW_UNFUSED, use_tmask=True)
+    b.set_state(init["u"], init["v"], init["p"])
+    b.step(5)
+    for k in res_a:
+        assert np.array_equal(b.field(k).get_data()[sl], res_a[k]), k
+    b.free()
 
 
 # ---------------------------------------------------------------------------------------------
