@@ -425,19 +425,27 @@ bool get_map(const void *base, int elem_bytes, int nx, int ny, int boxw, int box
     return true;
 }
 
-// pick the segment height so that the grid is a whole number of waves of `slots` resident CTAs
-int pick_seg_rows(int w, int h, int tx, int slots)
+// Pick the segment height.  Every segment costs two extra raw rows (its prologue) and its
+// row count is rounded up to whole chunks of `ry` rows, so: segments of about `target` rows,
+// the CTA count rounded up to whole waves of `slots` resident CTAs, and seg_rows + 2 a
+// multiple of `ry` whenever that does not add a segment.
+int pick_seg_rows(int w, int h, int tx, int slots, int ry, int target)
 {
     const int strips = (w + tx - 1) / tx;
-    // aim for segments of ~256 rows (prologue overhead 2/256), rounded to fill whole waves
-    int nseg = (h + 255) / 256;
+    int nseg = (h + target - 1) / target;
     if (nseg < 1) nseg = 1;
     long long ctas = static_cast<long long>(strips) * nseg;
     const long long waves = (ctas + slots - 1) / slots;
     nseg = static_cast<int>((waves * slots) / strips);
     if (nseg < 1) nseg = 1;
     if (nseg > h) nseg = h;
-    return (h + nseg - 1) / nseg;
+    int seg = (h + nseg - 1) / nseg;
+    // seg + 2 a multiple of ry: round up if the segment count stays the same, else down
+    const int up = ((seg + 2 + ry - 1) / ry) * ry - 2;
+    const int down = ((seg + 2) / ry) * ry - 2;
+    if (up >= 1 && (h + up - 1) / up == (h + seg - 1) / seg) seg = up;
+    else if (down >= ry) seg = down;
+    return seg;
 }
 
 template <int TX, int RY, int STAGES, int MINB, bool M, bool FIRST, bool ALN>
@@ -462,7 +470,16 @@ cudaError_t launch_tma_mf(const FusedArgs &a, cudaStream_t s)
     // columns below xs are masked; otherwise strips start at xs
     const int i_origin = aligned_origin ? ((a.b.xs - 1) / 16) * 16 + 1 : a.b.xs;
     const int w = a.b.xe - i_origin + 1, h = a.b.ye - a.b.ys + 1;
-    const int seg_rows = pick_seg_rows(w, h, TX, 148 * MINB);
+    static const int target = [] {
+        // Short segments keep the strips of a band in lockstep, so that together they sweep whole
+        // contiguous rows of DRAM and re-read each other's halo rows out of L2 (measured at
+        // 16384^2: 256 rows 0.93, 128 rows 0.95, 48 rows 0.995, 24-32 rows 1.01-1.02 of the
+        // measured copy bandwidth).  DLESM_SEG_ROWS overrides for experiments.
+        const char *e = std::getenv("DLESM_SEG_ROWS");
+        const int v = e ? std::atoi(e) : 32;
+        return v < 8 ? 32 : v;
+    }();
+    const int seg_rows = pick_seg_rows(w, h, TX, 148 * MINB, RY, target);
     prm.pitch = a.pitch; prm.b = a.b; prm.seg_rows = seg_rows; prm.i_origin = i_origin; prm.sc = a.sc;
     auto kern = fused_tma_kernel<TX, RY, STAGES, MINB, M, FIRST, ALN>;
     static bool attr_done = false;
@@ -510,6 +527,10 @@ const TmaVariant kTmaVariants[] = {
     {28, "tma-128x8x3-occ1", launch_tma<128, 8, 3, 1, true>},
     {29, "tma-128x2x8-occ2", launch_tma<128, 2, 8, 2, true>},
     {30, "tma-128x2x4-occ3", launch_tma<128, 2, 4, 3, true>},
+    {31, "tma-128x16x2-occ1", launch_tma<128, 16, 2, 1, true>},
+    {32, "tma-128x8x4-occ1", launch_tma<128, 8, 4, 1, true>},
+    {33, "tma-128x4x8-occ1", launch_tma<128, 4, 8, 1, true>},
+    {34, "tma-128x12x3-occ1", launch_tma<128, 12, 3, 1, true>},
 };
 const TmaVariant *find_tma(int id)
 {

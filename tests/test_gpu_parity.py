@@ -387,7 +387,7 @@ def test_sw_steps_match_oracle(n_x, n_y, align, mode, monkeypatch):
         assert abs(a - b) <= RTOL * abs(b)
 
 
-FUSED_VARIANTS = [1, 2, 5, 22, 23, 24, 25, 26, 27, 28, 29, 30]
+FUSED_VARIANTS = [1, 2, 5, 22, 23, 24, 25, 26, 27, 28, 29, 30, 31, 32, 33, 34]
 
 
 @pytest.mark.parametrize("variant", FUSED_VARIANTS)
