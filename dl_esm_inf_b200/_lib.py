@@ -43,6 +43,17 @@ class Comms(C.Structure):
                            "nrecvp")]
 
 
+_ll = C.c_longlong * MAXCOMM
+
+
+class CommPlan(C.Structure):
+    """dlesm_comm_plan: the per-peer message plan of the device exchange"""
+    _fields_ = [("npeers", C.c_int), ("peer", _ia), ("nsend", _ia), ("nrecv", _ia),
+                ("send_slot", _ia * MAXCOMM), ("recv_slot", _ia * MAXCOMM),
+                ("send_off", _ll), ("recv_off", _ll), ("send_n", _ll), ("recv_n", _ll),
+                ("send_total", C.c_longlong), ("recv_total", C.c_longlong)]
+
+
 class GridInfo(C.Structure):
     _fields_ = [("name", C.c_int), ("offset", C.c_int), ("global_nx", C.c_int),
                 ("global_ny", C.c_int), ("nx", C.c_int), ("ny", C.c_int), ("dx", C.c_double),
@@ -87,6 +98,7 @@ SIGNATURES = {
     "dlesm_decomp_free": (None, [_V]),
     "dlesm_map_comms": (_I, [_V, _I, _I, _I, _I, _I, _I, C.POINTER(Comms)]),
     "dlesm_iprocmap": (_I, [_V, _I, _I, _I]),
+    "dlesm_comm_plan_build": (_I, [C.POINTER(Comms), _I, C.POINTER(CommPlan)]),
     "dlesm_grid_create": (_V, [_I, _PI, _I]),
     "dlesm_grid_decompose": (_I, [_V] + [_I] * 6),
     "dlesm_grid_init": (_I, [_V, _D, _D, _PI, _I, _I]),

@@ -14,7 +14,7 @@ import ctypes as C
 import numpy as np
 
 from . import _lib
-from ._lib import Comms, FieldInfo, GridInfo, Region, Subdomain
+from ._lib import CommPlan, Comms, FieldInfo, GridInfo, Region, Subdomain
 
 # --- constants, same values as the Fortran parameters --------------------------------------
 GO_ARAKAWA_C, GO_ARAKAWA_B = 0, 1                                       # src/grid_mod.f90:45-46
@@ -155,6 +155,13 @@ def map_comms(decomp: decomposition_type, irank=None, nranks=None, pbc=(False, F
                                     int(pbc[0]), int(pbc[1]), halo_depths[0], halo_depths[1],
                                     C.byref(c)))
     return c
+
+
+def comm_plan(comms: Comms, irank=None) -> CommPlan:
+    """the per-peer message plan the device exchange derives from a rank's map_comms tables"""
+    p = CommPlan()
+    _chk(_lib.lib().dlesm_comm_plan_build(C.byref(comms), irank or get_rank(), C.byref(p)))
+    return p
 
 
 def iprocmap(decomp: decomposition_type, ia, ja, nranks=None):

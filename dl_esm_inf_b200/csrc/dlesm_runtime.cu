@@ -538,50 +538,87 @@ extern "C" int dlesm_dev_periodic_halos(void *f, int xs, int xe, int ys, int ye,
 // =========================================================================================
 // halo exchange
 // =========================================================================================
+extern "C" int dlesm_comm_plan_build(const dlesm_comms *t, int rank1, dlesm_comm_plan *out)
+{
+    std::memset(out, 0, sizeof(*out));
+    if (t->nsend > DLESM_MAXCOMM || t->nrecv > DLESM_MAXCOMM || t->nsend < 0 || t->nrecv < 0) {
+        set_error(DLESM_ERR_MAXCOMM, "comm plan: list longer than MaxComm");
+        return DLESM_ERR_MAXCOMM;
+    }
+    const int me0 = rank1 - 1;
+    // peers in ascending rank order
+    std::vector<int> peers;
+    auto note = [&](int p) {
+        if (std::find(peers.begin(), peers.end(), p) == peers.end()) peers.push_back(p);
+    };
+    for (int s = 0; s < t->nsend; ++s)
+        if (t->destination[s] >= 0 && t->nxsend[s] > 0) note(t->destination[s]);
+    for (int r = 0; r < t->nrecv; ++r)
+        if (t->source[r] >= 0 && t->nxrecv[r] > 0) note(t->source[r]);
+    std::sort(peers.begin(), peers.end());
+    if (peers.size() > DLESM_MAXCOMM) {
+        set_error(DLESM_ERR_MAXCOMM, "comm plan: more peers than MaxComm");
+        return DLESM_ERR_MAXCOMM;
+    }
+    out->npeers = static_cast<int>(peers.size());
+    long long so = 0, ro = 0;
+    for (int g = 0; g < out->npeers; ++g) {
+        const int p0 = peers[g];
+        out->peer[g] = p0;
+        std::vector<int> sends, recvs;
+        for (int s = 0; s < t->nsend; ++s)
+            if (t->destination[s] == p0 && t->nxsend[s] > 0) sends.push_back(s);
+        for (int r = 0; r < t->nrecv; ++r)
+            if (t->source[r] == p0 && t->nxrecv[r] > 0) recvs.push_back(r);
+        // both sides walk their messages for a peer in direction order (the tag of the
+        // reference); a message sent in direction d is received as direction d
+        std::stable_sort(sends.begin(), sends.end(), [&](int a, int b) { return t->dirsend[a] < t->dirsend[b]; });
+        std::stable_sort(recvs.begin(), recvs.end(), [&](int a, int b) { return t->dirrecv[a] < t->dirrecv[b]; });
+        out->nsend[g] = static_cast<int>(sends.size());
+        out->nrecv[g] = static_cast<int>(recvs.size());
+        out->send_off[g] = so;
+        out->recv_off[g] = ro;
+        for (size_t q = 0; q < sends.size(); ++q) {
+            out->send_slot[g][q] = sends[q];
+            out->send_n[g] += static_cast<long long>(t->nxsend[sends[q]]) * t->nysend[sends[q]];
+        }
+        for (size_t q = 0; q < recvs.size(); ++q) {
+            out->recv_slot[g][q] = recvs[q];
+            out->recv_n[g] += static_cast<long long>(t->nxrecv[recvs[q]]) * t->nyrecv[recvs[q]];
+        }
+        if (p0 == me0 && out->send_n[g] != out->recv_n[g]) {
+            set_error(DLESM_ERR_ARGS, "comm plan: self-messages do not pair up");
+            return DLESM_ERR_ARGS;
+        }
+        so += out->send_n[g];
+        ro += out->recv_n[g];
+    }
+    out->send_total = so;
+    out->recv_total = ro;
+    return DLESM_OK;
+}
+
 extern "C" int dlesm_dev_set_comms(const dlesm_comms *t)
 {
     Context &c = ctx();
+    dlesm_comm_plan plan;
+    int rc = dlesm_comm_plan_build(t, pstate().rank, &plan);
+    if (rc != DLESM_OK) return rc;
     c.comms = *t;
     c.groups.clear();
-    const int me0 = pstate().rank - 1;
-    auto group_of = [&](int peer0) -> PeerGroup & {
-        for (auto &g : c.groups)
-            if (g.peer0 == peer0) return g;
-        c.groups.push_back(PeerGroup());
-        c.groups.back().peer0 = peer0;
-        return c.groups.back();
-    };
-    if (t->nsend > DLESM_MAXCOMM || t->nrecv > DLESM_MAXCOMM || t->nsend < 0 || t->nrecv < 0) {
-        set_error(DLESM_ERR_MAXCOMM, "set_comms: list longer than MaxComm");
-        return DLESM_ERR_MAXCOMM;
+    for (int g = 0; g < plan.npeers; ++g) {
+        PeerGroup pg;
+        pg.peer0 = plan.peer[g];
+        pg.sends.assign(plan.send_slot[g], plan.send_slot[g] + plan.nsend[g]);
+        pg.recvs.assign(plan.recv_slot[g], plan.recv_slot[g] + plan.nrecv[g]);
+        pg.send_off = plan.send_off[g];
+        pg.recv_off = plan.recv_off[g];
+        pg.send_n = plan.send_n[g];
+        pg.recv_n = plan.recv_n[g];
+        c.groups.push_back(pg);
     }
-    for (int s = 0; s < t->nsend; ++s)
-        if (t->destination[s] >= 0 && t->nxsend[s] > 0) group_of(t->destination[s]).sends.push_back(s);
-    for (int r = 0; r < t->nrecv; ++r)
-        if (t->source[r] >= 0 && t->nxrecv[r] > 0) group_of(t->source[r]).recvs.push_back(r);
-    std::sort(c.groups.begin(), c.groups.end(),
-              [](const PeerGroup &a, const PeerGroup &b) { return a.peer0 < b.peer0; });
-    // Between two ranks the reference matches messages by tag = direction
-    // (src/parallel_comms_mod.f90:1606,1647); NCCL has no tags, so both sides walk their
-    // messages for a peer in direction order and they travel as one buffer per peer.
-    long long so = 0, ro = 0;
-    for (auto &g : c.groups) {
-        std::sort(g.sends.begin(), g.sends.end(), [&](int a, int b) { return t->dirsend[a] < t->dirsend[b]; });
-        std::sort(g.recvs.begin(), g.recvs.end(), [&](int a, int b) { return t->dirrecv[a] < t->dirrecv[b]; });
-        g.send_off = so;
-        g.recv_off = ro;
-        g.send_n = g.recv_n = 0;
-        for (int s : g.sends) g.send_n += static_cast<long long>(t->nxsend[s]) * t->nysend[s];
-        for (int r : g.recvs) g.recv_n += static_cast<long long>(t->nxrecv[r]) * t->nyrecv[r];
-        if (g.peer0 == me0 && g.send_n != g.recv_n) {
-            set_error(DLESM_ERR_ARGS, "set_comms: self-messages do not pair up");
-            return DLESM_ERR_ARGS;
-        }
-        so += g.send_n;
-        ro += g.recv_n;
-    }
-    c.send_total = so;
-    c.recv_total = ro;
+    c.send_total = plan.send_total;
+    c.recv_total = plan.recv_total;
     c.have_comms = true;
     return DLESM_OK;
 }

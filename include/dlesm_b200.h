@@ -180,6 +180,23 @@ int dlesm_map_comms(const dlesm_decomp_t *d, int irank1, int nranks, int pbc_x, 
 /* iprocmap (:1365-1398): owner (1-based) of global point (ia, ja) or 0 */
 int dlesm_iprocmap(const dlesm_decomp_t *d, int nranks, int ia, int ja);
 
+/* The message plan the device exchange derives from a rank's map_comms tables.  The reference
+ * posts one MPI message per list entry and matches them by tag = direction
+ * (src/parallel_comms_mod.f90:1606,1647); NCCL and NVLink peer copies have no tags, so all
+ * patches for one peer travel as ONE buffer whose segments are ordered by direction on both
+ * sides.  Host-only (no CUDA): tests/dist_host_worker.py drives a gloo exchange from it. */
+typedef struct {
+    int npeers;
+    int peer[DLESM_MAXCOMM];                    /* 0-based rank, ascending; may be this rank */
+    int nsend[DLESM_MAXCOMM], nrecv[DLESM_MAXCOMM];             /* segments per peer         */
+    int send_slot[DLESM_MAXCOMM][DLESM_MAXCOMM];  /* 0-based indices into the send lists ... */
+    int recv_slot[DLESM_MAXCOMM][DLESM_MAXCOMM];  /* ... and recv lists, in buffer order      */
+    long long send_off[DLESM_MAXCOMM], recv_off[DLESM_MAXCOMM];  /* element offsets, 1 field */
+    long long send_n[DLESM_MAXCOMM], recv_n[DLESM_MAXCOMM];      /* elements per field        */
+    long long send_total, recv_total;
+} dlesm_comm_plan;
+int dlesm_comm_plan_build(const dlesm_comms *tables, int rank1, dlesm_comm_plan *out);
+
 /* ------------------------------------------------------------------------------------ */
 /* HOST MIRROR: grid_type -- src/grid_mod.f90:75-157                                     */
 /* ------------------------------------------------------------------------------------ */

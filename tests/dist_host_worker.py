@@ -1,0 +1,188 @@
+"""CPU multi-process check of the host-side distributed logic (gloo, world_size >= 2).
+
+Every rank builds its own decomposition, grid, field bounds and map_comms tables through the
+product's C ABI (host-only entry points: no CUDA is touched), derives the per-peer message
+plan the device exchange uses (dlesm_comm_plan_build), and then really exchanges halos with
+its peers over gloo -- numpy pack in plan order, one buffer per peer, numpy unpack.  The
+result must equal the oracle's exchange_generic run over all ranks (bit for bit, edges and
+corners).  Also checks that the tables of different ranks pair up (every send has the matching
+receive on the peer) and that the NCCL-id bootstrap plumbing (128 bytes from rank 1 to all)
+works over the process group.
+
+This file is test infrastructure: the numpy pack/unpack here stands in for the CUDA pack/unpack
+kernels and gloo for NCCL, so that the plan logic is exercised by real processes on a CPU box.
+"""
+from __future__ import annotations
+
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+import dl_esm_inf_b200 as fd  # noqa: E402
+from dl_esm_inf_b200.api import comm_plan  # noqa: E402
+from oracle import oracle as O  # noqa: E402
+
+RANK = int(os.environ.get("RANK", 0))
+WORLD = int(os.environ.get("WORLD_SIZE", 1))
+BCS_EXT = (fd.GO_BC_EXTERNAL, fd.GO_BC_EXTERNAL, fd.GO_BC_NONE)
+BCS_PER = (fd.GO_BC_PERIODIC, fd.GO_BC_PERIODIC, fd.GO_BC_NONE)
+NCHECK = 0
+
+
+def ok(cond, msg):
+    global NCHECK
+    if not cond:
+        raise AssertionError("rank %d: %s" % (RANK + 1, msg))
+    NCHECK += 1
+
+
+def pack(a, c, slots, send=True):
+    out = []
+    for s in slots:
+        if send:
+            i0, j0, nx, ny = c.isrcsend[s], c.jsrcsend[s], c.nxsend[s], c.nysend[s]
+        else:
+            i0, j0, nx, ny = c.idesrecv[s], c.jdesrecv[s], c.nxrecv[s], c.nyrecv[s]
+        out.append(a[i0 - 1:i0 - 1 + nx, j0 - 1:j0 - 1 + ny].flatten(order="F"))   # i fastest
+    return np.concatenate(out) if out else np.zeros(0)
+
+
+def unpack(a, c, slots, buf):
+    q = 0
+    for s in slots:
+        i0, j0, nx, ny = c.idesrecv[s], c.jdesrecv[s], c.nxrecv[s], c.nyrecv[s]
+        a[i0 - 1:i0 - 1 + nx, j0 - 1:j0 - 1 + ny] = buf[q:q + nx * ny].reshape((nx, ny), order="F")
+        q += nx * ny
+
+
+def gloo_exchange(a, c, plan):
+    """what dlesm_dev_halo_exchange does, with gloo for NCCL and numpy for the kernels"""
+    ops, recvs, selfbuf = [], [], None
+    for g in range(plan.npeers):
+        peer = plan.peer[g]
+        sslots = [plan.send_slot[g][q] for q in range(plan.nsend[g])]
+        rslots = [plan.recv_slot[g][q] for q in range(plan.nrecv[g])]
+        sbuf = torch.from_numpy(pack(a, c, sslots))
+        ok(sbuf.numel() == plan.send_n[g], "send_n of the plan")
+        if peer == RANK:
+            selfbuf = (rslots, sbuf.numpy().copy())
+            continue
+        rbuf = torch.zeros(int(plan.recv_n[g]), dtype=torch.float64)
+        if sbuf.numel():
+            ops.append(dist.P2POp(dist.isend, sbuf, peer))
+        if rbuf.numel():
+            ops.append(dist.P2POp(dist.irecv, rbuf, peer))
+        recvs.append((rslots, rbuf))
+    if ops:
+        for w in dist.batch_isend_irecv(ops):
+            w.wait()
+    for rslots, rbuf in recvs:
+        unpack(a, c, rslots, rbuf.numpy())
+    if selfbuf:
+        unpack(a, c, *selfbuf)
+
+
+def tables_pair_up(c):
+    """every send of mine has the matching receive on the peer: same size, same direction"""
+    mine = [(c.destination[s], c.dirsend[s], c.nxsend[s], c.nysend[s]) for s in range(c.nsend)]
+    theirs = [(c.source[r], c.dirrecv[r], c.nxrecv[r], c.nyrecv[r]) for r in range(c.nrecv)]
+    gathered_s, gathered_r = [None] * WORLD, [None] * WORLD
+    dist.all_gather_object(gathered_s, mine)
+    dist.all_gather_object(gathered_r, theirs)
+    for dst, d, nx, ny in mine:
+        ok((RANK, d, nx, ny) in gathered_r[dst], "send to rank %d dir %d has no matching receive" % (dst + 1, d))
+    for src, d, nx, ny in theirs:
+        ok((RANK, d, nx, ny) in gathered_s[src], "receive from rank %d dir %d has no matching send" % (src + 1, d))
+
+
+def case(nx, ny, offset, bcs, periodic, alignment):
+    if alignment:
+        os.environ["DL_ESM_ALIGNMENT"] = str(alignment)
+    else:
+        os.environ.pop("DL_ESM_ALIGNMENT", None)
+    fd.set_extensions(fd.EXT_PERIODIC_DISTMEM if periodic else 0)
+    g = fd.grid_type(fd.GO_ARAKAWA_C, bcs, offset)
+    g.decompose(nx, ny)
+    try:
+        # grid_init installs the tables into the device context (host memory only)
+        fd.grid_init(g, 1.0, 1.0)
+    except fd.GoceanStop as e:  # pragma: no cover
+        raise AssertionError("grid_init failed: %s" % e)
+    c = g.comms
+    plan = comm_plan(c)
+    tables_pair_up(c)
+    rng = np.random.default_rng(1000 + nx * 7 + ny)
+    if periodic:
+        # The reference (and therefore the oracle's map_comms) refuses periodic BCs with more
+        # than one rank; the wrap-around tables are this project's extension and
+        # are defined by the serial semantics: after the exchange every halo cell, corners
+        # included, holds the value of the periodic global field at the wrapped position.
+        G = np.asfortranarray(rng.uniform(-1, 1, size=(nx, ny)))
+        sub = g.subdomain
+        li = sub.internal
+        a = np.full((g.nx, g.ny), -7.0, order="F")
+        gi = sub.glob.xstart + np.arange(li.nx) - 1
+        gj = sub.glob.ystart + np.arange(li.ny) - 1
+        a[li.xstart - 1:li.xstop, li.ystart - 1:li.ystop] = G[np.ix_(gi, gj)]
+        gloo_exchange(a, c, plan)
+        ji = np.arange(li.xstart - 1, li.xstop + 2)
+        jj = np.arange(li.ystart - 1, li.ystop + 2)
+        wi = (sub.glob.xstart + (ji - li.xstart) - 1) % nx
+        wj = (sub.glob.ystart + (jj - li.ystart) - 1) % ny
+        ok(np.array_equal(a[np.ix_(ji - 1, jj - 1)], G[np.ix_(wi, wj)]),
+           "periodic wrap-around exchange (%dx%d) does not reproduce the serial periodic halo" % (nx, ny))
+    else:
+        # the oracle's view of every rank
+        ogs, arrs = [], []
+        for r in range(1, WORLD + 1):
+            O.reset_saved_state()
+            og = O.Grid(O.GO_ARAKAWA_C, bcs, offset)
+            og.decompose(nx, ny, rank=r, nranks=WORLD)
+            og.init(1.0, 1.0, alignment=alignment or 1, dist_mem_enabled=True, metrics=False)
+            ogs.append(og)
+        ok((g.nx, g.ny) == (ogs[RANK].nx, ogs[RANK].ny), "allocation shape")
+        oc = ogs[RANK].comms
+        for name in ("nsend", "nrecv"):
+            ok(getattr(c, name) == getattr(oc, name), "%s differs from the oracle" % name)
+        for og in ogs:
+            arrs.append(np.asfortranarray(rng.uniform(-1, 1, size=(og.nx, og.ny))))
+        mine = arrs[RANK].copy(order="F")
+        O.exchange_all(arrs, [og.comms for og in ogs])
+        gloo_exchange(mine, c, plan)
+        ok(np.array_equal(mine, arrs[RANK]),
+           "gloo exchange by the product's plan differs from the oracle (%dx%d)" % (nx, ny))
+    os.environ.pop("DL_ESM_ALIGNMENT", None)
+    fd.set_extensions(0)
+
+
+def main():
+    dist.init_process_group("gloo")
+    fd.gocean_initialise(RANK + 1, WORLD)            # host only: no device, no NCCL
+    ok(fd.get_rank() == RANK + 1 and fd.get_num_ranks() == WORLD, "rank bookkeeping")
+    ok(fd.on_master() == (RANK == 0), "on_master")
+    # NCCL-id plumbing: 128 bytes from rank 1 to everyone through the process group
+    blob = torch.zeros(128, dtype=torch.uint8)
+    if RANK == 0:
+        blob = torch.arange(128, dtype=torch.uint8)
+    dist.broadcast(blob, 0)
+    ok(bytes(blob.numpy().tobytes()) == bytes(range(128)), "id broadcast")
+    for shape in ((10, 4), (4, 10), (10, 10), (37, 23), (64, 48)):
+        case(*shape, fd.GO_OFFSET_NE, BCS_EXT, False, None)
+    case(10, 10, fd.GO_OFFSET_NE, BCS_EXT, False, 8)
+    for shape in ((16, 16), (33, 47), (64, 96)):
+        case(*shape, fd.GO_OFFSET_SW, BCS_PER, True, 2)
+    dist.barrier()
+    if RANK == 0:
+        print("HOST DIST OK %d checks on %d ranks" % (NCHECK, WORLD), flush=True)
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

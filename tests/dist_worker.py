@@ -1,0 +1,255 @@
+"""Multi-rank GPU parity worker: one process per GPU, launched by tests/test_multi_gpu.py (or by
+hand) as
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+        --master-port P tests/dist_worker.py
+
+Every rank drives its tile through the public API (device-resident fields, NCCL / NVLink halo
+exchange) and compares with the CPU oracle, which simulates ALL ranks of the same decomposition
+in-process.  The cases are the reference's own distributed tests:
+example/model.f90, tests/dist_mem/test_halos.f90, test_gsum.f90, test_reduction.f90, plus the
+periodic shallow-water extension against the serial oracle run.
+Prints "DIST OK <n checks>" on rank 0 and exits 0, or raises.
+"""
+from __future__ import annotations
+
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+import dl_esm_inf_b200 as fd  # noqa: E402
+from oracle import oracle as O  # noqa: E402
+
+RANK = int(os.environ.get("RANK", 0))
+WORLD = int(os.environ.get("WORLD_SIZE", 1))
+LOCAL = int(os.environ.get("LOCAL_RANK", 0))
+BCS_EXT = (fd.GO_BC_EXTERNAL, fd.GO_BC_EXTERNAL, fd.GO_BC_NONE)
+BCS_PER = (fd.GO_BC_PERIODIC, fd.GO_BC_PERIODIC, fd.GO_BC_NONE)
+POINTS = (fd.GO_U_POINTS, fd.GO_V_POINTS, fd.GO_T_POINTS, fd.GO_F_POINTS)
+NCHECK = 0
+
+
+def ok(cond, msg):
+    global NCHECK
+    if not cond:
+        raise AssertionError("rank %d: %s" % (RANK + 1, msg))
+    NCHECK += 1
+
+
+def bring_up():
+    torch.cuda.set_device(LOCAL)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", LOCAL))
+    fd.gocean_initialise(RANK + 1, WORLD, device=LOCAL)
+    idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
+    if RANK == 0:
+        idt = torch.frombuffer(bytearray(fd.comm_unique_id()), dtype=torch.uint8).cuda()
+    dist.broadcast(idt, 0)
+    fd.gocean_initialise(RANK + 1, WORLD, device=LOCAL, comm_id=bytes(idt.cpu().numpy().tobytes()))
+
+
+def oracle_grids(nx, ny, offset, bcs, tmask=True, alignment=1):
+    """the oracle's grid of every rank"""
+    out = []
+    for r in range(1, WORLD + 1):
+        O.reset_saved_state()
+        g = O.Grid(O.GO_ARAKAWA_C, bcs, offset)
+        g.decompose(nx, ny, rank=r, nranks=WORLD)
+        tm = None
+        if tmask:
+            tm = np.ones((g.subdomain.glob.nx, g.subdomain.glob.ny), dtype=np.int32, order="F")
+        g.init(1.0, 1.0, tmask=tm, alignment=alignment)
+        out.append(g)
+    return out
+
+
+def my_grid(nx, ny, offset, bcs, tmask=True, dx=1.0, dy=1.0):
+    g = fd.grid_type(fd.GO_ARAKAWA_C, bcs, offset)
+    g.decompose(nx, ny)
+    tm = None
+    if tmask:
+        sub = g.subdomain
+        tm = np.ones((sub.glob.nx, sub.glob.ny), dtype=np.int32, order="F")
+    fd.grid_init(g, dx, dy, tm)
+    return g
+
+
+def hill(og, fb_internal, points, nx_alloc, ny_alloc):
+    """tests/dist_mem/test_halos.f90:142-189: externals get a wrong-but-plausible value, the
+    internal region 10000*xpos + ypos at the staggered global position"""
+    a = np.full((nx_alloc, ny_alloc), -1000.0 - og.rank, order="F")
+    sub = og.subdomain
+    i = fb_internal
+    for jj in range(i.ystart, i.ystop + 1):
+        for ji in range(i.xstart, i.xstop + 1):
+            xpos = float(sub.glob.xstart + ji - sub.internal.xstart)
+            ypos = float(sub.glob.ystart + jj - sub.internal.ystart)
+            if points == fd.GO_U_POINTS or points == fd.GO_F_POINTS:
+                xpos += 0.5
+            if points == fd.GO_V_POINTS or points == fd.GO_F_POINTS:
+                ypos += 0.5
+            a[ji - 1, jj - 1] = 10000.0 * xpos + ypos
+    return a
+
+
+def case_example_model():
+    """example/model.f90:54-109 at np = WORLD: 4x10, NE offset, external BCs, fields = rank"""
+    ogs = oracle_grids(4, 10, O.GO_OFFSET_NE, BCS_EXT)
+    g = my_grid(4, 10, fd.GO_OFFSET_NE, BCS_EXT)
+    want = 0.0
+    ofs = [O.Field(og, O.GO_T_POINTS) for og in ogs]
+    for og, of in zip(ogs, ofs):
+        of.data[:, :] = float(og.rank)
+        want += of.checksum()
+    for pts in POINTS:
+        f = fd.r2d_field(g, pts)
+        fd.set_field(f, float(RANK + 1))
+        f.halo_exchange(1)
+        got = fd.field_checksum(f)
+        ok(abs(got - want) <= 1e-12 * abs(want), "example checksum %r != %r" % (got, want))
+        f.free()
+    if WORLD == 2:
+        ok(want == 60.0, "derived np=2 answer of example/model.f90 is 60.0, oracle says %r" % want)
+
+
+def case_halos(jpiglo, jpjglo, alignment=None):
+    """tests/dist_mem/test_halos.f90 pattern, all four staggerings, compared with the oracle's
+    exchange_generic on every cell of the local array (edges and corners)"""
+    if alignment:
+        os.environ["DL_ESM_ALIGNMENT"] = str(alignment)
+    else:
+        os.environ.pop("DL_ESM_ALIGNMENT", None)
+    ogs = oracle_grids(jpiglo, jpjglo, O.GO_OFFSET_NE, BCS_EXT, alignment=alignment or 1)
+    g = my_grid(jpiglo, jpjglo, fd.GO_OFFSET_NE, BCS_EXT)
+    og = ogs[RANK]
+    ok((g.nx, g.ny) == (og.nx, og.ny), "allocation shape %r vs oracle %r" % ((g.nx, g.ny), (og.nx, og.ny)))
+    fields, wants = [], []
+    for pts in POINTS:
+        arrs = []
+        for o in ogs:
+            fb = O.field_bounds(o, pts)
+            arrs.append(hill(o, fb.internal, pts, o.nx, o.ny))
+        mine = arrs[RANK].copy(order="F")
+        O.exchange_all(arrs, [o.comms for o in ogs])
+        f = fd.r2d_field(g, pts)
+        f.set_data(mine)
+        fields.append(f)
+        wants.append(arrs[RANK])
+    # two fields one by one, two in one grouped exchange
+    fields[0].halo_exchange(1)
+    fields[1].halo_exchange(1)
+    fd.halo_exchange_fields(fields[2:], 1)
+    for pts, f, want in zip(POINTS, fields, wants):
+        got = f.get_data()
+        ok(np.array_equal(got, want), "halo exchange %dx%d points %d differs from the oracle at %s"
+           % (jpiglo, jpjglo, pts, np.argwhere(got != want)[:4].tolist()))
+        # the reference's own assertion: edge halos equal hill within 1e-8 (test_halos.f90:191-265)
+        f.free()
+    os.environ.pop("DL_ESM_ALIGNMENT", None)
+
+
+def case_gsum():
+    """tests/dist_mem/test_gsum.f90: internal = 1, external = -100, checksum = jpiglo*jpjglo"""
+    g = my_grid(4, 10, fd.GO_OFFSET_NE, BCS_EXT)
+    for pts in POINTS:
+        f = fd.r2d_field(g, pts)
+        a = np.full((g.nx, g.ny), -100.0, order="F")
+        i = f.internal
+        a[i.xstart - 1:i.xstop, i.ystart - 1:i.ystop] = 1.0
+        f.set_data(a)
+        got = fd.field_checksum(f)
+        ok(abs(got - 40.0) < 1e-8, "gsum %r != 40" % got)
+        f.free()
+
+
+def case_reduction(n=10):
+    """tests/dist_mem/test_reduction.f90: scatter (i-1)+(j-1)*n, +1, gather on the master"""
+    g = fd.grid_type(fd.GO_ARAKAWA_C, BCS_EXT, fd.GO_OFFSET_NE)
+    g.decompose(n, n)
+    fd.grid_init(g, 1.0, 1.0)                      # no tmask, as the reference test
+    glob = np.asfortranarray(np.arange(n)[:, None] + np.arange(n)[None, :] * float(n))
+    f = fd.r2d_field(g, fd.GO_T_POINTS, init_global_data=glob)
+    sub = g.subdomain
+    a = f.get_data().copy(order="F")
+    i = sub.internal
+    for jj in range(i.ystart, i.ystop + 1):
+        for ji in range(i.xstart, i.xstop + 1):
+            gi, gj = sub.glob.xstart + ji - i.xstart, sub.glob.ystart + jj - i.ystart
+            ok(a[ji - 1, jj - 1] == (gi - 1) + (gj - 1) * n, "scatter value at (%d,%d)" % (ji, jj))
+    f.set_data(a + 1.0)
+    out = f.gather_inner_data()
+    if RANK == 0:
+        ok(np.array_equal(out, glob + 1.0), "gather_inner_data differs")
+    f.free()
+
+
+def case_shallow_water(n_x, n_y, nsteps, alignment, mode):
+    """periodic shallow water across ranks (extension F4) == the serial oracle, bit for bit"""
+    os.environ["DL_ESM_ALIGNMENT"] = str(alignment)
+    fd.set_extensions(fd.EXT_PERIODIC_DISTMEM)
+    osw = O.ShallowWater(n_x, n_y, alignment=1)
+    init = {k: osw.f[k].copy(order="F") for k in ("u", "v", "p")}
+    for _ in range(nsteps):
+        osw.step()
+    g = fd.grid_type(fd.GO_ARAKAWA_C, BCS_PER, fd.GO_OFFSET_SW)
+    g.decompose(n_x, n_y)
+    fd.grid_init(g, 1.0e5, 1.0e5)
+    sw = fd.shallow_water(g, mode=mode)
+    # this tile's part of the oracle's initial state, halo ring included (periodic wrap)
+    sub = g.subdomain
+    li = sub.internal
+    ji = np.arange(li.xstart - 1, li.xstop + 2)           # local 1-based columns incl. halo
+    jj = np.arange(li.ystart - 1, li.ystop + 2)
+    gi = (sub.glob.xstart + (ji - li.xstart) - 1) % n_x + 1   # 0-based index into the oracle array
+    gj = (sub.glob.ystart + (jj - li.ystart) - 1) % n_y + 1
+    local = {}
+    for k in ("u", "v", "p"):
+        a = np.zeros((g.nx, g.ny), order="F")
+        a[np.ix_(ji - 1, jj - 1)] = init[k][np.ix_(gi, gj)]
+        local[k] = a
+    sw.set_state(local["u"], local["v"], local["p"])
+    sw.step(nsteps)
+    oi = osw.fb["t"].internal
+    for name in ("u", "v", "p", "uold", "vold", "pold"):
+        out = sw.field(name).gather_inner_data()
+        if RANK == 0:
+            want = osw.f[name][oi.xstart - 1:oi.xstop, oi.ystart - 1:oi.ystop]
+            ok(np.array_equal(out, want), "shallow water %dx%d mode %d field %s: %d cells differ, max rel %.3e"
+               % (n_x, n_y, mode, name, int((out != want).sum()),
+                  float(np.max(np.abs(out - want) / np.maximum(np.abs(want), 1e-300)))))
+    got, want = sw.checksums(), osw.checksums()
+    for a, b in zip(got, want):
+        ok(abs(a - b) <= 1e-12 * abs(b), "checksum %r vs oracle %r" % (a, b))
+    sw.free()
+    fd.set_extensions(0)
+    os.environ.pop("DL_ESM_ALIGNMENT", None)
+
+
+def main():
+    bring_up()
+    case_example_model()
+    case_gsum()
+    for shape in ((10, 4), (4, 10), (10, 10), (37, 23)):
+        case_halos(*shape)
+    case_halos(10, 10, alignment=8)
+    case_halos(64, 48, alignment=64)
+    case_reduction(10)
+    for mode in (fd.SW_UNFUSED, fd.SW_FUSED):
+        case_shallow_water(64, 96, 5, 2, mode)
+        case_shallow_water(130, 77, 4, 64, mode)
+    case_shallow_water(1024, 1024, 3, 64, fd.SW_FUSED)
+    dist.barrier()
+    fd.gocean_finalise()
+    if RANK == 0:
+        print("DIST OK %d checks on %d ranks" % (NCHECK, WORLD), flush=True)
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
