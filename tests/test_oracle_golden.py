@@ -192,3 +192,22 @@ def test_device_io(alignment):
         want[4:8, 4:8] = 0.0
         want[4:6, 4:6] = 2.0
         assert np.array_equal(f.data, want)
+
+
+# --- the fixture file itself -----------------------------------------------------------
+def test_golden_fixture_matches_what_these_tests_assert():
+    """tests/golden/reference_known_answers.json is the committed record of the reference's
+    known answers; the numbers asserted above must be the ones in the file."""
+    import json
+    import os
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "reference_known_answers.json")
+    gold = json.load(open(path))
+    for nranks, want in gold["example_model"]["checksum_by_nranks"].items():
+        test_example_model(int(nranks), want)
+    g = make_ranks(1, *gold["example_model"]["domain"])[0]
+    assert [g.nx, g.ny] == gold["example_model"]["alloc_A1"]
+    assert gold["test_gsum"]["checksum"] == gold["test_gsum"]["domain"][0] * gold["test_gsum"]["domain"][1]
+    for nranks, jpiglo, jpjglo in gold["test_halos"]["cases"]:
+        test_halos(nranks, jpiglo, jpjglo)
+    for a in gold["test_device_io"]["alignments"]:
+        test_device_io(a)
