@@ -167,6 +167,23 @@ SIGNATURES = {
 _lib = None
 
 
+def _preload_nccl():
+    """libdlesm_b200.so needs `libnccl.so.2`.  If the launcher (torch.distributed) is imported
+    later in the same process it insists on its own, newer wheel copy of that soname; loading
+    the system copy first would leave torch with missing symbols.  So prefer the wheel's copy
+    when it exists (same soname: the dynamic loader then reuses it for both)."""
+    import importlib.util
+    try:
+        spec = importlib.util.find_spec("nvidia")
+    except (ImportError, ValueError):
+        spec = None
+    for base in (spec.submodule_search_locations if spec and spec.submodule_search_locations else []):
+        cand = os.path.join(base, "nccl", "lib", "libnccl.so.2")
+        if os.path.exists(cand):
+            C.CDLL(cand, mode=C.RTLD_GLOBAL)
+            return
+
+
 def lib():
     """The loaded product library.  Raises if it has not been built (python -m
     dl_esm_inf_b200.build, or __graft_entry__.build())."""
@@ -177,6 +194,7 @@ def lib():
         raise RuntimeError(
             "libdlesm_b200.so is missing (%s). Build it with `python -m dl_esm_inf_b200.build`; "
             "there is no CPU fallback." % LIB_PATH)
+    _preload_nccl()
     L = C.CDLL(LIB_PATH, mode=C.RTLD_GLOBAL)
     for name, (res, args) in SIGNATURES.items():
         fn = getattr(L, name)  # AttributeError if the .so lacks a declared symbol
