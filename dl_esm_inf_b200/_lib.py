@@ -88,6 +88,7 @@ SIGNATURES = {
     "dlesm_get_num_ranks": (_I, []),
     "dlesm_on_master": (_I, []),
     "dlesm_global_sum": (_I, [_PD]),
+    "dlesm_gather_host": (_I, [_PD, C.c_longlong, _PD]),
     "dlesm_reset_saved_state": (None, []),
     "dlesm_set_extensions": (_I, [_I]),
     "dlesm_go_decompose": (_V, [_I] * 6),

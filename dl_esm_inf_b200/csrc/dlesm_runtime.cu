@@ -256,6 +256,45 @@ extern "C" int dlesm_global_sum(double *var)
     return DLESM_OK;
 }
 
+// gather (src/parallel/parallel_utils_mod.f90:242-255; stub :154-161): every rank contributes n
+// doubles from host memory, rank 1 receives them back to back.  Staged through the device so the
+// transfer rides NCCL/NVLink like every other message of this library.
+extern "C" int dlesm_gather_host(const double *send_buffer, long long n, double *recv_buffer)
+{
+    clear_error();
+    const int nranks = pstate().nranks, me = pstate().rank;
+    if (n < 0 || !send_buffer || (me == 1 && !recv_buffer)) {
+        set_error(DLESM_ERR_ARGS, "gather: invalid arguments");
+        return DLESM_ERR_ARGS;
+    }
+    if (nranks == 1) {
+        std::memcpy(recv_buffer, send_buffer, static_cast<size_t>(n) * sizeof(double));
+        return DLESM_OK;
+    }
+    Context &c = ctx();
+    if (!c.comm_ready) {
+        set_error(DLESM_ERR_STATE, "gather: communicator not initialised (dlesm_comm_init)");
+        return DLESM_ERR_STATE;
+    }
+    const size_t un = static_cast<size_t>(n);
+    int rc = ensure_scratch(un * (me == 1 ? nranks : 1));
+    if (rc != DLESM_OK) return rc;
+    CU(cudaMemcpyAsync(c.scratch, send_buffer, un * sizeof(double), cudaMemcpyHostToDevice, c.stream));
+    NC(ncclGroupStart());
+    if (me == 1) {
+        for (int r = 1; r < nranks; ++r)
+            NC(ncclRecv(c.scratch + static_cast<size_t>(r) * un, un, ncclDouble, r, c.comm, c.stream));
+    } else {
+        NC(ncclSend(c.scratch, un, ncclDouble, 0, c.comm, c.stream));
+    }
+    NC(ncclGroupEnd());
+    if (me == 1)
+        CU(cudaMemcpyAsync(recv_buffer, c.scratch, un * nranks * sizeof(double), cudaMemcpyDeviceToHost,
+                           c.stream));
+    CU(cudaStreamSynchronize(c.stream));
+    return DLESM_OK;
+}
+
 // =========================================================================================
 // decomposition / comm tables (host only)
 // =========================================================================================

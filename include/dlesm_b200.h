@@ -134,6 +134,9 @@ int dlesm_on_master(void);     /* src/parallel_mod.f90:337-340 */
 /* global_sum (parallel_utils_mod.f90:230-238): in-place sum over ranks of one double
  * (no-op for one rank, as the stub :148-150) */
 int dlesm_global_sum(double *var);
+/* gather (parallel_utils_mod.f90:242-255, stub :154-161): every rank contributes n doubles
+ * (host memory); rank 1's recv_buffer (n * nranks doubles) receives them in rank order. */
+int dlesm_gather_host(const double *send_buffer, long long n, double *recv_buffer);
 /* go_decompose keeps halo_width between calls (SAVEd local, src/parallel_mod.f90:103-105);
  * this resets it to 1 as at program start. */
 void dlesm_reset_saved_state(void);
