@@ -429,6 +429,24 @@ class shallow_water:
     def step(self, nsteps=1):
         _chk(_lib.lib().dlesm_sw_step(self._h, nsteps))
 
+    def step_host(self, host_in, host_out=None, band_rows=0):
+        """One step with HOST state: host_in = (u, v, p, uold, vold, pold) Fortran-ordered
+        (nx, ny) float64 arrays (or raw addresses of such buffers); results land in host_out
+        (default: in place).  Upload, sweep and download are pipelined in row bands."""
+        if host_out is None:
+            host_out = host_in
+        PD = C.POINTER(C.c_double)
+
+        def ptr(a):
+            if isinstance(a, np.ndarray):
+                assert a.dtype == np.float64 and a.flags.f_contiguous
+                return a.ctypes.data_as(PD)
+            return C.cast(a, PD)
+
+        ins = (PD * 6)(*[ptr(a) for a in host_in])
+        outs = (PD * 6)(*[ptr(a) for a in host_out])
+        _chk(_lib.lib().dlesm_sw_step_host(self._h, ins, outs, int(band_rows)))
+
     def checksums(self):
         return tuple(field_checksum(self.field(n)) for n in ("p", "u", "v"))
 

@@ -41,6 +41,10 @@ struct Context {
     bool device_ready = false;
     int device = -1;
     cudaStream_t stream = nullptr;
+    cudaStream_t s_h2d = nullptr, s_d2h = nullptr;  // copy streams of the banded host step
+    std::vector<cudaEvent_t> band_events;           // reused pool (2 per band + 1)
+    double *ring_host = nullptr;                    // pinned staging of the halo ring
+    size_t ring_host_n = 0;
     double *partials = nullptr;   // checksum partials + result
     double *result = nullptr;
     double *host_result = nullptr;  // pinned
@@ -179,6 +183,8 @@ extern "C" int dlesm_device_init(int device)
     }
     CU(cudaSetDevice(device));
     CU(cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&c.s_h2d, cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&c.s_d2h, cudaStreamNonBlocking));
     CU(cudaMalloc(&c.partials, (k::kChecksumBlocks + 8) * sizeof(double)));
     c.result = c.partials + k::kChecksumBlocks;
     CU(cudaMallocHost(&c.host_result, 8 * sizeof(double)));
@@ -1573,6 +1579,125 @@ extern "C" int dlesm_sw_step(dlesm_sw_t *s, int nsteps)
         if (first) s->tdt = s->tdt + s->tdt;
         ++s->ncycle;
     }
+    return DLESM_OK;
+}
+
+// One model time step driven with HOST state (the `e2e` path of bench.py): instead of
+// write_to_device x6 -> step -> read_from_device x6 back to back (H2D, compute and D2H
+// serialised: 2 x 12.9 GB over one PCIe direction at a time at 16384^2), the tile is streamed
+// through the device in row bands.  Band k+1 uploads while band k is swept while band k-1
+// downloads: three streams, both PCIe directions busy, the sweep hidden behind the copies.
+// Each row of each field crosses the bus exactly once per direction.
+extern "C" int dlesm_sw_step_host(dlesm_sw_t *s, const double *const host_in[6], double *const host_out[6],
+                                  int band_rows)
+{
+    clear_error();
+    if (!s || s->mode != DLESM_SW_FUSED) {
+        set_error(DLESM_ERR_ARGS, "sw_step_host: needs a fused-mode shallow-water object");
+        return DLESM_ERR_ARGS;
+    }
+    int rc = ensure_device();
+    if (rc != DLESM_OK) return rc;
+    Context &c = ctx();
+    dlesm_grid &g = *s->grid;
+    dlesm_field **f = s->f;
+    const dlesm_region &rt = f[DLESM_SW_P]->fb.internal;
+    const int nx = f[0]->nx, ny = f[0]->ny;
+    const size_t row_bytes = static_cast<size_t>(nx) * sizeof(double);
+    if (band_rows <= 0) band_rows = std::max(64, ((rt.ny / 128) + 31) / 32 * 32);
+    const int nbands = (rt.ny + band_rows - 1) / band_rows;
+    while (c.band_events.size() < static_cast<size_t>(2 * nbands + 2)) {
+        cudaEvent_t e;
+        CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        c.band_events.push_back(e);
+    }
+    const int first = s->ncycle == 0;
+    // inputs: device slots U,V,P,UOLD,VOLD,POLD; outputs: UNEW,VNEW,PNEW + the filtered *OLD
+    static const int in_slot[6] = {DLESM_SW_U, DLESM_SW_V, DLESM_SW_P, DLESM_SW_UOLD, DLESM_SW_VOLD, DLESM_SW_POLD};
+    static const int out_slot[6] = {DLESM_SW_UNEW, DLESM_SW_VNEW, DLESM_SW_PNEW,
+                                    DLESM_SW_UOLD, DLESM_SW_VOLD, DLESM_SW_POLD};
+    // whatever is queued on the library stream (a previous step) must finish before we overwrite
+    cudaEvent_t e_start = c.band_events[2 * nbands];
+    CU(cudaEventRecord(e_start, c.stream));
+    CU(cudaStreamWaitEvent(c.s_h2d, e_start, 0));
+    CU(cudaStreamWaitEvent(c.s_d2h, e_start, 0));
+    int up_next = 1;  // next row (1-based) not yet uploaded
+    for (int b = 0; b < nbands; ++b) {
+        const int j0 = rt.ystart + b * band_rows;
+        const int j1 = std::min(rt.ystop, j0 + band_rows - 1);
+        // rows the sweep of [j0, j1] reads: j0-1 .. j1+1 of u,v,p; j0..j1 of the old fields
+        const int up_to = (b == nbands - 1) ? ny : j1 + 1;
+        if (up_to >= up_next) {
+            const size_t off = static_cast<size_t>(up_next - 1) * nx;
+            const size_t bytes = static_cast<size_t>(up_to - up_next + 1) * row_bytes;
+            for (int q = 0; q < 6; ++q)
+                CU(cudaMemcpyAsync(static_cast<double *>(f[in_slot[q]]->dptr) + off, host_in[q] + off, bytes,
+                                   cudaMemcpyHostToDevice, c.s_h2d));
+            up_next = up_to + 1;
+        }
+        cudaEvent_t e_up = c.band_events[2 * b], e_done = c.band_events[2 * b + 1];
+        CU(cudaEventRecord(e_up, c.s_h2d));
+        CU(cudaStreamWaitEvent(c.stream, e_up, 0));
+        rc = dlesm_sw_step_fused(f[DLESM_SW_U]->dptr, f[DLESM_SW_V]->dptr, f[DLESM_SW_P]->dptr,
+                                 f[DLESM_SW_UOLD]->dptr, f[DLESM_SW_VOLD]->dptr, f[DLESM_SW_POLD]->dptr,
+                                 f[DLESM_SW_UNEW]->dptr, f[DLESM_SW_VNEW]->dptr, f[DLESM_SW_PNEW]->dptr,
+                                 g.info.dx, g.info.dy, s->tdt, s->alpha, first, rt.xstart, rt.xstop, j0, j1,
+                                 s->tmask_dev, s->variant);
+        if (rc != DLESM_OK) return rc;
+        CU(cudaEventRecord(e_done, c.stream));
+        CU(cudaStreamWaitEvent(c.s_d2h, e_done, 0));
+        const size_t off = static_cast<size_t>(j0 - 1) * nx;
+        const size_t bytes = static_cast<size_t>(j1 - j0 + 1) * row_bytes;
+        for (int q = 0; q < 6; ++q)
+            CU(cudaMemcpyAsync(host_out[q] + off, static_cast<const double *>(f[out_slot[q]]->dptr) + off, bytes,
+                               cudaMemcpyDeviceToHost, c.s_d2h));
+    }
+    // halo ring of the three new fields: periodic copies (one rank) or the NCCL exchange
+    rc = sw_fill_halos(s, DLESM_SW_UNEW, 3);
+    if (rc != DLESM_OK) return rc;
+    // ring -> host: the two halo rows are contiguous; the two halo columns are gathered on the
+    // device, shipped as one block and scattered by the host
+    const size_t col_n = static_cast<size_t>(ny);
+    rc = ensure_scratch(6 * col_n);
+    if (rc != DLESM_OK) return rc;
+    if (c.ring_host_n < 6 * col_n) {
+        if (c.ring_host) cudaFreeHost(c.ring_host);
+        c.ring_host = nullptr;
+        c.ring_host_n = 0;
+        CU(cudaMallocHost(&c.ring_host, 6 * col_n * sizeof(double)));
+        c.ring_host_n = 6 * col_n;
+    }
+    const int xw = rt.xstart - 1, xe = rt.xstop + 1;
+    for (int q = 0; q < 3; ++q) {
+        const double *d = static_cast<const double *>(f[DLESM_SW_UNEW + q]->dptr);
+        CU(k::gather_box(d, nx, k::Box{xw, xw, 1, ny}, c.scratch + (2 * q) * col_n, c.stream));
+        CU(k::gather_box(d, nx, k::Box{xe, xe, 1, ny}, c.scratch + (2 * q + 1) * col_n, c.stream));
+    }
+    CU(cudaMemcpyAsync(c.ring_host, c.scratch, 6 * col_n * sizeof(double), cudaMemcpyDeviceToHost, c.stream));
+    // all band downloads must have landed before the ring rows/columns overwrite their edges
+    cudaEvent_t e_dl = c.band_events[2 * nbands + 1];
+    CU(cudaEventRecord(e_dl, c.s_d2h));
+    CU(cudaStreamWaitEvent(c.stream, e_dl, 0));
+    for (int q = 0; q < 3; ++q) {
+        const double *d = static_cast<const double *>(f[DLESM_SW_UNEW + q]->dptr);
+        const int rows[2] = {rt.ystart - 1, rt.ystop + 1};
+        for (int r : rows) {
+            const size_t off = static_cast<size_t>(r - 1) * nx;
+            CU(cudaMemcpyAsync(host_out[q] + off, d + off, row_bytes, cudaMemcpyDeviceToHost, c.stream));
+        }
+    }
+    CU(cudaStreamSynchronize(c.stream));
+    for (int q = 0; q < 3; ++q) {
+        double *h = host_out[q];
+        const double *w = c.ring_host + (2 * q) * col_n, *e = c.ring_host + (2 * q + 1) * col_n;
+        for (int j = rt.ystart - 1; j <= rt.ystop + 1; ++j) {
+            h[static_cast<size_t>(j - 1) * nx + (xw - 1)] = w[j - 1];
+            h[static_cast<size_t>(j - 1) * nx + (xe - 1)] = e[j - 1];
+        }
+    }
+    for (int q = 0; q < 3; ++q) std::swap(f[DLESM_SW_U + q]->dptr, f[DLESM_SW_UNEW + q]->dptr);
+    if (first) s->tdt = s->tdt + s->tdt;
+    ++s->ncycle;
     return DLESM_OK;
 }
 

@@ -419,6 +419,16 @@ int dlesm_sw_init_device(dlesm_sw_t *s);
 /* initial u,v,p from host arrays (nx,ny) incl. valid halos; uold,vold,pold <- copies */
 int dlesm_sw_set_state(dlesm_sw_t *s, const double *u, const double *v, const double *p);
 int dlesm_sw_step(dlesm_sw_t *s, int nsteps);
+/* One time step with HOST state, streamed through the device in row bands (upload of band
+ * k+1, sweep of band k and download of band k-1 overlap; both PCIe directions busy).
+ * host_in[6]  = u, v, p, uold, vold, pold  (nx*ny each, column-major, u/v/p with valid halos);
+ * host_out[6] = the new u, v, p (halos filled) and the time-filtered uold, vold, pold.
+ * host_out[q] may be host_in[q] (in place).  Pinned memory (dlesm_host_alloc/register) makes
+ * the copies asynchronous.  Equivalent to write_to_device x6, dlesm_sw_step(s, 1),
+ * read_from_device x6 of the reference's hooks; the device state ends up the same.
+ * band_rows <= 0 selects the default.  Fused mode only. */
+int dlesm_sw_step_host(dlesm_sw_t *s, const double *const host_in[6], double *const host_out[6],
+                       int band_rows);
 dlesm_field_t *dlesm_sw_field(dlesm_sw_t *s, int which);
 int dlesm_sw_set_variant(dlesm_sw_t *s, int variant);
 /* kernels launched by this library since process start (all streams) */

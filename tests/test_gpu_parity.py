@@ -559,3 +559,41 @@ def test_fullsize_translation_invariance_and_fused_equals_unfused(n, align, monk
     for k in ("u", "v", "p"):
         assert np.array_equal(c.field(k).get_data()[sl], np.roll(res_a[k], (sx, sy), axis=(0, 1))), k
     c.free()
+
+
+# ---------------------------------------------------------------------------------------------
+# the step with HOST state, pipelined in row bands (bench.py's e2e path)
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("n_x,n_y,align,band_rows,masked", [
+    (64, 64, None, 0, False), (130, 77, 64, 10, False), (257, 300, 2, 64, False),
+    (300, 523, 64, 97, True), (1024, 1024, 64, 0, False), (96, 40, 64, 1000, False)])
+@pytest.mark.parametrize("in_place", [True, False])
+def test_step_host_banded_matches_oracle(n_x, n_y, align, band_rows, masked, in_place, monkeypatch):
+    tm = periodic_island_mask(n_x + 2, n_y + 2, 12345) if masked else None
+    osw, sw = sw_pair(n_x, n_y, fd.SW_FUSED, alignment=align, tmask=tm, monkeypatch=monkeypatch)
+    names = ("u", "v", "p", "uold", "vold", "pold")
+    host = [np.asfortranarray(osw.f[n].copy()) for n in names]
+    i = osw.fb["t"].internal
+    inner = (slice(i.xstart - 1, i.xstop), slice(i.ystart - 1, i.ystop))
+    ring = (slice(i.xstart - 2, i.xstop + 1), slice(i.ystart - 2, i.ystop + 1))
+    for step in range(3):
+        osw.step()
+        if in_place:
+            sw.step_host(host, band_rows=band_rows)
+        else:
+            out = [np.full_like(a, np.nan) for a in host]
+            sw.step_host(host, out, band_rows=band_rows)
+            # only the results are defined in `out`: keep the padding beyond the halo ring
+            for n, a, o in zip(names, host, out):
+                sl = ring if n in ("u", "v", "p") else inner
+                assert not np.isnan(o[sl]).any(), n
+                a[sl] = o[sl]
+        for n, a in zip(names, host):
+            sl = ring if n in ("u", "v", "p") else inner       # new fields: halos included
+            assert np.array_equal(a[sl], osw.f[n][sl]), (n, step)
+    # the device ends in the same state as the host copies
+    assert_state_equal(osw, sw, internal_only=("uold", "vold", "pold"))
+    # and a device-resident step afterwards continues from it
+    osw.step()
+    sw.step(1)
+    assert_state_equal(osw, sw, internal_only=("uold", "vold", "pold"))
