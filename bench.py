@@ -199,6 +199,11 @@ def run_ours(args):
     sw = fd.shallow_water(grid, dt=90.0, alpha=0.001, mode=fd.SW_FUSED if args.mode == "fused" else fd.SW_UNFUSED)
     sw.set_variant(args.variant)
     sw.init_device()
+    halo = args.halo
+    if halo == "auto":
+        halo = "push" if (world > 1 and args.mode == "fused") else "exchange"
+    if halo == "push":
+        sw.set_halo_mode(fd.HALO_PUSH)              # collective: maps the neighbours' arrays (NVLink peer memory)
     mass0 = fd.field_checksum(sw.field("p"))
 
     sampler = ClockSampler(local_rank)
@@ -279,7 +284,10 @@ def run_ours(args):
                                    "double periodic, GO_OFFSET_SW, FP64, DL_ESM_ALIGNMENT=%d, mode=%s"
                                    % (n, n, gx, gy, probe.nx, probe.ny, args.alignment, args.mode),
                        "l2": "inputs larger than L2 (9 fields x %.2f GB per GPU)" % (grid.nx * grid.ny * 8 / 1e9),
-                       "fused_variant": args.variant, "parallelism": "tile-per-GPU %dx%d" % (probe.nx, probe.ny)},
+                       "fused_variant": args.variant, "parallelism": "tile-per-GPU %dx%d" % (probe.nx, probe.ny),
+                       "halo": ("push: the fused sweep stores the neighbours' halo cells over NVLink peer memory, "
+                                "flag hand-shake per step" if halo == "push" else
+                                ("periodic halo kernel" if world == 1 else "pack -> NCCL send/recv -> unpack"))},
             "clocks": clocks, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
             "e2e": e2e, "checksums_p_u_v": list(cks),
             "hbm_frac_of_measured_whole_step": (BYTES_PER_POINT * local_points * args.steps /
@@ -381,6 +389,8 @@ def main():
     ap.add_argument("--variant", type=int, default=0)
     ap.add_argument("--mode", default="fused", choices=["fused", "unfused"])
     ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--halo", default="auto", choices=["auto", "push", "exchange"],
+                    help="halo fill of the fused step: push (in-kernel peer stores) or exchange (NCCL); auto = push when N>1")
     ap.add_argument("--band-rows", type=int, default=0, help="row-band height of the pipelined host step (0 = default)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()

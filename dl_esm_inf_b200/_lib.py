@@ -143,6 +143,7 @@ SIGNATURES = {
     "dlesm_dev_periodic_halos": (_I, [_V, _I, _I, _I, _I, _I, _I]),
     "dlesm_dev_set_comms": (_I, [C.POINTER(Comms)]),
     "dlesm_dev_halo_exchange": (_I, [C.POINTER(_V), _I]),
+    "dlesm_dev_peer_register": (_I, [C.POINTER(_V), _I]),
     "dlesm_dev_grid_upload": (_I, [_I, _I, _PI, C.POINTER(_PD), C.POINTER(_V)]),
     "dlesm_compute_cu": (_I, [_V, _V, _V, _I, _I, _I, _I, _V]),
     "dlesm_compute_cv": (_I, [_V, _V, _V, _I, _I, _I, _I, _V]),
@@ -160,6 +161,7 @@ SIGNATURES = {
     "dlesm_sw_step_host": (_I, [_V, C.POINTER(_PD), C.POINTER(_PD), _I]),
     "dlesm_sw_field": (_V, [_V, _I]),
     "dlesm_sw_set_variant": (_I, [_V, _I]),
+    "dlesm_sw_set_halo_mode": (_I, [_V, _I]),
     "dlesm_kernel_launch_count": (C.c_longlong, []),
     "dlesm_profile_enable": (_I, [_I]),
     "dlesm_profile_read": (_I, [_PD, C.POINTER(C.c_longlong), _I]),

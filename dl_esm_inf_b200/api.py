@@ -31,6 +31,8 @@ GRID_ARRAYS = ("tmask", "dx_t", "dy_t", "dx_u", "dy_u", "dx_v", "dy_v", "dx_f", 
                "area_u", "area_v", "gphiu", "gphiv", "gphif", "xt", "yt")
 SW_FIELDS = ("u", "v", "p", "uold", "vold", "pold", "unew", "vnew", "pnew", "cu", "cv", "z", "h")
 SW_UNFUSED, SW_FUSED = 0, 1
+HALO_EXCHANGE, HALO_PUSH = 0, 1
+FUSED_PUSH = 0x1000
 
 
 class GoceanStop(RuntimeError):
@@ -425,6 +427,11 @@ class shallow_water:
 
     def set_variant(self, variant):
         _chk(_lib.lib().dlesm_sw_set_variant(self._h, variant))
+
+    def set_halo_mode(self, mode):
+        """HALO_EXCHANGE (periodic copies / pack-NCCL-unpack) or HALO_PUSH (the fused sweep stores
+        the neighbours' halo cells itself over NVLink peer memory).  Collective."""
+        _chk(_lib.lib().dlesm_sw_set_halo_mode(self._h, mode))
 
     def step(self, nsteps=1):
         _chk(_lib.lib().dlesm_sw_step(self._h, nsteps))

@@ -215,7 +215,24 @@ struct TmaStepParams {
     int seg_rows;
     int i_origin;   // first output column (1-based) of strip 0: b.xs, or lower to align strips to 128 B
     SwScalars sc;
+    PushPlan push;
 };
+
+// edge outputs of row j, column i -> the neighbours' halo cells (rare: only threads whose
+// column/segment meets a push box get here)
+__device__ __noinline__ void push_row(const PushPlan &pp, unsigned mask, int i, int j, double un, double vn,
+                                      double pn)
+{
+    for (unsigned m = mask; m; m &= m - 1) {
+        const PushSeg &g = pp.seg[__ffs(m) - 1];
+        if (j >= g.j0 && j <= g.j1) {
+            const size_t d = idx(g.dpitch, g.ides + (i - g.i0), g.jdes + (j - g.j0));
+            g.dst[0][d] = un;
+            g.dst[1][d] = vn;
+            g.dst[2][d] = pn;
+        }
+    }
+}
 
 constexpr int kDefaultTmaVariant = 25;
 constexpr int align128(int v) { return (v + 127) & ~127; }
@@ -254,7 +271,7 @@ __global__ void __launch_bounds__(TX + 32, MINB)
 fused_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_constant__ CUtensorMap tm_v,
                  const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUtensorMap tm_uo,
                  const __grid_constant__ CUtensorMap tm_vo, const __grid_constant__ CUtensorMap tm_po,
-                 const __grid_constant__ CUtensorMap tm_mask, const TmaStepParams prm)
+                 const __grid_constant__ CUtensorMap tm_mask, const __grid_constant__ TmaStepParams prm)
 {
     using Cfg = TmaCfg<TX, RY, STAGES, M, ALN>;
     constexpr int BW = Cfg::BW;
@@ -324,6 +341,14 @@ fused_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_constant
     const size_t pitch = static_cast<size_t>(prm.pitch);
     // steps whose outputs are stored: 2 <= t < nsteps
     int t_lo = active ? 2 : (1 << 30), t_hi = nsteps;
+    // push boxes this thread's column and this CTA's rows can meet (0 for almost every thread)
+    unsigned pmask = 0;
+    if (active)
+        for (int q = 0; q < prm.push.n; ++q) {
+            const PushSeg &g = prm.push.seg[q];
+            if (i >= g.i0 && i <= g.i1 && g.j1 >= j0 && g.j0 <= j1) pmask |= 1u << q;
+        }
+    int jrow = j0 - 2;
     for (int c = 0; c < nchunks; ++c) {
         const int s = c % STAGES;
         mbar_wait(&full[s], (c / STAGES) & 1);
@@ -356,8 +381,10 @@ fused_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_constant
                     if (!M || out.wv) __stcs(prm.vold + qo, out.vold);
                     if (!M || out.wt) __stcs(prm.pold + qo, out.pold);
                 }
+                if (pmask) push_row(prm.push, pmask, i, jrow, out.unew, out.vnew, out.pnew);
             }
             qo += pitch;
+            ++jrow;
         }
         t_lo -= RY;
         t_hi -= RY;
@@ -481,6 +508,7 @@ cudaError_t launch_tma_mf(const FusedArgs &a, cudaStream_t s)
     }();
     const int seg_rows = pick_seg_rows(w, h, TX, 148 * MINB, RY, target);
     prm.pitch = a.pitch; prm.b = a.b; prm.seg_rows = seg_rows; prm.i_origin = i_origin; prm.sc = a.sc;
+    prm.push = a.push;
     auto kern = fused_tma_kernel<TX, RY, STAGES, MINB, M, FIRST, ALN>;
     static bool attr_done = false;
     if (!attr_done) {
@@ -548,9 +576,16 @@ const char *fused_variant_name(int variant)
     return v ? v->name : "unknown";
 }
 
+bool fused_push_supported(const FusedArgs &a, int variant)
+{
+    const bool tma_ok = (a.pitch % 2 == 0) && (a.tmask == nullptr || a.pitch % 4 == 0) && encode_fn() != nullptr;
+    return tma_ok && variant != 1;
+}
+
 cudaError_t sw_step_fused(const FusedArgs &a, int variant, cudaStream_t s)
 {
     if (a.b.xe < a.b.xs || a.b.ye < a.b.ys) return cudaSuccess;
+    if (a.push.n > 0 && !fused_push_supported(a, variant)) return cudaErrorNotSupported;
     // FP64 rows must start 16-byte aligned (even pitch); int32 tmask rows need pitch % 4 == 0
     const bool tma_ok = (a.pitch % 2 == 0) && (a.tmask == nullptr || a.pitch % 4 == 0) && encode_fn() != nullptr;
     if (variant == 0) variant = tma_ok ? kDefaultTmaVariant : 1;

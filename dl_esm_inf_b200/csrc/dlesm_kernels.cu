@@ -360,6 +360,40 @@ cudaError_t gather_box(const double *f, int pitch, Box b, double *packed, cudaSt
 }
 
 // ---------------------------------------------------------------------------------------
+// Neighbour hand-shake of the halo push.  Launched after the fused sweep on the same stream:
+// the sweep's peer stores are complete when this kernel starts, so a system-scope release of
+// the epoch into each neighbour's flag array publishes them; then wait (acquire) until every
+// neighbour has published the same epoch into ours.  One thread per neighbour.  The wait is
+// bounded (~20 s of SM clocks): on time-out *err is set and the kernel returns instead of
+// hanging the GPU.
+// ---------------------------------------------------------------------------------------
+__global__ void peer_signal_wait_kernel(PeerFlags pf, unsigned long long epoch, int *err)
+{
+    const int q = threadIdx.x;
+    if (q >= pf.n) return;
+    __threadfence_system();
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(pf.remote[q]), "l"(epoch) : "memory");
+    const long long t0 = clock64();
+    for (;;) {
+        unsigned long long v;
+        asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(pf.local[q]) : "memory");
+        if (v >= epoch) break;
+        if (clock64() - t0 > 40000000000LL) {
+            atomicExch(err, 1);
+            break;
+        }
+        __nanosleep(200);
+    }
+}
+cudaError_t peer_signal_wait(const PeerFlags &pf, unsigned long long epoch, int *err, cudaStream_t s)
+{
+    if (pf.n <= 0) return cudaSuccess;
+    peer_signal_wait_kernel<<<1, 32, 0, s>>>(pf, epoch, err);
+    count_launch();
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------
 // Un-fused shallow-water sweeps.  One launch per reference-style kernel; the loop nest of
 // SURVEY CS-3 (jj outer, ji inner over the output field's internal region) becomes a 2-D
 // grid with i along threadIdx.x; the per-point functor is the "kernel code".

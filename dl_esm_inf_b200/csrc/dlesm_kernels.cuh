@@ -76,6 +76,34 @@ cudaError_t compute_pnew(double *pnew, const double *pold, const double *cu, con
 cudaError_t time_smooth(const double *f, const double *fnew, double *fold, int pitch, Box b,
                         double alpha, const int *tmask, int points, cudaStream_t s);
 
+// ---- halo push: the fused sweep stores its edge outputs straight into the neighbours' halo
+// cells (peer-mapped device memory over NVLink, or this rank's own array for a wrap-around
+// neighbour that is itself).  One entry per send-list entry of map_comms
+// (src/parallel_comms_mod.f90:70-83): source box in this rank's array -> (ides, jdes) in the
+// destination rank's array.
+constexpr int kMaxPush = 16;
+struct PushSeg {
+    int i0, i1, j0, j1;   // source box, 1-based inclusive
+    int ides, jdes;       // where (i0, j0) lands in the destination array
+    int dpitch;           // destination pitch
+    int pad_;
+    double *dst[3];       // destination unew, vnew, pnew
+};
+struct PushPlan {
+    int n;
+    int pad_;
+    PushSeg seg[kMaxPush];
+};
+// signal every remote neighbour that this rank's pushes of `epoch` are complete, then wait for
+// theirs.  remote[q]: this rank's slot in neighbour q's flag array; local[q]: neighbour q's
+// slot in this rank's flag array.  err (device int) is set if the wait times out.
+struct PeerFlags {
+    int n;
+    unsigned long long *remote[kMaxPush];
+    const unsigned long long *local[kMaxPush];
+};
+cudaError_t peer_signal_wait(const PeerFlags &pf, unsigned long long epoch, int *err, cudaStream_t s);
+
 // ---- the fused step ----
 struct FusedArgs {
     const double *u, *v, *p;
@@ -85,7 +113,10 @@ struct FusedArgs {
     int pitch, ny;
     Box b;              // internal region (identical for U,V,T,F under SW periodic)
     SwScalars sc;
+    PushPlan push;      // push.n == 0: halos of the new fields are left to the caller
 };
+// whether sw_step_fused can push halos for these arguments (TMA variants only)
+bool fused_push_supported(const FusedArgs &a, int variant);
 constexpr int kNumFusedVariants = 6;
 cudaError_t sw_step_fused(const FusedArgs &a, int variant, cudaStream_t s);
 const char *fused_variant_name(int variant);

@@ -1,6 +1,7 @@
 // dlesm_runtime.cu -- runtime context (device, stream, scratch, NCCL communicator, field
 // registry) and the C ABI of include/dlesm_b200.h.  There is no CPU fallback anywhere in
 // this file: a device entry point either runs its CUDA kernel or fails with DLESM_ERR_CUDA.
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <nccl.h>
 
@@ -8,6 +9,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <map>
 #include <mutex>
 #include <string>
 #include <unordered_map>
@@ -60,6 +62,17 @@ struct Context {
     dlesm_comms comms{};
     std::vector<PeerGroup> groups;
     long long send_total = 0, recv_total = 0;  // per field
+    // halo push: peer-mapped neighbours (dlesm_dev_peer_register)
+    struct PeerView {
+        std::vector<double *> by_rank;  // this field's counterpart on rank r (0-based), or null
+        std::vector<int> pitch_by_rank; // its pitch there (tile widths may differ by one)
+    };
+    std::unordered_map<const void *, PeerView> peers;
+    unsigned long long *flags = nullptr;              // [kMaxRanks] epochs published by neighbours
+    std::vector<unsigned long long *> peer_flags;     // neighbours' flag arrays, by rank
+    std::vector<void *> ipc_opened;                   // mappings to close at finalise
+    unsigned long long push_epoch = 0;
+    int *push_err = nullptr;                          // device flag: a neighbour wait timed out
     // profiling of the dominant kernel
     bool profile = false;
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events;
@@ -443,7 +456,16 @@ extern "C" int dlesm_dev_sync(void)
 {
     int rc = ensure_device();
     if (rc != DLESM_OK) return rc;
-    CU(cudaStreamSynchronize(ctx().stream));
+    Context &c = ctx();
+    CU(cudaStreamSynchronize(c.stream));
+    if (c.push_err) {
+        int flag = 0;
+        CU(cudaMemcpy(&flag, c.push_err, sizeof(int), cudaMemcpyDeviceToHost));
+        if (flag) {
+            set_error(DLESM_ERR_STATE, "halo push: a neighbour did not publish its epoch in time (ranks out of step?)");
+            return DLESM_ERR_STATE;
+        }
+    }
     return DLESM_OK;
 }
 
@@ -745,6 +767,168 @@ extern "C" int dlesm_dev_halo_exchange(void *const *fields, int nfields)
     return DLESM_OK;
 }
 
+// ---------------------------------------------------------------------------------------
+// Halo push set-up.  Collective over all ranks; every rank passes its fields in the same order.
+// Each field's allocation is exported with cudaIpcGetMemHandle, the handles travel through one
+// ncclAllGather, and the handles of this rank's neighbours (the destinations of its map_comms
+// send list) are opened, which maps the neighbours' arrays into this process over NVLink.
+// A flag array per rank is shared the same way for the per-step hand-shake.
+// ---------------------------------------------------------------------------------------
+namespace {
+constexpr int kMaxRanks = 64;
+struct IpcEntry {
+    cudaIpcMemHandle_t handle;
+    long long offset;   // bytes from the allocation base (cudaMalloc may sub-allocate)
+    int pitch, ny;
+};
+static_assert(sizeof(IpcEntry) == 80, "IpcEntry layout");
+
+typedef CUresult (*GetAddressRangeFn)(CUdeviceptr *, size_t *, CUdeviceptr);
+GetAddressRangeFn address_range_fn()
+{
+    static GetAddressRangeFn fn = [] {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuMemGetAddressRange", &p, cudaEnableDefault, &q) != cudaSuccess ||
+            q != cudaDriverEntryPointSuccess)
+            p = nullptr;
+        return reinterpret_cast<GetAddressRangeFn>(p);
+    }();
+    return fn;
+}
+
+int make_entry(const void *ptr, int pitch, int ny, IpcEntry &e)
+{
+    std::memset(&e, 0, sizeof(e));
+    GetAddressRangeFn fn = address_range_fn();
+    CUdeviceptr base = reinterpret_cast<CUdeviceptr>(ptr);
+    size_t size = 0;
+    if (!fn || fn(&base, &size, reinterpret_cast<CUdeviceptr>(ptr)) != CUDA_SUCCESS) {
+        set_error(DLESM_ERR_CUDA, "peer_register: cuMemGetAddressRange failed");
+        return DLESM_ERR_CUDA;
+    }
+    CU(cudaIpcGetMemHandle(&e.handle, reinterpret_cast<void *>(base)));
+    e.offset = static_cast<long long>(reinterpret_cast<CUdeviceptr>(ptr) - base);
+    e.pitch = pitch;
+    e.ny = ny;
+    return DLESM_OK;
+}
+
+std::map<std::string, void *> &opened_handles()
+{
+    static std::map<std::string, void *> m;
+    return m;
+}
+
+int open_entry(const IpcEntry &e, void **out)
+{
+    std::string key(reinterpret_cast<const char *>(&e.handle), sizeof(e.handle));
+    auto &m = opened_handles();
+    auto it = m.find(key);
+    void *base = nullptr;
+    if (it != m.end()) {
+        base = it->second;
+    } else {
+        CU(cudaIpcOpenMemHandle(&base, e.handle, cudaIpcMemLazyEnablePeerAccess));
+        m[key] = base;
+        ctx().ipc_opened.push_back(base);
+    }
+    *out = static_cast<char *>(base) + e.offset;
+    return DLESM_OK;
+}
+}  // namespace
+
+extern "C" int dlesm_dev_peer_register(void *const *fields, int nfields)
+{
+    clear_error();
+    Context &c = ctx();
+    if (nfields < 1 || nfields > 12) {
+        set_error(DLESM_ERR_ARGS, "peer_register: between 1 and 12 fields per call");
+        return DLESM_ERR_ARGS;
+    }
+    int rc = ensure_device();
+    if (rc != DLESM_OK) return rc;
+    const int nranks = pstate().nranks, me0 = pstate().rank - 1;
+    if (nranks > kMaxRanks) {
+        set_error(DLESM_ERR_ARGS, "peer_register: too many ranks");
+        return DLESM_ERR_ARGS;
+    }
+    std::vector<FieldRec> recs(nfields);
+    for (int q = 0; q < nfields; ++q) {
+        rc = lookup(fields[q], recs[q]);
+        if (rc != DLESM_OK) return rc;
+    }
+    if (!c.flags) {
+        CU(cudaMalloc(&c.flags, kMaxRanks * sizeof(unsigned long long)));
+        CU(cudaMemset(c.flags, 0, kMaxRanks * sizeof(unsigned long long)));
+        CU(cudaMalloc(&c.push_err, sizeof(int)));
+        CU(cudaMemset(c.push_err, 0, sizeof(int)));
+        c.peer_flags.assign(nranks, nullptr);
+        c.peer_flags[me0] = c.flags;
+    }
+    if (nranks == 1) {
+        for (int q = 0; q < nfields; ++q) {
+            Context::PeerView pv;
+            pv.by_rank.assign(1, static_cast<double *>(fields[q]));
+            pv.pitch_by_rank.assign(1, recs[q].nx);
+            c.peers[fields[q]] = pv;
+        }
+        return DLESM_OK;
+    }
+    if (!c.comm_ready || !c.have_comms) {
+        set_error(DLESM_ERR_STATE, "peer_register: needs dlesm_comm_init and dlesm_dev_set_comms first");
+        return DLESM_ERR_STATE;
+    }
+    // my entries: the fields, then the flag array
+    const int nent = nfields + 1;
+    std::vector<IpcEntry> mine(nent), all(static_cast<size_t>(nent) * nranks);
+    for (int q = 0; q < nfields; ++q) {
+        rc = make_entry(fields[q], recs[q].nx, recs[q].ny, mine[q]);
+        if (rc != DLESM_OK) return rc;
+    }
+    rc = make_entry(c.flags, 0, 0, mine[nfields]);
+    if (rc != DLESM_OK) return rc;
+    const size_t blob = sizeof(IpcEntry) * nent;
+    rc = ensure_scratch((blob * (nranks + 1) + 7) / 8);
+    if (rc != DLESM_OK) return rc;
+    char *dsend = reinterpret_cast<char *>(c.scratch), *drecv = dsend + blob;
+    CU(cudaMemcpyAsync(dsend, mine.data(), blob, cudaMemcpyHostToDevice, c.stream));
+    NC(ncclAllGather(dsend, drecv, blob, ncclChar, c.comm, c.stream));
+    CU(cudaMemcpyAsync(all.data(), drecv, blob * nranks, cudaMemcpyDeviceToHost, c.stream));
+    CU(cudaStreamSynchronize(c.stream));
+    // neighbours = peers of the exchange plan
+    std::vector<char> is_nb(nranks, 0);
+    for (const auto &g : c.groups) is_nb[g.peer0] = 1;
+    for (int q = 0; q < nfields; ++q) {
+        Context::PeerView pv;
+        pv.by_rank.assign(nranks, nullptr);
+        pv.pitch_by_rank.assign(nranks, 0);
+        c.peers[fields[q]] = pv;
+    }
+    for (int r = 0; r < nranks; ++r) {
+        if (!is_nb[r]) continue;
+        const IpcEntry *er = &all[static_cast<size_t>(r) * nent];
+        for (int q = 0; q < nfields; ++q) {
+            void *p = fields[q];
+            if (r != me0) {
+                rc = open_entry(er[q], &p);
+                if (rc != DLESM_OK) return rc;
+            }
+            c.peers[fields[q]].by_rank[r] = static_cast<double *>(p);
+            c.peers[fields[q]].pitch_by_rank[r] = er[q].pitch;
+        }
+        if (r != me0 && !c.peer_flags[r]) {
+            void *p = nullptr;
+            rc = open_entry(er[nfields], &p);
+            if (rc != DLESM_OK) return rc;
+            c.peer_flags[r] = static_cast<unsigned long long *>(p);
+        }
+    }
+    // nobody pushes before everybody has mapped: a one-double allreduce is the barrier
+    double one = 1.0;
+    return dlesm_global_sum(&one);
+}
+
 extern "C" int dlesm_dev_grid_upload(int nx, int ny, const int *tmask, const double *const metrics[16],
                                      void *device_ptrs[17])
 {
@@ -904,7 +1088,58 @@ extern "C" int dlesm_sw_step_fused(const void *u, const void *v, const void *p, 
     a.sc.fsdx = 4.0 / dx; a.sc.fsdy = 4.0 / dy;
     a.sc.tdts8 = tdt / 8.0; a.sc.tdtsdx = tdt / dx; a.sc.tdtsdy = tdt / dy;
     a.sc.alpha = alpha; a.sc.first = first;
+    a.push.n = 0;
     Context &c = ctx();
+    const bool push = (variant & DLESM_FUSED_PUSH) != 0;
+    variant &= ~DLESM_FUSED_PUSH;
+    k::PeerFlags pf{};
+    if (push) {
+        // one push box per send-list entry (src/parallel_comms_mod.f90:70-83), aimed at the
+        // destination rank's counterparts of unew, vnew, pnew
+        if (!c.have_comms) {
+            set_error(DLESM_ERR_STATE, "sw_step_fused: halo push needs the comm tables (dlesm_dev_set_comms)");
+            return DLESM_ERR_STATE;
+        }
+        if (!k::fused_push_supported(a, variant)) {
+            set_error(DLESM_ERR_ARGS, "sw_step_fused: halo push needs a TMA variant (even pitch; pitch % 4 == 0 with a mask)");
+            return DLESM_ERR_ARGS;
+        }
+        const void *outs[3] = {unew, vnew, pnew};
+        const Context::PeerView *pv[3];
+        for (int q = 0; q < 3; ++q) {
+            auto it = c.peers.find(outs[q]);
+            if (it == c.peers.end()) {
+                set_error(DLESM_ERR_STATE, "sw_step_fused: halo push needs unew, vnew, pnew registered (dlesm_dev_peer_register)");
+                return DLESM_ERR_STATE;
+            }
+            pv[q] = &it->second;
+        }
+        const dlesm_comms &t = c.comms;
+        const int me0 = pstate().rank - 1;
+        const bool single = pstate().nranks == 1;
+        bool seen[64] = {false};
+        for (int sidx = 0; sidx < t.nsend; ++sidx) {
+            const int dest = single ? 0 : t.destination[sidx];
+            k::PushSeg &g = a.push.seg[a.push.n++];
+            g.i0 = t.isrcsend[sidx]; g.i1 = g.i0 + t.nxsend[sidx] - 1;
+            g.j0 = t.jsrcsend[sidx]; g.j1 = g.j0 + t.nysend[sidx] - 1;
+            g.ides = t.idessend[sidx]; g.jdes = t.jdessend[sidx];
+            g.dpitch = pv[0]->pitch_by_rank[dest];
+            for (int q = 0; q < 3; ++q) {
+                g.dst[q] = pv[q]->by_rank[dest];
+                if (!g.dst[q]) {
+                    set_error(DLESM_ERR_STATE, "sw_step_fused: a neighbour's field is not mapped");
+                    return DLESM_ERR_STATE;
+                }
+            }
+            if (dest != me0 && !seen[dest]) {
+                seen[dest] = true;
+                pf.remote[pf.n] = c.peer_flags[dest] + me0;
+                pf.local[pf.n] = c.flags + dest;
+                ++pf.n;
+            }
+        }
+    }
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     if (c.profile) {
         if (c.prof_used == c.prof_events.size()) {
@@ -925,6 +1160,12 @@ extern "C" int dlesm_sw_step_fused(const void *u, const void *v, const void *p, 
     }
     if (e != cudaSuccess) return fail_cuda(e, "sw_step_fused");
     if (c.profile) CU(cudaEventRecord(e1, st));
+    if (push && pf.n > 0) {
+        // neighbours must not start their next sweep before these pushes landed, nor push into
+        // a buffer this rank is still reading: publish the epoch, wait for theirs
+        ++c.push_epoch;
+        CU(k::peer_signal_wait(pf, c.push_epoch, c.push_err, st));
+    }
     return DLESM_OK;
 }
 
@@ -1439,6 +1680,7 @@ struct dlesm_sw {
     long long ncycle = 0;
     const int *tmask_dev = nullptr;
     bool periodic_local = true;  // halos by local copies (1 rank) or by exchange (several)
+    bool push = false;           // halos stored by the fused sweep itself (DLESM_HALO_PUSH)
 };
 
 extern "C" dlesm_sw_t *dlesm_sw_create(dlesm_grid_t *g, double dt, double alpha, int mode, int use_tmask)
@@ -1497,6 +1739,40 @@ int sw_fill_halos(dlesm_sw *s, int first_field, int count)
 }
 }  // namespace
 
+extern "C" int dlesm_sw_set_halo_mode(dlesm_sw_t *s, int mode)
+{
+    clear_error();
+    if (mode == DLESM_HALO_EXCHANGE) {
+        s->push = false;
+        return DLESM_OK;
+    }
+    if (mode != DLESM_HALO_PUSH || s->mode != DLESM_SW_FUSED) {
+        set_error(DLESM_ERR_ARGS, "sw_set_halo_mode: DLESM_HALO_PUSH needs the fused mode");
+        return DLESM_ERR_ARGS;
+    }
+    if (s->f[0]->nx % 2 != 0 || (s->tmask_dev && s->f[0]->nx % 4 != 0)) {
+        set_error(DLESM_ERR_ARGS, "sw_set_halo_mode: halo push needs a TMA-eligible pitch (DL_ESM_ALIGNMENT even; a multiple of 4 with a mask)");
+        return DLESM_ERR_ARGS;
+    }
+    int rc;
+    if (pstate().nranks == 1) {
+        // the wrap-around neighbours are this rank itself: tables as map_comms builds them
+        dlesm_comms t;
+        rc = dlesm_map_comms(&s->grid->dh, 1, 1, 1, 1, 1, 1, &t);
+        if (rc == DLESM_OK) rc = dlesm_dev_set_comms(&t);
+        if (rc != DLESM_OK) return rc;
+    }
+    void *bufs[6];
+    for (int q = 0; q < 3; ++q) {
+        bufs[q] = s->f[DLESM_SW_U + q]->dptr;
+        bufs[3 + q] = s->f[DLESM_SW_UNEW + q]->dptr;
+    }
+    rc = dlesm_dev_peer_register(bufs, 6);   // collective
+    if (rc != DLESM_OK) return rc;
+    s->push = true;
+    return DLESM_OK;
+}
+
 extern "C" int dlesm_sw_init_device(dlesm_sw_t *s)
 {
     clear_error();
@@ -1549,10 +1825,12 @@ extern "C" int dlesm_sw_step(dlesm_sw_t *s, int nsteps)
             rc = dlesm_sw_step_fused(P(DLESM_SW_U), P(DLESM_SW_V), P(DLESM_SW_P), P(DLESM_SW_UOLD), P(DLESM_SW_VOLD),
                                      P(DLESM_SW_POLD), P(DLESM_SW_UNEW), P(DLESM_SW_VNEW), P(DLESM_SW_PNEW), dx, dy,
                                      s->tdt, s->alpha, first, rt.xstart, rt.xstop, rt.ystart, rt.ystop,
-                                     s->tmask_dev, s->variant);
+                                     s->tmask_dev, s->variant | (s->push ? DLESM_FUSED_PUSH : 0));
             if (rc != DLESM_OK) return rc;
-            rc = sw_fill_halos(s, DLESM_SW_UNEW, 3);
-            if (rc != DLESM_OK) return rc;
+            if (!s->push) {
+                rc = sw_fill_halos(s, DLESM_SW_UNEW, 3);
+                if (rc != DLESM_OK) return rc;
+            }
             // u <- unew by rotating the device buffers (copy_field semantics without the copy)
             for (int q = 0; q < 3; ++q) std::swap(f[DLESM_SW_U + q]->dptr, f[DLESM_SW_UNEW + q]->dptr);
         } else {

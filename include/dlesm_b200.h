@@ -395,6 +395,17 @@ int dlesm_time_smooth(const void *f, const void *fnew, void *fold, double alpha,
  * time-filtered uold,vold,pold in place.  96 B / point.  Halos of the new fields are NOT
  * filled (follow with dlesm_dev_periodic_halos or dlesm_dev_halo_exchange).  `variant`
  * selects the kernel (0 = default/best; others documented in DESIGN.md, for benchmarking). */
+/* Halo push (multi-GPU form of the fused step).  OR DLESM_FUSED_PUSH into `variant`: the sweep
+ * then also stores its edge outputs straight into the neighbours' halo cells of unew, vnew,
+ * pnew -- peer-mapped device memory over NVLink (or this rank's own array where the wrap-around
+ * neighbour is itself) -- following the send list installed by dlesm_dev_set_comms, and ends
+ * with a flag hand-shake between neighbours.  No pack / NCCL / unpack, no separate halo kernel:
+ * on return (stream order) the halos of the new fields are filled, corners included.
+ * Needs unew, vnew, pnew registered on every rank with dlesm_dev_peer_register (collective,
+ * same order everywhere; register both buffer sets when they rotate), a TMA-eligible pitch,
+ * and all ranks stepping in lockstep. */
+#define DLESM_FUSED_PUSH 0x1000
+int dlesm_dev_peer_register(void *const *fields, int nfields);
 int dlesm_sw_step_fused(const void *u, const void *v, const void *p, void *uold, void *vold,
                         void *pold, void *unew, void *vnew, void *pnew, double dx, double dy,
                         double tdt, double alpha, int first, int xstart, int xstop, int ystart,
@@ -431,6 +442,13 @@ int dlesm_sw_step_host(dlesm_sw_t *s, const double *const host_in[6], double *co
                        int band_rows);
 dlesm_field_t *dlesm_sw_field(dlesm_sw_t *s, int which);
 int dlesm_sw_set_variant(dlesm_sw_t *s, int variant);
+/* How the halos of unew, vnew, pnew get filled after the fused sweep:
+ * DLESM_HALO_EXCHANGE (default): periodic copies on one rank, pack -> NCCL -> unpack on several;
+ * DLESM_HALO_PUSH: the sweep stores them itself into the neighbours' arrays (DLESM_FUSED_PUSH).
+ * Collective: every rank must make the same call. */
+#define DLESM_HALO_EXCHANGE 0
+#define DLESM_HALO_PUSH 1
+int dlesm_sw_set_halo_mode(dlesm_sw_t *s, int mode);
 /* kernels launched by this library since process start (all streams) */
 long long dlesm_kernel_launch_count(void);
 /* CUDA-event time (ms) spent in dominant-kernel launches since the last call with reset=1,

@@ -25,6 +25,7 @@ import torch  # noqa: E402
 import torch.distributed as dist  # noqa: E402
 
 import dl_esm_inf_b200 as fd  # noqa: E402
+from dl_esm_inf_b200 import _lib  # noqa: E402
 from oracle import oracle as O  # noqa: E402
 
 RANK = int(os.environ.get("RANK", 0))
@@ -189,8 +190,24 @@ def case_reduction(n=10):
     f.free()
 
 
-def case_shallow_water(n_x, n_y, nsteps, alignment, mode):
-    """periodic shallow water across ranks (extension F4) == the serial oracle, bit for bit"""
+def case_gather():
+    """parallel_utils_mod gather (src/parallel/parallel_utils_mod.f90:242-255) over NCCL"""
+    import ctypes as C
+    n = 37
+    send = np.arange(n, dtype=np.float64) + 1000.0 * (RANK + 1)
+    recv = np.zeros(n * WORLD)
+    PD = C.POINTER(C.c_double)
+    rc = _lib.lib().dlesm_gather_host(send.ctypes.data_as(PD), n, recv.ctypes.data_as(PD))
+    ok(rc == 0, "gather rc %d" % rc)
+    if RANK == 0:
+        want = np.concatenate([np.arange(n) + 1000.0 * (r + 1) for r in range(WORLD)])
+        ok(np.array_equal(recv, want), "gather differs")
+
+
+def case_shallow_water(n_x, n_y, nsteps, alignment, mode, halo_mode=None):
+    """periodic shallow water across ranks (extension F4) == the serial oracle, bit for bit;
+    halo_mode HALO_PUSH: the fused sweep stores the neighbours' halo cells itself (NVLink peer
+    memory + flag hand-shake) instead of pack -> NCCL -> unpack"""
     os.environ["DL_ESM_ALIGNMENT"] = str(alignment)
     fd.set_extensions(fd.EXT_PERIODIC_DISTMEM)
     osw = O.ShallowWater(n_x, n_y, alignment=1)
@@ -214,7 +231,10 @@ def case_shallow_water(n_x, n_y, nsteps, alignment, mode):
         a[np.ix_(ji - 1, jj - 1)] = init[k][np.ix_(gi, gj)]
         local[k] = a
     sw.set_state(local["u"], local["v"], local["p"])
+    if halo_mode is not None:
+        sw.set_halo_mode(halo_mode)
     sw.step(nsteps)
+    fd.dev_sync()                                   # also reports a push hand-shake time-out
     oi = osw.fb["t"].internal
     for name in ("u", "v", "p", "uold", "vold", "pold"):
         out = sw.field(name).gather_inner_data()
@@ -244,6 +264,9 @@ def main():
         case_shallow_water(64, 96, 5, 2, mode)
         case_shallow_water(130, 77, 4, 64, mode)
     case_shallow_water(1024, 1024, 3, 64, fd.SW_FUSED)
+    case_gather()
+    for shape in ((64, 96, 5, 2), (130, 77, 4, 64), (300, 523, 7, 64), (1024, 1024, 6, 64)):
+        case_shallow_water(*shape, fd.SW_FUSED, halo_mode=fd.HALO_PUSH)
     dist.barrier()
     fd.gocean_finalise()
     if RANK == 0:

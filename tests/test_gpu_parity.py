@@ -597,3 +597,43 @@ def test_step_host_banded_matches_oracle(n_x, n_y, align, band_rows, masked, in_
     osw.step()
     sw.step(1)
     assert_state_equal(osw, sw, internal_only=("uold", "vold", "pold"))
+
+
+# ---------------------------------------------------------------------------------------------
+# halo push: the fused sweep stores the halo cells itself (here: wrap-around neighbours = this
+# rank, so the push targets are local; tests/dist_worker.py runs it across GPUs)
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("n_x,n_y,align,masked", [
+    (64, 64, 2, False), (130, 77, 64, False), (257, 300, 2, False), (127, 33, 64, False),
+    (300, 523, 64, True), (1024, 1024, 64, False)])
+def test_fused_halo_push_matches_oracle(n_x, n_y, align, masked, monkeypatch):
+    tm = periodic_island_mask(n_x + 2, n_y + 2, 12345) if masked else None
+    osw, sw = sw_pair(n_x, n_y, fd.SW_FUSED, alignment=align, tmask=tm, monkeypatch=monkeypatch)
+    try:
+        sw.set_halo_mode(fd.HALO_PUSH)
+        for _ in range(5):
+            osw.step()
+        sw.step(5)
+        fd.dev_sync()
+        # whole arrays: internal points AND the halo ring the sweep pushed (corners included)
+        assert_state_equal(osw, sw, internal_only=("uold", "vold", "pold"))
+        # switching back to the exchange path continues from the same state
+        sw.set_halo_mode(fd.HALO_EXCHANGE)
+        osw.step()
+        sw.step(1)
+        assert_state_equal(osw, sw, internal_only=("uold", "vold", "pold"))
+    finally:
+        empty = fd.Comms()
+        assert _lib.lib().dlesm_dev_set_comms(C.byref(empty)) == 0   # leave the module state clean
+
+
+def test_halo_push_needs_registration_and_tma_pitch(monkeypatch):
+    osw, sw = sw_pair(64, 64, fd.SW_FUSED, alignment=None, monkeypatch=monkeypatch)   # odd pitch 67
+    with pytest.raises(fd.GoceanStop):
+        sw.set_halo_mode(fd.HALO_PUSH)
+    L = _lib.lib()
+    f = [sw.field(n).device_ptr for n in ("u", "v", "p", "uold", "vold", "pold", "unew", "vnew", "pnew")]
+    i = osw.fb["t"].internal
+    rc = L.dlesm_sw_step_fused(*f, 1.0e5, 1.0e5, 90.0, 0.001, 1, i.xstart, i.xstop, i.ystart, i.ystop, None,
+                               fd.FUSED_PUSH)
+    assert rc != 0 and b"push" in L.dlesm_last_error()
