@@ -144,6 +144,7 @@ SIGNATURES = {
     "dlesm_dev_set_comms": (_I, [C.POINTER(Comms)]),
     "dlesm_dev_halo_exchange": (_I, [C.POINTER(_V), _I]),
     "dlesm_dev_peer_register": (_I, [C.POINTER(_V), _I]),
+    "dlesm_dev_peer_unregister_all": (_I, []),
     "dlesm_dev_grid_upload": (_I, [_I, _I, _PI, C.POINTER(_PD), C.POINTER(_V)]),
     "dlesm_compute_cu": (_I, [_V, _V, _V, _I, _I, _I, _I, _V]),
     "dlesm_compute_cv": (_I, [_V, _V, _V, _I, _I, _I, _I, _V]),

@@ -820,7 +820,9 @@ std::map<std::string, void *> &opened_handles()
     return m;
 }
 
-int open_entry(const IpcEntry &e, void **out)
+// `keep`: the mapping lives until finalise (flag arrays); otherwise until the next
+// dlesm_dev_peer_unregister_all
+int open_entry(const IpcEntry &e, void **out, bool keep)
 {
     std::string key(reinterpret_cast<const char *>(&e.handle), sizeof(e.handle));
     auto &m = opened_handles();
@@ -830,13 +832,34 @@ int open_entry(const IpcEntry &e, void **out)
         base = it->second;
     } else {
         CU(cudaIpcOpenMemHandle(&base, e.handle, cudaIpcMemLazyEnablePeerAccess));
-        m[key] = base;
-        ctx().ipc_opened.push_back(base);
+        if (!keep) {
+            m[key] = base;
+            ctx().ipc_opened.push_back(base);
+        }
     }
     *out = static_cast<char *>(base) + e.offset;
     return DLESM_OK;
 }
 }  // namespace
+
+// Collective.  Unmaps every neighbour field mapped by dlesm_dev_peer_register (CUDA requires
+// importers to close before the exporter frees) and ends with a barrier, after which each
+// rank may free its own registered fields.
+extern "C" int dlesm_dev_peer_unregister_all(void)
+{
+    clear_error();
+    Context &c = ctx();
+    if (c.device_ready) CU(cudaStreamSynchronize(c.stream));
+    for (void *base : c.ipc_opened) cudaIpcCloseMemHandle(base);
+    c.ipc_opened.clear();
+    opened_handles().clear();
+    c.peers.clear();
+    if (pstate().nranks > 1 && c.comm_ready) {
+        double one = 1.0;
+        return dlesm_global_sum(&one);
+    }
+    return DLESM_OK;
+}
 
 extern "C" int dlesm_dev_peer_register(void *const *fields, int nfields)
 {
@@ -911,7 +934,7 @@ extern "C" int dlesm_dev_peer_register(void *const *fields, int nfields)
         for (int q = 0; q < nfields; ++q) {
             void *p = fields[q];
             if (r != me0) {
-                rc = open_entry(er[q], &p);
+                rc = open_entry(er[q], &p, false);
                 if (rc != DLESM_OK) return rc;
             }
             c.peers[fields[q]].by_rank[r] = static_cast<double *>(p);
@@ -919,7 +942,7 @@ extern "C" int dlesm_dev_peer_register(void *const *fields, int nfields)
         }
         if (r != me0 && !c.peer_flags[r]) {
             void *p = nullptr;
-            rc = open_entry(er[nfields], &p);
+            rc = open_entry(er[nfields], &p, true);
             if (rc != DLESM_OK) return rc;
             c.peer_flags[r] = static_cast<unsigned long long *>(p);
         }
@@ -1681,6 +1704,7 @@ struct dlesm_sw {
     const int *tmask_dev = nullptr;
     bool periodic_local = true;  // halos by local copies (1 rank) or by exchange (several)
     bool push = false;           // halos stored by the fused sweep itself (DLESM_HALO_PUSH)
+    bool registered = false;     // buffers are mapped by the neighbours (dlesm_dev_peer_register)
 };
 
 extern "C" dlesm_sw_t *dlesm_sw_create(dlesm_grid_t *g, double dt, double alpha, int mode, int use_tmask)
@@ -1767,9 +1791,10 @@ extern "C" int dlesm_sw_set_halo_mode(dlesm_sw_t *s, int mode)
         bufs[q] = s->f[DLESM_SW_U + q]->dptr;
         bufs[3 + q] = s->f[DLESM_SW_UNEW + q]->dptr;
     }
-    rc = dlesm_dev_peer_register(bufs, 6);   // collective
+    rc = dlesm_dev_peer_unregister_all();    // the registered set is replaced (collective)
+    if (rc == DLESM_OK) rc = dlesm_dev_peer_register(bufs, 6);   // collective
     if (rc != DLESM_OK) return rc;
-    s->push = true;
+    s->push = s->registered = true;
     return DLESM_OK;
 }
 
@@ -1992,6 +2017,7 @@ extern "C" int dlesm_sw_set_variant(dlesm_sw_t *s, int variant)
 extern "C" void dlesm_sw_free(dlesm_sw_t *s)
 {
     if (!s) return;
+    if (s->registered) dlesm_dev_peer_unregister_all();   // collective, like the set_halo_mode that mapped them
     for (auto *fl : s->f)
         if (fl) dlesm_free_field(fl);
     delete s;

@@ -406,6 +406,9 @@ int dlesm_time_smooth(const void *f, const void *fnew, void *fold, double alpha,
  * and all ranks stepping in lockstep. */
 #define DLESM_FUSED_PUSH 0x1000
 int dlesm_dev_peer_register(void *const *fields, int nfields);
+/* Collective: unmap every neighbour field mapped so far, then barrier.  Call before freeing
+ * registered fields (importers must close a CUDA IPC mapping before the exporter frees). */
+int dlesm_dev_peer_unregister_all(void);
 int dlesm_sw_step_fused(const void *u, const void *v, const void *p, void *uold, void *vold,
                         void *pold, void *unew, void *vnew, void *pnew, double dx, double dy,
                         double tdt, double alpha, int first, int xstart, int xstop, int ystart,
