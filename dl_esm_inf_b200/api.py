@@ -26,6 +26,7 @@ HALO_WIDTH_X = HALO_WIDTH_Y = 1                                          # grid_
 NONE, Iplus, Iminus, Jplus, Jminus, IplusJplus, IminusJminus, IplusJminus, IminusJplus = range(9)
 MaxComm = 16
 EXT_PERIODIC_DISTMEM = 1
+EXT_HALO_DEPTH = 2
 
 GRID_ARRAYS = ("tmask", "dx_t", "dy_t", "dx_u", "dy_u", "dx_v", "dy_v", "dx_f", "dy_f", "area_t",
                "area_u", "area_v", "gphiu", "gphiv", "gphif", "xt", "yt")

@@ -1580,13 +1580,26 @@ extern "C" int dlesm_field_get_data(dlesm_field_t *f, double *host)
 extern "C" int dlesm_fields_halo_exchange(dlesm_field_t *const *f, int nfields, int depth)
 {
     clear_error();
-    (void)depth;  // "currently ignored and hardwired to 1" -- src/field_mod.f90:1226-1229
     if (nfields < 1 || nfields > k::kMaxExchangeFields) {
         set_error(DLESM_ERR_ARGS, "halo_exchange: between 1 and 8 fields per call");
         return DLESM_ERR_ARGS;
     }
     void *ptrs[k::kMaxExchangeFields];
     for (int q = 0; q < nfields; ++q) ptrs[q] = f[q]->dptr;
+    // The reference ignores `depth` ("currently ignored and hardwired to 1",
+    // src/field_mod.f90:1226-1229; MAX_HALO_DEPTH = 1, src/parallel_comms_mod.f90:48).  With the
+    // DLESM_EXT_HALO_DEPTH extension a deeper exchange is served from tables built for that
+    // depth, up to the halo width the grid was decomposed with.
+    dlesm_grid *g = f[0]->grid;
+    if (depth > 1 && (pstate().extensions & DLESM_EXT_HALO_DEPTH) && g->have_comms) {
+        dlesm_comms deep;
+        int rc = build_comms(g->decomp, pstate().rank, pstate().nranks, g->pbc_x, g->pbc_y, depth, depth, deep);
+        if (rc != DLESM_OK) return rc;
+        rc = dlesm_dev_set_comms(&deep);
+        if (rc == DLESM_OK) rc = dlesm_dev_halo_exchange(ptrs, nfields);
+        const int rc2 = dlesm_dev_set_comms(&g->comms);   // module-level state back to depth 1
+        return rc != DLESM_OK ? rc : rc2;
+    }
     return dlesm_dev_halo_exchange(ptrs, nfields);
 }
 extern "C" int dlesm_field_halo_exchange(dlesm_field_t *f, int depth)

@@ -144,6 +144,10 @@ void dlesm_reset_saved_state(void);
  * more than one rank (wrap-around neighbours); default 0 = refuse as the reference. */
 int dlesm_set_extensions(int flags);
 #define DLESM_EXT_PERIODIC_DISTMEM 1
+/* bit 1: honour halo_exchange(depth) for depth > 1, up to the halo_width the grid was
+ * decomposed with (the reference hard-wires depth 1: MAX_HALO_DEPTH, src/parallel_comms_mod.f90:48,
+ * src/field_mod.f90:1226-1229). */
+#define DLESM_EXT_HALO_DEPTH 2
 
 /* ------------------------------------------------------------------------------------ */
 /* HOST MIRROR: decomposition -- src/parallel_mod.f90:70-332, decomposition_mod.f90      */

@@ -162,6 +162,42 @@ def case(nx, ny, offset, bcs, periodic, alignment):
     fd.set_extensions(0)
 
 
+def case_depth(nx, ny, depth):
+    """extension: tables for halo_exchange(depth) on a grid decomposed with halo_width = depth.
+    Known answer: every halo cell within `depth` that lies inside the global domain ends up
+    holding the global field's value at its position (edges and corners)."""
+    os.environ.pop("DL_ESM_ALIGNMENT", None)
+    g = fd.grid_type(fd.GO_ARAKAWA_C, BCS_EXT, fd.GO_OFFSET_NE)
+    g.decompose(nx, ny, halo_width=depth)
+    fd.grid_init(g, 1.0, 1.0)
+    c = fd.map_comms(g.decomp, halo_depths=(depth, depth))
+    plan = comm_plan(c)
+    tables_pair_up(c)
+    G = np.asfortranarray(np.random.default_rng(77 + nx + ny).uniform(-1, 1, size=(nx, ny)))
+    sub = g.subdomain
+    li = sub.internal
+    ok(li.xstart == depth + 1, "halo_width shifts the internal region")
+    a = np.full((g.nx, g.ny), -7.0, order="F")
+    gi = sub.glob.xstart + np.arange(li.nx) - 1
+    gj = sub.glob.ystart + np.arange(li.ny) - 1
+    a[li.xstart - 1:li.xstop, li.ystart - 1:li.ystop] = G[np.ix_(gi, gj)]
+    want = a.copy(order="F")
+    gloo_exchange(a, c, plan)
+    for ji in range(li.xstart - depth, li.xstop + depth + 1):
+        for jj in range(li.ystart - depth, li.ystop + depth + 1):
+            gx, gy = sub.glob.xstart + ji - li.xstart, sub.glob.ystart + jj - li.ystart
+            if 1 <= gx <= nx and 1 <= gy <= ny:
+                want[ji - 1, jj - 1] = G[gx - 1, gy - 1]
+    ok(np.array_equal(a, want), "depth-%d exchange (%dx%d) does not reproduce the global field" % (depth, nx, ny))
+    # deeper than the decomposition's halo width is refused (reference: ierr from map_comms)
+    try:
+        fd.map_comms(g.decomp, halo_depths=(depth + 1, depth + 1))
+        ok(False, "depth beyond the halo width must be refused")
+    except fd.GoceanStop:
+        ok(True, "")
+    fd.gocean_initialise(RANK + 1, WORLD)            # go_decompose's SAVEd halo width back to 1
+
+
 def main():
     dist.init_process_group("gloo")
     fd.gocean_initialise(RANK + 1, WORLD)            # host only: no device, no NCCL
@@ -178,6 +214,9 @@ def main():
     case(10, 10, fd.GO_OFFSET_NE, BCS_EXT, False, 8)
     for shape in ((16, 16), (33, 47), (64, 96)):
         case(*shape, fd.GO_OFFSET_SW, BCS_PER, True, 2)
+    for shape in ((10, 10), (37, 23), (64, 48)):
+        case_depth(*shape, 2)
+    case_depth(40, 36, 3)
     dist.barrier()
     if RANK == 0:
         print("HOST DIST OK %d checks on %d ranks" % (NCHECK, WORLD), flush=True)

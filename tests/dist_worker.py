@@ -190,6 +190,57 @@ def case_reduction(n=10):
     f.free()
 
 
+def case_halos_depth2(n_x, n_y, depth=2):
+    """Extension (BASELINE config 5 "width-2 halos"): grid decomposed with
+    halo_width = depth, halo_exchange(depth).  Known answer, independent of any table: after the
+    exchange every halo cell within `depth` of the internal region that lies inside the global
+    domain holds the hill value of its global position (corners included)."""
+    os.environ.pop("DL_ESM_ALIGNMENT", None)
+    fd.set_extensions(fd.EXT_HALO_DEPTH)
+    g = fd.grid_type(fd.GO_ARAKAWA_C, BCS_EXT, fd.GO_OFFSET_NE)
+    g.decompose(n_x, n_y, halo_width=depth)
+    sub = g.subdomain
+    tm = np.ones((sub.glob.nx, sub.glob.ny), dtype=np.int32, order="F")
+    fd.grid_init(g, 1.0, 1.0, tm)
+    li = sub.internal
+    ok(li.xstart == depth + 1 and li.ystart == depth + 1, "internal region starts after %d halo cells" % depth)
+    flds, srcs = [], []
+    for k, pts in enumerate(POINTS):
+        f = fd.r2d_field(g, pts)
+        a = np.full((g.nx, g.ny), -777.0 - RANK, order="F")
+        ii = np.arange(li.xstart, li.xstop + 1)
+        jj = np.arange(li.ystart, li.ystop + 1)
+        a[np.ix_(ii - 1, jj - 1)] = (10000.0 * (sub.glob.xstart + ii - li.xstart)[:, None]
+                                     + (sub.glob.ystart + jj - li.ystart)[None, :] + 0.25 * k)
+        f.set_data(a)
+        flds.append(f)
+        srcs.append(a)
+    flds[0].halo_exchange(depth)
+    fd.halo_exchange_fields(flds[1:], depth)
+    for k, (f, src) in enumerate(zip(flds, srcs)):
+        got = f.get_data()
+        want = src.copy(order="F")
+        for ji in range(li.xstart - depth, li.xstop + depth + 1):
+            for jj_ in range(li.ystart - depth, li.ystop + depth + 1):
+                gx, gy = sub.glob.xstart + ji - li.xstart, sub.glob.ystart + jj_ - li.ystart
+                if 1 <= gx <= n_x and 1 <= gy <= n_y:
+                    want[ji - 1, jj_ - 1] = 10000.0 * gx + gy + 0.25 * k
+        ok(np.array_equal(got, want), "depth-%d exchange %dx%d field %d differs at %s"
+           % (depth, n_x, n_y, k, np.argwhere(got != want)[:4].tolist()))
+        f.free()
+    # without the extension the depth argument is ignored, as in the reference
+    fd.set_extensions(0)
+    f = fd.r2d_field(g, fd.GO_T_POINTS)
+    f.set_data(srcs[2])
+    f.halo_exchange(depth)
+    got = f.get_data()
+    outer = got.copy()
+    outer[li.xstart - 2:li.xstop + 1, li.ystart - 2:li.ystop + 1] = srcs[2][li.xstart - 2:li.xstop + 1, li.ystart - 2:li.ystop + 1]
+    ok(np.array_equal(outer, srcs[2]), "depth is ignored without the extension: only the width-1 ring may change")
+    f.free()
+    fd.gocean_initialise(RANK + 1, WORLD)           # resets go_decompose's SAVEd halo width to 1
+
+
 def case_gather():
     """parallel_utils_mod gather (src/parallel/parallel_utils_mod.f90:242-255) over NCCL"""
     import ctypes as C
@@ -265,6 +316,8 @@ def main():
         case_shallow_water(130, 77, 4, 64, mode)
     case_shallow_water(1024, 1024, 3, 64, fd.SW_FUSED)
     case_gather()
+    for shape in ((10, 10), (37, 23), (64, 48)):
+        case_halos_depth2(*shape)
     for shape in ((64, 96, 5, 2), (130, 77, 4, 64), (300, 523, 7, 64), (1024, 1024, 6, 64)):
         case_shallow_water(*shape, fd.SW_FUSED, halo_mode=fd.HALO_PUSH)
     dist.barrier()
