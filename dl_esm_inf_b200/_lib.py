@@ -68,6 +68,11 @@ class FieldInfo(C.Structure):
                 ("ntiles", C.c_int), ("data_on_device", C.c_int), ("device_ptr", C.c_void_p)]
 
 
+class GoArg(C.Structure):
+    """dlesm_go_arg: go_arg of src/argument_mod.f90:57-61 plus the element family"""
+    _fields_ = [("arg_intent", C.c_int), ("kind", C.c_int), ("element", C.c_int), ("stencil", C.c_int * 3)]
+
+
 # every symbol include/dlesm_b200.h declares; tests/test_abi.py checks header == this == .so
 _V = C.c_void_p
 _I = C.c_int
@@ -111,6 +116,7 @@ SIGNATURES = {
     "dlesm_grid_free": (None, [_V]),
     "dlesm_r2d_field_create": (_V, [_V, _I, _I, _PD, _I, _I]),
     "dlesm_field_get_info": (_I, [_V, C.POINTER(FieldInfo)]),
+    "dlesm_field_grid": (_V, [_V]),
     "dlesm_grid_field_bounds": (_I, [_V, _I, C.POINTER(FieldInfo)]),
     "dlesm_field_set_data": (_I, [_V, _PD]),
     "dlesm_field_get_data": (_I, [_V, _PD]),
@@ -167,6 +173,11 @@ SIGNATURES = {
     "dlesm_profile_enable": (_I, [_I]),
     "dlesm_profile_read": (_I, [_PD, C.POINTER(C.c_longlong), _I]),
     "dlesm_sw_free": (None, [_V]),
+    "dlesm_kernel_create": (_V, [C.c_char_p, C.c_char_p, C.POINTER(GoArg), _I, _I, _I]),
+    "dlesm_kernel_generated_source": (C.c_char_p, [_V]),
+    "dlesm_kernel_launch": (_I, [_V, C.POINTER(_V), _I, _PD, _I, _PI, _I]),
+    "dlesm_kernel_launch_dev": (_I, [_V, C.POINTER(_V), _I, _PD, _I, _PI, _I, _I, _I, _I, _I]),
+    "dlesm_kernel_free": (None, [_V]),
 }
 
 _lib = None

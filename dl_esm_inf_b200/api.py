@@ -468,3 +468,80 @@ class shallow_water:
             self.free()
         except Exception:
             pass
+
+
+# --- kernel_mod / argument_mod: metadata-driven kernel dispatch (the PSy layer) ---------------
+GO_READ, GO_WRITE, GO_READWRITE, GO_INC, GO_MIN, GO_MAX, GO_SUM = range(7)   # argument_mod.f90:39-46
+GO_R_SCALAR, GO_I_SCALAR = 0, 1                                               # :68
+GO_EVERY = 1
+GO_CU, GO_CV, GO_CT, GO_CF = 1, 2, 3, 4                                       # :71
+(GO_TIME_STEP, GO_GRID_AREA_T, GO_GRID_AREA_U, GO_GRID_AREA_V, GO_GRID_MASK_T, GO_GRID_DX_T,
+ GO_GRID_DX_U, GO_GRID_DX_V, GO_GRID_DY_T, GO_GRID_DY_U, GO_GRID_DY_V, GO_GRID_LAT_U, GO_GRID_LAT_V,
+ GO_GRID_DX_CONST, GO_GRID_DY_CONST, GO_GRID_X_MIN_INDEX, GO_GRID_X_MAX_INDEX, GO_GRID_Y_MIN_INDEX,
+ GO_GRID_Y_MAX_INDEX) = range(1, 20)                                          # :75-112
+GO_INTERNAL_PTS, GO_EXTERNAL_PTS, GO_ALL_PTS = 0, 1, 2                        # kernel_mod.f90:35-37
+GO_POINTWISE = (0, 10, 0)                                                     # go_stencil(000,010,000)
+ARG_FIELD, ARG_SCALAR, ARG_GRID = 0, 1, 2
+
+
+def go_arg(arg_intent, element, stencil=GO_POINTWISE, kind=None):
+    """go_arg(intent, element[, stencil]) -- src/argument_mod.f90:57-61.  `kind` says which family
+    the element belongs to (the Fortran names carry it; their integer values overlap); use
+    field_arg / scalar_arg / grid_arg to have it filled in."""
+    a = _lib.GoArg()
+    a.arg_intent, a.element = arg_intent, element
+    a.kind = ARG_FIELD if kind is None else kind
+    a.stencil[:] = list(stencil)
+    return a
+
+
+def field_arg(arg_intent, point_type, stencil=GO_POINTWISE):
+    return go_arg(arg_intent, point_type, stencil, ARG_FIELD)
+
+
+def scalar_arg(element, arg_intent=GO_READ):
+    return go_arg(arg_intent, element, GO_POINTWISE, ARG_SCALAR)
+
+
+def grid_arg(prop):
+    return go_arg(GO_READ, prop, GO_POINTWISE, ARG_GRID)
+
+
+class kernel_type:
+    """`type, extends(kernel_type)` of src/kernel_mod.f90:46-50 / src/infrastructure_mod.f90:13-26:
+    meta_args, ITERATES_OVER, index_offset and the per-point code -- here a CUDA C++ device
+    function `<name>_code(int ji, int jj, ...)` -- compiled into an sm_100a sweep by the library."""
+
+    def __init__(self, name, code, meta_args, iterates_over=GO_INTERNAL_PTS, index_offset=GO_OFFSET_ANY):
+        arr = (_lib.GoArg * len(meta_args))(*meta_args)
+        self.name = name
+        self._h = _chk_ptr(_lib.lib().dlesm_kernel_create(name.encode(), code.encode(), arr, len(meta_args),
+                                                          iterates_over, index_offset))
+
+    @property
+    def generated_source(self):
+        return _lib.lib().dlesm_kernel_generated_source(self._h).decode()
+
+    def __call__(self, fields, rscalars=(), iscalars=()):
+        """invoke(kernel(args...)): fields / real scalars / integer scalars in metadata order"""
+        fa = (C.c_void_p * max(1, len(fields)))(*[f._h for f in fields])
+        ra = (C.c_double * max(1, len(rscalars)))(*rscalars)
+        ia = (C.c_int * max(1, len(iscalars)))(*iscalars)
+        _chk(_lib.lib().dlesm_kernel_launch(self._h, fa, len(fields), ra, len(rscalars), ia, len(iscalars)))
+
+    def launch_dev(self, arrays, reals, ints, bounds):
+        aa = (C.c_void_p * max(1, len(arrays)))(*arrays)
+        ra = (C.c_double * max(1, len(reals)))(*reals)
+        ia = (C.c_int * max(1, len(ints)))(*ints)
+        _chk(_lib.lib().dlesm_kernel_launch_dev(self._h, aa, len(arrays), ra, len(reals), ia, len(ints), *bounds))
+
+    def free(self):
+        if getattr(self, "_h", None):
+            _lib.lib().dlesm_kernel_free(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass

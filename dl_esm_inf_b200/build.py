@@ -15,8 +15,8 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libdlesm_b200.so")
-SOURCES = ["dlesm_host.cpp", "dlesm_kernels.cu", "dlesm_fused.cu", "dlesm_runtime.cu"]
-HEADERS = ["dlesm_host.hpp", "dlesm_kernels.cuh", os.path.join("..", "..", "include", "dlesm_b200.h")]
+SOURCES = ["dlesm_host.cpp", "dlesm_kernels.cu", "dlesm_fused.cu", "dlesm_runtime.cu", "dlesm_psy.cu"]
+HEADERS = ["dlesm_host.hpp", "dlesm_kernels.cuh", "dlesm_internal.hpp", os.path.join("..", "..", "include", "dlesm_b200.h")]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
@@ -44,7 +44,7 @@ def needs_build() -> bool:
 def build(force: bool = False, verbose: bool = False) -> str:
     if not force and not needs_build():
         return LIB
-    cmd = [_nvcc()] + NVCC_FLAGS + ["-o", LIB] + [os.path.join(CSRC, s) for s in SOURCES] + ["-lnccl"]
+    cmd = [_nvcc()] + NVCC_FLAGS + ["-o", LIB] + [os.path.join(CSRC, s) for s in SOURCES] + ["-lnccl", "-ldl"]
     if verbose:
         cmd.insert(1, "-Xptxas")
         cmd.insert(2, "-v")

@@ -17,6 +17,7 @@
 
 #include "../../include/dlesm_b200.h"
 #include "dlesm_host.hpp"
+#include "dlesm_internal.hpp"
 #include "dlesm_kernels.cuh"
 
 using namespace dlesm;
@@ -155,6 +156,20 @@ int ensure_xbuf(size_t n)
 k::Box box_of(const dlesm_region &r) { return k::Box{r.xstart, r.xstop, r.ystart, r.ystop}; }
 
 }  // namespace
+
+namespace dlesm {
+int internal_ensure_device() { return ensure_device(); }
+cudaStream_t internal_stream() { return ctx().stream; }
+int internal_pitch_of(const void *device_ptr, int &pitch, int &ny)
+{
+    FieldRec r;
+    int rc = lookup(device_ptr, r);
+    if (rc != DLESM_OK) return rc;
+    pitch = r.nx;
+    ny = r.ny;
+    return DLESM_OK;
+}
+}  // namespace dlesm
 
 // =========================================================================================
 // errors, lifecycle
@@ -1517,6 +1532,7 @@ extern "C" dlesm_field_t *dlesm_r2d_field_create(dlesm_grid_t *g, int grid_point
     return f;
 }
 
+extern "C" dlesm_grid_t *dlesm_field_grid(const dlesm_field_t *f) { return f ? f->grid : nullptr; }
 extern "C" int dlesm_field_get_info(const dlesm_field_t *f, dlesm_field_info *out)
 {
     out->defined_on = f->fb.defined_on;

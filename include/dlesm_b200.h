@@ -282,6 +282,8 @@ typedef struct {
 dlesm_field_t *dlesm_r2d_field_create(dlesm_grid_t *g, int grid_points, int do_tile,
                                       const double *init_global_data, int gnx, int gny);
 int dlesm_field_get_info(const dlesm_field_t *f, dlesm_field_info *out);
+/* fld%grid (src/field_mod.f90:114) */
+dlesm_grid_t *dlesm_field_grid(const dlesm_field_t *f);
 /* set_field_bounds only (src/field_mod.f90:563-624): the regions and halo list a field of
  * this point type would get; no storage is allocated, so it works without a GPU
  * (device_ptr = NULL, data_on_device = 0 in the result). */
@@ -464,6 +466,83 @@ long long dlesm_kernel_launch_count(void);
 int dlesm_profile_enable(int on);
 int dlesm_profile_read(double *ms_total, long long *nlaunches, int reset);
 void dlesm_sw_free(dlesm_sw_t *s);
+
+/* ------------------------------------------------------------------------------------ */
+/* PSy LAYER: metadata-driven kernel dispatch -- kernel_mod / argument_mod                */
+/* (src/kernel_mod.f90:30-50, src/argument_mod.f90:39-112, the calling convention of      */
+/* src/infrastructure_mod.f90:13-41: `type, extends(kernel_type)` with meta_args,          */
+/* ITERATES_OVER, index_offset and a per-point `code(ji, jj, args...)`).                   */
+/*                                                                                      */
+/* The application supplies its per-point kernel as a CUDA C++ device function with the   */
+/* reference's calling convention,                                                       */
+/*     __device__ void <name>_code(int ji, int jj, <one parameter per meta_arg>)           */
+/* and the same metadata it would write in Fortran.  The library generates the sweep      */
+/* (the `do jj / do ji` nest of SURVEY CS-3 as a coalesced 2-D grid), compiles it for      */
+/* sm_100a with NVRTC (-fmad=false, like the rest of the library) and launches it over    */
+/* device-resident fields; grid-property arguments are resolved from the grid.             */
+/* Parameter types, by meta_arg:                                                         */
+/*   field, GO_READ                 -> dlesm_cfield  (a(ji,jj), 1-based, read-only)        */
+/*   field, GO_WRITE/READWRITE/INC  -> dlesm_field   (a(ji,jj) is an lvalue)               */
+/*   GO_R_SCALAR / GO_I_SCALAR      -> double / int                                       */
+/*   GO_GRID_MASK_T                 -> dlesm_imask   (int tmask(ji,jj))                    */
+/*   other GO_GRID_* arrays         -> dlesm_cfield                                       */
+/*   GO_GRID_DX_CONST / DY_CONST    -> double;  GO_GRID_{X,Y}_{MIN,MAX}_INDEX -> int       */
+/* ------------------------------------------------------------------------------------ */
+/* src/argument_mod.f90:39-46 */
+enum { DLESM_GO_READ = 0, DLESM_GO_WRITE, DLESM_GO_READWRITE, DLESM_GO_INC, DLESM_GO_MIN, DLESM_GO_MAX,
+       DLESM_GO_SUM };
+/* :68-71 */
+#define DLESM_GO_R_SCALAR 0
+#define DLESM_GO_I_SCALAR 1
+#define DLESM_GO_EVERY 1
+#define DLESM_GO_CU 1
+#define DLESM_GO_CV 2
+#define DLESM_GO_CT 3
+#define DLESM_GO_CF 4
+/* :75-112 */
+enum { DLESM_GO_TIME_STEP = 1, DLESM_GO_GRID_AREA_T, DLESM_GO_GRID_AREA_U, DLESM_GO_GRID_AREA_V,
+       DLESM_GO_GRID_MASK_T, DLESM_GO_GRID_DX_T, DLESM_GO_GRID_DX_U, DLESM_GO_GRID_DX_V,
+       DLESM_GO_GRID_DY_T, DLESM_GO_GRID_DY_U, DLESM_GO_GRID_DY_V, DLESM_GO_GRID_LAT_U,
+       DLESM_GO_GRID_LAT_V, DLESM_GO_GRID_DX_CONST, DLESM_GO_GRID_DY_CONST,
+       DLESM_GO_GRID_X_MIN_INDEX, DLESM_GO_GRID_X_MAX_INDEX, DLESM_GO_GRID_Y_MIN_INDEX,
+       DLESM_GO_GRID_Y_MAX_INDEX };
+/* src/kernel_mod.f90:35-37 */
+#define DLESM_GO_INTERNAL_PTS 0
+#define DLESM_GO_EXTERNAL_PTS 1
+#define DLESM_GO_ALL_PTS 2
+/* go_arg (src/argument_mod.f90:57-61).  In Fortran the element names carry their meaning; the
+ * integer values overlap (GO_CU == GO_TIME_STEP == GO_I_SCALAR == 1), so `kind` says which
+ * family `element` belongs to. */
+#define DLESM_ARG_FIELD 0  /* element = GO_CU / GO_CV / GO_CT / GO_CF / GO_EVERY */
+#define DLESM_ARG_SCALAR 1 /* element = GO_R_SCALAR / GO_I_SCALAR                 */
+#define DLESM_ARG_GRID 2   /* element = GO_GRID_*                                  */
+typedef struct {
+    int arg_intent; /* DLESM_GO_READ ...                                         */
+    int kind;       /* DLESM_ARG_*                                               */
+    int element;
+    int stencil[3]; /* go_stencil rows, e.g. {000, 010, 000} = GO_POINTWISE (informational) */
+} dlesm_go_arg;
+
+typedef struct dlesm_kernel dlesm_kernel_t;
+/* Build a kernel object.  Host only (NVRTC needs no GPU): compiles at once and reports
+ * compile errors through dlesm_last_error().  iterates_over = DLESM_GO_INTERNAL_PTS or
+ * DLESM_GO_ALL_PTS (GO_EXTERNAL_PTS is not supported, as in PSyclone); index_offset is checked
+ * against the grid at launch (DLESM_GO_OFFSET_ANY matches every grid). */
+dlesm_kernel_t *dlesm_kernel_create(const char *name, const char *cuda_source, const dlesm_go_arg *meta_args,
+                                    int nargs, int iterates_over, int index_offset);
+/* the generated translation unit (prelude + the application's source + the sweep), for inspection */
+const char *dlesm_kernel_generated_source(const dlesm_kernel_t *k);
+/* Sweep the kernel.  fields / rscalars / iscalars are consumed in metadata order (grid-property
+ * arguments take nothing from them).  The sweep covers the `internal` (GO_INTERNAL_PTS) or `whole`
+ * (GO_ALL_PTS) region of the first field argument that is written (GO_WRITE / READWRITE / INC). */
+int dlesm_kernel_launch(dlesm_kernel_t *k, dlesm_field_t *const *fields, int nfields, const double *rscalars,
+                        int nrscalars, const int *iscalars, int niscalars);
+/* Device-layer form for a Fortran PSy layer: arrays = device pointers of the field AND grid-array
+ * arguments in metadata order (fld%device_ptr, grid%tmask_device, ...); reals = GO_R_SCALARs and real
+ * grid scalars in order; ints = GO_I_SCALARs and index properties in order; explicit sweep bounds. */
+int dlesm_kernel_launch_dev(dlesm_kernel_t *k, void *const *arrays, int narrays, const double *reals, int nreals,
+                            const int *ints, int nints, int xstart, int xstop, int ystart, int ystop);
+void dlesm_kernel_free(dlesm_kernel_t *k);
 
 #ifdef __cplusplus
 }
