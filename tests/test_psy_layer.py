@@ -84,3 +84,141 @@ def test_metadata_is_validated():
         kernel_type("m", ok, [field_arg(GO_WRITE, GO_CT)], iterates_over=1)
     with pytest.raises(fd.GoceanStop):
         kernel_type("not an identifier", ok, [field_arg(GO_WRITE, GO_CT)])
+
+
+# ---------------------------------------------------------------------------------------------
+# GPU: the kernels against the numpy oracle
+# ---------------------------------------------------------------------------------------------
+GRID_NAMES = {"e1t": "dx_t", "e1u": "dx_u", "e1v": "dx_v", "e2t": "dy_t", "e2u": "dy_u", "e2v": "dy_v",
+              "e12t": "area_t", "e12u": "area_u", "e12v": "area_v", "gphiu": "gphiu", "gphiv": "gphiv"}
+
+
+class OracleModel:
+    """the same invoke as examples.nemolite2d.NemoLite2D.step, on host arrays"""
+
+    def __init__(self, grid, arrays, rdt, cbfr, visc):
+        self.a = {k: v.copy(order="F") for k, v in arrays.items()}
+        self.g = {k: grid.host_array(v) for k, v in GRID_NAMES.items()}
+        self.tmask = grid.get_tmask()
+        self.rdt, self.cbfr, self.visc = rdt, cbfr, visc
+        self.box = {}
+        for pts, nm in ((fd.GO_T_POINTS, "t"), (fd.GO_U_POINTS, "u"), (fd.GO_V_POINTS, "v")):
+            fb = grid.field_bounds(pts)
+            self.box[nm] = NO.Box(*fb.internal.box())
+            self.box[nm + "_all"] = NO.Box(*fb.whole.box())
+
+    def step(self, istep):
+        a, g, b, tm = self.a, self.g, self.box, self.tmask
+        phys = (self.rdt, self.cbfr, self.visc, N.OMEGA, N.D2R, N.G)
+        NO.continuity(b["t"], a["ssha"], a["sshn"], a["sshn_u"], a["sshn_v"], a["hu"], a["hv"], a["un"], a["vn"],
+                      self.rdt, g["e12t"])
+        NO.momentum_u(b["u"], a["ua"], a["un"], a["vn"], a["hu"], a["hv"], a["ht"], a["ssha_u"], a["sshn"],
+                      a["sshn_u"], a["sshn_v"], *phys, tm, g["e1u"], g["e1v"], g["e1t"], g["e2u"], g["e2t"],
+                      g["e12u"], g["gphiu"])
+        NO.momentum_v(b["v"], a["va"], a["un"], a["vn"], a["hu"], a["hv"], a["ht"], a["ssha_v"], a["sshn"],
+                      a["sshn_u"], a["sshn_v"], *phys, tm, g["e1v"], g["e1t"], g["e2u"], g["e2v"], g["e2t"],
+                      g["e12v"], g["gphiv"])
+        NO.bc_ssh(b["t"], istep, a["ssha"], self.rdt, tm)
+        NO.bc_solid_u(b["u"], a["ua"], tm)
+        NO.bc_solid_v(b["v"], a["va"], tm)
+        NO.field_copy(b["u_all"], a["un"], a["ua"])
+        NO.field_copy(b["v_all"], a["vn"], a["va"])
+        NO.field_copy(b["t_all"], a["sshn"], a["ssha"])
+        NO.next_sshu(b["u"], a["sshn_u"], a["sshn"], tm, g["e12t"], g["e12u"])
+        NO.next_sshv(b["v"], a["sshn_v"], a["sshn"], tm, g["e12t"], g["e12v"])
+
+
+def make_model(n_x, n_y, alignment, monkeypatch, dx=1000.0, dy=1200.0):
+    if alignment:
+        monkeypatch.setenv("DL_ESM_ALIGNMENT", str(alignment))
+    else:
+        monkeypatch.delenv("DL_ESM_ALIGNMENT", raising=False)
+    fd.gocean_initialise(1, 1, device=0)
+    g = fd.grid_type(fd.GO_ARAKAWA_C, BCS_EXT, fd.GO_OFFSET_NE)
+    g.decompose(n_x, n_y)
+    tm, state = N.global_setup(n_x, n_y)
+    ltm, local = N.localise(g, tm, state)
+    fd.grid_init(g, dx, dy, ltm)
+    model = N.NemoLite2D(g)
+    model.set_state(local)
+    return g, model, OracleModel(g, local, model.rdt, model.cbfr, model.visc)
+
+
+EXACT = ("sshn_u", "sshn_v", "hu", "hv", "ht", "ssha_u", "ssha_v")
+
+
+def compare(model, om, step, exact_all=False):
+    for nm in model.f:
+        got, want = model.f[nm].get_data(), om.a[nm]
+        if exact_all:
+            assert np.array_equal(got, want), (nm, step, np.argwhere(got != want)[:3].tolist())
+        else:
+            # sin() in momentum_{u,v} and bc_ssh: device libm vs host libm (last-bit differences)
+            err = np.abs(got - want)
+            assert np.all(err <= RTOL * np.maximum(np.abs(want), 1e-3)), (nm, step, float(err.max()))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n_x,n_y,alignment", [(20, 16, None), (67, 45, 64), (130, 77, 8), (256, 192, 64)])
+def test_nemolite2d_steps_match_oracle(n_x, n_y, alignment, monkeypatch):
+    g, model, om = make_model(n_x, n_y, alignment, monkeypatch)
+    launches0 = fd.kernel_launch_count()
+    for step in range(1, 6):
+        model.step(step)
+        om.step(step)
+        compare(model, om, step)
+    assert fd.kernel_launch_count() - launches0 >= 5 * 11      # eleven kernels per invoke
+    # the fields evolved (the test is not comparing two copies of the initial state)
+    assert not np.array_equal(om.a["un"], N.localise(g, *N.global_setup(n_x, n_y))[1]["un"])
+    model.free()
+
+
+@pytest.mark.gpu
+def test_kernels_without_sin_are_bit_exact(monkeypatch):
+    """continuity, bc_solid, copy (GO_ALL_PTS), next_ssh{u,v}: one kernel at a time"""
+    g, model, om = make_model(67, 45, 64, monkeypatch)
+    f, k, a, b, gr, tm = model.f, model.k, om.a, om.box, om.g, om.tmask
+    k["continuity"]([f[n] for n in ("ssha", "sshn", "sshn_u", "sshn_v", "hu", "hv", "un", "vn")], (model.rdt,))
+    NO.continuity(b["t"], a["ssha"], a["sshn"], a["sshn_u"], a["sshn_v"], a["hu"], a["hv"], a["un"], a["vn"],
+                  model.rdt, gr["e12t"])
+    k["bc_solid_u"]([f["ua"]])
+    NO.bc_solid_u(b["u"], a["ua"], tm)
+    k["bc_solid_v"]([f["va"]])
+    NO.bc_solid_v(b["v"], a["va"], tm)
+    k["copy"]([f["sshn"], f["ssha"]])
+    NO.field_copy(b["t_all"], a["sshn"], a["ssha"])
+    k["next_sshu"]([f["sshn_u"], f["sshn"]])
+    NO.next_sshu(b["u"], a["sshn_u"], a["sshn"], tm, gr["e12t"], gr["e12u"])
+    k["next_sshv"]([f["sshn_v"], f["sshn"]])
+    NO.next_sshv(b["v"], a["sshn_v"], a["sshn"], tm, gr["e12t"], gr["e12v"])
+    compare(model, om, 0, exact_all=True)
+    assert (a["ua"] == 0.0).any() and not np.array_equal(a["ssha"], N.localise(g, *N.global_setup(67, 45))[1]["ssha"])
+    model.free()
+
+
+@pytest.mark.gpu
+def test_device_layer_launch_and_argument_checks(monkeypatch):
+    """dlesm_kernel_launch_dev (what a Fortran PSy layer calls with fld%device_ptr and
+    grid%*_device) gives the same result as the host-mirror launch; wrong argument counts and a
+    kernel written for another index_offset are refused"""
+    g, model, om = make_model(40, 30, 64, monkeypatch)
+    f, k = model.f, model.k
+    names = ("ssha", "sshn", "sshn_u", "sshn_v", "hu", "hv", "un", "vn")
+    k["continuity"]([f[n] for n in names], (model.rdt,))
+    want = f["ssha"].get_data().copy()
+    fd.set_field(f["ssha"], -1.0)
+    i = f["ssha"].internal
+    k["continuity"].launch_dev([f[n].device_ptr for n in names] + [g.device_array("area_t")], (model.rdt,), (),
+                               (i.xstart, i.xstop, i.ystart, i.ystop))
+    got = f["ssha"].get_data()
+    sl = (slice(i.xstart - 1, i.xstop), slice(i.ystart - 1, i.ystop))
+    assert np.array_equal(got[sl], want[sl])
+    with pytest.raises(fd.GoceanStop):
+        k["continuity"]([f[n] for n in names[:-1]], (model.rdt,))
+    with pytest.raises(fd.GoceanStop):
+        k["continuity"]([f[n] for n in names], ())
+    sw_only = kernel_type("swk", "__device__ void swk_code(int ji, int jj, dlesm_field o) { o(ji, jj) = 1.0; }",
+                          [field_arg(GO_WRITE, GO_CT)], GO_INTERNAL_PTS, fd.GO_OFFSET_SW)
+    with pytest.raises(fd.GoceanStop):
+        sw_only([f["ssha"]])
+    model.free()
