@@ -322,20 +322,31 @@ def global_setup(n_x, n_y, seed=7):
     return tm, state
 
 
-def localise(grid, tm, state):
-    """this rank's part of a global set-up: index (i, j) of the global arrays is global point
-    (i, j) with the boundary ring at 0 and n+1; local arrays are (grid.nx, grid.ny)"""
+def _local_index(grid):
     sub = grid.subdomain
     li = sub.internal
     ji = np.arange(li.xstart - 1, li.xstop + 2)
     jj = np.arange(li.ystart - 1, li.ystop + 2)
-    gi = sub.glob.xstart + (ji - li.xstart)
-    gj = sub.glob.ystart + (jj - li.ystart)
+    return ji, jj, sub.glob.xstart + (ji - li.xstart), sub.glob.ystart + (jj - li.ystart)
+
+
+def local_tmask(grid, tm):
+    """this rank's part of the global mask, shaped like the tmask argument of grid_init
+    (src/grid_mod.f90:330): call after grid%decompose, before grid_init.  Index (i, j) of the
+    global array is global point (i, j), the boundary ring sitting at 0 and n+1."""
+    sub = grid.subdomain
+    ji, jj, gi, gj = _local_index(grid)
+    ltm = np.zeros((sub.glob.nx, sub.glob.ny), dtype=np.int32, order="F")
+    ltm[np.ix_(ji - 1, jj - 1)] = tm[np.ix_(gi, gj)]
+    return ltm
+
+
+def local_state(grid, state):
+    """this rank's part of the global fields as (grid.nx, grid.ny) arrays: call after grid_init"""
+    ji, jj, gi, gj = _local_index(grid)
     out = {}
     for nm, a in state.items():
         loc = np.zeros((grid.nx, grid.ny), order="F")
         loc[np.ix_(ji - 1, jj - 1)] = a[np.ix_(gi, gj)]
         out[nm] = loc
-    ltm = np.zeros((sub.glob.nx, sub.glob.ny), dtype=np.int32, order="F")
-    ltm[np.ix_(ji - 1, jj - 1)] = tm[np.ix_(gi, gj)]
-    return ltm, out
+    return out

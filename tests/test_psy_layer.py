@@ -137,8 +137,8 @@ def make_model(n_x, n_y, alignment, monkeypatch, dx=1000.0, dy=1200.0):
     g = fd.grid_type(fd.GO_ARAKAWA_C, BCS_EXT, fd.GO_OFFSET_NE)
     g.decompose(n_x, n_y)
     tm, state = N.global_setup(n_x, n_y)
-    ltm, local = N.localise(g, tm, state)
-    fd.grid_init(g, dx, dy, ltm)
+    fd.grid_init(g, dx, dy, N.local_tmask(g, tm))
+    local = N.local_state(g, state)
     model = N.NemoLite2D(g)
     model.set_state(local)
     return g, model, OracleModel(g, local, model.rdt, model.cbfr, model.visc)
@@ -169,7 +169,7 @@ def test_nemolite2d_steps_match_oracle(n_x, n_y, alignment, monkeypatch):
         compare(model, om, step)
     assert fd.kernel_launch_count() - launches0 >= 5 * 11      # eleven kernels per invoke
     # the fields evolved (the test is not comparing two copies of the initial state)
-    assert not np.array_equal(om.a["un"], N.localise(g, *N.global_setup(n_x, n_y))[1]["un"])
+    assert not np.array_equal(om.a["un"], N.local_state(g, N.global_setup(n_x, n_y)[1])["un"])
     model.free()
 
 
@@ -192,7 +192,7 @@ def test_kernels_without_sin_are_bit_exact(monkeypatch):
     k["next_sshv"]([f["sshn_v"], f["sshn"]])
     NO.next_sshv(b["v"], a["sshn_v"], a["sshn"], tm, gr["e12t"], gr["e12v"])
     compare(model, om, 0, exact_all=True)
-    assert (a["ua"] == 0.0).any() and not np.array_equal(a["ssha"], N.localise(g, *N.global_setup(67, 45))[1]["ssha"])
+    assert (a["ua"] == 0.0).any() and not np.array_equal(a["ssha"], N.local_state(g, N.global_setup(67, 45)[1])["ssha"])
     model.free()
 
 
