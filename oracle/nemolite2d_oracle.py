@@ -151,3 +151,63 @@ def next_sshv(b, sshn_v, sshn, tmask, e12t, e12v):
 def field_copy(b, output, inp):
     """src/infrastructure_mod.f90:32-41 over GO_ALL_PTS"""
     b.s(output)[...] = b.s(inp)
+
+
+GRID_NAMES = {"e1t": "dx_t", "e1u": "dx_u", "e1v": "dx_v", "e2t": "dy_t", "e2u": "dy_u", "e2v": "dy_v",
+              "e12t": "area_t", "e12u": "area_u", "e12v": "area_v", "gphiu": "gphiu", "gphiv": "gphiv"}
+
+
+class Model:
+    """The benchmark's invoke (same kernel order as examples.nemolite2d.NemoLite2D.step, without
+    the halo exchanges: one serial domain) on host arrays.
+    arrays: name -> (nx, ny) array; metrics: e1t.. -> (nx, ny) array; boxes: 't','u','v' internal
+    regions and 't_all','u_all','v_all' whole regions as Box."""
+
+    def __init__(self, arrays, metrics, tmask, boxes, rdt, cbfr, visc, omega, d2r, g):
+        self.a = {k: np.array(v, order="F", copy=True) for k, v in arrays.items()}
+        self.g, self.tmask, self.box = metrics, tmask, boxes
+        self.rdt, self.phys = rdt, (rdt, cbfr, visc, omega, d2r, g)
+
+    @classmethod
+    def serial_global(cls, n_x, n_y, tm, state, dx, dy, rdt, cbfr, visc, omega, d2r, g):
+        """one serial NE / external-BC domain of n_x x n_y points (src/parallel_mod.f90:272-290 with
+        one tile, halo width 1; src/grid_mod.f90:368-385 with DL_ESM_ALIGNMENT=1): arrays are
+        (n_x + 3, n_y + 3), internal region 2:n+1, the caller's ring-included global arrays sit
+        at 1:n+2."""
+        nx, ny = n_x + 3, n_y + 3
+
+        def pad(a, dtype):
+            out = np.zeros((nx, ny), dtype=dtype, order="F")
+            out[:n_x + 2, :n_y + 2] = a
+            return out
+        arrays = {k: pad(v, np.float64) for k, v in state.items()}
+        tmask = pad(tm, np.int32)
+        tmask[n_x + 2, :] = tmask[n_x + 1, :]       # high-x / high-y fill of grid_init (:416-431)
+        tmask[:, n_y + 2] = tmask[:, n_y + 1]
+        const = {"e1t": dx, "e1u": dx, "e1v": dx, "e2t": dy, "e2u": dy, "e2v": dy, "e12t": dx * dy, "e12u": dx * dy,
+                 "e12v": dx * dy, "gphiu": 50.0, "gphiv": 50.0}      # src/grid_mod.f90:461-503
+        metrics = {k: np.full((nx, ny), v, order="F") for k, v in const.items()}
+        boxes = {}
+        for nm in ("t", "u", "v"):                  # NE offset, external BCs: src/field_mod.f90:755-1000
+            boxes[nm] = Box(2, n_x + 1, 2, n_y + 1)
+            boxes[nm + "_all"] = Box(1, n_x + 2, 1, n_y + 2)
+        return cls(arrays, metrics, tmask, boxes, rdt, cbfr, visc, omega, d2r, g)
+
+    def step(self, istep):
+        a, g, b, tm = self.a, self.g, self.box, self.tmask
+        continuity(b["t"], a["ssha"], a["sshn"], a["sshn_u"], a["sshn_v"], a["hu"], a["hv"], a["un"], a["vn"],
+                   self.rdt, g["e12t"])
+        momentum_u(b["u"], a["ua"], a["un"], a["vn"], a["hu"], a["hv"], a["ht"], a["ssha_u"], a["sshn"],
+                   a["sshn_u"], a["sshn_v"], *self.phys, tm, g["e1u"], g["e1v"], g["e1t"], g["e2u"], g["e2t"],
+                   g["e12u"], g["gphiu"])
+        momentum_v(b["v"], a["va"], a["un"], a["vn"], a["hu"], a["hv"], a["ht"], a["ssha_v"], a["sshn"],
+                   a["sshn_u"], a["sshn_v"], *self.phys, tm, g["e1v"], g["e1t"], g["e2u"], g["e2v"], g["e2t"],
+                   g["e12v"], g["gphiv"])
+        bc_ssh(b["t"], istep, a["ssha"], self.rdt, tm)
+        bc_solid_u(b["u"], a["ua"], tm)
+        bc_solid_v(b["v"], a["va"], tm)
+        field_copy(b["u_all"], a["un"], a["ua"])
+        field_copy(b["v_all"], a["vn"], a["va"])
+        field_copy(b["t_all"], a["sshn"], a["ssha"])
+        next_sshu(b["u"], a["sshn_u"], a["sshn"], tm, g["e12t"], g["e12u"])
+        next_sshv(b["v"], a["sshn_v"], a["sshn"], tm, g["e12t"], g["e12v"])

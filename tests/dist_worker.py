@@ -241,6 +241,41 @@ def case_halos_depth2(n_x, n_y, depth=2):
     fd.gocean_initialise(RANK + 1, WORLD)           # resets go_decompose's SAVEd halo width to 1
 
 
+def case_nemolite2d(n_x, n_y, nsteps, alignment):
+    """The reference's own distributed configuration (NE offset, external BCs, T-mask) driving the
+    NEMOLite2D-style application on the PSy layer: N tiles with halo_exchange between the kernels
+    == the serial oracle of the whole basin, on the gathered internal fields."""
+    from examples import nemolite2d as N
+    from oracle import nemolite2d_oracle as NO
+    if alignment:
+        os.environ["DL_ESM_ALIGNMENT"] = str(alignment)
+    else:
+        os.environ.pop("DL_ESM_ALIGNMENT", None)
+    dx, dy = 1000.0, 1200.0
+    tm, state = N.global_setup(n_x, n_y)
+    g = fd.grid_type(fd.GO_ARAKAWA_C, BCS_EXT, fd.GO_OFFSET_NE)
+    g.decompose(n_x, n_y)
+    fd.grid_init(g, dx, dy, N.local_tmask(g, tm))
+    model = N.NemoLite2D(g)
+    model.set_state(N.local_state(g, state))
+    om = NO.Model.serial_global(n_x, n_y, tm, state, dx, dy, model.rdt, model.cbfr, model.visc, N.OMEGA, N.D2R, N.G)
+    for step in range(1, nsteps + 1):
+        model.step(step)
+        om.step(step)
+    for name in ("ssha", "sshn", "sshn_u", "sshn_v", "un", "vn", "ua", "va"):
+        out = model.f[name].gather_inner_data()
+        if RANK == 0:
+            want = om.a[name][1:n_x + 1, 1:n_y + 1]
+            err = np.abs(out - want)
+            ok(bool(np.all(err <= 1e-12 * np.maximum(np.abs(want), 1e-3))),
+               "nemolite2d %dx%d field %s: max abs err %.3e (sin() differs in the last bit between libm and the "
+               "device; everything else is exact)" % (n_x, n_y, name, float(err.max())))
+            ok(not np.array_equal(want, state[name][1:n_x + 1, 1:n_y + 1]) or name in ("sshn_u",),
+               "field %s evolved" % name)
+    model.free()
+    os.environ.pop("DL_ESM_ALIGNMENT", None)
+
+
 def case_gather():
     """parallel_utils_mod gather (src/parallel/parallel_utils_mod.f90:242-255) over NCCL"""
     import ctypes as C
@@ -318,6 +353,9 @@ def main():
     case_gather()
     for shape in ((10, 10), (37, 23), (64, 48)):
         case_halos_depth2(*shape)
+    case_nemolite2d(40, 36, 5, None)
+    case_nemolite2d(130, 77, 4, 64)
+    case_nemolite2d(257, 300, 3, 8)
     for shape in ((64, 96, 5, 2), (130, 77, 4, 64), (300, 523, 7, 64), (1024, 1024, 6, 64)):
         case_shallow_water(*shape, fd.SW_FUSED, halo_mode=fd.HALO_PUSH)
     dist.barrier()

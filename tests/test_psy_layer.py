@@ -89,43 +89,15 @@ def test_metadata_is_validated():
 # ---------------------------------------------------------------------------------------------
 # GPU: the kernels against the numpy oracle
 # ---------------------------------------------------------------------------------------------
-GRID_NAMES = {"e1t": "dx_t", "e1u": "dx_u", "e1v": "dx_v", "e2t": "dy_t", "e2u": "dy_u", "e2v": "dy_v",
-              "e12t": "area_t", "e12u": "area_u", "e12v": "area_v", "gphiu": "gphiu", "gphiv": "gphiv"}
-
-
-class OracleModel:
-    """the same invoke as examples.nemolite2d.NemoLite2D.step, on host arrays"""
-
-    def __init__(self, grid, arrays, rdt, cbfr, visc):
-        self.a = {k: v.copy(order="F") for k, v in arrays.items()}
-        self.g = {k: grid.host_array(v) for k, v in GRID_NAMES.items()}
-        self.tmask = grid.get_tmask()
-        self.rdt, self.cbfr, self.visc = rdt, cbfr, visc
-        self.box = {}
-        for pts, nm in ((fd.GO_T_POINTS, "t"), (fd.GO_U_POINTS, "u"), (fd.GO_V_POINTS, "v")):
-            fb = grid.field_bounds(pts)
-            self.box[nm] = NO.Box(*fb.internal.box())
-            self.box[nm + "_all"] = NO.Box(*fb.whole.box())
-
-    def step(self, istep):
-        a, g, b, tm = self.a, self.g, self.box, self.tmask
-        phys = (self.rdt, self.cbfr, self.visc, N.OMEGA, N.D2R, N.G)
-        NO.continuity(b["t"], a["ssha"], a["sshn"], a["sshn_u"], a["sshn_v"], a["hu"], a["hv"], a["un"], a["vn"],
-                      self.rdt, g["e12t"])
-        NO.momentum_u(b["u"], a["ua"], a["un"], a["vn"], a["hu"], a["hv"], a["ht"], a["ssha_u"], a["sshn"],
-                      a["sshn_u"], a["sshn_v"], *phys, tm, g["e1u"], g["e1v"], g["e1t"], g["e2u"], g["e2t"],
-                      g["e12u"], g["gphiu"])
-        NO.momentum_v(b["v"], a["va"], a["un"], a["vn"], a["hu"], a["hv"], a["ht"], a["ssha_v"], a["sshn"],
-                      a["sshn_u"], a["sshn_v"], *phys, tm, g["e1v"], g["e1t"], g["e2u"], g["e2v"], g["e2t"],
-                      g["e12v"], g["gphiv"])
-        NO.bc_ssh(b["t"], istep, a["ssha"], self.rdt, tm)
-        NO.bc_solid_u(b["u"], a["ua"], tm)
-        NO.bc_solid_v(b["v"], a["va"], tm)
-        NO.field_copy(b["u_all"], a["un"], a["ua"])
-        NO.field_copy(b["v_all"], a["vn"], a["va"])
-        NO.field_copy(b["t_all"], a["sshn"], a["ssha"])
-        NO.next_sshu(b["u"], a["sshn_u"], a["sshn"], tm, g["e12t"], g["e12u"])
-        NO.next_sshv(b["v"], a["sshn_v"], a["sshn"], tm, g["e12t"], g["e12v"])
+def oracle_model(grid, arrays, model):
+    """the oracle's Model over this grid's own metric arrays, mask and field bounds"""
+    metrics = {k: grid.host_array(v) for k, v in NO.GRID_NAMES.items()}
+    boxes = {}
+    for pts, nm in ((fd.GO_T_POINTS, "t"), (fd.GO_U_POINTS, "u"), (fd.GO_V_POINTS, "v")):
+        fb = grid.field_bounds(pts)
+        boxes[nm] = NO.Box(*fb.internal.box())
+        boxes[nm + "_all"] = NO.Box(*fb.whole.box())
+    return NO.Model(arrays, metrics, grid.get_tmask(), boxes, model.rdt, model.cbfr, model.visc, N.OMEGA, N.D2R, N.G)
 
 
 def make_model(n_x, n_y, alignment, monkeypatch, dx=1000.0, dy=1200.0):
@@ -141,7 +113,7 @@ def make_model(n_x, n_y, alignment, monkeypatch, dx=1000.0, dy=1200.0):
     local = N.local_state(g, state)
     model = N.NemoLite2D(g)
     model.set_state(local)
-    return g, model, OracleModel(g, local, model.rdt, model.cbfr, model.visc)
+    return g, model, oracle_model(g, local, model)
 
 
 EXACT = ("sshn_u", "sshn_v", "hu", "hv", "ht", "ssha_u", "ssha_v")
