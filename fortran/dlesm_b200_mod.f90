@@ -252,6 +252,43 @@ module dlesm_b200_mod
      end function
   end interface
 
+  !> go_arg across the boundary (include/dlesm_b200.h `dlesm_go_arg`): src/argument_mod.f90:57-61
+  !! plus the element family (0 field, 1 scalar, 2 grid property), since the integer values of
+  !! GO_CU, GO_TIME_STEP and GO_I_SCALAR overlap.
+  type, bind(C) :: dlesm_go_arg
+     integer(c_int) :: arg_intent, kind, element
+     integer(c_int) :: stencil(3)
+  end type dlesm_go_arg
+
+  interface
+     ! ---- PSy layer: metadata-driven kernel dispatch (src/kernel_mod.f90, src/argument_mod.f90)
+     function dlesm_kernel_create(name, cuda_source, meta_args, nargs, iterates_over, index_offset) &
+          bind(C, name="dlesm_kernel_create") result(kern)
+       import :: c_ptr, c_char, c_int, dlesm_go_arg
+       character(kind=c_char), dimension(*), intent(in) :: name, cuda_source   ! NUL-terminated
+       type(dlesm_go_arg), dimension(*), intent(in) :: meta_args
+       integer(c_int), value :: nargs, iterates_over, index_offset
+       type(c_ptr) :: kern
+     end function
+     !> arrays = fld%device_ptr / grid%*_device of the field and grid-array arguments in metadata
+     !! order; reals / ints = scalar arguments and scalar grid properties in metadata order
+     function dlesm_kernel_launch_dev(kern, arrays, narrays, reals, nreals, ints, nints, &
+                                      xstart, xstop, ystart, ystop)                      &
+          bind(C, name="dlesm_kernel_launch_dev") result(ierr)
+       import :: c_ptr, c_int, c_double
+       type(c_ptr), value :: kern
+       type(c_ptr), dimension(*), intent(in) :: arrays
+       real(c_double), dimension(*), intent(in) :: reals
+       integer(c_int), dimension(*), intent(in) :: ints
+       integer(c_int), value :: narrays, nreals, nints, xstart, xstop, ystart, ystop
+       integer(c_int) :: ierr
+     end function
+     subroutine dlesm_kernel_free(kern) bind(C, name="dlesm_kernel_free")
+       import :: c_ptr
+       type(c_ptr), value :: kern
+     end subroutine
+  end interface
+
 contains
 
   !> Turn a non-zero status into the reference's only error path, gocean_stop
