@@ -29,22 +29,26 @@ void note_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
 // ---------------------------------------------------------------------------------------
 // copy_field (src/field_mod.f90:1152-1159): out(:,:) = in(:,:), padding included.
-// 16 B/point.  Grid-stride, 2 x 16-byte loads in flight per thread.
+// 16 B/point.  Every CTA copies one contiguous 16 KB chunk (4 x 16-byte loads in flight per
+// thread) and CTAs are laid out in memory order, so the CTAs resident at any moment sweep one
+// contiguous window of DRAM -- the same lockstep effect that lifted the fused sweep (DESIGN.md
+// section 4); the earlier grid-stride form (accesses ~10 MB apart) reached 0.95 of the measured
+// copy bandwidth, the generated PSy copy sweep with this layout 1.05.
 // ---------------------------------------------------------------------------------------
+constexpr int kCopyUnroll = 4;
 __global__ void __launch_bounds__(256) copy_kernel(const double2 *__restrict__ in,
                                                    double2 *__restrict__ out, size_t n2,
                                                    const double *__restrict__ in_tail,
                                                    double *__restrict__ out_tail, int tail)
 {
-    const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
-    size_t t = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
-    for (; t + stride < n2; t += 2 * stride) {
-        const double2 a = __ldcs(in + t);
-        const double2 b = __ldcs(in + t + stride);
-        __stcs(out + t, a);
-        __stcs(out + t + stride, b);
-    }
-    if (t < n2) __stcs(out + t, __ldcs(in + t));
+    const size_t base = static_cast<size_t>(blockIdx.x) * (256 * kCopyUnroll) + threadIdx.x;
+    double2 v[kCopyUnroll];
+#pragma unroll
+    for (int q = 0; q < kCopyUnroll; ++q)
+        if (base + q * 256 < n2) v[q] = __ldcs(in + base + q * 256);
+#pragma unroll
+    for (int q = 0; q < kCopyUnroll; ++q)
+        if (base + q * 256 < n2) __stcs(out + base + q * 256, v[q]);
     if (blockIdx.x == 0 && static_cast<int>(threadIdx.x) < tail) out_tail[threadIdx.x] = in_tail[threadIdx.x];
 }
 
@@ -53,11 +57,11 @@ cudaError_t copy_field(const double *in, double *out, size_t n, cudaStream_t s)
     if (n == 0) return cudaSuccess;
     const size_t n2 = n / 2;
     const int tail = static_cast<int>(n - 2 * n2);
-    const unsigned blocks = static_cast<unsigned>(
-        n2 / 512 + 1 < static_cast<size_t>(kSMs) * 16 ? n2 / 512 + 1 : static_cast<size_t>(kSMs) * 16);
-    copy_kernel<<<blocks, 256, 0, s>>>(reinterpret_cast<const double2 *>(in),
-                                       reinterpret_cast<double2 *>(out), n2, in + 2 * n2,
-                                       out + 2 * n2, tail);
+    const size_t per_cta = 256 * kCopyUnroll;
+    const unsigned blocks = static_cast<unsigned>((n2 + per_cta - 1) / per_cta);
+    copy_kernel<<<blocks ? blocks : 1, 256, 0, s>>>(reinterpret_cast<const double2 *>(in),
+                                                   reinterpret_cast<double2 *>(out), n2, in + 2 * n2,
+                                                   out + 2 * n2, tail);
     count_launch();
     return cudaGetLastError();
 }

@@ -112,6 +112,39 @@ def main():
         if world == 1:
             hbm("periodic_halo_fill", n, 16, timed(a.apply_periodic_halos, reps), 2 * i.nx + 2 * (i.ny + 2),
                 note="halo cells only: latency-bound", **l2)
+        # PSy layer: generated sweeps (NVRTC) -- the reference's copy kernel over GO_ALL_PTS and the
+        # NEMOLite2D continuity kernel (9 arrays read, 1 written: 80 B/pt) on this grid
+        from dl_esm_inf_b200.api import (GO_ALL_PTS, GO_CT, GO_CU, GO_CV, GO_EVERY, GO_GRID_AREA_T, GO_INTERNAL_PTS,
+                                         GO_R_SCALAR, GO_READ, GO_WRITE, field_arg, grid_arg, kernel_type, scalar_arg)
+        kc = kernel_type("field_copy", "__device__ void field_copy_code(int ji, int jj, dlesm_field o, dlesm_cfield i)"
+                         " { o(ji, jj) = i(ji, jj); }", [field_arg(GO_WRITE, GO_EVERY), field_arg(GO_READ, GO_EVERY)],
+                         GO_ALL_PTS)
+        w = a.whole
+        hbm("psy_field_copy", n, 16, timed(lambda: kc([b, a]), reps), w.nx * w.ny, how="generated sweep (NVRTC)", **l2)
+        kc.free()
+        if n <= 16384:
+            cont = """__device__ void cont_code(int ji, int jj, dlesm_field ssha, dlesm_cfield sshn, dlesm_cfield sshn_u,
+                dlesm_cfield sshn_v, dlesm_cfield hu, dlesm_cfield hv, dlesm_cfield un, dlesm_cfield vn, double rdt,
+                dlesm_cfield e12t) {
+                const double r1 = (sshn_u(ji, jj) + hu(ji, jj)) * un(ji, jj);
+                const double r2 = (sshn_u(ji - 1, jj) + hu(ji - 1, jj)) * un(ji - 1, jj);
+                const double r3 = (sshn_v(ji, jj) + hv(ji, jj)) * vn(ji, jj);
+                const double r4 = (sshn_v(ji, jj - 1) + hv(ji, jj - 1)) * vn(ji, jj - 1);
+                ssha(ji, jj) = sshn(ji, jj) + (r2 - r1 + r4 - r3) * rdt / e12t(ji, jj); }"""
+            kk = kernel_type("cont", cont, [field_arg(GO_WRITE, GO_CT), field_arg(GO_READ, GO_CT),
+                                            field_arg(GO_READ, GO_CU), field_arg(GO_READ, GO_CV),
+                                            field_arg(GO_READ, GO_CU), field_arg(GO_READ, GO_CV),
+                                            field_arg(GO_READ, GO_CU), field_arg(GO_READ, GO_CV),
+                                            scalar_arg(GO_R_SCALAR), grid_arg(GO_GRID_AREA_T)], GO_INTERNAL_PTS)
+            extra = [fd.r2d_field(g, fd.GO_T_POINTS) for _ in range(6)]
+            for q, f in enumerate(extra):
+                fd.set_field(f, 1.0 + 0.1 * q)
+            flds = [b, a] + extra
+            hbm("psy_continuity", n, 80, timed(lambda: kk(flds, (20.0,)), reps), i.nx * i.ny,
+                how="generated sweep (NVRTC): 9 arrays read (incl. area_t), 1 written", **l2)
+            kk.free()
+            for f in extra:
+                f.free()
         a.free()
         b.free()
         if n <= 16384:
