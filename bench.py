@@ -184,10 +184,14 @@ def run_ours(args):
             dist.barrier()
             torch.cuda.synchronize()
 
-    # weak scaling: args.size^2 points per GPU; the tile grid is go_decompose's own choice
+    # weak scaling: args.size^2 points per GPU; strong: args.size^2 points in total (configs[3]
+    # names both).  The tile grid is go_decompose's own choice either way.
     n = args.size
     probe = fd.go_decompose(n, n)                       # tile grid for `world` ranks on a square domain
-    gx, gy = n * probe.nx, n * probe.ny
+    if args.scaling == "strong":
+        gx, gy = n, n
+    else:
+        gx, gy = n * probe.nx, n * probe.ny
     bcs = (fd.GO_BC_PERIODIC, fd.GO_BC_PERIODIC, fd.GO_BC_NONE)
     grid = fd.grid_type(fd.GO_ARAKAWA_C, bcs, fd.GO_OFFSET_SW)
     grid.decompose(gx, gy)
@@ -259,6 +263,22 @@ def run_ours(args):
         except Exception:
             pass
 
+    # ---- halo traffic of one step against NVLink (north_star: "halo traffic also as a fraction of
+    # NVLink bandwidth"): the map_comms send/recv lists of this rank x the three new fields ----
+    halo_traffic = None
+    if world > 1:
+        cm = grid.comms
+        sent = sum(cm.nxsend[q] * cm.nysend[q] for q in range(cm.nsend)
+                   if cm.destination[q] != rank) * 8 * 3
+        recv = sum(cm.nxrecv[q] * cm.nyrecv[q] for q in range(cm.nrecv)
+                   if cm.source[q] != rank) * 8 * 3
+        step_s = elapsed_ms * 1e-3 / args.steps
+        halo_traffic = {"sent_bytes_per_rank_per_step": sent, "recv_bytes_per_rank_per_step": recv,
+                        "messages_per_rank_per_step": int(cm.nsend),
+                        "nvlink_peak_GBs_both_directions": 1800.0,
+                        "nvlink_frac_of_step": (sent + recv) / step_s / 1.8e12,
+                        "step_minus_sweep_us": (elapsed_ms - kms.value) / args.steps * 1e3}
+
     # ---- e2e: the same step driven with HOST buffers through the field hooks ----
     e2e = run_e2e(args, fd, L, sw, grid, total_points, dist, torch) if args.e2e_steps > 0 else None
     sampler.stop_flag = True
@@ -279,17 +299,18 @@ def run_ours(args):
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "scaling": args.scaling, "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": "shallow-water C-grid step %dx%d per GPU (global %dx%d, tiles %dx%d), "
                                    "double periodic, GO_OFFSET_SW, FP64, DL_ESM_ALIGNMENT=%d, mode=%s"
-                                   % (n, n, gx, gy, probe.nx, probe.ny, args.alignment, args.mode),
+                                   % (sub.internal.nx, sub.internal.ny, gx, gy, probe.nx, probe.ny,
+                                      args.alignment, args.mode),
                        "l2": "inputs larger than L2 (9 fields x %.2f GB per GPU)" % (grid.nx * grid.ny * 8 / 1e9),
                        "fused_variant": args.variant, "parallelism": "tile-per-GPU %dx%d" % (probe.nx, probe.ny),
                        "halo": ("push: the fused sweep stores the neighbours' halo cells over NVLink peer memory, "
                                 "flag hand-shake per step" if halo == "push" else
                                 ("periodic halo kernel" if world == 1 else "pack -> NCCL send/recv -> unpack"))},
             "clocks": clocks, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
-            "e2e": e2e, "checksums_p_u_v": list(cks),
+            "e2e": e2e, "halo_traffic": halo_traffic, "checksums_p_u_v": list(cks),
             "hbm_frac_of_measured_whole_step": (BYTES_PER_POINT * local_points * args.steps /
                                                 (elapsed_ms * 1e-3) / 1e9) / peak,
         }
@@ -392,6 +413,9 @@ def main():
     ap.add_argument("--halo", default="auto", choices=["auto", "push", "exchange"],
                     help="halo fill of the fused step: push (in-kernel peer stores) or exchange (NCCL); auto = push when N>1")
     ap.add_argument("--band-rows", type=int, default=0, help="row-band height of the pipelined host step (0 = default)")
+    ap.add_argument("--scaling", choices=["weak", "strong"], default="weak",
+                    help="weak: --size^2 points per GPU (default, the metric's configuration); "
+                         "strong: --size^2 points in total, split by go_decompose")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
