@@ -194,7 +194,11 @@ def run_ours(args):
         gx, gy = n * probe.nx, n * probe.ny
     bcs = (fd.GO_BC_PERIODIC, fd.GO_BC_PERIODIC, fd.GO_BC_NONE)
     grid = fd.grid_type(fd.GO_ARAKAWA_C, bcs, fd.GO_OFFSET_SW)
-    grid.decompose(gx, gy)
+    if args.two_step:
+        fd.set_extensions(fd.EXT_PERIODIC_DISTMEM | fd.EXT_HALO_DEPTH if world > 1 else 0)
+        grid.decompose(gx, gy, halo_width=2)      # the two-step sweep needs two halo cells
+    else:
+        grid.decompose(gx, gy)
     fd.grid_init(grid, 1.0e5, 1.0e5)
     sub = grid.subdomain
     local_points = sub.internal.nx * sub.internal.ny
@@ -202,10 +206,12 @@ def run_ours(args):
 
     sw = fd.shallow_water(grid, dt=90.0, alpha=0.001, mode=fd.SW_FUSED if args.mode == "fused" else fd.SW_UNFUSED)
     sw.set_variant(args.variant)
+    if args.two_step:
+        sw.set_two_step(True, args.variant2)
     sw.init_device()
     halo = args.halo
     if halo == "auto":
-        halo = "push" if (world > 1 and args.mode == "fused") else "exchange"
+        halo = "push" if (world > 1 and args.mode == "fused" and not args.two_step) else "exchange"
     if halo == "push":
         sw.set_halo_mode(fd.HALO_PUSH)              # collective: maps the neighbours' arrays (NVLink peer memory)
     mass0 = fd.field_checksum(sw.field("p"))
@@ -249,17 +255,20 @@ def run_ours(args):
     roofline = None
     if kn.value > 0:
         k_ms = kms.value / kn.value
-        achieved = BYTES_PER_POINT * local_points / (k_ms * 1e-3) / 1e9
+        steps_per_launch = args.steps / kn.value          # 2 with --two-step (temporal blocking)
+        achieved = BYTES_PER_POINT * local_points * steps_per_launch / (k_ms * 1e-3) / 1e9
         roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                     "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
                     "kernel": "fused shallow-water sweep (variant %d)" % args.variant,
                     "kernel_ms": k_ms, "kernel_share_of_step": kms.value / elapsed_ms,
-                    "algorithmic_bytes_per_launch": BYTES_PER_POINT * local_points,
+                    "algorithmic_bytes_per_launch": BYTES_PER_POINT * local_points * steps_per_launch,
+                    "steps_per_launch": steps_per_launch,
                     "frac_of_nominal_8TBs": achieved / 8000.0}
         prof = os.path.join(ROOT, "profiles", "fused_traffic.json")
         try:
             with open(prof) as fh:
-                roofline["traffic"] = json.load(fh).get("dram_bytes_per_launch")
+                roofline["traffic"] = json.load(fh).get(
+                    "dram_bytes_per_launch_two_step" if args.two_step else "dram_bytes_per_launch")
         except Exception:
             pass
 
@@ -305,7 +314,7 @@ def run_ours(args):
                                    % (sub.internal.nx, sub.internal.ny, gx, gy, probe.nx, probe.ny,
                                       args.alignment, args.mode),
                        "l2": "inputs larger than L2 (9 fields x %.2f GB per GPU)" % (grid.nx * grid.ny * 8 / 1e9),
-                       "fused_variant": args.variant, "parallelism": "tile-per-GPU %dx%d" % (probe.nx, probe.ny),
+                       "fused_variant": args.variant, "two_step": bool(args.two_step), "parallelism": "tile-per-GPU %dx%d" % (probe.nx, probe.ny),
                        "halo": ("push: the fused sweep stores the neighbours' halo cells over NVLink peer memory, "
                                 "flag hand-shake per step" if halo == "push" else
                                 ("periodic halo kernel" if world == 1 else "pack -> NCCL send/recv -> unpack"))},
@@ -416,6 +425,9 @@ def main():
     ap.add_argument("--scaling", choices=["weak", "strong"], default="weak",
                     help="weak: --size^2 points per GPU (default, the metric's configuration); "
                          "strong: --size^2 points in total, split by go_decompose")
+    ap.add_argument("--two-step", action="store_true",
+                    help="two model steps per sweep (temporal blocking; tile decomposed with halo_width=2)")
+    ap.add_argument("--variant2", type=int, default=0, help="kernel variant of the two-step sweep")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -434,6 +434,10 @@ class shallow_water:
         the neighbours' halo cells itself over NVLink peer memory).  Collective."""
         _chk(_lib.lib().dlesm_sw_set_halo_mode(self._h, mode))
 
+    def set_two_step(self, on=True, variant2=0):
+        """two model steps per sweep (temporal blocking; needs grid.decompose(..., halo_width=2))"""
+        _chk(_lib.lib().dlesm_sw_set_two_step(self._h, int(bool(on)), variant2))
+
     def step(self, nsteps=1):
         _chk(_lib.lib().dlesm_sw_step(self._h, nsteps))
 

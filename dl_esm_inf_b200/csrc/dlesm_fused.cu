@@ -456,7 +456,7 @@ bool get_map(const void *base, int elem_bytes, int nx, int ny, int boxw, int box
 // row count is rounded up to whole chunks of `ry` rows, so: segments of about `target` rows,
 // the CTA count rounded up to whole waves of `slots` resident CTAs, and seg_rows + 2 a
 // multiple of `ry` whenever that does not add a segment.
-int pick_seg_rows(int w, int h, int tx, int slots, int ry, int target)
+int pick_seg_rows(int w, int h, int tx, int slots, int ry, int target, int extra = 2)
 {
     const int strips = (w + tx - 1) / tx;
     int nseg = (h + target - 1) / target;
@@ -467,9 +467,9 @@ int pick_seg_rows(int w, int h, int tx, int slots, int ry, int target)
     if (nseg < 1) nseg = 1;
     if (nseg > h) nseg = h;
     int seg = (h + nseg - 1) / nseg;
-    // seg + 2 a multiple of ry: round up if the segment count stays the same, else down
-    const int up = ((seg + 2 + ry - 1) / ry) * ry - 2;
-    const int down = ((seg + 2) / ry) * ry - 2;
+    // seg + extra a multiple of ry: round up if the segment count stays the same, else down
+    const int up = ((seg + extra + ry - 1) / ry) * ry - extra;
+    const int down = ((seg + extra) / ry) * ry - extra;
     if (up >= 1 && (h + up - 1) / up == (h + seg - 1) / seg) seg = up;
     else if (down >= ry) seg = down;
     return seg;
@@ -532,7 +532,233 @@ cudaError_t launch_tma(const FusedArgs &a, cudaStream_t s)
                  : launch_tma_mf<TX, RY, STAGES, MINB, false, false, ALN>(a, s);
 }
 
+// ---------------------------------------------------------------------------------------
+// Two model steps per sweep (temporal blocking).  Stage A is the march above, run on a strip
+// one column wider on each side and one row longer at each end, producing the intermediate
+// state (u1,v1,p1 and the once-filtered old fields) of step n+1; its rows go through a small
+// shared-memory exchange buffer so that stage B -- the same march again, fed by u1,v1,p1 of the
+// west / own / east column -- produces step n+2 two rows behind.  The intermediate state never
+// reaches memory: 6 reads + 6 writes per point for TWO steps.  Thread t of TX owns column
+// i_first - 1 + t in both stages; threads 1 .. TX-2 store.
+// ---------------------------------------------------------------------------------------
+struct Tma2Params {
+    double *u2, *v2, *p2, *uold2, *vold2, *pold2;
+    int pitch;
+    Box b;
+    int seg_rows;
+    SwScalars sc;
+};
+
+template <int TX, int RY, int STAGES>
+struct Tma2Cfg {
+    static constexpr int BW = TX + 4;    // raw tiles: west halo + TX + east halo, even start column
+    static constexpr int BWO = TX + 2;   // old tiles: TX columns, even start column
+    static constexpr int A = align128(BW * RY * 8);
+    static constexpr int AO = align128(BWO * RY * 8);
+    static constexpr int OFF_OLD = 3 * A;
+    static constexpr int STAGE_BYTES = 3 * A + 3 * AO;
+    static constexpr int TX_BYTES = 3 * BW * RY * 8 + 3 * BWO * RY * 8;
+    static constexpr int XW = TX + 2;    // exchange row: one pad column on each side
+    static constexpr int XBUF_BYTES = 3 * RY * XW * 8;   // u1, v1, p1 rows of one chunk
+    static constexpr int OFF_X = STAGES * STAGE_BYTES;
+    static constexpr int BAR_OFFSET = OFF_X + 2 * XBUF_BYTES;
+    static constexpr int SMEM_BYTES = BAR_OFFSET + STAGES * 8;
+    static constexpr int THREADS = TX;
+    static constexpr int OUT = TX - 2;   // output columns per strip
+};
+
+template <int TX, int RY, int STAGES, int MINB>
+__global__ void __launch_bounds__(TX, MINB)
+fused2_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_constant__ CUtensorMap tm_v,
+                  const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUtensorMap tm_uo,
+                  const __grid_constant__ CUtensorMap tm_vo, const __grid_constant__ CUtensorMap tm_po,
+                  const __grid_constant__ Tma2Params prm)
+{
+    using Cfg = Tma2Cfg<TX, RY, STAGES>;
+    constexpr int BW = Cfg::BW, BWO = Cfg::BWO, XW = Cfg::XW;
+    extern __shared__ __align__(1024) unsigned char fused_smem[];
+    uint64_t *full = reinterpret_cast<uint64_t *>(fused_smem + Cfg::BAR_OFFSET);
+
+    const int tid = threadIdx.x;
+    const int j0 = prm.b.ys + blockIdx.y * prm.seg_rows;
+    const int j1 = min(j0 + prm.seg_rows - 1, prm.b.ye);
+    const int nsteps = (j1 - j0 + 1) + 4;            // raw rows j0-2 .. j1+2
+    const int nchunks = (nsteps + RY - 1) / RY;
+    const int i_first = prm.b.xs + blockIdx.x * Cfg::OUT;   // first output column of this strip
+    const int x_box = (i_first - 3) & ~1;   // even 0-based column at/below thread 0's west neighbour
+    const int x_old = (i_first - 2) & ~1;   // even 0-based column at/below thread 0's own column
+
+    // No producer warp here: the per-chunk barrier between the two stages already tells thread 0
+    // that every warp is done with a ring stage, so it refills the stage right after it.  (A
+    // fifth warp would also cap the kernel at 168 registers: 10 warps on 4 schedulers.)
+    auto issue = [&](int c) {
+        const int s = c % STAGES;
+        unsigned char *st = fused_smem + s * Cfg::STAGE_BYTES;
+        const int y_raw = (j0 - 2) + c * RY - 1;   // 0-based row of the chunk's first raw row
+        const int y_old = y_raw - 1;               // stage A's outputs trail the raw rows by one
+        mbar_expect_tx(&full[s], Cfg::TX_BYTES);
+        tma_load_2d(st + 0 * Cfg::A, &tm_p, x_box, y_raw, &full[s]);
+        tma_load_2d(st + 1 * Cfg::A, &tm_u, x_box, y_raw, &full[s]);
+        tma_load_2d(st + 2 * Cfg::A, &tm_v, x_box, y_raw, &full[s]);
+        tma_load_2d(st + Cfg::OFF_OLD + 0 * Cfg::AO, &tm_uo, x_old, y_old, &full[s]);
+        tma_load_2d(st + Cfg::OFF_OLD + 1 * Cfg::AO, &tm_vo, x_old, y_old, &full[s]);
+        tma_load_2d(st + Cfg::OFF_OLD + 2 * Cfg::AO, &tm_po, x_old, y_old, &full[s]);
+    };
+    if (tid == 0) {
+        if (smem_u32(fused_smem) & 127u) __trap();
+        for (int s = 0; s < STAGES; ++s) mbar_init(&full[s], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        for (int c = 0; c < STAGES && c < nchunks; ++c) issue(c);
+    }
+    // pad columns of the exchange rows (read by threads 0 and TX-1 only, whose stage-B results
+    // are never stored): finite values so that no inf/nan is manufactured
+    for (int q = tid; q < 2 * 3 * RY * 2; q += TX) {
+        const int row = q >> 1, side = q & 1;        // row over (buffer, field, r)
+        double *xr = reinterpret_cast<double *>(fused_smem + Cfg::OFF_X) + row * XW;
+        xr[side ? XW - 1 : 0] = 1.0;
+    }
+    __syncthreads();
+
+    const int i = i_first - 1 + tid;
+    const bool active = tid >= 1 && tid <= TX - 2 && i <= prm.b.xe;
+    const int col = tid + ((i_first - 3) & 1);        // west neighbour's column inside the raw tile
+    const int colo = tid + ((i_first - 2) & 1);       // own column inside the old-field tile
+    const SwScalars sc = prm.sc;
+    Carry<false> ca, cb;
+    carry_init(ca);
+    carry_init(cb);
+    double uo1 = 0.0, vo1 = 0.0, po1 = 0.0;   // once-filtered old fields of the row stage B emits next
+    // raw step t ingests raw row j0-2+t; stage A emits row j0-3+t; stage B emits row j0-4+t
+    long long qo = (static_cast<long long>(j0) - 5) * prm.pitch + (i - 1);
+    const long long pitch = prm.pitch;
+    int t_lo = active ? 4 : (1 << 30), t_hi = nsteps;
+    for (int c = 0; c < nchunks; ++c) {
+        const int s = c % STAGES;
+        mbar_wait(&full[s], (c / STAGES) & 1);
+        const unsigned char *st = fused_smem + s * Cfg::STAGE_BYTES;
+        const double *sp = reinterpret_cast<const double *>(st + 0 * Cfg::A) + col;
+        const double *su = reinterpret_cast<const double *>(st + 1 * Cfg::A) + col;
+        const double *sv = reinterpret_cast<const double *>(st + 2 * Cfg::A) + col;
+        const double *suo = reinterpret_cast<const double *>(st + Cfg::OFF_OLD + 0 * Cfg::AO) + colo;
+        const double *svo = reinterpret_cast<const double *>(st + Cfg::OFF_OLD + 1 * Cfg::AO) + colo;
+        const double *spo = reinterpret_cast<const double *>(st + Cfg::OFF_OLD + 2 * Cfg::AO) + colo;
+        double *xb = reinterpret_cast<double *>(fused_smem + Cfg::OFF_X + (c & 1) * Cfg::XBUF_BYTES) + tid;
+        double uo_r[RY], vo_r[RY], po_r[RY];
+        // ---- stage A: RY raw rows -> RY rows of the intermediate state ----
+#pragma unroll
+        for (int r = 0; r < RY; ++r) {
+            Raw<false> N;
+            N.pW = sp[r * BW]; N.pC = sp[r * BW + 1]; N.pE = sp[r * BW + 2];
+            N.uW = su[r * BW]; N.uC = su[r * BW + 1]; N.uE = su[r * BW + 2];
+            N.vW = sv[r * BW]; N.vC = sv[r * BW + 1]; N.vE = sv[r * BW + 2];
+            Outs o;
+            ingest<false>(ca, N, sc, suo[r * BWO], svo[r * BWO], spo[r * BWO], o);
+            xb[(0 * RY + r) * XW + 1] = o.unew;
+            xb[(1 * RY + r) * XW + 1] = o.vnew;
+            xb[(2 * RY + r) * XW + 1] = o.pnew;
+            uo_r[r] = o.uold; vo_r[r] = o.vold; po_r[r] = o.pold;
+        }
+        __syncthreads();
+        if (tid == 0 && c + STAGES < nchunks) issue(c + STAGES);
+        // ---- stage B: those RY rows (west / own / east column) -> RY rows of step n+2 ----
+#pragma unroll
+        for (int r = 0; r < RY; ++r) {
+            Raw<false> N;
+            N.uW = xb[(0 * RY + r) * XW]; N.uC = xb[(0 * RY + r) * XW + 1]; N.uE = xb[(0 * RY + r) * XW + 2];
+            N.vW = xb[(1 * RY + r) * XW]; N.vC = xb[(1 * RY + r) * XW + 1]; N.vE = xb[(1 * RY + r) * XW + 2];
+            N.pW = xb[(2 * RY + r) * XW]; N.pC = xb[(2 * RY + r) * XW + 1]; N.pE = xb[(2 * RY + r) * XW + 2];
+            Outs o;
+            ingest<false>(cb, N, sc, uo1, vo1, po1, o);
+            uo1 = uo_r[r]; vo1 = vo_r[r]; po1 = po_r[r];
+            if (r >= t_lo && r < t_hi) {
+                __stcs(prm.u2 + qo, o.unew);
+                __stcs(prm.v2 + qo, o.vnew);
+                __stcs(prm.p2 + qo, o.pnew);
+                __stcs(prm.uold2 + qo, o.uold);
+                __stcs(prm.vold2 + qo, o.vold);
+                __stcs(prm.pold2 + qo, o.pold);
+            }
+            qo += pitch;
+        }
+        t_lo -= RY;
+        t_hi -= RY;
+    }
+}
+
+template <int TX, int RY, int STAGES, int MINB>
+cudaError_t launch_tma2(const Fused2Args &a, cudaStream_t s)
+{
+    using Cfg = Tma2Cfg<TX, RY, STAGES>;
+    CUtensorMap mu, mv, mp, muo, mvo, mpo;
+    if (!get_map(a.u, 8, a.pitch, a.ny, Cfg::BW, RY, mu) || !get_map(a.v, 8, a.pitch, a.ny, Cfg::BW, RY, mv) ||
+        !get_map(a.p, 8, a.pitch, a.ny, Cfg::BW, RY, mp) || !get_map(a.uold, 8, a.pitch, a.ny, Cfg::BWO, RY, muo) ||
+        !get_map(a.vold, 8, a.pitch, a.ny, Cfg::BWO, RY, mvo) || !get_map(a.pold, 8, a.pitch, a.ny, Cfg::BWO, RY, mpo))
+        return cudaErrorNotSupported;
+    Tma2Params prm;
+    prm.u2 = a.u2; prm.v2 = a.v2; prm.p2 = a.p2;
+    prm.uold2 = a.uold2; prm.vold2 = a.vold2; prm.pold2 = a.pold2;
+    const int w = a.b.xe - a.b.xs + 1, h = a.b.ye - a.b.ys + 1;
+    static const int target = [] {
+        // every segment recomputes two rows of the intermediate state and re-reads four raw rows,
+        // so segments are longer than the one-step sweep's; DLESM_SEG_ROWS2 overrides
+        const char *e = std::getenv("DLESM_SEG_ROWS2");
+        const int v = e ? std::atoi(e) : 60;
+        return v < 8 ? 60 : v;
+    }();
+    const int seg_rows = pick_seg_rows(w, h, Cfg::OUT, 148 * MINB, RY, target, 4);
+    prm.pitch = a.pitch; prm.b = a.b; prm.seg_rows = seg_rows; prm.sc = a.sc;
+    auto kern = fused2_tma_kernel<TX, RY, STAGES, MINB>;
+    static bool attr_done = false;
+    if (!attr_done) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
+        if (e != cudaSuccess) return e;
+        attr_done = true;
+    }
+    dim3 grid((w + Cfg::OUT - 1) / Cfg::OUT, (h + seg_rows - 1) / seg_rows);
+    kern<<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, s>>>(mu, mv, mp, muo, mvo, mpo, prm);
+    return cudaGetLastError();
+}
+
+struct Tma2Variant {
+    int id;
+    const char *name;
+    cudaError_t (*launch)(const Fused2Args &, cudaStream_t);
+};
+// {threads = columns of stage A (TMA boxes are at most 256 wide: 128 only), rows per chunk,
+// stages, resident CTAs per SM}
+const Tma2Variant kTma2Variants[] = {
+    {1, "tma2-128x4x3-occ2", launch_tma2<128, 4, 3, 2>},
+    {2, "tma2-128x4x2-occ2", launch_tma2<128, 4, 2, 2>},
+    {3, "tma2-128x2x3-occ3", launch_tma2<128, 2, 3, 3>},
+    {4, "tma2-128x2x4-occ2", launch_tma2<128, 2, 4, 2>},
+    {5, "tma2-128x2x2-occ3", launch_tma2<128, 2, 2, 3>},
+    {6, "tma2-128x8x2-occ1", launch_tma2<128, 8, 2, 1>},
+    {7, "tma2-128x1x4-occ3", launch_tma2<128, 1, 4, 3>},
+};
+constexpr int kDefaultTma2Variant = 2;
+
 }  // namespace
+
+bool fused2_supported(const Fused2Args &a)
+{
+    return a.pitch % 2 == 0 && encode_fn() != nullptr && a.b.xs >= 3 && a.b.ys >= 3 && a.b.xe + 2 <= a.pitch &&
+           a.b.ye + 2 <= a.ny && !a.sc.first;
+}
+
+cudaError_t sw_step2_fused(const Fused2Args &a, int variant, cudaStream_t s)
+{
+    if (a.b.xe < a.b.xs || a.b.ye < a.b.ys) return cudaSuccess;
+    if (!fused2_supported(a)) return cudaErrorNotSupported;
+    if (variant == 0) variant = kDefaultTma2Variant;
+    for (const auto &v : kTma2Variants)
+        if (v.id == variant) {
+            cudaError_t e = v.launch(a, s);
+            note_launch();
+            return e;
+        }
+    return cudaErrorInvalidValue;
+}
 
 namespace {
 struct TmaVariant {

@@ -262,6 +262,62 @@ cudaError_t periodic_halos(double *const *fields, int nfields, int pitch, Box in
     return cudaGetLastError();
 }
 
+// The same periodic fill to `depth` cells (extension: the reference's halo lists are one cell
+// deep, src/field_mod.f90:1394-1464).  Every frame cell reads its wrapped internal source, so
+// corners need no ordering.
+struct DeepHaloArgs {
+    double *f[kMaxExchangeFields];
+    int nfields, pitch, depth;
+    Box in;
+};
+
+__global__ void __launch_bounds__(256) periodic_halo_deep_kernel(DeepHaloArgs a)
+{
+    const int w = a.in.xe - a.in.xs + 1, h = a.in.ye - a.in.ys + 1, d = a.depth;
+    const int wf = w + 2 * d;
+    const long long nband = 2LL * d * wf;        // S then N bands, full frame width
+    const long long nside = 2LL * d * h;         // W then E side bands
+    const long long per_field = nband + nside;
+    const long long total = per_field * a.nfields;
+    for (long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; t < total;
+         t += static_cast<long long>(gridDim.x) * blockDim.x) {
+        const int kf = static_cast<int>(t / per_field);
+        long long c = t - kf * per_field;
+        int di, dj;
+        if (c < nband) {
+            const int rr = static_cast<int>(c / wf), ii = static_cast<int>(c - static_cast<long long>(rr) * wf);
+            di = a.in.xs - d + ii;
+            dj = rr < d ? a.in.ys - d + rr : a.in.ye + 1 + (rr - d);
+        } else {
+            c -= nband;
+            const int jj = static_cast<int>(c / (2 * d)), ii = static_cast<int>(c - static_cast<long long>(jj) * 2 * d);
+            dj = a.in.ys + jj;
+            di = ii < d ? a.in.xs - d + ii : a.in.xe + 1 + (ii - d);
+        }
+        int si = di, sj = dj;
+        if (si < a.in.xs) si += w; else if (si > a.in.xe) si -= w;
+        if (sj < a.in.ys) sj += h; else if (sj > a.in.ye) sj -= h;
+        double *f = a.f[kf];
+        f[idx(a.pitch, di, dj)] = f[idx(a.pitch, si, sj)];
+    }
+}
+
+cudaError_t periodic_halos_deep(double *const *fields, int nfields, int pitch, Box in, int depth, cudaStream_t s)
+{
+    if (nfields <= 0 || depth <= 0) return cudaSuccess;
+    if (nfields > kMaxExchangeFields) return cudaErrorInvalidValue;
+    const int w = in.xe - in.xs + 1, h = in.ye - in.ys + 1;
+    if (depth > w || depth > h) return cudaErrorInvalidValue;
+    DeepHaloArgs a;
+    for (int q = 0; q < nfields; ++q) a.f[q] = fields[q];
+    a.nfields = nfields; a.pitch = pitch; a.depth = depth; a.in = in;
+    const long long total = static_cast<long long>(nfields) * (2LL * depth * (w + 2 * depth) + 2LL * depth * h);
+    const unsigned blocks = total / 256 + 1 < kSMs * 4 ? static_cast<unsigned>(total / 256 + 1) : kSMs * 4;
+    periodic_halo_deep_kernel<<<blocks, 256, 0, s>>>(a);
+    count_launch();
+    return cudaGetLastError();
+}
+
 // ---------------------------------------------------------------------------------------
 // Halo pack / unpack (src/parallel_comms_mod.f90:1678-1683, 1788-1793): every patch of every
 // field in one launch; within a patch j is the outer and i the inner index, as the

@@ -121,6 +121,25 @@ constexpr int kNumFusedVariants = 6;
 cudaError_t sw_step_fused(const FusedArgs &a, int variant, cudaStream_t s);
 const char *fused_variant_name(int variant);
 
+// ---- two model steps in one sweep (temporal blocking): 96 B / point per TWO steps ----
+// Needs a tile with halo width >= 2: u,v,p valid to depth 2 around `b`, uold,vold,pold valid to
+// depth 1.  The intermediate state (step n+1) is recomputed on the depth-1 ring and never
+// stored.  Outputs (step n+2) go to separate arrays: u2,v2,p2 and the twice-filtered
+// uold2,vold2,pold2 (not in place: neighbouring CTAs still read the old fields' ring).
+// No tmask, not the first (unfiltered) step.
+struct Fused2Args {
+    const double *u, *v, *p, *uold, *vold, *pold;
+    double *u2, *v2, *p2, *uold2, *vold2, *pold2;
+    int pitch, ny;
+    Box b;
+    SwScalars sc;
+};
+bool fused2_supported(const Fused2Args &a);
+cudaError_t sw_step2_fused(const Fused2Args &a, int variant, cudaStream_t s);
+// periodic halo fill to `depth` cells on one rank (wrapped source index; corners included)
+cudaError_t periodic_halos_deep(double *const *fields, int nfields, int pitch, Box internal, int depth,
+                                cudaStream_t s);
+
 // classic initial conditions, synthetic (device sin/cos)
 cudaError_t sw_init(double *u, double *v, double *p, int pitch, Box b, int gx0, int gy0, int M,
                     int N, double dx, double dy, cudaStream_t s);

@@ -617,6 +617,21 @@ extern "C" int dlesm_dev_periodic_halos(void *f, int xs, int xe, int ys, int ye,
     return DLESM_OK;
 }
 
+extern "C" int dlesm_dev_periodic_halos_deep(void *f, int xs, int xe, int ys, int ye, int depth)
+{
+    FieldRec r;
+    int rc = lookup(f, r);
+    if (rc != DLESM_OK) return rc;
+    if (depth < 1 || xs <= depth || ys <= depth || xe + depth > r.nx || ye + depth > r.ny || depth > xe - xs + 1 ||
+        depth > ye - ys + 1) {
+        set_error(DLESM_ERR_ARGS, "periodic halos: the allocation has no room for a halo that deep");
+        return DLESM_ERR_ARGS;
+    }
+    double *fl[1] = {static_cast<double *>(f)};
+    CU(k::periodic_halos_deep(fl, 1, r.nx, k::Box{xs, xe, ys, ye}, depth, ctx().stream));
+    return DLESM_OK;
+}
+
 // =========================================================================================
 // halo exchange
 // =========================================================================================
@@ -1207,6 +1222,69 @@ extern "C" int dlesm_sw_step_fused(const void *u, const void *v, const void *p, 
     return DLESM_OK;
 }
 
+extern "C" int dlesm_sw_step2_fused(const void *u, const void *v, const void *p, const void *uold, const void *vold,
+                                    const void *pold, void *u2, void *v2, void *p2, void *uold2, void *vold2,
+                                    void *pold2, double dx, double dy, double tdt, double alpha, int xs, int xe,
+                                    int ys, int ye, int variant)
+{
+    SWEEP_PROLOGUE(u2)
+    (void)b;
+    const void *all[] = {u, v, p, uold, vold, pold, v2, p2, uold2, vold2, pold2};
+    for (const void *q : all) {
+        FieldRec r;
+        rc = lookup(q, r);
+        if (rc != DLESM_OK) return rc;
+        if (r.nx != pitch || r.ny != ny_) {
+            set_error(DLESM_ERR_ARGS, "sw_step2_fused: fields have different shapes");
+            return DLESM_ERR_ARGS;
+        }
+    }
+    const void *ins[] = {u, v, p, uold, vold, pold};
+    const void *outs[] = {u2, v2, p2, uold2, vold2, pold2};
+    for (const void *a : ins)
+        for (const void *o : outs)
+            if (a == o) {
+                set_error(DLESM_ERR_ARGS, "sw_step2_fused: outputs must not alias inputs (neighbouring blocks re-read the ring)");
+                return DLESM_ERR_ARGS;
+            }
+    k::Fused2Args a;
+    a.u = CD(u); a.v = CD(v); a.p = CD(p);
+    a.uold = CD(uold); a.vold = CD(vold); a.pold = CD(pold);
+    a.u2 = D(u2); a.v2 = D(v2); a.p2 = D(p2);
+    a.uold2 = D(uold2); a.vold2 = D(vold2); a.pold2 = D(pold2);
+    a.pitch = pitch; a.ny = ny_;
+    a.b = k::Box{xs, xe, ys, ye};
+    a.sc.fsdx = 4.0 / dx; a.sc.fsdy = 4.0 / dy;
+    a.sc.tdts8 = tdt / 8.0; a.sc.tdtsdx = tdt / dx; a.sc.tdtsdy = tdt / dy;
+    a.sc.alpha = alpha; a.sc.first = 0;
+    if (!k::fused2_supported(a)) {
+        set_error(DLESM_ERR_ARGS, "sw_step2_fused: needs an even pitch and a box with two halo cells on every side (halo_width >= 2)");
+        return DLESM_ERR_ARGS;
+    }
+    Context &c = ctx();
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    if (c.profile) {
+        if (c.prof_used == c.prof_events.size()) {
+            cudaEvent_t x, y;
+            CU(cudaEventCreate(&x));
+            CU(cudaEventCreate(&y));
+            c.prof_events.emplace_back(x, y);
+        }
+        e0 = c.prof_events[c.prof_used].first;
+        e1 = c.prof_events[c.prof_used].second;
+        ++c.prof_used;
+        CU(cudaEventRecord(e0, st));
+    }
+    cudaError_t e = k::sw_step2_fused(a, variant, st);
+    if (e == cudaErrorNotSupported || e == cudaErrorInvalidValue) {
+        set_error(DLESM_ERR_ARGS, "sw_step2_fused: variant not available (see DESIGN.md)");
+        return DLESM_ERR_ARGS;
+    }
+    if (e != cudaSuccess) return fail_cuda(e, "sw_step2_fused");
+    if (c.profile) CU(cudaEventRecord(e1, st));
+    return DLESM_OK;
+}
+
 extern "C" long long dlesm_kernel_launch_count(void) { return k::launch_count(); }
 extern "C" int dlesm_profile_enable(int on)
 {
@@ -1734,6 +1812,12 @@ struct dlesm_sw {
     bool periodic_local = true;  // halos by local copies (1 rank) or by exchange (several)
     bool push = false;           // halos stored by the fused sweep itself (DLESM_HALO_PUSH)
     bool registered = false;     // buffers are mapped by the neighbours (dlesm_dev_peer_register)
+    // two steps per sweep (dlesm_sw_set_two_step): second set of old fields (the two-step sweep
+    // cannot filter in place), and whether u,v,p / uold,vold,pold currently hold deep halos
+    bool two_step = false;
+    int variant2 = 0;
+    dlesm_field *old2[3] = {nullptr, nullptr, nullptr};
+    bool deep_valid = false;
 };
 
 extern "C" dlesm_sw_t *dlesm_sw_create(dlesm_grid_t *g, double dt, double alpha, int mode, int use_tmask)
@@ -1827,6 +1911,57 @@ extern "C" int dlesm_sw_set_halo_mode(dlesm_sw_t *s, int mode)
     return DLESM_OK;
 }
 
+namespace {
+// halos of u,v,p,uold,vold,pold two cells deep: wrapped copies on one rank, the depth-2
+// exchange (DLESM_EXT_HALO_DEPTH tables) on several
+int sw_fill_deep_halos(dlesm_sw *s)
+{
+    dlesm_field *fl[6];
+    for (int q = 0; q < 6; ++q) fl[q] = s->f[DLESM_SW_U + q];
+    if (s->periodic_local) {
+        double *dp[6];
+        for (int q = 0; q < 6; ++q) dp[q] = static_cast<double *>(fl[q]->dptr);
+        CU(k::periodic_halos_deep(dp, 6, fl[0]->nx, box_of(s->f[DLESM_SW_P]->fb.internal), 2, ctx().stream));
+        return DLESM_OK;
+    }
+    return dlesm_fields_halo_exchange(fl, 6, 2);
+}
+}  // namespace
+
+extern "C" int dlesm_sw_set_two_step(dlesm_sw_t *s, int on, int variant2)
+{
+    clear_error();
+    if (!on) {
+        s->two_step = false;
+        return DLESM_OK;
+    }
+    const dlesm_region &in = s->f[DLESM_SW_P]->fb.internal;
+    const int nx = s->f[0]->nx, ny = s->f[0]->ny;
+    if (s->mode != DLESM_SW_FUSED || s->tmask_dev || s->push) {
+        set_error(DLESM_ERR_ARGS, "sw_set_two_step: needs the fused mode without tmask and without halo push");
+        return DLESM_ERR_ARGS;
+    }
+    if (nx % 2 != 0 || in.xstart < 3 || in.ystart < 3 || in.xstop + 2 > nx || in.ystop + 2 > ny ||
+        in.xstop - in.xstart < 1 || in.ystop - in.ystart < 1) {
+        set_error(DLESM_ERR_ARGS, "sw_set_two_step: needs an even pitch and a grid decomposed with halo_width >= 2");
+        return DLESM_ERR_ARGS;
+    }
+    if (!s->periodic_local && !(pstate().extensions & DLESM_EXT_HALO_DEPTH)) {
+        set_error(DLESM_ERR_STATE, "sw_set_two_step: several ranks need DLESM_EXT_HALO_DEPTH (depth-2 exchange)");
+        return DLESM_ERR_STATE;
+    }
+    static const int pts[3] = {DLESM_GO_U_POINTS, DLESM_GO_V_POINTS, DLESM_GO_T_POINTS};
+    for (int q = 0; q < 3; ++q)
+        if (!s->old2[q]) {
+            s->old2[q] = dlesm_r2d_field_create(s->grid, pts[q], 0, nullptr, 0, 0);
+            if (!s->old2[q]) return last_status();
+        }
+    s->two_step = true;
+    s->variant2 = variant2;
+    s->deep_valid = false;
+    return DLESM_OK;
+}
+
 extern "C" int dlesm_sw_init_device(dlesm_sw_t *s)
 {
     clear_error();
@@ -1844,6 +1979,7 @@ extern "C" int dlesm_sw_init_device(dlesm_sw_t *s)
         if (rc != DLESM_OK) return rc;
     }
     s->ncycle = 0;
+    s->deep_valid = false;
     s->tdt = s->dt;
     return DLESM_OK;
 }
@@ -1859,6 +1995,7 @@ extern "C" int dlesm_sw_set_state(dlesm_sw_t *s, const double *u, const double *
         if (rc != DLESM_OK) return rc;
     }
     s->ncycle = 0;
+    s->deep_valid = false;
     s->tdt = s->dt;
     return DLESM_OK;
 }
@@ -1871,6 +2008,30 @@ extern "C" int dlesm_sw_step(dlesm_sw_t *s, int nsteps)
     for (int it = 0; it < nsteps; ++it) {
         const int first = s->ncycle == 0;
         dlesm_field **f = s->f;
+        if (s->two_step && !first && nsteps - it >= 2) {
+            // two steps in one sweep: 96 B / point for both
+            const dlesm_region &rt = f[DLESM_SW_P]->fb.internal;
+            int rc = DLESM_OK;
+            if (!s->deep_valid) rc = sw_fill_deep_halos(s);
+            if (rc != DLESM_OK) return rc;
+            rc = dlesm_sw_step2_fused(f[DLESM_SW_U]->dptr, f[DLESM_SW_V]->dptr, f[DLESM_SW_P]->dptr,
+                                      f[DLESM_SW_UOLD]->dptr, f[DLESM_SW_VOLD]->dptr, f[DLESM_SW_POLD]->dptr,
+                                      f[DLESM_SW_UNEW]->dptr, f[DLESM_SW_VNEW]->dptr, f[DLESM_SW_PNEW]->dptr,
+                                      s->old2[0]->dptr, s->old2[1]->dptr, s->old2[2]->dptr, dx, dy, s->tdt, s->alpha,
+                                      rt.xstart, rt.xstop, rt.ystart, rt.ystop, s->variant2);
+            if (rc != DLESM_OK) return rc;
+            for (int q = 0; q < 3; ++q) {
+                std::swap(f[DLESM_SW_U + q]->dptr, f[DLESM_SW_UNEW + q]->dptr);
+                std::swap(f[DLESM_SW_UOLD + q]->dptr, s->old2[q]->dptr);
+            }
+            rc = sw_fill_deep_halos(s);
+            if (rc != DLESM_OK) return rc;
+            s->deep_valid = true;
+            s->ncycle += 2;
+            ++it;
+            continue;
+        }
+        s->deep_valid = false;
         const dlesm_region &ru = f[DLESM_SW_U]->fb.internal, &rv = f[DLESM_SW_V]->fb.internal;
         const dlesm_region &rt = f[DLESM_SW_P]->fb.internal;
         int rc;
@@ -2030,6 +2191,7 @@ extern "C" int dlesm_sw_step_host(dlesm_sw_t *s, const double *const host_in[6],
     for (int q = 0; q < 3; ++q) std::swap(f[DLESM_SW_U + q]->dptr, f[DLESM_SW_UNEW + q]->dptr);
     if (first) s->tdt = s->tdt + s->tdt;
     ++s->ncycle;
+    s->deep_valid = false;
     return DLESM_OK;
 }
 
@@ -2048,6 +2210,8 @@ extern "C" void dlesm_sw_free(dlesm_sw_t *s)
     if (!s) return;
     if (s->registered) dlesm_dev_peer_unregister_all();   // collective, like the set_halo_mode that mapped them
     for (auto *fl : s->f)
+        if (fl) dlesm_free_field(fl);
+    for (auto *fl : s->old2)
         if (fl) dlesm_free_field(fl);
     delete s;
 }

@@ -420,6 +420,24 @@ int dlesm_sw_step_fused(const void *u, const void *v, const void *p, void *uold,
                         double tdt, double alpha, int first, int xstart, int xstop, int ystart,
                         int ystop, const void *tmask, int variant);
 
+/* TWO model steps in one sweep (temporal blocking; extension, no reference counterpart: the
+ * reference's formulation is one loop nest per kernel).  The intermediate state
+ * of step n+1 is recomputed on a one-cell ring around each CTA's block and never stored, so the
+ * two steps cost the 96 B / point of one.  Results are bit-identical to two dlesm_sw_step_fused
+ * calls with a halo fill in between.  Requirements: a tile decomposed with halo_width >= 2
+ * (xstart, ystart >= 3); u,v,p valid to depth 2 and uold,vold,pold valid to depth 1 around the
+ * box; `tdt` = 2*dt (not the first step); no tmask; even pitch.  Writes u2,v2,p2 (step n+2)
+ * and the twice-filtered uold2,vold2,pold2 on the box -- separate arrays, not in place.  Halos
+ * of the outputs are NOT filled (dlesm_dev_periodic_halos_deep / halo_exchange(depth 2)).
+ * `variant` 0 = default.  Timed by dlesm_profile_enable like dlesm_sw_step_fused. */
+int dlesm_sw_step2_fused(const void *u, const void *v, const void *p, const void *uold,
+                         const void *vold, const void *pold, void *u2, void *v2, void *p2,
+                         void *uold2, void *vold2, void *pold2, double dx, double dy, double tdt,
+                         double alpha, int xstart, int xstop, int ystart, int ystop, int variant);
+/* periodic halo fill of one field to `depth` cells on one rank (the reference's lists,
+ * src/field_mod.f90:1394-1464, are one cell deep; depth 1 == dlesm_dev_periodic_halos) */
+int dlesm_dev_periodic_halos_deep(void *f, int xstart, int xstop, int ystart, int ystop, int depth);
+
 /* ------------------------------------------------------------------------------------ */
 /* HOST MIRROR: the application ("PSy") layer for the shallow-water model -- not part of  */
 /* the reference library; provided so that tests/bench drive the fields the way a GOcean   */
@@ -458,6 +476,13 @@ int dlesm_sw_set_variant(dlesm_sw_t *s, int variant);
 #define DLESM_HALO_EXCHANGE 0
 #define DLESM_HALO_PUSH 1
 int dlesm_sw_set_halo_mode(dlesm_sw_t *s, int mode);
+/* on != 0: dlesm_sw_step advances two steps per sweep (dlesm_sw_step2_fused) whenever at least
+ * two steps remain and the first step is behind; an odd remainder runs the one-step sweep.
+ * Needs the fused mode, no tmask, an even pitch and a grid decomposed with halo_width >= 2;
+ * halos are then kept two cells deep (periodic copies on one rank, halo_exchange(depth 2) on
+ * several -- DLESM_EXT_HALO_DEPTH).  Allocates three more fields.  Not combined with
+ * DLESM_HALO_PUSH.  `variant2` selects the two-step kernel (0 = default). */
+int dlesm_sw_set_two_step(dlesm_sw_t *s, int on, int variant2);
 /* kernels launched by this library since process start (all streams) */
 long long dlesm_kernel_launch_count(void);
 /* CUDA-event time (ms) spent in dominant-kernel launches since the last call with reset=1,

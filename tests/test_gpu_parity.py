@@ -637,3 +637,82 @@ def test_halo_push_needs_registration_and_tma_pitch(monkeypatch):
     rc = L.dlesm_sw_step_fused(*f, 1.0e5, 1.0e5, 90.0, 0.001, 1, i.xstart, i.xstop, i.ystart, i.ystop, None,
                                fd.FUSED_PUSH)
     assert rc != 0 and b"push" in L.dlesm_last_error()
+
+
+# ---------------------------------------------------------------------------------------------
+# two model steps per sweep (temporal blocking) on a tile with halo width 2
+# ---------------------------------------------------------------------------------------------
+def sw_pair_hw2(n_x, n_y, alignment, monkeypatch, **kw):
+    """oracle on the reference's width-1 grid; product on the same domain decomposed with
+    halo_width=2 (internal region starts at 3), same internal values, wrapped halos"""
+    if alignment:
+        monkeypatch.setenv("DL_ESM_ALIGNMENT", str(alignment))
+    osw = O.ShallowWater(n_x, n_y, alignment=alignment or 1, **kw)
+    g = fd.grid_type(fd.GO_ARAKAWA_C, BCS_PER, fd.GO_OFFSET_SW)
+    g.decompose(n_x, n_y, halo_width=2)
+    fd.grid_init(g, kw.get("dx", 1.0e5), kw.get("dy", 1.0e5))
+    sw = fd.shallow_water(g, dt=kw.get("dt", 90.0), alpha=kw.get("alpha", 0.001), mode=fd.SW_FUSED)
+    oi = osw.fb["t"].internal
+    ii = sw.field("p").internal
+    assert (ii.xstart, ii.ystart, ii.nx, ii.ny) == (3, 3, n_x, n_y)
+    init = []
+    for n in ("u", "v", "p"):
+        core = osw.f[n][oi.xstart - 1:oi.xstop, oi.ystart - 1:oi.ystop]
+        a = np.zeros((g.nx, g.ny), order="F")
+        a[0:n_x + 4, 0:n_y + 4] = np.pad(core, 2, mode="wrap")
+        init.append(np.asfortranarray(a))
+    sw.set_state(*init)
+    return osw, sw
+
+
+def assert_internal_equal(osw, sw, halo=0):
+    oi = osw.fb["t"].internal
+    ii = sw.field("p").internal
+    for n in ("u", "v", "p", "uold", "vold", "pold"):
+        want = osw.f[n][oi.xstart - 1:oi.xstop, oi.ystart - 1:oi.ystop]
+        got = sw.field(n).get_data()
+        h = halo if n in ("u", "v", "p") else 0
+        want = np.pad(want, h, mode="wrap") if h else want
+        got = got[ii.xstart - 1 - h:ii.xstop + h, ii.ystart - 1 - h:ii.ystop + h]
+        if not np.array_equal(got, want):
+            bad = np.argwhere(got != want)
+            raise AssertionError("%s differs at %d points, first %s" % (n, len(bad), tuple(bad[0])))
+
+
+TWO_STEP_VARIANTS = [1, 2, 3, 4, 5, 6, 7]
+
+
+@pytest.mark.parametrize("variant2", TWO_STEP_VARIANTS)
+@pytest.mark.parametrize("n_x,n_y,align,nsteps", [(64, 64, 2, 7), (130, 77, 64, 6), (300, 523, 64, 5),
+                                                  (1024, 1024, 64, 9)])
+def test_two_step_sweep_matches_oracle(variant2, n_x, n_y, align, nsteps, monkeypatch):
+    """dlesm_sw_step with two steps per sweep == the oracle's one-step-at-a-time serial run, bit
+    for bit on every prognostic field (odd and even step counts: the first step and an odd
+    remainder run the one-step sweep)"""
+    try:
+        osw, sw = sw_pair_hw2(n_x, n_y, align, monkeypatch)
+        sw.set_two_step(True, variant2)
+        for _ in range(nsteps):
+            osw.step()
+        n0 = fd.kernel_launch_count()
+        sw.step(nsteps)
+        # 1 first step + pairs (+ 1 odd one): far fewer sweeps than steps
+        assert fd.kernel_launch_count() - n0 <= 3 * nsteps
+        assert_internal_equal(osw, sw, halo=1)
+        for a, b in zip(sw.checksums(), osw.checksums()):
+            assert abs(a - b) <= RTOL * abs(b)
+        # stepping on in two calls lands on the same state
+        osw.step(); osw.step(); osw.step()
+        sw.step(1)
+        sw.step(2)
+        assert_internal_equal(osw, sw, halo=1)
+    finally:
+        _lib.lib().dlesm_reset_saved_state()
+
+
+def test_two_step_needs_halo_width_two(monkeypatch):
+    monkeypatch.setenv("DL_ESM_ALIGNMENT", "2")
+    g = make_grid(64, 64, offset=fd.GO_OFFSET_SW, bcs=BCS_PER, tmask=None, dx=1.0e5, dy=1.0e5)
+    sw = fd.shallow_water(g, mode=fd.SW_FUSED)
+    with pytest.raises(fd.GoceanStop):
+        sw.set_two_step(True)
