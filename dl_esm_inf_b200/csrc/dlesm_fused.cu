@@ -686,10 +686,200 @@ fused2_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_constan
     }
 }
 
-template <int TX, int RY, int STAGES, int MINB>
-cudaError_t launch_tma2(const Fused2Args &a, cudaStream_t s)
+// ---------------------------------------------------------------------------------------
+// Two steps per sweep, second form: the two-step sweep is bound by the FP64 pipe, not by HBM
+// (ncu: 75 % FP64 pipe, 27 GB of DRAM traffic in 4.5 ms), and a third of its FP64 work is the
+// east / west copies of cu, z / cv, h every thread recomputes for itself.  Here every lane
+// computes the four intermediates of its own column only and takes the neighbours' through
+// warp shuffles.  Warps overlap by two columns (lane 0 and lane 31 only feed their
+// neighbours), so a warp yields 30 columns: 4 warps = 120 columns of the intermediate state,
+// 118 output columns per CTA.  The expression trees are unchanged -- lane l+1's cu(own) IS
+// lane l's cu(east), operand for operand -- so the bits are the same.
+// ---------------------------------------------------------------------------------------
+struct RawS {
+    double pW, pC, uC, uE, vW, vC;
+};
+struct CarryS {
+    RawS P;
+    double cuC_P, cuE_P, cuC_PP, cuE_PP, cvC_P, cvW_P, zC_P, zE_P, hC_PP;
+};
+__device__ __forceinline__ void carry_init(CarryS &c)
 {
-    using Cfg = Tma2Cfg<TX, RY, STAGES>;
+    c.P.pW = c.P.pC = 1.0;
+    c.P.uC = c.P.uE = c.P.vW = c.P.vC = 0.0;
+    c.cuC_P = c.cuE_P = c.cuC_PP = c.cuE_PP = c.cvC_P = c.cvW_P = c.zC_P = c.zE_P = c.hC_PP = 0.0;
+}
+__device__ __forceinline__ void ingest_sh(CarryS &c, const RawS &N, const SwScalars &sc, double uo, double vo,
+                                          double po, Outs &o)
+{
+    const RawS &P = c.P;
+    const double cuC_N = 0.5 * (N.pC + N.pW) * N.uC;
+    const double cvC_N = 0.5 * (N.pC + P.pC) * N.vC;
+    const double zC_N = (sc.fsdx * (N.vC - N.vW) - sc.fsdy * (N.uC - P.uC)) / (P.pW + P.pC + N.pC + N.pW);
+    const double hC_P = P.pC + 0.25 * (P.uE * P.uE + P.uC * P.uC + N.vC * N.vC + P.vC * P.vC);
+    const double cuE_N = __shfl_down_sync(0xffffffffu, cuC_N, 1);
+    const double zE_N = __shfl_down_sync(0xffffffffu, zC_N, 1);
+    const double cvW_N = __shfl_up_sync(0xffffffffu, cvC_N, 1);
+    const double hW_P = __shfl_up_sync(0xffffffffu, hC_P, 1);
+    o.unew = uo + sc.tdts8 * (zC_N + c.zC_P) * (cvC_N + cvW_N + c.cvW_P + c.cvC_P) -
+             sc.tdtsdx * (hC_P - hW_P);
+    o.vnew = vo - sc.tdts8 * (c.zE_P + c.zC_P) * (c.cuE_P + c.cuC_P + c.cuC_PP + c.cuE_PP) -
+             sc.tdtsdy * (hC_P - c.hC_PP);
+    o.pnew = po - sc.tdtsdx * (c.cuE_P - c.cuC_P) - sc.tdtsdy * (cvC_N - c.cvC_P);
+    o.uold = P.uC + sc.alpha * (o.unew - 2.0 * P.uC + uo);
+    o.vold = P.vC + sc.alpha * (o.vnew - 2.0 * P.vC + vo);
+    o.pold = P.pC + sc.alpha * (o.pnew - 2.0 * P.pC + po);
+    c.cuC_PP = c.cuC_P; c.cuE_PP = c.cuE_P;
+    c.cuC_P = cuC_N; c.cuE_P = cuE_N;
+    c.cvC_P = cvC_N; c.cvW_P = cvW_N;
+    c.zC_P = zC_N; c.zE_P = zE_N;
+    c.hC_PP = hC_P;
+    c.P = N;
+}
+
+template <int TX, int RY, int STAGES>
+struct Tma2sCfg {
+    static constexpr int NW = TX / 32;
+    static constexpr int VA = 30 * NW;   // columns of the intermediate state a CTA produces
+    static constexpr int OUT = VA - 2;   // output columns per CTA
+    static constexpr int BW = VA + 6;    // raw tiles: lanes' columns (VA + 2) + west + east, even start
+    static constexpr int BWO = VA + 4;   // old tiles: lanes' columns, even start
+    static constexpr int A = align128(BW * RY * 8);
+    static constexpr int AO = align128(BWO * RY * 8);
+    static constexpr int OFF_OLD = 3 * A;
+    static constexpr int STAGE_BYTES = 3 * A + 3 * AO;
+    static constexpr int TX_BYTES = 3 * BW * RY * 8 + 3 * BWO * RY * 8;
+    static constexpr int XW = VA + 4;    // exchange row: index of column x = x - i_first + 3
+    static constexpr int XBUF_BYTES = 3 * RY * XW * 8;
+    static constexpr int OFF_X = STAGES * STAGE_BYTES;
+    static constexpr int BAR_OFFSET = OFF_X + 2 * XBUF_BYTES;
+    static constexpr int SMEM_BYTES = BAR_OFFSET + STAGES * 8;
+    static constexpr int THREADS = TX;
+};
+
+template <int TX, int RY, int STAGES, int MINB>
+__global__ void __launch_bounds__(TX, MINB)
+fused2s_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_constant__ CUtensorMap tm_v,
+                   const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUtensorMap tm_uo,
+                   const __grid_constant__ CUtensorMap tm_vo, const __grid_constant__ CUtensorMap tm_po,
+                   const __grid_constant__ Tma2Params prm)
+{
+    using Cfg = Tma2sCfg<TX, RY, STAGES>;
+    constexpr int BW = Cfg::BW, BWO = Cfg::BWO, XW = Cfg::XW;
+    extern __shared__ __align__(1024) unsigned char fused_smem[];
+    uint64_t *full = reinterpret_cast<uint64_t *>(fused_smem + Cfg::BAR_OFFSET);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int j0 = prm.b.ys + blockIdx.y * prm.seg_rows;
+    const int j1 = min(j0 + prm.seg_rows - 1, prm.b.ye);
+    const int nsteps = (j1 - j0 + 1) + 4;            // raw rows j0-2 .. j1+2
+    const int nchunks = (nsteps + RY - 1) / RY;
+    const int i_first = prm.b.xs + blockIdx.x * Cfg::OUT;   // first output column of this CTA
+    // lane column (both stages): i_first + 30*warp + lane - 2
+    const int x_box = (i_first - 4) & ~1;   // even 0-based column at/below stage A lane 0's west neighbour
+    const int x_old = (i_first - 3) & ~1;   // even 0-based column at/below stage A lane 0's own column
+
+    auto issue = [&](int c) {
+        const int s = c % STAGES;
+        unsigned char *st = fused_smem + s * Cfg::STAGE_BYTES;
+        const int y_raw = (j0 - 2) + c * RY - 1;
+        const int y_old = y_raw - 1;
+        mbar_expect_tx(&full[s], Cfg::TX_BYTES);
+        tma_load_2d(st + 0 * Cfg::A, &tm_p, x_box, y_raw, &full[s]);
+        tma_load_2d(st + 1 * Cfg::A, &tm_u, x_box, y_raw, &full[s]);
+        tma_load_2d(st + 2 * Cfg::A, &tm_v, x_box, y_raw, &full[s]);
+        tma_load_2d(st + Cfg::OFF_OLD + 0 * Cfg::AO, &tm_uo, x_old, y_old, &full[s]);
+        tma_load_2d(st + Cfg::OFF_OLD + 1 * Cfg::AO, &tm_vo, x_old, y_old, &full[s]);
+        tma_load_2d(st + Cfg::OFF_OLD + 2 * Cfg::AO, &tm_po, x_old, y_old, &full[s]);
+    };
+    if (tid == 0) {
+        if (smem_u32(fused_smem) & 127u) __trap();
+        for (int s = 0; s < STAGES; ++s) mbar_init(&full[s], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        for (int c = 0; c < STAGES && c < nchunks; ++c) issue(c);
+    }
+    // exchange columns no stage-A lane writes (index 0, 1, VA+2, VA+3): finite values
+    for (int q = tid; q < 2 * 3 * RY * 4; q += TX) {
+        const int row = q >> 2, k4 = q & 3;
+        double *xr = reinterpret_cast<double *>(fused_smem + Cfg::OFF_X) + row * XW;
+        xr[k4 < 2 ? k4 : Cfg::VA + k4] = 1.0;
+    }
+    __syncthreads();
+
+    const int base = 30 * warp + lane;
+    const int i = i_first + base - 2;                 // this lane's column
+    // lanes 0 and 31 only feed their neighbours; the CTA's first and last intermediate columns
+    // (i_first - 1, i_first + OUT) have no valid neighbour on one side in stage B
+    const bool a_writes = lane >= 1 && lane <= 30;
+    const bool active = a_writes && i >= i_first && i < i_first + Cfg::OUT && i <= prm.b.xe;
+    const int xo = base + 1;                          // exchange index of this lane's column
+    const int col = base + ((i_first - 4) & 1);       // west neighbour inside the raw tile
+    const int colo = base + ((i_first - 3) & 1);      // own column inside the old tile
+    const SwScalars sc = prm.sc;
+    CarryS ca, cb;
+    carry_init(ca);
+    carry_init(cb);
+    double uo1 = 0.0, vo1 = 0.0, po1 = 0.0;
+    long long qo = (static_cast<long long>(j0) - 5) * prm.pitch + (i - 1);
+    const long long pitch = prm.pitch;
+    int t_lo = active ? 4 : (1 << 30), t_hi = nsteps;
+    for (int c = 0; c < nchunks; ++c) {
+        const int s = c % STAGES;
+        mbar_wait(&full[s], (c / STAGES) & 1);
+        const unsigned char *st = fused_smem + s * Cfg::STAGE_BYTES;
+        const double *sp = reinterpret_cast<const double *>(st + 0 * Cfg::A) + col;
+        const double *su = reinterpret_cast<const double *>(st + 1 * Cfg::A) + col;
+        const double *sv = reinterpret_cast<const double *>(st + 2 * Cfg::A) + col;
+        const double *suo = reinterpret_cast<const double *>(st + Cfg::OFF_OLD + 0 * Cfg::AO) + colo;
+        const double *svo = reinterpret_cast<const double *>(st + Cfg::OFF_OLD + 1 * Cfg::AO) + colo;
+        const double *spo = reinterpret_cast<const double *>(st + Cfg::OFF_OLD + 2 * Cfg::AO) + colo;
+        double *xb = reinterpret_cast<double *>(fused_smem + Cfg::OFF_X + (c & 1) * Cfg::XBUF_BYTES) + xo;
+        double uo_r[RY], vo_r[RY], po_r[RY];
+#pragma unroll
+        for (int r = 0; r < RY; ++r) {
+            RawS N;
+            N.pW = sp[r * BW]; N.pC = sp[r * BW + 1];
+            N.uC = su[r * BW + 1]; N.uE = su[r * BW + 2];
+            N.vW = sv[r * BW]; N.vC = sv[r * BW + 1];
+            Outs o;
+            ingest_sh(ca, N, sc, suo[r * BWO], svo[r * BWO], spo[r * BWO], o);
+            if (a_writes) {
+                xb[(0 * RY + r) * XW] = o.unew;
+                xb[(1 * RY + r) * XW] = o.vnew;
+                xb[(2 * RY + r) * XW] = o.pnew;
+            }
+            uo_r[r] = o.uold; vo_r[r] = o.vold; po_r[r] = o.pold;
+        }
+        __syncthreads();
+        if (tid == 0 && c + STAGES < nchunks) issue(c + STAGES);
+#pragma unroll
+        for (int r = 0; r < RY; ++r) {
+            RawS N;
+            N.uC = xb[(0 * RY + r) * XW]; N.uE = xb[(0 * RY + r) * XW + 1];
+            N.vW = xb[(1 * RY + r) * XW - 1]; N.vC = xb[(1 * RY + r) * XW];
+            N.pW = xb[(2 * RY + r) * XW - 1]; N.pC = xb[(2 * RY + r) * XW];
+            Outs o;
+            ingest_sh(cb, N, sc, uo1, vo1, po1, o);
+            uo1 = uo_r[r]; vo1 = vo_r[r]; po1 = po_r[r];
+            if (r >= t_lo && r < t_hi) {
+                __stcs(prm.u2 + qo, o.unew);
+                __stcs(prm.v2 + qo, o.vnew);
+                __stcs(prm.p2 + qo, o.pnew);
+                __stcs(prm.uold2 + qo, o.uold);
+                __stcs(prm.vold2 + qo, o.vold);
+                __stcs(prm.pold2 + qo, o.pold);
+            }
+            qo += pitch;
+        }
+        t_lo -= RY;
+        t_hi -= RY;
+    }
+}
+
+template <class Cfg, int RY, int MINB, class Kern>
+cudaError_t launch_tma2_generic(const Fused2Args &a, cudaStream_t s, Kern kern)
+{
     CUtensorMap mu, mv, mp, muo, mvo, mpo;
     if (!get_map(a.u, 8, a.pitch, a.ny, Cfg::BW, RY, mu) || !get_map(a.v, 8, a.pitch, a.ny, Cfg::BW, RY, mv) ||
         !get_map(a.p, 8, a.pitch, a.ny, Cfg::BW, RY, mp) || !get_map(a.uold, 8, a.pitch, a.ny, Cfg::BWO, RY, muo) ||
@@ -703,12 +893,11 @@ cudaError_t launch_tma2(const Fused2Args &a, cudaStream_t s)
         // every segment recomputes two rows of the intermediate state and re-reads four raw rows,
         // so segments are longer than the one-step sweep's; DLESM_SEG_ROWS2 overrides
         const char *e = std::getenv("DLESM_SEG_ROWS2");
-        const int v = e ? std::atoi(e) : 60;
-        return v < 8 ? 60 : v;
+        const int v = e ? std::atoi(e) : 124;
+        return v < 8 ? 124 : v;
     }();
     const int seg_rows = pick_seg_rows(w, h, Cfg::OUT, 148 * MINB, RY, target, 4);
     prm.pitch = a.pitch; prm.b = a.b; prm.seg_rows = seg_rows; prm.sc = a.sc;
-    auto kern = fused2_tma_kernel<TX, RY, STAGES, MINB>;
     static bool attr_done = false;
     if (!attr_done) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
@@ -718,6 +907,18 @@ cudaError_t launch_tma2(const Fused2Args &a, cudaStream_t s)
     dim3 grid((w + Cfg::OUT - 1) / Cfg::OUT, (h + seg_rows - 1) / seg_rows);
     kern<<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, s>>>(mu, mv, mp, muo, mvo, mpo, prm);
     return cudaGetLastError();
+}
+
+template <int TX, int RY, int STAGES, int MINB>
+cudaError_t launch_tma2(const Fused2Args &a, cudaStream_t s)
+{
+    return launch_tma2_generic<Tma2Cfg<TX, RY, STAGES>, RY, MINB>(a, s, fused2_tma_kernel<TX, RY, STAGES, MINB>);
+}
+
+template <int TX, int RY, int STAGES, int MINB>
+cudaError_t launch_tma2s(const Fused2Args &a, cudaStream_t s)
+{
+    return launch_tma2_generic<Tma2sCfg<TX, RY, STAGES>, RY, MINB>(a, s, fused2s_tma_kernel<TX, RY, STAGES, MINB>);
 }
 
 struct Tma2Variant {
@@ -735,6 +936,14 @@ const Tma2Variant kTma2Variants[] = {
     {5, "tma2-128x2x2-occ3", launch_tma2<128, 2, 2, 3>},
     {6, "tma2-128x8x2-occ1", launch_tma2<128, 8, 2, 1>},
     {7, "tma2-128x1x4-occ3", launch_tma2<128, 1, 4, 3>},
+    // ids >= 10: east / west intermediates through warp shuffles (118 output columns per CTA)
+    {10, "tma2s-128x4x2-occ2", launch_tma2s<128, 4, 2, 2>},
+    {11, "tma2s-128x4x3-occ2", launch_tma2s<128, 4, 3, 2>},
+    {12, "tma2s-128x2x3-occ3", launch_tma2s<128, 2, 3, 3>},
+    {13, "tma2s-128x2x4-occ2", launch_tma2s<128, 2, 4, 2>},
+    {14, "tma2s-128x4x2-occ3", launch_tma2s<128, 4, 2, 3>},
+    {15, "tma2s-256x4x2-occ1", launch_tma2s<256, 4, 2, 1>},
+    {16, "tma2s-256x2x3-occ1", launch_tma2s<256, 2, 3, 1>},
 };
 constexpr int kDefaultTma2Variant = 2;
 
