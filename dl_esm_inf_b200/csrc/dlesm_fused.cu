@@ -877,6 +877,141 @@ fused2s_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_consta
     }
 }
 
+// ---------------------------------------------------------------------------------------
+// Two steps per sweep, third form: warp-private.  ncu on the shuffle form showed 23 % of all
+// warp samples waiting at the per-chunk CTA barrier of the shared-memory exchange.  Here the
+// intermediate state crosses lanes by shuffle as well, so a warp depends on no other warp:
+// stage A row -> shuffle -> stage B row, interleaved row by row, no barrier, no exchange
+// buffer.  Lanes 2..29 store (28 columns per warp); a producer warp feeds the TMA ring as in the
+// one-step sweep.
+// ---------------------------------------------------------------------------------------
+template <int TX, int RY, int STAGES>
+struct Tma2wCfg {
+    static constexpr int NW = TX / 32;
+    static constexpr int OUT = 28 * NW;      // output columns per CTA
+    static constexpr int BW = 28 * NW + 8;   // raw tiles, even start column
+    static constexpr int BWO = 28 * NW + 6;  // old tiles, even start column
+    static constexpr int A = align128(BW * RY * 8);
+    static constexpr int AO = align128(BWO * RY * 8);
+    static constexpr int OFF_OLD = 3 * A;
+    static constexpr int STAGE_BYTES = 3 * A + 3 * AO;
+    static constexpr int TX_BYTES = 3 * BW * RY * 8 + 3 * BWO * RY * 8;
+    static constexpr int BAR_OFFSET = STAGES * STAGE_BYTES;
+    static constexpr int SMEM_BYTES = BAR_OFFSET + 2 * STAGES * 8;
+    static constexpr int THREADS = TX + 32;
+};
+
+template <int TX, int RY, int STAGES, int MINB>
+__global__ void __launch_bounds__(TX + 32, MINB)
+fused2w_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_constant__ CUtensorMap tm_v,
+                   const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUtensorMap tm_uo,
+                   const __grid_constant__ CUtensorMap tm_vo, const __grid_constant__ CUtensorMap tm_po,
+                   const __grid_constant__ Tma2Params prm)
+{
+    using Cfg = Tma2wCfg<TX, RY, STAGES>;
+    constexpr int BW = Cfg::BW, BWO = Cfg::BWO;
+    extern __shared__ __align__(1024) unsigned char fused_smem[];
+    uint64_t *full = reinterpret_cast<uint64_t *>(fused_smem + Cfg::BAR_OFFSET);
+    uint64_t *empty = full + STAGES;
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int j0 = prm.b.ys + blockIdx.y * prm.seg_rows;
+    const int j1 = min(j0 + prm.seg_rows - 1, prm.b.ye);
+    const int nsteps = (j1 - j0 + 1) + 4;            // raw rows j0-2 .. j1+2
+    const int nchunks = (nsteps + RY - 1) / RY;
+    const int i_first = prm.b.xs + blockIdx.x * Cfg::OUT;   // first output column of this CTA
+
+    if (tid == 0) {
+        if (smem_u32(fused_smem) & 127u) __trap();
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(&full[s], 1);
+            mbar_init(&empty[s], TX / 32);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    __syncthreads();
+
+    if (warp == TX / 32) {
+        if (lane == 0) {
+            const int x_box = (i_first - 4) & ~1;   // even 0-based column at/below lane 0's west neighbour
+            const int x_old = (i_first - 3) & ~1;   // even 0-based column at/below lane 0's own column
+            for (int c = 0; c < nchunks; ++c) {
+                const int s = c % STAGES;
+                if (c >= STAGES) mbar_wait(&empty[s], ((c / STAGES) - 1) & 1);
+                unsigned char *st = fused_smem + s * Cfg::STAGE_BYTES;
+                const int y_raw = (j0 - 2) + c * RY - 1;
+                const int y_old = y_raw - 1;
+                mbar_expect_tx(&full[s], Cfg::TX_BYTES);
+                tma_load_2d(st + 0 * Cfg::A, &tm_p, x_box, y_raw, &full[s]);
+                tma_load_2d(st + 1 * Cfg::A, &tm_u, x_box, y_raw, &full[s]);
+                tma_load_2d(st + 2 * Cfg::A, &tm_v, x_box, y_raw, &full[s]);
+                tma_load_2d(st + Cfg::OFF_OLD + 0 * Cfg::AO, &tm_uo, x_old, y_old, &full[s]);
+                tma_load_2d(st + Cfg::OFF_OLD + 1 * Cfg::AO, &tm_vo, x_old, y_old, &full[s]);
+                tma_load_2d(st + Cfg::OFF_OLD + 2 * Cfg::AO, &tm_po, x_old, y_old, &full[s]);
+            }
+        }
+        return;
+    }
+
+    // ---- consumer warps: lane column = i_first + 28*warp + lane - 2 in both stages ----
+    const int base = 28 * warp + lane;
+    const int i = i_first + base - 2;
+    const bool active = lane >= 2 && lane <= 29 && i <= prm.b.xe;
+    const int col = base + ((i_first - 4) & 1);       // west neighbour inside the raw tile
+    const int colo = base + ((i_first - 3) & 1);      // own column inside the old tile
+    const SwScalars sc = prm.sc;
+    CarryS ca, cb;
+    carry_init(ca);
+    carry_init(cb);
+    double uo1 = 0.0, vo1 = 0.0, po1 = 0.0;   // once-filtered old fields of the row stage B emits next
+    // raw step t ingests raw row j0-2+t; stage A emits row j0-3+t; stage B emits row j0-4+t
+    long long qo = (static_cast<long long>(j0) - 5) * prm.pitch + (i - 1);
+    const long long pitch = prm.pitch;
+    int t_lo = active ? 4 : (1 << 30), t_hi = nsteps;
+    for (int c = 0; c < nchunks; ++c) {
+        const int s = c % STAGES;
+        mbar_wait(&full[s], (c / STAGES) & 1);
+        const unsigned char *st = fused_smem + s * Cfg::STAGE_BYTES;
+        const double *sp = reinterpret_cast<const double *>(st + 0 * Cfg::A) + col;
+        const double *su = reinterpret_cast<const double *>(st + 1 * Cfg::A) + col;
+        const double *sv = reinterpret_cast<const double *>(st + 2 * Cfg::A) + col;
+        const double *suo = reinterpret_cast<const double *>(st + Cfg::OFF_OLD + 0 * Cfg::AO) + colo;
+        const double *svo = reinterpret_cast<const double *>(st + Cfg::OFF_OLD + 1 * Cfg::AO) + colo;
+        const double *spo = reinterpret_cast<const double *>(st + Cfg::OFF_OLD + 2 * Cfg::AO) + colo;
+#pragma unroll
+        for (int r = 0; r < RY; ++r) {
+            RawS N;
+            N.pW = sp[r * BW]; N.pC = sp[r * BW + 1];
+            N.uC = su[r * BW + 1]; N.uE = su[r * BW + 2];
+            N.vW = sv[r * BW]; N.vC = sv[r * BW + 1];
+            Outs oa;
+            ingest_sh(ca, N, sc, suo[r * BWO], svo[r * BWO], spo[r * BWO], oa);
+            RawS M;   // the intermediate state's row, neighbours by shuffle (valid on lanes 1..30)
+            M.uC = oa.unew; M.vC = oa.vnew; M.pC = oa.pnew;
+            M.uE = __shfl_down_sync(0xffffffffu, oa.unew, 1);
+            M.vW = __shfl_up_sync(0xffffffffu, oa.vnew, 1);
+            M.pW = __shfl_up_sync(0xffffffffu, oa.pnew, 1);
+            Outs ob;
+            ingest_sh(cb, M, sc, uo1, vo1, po1, ob);
+            uo1 = oa.uold; vo1 = oa.vold; po1 = oa.pold;
+            if (r >= t_lo && r < t_hi) {
+                __stcs(prm.u2 + qo, ob.unew);
+                __stcs(prm.v2 + qo, ob.vnew);
+                __stcs(prm.p2 + qo, ob.pnew);
+                __stcs(prm.uold2 + qo, ob.uold);
+                __stcs(prm.vold2 + qo, ob.vold);
+                __stcs(prm.pold2 + qo, ob.pold);
+            }
+            qo += pitch;
+        }
+        t_lo -= RY;
+        t_hi -= RY;
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty[s]);
+    }
+}
+
 template <class Cfg, int RY, int MINB, class Kern>
 cudaError_t launch_tma2_generic(const Fused2Args &a, cudaStream_t s, Kern kern)
 {
@@ -921,6 +1056,12 @@ cudaError_t launch_tma2s(const Fused2Args &a, cudaStream_t s)
     return launch_tma2_generic<Tma2sCfg<TX, RY, STAGES>, RY, MINB>(a, s, fused2s_tma_kernel<TX, RY, STAGES, MINB>);
 }
 
+template <int TX, int RY, int STAGES, int MINB>
+cudaError_t launch_tma2w(const Fused2Args &a, cudaStream_t s)
+{
+    return launch_tma2_generic<Tma2wCfg<TX, RY, STAGES>, RY, MINB>(a, s, fused2w_tma_kernel<TX, RY, STAGES, MINB>);
+}
+
 struct Tma2Variant {
     int id;
     const char *name;
@@ -944,8 +1085,16 @@ const Tma2Variant kTma2Variants[] = {
     {14, "tma2s-128x4x2-occ3", launch_tma2s<128, 4, 2, 3>},
     {15, "tma2s-256x4x2-occ1", launch_tma2s<256, 4, 2, 1>},
     {16, "tma2s-256x2x3-occ1", launch_tma2s<256, 2, 3, 1>},
+    // ids >= 20: warp-private (all neighbour data by shuffle, no CTA barrier; 28 columns per warp)
+    {20, "tma2w-128x4x3-occ2", launch_tma2w<128, 4, 3, 2>},
+    {21, "tma2w-128x4x2-occ2", launch_tma2w<128, 4, 2, 2>},
+    {22, "tma2w-128x2x4-occ2", launch_tma2w<128, 2, 4, 2>},
+    {23, "tma2w-256x4x3-occ1", launch_tma2w<256, 4, 3, 1>},
+    {24, "tma2w-128x8x2-occ2", launch_tma2w<128, 8, 2, 2>},
+    {25, "tma2w-64x4x3-occ4", launch_tma2w<64, 4, 3, 4>},
+    {26, "tma2w-96x4x3-occ3", launch_tma2w<96, 4, 3, 3>},
 };
-constexpr int kDefaultTma2Variant = 2;
+constexpr int kDefaultTma2Variant = 10;
 
 }  // namespace
 

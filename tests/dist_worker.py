@@ -290,20 +290,27 @@ def case_gather():
         ok(np.array_equal(recv, want), "gather differs")
 
 
-def case_shallow_water(n_x, n_y, nsteps, alignment, mode, halo_mode=None):
+def case_shallow_water(n_x, n_y, nsteps, alignment, mode, halo_mode=None, two_step=False):
     """periodic shallow water across ranks (extension F4) == the serial oracle, bit for bit;
     halo_mode HALO_PUSH: the fused sweep stores the neighbours' halo cells itself (NVLink peer
     memory + flag hand-shake) instead of pack -> NCCL -> unpack"""
     os.environ["DL_ESM_ALIGNMENT"] = str(alignment)
-    fd.set_extensions(fd.EXT_PERIODIC_DISTMEM)
+    fd.set_extensions(fd.EXT_PERIODIC_DISTMEM | (fd.EXT_HALO_DEPTH if two_step else 0))
     osw = O.ShallowWater(n_x, n_y, alignment=1)
     init = {k: osw.f[k].copy(order="F") for k in ("u", "v", "p")}
     for _ in range(nsteps):
         osw.step()
     g = fd.grid_type(fd.GO_ARAKAWA_C, BCS_PER, fd.GO_OFFSET_SW)
-    g.decompose(n_x, n_y)
+    if two_step:
+        # two model steps per sweep: tiles with two halo cells, halo_exchange(depth 2) of the six
+        # prognostic fields every second step (both extensions)
+        g.decompose(n_x, n_y, halo_width=2)
+    else:
+        g.decompose(n_x, n_y)
     fd.grid_init(g, 1.0e5, 1.0e5)
     sw = fd.shallow_water(g, mode=mode)
+    if two_step:
+        sw.set_two_step(True)
     # this tile's part of the oracle's initial state, halo ring included (periodic wrap)
     sub = g.subdomain
     li = sub.internal
@@ -335,6 +342,8 @@ def case_shallow_water(n_x, n_y, nsteps, alignment, mode, halo_mode=None):
     sw.free()
     fd.set_extensions(0)
     os.environ.pop("DL_ESM_ALIGNMENT", None)
+    if two_step:
+        fd.gocean_initialise(RANK + 1, WORLD)       # resets go_decompose's SAVEd halo width to 1
 
 
 def main():
@@ -358,6 +367,8 @@ def main():
     case_nemolite2d(257, 300, 3, 8)
     for shape in ((64, 96, 5, 2), (130, 77, 4, 64), (300, 523, 7, 64), (1024, 1024, 6, 64)):
         case_shallow_water(*shape, fd.SW_FUSED, halo_mode=fd.HALO_PUSH)
+    for shape in ((64, 96, 6, 2), (130, 77, 7, 64), (300, 523, 8, 64), (1024, 1024, 9, 64)):
+        case_shallow_water(*shape, fd.SW_FUSED, two_step=True)
     dist.barrier()
     fd.gocean_finalise()
     if RANK == 0:

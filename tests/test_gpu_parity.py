@@ -679,7 +679,7 @@ def assert_internal_equal(osw, sw, halo=0):
             raise AssertionError("%s differs at %d points, first %s" % (n, len(bad), tuple(bad[0])))
 
 
-TWO_STEP_VARIANTS = [1, 2, 3, 4, 5, 6, 7, 10, 11, 12, 13, 14, 15, 16]
+TWO_STEP_VARIANTS = [1, 2, 3, 4, 5, 6, 7, 10, 11, 12, 13, 14, 15, 16, 20, 21, 22, 23, 24, 25, 26]
 
 
 @pytest.mark.parametrize("variant2", TWO_STEP_VARIANTS)
