@@ -184,112 +184,154 @@ def run_ours(args):
             dist.barrier()
             torch.cuda.synchronize()
 
-    # weak scaling: args.size^2 points per GPU; strong: args.size^2 points in total (configs[3]
-    # names both).  The tile grid is go_decompose's own choice either way.
-    n = args.size
-    probe = fd.go_decompose(n, n)                       # tile grid for `world` ranks on a square domain
-    if args.scaling == "strong":
-        gx, gy = n, n
-    else:
-        gx, gy = n * probe.nx, n * probe.ny
-    bcs = (fd.GO_BC_PERIODIC, fd.GO_BC_PERIODIC, fd.GO_BC_NONE)
-    grid = fd.grid_type(fd.GO_ARAKAWA_C, bcs, fd.GO_OFFSET_SW)
-    if args.two_step:
-        fd.set_extensions(fd.EXT_PERIODIC_DISTMEM | fd.EXT_HALO_DEPTH if world > 1 else 0)
-        grid.decompose(gx, gy, halo_width=2)      # the two-step sweep needs two halo cells
-    else:
-        grid.decompose(gx, gy)
-    fd.grid_init(grid, 1.0e5, 1.0e5)
-    sub = grid.subdomain
-    local_points = sub.internal.nx * sub.internal.ny
-    total_points = gx * gy
-
-    sw = fd.shallow_water(grid, dt=90.0, alpha=0.001, mode=fd.SW_FUSED if args.mode == "fused" else fd.SW_UNFUSED)
-    sw.set_variant(args.variant)
-    if args.two_step:
-        sw.set_two_step(True, args.variant2)
-    sw.init_device()
-    halo = args.halo
-    if halo == "auto":
-        halo = "push" if (world > 1 and args.mode == "fused" and not args.two_step) else "exchange"
-    if halo == "push":
-        sw.set_halo_mode(fd.HALO_PUSH)              # collective: maps the neighbours' arrays (NVLink peer memory)
-    mass0 = fd.field_checksum(sw.field("p"))
-
     sampler = ClockSampler(local_rank)
     sampler.start()
-    sw.step(max(args.warmup, 3))
-    L.dlesm_profile_enable(1)
-    L.dlesm_profile_read(None, None, 1)
-    barrier()
-    launches0 = fd.kernel_launch_count()
-    t_wall0 = time.time()
-    L.dlesm_event_record(0)
-    sw.step(args.steps)
-    L.dlesm_event_record(1)
-    ms = C.c_double(0.0)
-    assert L.dlesm_event_elapsed_ms(0, 1, C.byref(ms)) == 0
-    barrier()
-    t_wall1 = time.time()
-    launches = fd.kernel_launch_count() - launches0
-    kms, kn = C.c_double(0.0), C.c_longlong(0)
-    L.dlesm_profile_read(C.byref(kms), C.byref(kn), 1)
-    L.dlesm_profile_enable(0)
-    clocks = sampler.summary(t_wall0, t_wall1)
 
-    elapsed_ms = ms.value
-    if dist is not None:
-        t = torch.tensor([elapsed_ms], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        elapsed_ms = float(t.item())
-    value = total_points * args.steps / (elapsed_ms * 1e-3)
+    def timed(two_step, run=True):
+        """one timed run of K steps: the one-step sweep (96 B/point per step) or the two-step sweep
+        (temporal blocking: 96 B/point per TWO steps, tiles with halo width 2)"""
+        # weak scaling: args.size^2 points per GPU; strong: args.size^2 points in total (configs[3]
+        # names both).  The tile grid is go_decompose's own choice either way.
+        n = args.size
+        probe = fd.go_decompose(n, n)                       # tile grid for `world` ranks on a square domain
+        if args.scaling == "strong":
+            gx, gy = n, n
+        else:
+            gx, gy = n * probe.nx, n * probe.ny
+        bcs = (fd.GO_BC_PERIODIC, fd.GO_BC_PERIODIC, fd.GO_BC_NONE)
+        grid = fd.grid_type(fd.GO_ARAKAWA_C, bcs, fd.GO_OFFSET_SW)
+        if two_step:
+            fd.set_extensions(fd.EXT_PERIODIC_DISTMEM | fd.EXT_HALO_DEPTH if world > 1 else 0)
+            grid.decompose(gx, gy, halo_width=2)      # the two-step sweep needs two halo cells
+        else:
+            grid.decompose(gx, gy)
+        fd.grid_init(grid, 1.0e5, 1.0e5)
+        sub = grid.subdomain
+        local_points = sub.internal.nx * sub.internal.ny
+        total_points = gx * gy
 
-    # parity guards on the timed state: mass conservation and finite checksums
-    cks = sw.checksums()
-    mass1 = cks[0]
-    assert all(np.isfinite(c) for c in cks), cks
-    assert abs(mass1 - mass0) <= 1e-11 * abs(mass0), (mass0, mass1)
+        sw = fd.shallow_water(grid, dt=90.0, alpha=0.001, mode=fd.SW_FUSED if args.mode == "fused" else fd.SW_UNFUSED)
+        sw.set_variant(args.variant)
+        if two_step:
+            sw.set_two_step(True, args.variant2)
+        sw.init_device()
+        halo = args.halo
+        if halo == "auto":
+            halo = "push" if (world > 1 and args.mode == "fused" and not two_step) else "exchange"
+        if halo == "push":
+            sw.set_halo_mode(fd.HALO_PUSH)              # collective: maps the neighbours' arrays (NVLink peer memory)
+        if not run:                                      # set-up only (the e2e leg's one-step tile)
+            return dict(sw=sw, grid=grid, total_points=total_points)
+        mass0 = fd.field_checksum(sw.field("p"))
 
-    # ---- roofline of the dominant kernel (fused sweep), timed live with CUDA events ----
-    peak, peak_src = measured_hbm_peak()
-    roofline = None
-    if kn.value > 0:
-        k_ms = kms.value / kn.value
-        steps_per_launch = args.steps / kn.value          # 2 with --two-step (temporal blocking)
-        achieved = BYTES_PER_POINT * local_points * steps_per_launch / (k_ms * 1e-3) / 1e9
-        roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                    "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                    "kernel": "fused shallow-water sweep (variant %d)" % args.variant,
-                    "kernel_ms": k_ms, "kernel_share_of_step": kms.value / elapsed_ms,
-                    "algorithmic_bytes_per_launch": BYTES_PER_POINT * local_points * steps_per_launch,
-                    "steps_per_launch": steps_per_launch,
-                    "frac_of_nominal_8TBs": achieved / 8000.0}
-        prof = os.path.join(ROOT, "profiles", "fused_traffic.json")
-        try:
-            with open(prof) as fh:
-                roofline["traffic"] = json.load(fh).get(
-                    "dram_bytes_per_launch_two_step" if args.two_step else "dram_bytes_per_launch")
-        except Exception:
-            pass
+        sw.step(max(args.warmup, 3))
+        L.dlesm_profile_enable(1)
+        L.dlesm_profile_read(None, None, 1)
+        barrier()
+        launches0 = fd.kernel_launch_count()
+        t_wall0 = time.time()
+        L.dlesm_event_record(0)
+        sw.step(args.steps)
+        L.dlesm_event_record(1)
+        ms = C.c_double(0.0)
+        assert L.dlesm_event_elapsed_ms(0, 1, C.byref(ms)) == 0
+        barrier()
+        t_wall1 = time.time()
+        launches = fd.kernel_launch_count() - launches0
+        kms, kn = C.c_double(0.0), C.c_longlong(0)
+        L.dlesm_profile_read(C.byref(kms), C.byref(kn), 1)
+        L.dlesm_profile_enable(0)
+        clocks = sampler.summary(t_wall0, t_wall1)
 
-    # ---- halo traffic of one step against NVLink (north_star: "halo traffic also as a fraction of
-    # NVLink bandwidth"): the map_comms send/recv lists of this rank x the three new fields ----
-    halo_traffic = None
-    if world > 1:
-        cm = grid.comms
-        sent = sum(cm.nxsend[q] * cm.nysend[q] for q in range(cm.nsend)
-                   if cm.destination[q] != rank) * 8 * 3
-        recv = sum(cm.nxrecv[q] * cm.nyrecv[q] for q in range(cm.nrecv)
-                   if cm.source[q] != rank) * 8 * 3
-        step_s = elapsed_ms * 1e-3 / args.steps
-        halo_traffic = {"sent_bytes_per_rank_per_step": sent, "recv_bytes_per_rank_per_step": recv,
-                        "messages_per_rank_per_step": int(cm.nsend),
-                        "nvlink_peak_GBs_both_directions": 1800.0,
-                        "nvlink_frac_of_step": (sent + recv) / step_s / 1.8e12,
-                        "step_minus_sweep_us": (elapsed_ms - kms.value) / args.steps * 1e3}
+        elapsed_ms = ms.value
+        if dist is not None:
+            t = torch.tensor([elapsed_ms], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            elapsed_ms = float(t.item())
+        value = total_points * args.steps / (elapsed_ms * 1e-3)
 
-    # ---- e2e: the same step driven with HOST buffers through the field hooks ----
-    e2e = run_e2e(args, fd, L, sw, grid, total_points, dist, torch) if args.e2e_steps > 0 else None
+        # parity guards on the timed state: mass conservation and finite checksums
+        cks = sw.checksums()
+        mass1 = cks[0]
+        assert all(np.isfinite(c) for c in cks), cks
+        assert abs(mass1 - mass0) <= 1e-11 * abs(mass0), (mass0, mass1)
+
+        # ---- roofline of the dominant kernel (fused sweep), timed live with CUDA events ----
+        peak, peak_src = measured_hbm_peak()
+        roofline = None
+        if kn.value > 0:
+            k_ms = kms.value / kn.value
+            steps_per_launch = args.steps / kn.value          # 2 with --two-step (temporal blocking)
+            achieved = BYTES_PER_POINT * local_points * steps_per_launch / (k_ms * 1e-3) / 1e9
+            roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                        "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                        "kernel": ("two-step fused shallow-water sweep (variant2 %d)" % args.variant2) if two_step
+                              else ("fused shallow-water sweep (variant %d)" % args.variant),
+                        "kernel_ms": k_ms, "kernel_share_of_step": kms.value / elapsed_ms,
+                        "algorithmic_bytes_per_launch": BYTES_PER_POINT * local_points * steps_per_launch,
+                        "steps_per_launch": steps_per_launch,
+                        "frac_of_nominal_8TBs": achieved / 8000.0}
+            if two_step:
+                # a two-step launch moves the state through HBM once for two steps: its own DRAM minimum
+                # is 96 B/point per LAUNCH, so `frac` (algorithmic bytes of both steps / time) exceeds 1;
+                # the kernel itself is bound by the FP64 pipe under the power cap, not by HBM
+                roofline["frac_of_hbm_on_kernel_dram_minimum"] = achieved / steps_per_launch / peak
+                roofline["note"] = ("temporal blocking: 2 model steps per launch for one pass over the state "
+                                    "(96 B/point per launch); frac > 1 against the per-step byte model means the "
+                                    "intermediate state never reached HBM; ncu: FP64 pipe is the busiest unit")
+            prof = os.path.join(ROOT, "profiles", "fused_traffic.json")
+            try:
+                with open(prof) as fh:
+                    roofline["traffic"] = json.load(fh).get(
+                        "dram_bytes_per_launch_two_step" if two_step else "dram_bytes_per_launch")
+            except Exception:
+                pass
+
+        # ---- halo traffic of one step against NVLink (north_star: "halo traffic also as a fraction of
+        # NVLink bandwidth"): the map_comms send/recv lists of this rank x the three new fields ----
+        halo_traffic = None
+        if world > 1:
+            # one-step: depth-1 lists x 3 new fields every step; two-step: depth-2 lists x 6 fields
+            # (u,v,p and the filtered old fields) every second step
+            cm = fd.map_comms(grid.decomp, pbc=(True, True), halo_depths=(2, 2)) if two_step else grid.comms
+            per_step = 8 * 6 / 2.0 if two_step else 8 * 3
+            sent = sum(cm.nxsend[q] * cm.nysend[q] for q in range(cm.nsend)
+                       if cm.destination[q] != rank) * per_step
+            recv = sum(cm.nxrecv[q] * cm.nyrecv[q] for q in range(cm.nrecv)
+                       if cm.source[q] != rank) * per_step
+            step_s = elapsed_ms * 1e-3 / args.steps
+            halo_traffic = {"sent_bytes_per_rank_per_step": sent, "recv_bytes_per_rank_per_step": recv,
+                            "messages_per_rank_per_step": int(cm.nsend),
+                            "nvlink_peak_GBs_both_directions": 1800.0,
+                            "nvlink_frac_of_step": (sent + recv) / step_s / 1.8e12,
+                            "step_minus_sweep_us": (elapsed_ms - kms.value) / args.steps * 1e3}
+
+        return dict(value=value, elapsed_ms=elapsed_ms, roofline=roofline, clocks=clocks, launches=int(launches),
+                    cks=cks, halo_traffic=halo_traffic, halo=halo, grid=grid, sw=sw, probe=probe, sub=sub, gx=gx,
+                    gy=gy, local_points=local_points, total_points=total_points, two_step=two_step)
+
+    sweep = "two" if args.two_step else args.sweep
+    if args.mode != "fused" or args.halo == "push":
+        sweep = "one"                                # the two-step sweep is a fused-mode, exchange-halo path
+    one = two = None
+    if sweep in ("one", "both"):
+        one = timed(False)
+    main = one
+    # ---- e2e: the same step driven with HOST buffers through the field hooks (one-step tile) ----
+    e2e = None
+    if args.e2e_steps > 0:
+        src = one if one is not None else timed(False, run=False)
+        e2e = run_e2e(args, fd, L, src["sw"], src["grid"], src["total_points"], dist, torch)
+        if one is None:
+            src["sw"].free()
+    if one is not None:
+        one["sw"].free()
+        one["sw"] = None
+    if sweep in ("two", "both"):
+        two = timed(True)
+        two["sw"].free()
+        two["sw"] = None
+        main = two
     sampler.stop_flag = True
 
     # ---- cpu baseline (rank 0, N=1 only): bounded sample on the box's host cores ----
@@ -305,26 +347,48 @@ def run_ours(args):
         cpu["serial_fd_lib_1core_1024sq"] = c1
 
     if rank == 0:
+        peak, _ = measured_hbm_peak()
+        R = main
+        sub, probe, grid = R["sub"], R["probe"], R["grid"]
+
+        def halo_text(r):
+            if r["two_step"]:
+                return ("periodic halo kernel, two cells deep, every second step" if world == 1 else
+                        "halo_exchange(depth 2) of six fields every second step: pack -> NCCL send/recv -> unpack")
+            if r["halo"] == "push":
+                return ("push: the fused sweep stores the neighbours' halo cells over NVLink peer memory, "
+                        "flag hand-shake per step")
+            return "periodic halo kernel" if world == 1 else "pack -> NCCL send/recv -> unpack"
+
         line = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": max(args.warmup, 3), "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True,
+            "metric": METRIC, "value": R["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": R["elapsed_ms"] / args.steps, "higher_is_better": True,
             "scaling": args.scaling, "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": "shallow-water C-grid step %dx%d per GPU (global %dx%d, tiles %dx%d), "
                                    "double periodic, GO_OFFSET_SW, FP64, DL_ESM_ALIGNMENT=%d, mode=%s"
-                                   % (sub.internal.nx, sub.internal.ny, gx, gy, probe.nx, probe.ny,
+                                   % (sub.internal.nx, sub.internal.ny, R["gx"], R["gy"], probe.nx, probe.ny,
                                       args.alignment, args.mode),
-                       "l2": "inputs larger than L2 (9 fields x %.2f GB per GPU)" % (grid.nx * grid.ny * 8 / 1e9),
-                       "fused_variant": args.variant, "two_step": bool(args.two_step), "parallelism": "tile-per-GPU %dx%d" % (probe.nx, probe.ny),
-                       "halo": ("push: the fused sweep stores the neighbours' halo cells over NVLink peer memory, "
-                                "flag hand-shake per step" if halo == "push" else
-                                ("periodic halo kernel" if world == 1 else "pack -> NCCL send/recv -> unpack"))},
-            "clocks": clocks, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
-            "e2e": e2e, "halo_traffic": halo_traffic, "checksums_p_u_v": list(cks),
-            "hbm_frac_of_measured_whole_step": (BYTES_PER_POINT * local_points * args.steps /
-                                                (elapsed_ms * 1e-3) / 1e9) / peak,
+                       "l2": "inputs larger than L2 (%d fields x %.2f GB per GPU)"
+                             % (12 if R["two_step"] else 9, grid.nx * grid.ny * 8 / 1e9),
+                       "fused_variant": args.variant,
+                       "sweep": ("two model steps per sweep (temporal blocking, halo width 2, variant2 %d): the "
+                                 "intermediate state never reaches HBM; bit-identical to stepping one at a time"
+                                 % args.variant2) if R["two_step"] else "one model step per sweep",
+                       "parallelism": "tile-per-GPU %dx%d" % (probe.nx, probe.ny),
+                       "halo": halo_text(R)},
+            "clocks": R["clocks"], "gpu_launches": R["launches"], "roofline": R["roofline"], "cpu_baseline": cpu,
+            "e2e": e2e, "halo_traffic": R["halo_traffic"], "checksums_p_u_v": list(R["cks"]),
+            "hbm_frac_of_measured_whole_step": (BYTES_PER_POINT * R["local_points"] * args.steps /
+                                                (R["elapsed_ms"] * 1e-3) / 1e9) / peak,
         }
+        if R["two_step"] and one is not None:
+            # the one-step formulation (the reference's: every step reads and writes the state once),
+            # measured in the same process just before
+            line["one_step"] = {"value": one["value"], "ms_per_step": one["elapsed_ms"] / args.steps,
+                                "roofline": one["roofline"], "clocks": one["clocks"],
+                                "gpu_launches": one["launches"], "halo": halo_text(one),
+                                "halo_traffic": one["halo_traffic"], "checksums_p_u_v": list(one["cks"])}
         print(json.dumps(line), flush=True)
-    sw.free()
     if dist is not None:
         dist.barrier()
         fd.gocean_finalise()
@@ -425,6 +489,10 @@ def main():
     ap.add_argument("--scaling", choices=["weak", "strong"], default="weak",
                     help="weak: --size^2 points per GPU (default, the metric's configuration); "
                          "strong: --size^2 points in total, split by go_decompose")
+    ap.add_argument("--sweep", choices=["one", "two", "both"], default="both",
+                    help="one: one model step per sweep (96 B/point/step); two: two steps per sweep (temporal "
+                         "blocking); both (default): measure one, then two, report two as `value` and one "
+                         "under `one_step`")
     ap.add_argument("--two-step", action="store_true",
                     help="two model steps per sweep (temporal blocking; tile decomposed with halo_width=2)")
     ap.add_argument("--variant2", type=int, default=0, help="kernel variant of the two-step sweep")
