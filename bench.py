@@ -217,7 +217,7 @@ def run_ours(args):
         sw.init_device()
         halo = args.halo
         if halo == "auto":
-            halo = "push" if (world > 1 and args.mode == "fused" and not two_step) else "exchange"
+            halo = "push" if (world > 1 and args.mode == "fused") else "exchange"
         if halo == "push":
             sw.set_halo_mode(fd.HALO_PUSH)              # collective: maps the neighbours' arrays (NVLink peer memory)
         if not run:                                      # set-up only (the e2e leg's one-step tile)
@@ -311,8 +311,8 @@ def run_ours(args):
                     gy=gy, local_points=local_points, total_points=total_points, two_step=two_step)
 
     sweep = "two" if args.two_step else args.sweep
-    if args.mode != "fused" or args.halo == "push":
-        sweep = "one"                                # the two-step sweep is a fused-mode, exchange-halo path
+    if args.mode != "fused":
+        sweep = "one"                                # the two-step sweep is a fused-mode path
     one = two = None
     if sweep in ("one", "both"):
         one = timed(False)
@@ -352,6 +352,9 @@ def run_ours(args):
         sub, probe, grid = R["sub"], R["probe"], R["grid"]
 
         def halo_text(r):
+            if r["two_step"] and r["halo"] == "push":
+                return ("push: the two-step sweep stores the neighbours' halo cells of its six outputs, two cells "
+                        "deep, over NVLink peer memory; flag hand-shake per sweep")
             if r["two_step"]:
                 return ("periodic halo kernel, two cells deep, every second step" if world == 1 else
                         "halo_exchange(depth 2) of six fields every second step: pack -> NCCL send/recv -> unpack")

@@ -547,7 +547,25 @@ struct Tma2Params {
     Box b;
     int seg_rows;
     SwScalars sc;
+    PushPlan2 push;
 };
+
+// edge outputs of row j, column i -> the neighbours' halo cells, two cells deep (rare path)
+__device__ __noinline__ void push_row2(const PushPlan2 &pp, unsigned mask, int i, int j, const Outs &o)
+{
+    for (unsigned m = mask; m; m &= m - 1) {
+        const PushSeg2 &g = pp.seg[__ffs(m) - 1];
+        if (j >= g.j0 && j <= g.j1) {
+            const size_t d = idx(g.dpitch, g.ides + (i - g.i0), g.jdes + (j - g.j0));
+            g.dst[0][d] = o.unew;
+            g.dst[1][d] = o.vnew;
+            g.dst[2][d] = o.pnew;
+            g.dst[3][d] = o.uold;
+            g.dst[4][d] = o.vold;
+            g.dst[5][d] = o.pold;
+        }
+    }
+}
 
 template <int TX, int RY, int STAGES>
 struct Tma2Cfg {
@@ -824,6 +842,14 @@ fused2s_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_consta
     long long qo = (static_cast<long long>(j0) - 5) * prm.pitch + (i - 1);
     const long long pitch = prm.pitch;
     int t_lo = active ? 4 : (1 << 30), t_hi = nsteps;
+    // push boxes this lane's column and this CTA's rows can meet (0 for almost every thread)
+    unsigned pmask = 0;
+    if (active)
+        for (int q = 0; q < prm.push.n; ++q) {
+            const PushSeg2 &g = prm.push.seg[q];
+            if (i >= g.i0 && i <= g.i1 && g.j1 >= j0 && g.j0 <= j1) pmask |= 1u << q;
+        }
+    int jrow = j0 - 4;
     for (int c = 0; c < nchunks; ++c) {
         const int s = c % STAGES;
         mbar_wait(&full[s], (c / STAGES) & 1);
@@ -869,8 +895,10 @@ fused2s_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_consta
                 __stcs(prm.uold2 + qo, o.uold);
                 __stcs(prm.vold2 + qo, o.vold);
                 __stcs(prm.pold2 + qo, o.pold);
+                if (pmask) push_row2(prm.push, pmask, i, jrow, o);
             }
             qo += pitch;
+            ++jrow;
         }
         t_lo -= RY;
         t_hi -= RY;
@@ -1033,6 +1061,7 @@ cudaError_t launch_tma2_generic(const Fused2Args &a, cudaStream_t s, Kern kern)
     }();
     const int seg_rows = pick_seg_rows(w, h, Cfg::OUT, 148 * MINB, RY, target, 4);
     prm.pitch = a.pitch; prm.b = a.b; prm.seg_rows = seg_rows; prm.sc = a.sc;
+    prm.push = a.push;
     static bool attr_done = false;
     if (!attr_done) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
@@ -1104,10 +1133,13 @@ bool fused2_supported(const Fused2Args &a)
            a.b.ye + 2 <= a.ny && !a.sc.first;
 }
 
+bool fused2_push_supported(int variant) { return variant == 0 || (variant >= 10 && variant < 20); }
+
 cudaError_t sw_step2_fused(const Fused2Args &a, int variant, cudaStream_t s)
 {
     if (a.b.xe < a.b.xs || a.b.ye < a.b.ys) return cudaSuccess;
     if (!fused2_supported(a)) return cudaErrorNotSupported;
+    if (a.push.n > 0 && !fused2_push_supported(variant)) return cudaErrorNotSupported;
     if (variant == 0) variant = kDefaultTma2Variant;
     for (const auto &v : kTma2Variants)
         if (v.id == variant) {

@@ -127,14 +127,30 @@ const char *fused_variant_name(int variant);
 // stored.  Outputs (step n+2) go to separate arrays: u2,v2,p2 and the twice-filtered
 // uold2,vold2,pold2 (not in place: neighbouring CTAs still read the old fields' ring).
 // No tmask, not the first (unfiltered) step.
+// halo push of the two-step sweep: like PushSeg, six destinations (u2,v2,p2,uold2,vold2,pold2)
+struct PushSeg2 {
+    int i0, i1, j0, j1;
+    int ides, jdes;
+    int dpitch;
+    int pad_;
+    double *dst[6];
+};
+struct PushPlan2 {
+    int n;
+    int pad_;
+    PushSeg2 seg[kMaxPush];
+};
 struct Fused2Args {
     const double *u, *v, *p, *uold, *vold, *pold;
     double *u2, *v2, *p2, *uold2, *vold2, *pold2;
     int pitch, ny;
     Box b;
     SwScalars sc;
+    PushPlan2 push;     // push.n == 0: halos of the outputs are left to the caller
 };
 bool fused2_supported(const Fused2Args &a);
+// whether `variant` of the two-step sweep can push halos (the shuffle form, ids 10..19 and 0)
+bool fused2_push_supported(int variant);
 cudaError_t sw_step2_fused(const Fused2Args &a, int variant, cudaStream_t s);
 // periodic halo fill to `depth` cells on one rank (wrapped source index; corners included)
 cudaError_t periodic_halos_deep(double *const *fields, int nfields, int pitch, Box internal, int depth,

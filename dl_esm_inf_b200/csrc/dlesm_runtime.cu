@@ -1261,7 +1261,57 @@ extern "C" int dlesm_sw_step2_fused(const void *u, const void *v, const void *p,
         set_error(DLESM_ERR_ARGS, "sw_step2_fused: needs an even pitch and a box with two halo cells on every side (halo_width >= 2)");
         return DLESM_ERR_ARGS;
     }
+    a.push.n = 0;
     Context &c = ctx();
+    const bool push = (variant & DLESM_FUSED_PUSH) != 0;
+    variant &= ~DLESM_FUSED_PUSH;
+    k::PeerFlags pf{};
+    if (push) {
+        // one push box per send-list entry of the installed tables (which must be the depth-2
+        // ones), aimed at the destination rank's counterparts of the six outputs
+        if (!c.have_comms) {
+            set_error(DLESM_ERR_STATE, "sw_step2_fused: halo push needs the depth-2 comm tables (dlesm_dev_set_comms)");
+            return DLESM_ERR_STATE;
+        }
+        if (!k::fused2_push_supported(variant)) {
+            set_error(DLESM_ERR_ARGS, "sw_step2_fused: halo push needs the shuffle form of the sweep (variant 0 or 10..19)");
+            return DLESM_ERR_ARGS;
+        }
+        const Context::PeerView *pv[6];
+        for (int q = 0; q < 6; ++q) {
+            auto it = c.peers.find(outs[q]);
+            if (it == c.peers.end()) {
+                set_error(DLESM_ERR_STATE, "sw_step2_fused: halo push needs the six outputs registered (dlesm_dev_peer_register)");
+                return DLESM_ERR_STATE;
+            }
+            pv[q] = &it->second;
+        }
+        const dlesm_comms &t = c.comms;
+        const int me0 = pstate().rank - 1;
+        const bool single = pstate().nranks == 1;
+        bool seen[64] = {false};
+        for (int sidx = 0; sidx < t.nsend; ++sidx) {
+            const int dest = single ? 0 : t.destination[sidx];
+            k::PushSeg2 &g = a.push.seg[a.push.n++];
+            g.i0 = t.isrcsend[sidx]; g.i1 = g.i0 + t.nxsend[sidx] - 1;
+            g.j0 = t.jsrcsend[sidx]; g.j1 = g.j0 + t.nysend[sidx] - 1;
+            g.ides = t.idessend[sidx]; g.jdes = t.jdessend[sidx];
+            g.dpitch = pv[0]->pitch_by_rank[dest];
+            for (int q = 0; q < 6; ++q) {
+                g.dst[q] = pv[q]->by_rank[dest];
+                if (!g.dst[q]) {
+                    set_error(DLESM_ERR_STATE, "sw_step2_fused: a neighbour's field is not mapped");
+                    return DLESM_ERR_STATE;
+                }
+            }
+            if (dest != me0 && !seen[dest]) {
+                seen[dest] = true;
+                pf.remote[pf.n] = c.peer_flags[dest] + me0;
+                pf.local[pf.n] = c.flags + dest;
+                ++pf.n;
+            }
+        }
+    }
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     if (c.profile) {
         if (c.prof_used == c.prof_events.size()) {
@@ -1282,6 +1332,10 @@ extern "C" int dlesm_sw_step2_fused(const void *u, const void *v, const void *p,
     }
     if (e != cudaSuccess) return fail_cuda(e, "sw_step2_fused");
     if (c.profile) CU(cudaEventRecord(e1, st));
+    if (push && pf.n > 0) {
+        ++c.push_epoch;
+        CU(k::peer_signal_wait(pf, c.push_epoch, c.push_err, st));
+    }
     return DLESM_OK;
 }
 
@@ -1876,6 +1930,38 @@ int sw_fill_halos(dlesm_sw *s, int first_field, int count)
 }
 }  // namespace
 
+namespace {
+// Halo push set-up of the model (collective): install the comm tables at the depth the sweeps
+// push (1, or 2 with the two-step sweep) and map the neighbours' counterparts of every buffer a
+// sweep stores into -- both rotating sets of u,v,p and, with the two-step sweep, of the old fields.
+int sw_configure_push(dlesm_sw *s)
+{
+    const int depth = s->two_step ? 2 : 1;
+    dlesm_grid &g = *s->grid;
+    dlesm_comms t;
+    int rc;
+    if (pstate().nranks == 1)
+        rc = dlesm_map_comms(&g.dh, 1, 1, 1, 1, depth, depth, &t);   // wrap-around neighbours = this rank
+    else
+        rc = build_comms(g.decomp, pstate().rank, pstate().nranks, g.pbc_x, g.pbc_y, depth, depth, t);
+    if (rc == DLESM_OK) rc = dlesm_dev_set_comms(&t);
+    if (rc != DLESM_OK) return rc;
+    void *bufs[12];
+    int n = 0;
+    for (int q = 0; q < 3; ++q) bufs[n++] = s->f[DLESM_SW_U + q]->dptr;
+    for (int q = 0; q < 3; ++q) bufs[n++] = s->f[DLESM_SW_UNEW + q]->dptr;
+    if (s->two_step) {
+        for (int q = 0; q < 3; ++q) bufs[n++] = s->f[DLESM_SW_UOLD + q]->dptr;
+        for (int q = 0; q < 3; ++q) bufs[n++] = s->old2[q]->dptr;
+    }
+    rc = dlesm_dev_peer_unregister_all();    // the registered set is replaced (collective)
+    if (rc == DLESM_OK) rc = dlesm_dev_peer_register(bufs, n);   // collective
+    if (rc != DLESM_OK) return rc;
+    s->registered = true;
+    return DLESM_OK;
+}
+}  // namespace
+
 extern "C" int dlesm_sw_set_halo_mode(dlesm_sw_t *s, int mode)
 {
     clear_error();
@@ -1891,24 +1977,8 @@ extern "C" int dlesm_sw_set_halo_mode(dlesm_sw_t *s, int mode)
         set_error(DLESM_ERR_ARGS, "sw_set_halo_mode: halo push needs a TMA-eligible pitch (DL_ESM_ALIGNMENT even; a multiple of 4 with a mask)");
         return DLESM_ERR_ARGS;
     }
-    int rc;
-    if (pstate().nranks == 1) {
-        // the wrap-around neighbours are this rank itself: tables as map_comms builds them
-        dlesm_comms t;
-        rc = dlesm_map_comms(&s->grid->dh, 1, 1, 1, 1, 1, 1, &t);
-        if (rc == DLESM_OK) rc = dlesm_dev_set_comms(&t);
-        if (rc != DLESM_OK) return rc;
-    }
-    void *bufs[6];
-    for (int q = 0; q < 3; ++q) {
-        bufs[q] = s->f[DLESM_SW_U + q]->dptr;
-        bufs[3 + q] = s->f[DLESM_SW_UNEW + q]->dptr;
-    }
-    rc = dlesm_dev_peer_unregister_all();    // the registered set is replaced (collective)
-    if (rc == DLESM_OK) rc = dlesm_dev_peer_register(bufs, 6);   // collective
-    if (rc != DLESM_OK) return rc;
-    s->push = s->registered = true;
-    return DLESM_OK;
+    s->push = true;
+    return sw_configure_push(s);
 }
 
 namespace {
@@ -1924,6 +1994,12 @@ int sw_fill_deep_halos(dlesm_sw *s)
         CU(k::periodic_halos_deep(dp, 6, fl[0]->nx, box_of(s->f[DLESM_SW_P]->fb.internal), 2, ctx().stream));
         return DLESM_OK;
     }
+    if (s->push) {
+        // the installed tables are already the depth-2 ones (sw_configure_push)
+        void *ptrs[6];
+        for (int q = 0; q < 6; ++q) ptrs[q] = fl[q]->dptr;
+        return dlesm_dev_halo_exchange(ptrs, 6);
+    }
     return dlesm_fields_halo_exchange(fl, 6, 2);
 }
 }  // namespace
@@ -1937,8 +2013,8 @@ extern "C" int dlesm_sw_set_two_step(dlesm_sw_t *s, int on, int variant2)
     }
     const dlesm_region &in = s->f[DLESM_SW_P]->fb.internal;
     const int nx = s->f[0]->nx, ny = s->f[0]->ny;
-    if (s->mode != DLESM_SW_FUSED || s->tmask_dev || s->push) {
-        set_error(DLESM_ERR_ARGS, "sw_set_two_step: needs the fused mode without tmask and without halo push");
+    if (s->mode != DLESM_SW_FUSED || s->tmask_dev) {
+        set_error(DLESM_ERR_ARGS, "sw_set_two_step: needs the fused mode without tmask");
         return DLESM_ERR_ARGS;
     }
     if (nx % 2 != 0 || in.xstart < 3 || in.ystart < 3 || in.xstop + 2 > nx || in.ystop + 2 > ny ||
@@ -1959,6 +2035,7 @@ extern "C" int dlesm_sw_set_two_step(dlesm_sw_t *s, int on, int variant2)
     s->two_step = true;
     s->variant2 = variant2;
     s->deep_valid = false;
+    if (s->push) return sw_configure_push(s);   // tables two cells deep, the old fields mapped too
     return DLESM_OK;
 }
 
@@ -2018,13 +2095,14 @@ extern "C" int dlesm_sw_step(dlesm_sw_t *s, int nsteps)
                                       f[DLESM_SW_UOLD]->dptr, f[DLESM_SW_VOLD]->dptr, f[DLESM_SW_POLD]->dptr,
                                       f[DLESM_SW_UNEW]->dptr, f[DLESM_SW_VNEW]->dptr, f[DLESM_SW_PNEW]->dptr,
                                       s->old2[0]->dptr, s->old2[1]->dptr, s->old2[2]->dptr, dx, dy, s->tdt, s->alpha,
-                                      rt.xstart, rt.xstop, rt.ystart, rt.ystop, s->variant2);
+                                      rt.xstart, rt.xstop, rt.ystart, rt.ystop,
+                                      s->variant2 | (s->push ? DLESM_FUSED_PUSH : 0));
             if (rc != DLESM_OK) return rc;
             for (int q = 0; q < 3; ++q) {
                 std::swap(f[DLESM_SW_U + q]->dptr, f[DLESM_SW_UNEW + q]->dptr);
                 std::swap(f[DLESM_SW_UOLD + q]->dptr, s->old2[q]->dptr);
             }
-            rc = sw_fill_deep_halos(s);
+            if (!s->push) rc = sw_fill_deep_halos(s);   // with push the sweep stored the halos itself
             if (rc != DLESM_OK) return rc;
             s->deep_valid = true;
             s->ncycle += 2;

@@ -428,7 +428,10 @@ int dlesm_sw_step_fused(const void *u, const void *v, const void *p, void *uold,
  * (xstart, ystart >= 3); u,v,p valid to depth 2 and uold,vold,pold valid to depth 1 around the
  * box; `tdt` = 2*dt (not the first step); no tmask; even pitch.  Writes u2,v2,p2 (step n+2)
  * and the twice-filtered uold2,vold2,pold2 on the box -- separate arrays, not in place.  Halos
- * of the outputs are NOT filled (dlesm_dev_periodic_halos_deep / halo_exchange(depth 2)).
+ * of the outputs are NOT filled (dlesm_dev_periodic_halos_deep / halo_exchange(depth 2)) unless
+ * DLESM_FUSED_PUSH is ORed into `variant`: then the sweep pushes them into the neighbours' arrays
+ * as dlesm_sw_step_fused does, following the installed send list (install the depth-2 tables
+ * with dlesm_dev_set_comms; register all six outputs with dlesm_dev_peer_register).
  * `variant` 0 = default.  Timed by dlesm_profile_enable like dlesm_sw_step_fused. */
 int dlesm_sw_step2_fused(const void *u, const void *v, const void *p, const void *uold,
                          const void *vold, const void *pold, void *u2, void *v2, void *p2,
@@ -480,8 +483,10 @@ int dlesm_sw_set_halo_mode(dlesm_sw_t *s, int mode);
  * two steps remain and the first step is behind; an odd remainder runs the one-step sweep.
  * Needs the fused mode, no tmask, an even pitch and a grid decomposed with halo_width >= 2;
  * halos are then kept two cells deep (periodic copies on one rank, halo_exchange(depth 2) on
- * several -- DLESM_EXT_HALO_DEPTH).  Allocates three more fields.  Not combined with
- * DLESM_HALO_PUSH.  `variant2` selects the two-step kernel (0 = default). */
+ * several -- DLESM_EXT_HALO_DEPTH).  Allocates three more fields.  With DLESM_HALO_PUSH (either
+ * call order; both collective) the two-step sweep stores the neighbours' halo cells of its six
+ * outputs itself, two cells deep, and no exchange follows it.  `variant2` selects the two-step
+ * kernel (0 = default). */
 int dlesm_sw_set_two_step(dlesm_sw_t *s, int on, int variant2);
 /* kernels launched by this library since process start (all streams) */
 long long dlesm_kernel_launch_count(void);

@@ -710,6 +710,37 @@ def test_two_step_sweep_matches_oracle(variant2, n_x, n_y, align, nsteps, monkey
         _lib.lib().dlesm_reset_saved_state()
 
 
+@pytest.mark.parametrize("order", ["two_step_first", "push_first"])
+@pytest.mark.parametrize("n_x,n_y,align,nsteps", [(64, 64, 2, 7), (130, 77, 64, 6), (300, 523, 64, 8),
+                                                  (1024, 1024, 64, 9)])
+def test_two_step_sweep_with_halo_push(order, n_x, n_y, align, nsteps, monkeypatch):
+    """the two-step sweep storing its own halos two cells deep (push boxes from the depth-2 send
+    list; on one GPU the wrap-around neighbours are the rank itself) == the oracle, bit for bit"""
+    try:
+        osw, sw = sw_pair_hw2(n_x, n_y, align, monkeypatch)
+        if order == "two_step_first":
+            sw.set_two_step(True)
+            sw.set_halo_mode(fd.HALO_PUSH)
+        else:
+            sw.set_halo_mode(fd.HALO_PUSH)
+            sw.set_two_step(True)
+        for _ in range(nsteps):
+            osw.step()
+        sw.step(nsteps)
+        assert_internal_equal(osw, sw, halo=1)
+        osw.step(); osw.step(); osw.step()
+        sw.step(3)
+        assert_internal_equal(osw, sw, halo=1)
+        # the halos the sweep pushed are two cells deep
+        oi = osw.fb["t"].internal
+        ii = sw.field("p").internal
+        want = np.pad(osw.f["p"][oi.xstart - 1:oi.xstop, oi.ystart - 1:oi.ystop], 2, mode="wrap")
+        got = sw.field("p").get_data()[ii.xstart - 3:ii.xstop + 2, ii.ystart - 3:ii.ystop + 2]
+        assert np.array_equal(got, want)
+    finally:
+        _lib.lib().dlesm_reset_saved_state()
+
+
 def test_two_step_needs_halo_width_two(monkeypatch):
     monkeypatch.setenv("DL_ESM_ALIGNMENT", "2")
     g = make_grid(64, 64, offset=fd.GO_OFFSET_SW, bcs=BCS_PER, tmask=None, dx=1.0e5, dy=1.0e5)
