@@ -551,18 +551,19 @@ struct Tma2Params {
 };
 
 // edge outputs of row j, column i -> the neighbours' halo cells, two cells deep (rare path)
-__device__ __noinline__ void push_row2(const PushPlan2 &pp, unsigned mask, int i, int j, const Outs &o)
+__device__ __noinline__ void push_row2(const PushPlan2 &pp, unsigned mask, int i, int j, double un, double vn,
+                                       double pn, double uo, double vo, double po)
 {
     for (unsigned m = mask; m; m &= m - 1) {
         const PushSeg2 &g = pp.seg[__ffs(m) - 1];
         if (j >= g.j0 && j <= g.j1) {
             const size_t d = idx(g.dpitch, g.ides + (i - g.i0), g.jdes + (j - g.j0));
-            g.dst[0][d] = o.unew;
-            g.dst[1][d] = o.vnew;
-            g.dst[2][d] = o.pnew;
-            g.dst[3][d] = o.uold;
-            g.dst[4][d] = o.vold;
-            g.dst[5][d] = o.pold;
+            g.dst[0][d] = un;
+            g.dst[1][d] = vn;
+            g.dst[2][d] = pn;
+            g.dst[3][d] = uo;
+            g.dst[4][d] = vo;
+            g.dst[5][d] = po;
         }
     }
 }
@@ -849,6 +850,8 @@ fused2s_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_consta
             const PushSeg2 &g = prm.push.seg[q];
             if (i >= g.i0 && i <= g.i1 && g.j1 >= j0 && g.j0 <= j1) pmask |= 1u << q;
         }
+    const int pfirst = pmask ? __ffs(pmask) - 1 : 0;
+    const unsigned prest = pmask & (pmask - 1);
     int jrow = j0 - 4;
     for (int c = 0; c < nchunks; ++c) {
         const int s = c % STAGES;
@@ -895,7 +898,17 @@ fused2s_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_consta
                 __stcs(prm.uold2 + qo, o.uold);
                 __stcs(prm.vold2 + qo, o.vold);
                 __stcs(prm.pold2 + qo, o.pold);
-                if (pmask) push_row2(prm.push, pmask, i, jrow, o);
+                if (pmask) {
+                    // first box inline (an x-edge column meets it on every row; a call would save and
+                    // restore ~150 live registers each time), the rest -- corners -- out of line
+                    const PushSeg2 &g = prm.push.seg[pfirst];
+                    if (jrow >= g.j0 && jrow <= g.j1) {
+                        const size_t d = idx(g.dpitch, g.ides + (i - g.i0), g.jdes + (jrow - g.j0));
+                        g.dst[0][d] = o.unew; g.dst[1][d] = o.vnew; g.dst[2][d] = o.pnew;
+                        g.dst[3][d] = o.uold; g.dst[4][d] = o.vold; g.dst[5][d] = o.pold;
+                    }
+                    if (prest) push_row2(prm.push, prest, i, jrow, o.unew, o.vnew, o.pnew, o.uold, o.vold, o.pold);
+                }
             }
             qo += pitch;
             ++jrow;
