@@ -250,6 +250,23 @@ module dlesm_b200_mod
        integer(c_int), value :: first, xstart, xstop, ystart, ystop, variant
        integer(c_int) :: ierr
      end function
+     ! two model steps in one sweep (tile decomposed with halo_width >= 2; include/dlesm_b200.h)
+     function dlesm_sw_step2_fused(u, v, p, uold, vold, pold, u2, v2, p2, uold2, vold2, pold2, dx, dy, tdt, &
+                                   alpha, xstart, xstop, ystart, ystop, variant)                              &
+          bind(C, name="dlesm_sw_step2_fused") result(ierr)
+       import :: c_int, c_ptr, c_double
+       type(c_ptr), value :: u, v, p, uold, vold, pold, u2, v2, p2, uold2, vold2, pold2
+       real(c_double), value :: dx, dy, tdt, alpha
+       integer(c_int), value :: xstart, xstop, ystart, ystop, variant
+       integer(c_int) :: ierr
+     end function
+     function dlesm_dev_periodic_halos_deep(f, xstart, xstop, ystart, ystop, depth)                          &
+          bind(C, name="dlesm_dev_periodic_halos_deep") result(ierr)
+       import :: c_int, c_ptr
+       type(c_ptr), value :: f
+       integer(c_int), value :: xstart, xstop, ystart, ystop, depth
+       integer(c_int) :: ierr
+     end function
   end interface
 
   !> go_arg across the boundary (include/dlesm_b200.h `dlesm_go_arg`): src/argument_mod.f90:57-61

@@ -13,7 +13,7 @@ module shallow_psy_mod
   use dlesm_b200_mod
   implicit none
   private
-  public :: sw_step_fused, sw_step_unfused
+  public :: sw_step_fused, sw_step2_fused, sw_step_unfused
 
 contains
 
@@ -39,6 +39,39 @@ contains
          p%grid%tmask_device, 0_c_int), 'sw_step_fused')
     call fill_halos_3(unew, vnew, pnew)
   end subroutine sw_step_fused
+
+  !> TWO model time steps in one sweep (temporal blocking): the state crosses HBM once for both.
+  !! Needs grid%decompose(..., halo_width=2); u,v,p with halos two cells deep and uold,vold,pold
+  !! one cell deep on entry (fill_halos_deep below); never the first step (tdt = 2*dt).  On return
+  !! u2,v2,p2 hold step n+2 and uold2,vold2,pold2 the twice-filtered old fields, halos two cells
+  !! deep; the caller rotates (u,u2), (uold,uold2) etc. by swapping the r2d_field objects.
+  subroutine sw_step2_fused(u, v, p, uold, vold, pold, u2, v2, p2, uold2, vold2, pold2, tdt, alpha)
+    type(r2d_field), intent(inout) :: u, v, p, uold, vold, pold, u2, v2, p2, uold2, vold2, pold2
+    real(go_wp), intent(in) :: tdt, alpha
+    call dlesm_check(dlesm_sw_step2_fused(u%device_ptr, v%device_ptr, p%device_ptr,           &
+         uold%device_ptr, vold%device_ptr, pold%device_ptr,                                    &
+         u2%device_ptr, v2%device_ptr, p2%device_ptr,                                          &
+         uold2%device_ptr, vold2%device_ptr, pold2%device_ptr,                                 &
+         real(p%grid%dx, c_double), real(p%grid%dy, c_double), real(tdt, c_double),            &
+         real(alpha, c_double),                                                                &
+         int(p%internal%xstart, c_int), int(p%internal%xstop, c_int),                          &
+         int(p%internal%ystart, c_int), int(p%internal%ystop, c_int), 0_c_int), 'sw_step2_fused')
+    call fill_halos_deep(u2);     call fill_halos_deep(v2);     call fill_halos_deep(p2)
+    call fill_halos_deep(uold2);  call fill_halos_deep(vold2);  call fill_halos_deep(pold2)
+  end subroutine sw_step2_fused
+
+  !> halos two cells deep: wrapped copies on one rank, halo_exchange(depth=2) on several
+  !! (the DLESM_EXT_HALO_DEPTH extension; the reference ignores depth, src/field_mod.f90:1226-1229)
+  subroutine fill_halos_deep(f)
+    type(r2d_field), intent(inout) :: f
+    if (get_num_ranks() == 1) then
+       call dlesm_check(dlesm_dev_periodic_halos_deep(f%device_ptr,                            &
+            int(f%internal%xstart, c_int), int(f%internal%xstop, c_int),                       &
+            int(f%internal%ystart, c_int), int(f%internal%ystop, c_int), 2_c_int), 'halos_deep')
+    else
+       call f%halo_exchange(2)
+    end if
+  end subroutine fill_halos_deep
 
   !> The same step, one launch per kernel, each over its output field's internal region.
   subroutine sw_step_unfused(u, v, p, uold, vold, pold, unew, vnew, pnew, cu, cv, z, h, &
