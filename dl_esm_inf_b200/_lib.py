@@ -170,7 +170,7 @@ SIGNATURES = {
     "dlesm_sw_set_variant": (_I, [_V, _I]),
     "dlesm_sw_set_halo_mode": (_I, [_V, _I]),
     "dlesm_sw_set_two_step": (_I, [_V, _I, _I]),
-    "dlesm_sw_step2_fused": (_I, [_V] * 12 + [_D, _D, _D, _D, _I, _I, _I, _I, _I]),
+    "dlesm_sw_step2_fused": (_I, [_V] * 12 + [_D, _D, _D, _D, _I, _I, _I, _I, _V, _I]),
     "dlesm_dev_periodic_halos_deep": (_I, [_V, _I, _I, _I, _I, _I]),
     "dlesm_kernel_launch_count": (C.c_longlong, []),
     "dlesm_profile_enable": (_I, [_I]),

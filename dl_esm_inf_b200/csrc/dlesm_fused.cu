@@ -721,21 +721,33 @@ struct RawS {
 struct CarryS {
     RawS P;
     double cuC_P, cuE_P, cuC_PP, cuE_PP, cvC_P, cvW_P, zC_P, zE_P, hC_PP;
+    bool tC_P, tW_P, tC_PP;   // tmask of row j-1 (own, west) and j-2 (own); masked runs only
 };
 __device__ __forceinline__ void carry_init(CarryS &c)
 {
+    c.tC_P = c.tW_P = c.tC_PP = true;
     c.P.pW = c.P.pC = 1.0;
     c.P.uC = c.P.uE = c.P.vW = c.P.vC = 0.0;
     c.cuC_P = c.cuE_P = c.cuC_PP = c.cuE_PP = c.cvC_P = c.cvW_P = c.zC_P = c.zE_P = c.hC_PP = 0.0;
 }
-__device__ __forceinline__ void ingest_sh(CarryS &c, const RawS &N, const SwScalars &sc, double uo, double vo,
-                                          double po, Outs &o)
+// tC, tW: tmask == 1 at row N for the own and the west column (M only).  The masked rule is the
+// one of ingest<true>: intermediates are 0 unless every T cell they straddle is wet, a dry
+// prognostic point keeps its value and is not filtered -- the neighbours' copies arrive masked.
+template <bool M>
+__device__ __forceinline__ void ingest_sh(CarryS &c, const RawS &N, bool tC, bool tW, const SwScalars &sc,
+                                          double uo, double vo, double po, Outs &o)
 {
     const RawS &P = c.P;
-    const double cuC_N = 0.5 * (N.pC + N.pW) * N.uC;
-    const double cvC_N = 0.5 * (N.pC + P.pC) * N.vC;
-    const double zC_N = (sc.fsdx * (N.vC - N.vW) - sc.fsdy * (N.uC - P.uC)) / (P.pW + P.pC + N.pC + N.pW);
-    const double hC_P = P.pC + 0.25 * (P.uE * P.uE + P.uC * P.uC + N.vC * N.vC + P.vC * P.vC);
+    double cuC_N = 0.5 * (N.pC + N.pW) * N.uC;
+    double cvC_N = 0.5 * (N.pC + P.pC) * N.vC;
+    double zC_N = (sc.fsdx * (N.vC - N.vW) - sc.fsdy * (N.uC - P.uC)) / (P.pW + P.pC + N.pC + N.pW);
+    double hC_P = P.pC + 0.25 * (P.uE * P.uE + P.uC * P.uC + N.vC * N.vC + P.vC * P.vC);
+    if (M) {
+        if (!(tC && tW)) cuC_N = 0.0;
+        if (!(tC && c.tC_P)) cvC_N = 0.0;
+        if (!(tC && tW && c.tC_P && c.tW_P)) zC_N = 0.0;
+        if (!c.tC_P) hC_P = 0.0;
+    }
     const double cuE_N = __shfl_down_sync(0xffffffffu, cuC_N, 1);
     const double zE_N = __shfl_down_sync(0xffffffffu, zC_N, 1);
     const double cvW_N = __shfl_up_sync(0xffffffffu, cvC_N, 1);
@@ -745,9 +757,26 @@ __device__ __forceinline__ void ingest_sh(CarryS &c, const RawS &N, const SwScal
     o.vnew = vo - sc.tdts8 * (c.zE_P + c.zC_P) * (c.cuE_P + c.cuC_P + c.cuC_PP + c.cuE_PP) -
              sc.tdtsdy * (hC_P - c.hC_PP);
     o.pnew = po - sc.tdtsdx * (c.cuE_P - c.cuC_P) - sc.tdtsdy * (cvC_N - c.cvC_P);
+    bool wu = true, wv = true, wt = true;
+    if (M) {
+        wu = c.tC_P && c.tW_P;
+        wv = c.tC_P && c.tC_PP;
+        wt = c.tC_P;
+        if (!wu) o.unew = P.uC;
+        if (!wv) o.vnew = P.vC;
+        if (!wt) o.pnew = P.pC;
+    }
     o.uold = P.uC + sc.alpha * (o.unew - 2.0 * P.uC + uo);
     o.vold = P.vC + sc.alpha * (o.vnew - 2.0 * P.vC + vo);
     o.pold = P.pC + sc.alpha * (o.pnew - 2.0 * P.pC + po);
+    if (M) {
+        if (!wu) o.uold = uo;
+        if (!wv) o.vold = vo;
+        if (!wt) o.pold = po;
+        c.tC_PP = c.tC_P;
+        c.tC_P = tC;
+        c.tW_P = tW;
+    }
     c.cuC_PP = c.cuC_P; c.cuE_PP = c.cuE_P;
     c.cuC_P = cuC_N; c.cuE_P = cuE_N;
     c.cvC_P = cvC_N; c.cvW_P = cvW_N;
@@ -756,18 +785,21 @@ __device__ __forceinline__ void ingest_sh(CarryS &c, const RawS &N, const SwScal
     c.P = N;
 }
 
-template <int TX, int RY, int STAGES>
+template <int TX, int RY, int STAGES, bool M = false>
 struct Tma2sCfg {
     static constexpr int NW = TX / 32;
     static constexpr int VA = 30 * NW;   // columns of the intermediate state a CTA produces
     static constexpr int OUT = VA - 2;   // output columns per CTA
     static constexpr int BW = VA + 6;    // raw tiles: lanes' columns (VA + 2) + west + east, even start
     static constexpr int BWO = VA + 4;   // old tiles: lanes' columns, even start
+    static constexpr int BWM = VA + 8;   // int32 tmask tile: lanes' columns, start column a multiple of four
     static constexpr int A = align128(BW * RY * 8);
     static constexpr int AO = align128(BWO * RY * 8);
+    static constexpr int AM = M ? align128(BWM * RY * 4) : 0;
     static constexpr int OFF_OLD = 3 * A;
-    static constexpr int STAGE_BYTES = 3 * A + 3 * AO;
-    static constexpr int TX_BYTES = 3 * BW * RY * 8 + 3 * BWO * RY * 8;
+    static constexpr int OFF_MASK = 3 * A + 3 * AO;
+    static constexpr int STAGE_BYTES = 3 * A + 3 * AO + AM;
+    static constexpr int TX_BYTES = 3 * BW * RY * 8 + 3 * BWO * RY * 8 + (M ? BWM * RY * 4 : 0);
     static constexpr int XW = VA + 4;    // exchange row: index of column x = x - i_first + 3
     static constexpr int XBUF_BYTES = 3 * RY * XW * 8;
     static constexpr int OFF_X = STAGES * STAGE_BYTES;
@@ -776,15 +808,15 @@ struct Tma2sCfg {
     static constexpr int THREADS = TX;
 };
 
-template <int TX, int RY, int STAGES, int MINB>
+template <int TX, int RY, int STAGES, int MINB, bool M>
 __global__ void __launch_bounds__(TX, MINB)
 fused2s_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_constant__ CUtensorMap tm_v,
                    const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUtensorMap tm_uo,
                    const __grid_constant__ CUtensorMap tm_vo, const __grid_constant__ CUtensorMap tm_po,
-                   const __grid_constant__ Tma2Params prm)
+                   const __grid_constant__ CUtensorMap tm_mask, const __grid_constant__ Tma2Params prm)
 {
-    using Cfg = Tma2sCfg<TX, RY, STAGES>;
-    constexpr int BW = Cfg::BW, BWO = Cfg::BWO, XW = Cfg::XW;
+    using Cfg = Tma2sCfg<TX, RY, STAGES, M>;
+    constexpr int BW = Cfg::BW, BWO = Cfg::BWO, BWM = Cfg::BWM, XW = Cfg::XW;
     extern __shared__ __align__(1024) unsigned char fused_smem[];
     uint64_t *full = reinterpret_cast<uint64_t *>(fused_smem + Cfg::BAR_OFFSET);
 
@@ -797,6 +829,7 @@ fused2s_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_consta
     // lane column (both stages): i_first + 30*warp + lane - 2
     const int x_box = (i_first - 4) & ~1;   // even 0-based column at/below stage A lane 0's west neighbour
     const int x_old = (i_first - 3) & ~1;   // even 0-based column at/below stage A lane 0's own column
+    const int x_msk = (i_first - 3) & ~3;   // the int32 tmask tile starts on a multiple of four columns
 
     auto issue = [&](int c) {
         const int s = c % STAGES;
@@ -810,6 +843,7 @@ fused2s_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_consta
         tma_load_2d(st + Cfg::OFF_OLD + 0 * Cfg::AO, &tm_uo, x_old, y_old, &full[s]);
         tma_load_2d(st + Cfg::OFF_OLD + 1 * Cfg::AO, &tm_vo, x_old, y_old, &full[s]);
         tma_load_2d(st + Cfg::OFF_OLD + 2 * Cfg::AO, &tm_po, x_old, y_old, &full[s]);
+        if (M) tma_load_2d(st + Cfg::OFF_MASK, &tm_mask, x_msk, y_raw, &full[s]);
     };
     if (tid == 0) {
         if (smem_u32(fused_smem) & 127u) __trap();
@@ -835,6 +869,7 @@ fused2s_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_consta
     const int xo = base + 1;                          // exchange index of this lane's column
     const int col = base + ((i_first - 4) & 1);       // west neighbour inside the raw tile
     const int colo = base + ((i_first - 3) & 1);      // own column inside the old tile
+    const int colm = base + ((i_first - 3) & 3);      // own column inside the tmask tile
     const SwScalars sc = prm.sc;
     CarryS ca, cb;
     carry_init(ca);
@@ -864,15 +899,23 @@ fused2s_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_consta
         const double *svo = reinterpret_cast<const double *>(st + Cfg::OFF_OLD + 1 * Cfg::AO) + colo;
         const double *spo = reinterpret_cast<const double *>(st + Cfg::OFF_OLD + 2 * Cfg::AO) + colo;
         double *xb = reinterpret_cast<double *>(fused_smem + Cfg::OFF_X + (c & 1) * Cfg::XBUF_BYTES) + xo;
+        const int *sm = reinterpret_cast<const int *>(st + Cfg::OFF_MASK) + colm;
         double uo_r[RY], vo_r[RY], po_r[RY];
+        bool tbC[RY], tbW[RY];   // stage B's row is stage A's previous row: its masks are A's carried ones
 #pragma unroll
         for (int r = 0; r < RY; ++r) {
             RawS N;
             N.pW = sp[r * BW]; N.pC = sp[r * BW + 1];
             N.uC = su[r * BW + 1]; N.uE = su[r * BW + 2];
             N.vW = sv[r * BW]; N.vC = sv[r * BW + 1];
+            bool tC = true, tW = true;
+            if (M) {
+                tC = sm[r * BWM] == 1;
+                tW = __shfl_up_sync(0xffffffffu, static_cast<int>(tC), 1) != 0;
+                tbC[r] = ca.tC_P; tbW[r] = ca.tW_P;
+            }
             Outs o;
-            ingest_sh(ca, N, sc, suo[r * BWO], svo[r * BWO], spo[r * BWO], o);
+            ingest_sh<M>(ca, N, tC, tW, sc, suo[r * BWO], svo[r * BWO], spo[r * BWO], o);
             if (a_writes) {
                 xb[(0 * RY + r) * XW] = o.unew;
                 xb[(1 * RY + r) * XW] = o.vnew;
@@ -889,7 +932,7 @@ fused2s_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_consta
             N.vW = xb[(1 * RY + r) * XW - 1]; N.vC = xb[(1 * RY + r) * XW];
             N.pW = xb[(2 * RY + r) * XW - 1]; N.pC = xb[(2 * RY + r) * XW];
             Outs o;
-            ingest_sh(cb, N, sc, uo1, vo1, po1, o);
+            ingest_sh<M>(cb, N, M ? tbC[r] : true, M ? tbW[r] : true, sc, uo1, vo1, po1, o);
             uo1 = uo_r[r]; vo1 = vo_r[r]; po1 = po_r[r];
             if (r >= t_lo && r < t_hi) {
                 __stcs(prm.u2 + qo, o.unew);
@@ -1027,14 +1070,14 @@ fused2w_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_consta
             N.uC = su[r * BW + 1]; N.uE = su[r * BW + 2];
             N.vW = sv[r * BW]; N.vC = sv[r * BW + 1];
             Outs oa;
-            ingest_sh(ca, N, sc, suo[r * BWO], svo[r * BWO], spo[r * BWO], oa);
+            ingest_sh<false>(ca, N, true, true, sc, suo[r * BWO], svo[r * BWO], spo[r * BWO], oa);
             RawS M;   // the intermediate state's row, neighbours by shuffle (valid on lanes 1..30)
             M.uC = oa.unew; M.vC = oa.vnew; M.pC = oa.pnew;
             M.uE = __shfl_down_sync(0xffffffffu, oa.unew, 1);
             M.vW = __shfl_up_sync(0xffffffffu, oa.vnew, 1);
             M.pW = __shfl_up_sync(0xffffffffu, oa.pnew, 1);
             Outs ob;
-            ingest_sh(cb, M, sc, uo1, vo1, po1, ob);
+            ingest_sh<false>(cb, M, true, true, sc, uo1, vo1, po1, ob);
             uo1 = oa.uold; vo1 = oa.vold; po1 = oa.pold;
             if (r >= t_lo && r < t_hi) {
                 __stcs(prm.u2 + qo, ob.unew);
@@ -1092,10 +1135,48 @@ cudaError_t launch_tma2(const Fused2Args &a, cudaStream_t s)
     return launch_tma2_generic<Tma2Cfg<TX, RY, STAGES>, RY, MINB>(a, s, fused2_tma_kernel<TX, RY, STAGES, MINB>);
 }
 
+template <int TX, int RY, int STAGES, int MINB, bool M>
+cudaError_t launch_tma2s_m(const Fused2Args &a, cudaStream_t s)
+{
+    using Cfg = Tma2sCfg<TX, RY, STAGES, M>;
+    CUtensorMap mu, mv, mp, muo, mvo, mpo, mm;
+    if (!get_map(a.u, 8, a.pitch, a.ny, Cfg::BW, RY, mu) || !get_map(a.v, 8, a.pitch, a.ny, Cfg::BW, RY, mv) ||
+        !get_map(a.p, 8, a.pitch, a.ny, Cfg::BW, RY, mp) || !get_map(a.uold, 8, a.pitch, a.ny, Cfg::BWO, RY, muo) ||
+        !get_map(a.vold, 8, a.pitch, a.ny, Cfg::BWO, RY, mvo) || !get_map(a.pold, 8, a.pitch, a.ny, Cfg::BWO, RY, mpo))
+        return cudaErrorNotSupported;
+    if (M) {
+        if (!get_map(a.tmask, 4, a.pitch, a.ny, Cfg::BWM, RY, mm)) return cudaErrorNotSupported;
+    } else {
+        mm = mp;  // unused by the unmasked kernel
+    }
+    Tma2Params prm;
+    prm.u2 = a.u2; prm.v2 = a.v2; prm.p2 = a.p2;
+    prm.uold2 = a.uold2; prm.vold2 = a.vold2; prm.pold2 = a.pold2;
+    const int w = a.b.xe - a.b.xs + 1, h = a.b.ye - a.b.ys + 1;
+    static const int target = [] {
+        const char *e = std::getenv("DLESM_SEG_ROWS2");
+        const int v = e ? std::atoi(e) : 124;
+        return v < 8 ? 124 : v;
+    }();
+    const int seg_rows = pick_seg_rows(w, h, Cfg::OUT, 148 * MINB, RY, target, 4);
+    prm.pitch = a.pitch; prm.b = a.b; prm.seg_rows = seg_rows; prm.sc = a.sc;
+    prm.push = a.push;
+    auto kern = fused2s_tma_kernel<TX, RY, STAGES, MINB, M>;
+    static bool attr_done = false;
+    if (!attr_done) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
+        if (e != cudaSuccess) return e;
+        attr_done = true;
+    }
+    dim3 grid((w + Cfg::OUT - 1) / Cfg::OUT, (h + seg_rows - 1) / seg_rows);
+    kern<<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, s>>>(mu, mv, mp, muo, mvo, mpo, mm, prm);
+    return cudaGetLastError();
+}
 template <int TX, int RY, int STAGES, int MINB>
 cudaError_t launch_tma2s(const Fused2Args &a, cudaStream_t s)
 {
-    return launch_tma2_generic<Tma2sCfg<TX, RY, STAGES>, RY, MINB>(a, s, fused2s_tma_kernel<TX, RY, STAGES, MINB>);
+    return a.tmask ? launch_tma2s_m<TX, RY, STAGES, MINB, true>(a, s)
+                   : launch_tma2s_m<TX, RY, STAGES, MINB, false>(a, s);
 }
 
 template <int TX, int RY, int STAGES, int MINB>
@@ -1142,6 +1223,7 @@ constexpr int kDefaultTma2Variant = 10;
 
 bool fused2_supported(const Fused2Args &a)
 {
+    if (a.tmask && a.pitch % 4 != 0) return false;   // the int32 tmask tile needs 16-byte row starts
     return a.pitch % 2 == 0 && encode_fn() != nullptr && a.b.xs >= 3 && a.b.ys >= 3 && a.b.xe + 2 <= a.pitch &&
            a.b.ye + 2 <= a.ny && !a.sc.first;
 }
@@ -1152,7 +1234,7 @@ cudaError_t sw_step2_fused(const Fused2Args &a, int variant, cudaStream_t s)
 {
     if (a.b.xe < a.b.xs || a.b.ye < a.b.ys) return cudaSuccess;
     if (!fused2_supported(a)) return cudaErrorNotSupported;
-    if (a.push.n > 0 && !fused2_push_supported(variant)) return cudaErrorNotSupported;
+    if ((a.push.n > 0 || a.tmask) && !fused2_push_supported(variant)) return cudaErrorNotSupported;
     if (variant == 0) variant = kDefaultTma2Variant;
     for (const auto &v : kTma2Variants)
         if (v.id == variant) {

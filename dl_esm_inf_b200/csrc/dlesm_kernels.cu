@@ -318,6 +318,26 @@ cudaError_t periodic_halos_deep(double *const *fields, int nfields, int pitch, B
     return cudaGetLastError();
 }
 
+// tmask <-> FP64 image of it, so that the mask can ride the FP64 halo machinery once (the
+// two-step sweep needs the periodic mask two cells deep; grid_init replicates it outward instead)
+__global__ void __launch_bounds__(256) mask_convert_kernel(int *__restrict__ m, double *__restrict__ d, size_t n,
+                                                           int to_double)
+{
+    for (size_t t = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; t < n;
+         t += static_cast<size_t>(gridDim.x) * blockDim.x) {
+        if (to_double) d[t] = static_cast<double>(m[t]);
+        else m[t] = static_cast<int>(d[t]);
+    }
+}
+cudaError_t mask_convert(int *m, double *d, size_t n, bool to_double, cudaStream_t s)
+{
+    if (n == 0) return cudaSuccess;
+    const unsigned blocks = n / 256 + 1 < kSMs * 8 ? static_cast<unsigned>(n / 256 + 1) : kSMs * 8;
+    mask_convert_kernel<<<blocks, 256, 0, s>>>(m, d, n, to_double ? 1 : 0);
+    count_launch();
+    return cudaGetLastError();
+}
+
 // ---------------------------------------------------------------------------------------
 // Halo pack / unpack (src/parallel_comms_mod.f90:1678-1683, 1788-1793): every patch of every
 // field in one launch; within a patch j is the outer and i the inner index, as the

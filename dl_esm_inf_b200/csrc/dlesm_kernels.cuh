@@ -143,18 +143,23 @@ struct PushPlan2 {
 struct Fused2Args {
     const double *u, *v, *p, *uold, *vold, *pold;
     double *u2, *v2, *p2, *uold2, *vold2, *pold2;
+    const int *tmask;   // may be null; must hold the PERIODIC mask two cells deep around b
     int pitch, ny;
     Box b;
     SwScalars sc;
     PushPlan2 push;     // push.n == 0: halos of the outputs are left to the caller
 };
 bool fused2_supported(const Fused2Args &a);
-// whether `variant` of the two-step sweep can push halos (the shuffle form, ids 10..19 and 0)
+// whether `variant` of the two-step sweep can push halos / take a tmask (the shuffle form, ids
+// 10..19 and 0)
 bool fused2_push_supported(int variant);
 cudaError_t sw_step2_fused(const Fused2Args &a, int variant, cudaStream_t s);
 // periodic halo fill to `depth` cells on one rank (wrapped source index; corners included)
 cudaError_t periodic_halos_deep(double *const *fields, int nfields, int pitch, Box internal, int depth,
                                 cudaStream_t s);
+
+// m[t] -> d[t] (to_double) or d[t] -> m[t]: the tmask rides the FP64 halo machinery once
+cudaError_t mask_convert(int *m, double *d, size_t n, bool to_double, cudaStream_t s);
 
 // classic initial conditions, synthetic (device sin/cos)
 cudaError_t sw_init(double *u, double *v, double *p, int pitch, Box b, int gx0, int gy0, int M,

@@ -1225,7 +1225,7 @@ extern "C" int dlesm_sw_step_fused(const void *u, const void *v, const void *p, 
 extern "C" int dlesm_sw_step2_fused(const void *u, const void *v, const void *p, const void *uold, const void *vold,
                                     const void *pold, void *u2, void *v2, void *p2, void *uold2, void *vold2,
                                     void *pold2, double dx, double dy, double tdt, double alpha, int xs, int xe,
-                                    int ys, int ye, int variant)
+                                    int ys, int ye, const void *tm, int variant)
 {
     SWEEP_PROLOGUE(u2)
     (void)b;
@@ -1251,6 +1251,7 @@ extern "C" int dlesm_sw_step2_fused(const void *u, const void *v, const void *p,
     a.u = CD(u); a.v = CD(v); a.p = CD(p);
     a.uold = CD(uold); a.vold = CD(vold); a.pold = CD(pold);
     a.u2 = D(u2); a.v2 = D(v2); a.p2 = D(p2);
+    a.tmask = static_cast<const int *>(tm);
     a.uold2 = D(uold2); a.vold2 = D(vold2); a.pold2 = D(pold2);
     a.pitch = pitch; a.ny = ny_;
     a.b = k::Box{xs, xe, ys, ye};
@@ -1258,7 +1259,7 @@ extern "C" int dlesm_sw_step2_fused(const void *u, const void *v, const void *p,
     a.sc.tdts8 = tdt / 8.0; a.sc.tdtsdx = tdt / dx; a.sc.tdtsdy = tdt / dy;
     a.sc.alpha = alpha; a.sc.first = 0;
     if (!k::fused2_supported(a)) {
-        set_error(DLESM_ERR_ARGS, "sw_step2_fused: needs an even pitch and a box with two halo cells on every side (halo_width >= 2)");
+        set_error(DLESM_ERR_ARGS, "sw_step2_fused: needs an even pitch (a multiple of 4 with a mask) and a box with two halo cells on every side (halo_width >= 2)");
         return DLESM_ERR_ARGS;
     }
     a.push.n = 0;
@@ -1872,6 +1873,7 @@ struct dlesm_sw {
     int variant2 = 0;
     dlesm_field *old2[3] = {nullptr, nullptr, nullptr};
     bool deep_valid = false;
+    int *tmask2 = nullptr;       // the tmask with a PERIODIC ring two cells deep (two-step sweep, masked)
 };
 
 extern "C" dlesm_sw_t *dlesm_sw_create(dlesm_grid_t *g, double dt, double alpha, int mode, int use_tmask)
@@ -2013,8 +2015,12 @@ extern "C" int dlesm_sw_set_two_step(dlesm_sw_t *s, int on, int variant2)
     }
     const dlesm_region &in = s->f[DLESM_SW_P]->fb.internal;
     const int nx = s->f[0]->nx, ny = s->f[0]->ny;
-    if (s->mode != DLESM_SW_FUSED || s->tmask_dev) {
-        set_error(DLESM_ERR_ARGS, "sw_set_two_step: needs the fused mode without tmask");
+    if (s->mode != DLESM_SW_FUSED) {
+        set_error(DLESM_ERR_ARGS, "sw_set_two_step: needs the fused mode");
+        return DLESM_ERR_ARGS;
+    }
+    if (s->tmask_dev && nx % 4 != 0) {
+        set_error(DLESM_ERR_ARGS, "sw_set_two_step: with a tmask the pitch must be a multiple of 4 (DL_ESM_ALIGNMENT)");
         return DLESM_ERR_ARGS;
     }
     if (nx % 2 != 0 || in.xstart < 3 || in.ystart < 3 || in.xstop + 2 > nx || in.ystop + 2 > ny ||
@@ -2032,6 +2038,28 @@ extern "C" int dlesm_sw_set_two_step(dlesm_sw_t *s, int on, int variant2)
             s->old2[q] = dlesm_r2d_field_create(s->grid, pts[q], 0, nullptr, 0, 0);
             if (!s->old2[q]) return last_status();
         }
+    if (s->tmask_dev && !s->tmask2) {
+        // grid_init replicates the mask outward beyond the first halo ring (src/grid_mod.f90:400-431);
+        // the two-step sweep reads the ring two cells deep, where the periodic model needs the
+        // wrapped mask.  Build it once: mask -> FP64 image -> depth-2 halo fill -> mask.
+        const size_t n = static_cast<size_t>(nx) * ny;
+        dlesm_field *tmp = dlesm_r2d_field_create(s->grid, DLESM_GO_T_POINTS, 0, nullptr, 0, 0);
+        if (!tmp) return last_status();
+        CU(cudaMalloc(&s->tmask2, n * sizeof(int)));
+        CU(cudaMemcpyAsync(s->tmask2, s->tmask_dev, n * sizeof(int), cudaMemcpyDeviceToDevice, ctx().stream));
+        CU(k::mask_convert(s->tmask2, static_cast<double *>(tmp->dptr), n, true, ctx().stream));
+        int rc = DLESM_OK;
+        if (s->periodic_local) {
+            double *dp[1] = {static_cast<double *>(tmp->dptr)};
+            CU(k::periodic_halos_deep(dp, 1, nx, box_of(in), 2, ctx().stream));
+        } else {
+            rc = dlesm_fields_halo_exchange(&tmp, 1, 2);
+        }
+        if (rc == DLESM_OK) CU(k::mask_convert(s->tmask2, static_cast<double *>(tmp->dptr), n, false, ctx().stream));
+        CU(cudaStreamSynchronize(ctx().stream));
+        dlesm_free_field(tmp);
+        if (rc != DLESM_OK) return rc;
+    }
     s->two_step = true;
     s->variant2 = variant2;
     s->deep_valid = false;
@@ -2095,7 +2123,7 @@ extern "C" int dlesm_sw_step(dlesm_sw_t *s, int nsteps)
                                       f[DLESM_SW_UOLD]->dptr, f[DLESM_SW_VOLD]->dptr, f[DLESM_SW_POLD]->dptr,
                                       f[DLESM_SW_UNEW]->dptr, f[DLESM_SW_VNEW]->dptr, f[DLESM_SW_PNEW]->dptr,
                                       s->old2[0]->dptr, s->old2[1]->dptr, s->old2[2]->dptr, dx, dy, s->tdt, s->alpha,
-                                      rt.xstart, rt.xstop, rt.ystart, rt.ystop,
+                                      rt.xstart, rt.xstop, rt.ystart, rt.ystop, s->tmask2,
                                       s->variant2 | (s->push ? DLESM_FUSED_PUSH : 0));
             if (rc != DLESM_OK) return rc;
             for (int q = 0; q < 3; ++q) {
@@ -2291,5 +2319,6 @@ extern "C" void dlesm_sw_free(dlesm_sw_t *s)
         if (fl) dlesm_free_field(fl);
     for (auto *fl : s->old2)
         if (fl) dlesm_free_field(fl);
+    if (s->tmask2) cudaFree(s->tmask2);
     delete s;
 }

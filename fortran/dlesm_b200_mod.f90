@@ -252,10 +252,10 @@ module dlesm_b200_mod
      end function
      ! two model steps in one sweep (tile decomposed with halo_width >= 2; include/dlesm_b200.h)
      function dlesm_sw_step2_fused(u, v, p, uold, vold, pold, u2, v2, p2, uold2, vold2, pold2, dx, dy, tdt, &
-                                   alpha, xstart, xstop, ystart, ystop, variant)                              &
+                                   alpha, xstart, xstop, ystart, ystop, tmask, variant)                       &
           bind(C, name="dlesm_sw_step2_fused") result(ierr)
        import :: c_int, c_ptr, c_double
-       type(c_ptr), value :: u, v, p, uold, vold, pold, u2, v2, p2, uold2, vold2, pold2
+       type(c_ptr), value :: u, v, p, uold, vold, pold, u2, v2, p2, uold2, vold2, pold2, tmask
        real(c_double), value :: dx, dy, tdt, alpha
        integer(c_int), value :: xstart, xstop, ystart, ystop, variant
        integer(c_int) :: ierr

@@ -55,7 +55,7 @@ contains
          real(p%grid%dx, c_double), real(p%grid%dy, c_double), real(tdt, c_double),            &
          real(alpha, c_double),                                                                &
          int(p%internal%xstart, c_int), int(p%internal%xstop, c_int),                          &
-         int(p%internal%ystart, c_int), int(p%internal%ystop, c_int), 0_c_int), 'sw_step2_fused')
+         int(p%internal%ystart, c_int), int(p%internal%ystop, c_int), c_null_ptr, 0_c_int), 'sw_step2_fused')
     call fill_halos_deep(u2);     call fill_halos_deep(v2);     call fill_halos_deep(p2)
     call fill_halos_deep(uold2);  call fill_halos_deep(vold2);  call fill_halos_deep(pold2)
   end subroutine sw_step2_fused

@@ -426,7 +426,9 @@ int dlesm_sw_step_fused(const void *u, const void *v, const void *p, void *uold,
  * two steps cost the 96 B / point of one.  Results are bit-identical to two dlesm_sw_step_fused
  * calls with a halo fill in between.  Requirements: a tile decomposed with halo_width >= 2
  * (xstart, ystart >= 3); u,v,p valid to depth 2 and uold,vold,pold valid to depth 1 around the
- * box; `tdt` = 2*dt (not the first step); no tmask; even pitch.  Writes u2,v2,p2 (step n+2)
+ * box; `tdt` = 2*dt (not the first step); even pitch.  `tmask` (may be NULL; int32, pitch a
+ * multiple of 4) must hold the periodic mask two cells deep around the box -- grid_init
+ * replicates outward beyond the first ring, dlesm_sw_set_two_step builds the wrapped copy.  Writes u2,v2,p2 (step n+2)
  * and the twice-filtered uold2,vold2,pold2 on the box -- separate arrays, not in place.  Halos
  * of the outputs are NOT filled (dlesm_dev_periodic_halos_deep / halo_exchange(depth 2)) unless
  * DLESM_FUSED_PUSH is ORed into `variant`: then the sweep pushes them into the neighbours' arrays
@@ -436,7 +438,8 @@ int dlesm_sw_step_fused(const void *u, const void *v, const void *p, void *uold,
 int dlesm_sw_step2_fused(const void *u, const void *v, const void *p, const void *uold,
                          const void *vold, const void *pold, void *u2, void *v2, void *p2,
                          void *uold2, void *vold2, void *pold2, double dx, double dy, double tdt,
-                         double alpha, int xstart, int xstop, int ystart, int ystop, int variant);
+                         double alpha, int xstart, int xstop, int ystart, int ystop, const void *tmask,
+                         int variant);
 /* periodic halo fill of one field to `depth` cells on one rank (the reference's lists,
  * src/field_mod.f90:1394-1464, are one cell deep; depth 1 == dlesm_dev_periodic_halos) */
 int dlesm_dev_periodic_halos_deep(void *f, int xstart, int xstop, int ystart, int ystop, int depth);
@@ -481,7 +484,8 @@ int dlesm_sw_set_variant(dlesm_sw_t *s, int variant);
 int dlesm_sw_set_halo_mode(dlesm_sw_t *s, int mode);
 /* on != 0: dlesm_sw_step advances two steps per sweep (dlesm_sw_step2_fused) whenever at least
  * two steps remain and the first step is behind; an odd remainder runs the one-step sweep.
- * Needs the fused mode, no tmask, an even pitch and a grid decomposed with halo_width >= 2;
+ * Needs the fused mode, an even pitch (a multiple of 4 with a tmask) and a grid decomposed with
+ * halo_width >= 2;
  * halos are then kept two cells deep (periodic copies on one rank, halo_exchange(depth 2) on
  * several -- DLESM_EXT_HALO_DEPTH).  Allocates three more fields.  With DLESM_HALO_PUSH (either
  * call order; both collective) the two-step sweep stores the neighbours' halo cells of its six

@@ -642,16 +642,20 @@ def test_halo_push_needs_registration_and_tma_pitch(monkeypatch):
 # ---------------------------------------------------------------------------------------------
 # two model steps per sweep (temporal blocking) on a tile with halo width 2
 # ---------------------------------------------------------------------------------------------
-def sw_pair_hw2(n_x, n_y, alignment, monkeypatch, **kw):
+def sw_pair_hw2(n_x, n_y, alignment, monkeypatch, tmask=None, **kw):
     """oracle on the reference's width-1 grid; product on the same domain decomposed with
     halo_width=2 (internal region starts at 3), same internal values, wrapped halos"""
     if alignment:
         monkeypatch.setenv("DL_ESM_ALIGNMENT", str(alignment))
-    osw = O.ShallowWater(n_x, n_y, alignment=alignment or 1, **kw)
+    osw = O.ShallowWater(n_x, n_y, alignment=alignment or 1, tmask=tmask, **kw)
     g = fd.grid_type(fd.GO_ARAKAWA_C, BCS_PER, fd.GO_OFFSET_SW)
     g.decompose(n_x, n_y, halo_width=2)
-    fd.grid_init(g, kw.get("dx", 1.0e5), kw.get("dy", 1.0e5))
-    sw = fd.shallow_water(g, dt=kw.get("dt", 90.0), alpha=kw.get("alpha", 0.001), mode=fd.SW_FUSED)
+    tm2 = None
+    if tmask is not None:      # the same mask on the (n+4)^2 extent of the width-2 tile
+        tm2 = np.asfortranarray(np.pad(tmask[1:-1, 1:-1], 2, mode="wrap").astype(np.int32))
+    fd.grid_init(g, kw.get("dx", 1.0e5), kw.get("dy", 1.0e5), tm2)
+    sw = fd.shallow_water(g, dt=kw.get("dt", 90.0), alpha=kw.get("alpha", 0.001), mode=fd.SW_FUSED,
+                          use_tmask=tmask is not None)
     oi = osw.fb["t"].internal
     ii = sw.field("p").internal
     assert (ii.xstart, ii.ystart, ii.nx, ii.ny) == (3, 3, n_x, n_y)
@@ -737,6 +741,34 @@ def test_two_step_sweep_with_halo_push(order, n_x, n_y, align, nsteps, monkeypat
         want = np.pad(osw.f["p"][oi.xstart - 1:oi.xstop, oi.ystart - 1:oi.ystop], 2, mode="wrap")
         got = sw.field("p").get_data()[ii.xstart - 3:ii.xstop + 2, ii.ystart - 3:ii.ystop + 2]
         assert np.array_equal(got, want)
+    finally:
+        _lib.lib().dlesm_reset_saved_state()
+
+
+@pytest.mark.parametrize("push", [False, True])
+@pytest.mark.parametrize("variant2", [0, 11, 12, 13, 14, 15, 16])
+@pytest.mark.parametrize("n_x,n_y,align,seed,nsteps", [(96, 80, 4, None, 7), (70, 51, 64, 12345, 6),
+                                                       (300, 523, 64, None, 5), (512, 512, 64, None, 8)])
+def test_two_step_sweep_with_tmask(push, variant2, n_x, n_y, align, seed, nsteps, monkeypatch):
+    """BASELINE config 3 pattern on the two-step sweep: land islands / LCG 3 % land, masked rule of
+    the oracle (dry points keep their value, are not filtered), bit for bit; the mask ring two cells
+    deep is the wrapped one the sweep needs, not grid_init's outward replication"""
+    if push and variant2 not in (0, 14):
+        pytest.skip("push x variant covered by the unmasked tests")
+    try:
+        tm = periodic_island_mask(n_x + 2, n_y + 2, seed)
+        assert (tm == 0).any()
+        osw, sw = sw_pair_hw2(n_x, n_y, align, monkeypatch, tmask=tm)
+        sw.set_two_step(True, variant2)
+        if push:
+            sw.set_halo_mode(fd.HALO_PUSH)
+        for _ in range(nsteps):
+            osw.step()
+        sw.step(nsteps)
+        assert_internal_equal(osw, sw, halo=1)
+        osw.step(); osw.step(); osw.step()
+        sw.step(3)
+        assert_internal_equal(osw, sw, halo=1)
     finally:
         _lib.lib().dlesm_reset_saved_state()
 
