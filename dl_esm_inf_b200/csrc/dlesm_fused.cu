@@ -61,7 +61,9 @@ struct Outs {
 
 // One marching step: raw row N = row j arrives; produces outputs of row j-1.
 // Expression trees are those of oracle/dlesm_oracle_sw.c (SURVEY.md a-S), term by term.
-template <bool M>
+// APPLY = false on a masked run skips the mask selects (the caller has established that every
+// mask value this step looks at is wet); the masks are still carried along.
+template <bool M, bool APPLY = M>
 __device__ __forceinline__ void ingest(Carry<M> &c, const Raw<M> &N, const SwScalars &sc, double uo,
                                        double vo, double po, Outs &o)
 {
@@ -74,7 +76,7 @@ __device__ __forceinline__ void ingest(Carry<M> &c, const Raw<M> &N, const SwSca
     double zE_N = (sc.fsdx * (N.vE - N.vC) - sc.fsdy * (N.uE - P.uE)) / (P.pC + P.pE + N.pE + N.pC);
     double hC_P = P.pC + 0.25 * (P.uE * P.uE + P.uC * P.uC + N.vC * N.vC + P.vC * P.vC);
     double hW_P = P.pW + 0.25 * (P.uC * P.uC + P.uW * P.uW + N.vW * N.vW + P.vW * P.vW);
-    if (M) {
+    if (APPLY) {
         if (!(N.tC && N.tW)) cuC_N = 0.0;
         if (!(N.tE && N.tC)) cuE_N = 0.0;
         if (!(N.tC && P.tC)) cvC_N = 0.0;
@@ -90,7 +92,7 @@ __device__ __forceinline__ void ingest(Carry<M> &c, const Raw<M> &N, const SwSca
              sc.tdtsdy * (hC_P - c.hC_PP);
     o.pnew = po - sc.tdtsdx * (c.cuE_P - c.cuC_P) - sc.tdtsdy * (cvC_N - c.cvC_P);
     o.wu = o.wv = o.wt = true;
-    if (M) {
+    if (APPLY) {
         o.wu = P.tC && P.tW;
         o.wv = P.tC && c.tC_PP;
         o.wt = P.tC;
@@ -349,6 +351,7 @@ fused_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_constant
             if (i >= g.i0 && i <= g.i1 && g.j1 >= j0 && g.j0 <= j1) pmask |= 1u << q;
         }
     int jrow = j0 - 2;
+    bool wet0 = true, wet1 = true, wet2 = true;   // warp-wide "row all wet", newest first (masked runs)
     for (int c = 0; c < nchunks; ++c) {
         const int s = c % STAGES;
         mbar_wait(&full[s], (c / STAGES) & 1);
@@ -371,7 +374,16 @@ fused_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_constant
             }
             const double uo = suo[r * BWO], vo = svo[r * BWO], po = spo[r * BWO];
             Outs out;
-            ingest<M>(cr, N, sc, uo, vo, po, out);
+            if (M) {
+                // rows j, j-1, j-2 all wet across the warp's columns and their neighbours
+                // (warp-uniform): the unmasked march gives the same bits without the selects
+                wet2 = wet1; wet1 = wet0;
+                wet0 = __all_sync(0xffffffffu, N.tW && N.tC && N.tE);
+                if (wet0 && wet1 && wet2) ingest<M, false>(cr, N, sc, uo, vo, po, out);
+                else ingest<M, true>(cr, N, sc, uo, vo, po, out);
+            } else {
+                ingest<M>(cr, N, sc, uo, vo, po, out);
+            }
             if (r >= t_lo && r < t_hi) {
                 __stcs(prm.unew + qo, out.unew);
                 __stcs(prm.vnew + qo, out.vnew);
@@ -730,7 +742,8 @@ __device__ __forceinline__ void carry_init(CarryS &c)
     c.P.uC = c.P.uE = c.P.vW = c.P.vC = 0.0;
     c.cuC_P = c.cuE_P = c.cuC_PP = c.cuE_PP = c.cvC_P = c.cvW_P = c.zC_P = c.zE_P = c.hC_PP = 0.0;
 }
-// tC, tW: tmask == 1 at row N for the own and the west column (M only).  The masked rule is the
+// tC, tW: tmask == 1 at row N for the own and the west column (M only; the caller rotates the
+// carried masks with rotate_masks afterwards, so that an all-wet warp can take ingest_sh<false>).  The masked rule is the
 // one of ingest<true>: intermediates are 0 unless every T cell they straddle is wet, a dry
 // prognostic point keeps its value and is not filtered -- the neighbours' copies arrive masked.
 template <bool M>
@@ -773,9 +786,6 @@ __device__ __forceinline__ void ingest_sh(CarryS &c, const RawS &N, bool tC, boo
         if (!wu) o.uold = uo;
         if (!wv) o.vold = vo;
         if (!wt) o.pold = po;
-        c.tC_PP = c.tC_P;
-        c.tC_P = tC;
-        c.tW_P = tW;
     }
     c.cuC_PP = c.cuC_P; c.cuE_PP = c.cuE_P;
     c.cuC_P = cuC_N; c.cuE_P = cuE_N;
@@ -783,6 +793,13 @@ __device__ __forceinline__ void ingest_sh(CarryS &c, const RawS &N, bool tC, boo
     c.zC_P = zC_N; c.zE_P = zE_N;
     c.hC_PP = hC_P;
     c.P = N;
+}
+
+__device__ __forceinline__ void rotate_masks(CarryS &c, bool tC, bool tW)
+{
+    c.tC_PP = c.tC_P;
+    c.tC_P = tC;
+    c.tW_P = tW;
 }
 
 template <int TX, int RY, int STAGES, bool M = false>
@@ -875,6 +892,7 @@ fused2s_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_consta
     carry_init(ca);
     carry_init(cb);
     double uo1 = 0.0, vo1 = 0.0, po1 = 0.0;
+    bool wet0 = true, wet1 = true, wet2 = true, wet3 = true;   // warp-wide "row all wet", newest first
     long long qo = (static_cast<long long>(j0) - 5) * prm.pitch + (i - 1);
     const long long pitch = prm.pitch;
     int t_lo = active ? 4 : (1 << 30), t_hi = nsteps;
@@ -902,6 +920,7 @@ fused2s_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_consta
         const int *sm = reinterpret_cast<const int *>(st + Cfg::OFF_MASK) + colm;
         double uo_r[RY], vo_r[RY], po_r[RY];
         bool tbC[RY], tbW[RY];   // stage B's row is stage A's previous row: its masks are A's carried ones
+        bool fastB[RY];
 #pragma unroll
         for (int r = 0; r < RY; ++r) {
             RawS N;
@@ -909,13 +928,24 @@ fused2s_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_consta
             N.uC = su[r * BW + 1]; N.uE = su[r * BW + 2];
             N.vW = sv[r * BW]; N.vC = sv[r * BW + 1];
             bool tC = true, tW = true;
+            Outs o;
             if (M) {
                 tC = sm[r * BWM] == 1;
                 tW = __shfl_up_sync(0xffffffffu, static_cast<int>(tC), 1) != 0;
                 tbC[r] = ca.tC_P; tbW[r] = ca.tW_P;
+                // rows N, P, PP all wet across the warp (warp-uniform): the unmasked march gives the
+                // same bits without the selects -- almost every warp-row away from the islands
+                wet3 = wet2; wet2 = wet1; wet1 = wet0;
+                wet0 = __all_sync(0xffffffffu, tC);
+                fastB[r] = wet1 && wet2 && wet3;
+                if (wet0 && wet1 && wet2)
+                    ingest_sh<false>(ca, N, true, true, sc, suo[r * BWO], svo[r * BWO], spo[r * BWO], o);
+                else
+                    ingest_sh<true>(ca, N, tC, tW, sc, suo[r * BWO], svo[r * BWO], spo[r * BWO], o);
+                rotate_masks(ca, tC, tW);
+            } else {
+                ingest_sh<false>(ca, N, true, true, sc, suo[r * BWO], svo[r * BWO], spo[r * BWO], o);
             }
-            Outs o;
-            ingest_sh<M>(ca, N, tC, tW, sc, suo[r * BWO], svo[r * BWO], spo[r * BWO], o);
             if (a_writes) {
                 xb[(0 * RY + r) * XW] = o.unew;
                 xb[(1 * RY + r) * XW] = o.vnew;
@@ -932,7 +962,13 @@ fused2s_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_consta
             N.vW = xb[(1 * RY + r) * XW - 1]; N.vC = xb[(1 * RY + r) * XW];
             N.pW = xb[(2 * RY + r) * XW - 1]; N.pC = xb[(2 * RY + r) * XW];
             Outs o;
-            ingest_sh<M>(cb, N, M ? tbC[r] : true, M ? tbW[r] : true, sc, uo1, vo1, po1, o);
+            if (M) {
+                if (fastB[r]) ingest_sh<false>(cb, N, true, true, sc, uo1, vo1, po1, o);
+                else ingest_sh<true>(cb, N, tbC[r], tbW[r], sc, uo1, vo1, po1, o);
+                rotate_masks(cb, tbC[r], tbW[r]);
+            } else {
+                ingest_sh<false>(cb, N, true, true, sc, uo1, vo1, po1, o);
+            }
             uo1 = uo_r[r]; vo1 = vo_r[r]; po1 = po_r[r];
             if (r >= t_lo && r < t_hi) {
                 __stcs(prm.u2 + qo, o.unew);

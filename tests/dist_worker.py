@@ -290,13 +290,23 @@ def case_gather():
         ok(np.array_equal(recv, want), "gather differs")
 
 
-def case_shallow_water(n_x, n_y, nsteps, alignment, mode, halo_mode=None, two_step=False):
+def island_mask(n_x, n_y):
+    """land islands on the global (n_x, n_y) T points (the pattern of tests/test_gpu_parity.py)"""
+    i = np.arange(1, n_x + 1)[:, None]
+    j = np.arange(1, n_y + 1)[None, :]
+    land = ((i % 64 >= 20) & (i % 64 <= 27)) & ((j % 64 >= 30) & (j % 64 <= 37))
+    return np.where(land, 0, 1).astype(np.int32)
+
+
+def case_shallow_water(n_x, n_y, nsteps, alignment, mode, halo_mode=None, two_step=False, masked=False):
     """periodic shallow water across ranks (extension F4) == the serial oracle, bit for bit;
     halo_mode HALO_PUSH: the fused sweep stores the neighbours' halo cells itself (NVLink peer
     memory + flag hand-shake) instead of pack -> NCCL -> unpack"""
     os.environ["DL_ESM_ALIGNMENT"] = str(alignment)
     fd.set_extensions(fd.EXT_PERIODIC_DISTMEM | (fd.EXT_HALO_DEPTH if two_step else 0))
-    osw = O.ShallowWater(n_x, n_y, alignment=1)
+    gmask = island_mask(n_x, n_y) if masked else None
+    osw = O.ShallowWater(n_x, n_y, alignment=1,
+                         tmask=np.asfortranarray(np.pad(gmask, 1, mode="wrap")) if masked else None)
     init = {k: osw.f[k].copy(order="F") for k in ("u", "v", "p")}
     for _ in range(nsteps):
         osw.step()
@@ -307,8 +317,15 @@ def case_shallow_water(n_x, n_y, nsteps, alignment, mode, halo_mode=None, two_st
         g.decompose(n_x, n_y, halo_width=2)
     else:
         g.decompose(n_x, n_y)
-    fd.grid_init(g, 1.0e5, 1.0e5)
-    sw = fd.shallow_water(g, mode=mode)
+    tm = None
+    if masked:
+        # this tile's part of the global mask over its whole extent (halo cells wrap around)
+        sb, hw = g.subdomain, g.subdomain.internal.xstart - 1
+        mi = (sb.glob.xstart - 1 - hw + np.arange(sb.glob.nx)) % n_x
+        mj = (sb.glob.ystart - 1 - hw + np.arange(sb.glob.ny)) % n_y
+        tm = np.asfortranarray(gmask[np.ix_(mi, mj)])
+    fd.grid_init(g, 1.0e5, 1.0e5, tm)
+    sw = fd.shallow_water(g, mode=mode, use_tmask=masked)
     if two_step:
         sw.set_two_step(True)
         if halo_mode is not None:
@@ -373,6 +390,12 @@ def main():
     for shape in ((64, 96, 6, 2), (130, 77, 7, 64), (300, 523, 8, 64), (1024, 1024, 9, 64)):
         case_shallow_water(*shape, fd.SW_FUSED, two_step=True)
         case_shallow_water(*shape, fd.SW_FUSED, halo_mode=fd.HALO_PUSH, two_step=True)
+    # tmask with land points across ranks (config 3 pattern): one-step sweep, then the two-step sweep
+    # whose mask ring two cells deep comes from one depth-2 exchange of the mask
+    for shape in ((130, 77, 6, 64), (300, 523, 7, 64)):
+        case_shallow_water(*shape, fd.SW_FUSED, masked=True)
+        case_shallow_water(*shape, fd.SW_FUSED, two_step=True, masked=True)
+        case_shallow_water(*shape, fd.SW_FUSED, halo_mode=fd.HALO_PUSH, two_step=True, masked=True)
     dist.barrier()
     fd.gocean_finalise()
     if RANK == 0:
