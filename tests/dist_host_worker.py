@@ -198,6 +198,42 @@ def case_depth(nx, ny, depth):
     fd.gocean_initialise(RANK + 1, WORLD)            # go_decompose's SAVEd halo width back to 1
 
 
+def case_depth_periodic(nx, ny, depth=2):
+    """the tables the two-step sweep runs on (both extensions): periodic wrap AND depth 2 on a tile
+    with halo_width 2 -- used by its halo_exchange(depth 2) and, entry for entry, as its push
+    boxes.  Known answer: every cell within `depth` of the internal region, corners included,
+    holds the periodic global field at the wrapped position; source boxes lie inside the internal
+    region (so pushing them from the sweep equals exchanging them afterwards)."""
+    os.environ.pop("DL_ESM_ALIGNMENT", None)
+    fd.set_extensions(fd.EXT_PERIODIC_DISTMEM | fd.EXT_HALO_DEPTH)
+    g = fd.grid_type(fd.GO_ARAKAWA_C, (fd.GO_BC_PERIODIC, fd.GO_BC_PERIODIC, fd.GO_BC_NONE), fd.GO_OFFSET_SW)
+    g.decompose(nx, ny, halo_width=depth)
+    fd.grid_init(g, 1.0, 1.0)
+    c = fd.map_comms(g.decomp, pbc=(True, True), halo_depths=(depth, depth))
+    plan = comm_plan(c)
+    tables_pair_up(c)
+    sub = g.subdomain
+    li = sub.internal
+    for q in range(c.nsend):
+        ok(li.xstart <= c.isrcsend[q] and c.isrcsend[q] + c.nxsend[q] - 1 <= li.xstop and
+           li.ystart <= c.jsrcsend[q] and c.jsrcsend[q] + c.nysend[q] - 1 <= li.ystop,
+           "send box %d leaves the internal region" % q)
+    G = np.asfortranarray(np.random.default_rng(99 + nx + ny).uniform(-1, 1, size=(nx, ny)))
+    a = np.full((g.nx, g.ny), -7.0, order="F")
+    gi = sub.glob.xstart + np.arange(li.nx) - 1
+    gj = sub.glob.ystart + np.arange(li.ny) - 1
+    a[li.xstart - 1:li.xstop, li.ystart - 1:li.ystop] = G[np.ix_(gi, gj)]
+    gloo_exchange(a, c, plan)
+    ji = np.arange(li.xstart - depth, li.xstop + depth + 1)
+    jj = np.arange(li.ystart - depth, li.ystop + depth + 1)
+    wi = (sub.glob.xstart + (ji - li.xstart) - 1) % nx
+    wj = (sub.glob.ystart + (jj - li.ystart) - 1) % ny
+    ok(np.array_equal(a[np.ix_(ji - 1, jj - 1)], G[np.ix_(wi, wj)]),
+       "periodic depth-%d exchange (%dx%d) does not reproduce the serial periodic halo" % (depth, nx, ny))
+    fd.set_extensions(0)
+    fd.gocean_initialise(RANK + 1, WORLD)            # go_decompose's SAVEd halo width back to 1
+
+
 def main():
     dist.init_process_group("gloo")
     fd.gocean_initialise(RANK + 1, WORLD)            # host only: no device, no NCCL
@@ -217,6 +253,8 @@ def main():
     for shape in ((10, 10), (37, 23), (64, 48)):
         case_depth(*shape, 2)
     case_depth(40, 36, 3)
+    for shape in ((16, 24), (37, 23), (64, 48)):
+        case_depth_periodic(*shape)
     dist.barrier()
     if RANK == 0:
         print("HOST DIST OK %d checks on %d ranks" % (NCHECK, WORLD), flush=True)
