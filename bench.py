@@ -485,6 +485,38 @@ def run_e2e(args, fd, L, sw, grid, total_points, dist, torch):
         out["host_checksums_u_v_p"] = cks
     for p, _ in host:
         L.dlesm_host_free(p)
+    # the bound of this path is the PCIe link, both directions at once: measure it the plain way
+    # (two 1 GiB pinned buffers, one copy per direction on its own stream, CUDA events) and state
+    # the step's traffic against it
+    try:
+        nb = 1 << 30
+        h_up = torch.empty(nb, dtype=torch.uint8).pin_memory()
+        h_dn = torch.empty(nb, dtype=torch.uint8).pin_memory()
+        d_up = torch.empty(nb, dtype=torch.uint8, device="cuda")
+        d_dn = torch.empty(nb, dtype=torch.uint8, device="cuda")
+        s_up, s_dn = torch.cuda.Stream(), torch.cuda.Stream()
+        best = 0.0
+        for it in range(4):
+            torch.cuda.synchronize()
+            e0, e1, e2, e3 = (torch.cuda.Event(enable_timing=True) for _ in range(4))
+            with torch.cuda.stream(s_up):
+                e0.record()
+                d_up.copy_(h_up, non_blocking=True)
+                e1.record()
+            with torch.cuda.stream(s_dn):
+                e2.record()
+                h_dn.copy_(d_dn, non_blocking=True)
+                e3.record()
+            torch.cuda.synchronize()
+            ms_both = max(e0.elapsed_time(e1), e2.elapsed_time(e3))
+            if it > 0:
+                best = max(best, nb / (ms_both * 1e-3) / 1e9)
+        out["pcie_GBs_per_direction_both_busy_measured"] = best
+        out["pcie_GBs_per_direction_achieved"] = 6 * nbytes / (el / args.e2e_steps * 1e-3) / 1e9
+        out["frac_of_pcie"] = out["pcie_GBs_per_direction_achieved"] / best if best > 0 else None
+        del h_up, h_dn, d_up, d_dn
+    except Exception as exc:          # the measurement is informational
+        out["pcie_note"] = "bidirectional copy probe failed: %s" % exc
     return out
 
 
