@@ -390,6 +390,11 @@ def main():
     for shape in ((64, 96, 6, 2), (130, 77, 7, 64), (300, 523, 8, 64), (1024, 1024, 9, 64)):
         case_shallow_water(*shape, fd.SW_FUSED, two_step=True)
         case_shallow_water(*shape, fd.SW_FUSED, halo_mode=fd.HALO_PUSH, two_step=True)
+    # tile widths that differ by one across ranks with DL_ESM_ALIGNMENT=2: the neighbours' pitches
+    # differ (x split, 4+ ranks), so every push box uses the destination's pitch
+    case_shallow_water(131, 77, 6, 2, fd.SW_FUSED, halo_mode=fd.HALO_PUSH)
+    case_shallow_water(131, 77, 7, 2, fd.SW_FUSED, two_step=True)
+    case_shallow_water(131, 77, 7, 2, fd.SW_FUSED, halo_mode=fd.HALO_PUSH, two_step=True)
     # tmask with land points across ranks (config 3 pattern): one-step sweep, then the two-step sweep
     # whose mask ring two cells deep comes from one depth-2 exchange of the mask
     for shape in ((130, 77, 6, 64), (300, 523, 7, 64)):
