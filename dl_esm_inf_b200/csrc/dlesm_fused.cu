@@ -1148,8 +1148,8 @@ cudaError_t launch_tma2_generic(const Fused2Args &a, cudaStream_t s, Kern kern)
         // every segment recomputes two rows of the intermediate state and re-reads four raw rows,
         // so segments are longer than the one-step sweep's; DLESM_SEG_ROWS2 overrides
         const char *e = std::getenv("DLESM_SEG_ROWS2");
-        const int v = e ? std::atoi(e) : 124;
-        return v < 8 ? 124 : v;
+        const int v = e ? std::atoi(e) : 252;
+        return v < 8 ? 252 : v;
     }();
     const int seg_rows = pick_seg_rows(w, h, Cfg::OUT, 148 * MINB, RY, target, 4);
     prm.pitch = a.pitch; prm.b = a.b; prm.seg_rows = seg_rows; prm.sc = a.sc;
@@ -1191,8 +1191,8 @@ cudaError_t launch_tma2s_m(const Fused2Args &a, cudaStream_t s)
     const int w = a.b.xe - a.b.xs + 1, h = a.b.ye - a.b.ys + 1;
     static const int target = [] {
         const char *e = std::getenv("DLESM_SEG_ROWS2");
-        const int v = e ? std::atoi(e) : 124;
-        return v < 8 ? 124 : v;
+        const int v = e ? std::atoi(e) : 252;
+        return v < 8 ? 252 : v;
     }();
     const int seg_rows = pick_seg_rows(w, h, Cfg::OUT, 148 * MINB, RY, target, 4);
     prm.pitch = a.pitch; prm.b = a.b; prm.seg_rows = seg_rows; prm.sc = a.sc;
