@@ -1,9 +1,6 @@
 #!/bin/bash
-# banded host step: parity + e2e timing at a few band heights
 mkdir -p gpurun_out
-python -m pytest tests/test_gpu_parity.py -q -x -k "step_host" > gpurun_out/pytest_step_host.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_step_host.log
-tail -3 gpurun_out/pytest_step_host.log
-for br in 0 64 256 1024; do
-  python bench.py --steps 5 --warmup 3 --no-cpu-baseline --e2e-steps 3 --band-rows $br > gpurun_out/e2e_band$br.log 2>&1
-  echo "band $br rc=$?"; grep -o '"e2e": {[^}]*}[^}]*}' gpurun_out/e2e_band$br.log | cut -c1-400
+for br in 0 64 256 512 1024; do
+  timeout 300 python bench.py --sweep one --steps 6 --warmup 3 --e2e-steps 4 --band-rows $br --no-cpu-baseline > gpurun_out/r01t_e2e.log 2>&1
+  grep '^{' gpurun_out/r01t_e2e.log | python -c "import sys,json; d=json.loads(sys.stdin.read()); e=d['e2e']; print('band $br', round(e['ms_per_step'],1), round(e['pcie_GBs_per_direction_achieved'],1), round(e['pcie_GBs_per_direction_both_busy_measured'],1), round(e['frac_of_pcie'],3))"
 done
