@@ -838,11 +838,27 @@ fused2s_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_consta
     uint64_t *full = reinterpret_cast<uint64_t *>(fused_smem + Cfg::BAR_OFFSET);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int j0 = prm.b.ys + blockIdx.y * prm.seg_rows;
+    // CTA -> (strip, segment).  With halo push the two x-edge strips store into the neighbours' columns on
+    // every row and run noticeably longer; launched last they are the tail of a short sweep (8192x4096
+    // tile: +10 %), so they are mapped to the lowest block ids and start in the first wave.
+    int bx = blockIdx.x, by = blockIdx.y;
+    if (prm.push.n > 0 && gridDim.x > 2) {
+        const int S = gridDim.x, G = gridDim.y;
+        const int L = blockIdx.y * S + blockIdx.x;
+        if (L < 2 * G) {
+            bx = L < G ? 0 : S - 1;
+            by = L < G ? L : L - G;
+        } else {
+            const int Lr = L - 2 * G;
+            bx = 1 + Lr % (S - 2);
+            by = Lr / (S - 2);
+        }
+    }
+    const int j0 = prm.b.ys + by * prm.seg_rows;
     const int j1 = min(j0 + prm.seg_rows - 1, prm.b.ye);
     const int nsteps = (j1 - j0 + 1) + 4;            // raw rows j0-2 .. j1+2
     const int nchunks = (nsteps + RY - 1) / RY;
-    const int i_first = prm.b.xs + blockIdx.x * Cfg::OUT;   // first output column of this CTA
+    const int i_first = prm.b.xs + bx * Cfg::OUT;   // first output column of this CTA
     // lane column (both stages): i_first + 30*warp + lane - 2
     const int x_box = (i_first - 4) & ~1;   // even 0-based column at/below stage A lane 0's west neighbour
     const int x_old = (i_first - 3) & ~1;   // even 0-based column at/below stage A lane 0's own column
