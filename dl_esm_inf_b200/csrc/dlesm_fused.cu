@@ -284,11 +284,26 @@ fused_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_constant
     uint64_t *empty = full + STAGES;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int j0 = prm.b.ys + blockIdx.y * prm.seg_rows;
+    // with halo push the x-edge strips (they store into the neighbours' columns on every row) get
+    // the lowest block ids, so that they are not the tail of a short sweep
+    int bx = blockIdx.x, by = blockIdx.y;
+    if (prm.push.n > 0 && gridDim.x > 2) {
+        const int S = gridDim.x, G = gridDim.y;
+        const int L = blockIdx.y * S + blockIdx.x;
+        if (L < 2 * G) {
+            bx = L < G ? 0 : S - 1;
+            by = L < G ? L : L - G;
+        } else {
+            const int Lr = L - 2 * G;
+            bx = 1 + Lr % (S - 2);
+            by = Lr / (S - 2);
+        }
+    }
+    const int j0 = prm.b.ys + by * prm.seg_rows;
     const int j1 = min(j0 + prm.seg_rows - 1, prm.b.ye);
     const int nsteps = (j1 - j0 + 1) + 2;            // raw rows j0-1 .. j1+1
     const int nchunks = (nsteps + RY - 1) / RY;
-    const int i_first = prm.i_origin + blockIdx.x * TX;   // first output column of this strip
+    const int i_first = prm.i_origin + bx * TX;   // first output column of this strip
 
     if (tid == 0) {
         if (smem_u32(fused_smem) & 127u) __trap();
@@ -350,6 +365,8 @@ fused_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_constant
             const PushSeg &g = prm.push.seg[q];
             if (i >= g.i0 && i <= g.i1 && g.j1 >= j0 && g.j0 <= j1) pmask |= 1u << q;
         }
+    const int pfirst = pmask ? __ffs(pmask) - 1 : 0;
+    const unsigned prest = pmask & (pmask - 1);
     int jrow = j0 - 2;
     bool wet0 = true, wet1 = true, wet2 = true;   // warp-wide "row all wet", newest first (masked runs)
     for (int c = 0; c < nchunks; ++c) {
@@ -393,7 +410,15 @@ fused_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_constant
                     if (!M || out.wv) __stcs(prm.vold + qo, out.vold);
                     if (!M || out.wt) __stcs(prm.pold + qo, out.pold);
                 }
-                if (pmask) push_row(prm.push, pmask, i, jrow, out.unew, out.vnew, out.pnew);
+                if (pmask) {
+                    // first box inline (an x-edge column meets it on every row), the rest out of line
+                    const PushSeg &g = prm.push.seg[pfirst];
+                    if (jrow >= g.j0 && jrow <= g.j1) {
+                        const size_t d = idx(g.dpitch, g.ides + (i - g.i0), g.jdes + (jrow - g.j0));
+                        g.dst[0][d] = out.unew; g.dst[1][d] = out.vnew; g.dst[2][d] = out.pnew;
+                    }
+                    if (prest) push_row(prm.push, prest, i, jrow, out.unew, out.vnew, out.pnew);
+                }
             }
             qo += pitch;
             ++jrow;
