@@ -20,7 +20,7 @@ def _latest(pattern):
 
 
 def test_our_arm_line_has_every_contract_key():
-    d = json.load(open(_latest("r01r_bench_n1.json")))
+    d = json.load(open(_latest("r01z_bench_n1.json")))
     for k in ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling",
               "vs_baseline", "dtype", "data", "config", "clocks", "e2e", "gpu_launches", "roofline", "cpu_baseline"):
         assert k in d, k
