@@ -284,26 +284,11 @@ fused_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_constant
     uint64_t *empty = full + STAGES;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    // with halo push the x-edge strips (they store into the neighbours' columns on every row) get
-    // the lowest block ids, so that they are not the tail of a short sweep
-    int bx = blockIdx.x, by = blockIdx.y;
-    if (prm.push.n > 0 && gridDim.x > 2) {
-        const int S = gridDim.x, G = gridDim.y;
-        const int L = blockIdx.y * S + blockIdx.x;
-        if (L < 2 * G) {
-            bx = L < G ? 0 : S - 1;
-            by = L < G ? L : L - G;
-        } else {
-            const int Lr = L - 2 * G;
-            bx = 1 + Lr % (S - 2);
-            by = Lr / (S - 2);
-        }
-    }
-    const int j0 = prm.b.ys + by * prm.seg_rows;
+    const int j0 = prm.b.ys + blockIdx.y * prm.seg_rows;
     const int j1 = min(j0 + prm.seg_rows - 1, prm.b.ye);
     const int nsteps = (j1 - j0 + 1) + 2;            // raw rows j0-1 .. j1+1
     const int nchunks = (nsteps + RY - 1) / RY;
-    const int i_first = prm.i_origin + bx * TX;   // first output column of this strip
+    const int i_first = prm.i_origin + blockIdx.x * TX;   // first output column of this strip
 
     if (tid == 0) {
         if (smem_u32(fused_smem) & 127u) __trap();
@@ -365,8 +350,6 @@ fused_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_constant
             const PushSeg &g = prm.push.seg[q];
             if (i >= g.i0 && i <= g.i1 && g.j1 >= j0 && g.j0 <= j1) pmask |= 1u << q;
         }
-    const int pfirst = pmask ? __ffs(pmask) - 1 : 0;
-    const unsigned prest = pmask & (pmask - 1);
     int jrow = j0 - 2;
     bool wet0 = true, wet1 = true, wet2 = true;   // warp-wide "row all wet", newest first (masked runs)
     for (int c = 0; c < nchunks; ++c) {
@@ -410,15 +393,7 @@ fused_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_constant
                     if (!M || out.wv) __stcs(prm.vold + qo, out.vold);
                     if (!M || out.wt) __stcs(prm.pold + qo, out.pold);
                 }
-                if (pmask) {
-                    // first box inline (an x-edge column meets it on every row), the rest out of line
-                    const PushSeg &g = prm.push.seg[pfirst];
-                    if (jrow >= g.j0 && jrow <= g.j1) {
-                        const size_t d = idx(g.dpitch, g.ides + (i - g.i0), g.jdes + (jrow - g.j0));
-                        g.dst[0][d] = out.unew; g.dst[1][d] = out.vnew; g.dst[2][d] = out.pnew;
-                    }
-                    if (prest) push_row(prm.push, prest, i, jrow, out.unew, out.vnew, out.pnew);
-                }
+                if (pmask) push_row(prm.push, pmask, i, jrow, out.unew, out.vnew, out.pnew);
             }
             qo += pitch;
             ++jrow;
@@ -863,22 +838,11 @@ fused2s_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_consta
     uint64_t *full = reinterpret_cast<uint64_t *>(fused_smem + Cfg::BAR_OFFSET);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    // CTA -> (strip, segment).  With halo push the two x-edge strips store into the neighbours' columns on
-    // every row and run noticeably longer; launched last they are the tail of a short sweep (8192x4096
-    // tile: +10 %), so they are mapped to the lowest block ids and start in the first wave.
-    int bx = blockIdx.x, by = blockIdx.y;
-    if (prm.push.n > 0 && gridDim.x > 2) {
-        const int S = gridDim.x, G = gridDim.y;
-        const int L = blockIdx.y * S + blockIdx.x;
-        if (L < 2 * G) {
-            bx = L < G ? 0 : S - 1;
-            by = L < G ? L : L - G;
-        } else {
-            const int Lr = L - 2 * G;
-            bx = 1 + Lr % (S - 2);
-            by = Lr / (S - 2);
-        }
-    }
+    // (Mapping the x-edge strips, which push on every row, to the lowest block ids removed the tail of
+    // short sweeps when those neighbours are the rank itself, but with REMOTE x neighbours it bunches
+    // ~100k single-cell NVLink stores into the first waves: 2x2 tiles, 4.8 -> 7.0 ms per launch.  Natural
+    // order spreads them over the sweep.)
+    const int bx = blockIdx.x, by = blockIdx.y;
     const int j0 = prm.b.ys + by * prm.seg_rows;
     const int j1 = min(j0 + prm.seg_rows - 1, prm.b.ye);
     const int nsteps = (j1 - j0 + 1) + 4;            // raw rows j0-2 .. j1+2
@@ -1189,8 +1153,8 @@ cudaError_t launch_tma2_generic(const Fused2Args &a, cudaStream_t s, Kern kern)
         // every segment recomputes two rows of the intermediate state and re-reads four raw rows,
         // so segments are longer than the one-step sweep's; DLESM_SEG_ROWS2 overrides
         const char *e = std::getenv("DLESM_SEG_ROWS2");
-        const int v = e ? std::atoi(e) : 252;
-        return v < 8 ? 252 : v;
+        const int v = e ? std::atoi(e) : 124;
+        return v < 8 ? 124 : v;
     }();
     const int seg_rows = pick_seg_rows(w, h, Cfg::OUT, 148 * MINB, RY, target, 4);
     prm.pitch = a.pitch; prm.b = a.b; prm.seg_rows = seg_rows; prm.sc = a.sc;
@@ -1232,8 +1196,8 @@ cudaError_t launch_tma2s_m(const Fused2Args &a, cudaStream_t s)
     const int w = a.b.xe - a.b.xs + 1, h = a.b.ye - a.b.ys + 1;
     static const int target = [] {
         const char *e = std::getenv("DLESM_SEG_ROWS2");
-        const int v = e ? std::atoi(e) : 252;
-        return v < 8 ? 252 : v;
+        const int v = e ? std::atoi(e) : 124;
+        return v < 8 ? 124 : v;
     }();
     const int seg_rows = pick_seg_rows(w, h, Cfg::OUT, 148 * MINB, RY, target, 4);
     prm.pitch = a.pitch; prm.b = a.b; prm.seg_rows = seg_rows; prm.sc = a.sc;
