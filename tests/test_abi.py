@@ -70,6 +70,14 @@ def test_device_entry_points_fail_loudly_without_gpu():
     with pytest.raises(fd.GoceanStop) as e:
         fd.r2d_field(g, fd.GO_T_POINTS)
     assert e.value.code == -20
+    # the sweeps and the deep halo fill refuse pointers they did not allocate: nothing computes on the host
+    bogus = [C.c_void_p(0x1000 + 64 * k) for k in range(12)]
+    rc = L.dlesm_sw_step2_fused(*bogus, 1.0, 1.0, 180.0, 0.001, 3, 10, 3, 10, None, 0)
+    assert rc < 0 and L.dlesm_last_error()
+    rc = L.dlesm_sw_step_fused(*bogus[:9], 1.0, 1.0, 180.0, 0.001, 0, 2, 9, 2, 9, None, 0)
+    assert rc < 0
+    rc = L.dlesm_dev_periodic_halos_deep(bogus[0], 3, 10, 3, 10, 2)
+    assert rc < 0
 
 
 def test_grid_constructor_validation():
