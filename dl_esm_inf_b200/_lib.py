@@ -83,6 +83,7 @@ _PI = C.POINTER(C.c_int)
 SIGNATURES = {
     "dlesm_last_error": (C.c_char_p, []),
     "dlesm_version": (C.c_char_p, []),
+    "dlesm_source_hash": (C.c_char_p, []),
     "dlesm_parallel_init": (_I, [_I, _I]),
     "dlesm_device_init": (_I, [_I]),
     "dlesm_comm_unique_id": (_I, [_V]),
@@ -117,6 +118,9 @@ SIGNATURES = {
     "dlesm_r2d_field_create": (_V, [_V, _I, _I, _PD, _I, _I]),
     "dlesm_field_get_info": (_I, [_V, C.POINTER(FieldInfo)]),
     "dlesm_field_grid": (_V, [_V]),
+    "dlesm_field_tile": (_I, [_V, _I, C.POINTER(Region), C.POINTER(Region)]),
+    "dlesm_field_halo_is_dirty": (_I, [_V, _I]),
+    "dlesm_field_set_halo_dirty": (_I, [_V]),
     "dlesm_grid_field_bounds": (_I, [_V, _I, C.POINTER(FieldInfo)]),
     "dlesm_field_set_data": (_I, [_V, _PD]),
     "dlesm_field_get_data": (_I, [_V, _PD]),
@@ -150,7 +154,11 @@ SIGNATURES = {
     "dlesm_dev_set_comms": (_I, [C.POINTER(Comms)]),
     "dlesm_dev_halo_exchange": (_I, [C.POINTER(_V), _I]),
     "dlesm_dev_peer_register": (_I, [C.POINTER(_V), _I]),
+    "dlesm_dev_peer_unregister": (_I, [C.POINTER(_V), _I]),
     "dlesm_dev_peer_unregister_all": (_I, []),
+    "dlesm_set_arith": (_I, [_I]),
+    "dlesm_get_arith": (_I, []),
+    "dlesm_dev_set_sweep_tiles": (_I, [_I, _I]),
     "dlesm_dev_grid_upload": (_I, [_I, _I, _PI, C.POINTER(_PD), C.POINTER(_V)]),
     "dlesm_compute_cu": (_I, [_V, _V, _V, _I, _I, _I, _I, _V]),
     "dlesm_compute_cv": (_I, [_V, _V, _V, _I, _I, _I, _I, _V]),
@@ -176,6 +184,8 @@ SIGNATURES = {
     "dlesm_profile_enable": (_I, [_I]),
     "dlesm_profile_read": (_I, [_PD, C.POINTER(C.c_longlong), _I]),
     "dlesm_sw_free": (None, [_V]),
+    "dlesm_sw_free_local": (None, [_V]),
+    "dlesm_sw_launch_grid": (_I, [_V, _I, _PI]),
     "dlesm_kernel_create": (_V, [C.c_char_p, C.c_char_p, C.POINTER(GoArg), _I, _I, _I]),
     "dlesm_kernel_generated_source": (C.c_char_p, [_V]),
     "dlesm_kernel_launch": (_I, [_V, C.POINTER(_V), _I, _PD, _I, _PI, _I]),

@@ -27,6 +27,8 @@ NONE, Iplus, Iminus, Jplus, Jminus, IplusJplus, IminusJminus, IplusJminus, Iminu
 MaxComm = 16
 EXT_PERIODIC_DISTMEM = 1
 EXT_HALO_DEPTH = 2
+EXT_DIRTY_HALOS = 4
+ARITH_EXACT, ARITH_CONTRACTED = 0, 1
 
 GRID_ARRAYS = ("tmask", "dx_t", "dy_t", "dx_u", "dy_u", "dx_v", "dy_v", "dx_f", "dy_f", "area_t",
                "area_u", "area_v", "gphiu", "gphiv", "gphif", "xt", "yt")
@@ -335,6 +337,19 @@ class r2d_field:
         """src/field_mod.f90:1231-1256"""
         _chk(_lib.lib().dlesm_field_halo_exchange(self._h, depth))
 
+    def tile(self, itile):
+        """tile(itile)%internal, %whole (src/field_mod.f90:316-319), 1 <= itile <= ntiles"""
+        a, b = Region(), Region()
+        _chk(_lib.lib().dlesm_field_tile(self._h, itile, C.byref(a), C.byref(b)))
+        return a, b
+
+    def halo_is_dirty(self, depth=1):
+        """halo_type%needs_update as a query (src/halo_mod.f90:10-40)"""
+        return bool(_lib.lib().dlesm_field_halo_is_dirty(self._h, depth))
+
+    def set_halo_dirty(self):
+        _chk(_lib.lib().dlesm_field_set_halo_dirty(self._h))
+
     def apply_periodic_halos(self):
         """for ihalo = 1..num_halos: copy_field(fld, halo%source, halo%dest) (SURVEY CS-6)"""
         _chk(_lib.lib().dlesm_field_apply_periodic_halos(self._h))
@@ -402,6 +417,21 @@ def kernel_launch_count():
     return _lib.lib().dlesm_kernel_launch_count()
 
 
+def set_arith(mode):
+    """ARITH_EXACT (one rounding per operation, bit-identical to the oracle) or ARITH_CONTRACTED
+    (FMA contraction in the fused sweeps; within 1e-12 relative of the exact results)"""
+    _chk(_lib.lib().dlesm_set_arith(mode))
+
+
+def get_arith():
+    return _lib.lib().dlesm_get_arith()
+
+
+def set_sweep_tiles(ntilex=0, ntiley=0):
+    """the tile grid of the sweeps, what GOCEAN_OMP_GRID="AxB" sets (0 = the library's choice)"""
+    _chk(_lib.lib().dlesm_dev_set_sweep_tiles(ntilex, ntiley))
+
+
 # --- application layer: shallow water ------------------------------------------------------------
 class shallow_water:
     """The GOcean "shallow" time-stepping driven over fd_lib fields (not part of the reference
@@ -462,14 +492,24 @@ class shallow_water:
     def checksums(self):
         return tuple(field_checksum(self.field(n)) for n in ("p", "u", "v"))
 
+    def launch_grid(self, two_step=False):
+        """(grid.x, grid.y) of the one-step or two-step sweep of this model"""
+        g = (C.c_int * 2)()
+        _chk(_lib.lib().dlesm_sw_launch_grid(self._h, int(bool(two_step)), g))
+        return g[0], g[1]
+
     def free(self):
+        """Collective when the object pushes halos on several ranks: call it on every rank."""
         if self._h:
             _lib.lib().dlesm_sw_free(self._h)
             self._h = None
 
     def __del__(self):
+        # a finaliser must never enter a collective: local release only
         try:
-            self.free()
+            if self._h:
+                _lib.lib().dlesm_sw_free_local(self._h)
+                self._h = None
         except Exception:
             pass
 

@@ -1,4 +1,4 @@
-// dlesm_fused.cu -- the whole shallow-water step as ONE sweep (96 B / point).
+// dlesm_fused.cu -- the whole shallow-water step as ONE sweep (96 B / point), and two steps as one.
 //
 // Every thread owns one column i and marches along j, carrying in registers everything the
 // next row reuses: the previous raw row of p,u,v (3 columns wide) and the intermediates
@@ -12,13 +12,18 @@
 // of p,u,v instead of being wrapped after the fact; with identical operands and -fmad=false
 // this gives the same bits as the reference-style sequence "sweep, halo-copy, sweep".
 //
+// This file is compiled TWICE (dl_esm_inf_b200/build.py): with -fmad=false into namespace
+// k::fma_off (one rounding per operation, bit-identical to the oracle) and with -fmad=true
+// -DDLESM_CONTRACTED into k::fma_on (the compiler contracts a*b+c into DFMA: fewer FP64
+// instructions, results within 1e-12 relative of the oracle).  dlesm_set_arith selects.
+//
 // Variants (dlesm_sw_step_fused's `variant`):
-//   1  direct : raw rows come straight from global memory through L1 (any pitch, tmask ok)
-//   2+ tma    : a producer warp streams row chunks of all six inputs into a shared-memory
-//               ring with cp.async.bulk.tensor (TMA) + mbarrier full/empty pairs; consumer
-//               warps march out of shared memory.  Needs a 16-byte-multiple pitch
-//               (DL_ESM_ALIGNMENT even), no tmask.
-//   0  auto   : tma when eligible, else direct.
+//   1     direct : raw rows come straight from global memory through L1 (any pitch, tmask ok)
+//   5, 23, 25 tma : a producer warp streams row chunks of all six inputs (and the byte image of
+//               the tmask) into a shared-memory ring with cp.async.bulk.tensor (TMA) + mbarrier
+//               full/empty pairs; consumer warps march out of shared memory.  Needs a
+//               16-byte-multiple pitch (DL_ESM_ALIGNMENT even).
+//   0     auto   : tma when eligible, else direct.
 #include <cuda.h>
 
 #include <cstdint>
@@ -26,11 +31,19 @@
 #include <map>
 #include <mutex>
 #include <tuple>
+#include <type_traits>
 
 #include "dlesm_kernels.cuh"
 
+#ifdef DLESM_CONTRACTED
+#define DLESM_FNS fma_on
+#else
+#define DLESM_FNS fma_off
+#endif
+
 namespace dlesm {
 namespace k {
+namespace DLESM_FNS {
 
 namespace {
 __host__ __device__ inline size_t idx(int pitch, int i, int j)
@@ -68,10 +81,12 @@ __device__ __forceinline__ void ingest(Carry<M> &c, const Raw<M> &N, const SwSca
                                        double vo, double po, Outs &o)
 {
     const Raw<M> &P = c.P;
-    double cuC_N = 0.5 * (N.pC + N.pW) * N.uC;
-    double cuE_N = 0.5 * (N.pE + N.pC) * N.uE;
-    double cvC_N = 0.5 * (N.pC + P.pC) * N.vC;
-    double cvW_N = 0.5 * (N.pW + P.pW) * N.vW;
+    // cu, cv are carried DOUBLED (the 0.5 of cu = 0.5*(p+p)*u is folded into tdts8h, tdtsdxh,
+    // tdtsdyh: an exact power-of-two rescaling, same bits; see SwScalars)
+    double cuC_N = (N.pC + N.pW) * N.uC;
+    double cuE_N = (N.pE + N.pC) * N.uE;
+    double cvC_N = (N.pC + P.pC) * N.vC;
+    double cvW_N = (N.pW + P.pW) * N.vW;
     double zC_N = (sc.fsdx * (N.vC - N.vW) - sc.fsdy * (N.uC - P.uC)) / (P.pW + P.pC + N.pC + N.pW);
     double zE_N = (sc.fsdx * (N.vE - N.vC) - sc.fsdy * (N.uE - P.uE)) / (P.pC + P.pE + N.pE + N.pC);
     double hC_P = P.pC + 0.25 * (P.uE * P.uE + P.uC * P.uC + N.vC * N.vC + P.vC * P.vC);
@@ -86,11 +101,11 @@ __device__ __forceinline__ void ingest(Carry<M> &c, const Raw<M> &N, const SwSca
         if (!P.tC) hC_P = 0.0;
         if (!P.tW) hW_P = 0.0;
     }
-    o.unew = uo + sc.tdts8 * (zC_N + c.zC_P) * (cvC_N + cvW_N + c.cvW_P + c.cvC_P) -
+    o.unew = uo + sc.tdts8h * (zC_N + c.zC_P) * (cvC_N + cvW_N + c.cvW_P + c.cvC_P) -
              sc.tdtsdx * (hC_P - hW_P);
-    o.vnew = vo - sc.tdts8 * (c.zE_P + c.zC_P) * (c.cuE_P + c.cuC_P + c.cuC_PP + c.cuE_PP) -
+    o.vnew = vo - sc.tdts8h * (c.zE_P + c.zC_P) * (c.cuE_P + c.cuC_P + c.cuC_PP + c.cuE_PP) -
              sc.tdtsdy * (hC_P - c.hC_PP);
-    o.pnew = po - sc.tdtsdx * (c.cuE_P - c.cuC_P) - sc.tdtsdy * (cvC_N - c.cvC_P);
+    o.pnew = po - sc.tdtsdxh * (c.cuE_P - c.cuC_P) - sc.tdtsdyh * (cvC_N - c.cvC_P);
     o.wu = o.wv = o.wt = true;
     if (APPLY) {
         o.wu = P.tC && P.tW;
@@ -210,12 +225,32 @@ __device__ __forceinline__ void tma_load_2d(void *dst, const CUtensorMap *map, i
         : "memory");
 }
 
+// How blockIdx maps to columns and rows: the CUDA tile grid (SweepTiles; the analogue of the
+// reference's OpenMP tiles, src/field_mod.f90:300-325).  x-tile `a` starts at x0 + a*tw + min(a, xextra)
+// and is tw (+1 for the first xextra tiles: go_decompose's remainder rule, src/parallel_mod.f90:211-223)
+// columns wide; it is cut into `strips` strips of the kernel's output width.  y-tile (segment) `by`
+// starts at ys + by*th + min(by, yextra) and is th (+1) rows long; one CTA marches it.
+struct TileMap {
+    int strips;
+    int x0, tw, xextra;
+    int th, yextra;
+};
+__device__ __forceinline__ void tile_of_block(const TileMap &t, const Box &b, int bx, int by, int out_cols,
+                                              int &i_first, int &i_last, int &j0, int &j1)
+{
+    const int a = bx / t.strips, sidx = bx - a * t.strips;
+    const int tx0 = t.x0 + a * t.tw + min(a, t.xextra);
+    i_first = tx0 + sidx * out_cols;
+    i_last = min(tx0 + t.tw + (a < t.xextra ? 1 : 0) - 1, b.xe);
+    j0 = b.ys + by * t.th + min(by, t.yextra);
+    j1 = min(j0 + t.th + (by < t.yextra ? 1 : 0) - 1, b.ye);
+}
+
 struct TmaStepParams {
     double *unew, *vnew, *pnew, *uold, *vold, *pold;
     int pitch;
     Box b;
-    int seg_rows;
-    int i_origin;   // first output column (1-based) of strip 0: b.xs, or lower to align strips to 128 B
+    TileMap tm;
     SwScalars sc;
     PushPlan push;
 };
@@ -237,28 +272,32 @@ __device__ __noinline__ void push_row(const PushPlan &pp, unsigned mask, int i, 
 }
 
 constexpr int kDefaultTmaVariant = 25;
+constexpr int kUnalignedTmaVariant = 5;   // strips start at the x-tile's first column (tiles.nx > 1)
 constexpr int align128(int v) { return (v + 127) & ~127; }
+constexpr int align16(int v) { return (v + 15) & ~15; }
 
 template <int TX, int RY, int STAGES, bool M, bool ALN>
 struct TmaCfg {
     // TMA needs the first element of a box 16-byte aligned (even FP64 column; measured with
     // tools/tma_probe.cu: an odd start column raises "illegal instruction").  Every tile
     // therefore starts at the even column at or below the strip's west halo column and is
-    // TX + 4 wide, which covers west halo + TX + east halo for either parity.  The int32
-    // tmask tile starts at a multiple of four columns and is TX + 8 wide for the same reason.
+    // TX + 4 wide, which covers west halo + TX + east halo for either parity.
     // uold/vold/pold need no halo columns: with the 128-byte aligned strip origin (ALN) their
     // tiles are exactly the TX output columns (whole 32-byte sectors, nothing shared with the
     // neighbouring strip); otherwise they start at the even column at or below the first one.
+    // The tmask rides the ring as its BYTE image (1 = wet; mask_to_bytes): the tile starts at the
+    // multiple of 16 columns at or below the west halo column and covers west halo + TX + east halo
+    // from any such start: 160 bytes per row for 128 columns (the int32 mask tile was 544).
     static constexpr int BW = TX + 4;
     static constexpr int BWO = ALN ? TX : TX + 2;
-    static constexpr int BWM = TX + 8;
+    static constexpr int BWM = align16(TX + 2 + 15);
     static constexpr int A = align128(BW * RY * 8);
     static constexpr int AO = align128(BWO * RY * 8);
-    static constexpr int AM = M ? align128(BWM * RY * 4) : 0;
+    static constexpr int AM = M ? align128(BWM * RY) : 0;
     static constexpr int OFF_OLD = 3 * A;
     static constexpr int OFF_MASK = 3 * A + 3 * AO;
     static constexpr int STAGE_BYTES = 3 * A + 3 * AO + AM;
-    static constexpr int TX_BYTES = 3 * BW * RY * 8 + 3 * BWO * RY * 8 + (M ? BWM * RY * 4 : 0);
+    static constexpr int TX_BYTES = 3 * BW * RY * 8 + 3 * BWO * RY * 8 + (M ? BWM * RY : 0);
     static constexpr int BAR_OFFSET = STAGES * STAGE_BYTES;
     static constexpr int SMEM_BYTES = BAR_OFFSET + 2 * STAGES * 8;
     static constexpr int THREADS = TX + 32;
@@ -284,11 +323,10 @@ fused_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_constant
     uint64_t *empty = full + STAGES;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int j0 = prm.b.ys + blockIdx.y * prm.seg_rows;
-    const int j1 = min(j0 + prm.seg_rows - 1, prm.b.ye);
+    int i_first, i_last, j0, j1;   // first output column of this strip, last column of its x-tile, rows
+    tile_of_block(prm.tm, prm.b, blockIdx.x, blockIdx.y, TX, i_first, i_last, j0, j1);
     const int nsteps = (j1 - j0 + 1) + 2;            // raw rows j0-1 .. j1+1
     const int nchunks = (nsteps + RY - 1) / RY;
-    const int i_first = prm.i_origin + blockIdx.x * TX;   // first output column of this strip
 
     if (tid == 0) {
         if (smem_u32(fused_smem) & 127u) __trap();
@@ -305,7 +343,7 @@ fused_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_constant
         // ---- producer warp: one lane feeds the ring ----
         if (lane == 0) {
             const int x_box = (i_first - 2) & ~1;   // even 0-based column at/below the west halo column
-            const int x_box_m = (i_first - 2) & ~3;
+            const int x_box_m = (i_first - 2) & ~15;
             const int x_old = (i_first - 1) & ~1;   // == i_first - 1 when ALN
             for (int c = 0; c < nchunks; ++c) {
                 const int s = c % STAGES;
@@ -331,9 +369,9 @@ fused_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_constant
     // rows of the array, or TMA's zero fill outside it); only the stores are predicated, so
     // the unrolled row loop is straight-line code.
     const int i = i_first + tid;
-    const bool active = i <= prm.b.xe && i >= prm.b.xs;
+    const bool active = i <= i_last && i >= prm.b.xs;
     const int col = tid + ((i_first - 2) & 1);        // west neighbour's column inside the tile
-    const int colm = tid + ((i_first - 2) & 3);
+    const int colm = tid + ((i_first - 2) & 15);
     const int colo = tid + ((i_first - 1) & 1);       // own column inside the old-field tile
     const SwScalars sc = prm.sc;
     Carry<M> cr;
@@ -351,7 +389,7 @@ fused_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_constant
             if (i >= g.i0 && i <= g.i1 && g.j1 >= j0 && g.j0 <= j1) pmask |= 1u << q;
         }
     int jrow = j0 - 2;
-    bool wet0 = true, wet1 = true, wet2 = true;   // warp-wide "row all wet", newest first (masked runs)
+    bool wet_prev = false;   // the previous chunk was all wet across this warp's columns and their neighbours
     for (int c = 0; c < nchunks; ++c) {
         const int s = c % STAGES;
         mbar_wait(&full[s], (c / STAGES) & 1);
@@ -362,41 +400,54 @@ fused_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_constant
         const double *suo = reinterpret_cast<const double *>(st + Cfg::OFF_OLD + 0 * Cfg::AO) + colo;
         const double *svo = reinterpret_cast<const double *>(st + Cfg::OFF_OLD + 1 * Cfg::AO) + colo;
         const double *spo = reinterpret_cast<const double *>(st + Cfg::OFF_OLD + 2 * Cfg::AO) + colo;
-        const int *sm = reinterpret_cast<const int *>(st + Cfg::OFF_MASK) + colm;
+        const unsigned char *sm = st + Cfg::OFF_MASK + colm;
+        // one pass of the chunk's rows; APPLY = false skips the mask selects (same bits when every
+        // mask value the rows look at is wet)
+        auto rows = [&](auto apply_tag) {
+            constexpr bool APPLY = decltype(apply_tag)::value;
 #pragma unroll
-        for (int r = 0; r < RY; ++r) {
-            Raw<M> N;
-            N.pW = sp[r * BW]; N.pC = sp[r * BW + 1]; N.pE = sp[r * BW + 2];
-            N.uW = su[r * BW]; N.uC = su[r * BW + 1]; N.uE = su[r * BW + 2];
-            N.vW = sv[r * BW]; N.vC = sv[r * BW + 1]; N.vE = sv[r * BW + 2];
-            if (M) {
-                N.tW = sm[r * BWM] == 1; N.tC = sm[r * BWM + 1] == 1; N.tE = sm[r * BWM + 2] == 1;
-            }
-            const double uo = suo[r * BWO], vo = svo[r * BWO], po = spo[r * BWO];
-            Outs out;
-            if (M) {
-                // rows j, j-1, j-2 all wet across the warp's columns and their neighbours
-                // (warp-uniform): the unmasked march gives the same bits without the selects
-                wet2 = wet1; wet1 = wet0;
-                wet0 = __all_sync(0xffffffffu, N.tW && N.tC && N.tE);
-                if (wet0 && wet1 && wet2) ingest<M, false>(cr, N, sc, uo, vo, po, out);
-                else ingest<M, true>(cr, N, sc, uo, vo, po, out);
-            } else {
-                ingest<M>(cr, N, sc, uo, vo, po, out);
-            }
-            if (r >= t_lo && r < t_hi) {
-                __stcs(prm.unew + qo, out.unew);
-                __stcs(prm.vnew + qo, out.vnew);
-                __stcs(prm.pnew + qo, out.pnew);
-                if (!FIRST) {
-                    if (!M || out.wu) __stcs(prm.uold + qo, out.uold);
-                    if (!M || out.wv) __stcs(prm.vold + qo, out.vold);
-                    if (!M || out.wt) __stcs(prm.pold + qo, out.pold);
+            for (int r = 0; r < RY; ++r) {
+                Raw<M> N;
+                N.pW = sp[r * BW]; N.pC = sp[r * BW + 1]; N.pE = sp[r * BW + 2];
+                N.uW = su[r * BW]; N.uC = su[r * BW + 1]; N.uE = su[r * BW + 2];
+                N.vW = sv[r * BW]; N.vC = sv[r * BW + 1]; N.vE = sv[r * BW + 2];
+                if (M) {
+                    if (APPLY) {
+                        N.tW = sm[r * BWM] == 1; N.tC = sm[r * BWM + 1] == 1; N.tE = sm[r * BWM + 2] == 1;
+                    } else {
+                        N.tW = N.tC = N.tE = true;
+                    }
                 }
-                if (pmask) push_row(prm.push, pmask, i, jrow, out.unew, out.vnew, out.pnew);
+                const double uo = suo[r * BWO], vo = svo[r * BWO], po = spo[r * BWO];
+                Outs out;
+                ingest<M, APPLY>(cr, N, sc, uo, vo, po, out);
+                if (r >= t_lo && r < t_hi) {
+                    __stcs(prm.unew + qo, out.unew);
+                    __stcs(prm.vnew + qo, out.vnew);
+                    __stcs(prm.pnew + qo, out.pnew);
+                    if (!FIRST) {
+                        if (!APPLY || out.wu) __stcs(prm.uold + qo, out.uold);
+                        if (!APPLY || out.wv) __stcs(prm.vold + qo, out.vold);
+                        if (!APPLY || out.wt) __stcs(prm.pold + qo, out.pold);
+                    }
+                    if (pmask) push_row(prm.push, pmask, i, jrow, out.unew, out.vnew, out.pnew);
+                }
+                qo += pitch;
+                ++jrow;
             }
-            qo += pitch;
-            ++jrow;
+        };
+        if constexpr (M) {
+            // all-wet test hoisted to the chunk (warp-uniform): a row looks back two rows, so the
+            // unmasked march is taken when this chunk and the previous one are wet throughout
+            bool w = true;
+#pragma unroll
+            for (int r = 0; r < RY; ++r) w = w && sm[r * BWM] == 1 && sm[r * BWM + 1] == 1 && sm[r * BWM + 2] == 1;
+            const bool wet_now = __all_sync(0xffffffffu, w);
+            if (wet_now && wet_prev) rows(std::false_type{});
+            else rows(std::true_type{});
+            wet_prev = wet_now;
+        } else {
+            rows(std::false_type{});
         }
         t_lo -= RY;
         t_hi -= RY;
@@ -427,7 +478,7 @@ EncodeTiledFn encode_fn()
 std::mutex g_map_mutex;
 std::map<std::tuple<const void *, int, int, int, int, int>, CUtensorMap> g_maps;
 
-// 2-D tiled tensor map over a column-major (nx, ny) array of FP64 (elem_bytes 8) or int32 (4)
+// 2-D tiled tensor map over a column-major (nx, ny) array of FP64 (elem_bytes 8) or bytes (1)
 bool get_map(const void *base, int elem_bytes, int nx, int ny, int boxw, int boxh, CUtensorMap &out)
 {
     std::lock_guard<std::mutex> lock(g_map_mutex);
@@ -443,20 +494,11 @@ bool get_map(const void *base, int elem_bytes, int nx, int ny, int boxw, int box
     cuuint64_t gstride[1] = {static_cast<cuuint64_t>(nx) * elem_bytes};
     cuuint32_t box[2] = {static_cast<cuuint32_t>(boxw), static_cast<cuuint32_t>(boxh)};
     cuuint32_t estr[2] = {1, 1};
-    // L2 promotion of the TMA reads; DLESM_TMA_L2PROMO=0..3 (none, 64 B, 128 B, 256 B) overrides
-    // the default for the experiments recorded in DESIGN.md
-    static const int promo = [] {
-        const char *e = std::getenv("DLESM_TMA_L2PROMO");
-        const int v = e ? std::atoi(e) : 3;
-        return v < 0 || v > 3 ? 3 : v;
-    }();
-    const CUtensorMapL2promotion promos[4] = {CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_64B,
-                                              CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-                                              CU_TENSOR_MAP_L2_PROMOTION_L2_256B};
     CUtensorMap m;
-    CUresult r = fn(&m, elem_bytes == 8 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT64 : CU_TENSOR_MAP_DATA_TYPE_INT32, 2,
+    CUresult r = fn(&m, elem_bytes == 8 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT64 : CU_TENSOR_MAP_DATA_TYPE_UINT8, 2,
                     const_cast<void *>(base), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                    CU_TENSOR_MAP_SWIZZLE_NONE, promos[promo], CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                    CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return false;
     if (g_maps.size() > 256) g_maps.clear();
     g_maps[key] = m;
@@ -464,9 +506,22 @@ bool get_map(const void *base, int elem_bytes, int nx, int ny, int boxw, int box
     return true;
 }
 
-// Pick the segment height.  Every segment costs two extra raw rows (its prologue) and its
+// opt a kernel into more than 48 KB of dynamic shared memory, once per kernel
+cudaError_t allow_smem(const void *kern, int bytes)
+{
+    static std::mutex mu;
+    static std::map<const void *, int> done;
+    std::lock_guard<std::mutex> lock(mu);
+    auto it = done.find(kern);
+    if (it != done.end() && it->second >= bytes) return cudaSuccess;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e == cudaSuccess) done[kern] = bytes;
+    return e;
+}
+
+// Pick the segment height.  Every segment costs `extra` more raw rows (its prologue) and its
 // row count is rounded up to whole chunks of `ry` rows, so: segments of about `target` rows,
-// the CTA count rounded up to whole waves of `slots` resident CTAs, and seg_rows + 2 a
+// the CTA count rounded up to whole waves of `slots` resident CTAs, and seg_rows + extra a
 // multiple of `ry` whenever that does not add a segment.
 int pick_seg_rows(int w, int h, int tx, int slots, int ry, int target, int extra = 2)
 {
@@ -487,48 +542,83 @@ int pick_seg_rows(int w, int h, int tx, int slots, int ry, int target, int extra
     return seg;
 }
 
+int env_rows(const char *name, int dflt)
+{
+    const char *e = std::getenv(name);
+    const int v = e ? std::atoi(e) : dflt;
+    return v < 8 ? dflt : v;
+}
+
+// The launch geometry: SweepTiles (the reference's tile-grid knob) -> TileMap + grid.
+//   tiles.ny > 0 : that many segments along j, go_decompose's remainder rule;
+//   tiles.ny = 0 : the library's choice (pick_seg_rows around `target` rows);
+//   tiles.nx > 1 : that many x-tiles starting at b.xs, each cut into strips of `out_cols`;
+//   else         : one x-tile starting at `x0` (the aligned origin).
+void make_tile_map(const Box &b, SweepTiles tiles, int x0, int out_cols, int slots, int ry, int target, int extra,
+                   TileMap &tm, dim3 &grid)
+{
+    const int h = b.ye - b.ys + 1;
+    int ntx = tiles.nx > 1 ? tiles.nx : 1;
+    if (ntx > 1) x0 = b.xs;
+    const int w = b.xe - x0 + 1;
+    if (ntx > w) ntx = w;
+    tm.x0 = x0;
+    tm.tw = w / ntx;
+    tm.xextra = w % ntx;
+    tm.strips = (tm.tw + (tm.xextra ? 1 : 0) + out_cols - 1) / out_cols;
+    int nty;
+    if (tiles.ny > 0) {
+        nty = tiles.ny > h ? h : tiles.ny;
+        tm.th = h / nty;
+        tm.yextra = h % nty;
+    } else {
+        tm.th = pick_seg_rows(w, h, out_cols, slots, ry, target, extra);
+        tm.yextra = 0;
+        nty = (h + tm.th - 1) / tm.th;
+    }
+    grid = dim3(static_cast<unsigned>(tm.strips * ntx), static_cast<unsigned>(nty));
+}
+
+template <int TX, int RY, int STAGES, int MINB, bool ALN>
+void tma_geometry(const FusedArgs &a, TileMap &tm, dim3 &grid)
+{
+    // aligned origin: strips start on 128-byte lines of the row (1-based column 1 + 16k), the
+    // columns below xs are masked; otherwise strips start at xs.
+    // Short segments keep the strips of a band in lockstep, so that together they sweep whole
+    // contiguous rows of DRAM and re-read each other's halo rows out of L2 (measured at
+    // 16384^2: 256 rows 0.93, 128 rows 0.95, 48 rows 0.995, 24-32 rows 1.01-1.02 of the
+    // measured copy bandwidth).  DLESM_SEG_ROWS overrides for experiments.
+    static const int target = env_rows("DLESM_SEG_ROWS", 32);
+    const int x0 = ALN ? ((a.b.xs - 1) / 16) * 16 + 1 : a.b.xs;
+    make_tile_map(a.b, a.tiles, x0, TX, 148 * MINB, RY, target, 2, tm, grid);
+}
+
 template <int TX, int RY, int STAGES, int MINB, bool M, bool FIRST, bool ALN>
 cudaError_t launch_tma_mf(const FusedArgs &a, cudaStream_t s)
 {
     using Cfg = TmaCfg<TX, RY, STAGES, M, ALN>;
-    constexpr bool aligned_origin = ALN;
     CUtensorMap mu, mv, mp, muo, mvo, mpo, mm;
     if (!get_map(a.u, 8, a.pitch, a.ny, Cfg::BW, RY, mu) || !get_map(a.v, 8, a.pitch, a.ny, Cfg::BW, RY, mv) ||
         !get_map(a.p, 8, a.pitch, a.ny, Cfg::BW, RY, mp) || !get_map(a.uold, 8, a.pitch, a.ny, Cfg::BWO, RY, muo) ||
         !get_map(a.vold, 8, a.pitch, a.ny, Cfg::BWO, RY, mvo) || !get_map(a.pold, 8, a.pitch, a.ny, Cfg::BWO, RY, mpo))
         return cudaErrorNotSupported;
     if (M) {
-        if (!get_map(a.tmask, 4, a.pitch, a.ny, Cfg::BWM, RY, mm)) return cudaErrorNotSupported;
+        if (!a.mask8 || a.mask8_pitch % 16 != 0 ||
+            !get_map(a.mask8, 1, a.mask8_pitch, a.ny, Cfg::BWM, RY, mm))
+            return cudaErrorNotSupported;
     } else {
         mm = mp;  // unused by the unmasked kernel
     }
     TmaStepParams prm;
     prm.unew = a.unew; prm.vnew = a.vnew; prm.pnew = a.pnew;
     prm.uold = a.uold; prm.vold = a.vold; prm.pold = a.pold;
-    // aligned origin: strips start on 128-byte lines of the row (1-based column 1 + 16k), the
-    // columns below xs are masked; otherwise strips start at xs
-    const int i_origin = aligned_origin ? ((a.b.xs - 1) / 16) * 16 + 1 : a.b.xs;
-    const int w = a.b.xe - i_origin + 1, h = a.b.ye - a.b.ys + 1;
-    static const int target = [] {
-        // Short segments keep the strips of a band in lockstep, so that together they sweep whole
-        // contiguous rows of DRAM and re-read each other's halo rows out of L2 (measured at
-        // 16384^2: 256 rows 0.93, 128 rows 0.95, 48 rows 0.995, 24-32 rows 1.01-1.02 of the
-        // measured copy bandwidth).  DLESM_SEG_ROWS overrides for experiments.
-        const char *e = std::getenv("DLESM_SEG_ROWS");
-        const int v = e ? std::atoi(e) : 32;
-        return v < 8 ? 32 : v;
-    }();
-    const int seg_rows = pick_seg_rows(w, h, TX, 148 * MINB, RY, target);
-    prm.pitch = a.pitch; prm.b = a.b; prm.seg_rows = seg_rows; prm.i_origin = i_origin; prm.sc = a.sc;
+    dim3 grid;
+    tma_geometry<TX, RY, STAGES, MINB, ALN>(a, prm.tm, grid);
+    prm.pitch = a.pitch; prm.b = a.b; prm.sc = a.sc;
     prm.push = a.push;
     auto kern = fused_tma_kernel<TX, RY, STAGES, MINB, M, FIRST, ALN>;
-    static bool attr_done = false;
-    if (!attr_done) {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
-        if (e != cudaSuccess) return e;
-        attr_done = true;
-    }
-    dim3 grid((w + TX - 1) / TX, (h + seg_rows - 1) / seg_rows);
+    cudaError_t e = allow_smem(reinterpret_cast<const void *>(kern), Cfg::SMEM_BYTES);
+    if (e != cudaSuccess) return e;
     kern<<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, s>>>(mu, mv, mp, muo, mvo, mpo, mm, prm);
     return cudaGetLastError();
 }
@@ -543,21 +633,36 @@ cudaError_t launch_tma(const FusedArgs &a, cudaStream_t s)
     return first ? launch_tma_mf<TX, RY, STAGES, MINB, false, true, ALN>(a, s)
                  : launch_tma_mf<TX, RY, STAGES, MINB, false, false, ALN>(a, s);
 }
+template <int TX, int RY, int STAGES, int MINB, bool ALN>
+void grid_tma(const FusedArgs &a, int grid[2])
+{
+    TileMap tm;
+    dim3 g;
+    tma_geometry<TX, RY, STAGES, MINB, ALN>(a, tm, g);
+    grid[0] = static_cast<int>(g.x);
+    grid[1] = static_cast<int>(g.y);
+}
 
 // ---------------------------------------------------------------------------------------
 // Two model steps per sweep (temporal blocking).  Stage A is the march above, run on a strip
 // one column wider on each side and one row longer at each end, producing the intermediate
-// state (u1,v1,p1 and the once-filtered old fields) of step n+1; its rows go through a small
-// shared-memory exchange buffer so that stage B -- the same march again, fed by u1,v1,p1 of the
-// west / own / east column -- produces step n+2 two rows behind.  The intermediate state never
-// reaches memory: 6 reads + 6 writes per point for TWO steps.  Thread t of TX owns column
-// i_first - 1 + t in both stages; threads 1 .. TX-2 store.
+// state (u1,v1,p1 and the once-filtered old fields) of step n+1; stage B -- the same march
+// again, fed by u1,v1,p1 of the west / own / east column -- produces step n+2 two rows behind.
+// The intermediate state never reaches memory: 6 reads + 6 writes per point for TWO steps.
+//
+// Every lane computes the four intermediates (cu, cv, z, h) of its own column only and takes the
+// neighbours' through warp shuffles (the first form of this sweep, where every thread recomputed
+// its east / west copies, spent a third of its FP64 work on them: ncu 75 % FP64 pipe).  Warps
+// overlap by two columns (lane 0 and lane 31 only feed their neighbours), so a warp yields 30
+// columns: 4 warps = 120 columns of the intermediate state, 118 output columns per CTA.  The
+// expression trees are unchanged -- lane l+1's cu(own) IS lane l's cu(east), operand for
+// operand -- so the bits are the same.
 // ---------------------------------------------------------------------------------------
 struct Tma2Params {
     double *u2, *v2, *p2, *uold2, *vold2, *pold2;
     int pitch;
     Box b;
-    int seg_rows;
+    TileMap tm;
     SwScalars sc;
     PushPlan2 push;
 };
@@ -580,153 +685,6 @@ __device__ __noinline__ void push_row2(const PushPlan2 &pp, unsigned mask, int i
     }
 }
 
-template <int TX, int RY, int STAGES>
-struct Tma2Cfg {
-    static constexpr int BW = TX + 4;    // raw tiles: west halo + TX + east halo, even start column
-    static constexpr int BWO = TX + 2;   // old tiles: TX columns, even start column
-    static constexpr int A = align128(BW * RY * 8);
-    static constexpr int AO = align128(BWO * RY * 8);
-    static constexpr int OFF_OLD = 3 * A;
-    static constexpr int STAGE_BYTES = 3 * A + 3 * AO;
-    static constexpr int TX_BYTES = 3 * BW * RY * 8 + 3 * BWO * RY * 8;
-    static constexpr int XW = TX + 2;    // exchange row: one pad column on each side
-    static constexpr int XBUF_BYTES = 3 * RY * XW * 8;   // u1, v1, p1 rows of one chunk
-    static constexpr int OFF_X = STAGES * STAGE_BYTES;
-    static constexpr int BAR_OFFSET = OFF_X + 2 * XBUF_BYTES;
-    static constexpr int SMEM_BYTES = BAR_OFFSET + STAGES * 8;
-    static constexpr int THREADS = TX;
-    static constexpr int OUT = TX - 2;   // output columns per strip
-};
-
-template <int TX, int RY, int STAGES, int MINB>
-__global__ void __launch_bounds__(TX, MINB)
-fused2_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_constant__ CUtensorMap tm_v,
-                  const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUtensorMap tm_uo,
-                  const __grid_constant__ CUtensorMap tm_vo, const __grid_constant__ CUtensorMap tm_po,
-                  const __grid_constant__ Tma2Params prm)
-{
-    using Cfg = Tma2Cfg<TX, RY, STAGES>;
-    constexpr int BW = Cfg::BW, BWO = Cfg::BWO, XW = Cfg::XW;
-    extern __shared__ __align__(1024) unsigned char fused_smem[];
-    uint64_t *full = reinterpret_cast<uint64_t *>(fused_smem + Cfg::BAR_OFFSET);
-
-    const int tid = threadIdx.x;
-    const int j0 = prm.b.ys + blockIdx.y * prm.seg_rows;
-    const int j1 = min(j0 + prm.seg_rows - 1, prm.b.ye);
-    const int nsteps = (j1 - j0 + 1) + 4;            // raw rows j0-2 .. j1+2
-    const int nchunks = (nsteps + RY - 1) / RY;
-    const int i_first = prm.b.xs + blockIdx.x * Cfg::OUT;   // first output column of this strip
-    const int x_box = (i_first - 3) & ~1;   // even 0-based column at/below thread 0's west neighbour
-    const int x_old = (i_first - 2) & ~1;   // even 0-based column at/below thread 0's own column
-
-    // No producer warp here: the per-chunk barrier between the two stages already tells thread 0
-    // that every warp is done with a ring stage, so it refills the stage right after it.  (A
-    // fifth warp would also cap the kernel at 168 registers: 10 warps on 4 schedulers.)
-    auto issue = [&](int c) {
-        const int s = c % STAGES;
-        unsigned char *st = fused_smem + s * Cfg::STAGE_BYTES;
-        const int y_raw = (j0 - 2) + c * RY - 1;   // 0-based row of the chunk's first raw row
-        const int y_old = y_raw - 1;               // stage A's outputs trail the raw rows by one
-        mbar_expect_tx(&full[s], Cfg::TX_BYTES);
-        tma_load_2d(st + 0 * Cfg::A, &tm_p, x_box, y_raw, &full[s]);
-        tma_load_2d(st + 1 * Cfg::A, &tm_u, x_box, y_raw, &full[s]);
-        tma_load_2d(st + 2 * Cfg::A, &tm_v, x_box, y_raw, &full[s]);
-        tma_load_2d(st + Cfg::OFF_OLD + 0 * Cfg::AO, &tm_uo, x_old, y_old, &full[s]);
-        tma_load_2d(st + Cfg::OFF_OLD + 1 * Cfg::AO, &tm_vo, x_old, y_old, &full[s]);
-        tma_load_2d(st + Cfg::OFF_OLD + 2 * Cfg::AO, &tm_po, x_old, y_old, &full[s]);
-    };
-    if (tid == 0) {
-        if (smem_u32(fused_smem) & 127u) __trap();
-        for (int s = 0; s < STAGES; ++s) mbar_init(&full[s], 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        for (int c = 0; c < STAGES && c < nchunks; ++c) issue(c);
-    }
-    // pad columns of the exchange rows (read by threads 0 and TX-1 only, whose stage-B results
-    // are never stored): finite values so that no inf/nan is manufactured
-    for (int q = tid; q < 2 * 3 * RY * 2; q += TX) {
-        const int row = q >> 1, side = q & 1;        // row over (buffer, field, r)
-        double *xr = reinterpret_cast<double *>(fused_smem + Cfg::OFF_X) + row * XW;
-        xr[side ? XW - 1 : 0] = 1.0;
-    }
-    __syncthreads();
-
-    const int i = i_first - 1 + tid;
-    const bool active = tid >= 1 && tid <= TX - 2 && i <= prm.b.xe;
-    const int col = tid + ((i_first - 3) & 1);        // west neighbour's column inside the raw tile
-    const int colo = tid + ((i_first - 2) & 1);       // own column inside the old-field tile
-    const SwScalars sc = prm.sc;
-    Carry<false> ca, cb;
-    carry_init(ca);
-    carry_init(cb);
-    double uo1 = 0.0, vo1 = 0.0, po1 = 0.0;   // once-filtered old fields of the row stage B emits next
-    // raw step t ingests raw row j0-2+t; stage A emits row j0-3+t; stage B emits row j0-4+t
-    long long qo = (static_cast<long long>(j0) - 5) * prm.pitch + (i - 1);
-    const long long pitch = prm.pitch;
-    int t_lo = active ? 4 : (1 << 30), t_hi = nsteps;
-    for (int c = 0; c < nchunks; ++c) {
-        const int s = c % STAGES;
-        mbar_wait(&full[s], (c / STAGES) & 1);
-        const unsigned char *st = fused_smem + s * Cfg::STAGE_BYTES;
-        const double *sp = reinterpret_cast<const double *>(st + 0 * Cfg::A) + col;
-        const double *su = reinterpret_cast<const double *>(st + 1 * Cfg::A) + col;
-        const double *sv = reinterpret_cast<const double *>(st + 2 * Cfg::A) + col;
-        const double *suo = reinterpret_cast<const double *>(st + Cfg::OFF_OLD + 0 * Cfg::AO) + colo;
-        const double *svo = reinterpret_cast<const double *>(st + Cfg::OFF_OLD + 1 * Cfg::AO) + colo;
-        const double *spo = reinterpret_cast<const double *>(st + Cfg::OFF_OLD + 2 * Cfg::AO) + colo;
-        double *xb = reinterpret_cast<double *>(fused_smem + Cfg::OFF_X + (c & 1) * Cfg::XBUF_BYTES) + tid;
-        double uo_r[RY], vo_r[RY], po_r[RY];
-        // ---- stage A: RY raw rows -> RY rows of the intermediate state ----
-#pragma unroll
-        for (int r = 0; r < RY; ++r) {
-            Raw<false> N;
-            N.pW = sp[r * BW]; N.pC = sp[r * BW + 1]; N.pE = sp[r * BW + 2];
-            N.uW = su[r * BW]; N.uC = su[r * BW + 1]; N.uE = su[r * BW + 2];
-            N.vW = sv[r * BW]; N.vC = sv[r * BW + 1]; N.vE = sv[r * BW + 2];
-            Outs o;
-            ingest<false>(ca, N, sc, suo[r * BWO], svo[r * BWO], spo[r * BWO], o);
-            xb[(0 * RY + r) * XW + 1] = o.unew;
-            xb[(1 * RY + r) * XW + 1] = o.vnew;
-            xb[(2 * RY + r) * XW + 1] = o.pnew;
-            uo_r[r] = o.uold; vo_r[r] = o.vold; po_r[r] = o.pold;
-        }
-        __syncthreads();
-        if (tid == 0 && c + STAGES < nchunks) issue(c + STAGES);
-        // ---- stage B: those RY rows (west / own / east column) -> RY rows of step n+2 ----
-#pragma unroll
-        for (int r = 0; r < RY; ++r) {
-            Raw<false> N;
-            N.uW = xb[(0 * RY + r) * XW]; N.uC = xb[(0 * RY + r) * XW + 1]; N.uE = xb[(0 * RY + r) * XW + 2];
-            N.vW = xb[(1 * RY + r) * XW]; N.vC = xb[(1 * RY + r) * XW + 1]; N.vE = xb[(1 * RY + r) * XW + 2];
-            N.pW = xb[(2 * RY + r) * XW]; N.pC = xb[(2 * RY + r) * XW + 1]; N.pE = xb[(2 * RY + r) * XW + 2];
-            Outs o;
-            ingest<false>(cb, N, sc, uo1, vo1, po1, o);
-            uo1 = uo_r[r]; vo1 = vo_r[r]; po1 = po_r[r];
-            if (r >= t_lo && r < t_hi) {
-                __stcs(prm.u2 + qo, o.unew);
-                __stcs(prm.v2 + qo, o.vnew);
-                __stcs(prm.p2 + qo, o.pnew);
-                __stcs(prm.uold2 + qo, o.uold);
-                __stcs(prm.vold2 + qo, o.vold);
-                __stcs(prm.pold2 + qo, o.pold);
-            }
-            qo += pitch;
-        }
-        t_lo -= RY;
-        t_hi -= RY;
-    }
-}
-
-// ---------------------------------------------------------------------------------------
-// Two steps per sweep, second form: the two-step sweep is bound by the FP64 pipe, not by HBM
-// (ncu: 75 % FP64 pipe, 27 GB of DRAM traffic in 4.5 ms), and a third of its FP64 work is the
-// east / west copies of cu, z / cv, h every thread recomputes for itself.  Here every lane
-// computes the four intermediates of its own column only and takes the neighbours' through
-// warp shuffles.  Warps overlap by two columns (lane 0 and lane 31 only feed their
-// neighbours), so a warp yields 30 columns: 4 warps = 120 columns of the intermediate state,
-// 118 output columns per CTA.  The expression trees are unchanged -- lane l+1's cu(own) IS
-// lane l's cu(east), operand for operand -- so the bits are the same.
-// ---------------------------------------------------------------------------------------
 struct RawS {
     double pW, pC, uC, uE, vW, vC;
 };
@@ -751,8 +709,8 @@ __device__ __forceinline__ void ingest_sh(CarryS &c, const RawS &N, bool tC, boo
                                           double uo, double vo, double po, Outs &o)
 {
     const RawS &P = c.P;
-    double cuC_N = 0.5 * (N.pC + N.pW) * N.uC;
-    double cvC_N = 0.5 * (N.pC + P.pC) * N.vC;
+    double cuC_N = (N.pC + N.pW) * N.uC;   // doubled, like ingest()
+    double cvC_N = (N.pC + P.pC) * N.vC;
     double zC_N = (sc.fsdx * (N.vC - N.vW) - sc.fsdy * (N.uC - P.uC)) / (P.pW + P.pC + N.pC + N.pW);
     double hC_P = P.pC + 0.25 * (P.uE * P.uE + P.uC * P.uC + N.vC * N.vC + P.vC * P.vC);
     if (M) {
@@ -765,11 +723,11 @@ __device__ __forceinline__ void ingest_sh(CarryS &c, const RawS &N, bool tC, boo
     const double zE_N = __shfl_down_sync(0xffffffffu, zC_N, 1);
     const double cvW_N = __shfl_up_sync(0xffffffffu, cvC_N, 1);
     const double hW_P = __shfl_up_sync(0xffffffffu, hC_P, 1);
-    o.unew = uo + sc.tdts8 * (zC_N + c.zC_P) * (cvC_N + cvW_N + c.cvW_P + c.cvC_P) -
+    o.unew = uo + sc.tdts8h * (zC_N + c.zC_P) * (cvC_N + cvW_N + c.cvW_P + c.cvC_P) -
              sc.tdtsdx * (hC_P - hW_P);
-    o.vnew = vo - sc.tdts8 * (c.zE_P + c.zC_P) * (c.cuE_P + c.cuC_P + c.cuC_PP + c.cuE_PP) -
+    o.vnew = vo - sc.tdts8h * (c.zE_P + c.zC_P) * (c.cuE_P + c.cuC_P + c.cuC_PP + c.cuE_PP) -
              sc.tdtsdy * (hC_P - c.hC_PP);
-    o.pnew = po - sc.tdtsdx * (c.cuE_P - c.cuC_P) - sc.tdtsdy * (cvC_N - c.cvC_P);
+    o.pnew = po - sc.tdtsdxh * (c.cuE_P - c.cuC_P) - sc.tdtsdyh * (cvC_N - c.cvC_P);
     bool wu = true, wv = true, wt = true;
     if (M) {
         wu = c.tC_P && c.tW_P;
@@ -809,14 +767,14 @@ struct Tma2sCfg {
     static constexpr int OUT = VA - 2;   // output columns per CTA
     static constexpr int BW = VA + 6;    // raw tiles: lanes' columns (VA + 2) + west + east, even start
     static constexpr int BWO = VA + 4;   // old tiles: lanes' columns, even start
-    static constexpr int BWM = VA + 8;   // int32 tmask tile: lanes' columns, start column a multiple of four
+    static constexpr int BWM = align16(VA + 2 + 15);   // byte tmask tile: lanes' columns from a multiple of 16
     static constexpr int A = align128(BW * RY * 8);
     static constexpr int AO = align128(BWO * RY * 8);
-    static constexpr int AM = M ? align128(BWM * RY * 4) : 0;
+    static constexpr int AM = M ? align128(BWM * RY) : 0;
     static constexpr int OFF_OLD = 3 * A;
     static constexpr int OFF_MASK = 3 * A + 3 * AO;
     static constexpr int STAGE_BYTES = 3 * A + 3 * AO + AM;
-    static constexpr int TX_BYTES = 3 * BW * RY * 8 + 3 * BWO * RY * 8 + (M ? BWM * RY * 4 : 0);
+    static constexpr int TX_BYTES = 3 * BW * RY * 8 + 3 * BWO * RY * 8 + (M ? BWM * RY : 0);
     static constexpr int XW = VA + 4;    // exchange row: index of column x = x - i_first + 3
     static constexpr int XBUF_BYTES = 3 * RY * XW * 8;
     static constexpr int OFF_X = STAGES * STAGE_BYTES;
@@ -825,7 +783,12 @@ struct Tma2sCfg {
     static constexpr int THREADS = TX;
 };
 
-template <int TX, int RY, int STAGES, int MINB, bool M>
+// PIPE: software-pipelined form.  Between two CTA barriers a warp runs stage B of the PREVIOUS
+// chunk and stage A of the current one -- two independent instruction streams (more ILP for the
+// fixed-latency FP64 chains, and the wait for the TMA data of chunk c hides behind B(c-1)) --
+// instead of A(c) | barrier | B(c).  Same exchange buffers (A(c+1) overwrites what B(c-1) read one
+// barrier earlier), same arithmetic, same bits.
+template <int TX, int RY, int STAGES, int MINB, bool M, bool PIPE>
 __global__ void __launch_bounds__(TX, MINB)
 fused2s_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_constant__ CUtensorMap tm_v,
                    const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUtensorMap tm_uo,
@@ -842,16 +805,14 @@ fused2s_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_consta
     // short sweeps when those neighbours are the rank itself, but with REMOTE x neighbours it bunches
     // ~100k single-cell NVLink stores into the first waves: 2x2 tiles, 4.8 -> 7.0 ms per launch.  Natural
     // order spreads them over the sweep.)
-    const int bx = blockIdx.x, by = blockIdx.y;
-    const int j0 = prm.b.ys + by * prm.seg_rows;
-    const int j1 = min(j0 + prm.seg_rows - 1, prm.b.ye);
+    int i_first, i_last, j0, j1;   // first output column of this CTA, last column of its x-tile, rows
+    tile_of_block(prm.tm, prm.b, blockIdx.x, blockIdx.y, Cfg::OUT, i_first, i_last, j0, j1);
     const int nsteps = (j1 - j0 + 1) + 4;            // raw rows j0-2 .. j1+2
     const int nchunks = (nsteps + RY - 1) / RY;
-    const int i_first = prm.b.xs + bx * Cfg::OUT;   // first output column of this CTA
     // lane column (both stages): i_first + 30*warp + lane - 2
     const int x_box = (i_first - 4) & ~1;   // even 0-based column at/below stage A lane 0's west neighbour
     const int x_old = (i_first - 3) & ~1;   // even 0-based column at/below stage A lane 0's own column
-    const int x_msk = (i_first - 3) & ~3;   // the int32 tmask tile starts on a multiple of four columns
+    const int x_msk = (i_first - 3) & ~15;  // the byte tmask tile starts on a multiple of 16 columns
 
     auto issue = [&](int c) {
         const int s = c % STAGES;
@@ -867,6 +828,9 @@ fused2s_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_consta
         tma_load_2d(st + Cfg::OFF_OLD + 2 * Cfg::AO, &tm_po, x_old, y_old, &full[s]);
         if (M) tma_load_2d(st + Cfg::OFF_MASK, &tm_mask, x_msk, y_raw, &full[s]);
     };
+    // No producer warp here: the per-chunk barrier between the two stages already tells thread 0
+    // that every warp is done with a ring stage, so it refills the stage right after it.  (A
+    // fifth warp would also cap the kernel at 168 registers: 10 warps on 4 schedulers.)
     if (tid == 0) {
         if (smem_u32(fused_smem) & 127u) __trap();
         for (int s = 0; s < STAGES; ++s) mbar_init(&full[s], 1);
@@ -887,17 +851,17 @@ fused2s_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_consta
     // lanes 0 and 31 only feed their neighbours; the CTA's first and last intermediate columns
     // (i_first - 1, i_first + OUT) have no valid neighbour on one side in stage B
     const bool a_writes = lane >= 1 && lane <= 30;
-    const bool active = a_writes && i >= i_first && i < i_first + Cfg::OUT && i <= prm.b.xe;
+    const bool active = a_writes && i >= i_first && i < i_first + Cfg::OUT && i <= i_last;
     const int xo = base + 1;                          // exchange index of this lane's column
     const int col = base + ((i_first - 4) & 1);       // west neighbour inside the raw tile
     const int colo = base + ((i_first - 3) & 1);      // own column inside the old tile
-    const int colm = base + ((i_first - 3) & 3);      // own column inside the tmask tile
+    const int colm = base + ((i_first - 3) & 15);     // own column inside the tmask tile
     const SwScalars sc = prm.sc;
     CarryS ca, cb;
     carry_init(ca);
     carry_init(cb);
     double uo1 = 0.0, vo1 = 0.0, po1 = 0.0;
-    bool wet0 = true, wet1 = true, wet2 = true, wet3 = true;   // warp-wide "row all wet", newest first
+    bool wet_prev = false;    // the previous chunk was all wet across this warp's columns
     long long qo = (static_cast<long long>(j0) - 5) * prm.pitch + (i - 1);
     const long long pitch = prm.pitch;
     int t_lo = active ? 4 : (1 << 30), t_hi = nsteps;
@@ -911,7 +875,14 @@ fused2s_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_consta
     const int pfirst = pmask ? __ffs(pmask) - 1 : 0;
     const unsigned prest = pmask & (pmask - 1);
     int jrow = j0 - 4;
-    for (int c = 0; c < nchunks; ++c) {
+
+    // state handed from stage A of a chunk to stage B of the same chunk
+    double uo_r[RY], vo_r[RY], po_r[RY];
+    bool tbC[RY], tbW[RY];   // stage B's row is stage A's previous row: its masks are A's carried ones
+    bool fastB = false;
+
+    // ---- stage A of chunk c: RY raw rows -> RY rows of the intermediate state ----
+    auto stage_a = [&](int c) {
         const int s = c % STAGES;
         mbar_wait(&full[s], (c / STAGES) & 1);
         const unsigned char *st = fused_smem + s * Cfg::STAGE_BYTES;
@@ -922,93 +893,138 @@ fused2s_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_consta
         const double *svo = reinterpret_cast<const double *>(st + Cfg::OFF_OLD + 1 * Cfg::AO) + colo;
         const double *spo = reinterpret_cast<const double *>(st + Cfg::OFF_OLD + 2 * Cfg::AO) + colo;
         double *xb = reinterpret_cast<double *>(fused_smem + Cfg::OFF_X + (c & 1) * Cfg::XBUF_BYTES) + xo;
-        const int *sm = reinterpret_cast<const int *>(st + Cfg::OFF_MASK) + colm;
-        double uo_r[RY], vo_r[RY], po_r[RY];
-        bool tbC[RY], tbW[RY];   // stage B's row is stage A's previous row: its masks are A's carried ones
-        bool fastB[RY];
+        const unsigned char *sm = st + Cfg::OFF_MASK + colm;
+        auto rows = [&](auto apply_tag) {
+            constexpr bool APPLY = decltype(apply_tag)::value;
 #pragma unroll
-        for (int r = 0; r < RY; ++r) {
-            RawS N;
-            N.pW = sp[r * BW]; N.pC = sp[r * BW + 1];
-            N.uC = su[r * BW + 1]; N.uE = su[r * BW + 2];
-            N.vW = sv[r * BW]; N.vC = sv[r * BW + 1];
-            bool tC = true, tW = true;
-            Outs o;
-            if (M) {
-                tC = sm[r * BWM] == 1;
-                tW = __shfl_up_sync(0xffffffffu, static_cast<int>(tC), 1) != 0;
-                tbC[r] = ca.tC_P; tbW[r] = ca.tW_P;
-                // rows N, P, PP all wet across the warp (warp-uniform): the unmasked march gives the
-                // same bits without the selects -- almost every warp-row away from the islands
-                wet3 = wet2; wet2 = wet1; wet1 = wet0;
-                wet0 = __all_sync(0xffffffffu, tC);
-                fastB[r] = wet1 && wet2 && wet3;
-                if (wet0 && wet1 && wet2)
-                    ingest_sh<false>(ca, N, true, true, sc, suo[r * BWO], svo[r * BWO], spo[r * BWO], o);
-                else
+            for (int r = 0; r < RY; ++r) {
+                RawS N;
+                N.pW = sp[r * BW]; N.pC = sp[r * BW + 1];
+                N.uC = su[r * BW + 1]; N.uE = su[r * BW + 2];
+                N.vW = sv[r * BW]; N.vC = sv[r * BW + 1];
+                Outs o;
+                if (APPLY) {
+                    const bool tC = sm[r * BWM] == 1;
+                    const bool tW = __shfl_up_sync(0xffffffffu, static_cast<int>(tC), 1) != 0;
+                    tbC[r] = ca.tC_P; tbW[r] = ca.tW_P;
                     ingest_sh<true>(ca, N, tC, tW, sc, suo[r * BWO], svo[r * BWO], spo[r * BWO], o);
-                rotate_masks(ca, tC, tW);
-            } else {
-                ingest_sh<false>(ca, N, true, true, sc, suo[r * BWO], svo[r * BWO], spo[r * BWO], o);
-            }
-            if (a_writes) {
-                xb[(0 * RY + r) * XW] = o.unew;
-                xb[(1 * RY + r) * XW] = o.vnew;
-                xb[(2 * RY + r) * XW] = o.pnew;
-            }
-            uo_r[r] = o.uold; vo_r[r] = o.vold; po_r[r] = o.pold;
-        }
-        __syncthreads();
-        if (tid == 0 && c + STAGES < nchunks) issue(c + STAGES);
-#pragma unroll
-        for (int r = 0; r < RY; ++r) {
-            RawS N;
-            N.uC = xb[(0 * RY + r) * XW]; N.uE = xb[(0 * RY + r) * XW + 1];
-            N.vW = xb[(1 * RY + r) * XW - 1]; N.vC = xb[(1 * RY + r) * XW];
-            N.pW = xb[(2 * RY + r) * XW - 1]; N.pC = xb[(2 * RY + r) * XW];
-            Outs o;
-            if (M) {
-                if (fastB[r]) ingest_sh<false>(cb, N, true, true, sc, uo1, vo1, po1, o);
-                else ingest_sh<true>(cb, N, tbC[r], tbW[r], sc, uo1, vo1, po1, o);
-                rotate_masks(cb, tbC[r], tbW[r]);
-            } else {
-                ingest_sh<false>(cb, N, true, true, sc, uo1, vo1, po1, o);
-            }
-            uo1 = uo_r[r]; vo1 = vo_r[r]; po1 = po_r[r];
-            if (r >= t_lo && r < t_hi) {
-                __stcs(prm.u2 + qo, o.unew);
-                __stcs(prm.v2 + qo, o.vnew);
-                __stcs(prm.p2 + qo, o.pnew);
-                __stcs(prm.uold2 + qo, o.uold);
-                __stcs(prm.vold2 + qo, o.vold);
-                __stcs(prm.pold2 + qo, o.pold);
-                if (pmask) {
-                    // first box inline (an x-edge column meets it on every row; a call would save and
-                    // restore ~150 live registers each time), the rest -- corners -- out of line
-                    const PushSeg2 &g = prm.push.seg[pfirst];
-                    if (jrow >= g.j0 && jrow <= g.j1) {
-                        const size_t d = idx(g.dpitch, g.ides + (i - g.i0), g.jdes + (jrow - g.j0));
-                        g.dst[0][d] = o.unew; g.dst[1][d] = o.vnew; g.dst[2][d] = o.pnew;
-                        g.dst[3][d] = o.uold; g.dst[4][d] = o.vold; g.dst[5][d] = o.pold;
-                    }
-                    if (prest) push_row2(prm.push, prest, i, jrow, o.unew, o.vnew, o.pnew, o.uold, o.vold, o.pold);
+                    rotate_masks(ca, tC, tW);
+                } else {
+                    ingest_sh<false>(ca, N, true, true, sc, suo[r * BWO], svo[r * BWO], spo[r * BWO], o);
                 }
+                if (a_writes) {
+                    xb[(0 * RY + r) * XW] = o.unew;
+                    xb[(1 * RY + r) * XW] = o.vnew;
+                    xb[(2 * RY + r) * XW] = o.pnew;
+                }
+                uo_r[r] = o.uold; vo_r[r] = o.vold; po_r[r] = o.pold;
             }
-            qo += pitch;
-            ++jrow;
+        };
+        if constexpr (M) {
+            // all-wet test hoisted to the chunk (warp-uniform).  Stage A's rows look back two raw
+            // rows, stage B's three: both take the unmasked march -- same bits, no selects --
+            // when this chunk and the previous one are wet throughout.
+            bool w = true;
+#pragma unroll
+            for (int r = 0; r < RY; ++r) w = w && sm[r * BWM] == 1;
+            const bool wet_now = __all_sync(0xffffffffu, w);
+            fastB = wet_now && wet_prev;
+            wet_prev = wet_now;
+            if (fastB) {
+                rows(std::false_type{});
+                ca.tC_P = ca.tW_P = ca.tC_PP = true;
+            } else {
+                rows(std::true_type{});
+            }
+        } else {
+            rows(std::false_type{});
+        }
+    };
+
+    // ---- stage B of chunk c: those RY rows (west / own / east column) -> RY rows of step n+2 ----
+    auto stage_b = [&](int c) {
+        const double *xb = reinterpret_cast<const double *>(fused_smem + Cfg::OFF_X + (c & 1) * Cfg::XBUF_BYTES) + xo;
+        auto rows = [&](auto apply_tag) {
+            constexpr bool APPLY = decltype(apply_tag)::value;
+#pragma unroll
+            for (int r = 0; r < RY; ++r) {
+                RawS N;
+                N.uC = xb[(0 * RY + r) * XW]; N.uE = xb[(0 * RY + r) * XW + 1];
+                N.vW = xb[(1 * RY + r) * XW - 1]; N.vC = xb[(1 * RY + r) * XW];
+                N.pW = xb[(2 * RY + r) * XW - 1]; N.pC = xb[(2 * RY + r) * XW];
+                Outs o;
+                if (APPLY) {
+                    ingest_sh<true>(cb, N, tbC[r], tbW[r], sc, uo1, vo1, po1, o);
+                    rotate_masks(cb, tbC[r], tbW[r]);
+                } else {
+                    ingest_sh<false>(cb, N, true, true, sc, uo1, vo1, po1, o);
+                }
+                uo1 = uo_r[r]; vo1 = vo_r[r]; po1 = po_r[r];
+                if (r >= t_lo && r < t_hi) {
+                    __stcs(prm.u2 + qo, o.unew);
+                    __stcs(prm.v2 + qo, o.vnew);
+                    __stcs(prm.p2 + qo, o.pnew);
+                    __stcs(prm.uold2 + qo, o.uold);
+                    __stcs(prm.vold2 + qo, o.vold);
+                    __stcs(prm.pold2 + qo, o.pold);
+                    if (pmask) {
+                        // first box inline (an x-edge column meets it on every row; a call would save and
+                        // restore ~150 live registers each time), the rest -- corners -- out of line
+                        const PushSeg2 &g = prm.push.seg[pfirst];
+                        if (jrow >= g.j0 && jrow <= g.j1) {
+                            const size_t d = idx(g.dpitch, g.ides + (i - g.i0), g.jdes + (jrow - g.j0));
+                            g.dst[0][d] = o.unew; g.dst[1][d] = o.vnew; g.dst[2][d] = o.pnew;
+                            g.dst[3][d] = o.uold; g.dst[4][d] = o.vold; g.dst[5][d] = o.pold;
+                        }
+                        if (prest) push_row2(prm.push, prest, i, jrow, o.unew, o.vnew, o.pnew, o.uold, o.vold, o.pold);
+                    }
+                }
+                qo += pitch;
+                ++jrow;
+            }
+        };
+        if constexpr (M) {
+            if (fastB) {
+                rows(std::false_type{});
+                cb.tC_P = cb.tW_P = cb.tC_PP = true;
+            } else {
+                rows(std::true_type{});
+            }
+        } else {
+            rows(std::false_type{});
         }
         t_lo -= RY;
         t_hi -= RY;
+    };
+
+    if (!PIPE) {
+        for (int c = 0; c < nchunks; ++c) {
+            stage_a(c);
+            __syncthreads();
+            if (tid == 0 && c + STAGES < nchunks) issue(c + STAGES);
+            stage_b(c);
+        }
+    } else {
+        stage_a(0);
+        __syncthreads();
+        if (tid == 0 && STAGES < nchunks) issue(STAGES);
+        for (int c = 1; c < nchunks; ++c) {
+            stage_b(c - 1);   // reads the exchange rows A(c-1) wrote before the last barrier
+            stage_a(c);       // overwrites the rows B(c-2) read before the last barrier
+            __syncthreads();
+            if (tid == 0 && c + STAGES < nchunks) issue(c + STAGES);
+        }
+        stage_b(nchunks - 1);
     }
 }
 
 // ---------------------------------------------------------------------------------------
-// Two steps per sweep, third form: warp-private.  ncu on the shuffle form showed 23 % of all
+// Two steps per sweep, warp-private form.  ncu on the shuffle form showed 23 % of all
 // warp samples waiting at the per-chunk CTA barrier of the shared-memory exchange.  Here the
 // intermediate state crosses lanes by shuffle as well, so a warp depends on no other warp:
 // stage A row -> shuffle -> stage B row, interleaved row by row, no barrier, no exchange
 // buffer.  Lanes 2..29 store (28 columns per warp); a producer warp feeds the TMA ring as in the
-// one-step sweep.
+// one-step sweep.  No tmask, no halo push.
 // ---------------------------------------------------------------------------------------
 template <int TX, int RY, int STAGES>
 struct Tma2wCfg {
@@ -1031,7 +1047,7 @@ __global__ void __launch_bounds__(TX + 32, MINB)
 fused2w_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_constant__ CUtensorMap tm_v,
                    const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUtensorMap tm_uo,
                    const __grid_constant__ CUtensorMap tm_vo, const __grid_constant__ CUtensorMap tm_po,
-                   const __grid_constant__ Tma2Params prm)
+                   const __grid_constant__ CUtensorMap, const __grid_constant__ Tma2Params prm)
 {
     using Cfg = Tma2wCfg<TX, RY, STAGES>;
     constexpr int BW = Cfg::BW, BWO = Cfg::BWO;
@@ -1040,11 +1056,10 @@ fused2w_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_consta
     uint64_t *empty = full + STAGES;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int j0 = prm.b.ys + blockIdx.y * prm.seg_rows;
-    const int j1 = min(j0 + prm.seg_rows - 1, prm.b.ye);
+    int i_first, i_last, j0, j1;
+    tile_of_block(prm.tm, prm.b, blockIdx.x, blockIdx.y, Cfg::OUT, i_first, i_last, j0, j1);
     const int nsteps = (j1 - j0 + 1) + 4;            // raw rows j0-2 .. j1+2
     const int nchunks = (nsteps + RY - 1) / RY;
-    const int i_first = prm.b.xs + blockIdx.x * Cfg::OUT;   // first output column of this CTA
 
     if (tid == 0) {
         if (smem_u32(fused_smem) & 127u) __trap();
@@ -1082,7 +1097,7 @@ fused2w_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_consta
     // ---- consumer warps: lane column = i_first + 28*warp + lane - 2 in both stages ----
     const int base = 28 * warp + lane;
     const int i = i_first + base - 2;
-    const bool active = lane >= 2 && lane <= 29 && i <= prm.b.xe;
+    const bool active = lane >= 2 && lane <= 29 && i <= i_last;
     const int col = base + ((i_first - 4) & 1);       // west neighbour inside the raw tile
     const int colo = base + ((i_first - 3) & 1);      // own column inside the old tile
     const SwScalars sc = prm.sc;
@@ -1137,136 +1152,113 @@ fused2w_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_consta
     }
 }
 
-template <class Cfg, int RY, int MINB, class Kern>
+// every segment recomputes two rows of the intermediate state and re-reads four raw rows, so
+// segments are longer than the one-step sweep's; DLESM_SEG_ROWS2 overrides
+template <class Cfg, int RY, int MINB>
+void tma2_geometry(const Fused2Args &a, TileMap &tm, dim3 &grid)
+{
+    static const int target = env_rows("DLESM_SEG_ROWS2", 124);
+    make_tile_map(a.b, a.tiles, a.b.xs, Cfg::OUT, 148 * MINB, RY, target, 4, tm, grid);
+}
+
+template <class Cfg, int RY, int MINB, bool M, class Kern>
 cudaError_t launch_tma2_generic(const Fused2Args &a, cudaStream_t s, Kern kern)
 {
-    CUtensorMap mu, mv, mp, muo, mvo, mpo;
-    if (!get_map(a.u, 8, a.pitch, a.ny, Cfg::BW, RY, mu) || !get_map(a.v, 8, a.pitch, a.ny, Cfg::BW, RY, mv) ||
-        !get_map(a.p, 8, a.pitch, a.ny, Cfg::BW, RY, mp) || !get_map(a.uold, 8, a.pitch, a.ny, Cfg::BWO, RY, muo) ||
-        !get_map(a.vold, 8, a.pitch, a.ny, Cfg::BWO, RY, mvo) || !get_map(a.pold, 8, a.pitch, a.ny, Cfg::BWO, RY, mpo))
-        return cudaErrorNotSupported;
-    Tma2Params prm;
-    prm.u2 = a.u2; prm.v2 = a.v2; prm.p2 = a.p2;
-    prm.uold2 = a.uold2; prm.vold2 = a.vold2; prm.pold2 = a.pold2;
-    const int w = a.b.xe - a.b.xs + 1, h = a.b.ye - a.b.ys + 1;
-    static const int target = [] {
-        // every segment recomputes two rows of the intermediate state and re-reads four raw rows,
-        // so segments are longer than the one-step sweep's; DLESM_SEG_ROWS2 overrides
-        const char *e = std::getenv("DLESM_SEG_ROWS2");
-        const int v = e ? std::atoi(e) : 124;
-        return v < 8 ? 124 : v;
-    }();
-    const int seg_rows = pick_seg_rows(w, h, Cfg::OUT, 148 * MINB, RY, target, 4);
-    prm.pitch = a.pitch; prm.b = a.b; prm.seg_rows = seg_rows; prm.sc = a.sc;
-    prm.push = a.push;
-    static bool attr_done = false;
-    if (!attr_done) {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
-        if (e != cudaSuccess) return e;
-        attr_done = true;
-    }
-    dim3 grid((w + Cfg::OUT - 1) / Cfg::OUT, (h + seg_rows - 1) / seg_rows);
-    kern<<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, s>>>(mu, mv, mp, muo, mvo, mpo, prm);
-    return cudaGetLastError();
-}
-
-template <int TX, int RY, int STAGES, int MINB>
-cudaError_t launch_tma2(const Fused2Args &a, cudaStream_t s)
-{
-    return launch_tma2_generic<Tma2Cfg<TX, RY, STAGES>, RY, MINB>(a, s, fused2_tma_kernel<TX, RY, STAGES, MINB>);
-}
-
-template <int TX, int RY, int STAGES, int MINB, bool M>
-cudaError_t launch_tma2s_m(const Fused2Args &a, cudaStream_t s)
-{
-    using Cfg = Tma2sCfg<TX, RY, STAGES, M>;
     CUtensorMap mu, mv, mp, muo, mvo, mpo, mm;
     if (!get_map(a.u, 8, a.pitch, a.ny, Cfg::BW, RY, mu) || !get_map(a.v, 8, a.pitch, a.ny, Cfg::BW, RY, mv) ||
         !get_map(a.p, 8, a.pitch, a.ny, Cfg::BW, RY, mp) || !get_map(a.uold, 8, a.pitch, a.ny, Cfg::BWO, RY, muo) ||
         !get_map(a.vold, 8, a.pitch, a.ny, Cfg::BWO, RY, mvo) || !get_map(a.pold, 8, a.pitch, a.ny, Cfg::BWO, RY, mpo))
         return cudaErrorNotSupported;
-    if (M) {
-        if (!get_map(a.tmask, 4, a.pitch, a.ny, Cfg::BWM, RY, mm)) return cudaErrorNotSupported;
+    if constexpr (M) {
+        if (!a.mask8 || a.mask8_pitch % 16 != 0 || !get_map(a.mask8, 1, a.mask8_pitch, a.ny, Cfg::BWM, RY, mm))
+            return cudaErrorNotSupported;
     } else {
-        mm = mp;  // unused by the unmasked kernel
+        mm = mp;  // unused by the unmasked kernels
     }
     Tma2Params prm;
     prm.u2 = a.u2; prm.v2 = a.v2; prm.p2 = a.p2;
     prm.uold2 = a.uold2; prm.vold2 = a.vold2; prm.pold2 = a.pold2;
-    const int w = a.b.xe - a.b.xs + 1, h = a.b.ye - a.b.ys + 1;
-    static const int target = [] {
-        const char *e = std::getenv("DLESM_SEG_ROWS2");
-        const int v = e ? std::atoi(e) : 124;
-        return v < 8 ? 124 : v;
-    }();
-    const int seg_rows = pick_seg_rows(w, h, Cfg::OUT, 148 * MINB, RY, target, 4);
-    prm.pitch = a.pitch; prm.b = a.b; prm.seg_rows = seg_rows; prm.sc = a.sc;
+    dim3 grid;
+    tma2_geometry<Cfg, RY, MINB>(a, prm.tm, grid);
+    prm.pitch = a.pitch; prm.b = a.b; prm.sc = a.sc;
     prm.push = a.push;
-    auto kern = fused2s_tma_kernel<TX, RY, STAGES, MINB, M>;
-    static bool attr_done = false;
-    if (!attr_done) {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
-        if (e != cudaSuccess) return e;
-        attr_done = true;
-    }
-    dim3 grid((w + Cfg::OUT - 1) / Cfg::OUT, (h + seg_rows - 1) / seg_rows);
+    // per KERNEL, not per instantiation of this launcher: kernels that differ only in a template
+    // argument of their own (PIPE) share this function
+    cudaError_t e = allow_smem(reinterpret_cast<const void *>(kern), Cfg::SMEM_BYTES);
+    if (e != cudaSuccess) return e;
     kern<<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, s>>>(mu, mv, mp, muo, mvo, mpo, mm, prm);
     return cudaGetLastError();
 }
-template <int TX, int RY, int STAGES, int MINB>
+
+template <int TX, int RY, int STAGES, int MINB, bool PIPE>
 cudaError_t launch_tma2s(const Fused2Args &a, cudaStream_t s)
 {
-    return a.tmask ? launch_tma2s_m<TX, RY, STAGES, MINB, true>(a, s)
-                   : launch_tma2s_m<TX, RY, STAGES, MINB, false>(a, s);
+    if (a.mask8)
+        return launch_tma2_generic<Tma2sCfg<TX, RY, STAGES, true>, RY, MINB, true>(
+            a, s, fused2s_tma_kernel<TX, RY, STAGES, MINB, true, PIPE>);
+    return launch_tma2_generic<Tma2sCfg<TX, RY, STAGES, false>, RY, MINB, false>(
+        a, s, fused2s_tma_kernel<TX, RY, STAGES, MINB, false, PIPE>);
+}
+template <int TX, int RY, int STAGES, int MINB, bool PIPE>
+void grid_tma2s(const Fused2Args &a, int grid[2])
+{
+    TileMap tm;
+    dim3 g;
+    tma2_geometry<Tma2sCfg<TX, RY, STAGES, false>, RY, MINB>(a, tm, g);
+    grid[0] = static_cast<int>(g.x);
+    grid[1] = static_cast<int>(g.y);
 }
 
 template <int TX, int RY, int STAGES, int MINB>
 cudaError_t launch_tma2w(const Fused2Args &a, cudaStream_t s)
 {
-    return launch_tma2_generic<Tma2wCfg<TX, RY, STAGES>, RY, MINB>(a, s, fused2w_tma_kernel<TX, RY, STAGES, MINB>);
+    return launch_tma2_generic<Tma2wCfg<TX, RY, STAGES>, RY, MINB, false>(a, s, fused2w_tma_kernel<TX, RY, STAGES, MINB>);
+}
+template <int TX, int RY, int STAGES, int MINB>
+void grid_tma2w(const Fused2Args &a, int grid[2])
+{
+    TileMap tm;
+    dim3 g;
+    tma2_geometry<Tma2wCfg<TX, RY, STAGES>, RY, MINB>(a, tm, g);
+    grid[0] = static_cast<int>(g.x);
+    grid[1] = static_cast<int>(g.y);
 }
 
 struct Tma2Variant {
     int id;
     const char *name;
     cudaError_t (*launch)(const Fused2Args &, cudaStream_t);
+    void (*grid)(const Fused2Args &, int[2]);
 };
-// {threads = columns of stage A (TMA boxes are at most 256 wide: 128 only), rows per chunk,
-// stages, resident CTAs per SM}
+// {threads = columns of stage A (TMA boxes are at most 256 wide: 128 only), rows per chunk, stages,
+// resident CTAs per SM}.  Shipped + one alternate per idea (the other shapes measured in round 1 --
+// RY 2 / 8, 3-4 stages, 256 threads -- were within 1 % or slower: DESIGN.md section 4b):
+//   10       shuffle form, A | barrier | B per chunk (round 1's shipped kernel)
+//   17       shuffle form, software-pipelined: B(c-1) and A(c) between two barriers
+//   20       warp-private (all neighbour data by shuffle, no CTA barrier; 28 columns per warp)
 const Tma2Variant kTma2Variants[] = {
-    {1, "tma2-128x4x3-occ2", launch_tma2<128, 4, 3, 2>},
-    {2, "tma2-128x4x2-occ2", launch_tma2<128, 4, 2, 2>},
-    {3, "tma2-128x2x3-occ3", launch_tma2<128, 2, 3, 3>},
-    {4, "tma2-128x2x4-occ2", launch_tma2<128, 2, 4, 2>},
-    {5, "tma2-128x2x2-occ3", launch_tma2<128, 2, 2, 3>},
-    {6, "tma2-128x8x2-occ1", launch_tma2<128, 8, 2, 1>},
-    {7, "tma2-128x1x4-occ3", launch_tma2<128, 1, 4, 3>},
-    // ids >= 10: east / west intermediates through warp shuffles (118 output columns per CTA)
-    {10, "tma2s-128x4x2-occ2", launch_tma2s<128, 4, 2, 2>},
-    {11, "tma2s-128x4x3-occ2", launch_tma2s<128, 4, 3, 2>},
-    {12, "tma2s-128x2x3-occ3", launch_tma2s<128, 2, 3, 3>},
-    {13, "tma2s-128x2x4-occ2", launch_tma2s<128, 2, 4, 2>},
-    {14, "tma2s-128x4x2-occ3", launch_tma2s<128, 4, 2, 3>},
-    {15, "tma2s-256x4x2-occ1", launch_tma2s<256, 4, 2, 1>},
-    {16, "tma2s-256x2x3-occ1", launch_tma2s<256, 2, 3, 1>},
-    // ids >= 20: warp-private (all neighbour data by shuffle, no CTA barrier; 28 columns per warp)
-    {20, "tma2w-128x4x3-occ2", launch_tma2w<128, 4, 3, 2>},
-    {21, "tma2w-128x4x2-occ2", launch_tma2w<128, 4, 2, 2>},
-    {22, "tma2w-128x2x4-occ2", launch_tma2w<128, 2, 4, 2>},
-    {23, "tma2w-256x4x3-occ1", launch_tma2w<256, 4, 3, 1>},
-    {24, "tma2w-128x8x2-occ2", launch_tma2w<128, 8, 2, 2>},
-    {25, "tma2w-64x4x3-occ4", launch_tma2w<64, 4, 3, 4>},
-    {26, "tma2w-96x4x3-occ3", launch_tma2w<96, 4, 3, 3>},
+    {10, "tma2s-128x4x2-occ2", launch_tma2s<128, 4, 2, 2, false>, grid_tma2s<128, 4, 2, 2, false>},
+    {17, "tma2s-128x4x2-occ2-pipelined", launch_tma2s<128, 4, 2, 2, true>, grid_tma2s<128, 4, 2, 2, true>},
+    {20, "tma2w-128x4x3-occ2", launch_tma2w<128, 4, 3, 2>, grid_tma2w<128, 4, 3, 2>},
 };
-constexpr int kDefaultTma2Variant = 10;
+int default_tma2_variant()
+{
+    static const int v = [] {
+        const char *e = std::getenv("DLESM_VARIANT2");
+        const int x = e ? std::atoi(e) : 0;
+        for (const auto &t : kTma2Variants)
+            if (t.id == x) return x;
+        return 10;
+    }();
+    return v;
+}
 
 }  // namespace
 
 bool fused2_supported(const Fused2Args &a)
 {
-    if (a.tmask && a.pitch % 4 != 0) return false;   // the int32 tmask tile needs 16-byte row starts
     return a.pitch % 2 == 0 && encode_fn() != nullptr && a.b.xs >= 3 && a.b.ys >= 3 && a.b.xe + 2 <= a.pitch &&
-           a.b.ye + 2 <= a.ny && !a.sc.first;
+           a.b.ye + 2 <= a.ny && !a.sc.first && (a.mask8 == nullptr || a.mask8_pitch % 16 == 0);
 }
 
 bool fused2_push_supported(int variant) { return variant == 0 || (variant >= 10 && variant < 20); }
@@ -1275,8 +1267,8 @@ cudaError_t sw_step2_fused(const Fused2Args &a, int variant, cudaStream_t s)
 {
     if (a.b.xe < a.b.xs || a.b.ye < a.b.ys) return cudaSuccess;
     if (!fused2_supported(a)) return cudaErrorNotSupported;
-    if ((a.push.n > 0 || a.tmask) && !fused2_push_supported(variant)) return cudaErrorNotSupported;
-    if (variant == 0) variant = kDefaultTma2Variant;
+    if (variant == 0) variant = default_tma2_variant();
+    if ((a.push.n > 0 || a.mask8) && !fused2_push_supported(variant)) return cudaErrorNotSupported;
     for (const auto &v : kTma2Variants)
         if (v.id == variant) {
             cudaError_t e = v.launch(a, s);
@@ -1286,37 +1278,47 @@ cudaError_t sw_step2_fused(const Fused2Args &a, int variant, cudaStream_t s)
     return cudaErrorInvalidValue;
 }
 
+void fused2_grid(const Fused2Args &a, int variant, int grid[2])
+{
+    grid[0] = grid[1] = 0;
+    if (variant == 0) variant = default_tma2_variant();
+    for (const auto &v : kTma2Variants)
+        if (v.id == variant) v.grid(a, grid);
+}
+
 namespace {
 struct TmaVariant {
     int id;
     const char *name;
     cudaError_t (*launch)(const FusedArgs &, cudaStream_t);
+    void (*grid)(const FusedArgs &, int[2]);
 };
-// {columns, rows per chunk, stages, resident CTAs per SM}.  ids >= 20 start every strip on a
-// 128-byte line of the row (aligned origin); ids < 20 start strips at xstart (kept for the
-// comparison in DESIGN.md).
+// {columns, rows per chunk, stages, resident CTAs per SM}.  25 is the shipped kernel (strips on
+// 128-byte lines of the row), 23 the alternate chunk shape, 5 the same kernel as 25 with strips
+// starting at the first column of their x-tile (used when the tile-grid knob asks for x-tiles).
 const TmaVariant kTmaVariants[] = {
-    {2, "tma-128x4x2-occ3-unaligned", launch_tma<128, 4, 2, 3, false>},
-    {5, "tma-128x4x3-occ2-unaligned", launch_tma<128, 4, 3, 2, false>},
-    {22, "tma-128x4x2-occ3", launch_tma<128, 4, 2, 3, true>},
-    {23, "tma-128x8x2-occ2", launch_tma<128, 8, 2, 2, true>},
-    {24, "tma-128x4x3-occ3", launch_tma<128, 4, 3, 3, true>},
-    {25, "tma-128x4x3-occ2", launch_tma<128, 4, 3, 2, true>},
-    {26, "tma-128x4x4-occ2", launch_tma<128, 4, 4, 2, true>},
-    {27, "tma-128x2x6-occ2", launch_tma<128, 2, 6, 2, true>},
-    {28, "tma-128x8x3-occ1", launch_tma<128, 8, 3, 1, true>},
-    {29, "tma-128x2x8-occ2", launch_tma<128, 2, 8, 2, true>},
-    {30, "tma-128x2x4-occ3", launch_tma<128, 2, 4, 3, true>},
-    {31, "tma-128x16x2-occ1", launch_tma<128, 16, 2, 1, true>},
-    {32, "tma-128x8x4-occ1", launch_tma<128, 8, 4, 1, true>},
-    {33, "tma-128x4x8-occ1", launch_tma<128, 4, 8, 1, true>},
-    {34, "tma-128x12x3-occ1", launch_tma<128, 12, 3, 1, true>},
+    {5, "tma-128x4x3-occ2-unaligned", launch_tma<128, 4, 3, 2, false>, grid_tma<128, 4, 3, 2, false>},
+    {23, "tma-128x8x2-occ2", launch_tma<128, 8, 2, 2, true>, grid_tma<128, 8, 2, 2, true>},
+    {25, "tma-128x4x3-occ2", launch_tma<128, 4, 3, 2, true>, grid_tma<128, 4, 3, 2, true>},
 };
 const TmaVariant *find_tma(int id)
 {
     for (const auto &v : kTmaVariants)
         if (v.id == id) return &v;
     return nullptr;
+}
+bool tma_eligible(const FusedArgs &a)
+{
+    // FP64 rows must start 16-byte aligned (even pitch); a masked run needs the byte image
+    return (a.pitch % 2 == 0) && (a.tmask == nullptr || (a.mask8 != nullptr && a.mask8_pitch % 16 == 0)) &&
+           encode_fn() != nullptr;
+}
+int resolve_variant(const FusedArgs &a, int variant)
+{
+    if (variant == 0) variant = tma_eligible(a) ? kDefaultTmaVariant : 1;
+    // strips of an aligned-origin kernel must start on 128-byte lines; x-tiles start anywhere
+    if (variant >= 20 && a.tiles.nx > 1) variant = kUnalignedTmaVariant;
+    return variant;
 }
 }  // namespace
 
@@ -1328,19 +1330,14 @@ const char *fused_variant_name(int variant)
     return v ? v->name : "unknown";
 }
 
-bool fused_push_supported(const FusedArgs &a, int variant)
-{
-    const bool tma_ok = (a.pitch % 2 == 0) && (a.tmask == nullptr || a.pitch % 4 == 0) && encode_fn() != nullptr;
-    return tma_ok && variant != 1;
-}
+bool fused_push_supported(const FusedArgs &a, int variant) { return tma_eligible(a) && variant != 1; }
 
 cudaError_t sw_step_fused(const FusedArgs &a, int variant, cudaStream_t s)
 {
     if (a.b.xe < a.b.xs || a.b.ye < a.b.ys) return cudaSuccess;
     if (a.push.n > 0 && !fused_push_supported(a, variant)) return cudaErrorNotSupported;
-    // FP64 rows must start 16-byte aligned (even pitch); int32 tmask rows need pitch % 4 == 0
-    const bool tma_ok = (a.pitch % 2 == 0) && (a.tmask == nullptr || a.pitch % 4 == 0) && encode_fn() != nullptr;
-    if (variant == 0) variant = tma_ok ? kDefaultTmaVariant : 1;
+    const bool tma_ok = tma_eligible(a);
+    variant = resolve_variant(a, variant);
     if (variant >= 2 && !tma_ok) return cudaErrorNotSupported;
     cudaError_t e;
     if (variant == 1) {
@@ -1359,5 +1356,19 @@ cudaError_t sw_step_fused(const FusedArgs &a, int variant, cudaStream_t s)
     return e;
 }
 
+void fused_grid(const FusedArgs &a, int variant, int grid[2])
+{
+    variant = resolve_variant(a, variant);
+    if (variant == 1) {
+        grid[0] = (a.b.xe - a.b.xs + 1 + 127) / 128;
+        grid[1] = (a.b.ye - a.b.ys + 1 + 63) / 64;
+        return;
+    }
+    grid[0] = grid[1] = 0;
+    const TmaVariant *v = find_tma(variant);
+    if (v) v->grid(a, grid);
+}
+
+}  // namespace DLESM_FNS
 }  // namespace k
 }  // namespace dlesm

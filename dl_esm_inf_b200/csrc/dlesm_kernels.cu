@@ -338,6 +338,29 @@ cudaError_t mask_convert(int *m, double *d, size_t n, bool to_double, cudaStream
     return cudaGetLastError();
 }
 
+// byte image of the tmask for the TMA ring of the fused sweeps: 1 = wet (tmask == 1), 0 otherwise;
+// its own row pitch (a multiple of 16 bytes: TMA rows must start 16-byte aligned whatever
+// DL_ESM_ALIGNMENT is); columns beyond the array are dry
+__global__ void __launch_bounds__(256) mask_to_bytes_kernel(const int *__restrict__ m, int pitch, int ny,
+                                                            unsigned char *__restrict__ m8, int pitch8)
+{
+    const size_t n = static_cast<size_t>(pitch8) * ny;
+    for (size_t t = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; t < n;
+         t += static_cast<size_t>(gridDim.x) * blockDim.x) {
+        const size_t j = t / pitch8, i = t - j * pitch8;
+        m8[t] = (i < static_cast<size_t>(pitch) && m[j * pitch + i] == 1) ? 1 : 0;
+    }
+}
+cudaError_t mask_to_bytes(const int *m, int pitch, int ny, unsigned char *m8, int pitch8, cudaStream_t s)
+{
+    const size_t n = static_cast<size_t>(pitch8) * ny;
+    if (n == 0) return cudaSuccess;
+    const unsigned blocks = n / 256 + 1 < kSMs * 8 ? static_cast<unsigned>(n / 256 + 1) : kSMs * 8;
+    mask_to_bytes_kernel<<<blocks, 256, 0, s>>>(m, pitch, ny, m8, pitch8);
+    count_launch();
+    return cudaGetLastError();
+}
+
 // ---------------------------------------------------------------------------------------
 // Halo pack / unpack (src/parallel_comms_mod.f90:1678-1683, 1788-1793): every patch of every
 // field in one launch; within a patch j is the outer and i the inner index, as the
@@ -444,8 +467,8 @@ cudaError_t gather_box(const double *f, int pitch, Box b, double *packed, cudaSt
 // the sweep's peer stores are complete when this kernel starts, so a system-scope release of
 // the epoch into each neighbour's flag array publishes them; then wait (acquire) until every
 // neighbour has published the same epoch into ours.  One thread per neighbour.  The wait is
-// bounded (~20 s of SM clocks): on time-out *err is set and the kernel returns instead of
-// hanging the GPU.
+// bounded (~20 s of SM clocks): on time-out *err is set and the kernel TRAPS -- the run ends with
+// a CUDA error on the next call instead of hanging the GPU or sweeping over stale halos.
 // ---------------------------------------------------------------------------------------
 __global__ void peer_signal_wait_kernel(PeerFlags pf, unsigned long long epoch, int *err)
 {
@@ -459,8 +482,13 @@ __global__ void peer_signal_wait_kernel(PeerFlags pf, unsigned long long epoch, 
         asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(pf.local[q]) : "memory");
         if (v >= epoch) break;
         if (clock64() - t0 > 40000000000LL) {
+            // ~20 s of SM clocks without the neighbour's epoch: the ranks are out of step.  Carrying
+            // on would sweep over halos that were never pushed, so the time-out is FATAL: the flag is
+            // set for dlesm_dev_sync's message and the kernel traps, which fails every later CUDA
+            // call of this process (checksum, get_data, gather ... all return DLESM_ERR_CUDA).
             atomicExch(err, 1);
-            break;
+            __threadfence_system();
+            __trap();
         }
         __nanosleep(200);
     }

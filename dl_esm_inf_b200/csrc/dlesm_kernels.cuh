@@ -34,8 +34,21 @@ struct SwScalars {
     double fsdx, fsdy;       // 4/dx, 4/dy
     double tdts8, tdtsdx, tdtsdy;
     double alpha;
+    // the same constants halved (exact): the fused sweeps carry 2*cu, 2*cv -- they drop the 0.5 of
+    // cu = 0.5*(p+p)*u and fold it into the constants cu, cv are multiplied by.  Scaling by a power
+    // of two commutes with rounding, so the results keep their bits.
+    double tdts8h, tdtsdxh, tdtsdyh;
     int first;               // 1 => no time filter
 };
+inline SwScalars make_scalars(double dx, double dy, double tdt, double alpha, int first)
+{
+    SwScalars sc;
+    sc.fsdx = 4.0 / dx; sc.fsdy = 4.0 / dy;
+    sc.tdts8 = tdt / 8.0; sc.tdtsdx = tdt / dx; sc.tdtsdy = tdt / dy;
+    sc.tdts8h = 0.5 * sc.tdts8; sc.tdtsdxh = 0.5 * sc.tdtsdx; sc.tdtsdyh = 0.5 * sc.tdtsdy;
+    sc.alpha = alpha; sc.first = first;
+    return sc;
+}
 
 // ---- field_mod operations ----
 cudaError_t copy_field(const double *in, double *out, size_t n, cudaStream_t s);
@@ -105,28 +118,33 @@ struct PeerFlags {
 cudaError_t peer_signal_wait(const PeerFlags &pf, unsigned long long epoch, int *err, cudaStream_t s);
 
 // ---- the fused step ----
+// Tile grid of a sweep: the CUDA analogue of the reference's OpenMP tile grid (GOCEAN_OMP_GRID="AxB",
+// r2d_field(..., do_tile), src/field_mod.f90:300-325,1473-1503).  nx tiles across the swept box, each
+// cut into strips of the kernel's width; ny tiles along j, one CTA marching each.  0 = the library's
+// own choice (one x-tile on 128-byte lines; segment height picked for whole waves of CTAs).
+struct SweepTiles {
+    int nx, ny;
+};
 struct FusedArgs {
     const double *u, *v, *p;
     double *uold, *vold, *pold;
     double *unew, *vnew, *pnew;
-    const int *tmask;   // may be null
+    const int *tmask;            // int32 (nx, ny) as grid_init builds it; may be null (all wet)
+    const unsigned char *mask8;  // byte image of tmask (1 = wet) with row pitch `mask8_pitch`, for the TMA ring
+    int mask8_pitch;
     int pitch, ny;
     Box b;              // internal region (identical for U,V,T,F under SW periodic)
     SwScalars sc;
+    SweepTiles tiles;
     PushPlan push;      // push.n == 0: halos of the new fields are left to the caller
 };
-// whether sw_step_fused can push halos for these arguments (TMA variants only)
-bool fused_push_supported(const FusedArgs &a, int variant);
-constexpr int kNumFusedVariants = 6;
-cudaError_t sw_step_fused(const FusedArgs &a, int variant, cudaStream_t s);
-const char *fused_variant_name(int variant);
 
 // ---- two model steps in one sweep (temporal blocking): 96 B / point per TWO steps ----
 // Needs a tile with halo width >= 2: u,v,p valid to depth 2 around `b`, uold,vold,pold valid to
 // depth 1.  The intermediate state (step n+1) is recomputed on the depth-1 ring and never
 // stored.  Outputs (step n+2) go to separate arrays: u2,v2,p2 and the twice-filtered
 // uold2,vold2,pold2 (not in place: neighbouring CTAs still read the old fields' ring).
-// No tmask, not the first (unfiltered) step.
+// Not the first (unfiltered) step.
 // halo push of the two-step sweep: like PushSeg, six destinations (u2,v2,p2,uold2,vold2,pold2)
 struct PushSeg2 {
     int i0, i1, j0, j1;
@@ -143,23 +161,45 @@ struct PushPlan2 {
 struct Fused2Args {
     const double *u, *v, *p, *uold, *vold, *pold;
     double *u2, *v2, *p2, *uold2, *vold2, *pold2;
-    const int *tmask;   // may be null; must hold the PERIODIC mask two cells deep around b
+    const unsigned char *mask8;  // may be null; byte image of the PERIODIC mask two cells deep around b
+    int mask8_pitch;
     int pitch, ny;
     Box b;
     SwScalars sc;
+    SweepTiles tiles;
     PushPlan2 push;     // push.n == 0: halos of the outputs are left to the caller
 };
-bool fused2_supported(const Fused2Args &a);
-// whether `variant` of the two-step sweep can push halos / take a tmask (the shuffle form, ids
-// 10..19 and 0)
-bool fused2_push_supported(int variant);
-cudaError_t sw_step2_fused(const Fused2Args &a, int variant, cudaStream_t s);
+
+// The fused sweeps exist twice: namespace fma_off is compiled with -fmad=false (one rounding per
+// operation: bit-identical to the oracle and to the reference's FMA-free Fortran), fma_on is the
+// same source compiled with -fmad=true (contracted arithmetic: fewer FP64 instructions, results
+// within 1e-12 relative of the oracle instead of bit-equal).  dlesm_set_arith selects.
+#define DLESM_FUSED_API(NS)                                                                          \
+    namespace NS {                                                                                   \
+    /* whether sw_step_fused can push halos for these arguments (TMA variants only) */               \
+    bool fused_push_supported(const FusedArgs &a, int variant);                                      \
+    cudaError_t sw_step_fused(const FusedArgs &a, int variant, cudaStream_t s);                      \
+    const char *fused_variant_name(int variant);                                                     \
+    bool fused2_supported(const Fused2Args &a);                                                      \
+    /* whether `variant` of the two-step sweep can push halos / take a mask (the shuffle form) */    \
+    bool fused2_push_supported(int variant);                                                         \
+    cudaError_t sw_step2_fused(const Fused2Args &a, int variant, cudaStream_t s);                    \
+    /* launch geometry the sweep would use (grid.x, grid.y) -- for the tiling knob's tests */        \
+    void fused_grid(const FusedArgs &a, int variant, int grid[2]);                                   \
+    void fused2_grid(const Fused2Args &a, int variant, int grid[2]);                                 \
+    }
+DLESM_FUSED_API(fma_off)
+DLESM_FUSED_API(fma_on)
+#undef DLESM_FUSED_API
+
 // periodic halo fill to `depth` cells on one rank (wrapped source index; corners included)
 cudaError_t periodic_halos_deep(double *const *fields, int nfields, int pitch, Box internal, int depth,
                                 cudaStream_t s);
 
 // m[t] -> d[t] (to_double) or d[t] -> m[t]: the tmask rides the FP64 halo machinery once
 cudaError_t mask_convert(int *m, double *d, size_t n, bool to_double, cudaStream_t s);
+// byte image of an int32 tmask for the TMA ring: m8[(j-1)*pitch8 + (i-1)] = (tmask(i,j) == 1)
+cudaError_t mask_to_bytes(const int *m, int pitch, int ny, unsigned char *m8, int pitch8, cudaStream_t s);
 
 // classic initial conditions, synthetic (device sin/cos)
 cudaError_t sw_init(double *u, double *v, double *p, int pitch, Box b, int gx0, int gy0, int M,

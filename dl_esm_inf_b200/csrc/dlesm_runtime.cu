@@ -29,6 +29,10 @@ namespace {
 
 struct FieldRec {
     int nx, ny;
+    // dirty-flag halos (halo_type%needs_update, src/halo_mod.f90:10-25): the depth to which this
+    // array's halos are known to be up to date; 0 = out of date.  Every entry point that writes the
+    // array resets it, halo_exchange / the periodic fill / a pushing sweep set it.
+    int clean_depth = 0;
 };
 
 struct PeerGroup {
@@ -37,6 +41,15 @@ struct PeerGroup {
     std::vector<int> recvs;
     long long send_off = 0, recv_off = 0;  // element offsets for ONE field
     long long send_n = 0, recv_n = 0;
+};
+
+// one set of map_comms tables with the per-peer message plan derived from it
+struct CommTables {
+    dlesm_comms t{};
+    std::vector<PeerGroup> groups;
+    long long send_total = 0, recv_total = 0;  // per field
+    int depth = 1;                             // halo depth the tables were built for
+    bool valid = false;
 };
 
 struct Context {
@@ -59,21 +72,29 @@ struct Context {
     // communication
     bool comm_ready = false;
     ncclComm_t comm = nullptr;
-    bool have_comms = false;
-    dlesm_comms comms{};
-    std::vector<PeerGroup> groups;
-    long long send_total = 0, recv_total = 0;  // per field
+    CommTables installed;   // dlesm_dev_set_comms: the module-level tables of parallel_comms_mod
     // halo push: peer-mapped neighbours (dlesm_dev_peer_register)
     struct PeerView {
         std::vector<double *> by_rank;  // this field's counterpart on rank r (0-based), or null
         std::vector<int> pitch_by_rank; // its pitch there (tile widths may differ by one)
+        std::vector<std::string> handles;   // IPC handles this view holds a reference on
     };
     std::unordered_map<const void *, PeerView> peers;
     unsigned long long *flags = nullptr;              // [kMaxRanks] epochs published by neighbours
     std::vector<unsigned long long *> peer_flags;     // neighbours' flag arrays, by rank
-    std::vector<void *> ipc_opened;                   // mappings to close at finalise
+    std::vector<void *> flag_mappings;                // flag-array mappings, closed at finalise
     unsigned long long push_epoch = 0;
     int *push_err = nullptr;                          // device flag: a neighbour wait timed out
+    // arithmetic of the fused sweeps (dlesm_set_arith) and the tile-grid knob (GOCEAN_OMP_GRID)
+    int arith = DLESM_ARITH_EXACT;
+    k::SweepTiles sweep_tiles{0, 0};
+    bool tiling_initialised = false;   // `tiling_initialised` of src/field_mod.f90:236
+    // byte images of int32 tmasks for the TMA ring, keyed by the mask's device pointer
+    struct Mask8 {
+        unsigned char *p = nullptr;
+        int pitch = 0;
+    };
+    std::unordered_map<const void *, Mask8> mask8;
     // profiling of the dominant kernel
     bool profile = false;
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events;
@@ -127,6 +148,22 @@ int lookup(const void *p, FieldRec &out)
     return DLESM_OK;
 }
 
+// dirty-flag halos: see FieldRec::clean_depth
+void mark_written(const void *p)
+{
+    Context &c = ctx();
+    std::lock_guard<std::mutex> lock(c.mu);
+    auto it = c.registry.find(p);
+    if (it != c.registry.end()) it->second.clean_depth = 0;
+}
+void mark_clean(const void *p, int depth)
+{
+    Context &c = ctx();
+    std::lock_guard<std::mutex> lock(c.mu);
+    auto it = c.registry.find(p);
+    if (it != c.registry.end()) it->second.clean_depth = depth;
+}
+
 int ensure_scratch(size_t n)
 {
     Context &c = ctx();
@@ -176,7 +213,6 @@ int internal_pitch_of(const void *device_ptr, int &pitch, int &ny)
 // =========================================================================================
 extern "C" const char *dlesm_last_error(void) { return last_error_cstr(); }
 extern "C" int dlesm_last_status(void) { return last_status(); }
-extern "C" const char *dlesm_version(void) { return "dlesm_b200 0.1 (sm_100a, FP64, fmad=false)"; }
 
 extern "C" int dlesm_parallel_init(int rank1, int nranks)
 {
@@ -218,6 +254,8 @@ extern "C" int dlesm_device_init(int device)
     CU(cudaMallocHost(&c.host_result, 8 * sizeof(double)));
     c.device = device;
     c.device_ready = true;
+    if (const char *ar = std::getenv("DLESM_ARITH"))
+        if (std::strcmp(ar, "fma") == 0 || std::strcmp(ar, "contracted") == 0) c.arith = DLESM_ARITH_CONTRACTED;
     return DLESM_OK;
 }
 
@@ -266,7 +304,13 @@ extern "C" void dlesm_parallel_abort(const char *msg)
 extern "C" int dlesm_get_rank(void) { return pstate().rank; }
 extern "C" int dlesm_get_num_ranks(void) { return pstate().nranks; }
 extern "C" int dlesm_on_master(void) { return pstate().rank == 1; }
-extern "C" void dlesm_reset_saved_state(void) { reset_saved_state(); }
+extern "C" void dlesm_reset_saved_state(void)
+{
+    reset_saved_state();
+    // the SAVEd tiling of field_mod (`tiling_initialised`, `decomp`: src/field_mod.f90:236-240)
+    ctx().tiling_initialised = false;
+    ctx().sweep_tiles = k::SweepTiles{0, 0};
+}
 extern "C" int dlesm_set_extensions(int flags)
 {
     pstate().extensions = flags;
@@ -453,6 +497,7 @@ int hook_copy(void *device, void *host, bool to_device, int startx, int starty, 
                                  static_cast<size_t>(nx) * sizeof(double), ny, kind, c.stream));
     }
     if (blocking) CU(cudaStreamSynchronize(c.stream));
+    if (to_device) mark_written(device);
     return DLESM_OK;
 }
 }  // namespace
@@ -552,6 +597,7 @@ extern "C" int dlesm_dev_copy_field(const void *in, void *out)
     }
     CU(k::copy_field(static_cast<const double *>(in), static_cast<double *>(out),
                      static_cast<size_t>(a.nx) * a.ny, ctx().stream));
+    mark_clean(out, a.clean_depth);   // the whole array incl. its halos is copied
     return DLESM_OK;
 }
 
@@ -574,6 +620,7 @@ extern "C" int dlesm_dev_copy_patch(void *f, int sxs, int sxe, int sys, int sye,
     if (rc != DLESM_OK) return rc;
     CU(k::copy_patch(static_cast<double *>(f), r.nx, k::Box{sxs, sxe, sys, sye}, k::Box{dxs, dxe, dys, dye},
                      ctx().scratch, ctx().stream));
+    mark_written(f);
     return DLESM_OK;
 }
 
@@ -583,6 +630,7 @@ extern "C" int dlesm_dev_set_field(void *f, double val)
     int rc = lookup(f, r);
     if (rc != DLESM_OK) return rc;
     CU(k::set_field(static_cast<double *>(f), static_cast<size_t>(r.nx) * r.ny, val, ctx().stream));
+    mark_written(f);
     return DLESM_OK;
 }
 
@@ -614,6 +662,7 @@ extern "C" int dlesm_dev_periodic_halos(void *f, int xs, int xe, int ys, int ye,
     }
     double *fl[1] = {static_cast<double *>(f)};
     CU(k::periodic_halos(fl, 1, r.nx, k::Box{xs, xe, ys, ye}, px != 0, py != 0, ctx().stream));
+    if (px && py) mark_clean(f, 1);
     return DLESM_OK;
 }
 
@@ -629,6 +678,7 @@ extern "C" int dlesm_dev_periodic_halos_deep(void *f, int xs, int xe, int ys, in
     }
     double *fl[1] = {static_cast<double *>(f)};
     CU(k::periodic_halos_deep(fl, 1, r.nx, k::Box{xs, xe, ys, ye}, depth, ctx().stream));
+    mark_clean(f, depth);
     return DLESM_OK;
 }
 
@@ -695,14 +745,14 @@ extern "C" int dlesm_comm_plan_build(const dlesm_comms *t, int rank1, dlesm_comm
     return DLESM_OK;
 }
 
-extern "C" int dlesm_dev_set_comms(const dlesm_comms *t)
+namespace {
+int build_tables(const dlesm_comms *t, int depth, CommTables &out)
 {
-    Context &c = ctx();
     dlesm_comm_plan plan;
     int rc = dlesm_comm_plan_build(t, pstate().rank, &plan);
     if (rc != DLESM_OK) return rc;
-    c.comms = *t;
-    c.groups.clear();
+    out.t = *t;
+    out.groups.clear();
     for (int g = 0; g < plan.npeers; ++g) {
         PeerGroup pg;
         pg.peer0 = plan.peer[g];
@@ -712,48 +762,70 @@ extern "C" int dlesm_dev_set_comms(const dlesm_comms *t)
         pg.recv_off = plan.recv_off[g];
         pg.send_n = plan.send_n[g];
         pg.recv_n = plan.recv_n[g];
-        c.groups.push_back(pg);
+        out.groups.push_back(pg);
     }
-    c.send_total = plan.send_total;
-    c.recv_total = plan.recv_total;
-    c.have_comms = true;
+    out.send_total = plan.send_total;
+    out.recv_total = plan.recv_total;
+    out.depth = depth;
+    out.valid = true;
     return DLESM_OK;
 }
 
-extern "C" int dlesm_dev_halo_exchange(void *const *fields, int nfields)
+// exchange_generic on device-resident fields with the given tables.  With DLESM_EXT_DIRTY_HALOS
+// fields whose halos are already up to date to the tables' depth are left out (all clean: no launch).
+int exchange_with(void *const *fields_in, int nfields_in, const CommTables &ct)
 {
     Context &c = ctx();
-    if (!c.have_comms || (c.comms.nsend == 0 && c.comms.nrecv == 0)) return DLESM_OK;  // nothing to do
-    if (nfields < 1 || nfields > k::kMaxExchangeFields) {
+    if (!ct.valid || (ct.t.nsend == 0 && ct.t.nrecv == 0)) return DLESM_OK;  // nothing to do
+    if (nfields_in < 1 || nfields_in > k::kMaxExchangeFields) {
         set_error(DLESM_ERR_ARGS, "halo_exchange: between 1 and 8 fields per call");
         return DLESM_ERR_ARGS;
     }
     int rc = ensure_device();
     if (rc != DLESM_OK) return rc;
-    FieldRec r0;
-    rc = lookup(fields[0], r0);
-    if (rc != DLESM_OK) return rc;
-    for (int q = 1; q < nfields; ++q) {
+    void *fields[k::kMaxExchangeFields];
+    int nfields = 0;
+    FieldRec r0{};
+    const bool skip_clean = (pstate().extensions & DLESM_EXT_DIRTY_HALOS) != 0;
+    for (int q = 0; q < nfields_in; ++q) {
         FieldRec rq;
-        rc = lookup(fields[q], rq);
+        rc = lookup(fields_in[q], rq);
         if (rc != DLESM_OK) return rc;
+        if (q == 0) r0 = rq;
         if (rq.nx != r0.nx || rq.ny != r0.ny) {
             set_error(DLESM_ERR_ARGS, "halo_exchange: fields have different shapes");
             return DLESM_ERR_ARGS;
         }
+        if (skip_clean && rq.clean_depth >= ct.depth) continue;
+        fields[nfields++] = fields_in[q];
     }
-    const long long tot = std::max(c.send_total, c.recv_total) * nfields;
+    if (nfields == 0) return DLESM_OK;   // every halo is up to date: nothing is launched
+    const dlesm_comms &t = ct.t;
+    // the tables may come from another grid (module-level state): every patch must lie inside
+    // the fields, or the pack / unpack kernels would run off the allocation
+    for (int q = 0; q < t.nsend; ++q)
+        if (t.nxsend[q] > 0 && (t.isrcsend[q] < 1 || t.jsrcsend[q] < 1 || t.isrcsend[q] + t.nxsend[q] - 1 > r0.nx ||
+                                t.jsrcsend[q] + t.nysend[q] - 1 > r0.ny)) {
+            set_error(DLESM_ERR_ARGS, "halo_exchange: a send patch of the installed tables lies outside the field (tables of another grid?)");
+            return DLESM_ERR_ARGS;
+        }
+    for (int q = 0; q < t.nrecv; ++q)
+        if (t.nxrecv[q] > 0 && (t.idesrecv[q] < 1 || t.jdesrecv[q] < 1 || t.idesrecv[q] + t.nxrecv[q] - 1 > r0.nx ||
+                                t.jdesrecv[q] + t.nyrecv[q] - 1 > r0.ny)) {
+            set_error(DLESM_ERR_ARGS, "halo_exchange: a receive patch of the installed tables lies outside the field (tables of another grid?)");
+            return DLESM_ERR_ARGS;
+        }
+    const long long tot = std::max(ct.send_total, ct.recv_total) * nfields;
     rc = ensure_xbuf(static_cast<size_t>(tot) + 1);
     if (rc != DLESM_OK) return rc;
     const int me0 = pstate().rank - 1;
-    const dlesm_comms &t = c.comms;
 
     k::PackPlan sp{}, rp{};
     sp.nfields = rp.nfields = nfields;
     sp.pitch = rp.pitch = r0.nx;
     for (int q = 0; q < nfields; ++q) sp.fields[q] = rp.fields[q] = static_cast<double *>(fields[q]);
     bool remote = false;
-    for (const auto &g : c.groups) {
+    for (const auto &g : ct.groups) {
         long long off = g.send_off * nfields;
         for (int s : g.sends) {
             k::Segment &sg = sp.seg[sp.nseg++];
@@ -776,7 +848,7 @@ extern "C" int dlesm_dev_halo_exchange(void *const *fields, int nfields)
     }
     CU(k::pack(sp, c.sendbuf, c.stream));
     if (remote) NC(ncclGroupStart());
-    for (const auto &g : c.groups) {
+    for (const auto &g : ct.groups) {
         if (g.peer0 == me0) {
             // wrap-around neighbour is this rank itself: the "message" never leaves the device
             if (g.send_n > 0)
@@ -794,7 +866,34 @@ extern "C" int dlesm_dev_halo_exchange(void *const *fields, int nfields)
     }
     if (remote) NC(ncclGroupEnd());
     CU(k::unpack(rp, c.recvbuf, c.stream));
+    for (int q = 0; q < nfields; ++q) mark_clean(fields[q], ct.depth);
     return DLESM_OK;
+}
+}  // namespace
+
+extern "C" int dlesm_dev_set_comms(const dlesm_comms *t)
+{
+    clear_error();
+    Context &c = ctx();
+    if (!t) {   // back to the state before any grid_init: no tables
+        c.installed = CommTables{};
+        return DLESM_OK;
+    }
+    // depth of the tables = the widest strip they receive
+    int depth = 1;
+    for (int q = 0; q < t->nrecv && q < DLESM_MAXCOMM; ++q)
+        depth = std::max(depth, std::min(t->nxrecv[q], t->nyrecv[q]));
+    CommTables ct;
+    int rc = build_tables(t, depth, ct);
+    if (rc != DLESM_OK) return rc;
+    c.installed = ct;
+    return DLESM_OK;
+}
+
+extern "C" int dlesm_dev_halo_exchange(void *const *fields, int nfields)
+{
+    clear_error();
+    return exchange_with(fields, nfields, ctx().installed);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -803,6 +902,9 @@ extern "C" int dlesm_dev_halo_exchange(void *const *fields, int nfields)
 // ncclAllGather, and the handles of this rank's neighbours (the destinations of its map_comms
 // send list) are opened, which maps the neighbours' arrays into this process over NVLink.
 // A flag array per rank is shared the same way for the per-step hand-shake.
+// Mappings are reference-counted per IPC handle (cudaMalloc may serve several fields from one
+// allocation): a field's registration can be dropped (dlesm_dev_peer_unregister) without
+// unmapping what another registered field -- of this or of another model object -- still uses.
 // ---------------------------------------------------------------------------------------
 namespace {
 constexpr int kMaxRanks = 64;
@@ -844,56 +946,61 @@ int make_entry(const void *ptr, int pitch, int ny, IpcEntry &e)
     return DLESM_OK;
 }
 
-std::map<std::string, void *> &opened_handles()
+struct OpenedHandle {
+    void *base = nullptr;
+    int refs = 0;
+};
+std::map<std::string, OpenedHandle> &opened_handles()
 {
-    static std::map<std::string, void *> m;
+    static std::map<std::string, OpenedHandle> m;
     return m;
 }
 
-// `keep`: the mapping lives until finalise (flag arrays); otherwise until the next
-// dlesm_dev_peer_unregister_all
-int open_entry(const IpcEntry &e, void **out, bool keep)
+// maps the allocation behind `e` (or reuses the mapping) and takes one reference on it; `key_out`
+// identifies the mapping for release_handle
+int open_entry(const IpcEntry &e, void **out, std::string &key_out)
 {
-    std::string key(reinterpret_cast<const char *>(&e.handle), sizeof(e.handle));
+    key_out.assign(reinterpret_cast<const char *>(&e.handle), sizeof(e.handle));
+    auto &m = opened_handles();
+    auto it = m.find(key_out);
+    if (it == m.end()) {
+        void *base = nullptr;
+        CU(cudaIpcOpenMemHandle(&base, e.handle, cudaIpcMemLazyEnablePeerAccess));
+        it = m.emplace(key_out, OpenedHandle{base, 0}).first;
+    }
+    ++it->second.refs;
+    *out = static_cast<char *>(it->second.base) + e.offset;
+    return DLESM_OK;
+}
+void release_handle(const std::string &key)
+{
     auto &m = opened_handles();
     auto it = m.find(key);
-    void *base = nullptr;
-    if (it != m.end()) {
-        base = it->second;
-    } else {
-        CU(cudaIpcOpenMemHandle(&base, e.handle, cudaIpcMemLazyEnablePeerAccess));
-        if (!keep) {
-            m[key] = base;
-            ctx().ipc_opened.push_back(base);
-        }
+    if (it == m.end()) return;
+    if (--it->second.refs <= 0) {
+        cudaIpcCloseMemHandle(it->second.base);
+        m.erase(it);
     }
-    *out = static_cast<char *>(base) + e.offset;
-    return DLESM_OK;
 }
-}  // namespace
 
-// Collective.  Unmaps every neighbour field mapped by dlesm_dev_peer_register (CUDA requires
-// importers to close before the exporter frees) and ends with a barrier, after which each
-// rank may free its own registered fields.
-extern "C" int dlesm_dev_peer_unregister_all(void)
+int barrier_all()
 {
-    clear_error();
-    Context &c = ctx();
-    if (c.device_ready) CU(cudaStreamSynchronize(c.stream));
-    for (void *base : c.ipc_opened) cudaIpcCloseMemHandle(base);
-    c.ipc_opened.clear();
-    opened_handles().clear();
-    c.peers.clear();
-    if (pstate().nranks > 1 && c.comm_ready) {
+    if (pstate().nranks > 1 && ctx().comm_ready) {
         double one = 1.0;
-        return dlesm_global_sum(&one);
+        return dlesm_global_sum(&one);   // a one-double allreduce is the barrier
     }
     return DLESM_OK;
 }
 
-extern "C" int dlesm_dev_peer_register(void *const *fields, int nfields)
+// neighbours (0-based ranks) named by a set of tables
+void neighbours_of(const CommTables &ct, std::vector<char> &is_nb)
 {
-    clear_error();
+    for (const auto &g : ct.groups)
+        if (g.peer0 >= 0 && g.peer0 < static_cast<int>(is_nb.size())) is_nb[g.peer0] = 1;
+}
+
+int peer_register_with(void *const *fields, int nfields, const CommTables &ct)
+{
     Context &c = ctx();
     if (nfields < 1 || nfields > 12) {
         set_error(DLESM_ERR_ARGS, "peer_register: between 1 and 12 fields per call");
@@ -910,6 +1017,10 @@ extern "C" int dlesm_dev_peer_register(void *const *fields, int nfields)
     for (int q = 0; q < nfields; ++q) {
         rc = lookup(fields[q], recs[q]);
         if (rc != DLESM_OK) return rc;
+        if (c.peers.count(fields[q])) {
+            set_error(DLESM_ERR_STATE, "peer_register: field is already registered (unregister it first)");
+            return DLESM_ERR_STATE;
+        }
     }
     if (!c.flags) {
         CU(cudaMalloc(&c.flags, kMaxRanks * sizeof(unsigned long long)));
@@ -928,8 +1039,8 @@ extern "C" int dlesm_dev_peer_register(void *const *fields, int nfields)
         }
         return DLESM_OK;
     }
-    if (!c.comm_ready || !c.have_comms) {
-        set_error(DLESM_ERR_STATE, "peer_register: needs dlesm_comm_init and dlesm_dev_set_comms first");
+    if (!c.comm_ready || !ct.valid) {
+        set_error(DLESM_ERR_STATE, "peer_register: needs dlesm_comm_init and the comm tables (dlesm_dev_set_comms) first");
         return DLESM_ERR_STATE;
     }
     // my entries: the fields, then the flag array
@@ -949,9 +1060,8 @@ extern "C" int dlesm_dev_peer_register(void *const *fields, int nfields)
     NC(ncclAllGather(dsend, drecv, blob, ncclChar, c.comm, c.stream));
     CU(cudaMemcpyAsync(all.data(), drecv, blob * nranks, cudaMemcpyDeviceToHost, c.stream));
     CU(cudaStreamSynchronize(c.stream));
-    // neighbours = peers of the exchange plan
     std::vector<char> is_nb(nranks, 0);
-    for (const auto &g : c.groups) is_nb[g.peer0] = 1;
+    neighbours_of(ct, is_nb);
     for (int q = 0; q < nfields; ++q) {
         Context::PeerView pv;
         pv.by_rank.assign(nranks, nullptr);
@@ -964,22 +1074,63 @@ extern "C" int dlesm_dev_peer_register(void *const *fields, int nfields)
         for (int q = 0; q < nfields; ++q) {
             void *p = fields[q];
             if (r != me0) {
-                rc = open_entry(er[q], &p, false);
+                std::string key;
+                rc = open_entry(er[q], &p, key);
                 if (rc != DLESM_OK) return rc;
+                c.peers[fields[q]].handles.push_back(key);
             }
             c.peers[fields[q]].by_rank[r] = static_cast<double *>(p);
             c.peers[fields[q]].pitch_by_rank[r] = er[q].pitch;
         }
         if (r != me0 && !c.peer_flags[r]) {
-            void *p = nullptr;
-            rc = open_entry(er[nfields], &p, true);
-            if (rc != DLESM_OK) return rc;
-            c.peer_flags[r] = static_cast<unsigned long long *>(p);
+            // the flag arrays live as long as the library: mapped once, closed at finalise
+            void *base = nullptr;
+            CU(cudaIpcOpenMemHandle(&base, er[nfields].handle, cudaIpcMemLazyEnablePeerAccess));
+            c.flag_mappings.push_back(base);
+            c.peer_flags[r] = reinterpret_cast<unsigned long long *>(static_cast<char *>(base) + er[nfields].offset);
         }
     }
-    // nobody pushes before everybody has mapped: a one-double allreduce is the barrier
-    double one = 1.0;
-    return dlesm_global_sum(&one);
+    // nobody pushes before everybody has mapped
+    return barrier_all();
+}
+
+int peer_unregister_fields(void *const *fields, int nfields)
+{
+    Context &c = ctx();
+    if (c.device_ready) CU(cudaStreamSynchronize(c.stream));
+    for (int q = 0; q < nfields; ++q) {
+        auto it = c.peers.find(fields[q]);
+        if (it == c.peers.end()) continue;
+        for (const auto &key : it->second.handles) release_handle(key);
+        c.peers.erase(it);
+    }
+    return barrier_all();
+}
+}  // namespace
+
+// Collective.  Drops the registration of these fields: the neighbours' mappings they hold are
+// released (closed when no other registered field uses the same allocation), then a barrier, after
+// which each rank may free its own fields (CUDA requires importers to close before the exporter frees).
+extern "C" int dlesm_dev_peer_unregister(void *const *fields, int nfields)
+{
+    clear_error();
+    return peer_unregister_fields(fields, nfields);
+}
+
+// Collective.  Drops every registration made so far.
+extern "C" int dlesm_dev_peer_unregister_all(void)
+{
+    clear_error();
+    Context &c = ctx();
+    std::vector<void *> all;
+    for (const auto &kv : c.peers) all.push_back(const_cast<void *>(kv.first));
+    return peer_unregister_fields(all.data(), static_cast<int>(all.size()));
+}
+
+extern "C" int dlesm_dev_peer_register(void *const *fields, int nfields)
+{
+    clear_error();
+    return peer_register_with(fields, nfields, ctx().installed);
 }
 
 extern "C" int dlesm_dev_grid_upload(int nx, int ny, const int *tmask, const double *const metrics[16],
@@ -1033,6 +1184,7 @@ int check_box(int pitch, int ny, int xs, int xe, int ys, int ye)
     int rc = pitch_of(outptr, pitch, ny_);                       \
     if (rc == DLESM_OK) rc = check_box(pitch, ny_, xs, xe, ys, ye); \
     if (rc != DLESM_OK) return rc;                               \
+    mark_written(outptr);                                        \
     const k::Box b{xs, xe, ys, ye};                              \
     cudaStream_t st = ctx().stream;
 }  // namespace
@@ -1114,10 +1266,115 @@ extern "C" int dlesm_time_smooth(const void *f, const void *fnew, void *fold, do
     return DLESM_OK;
 }
 
-extern "C" int dlesm_sw_step_fused(const void *u, const void *v, const void *p, void *uold, void *vold, void *pold,
-                                   void *unew, void *vnew, void *pnew, double dx, double dy, double tdt,
-                                   double alpha, int first, int xs, int xe, int ys, int ye, const void *tm,
-                                   int variant)
+namespace {
+// byte image of an int32 tmask, built on first use and cached by the mask's device pointer
+// (grid%tmask is immutable after grid_init); freed by release_mask8 / at finalise
+int mask8_of(const void *tmask, int pitch, int ny, const unsigned char *&m8, int &pitch8)
+{
+    Context &c = ctx();
+    auto it = c.mask8.find(tmask);
+    if (it == c.mask8.end()) {
+        Context::Mask8 m;
+        m.pitch = (pitch + 15) & ~15;
+        CU(cudaMalloc(&m.p, static_cast<size_t>(m.pitch) * ny));
+        CU(k::mask_to_bytes(static_cast<const int *>(tmask), pitch, ny, m.p, m.pitch, c.stream));
+        it = c.mask8.emplace(tmask, m).first;
+    }
+    m8 = it->second.p;
+    pitch8 = it->second.pitch;
+    return DLESM_OK;
+}
+void release_mask8(const void *tmask)
+{
+    Context &c = ctx();
+    auto it = c.mask8.find(tmask);
+    if (it == c.mask8.end()) return;
+    if (c.device_ready) cudaStreamSynchronize(c.stream);
+    cudaFree(it->second.p);
+    c.mask8.erase(it);
+}
+
+struct ProfScope {
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+};
+int prof_begin(ProfScope &ps, cudaStream_t st)
+{
+    Context &c = ctx();
+    if (!c.profile) return DLESM_OK;
+    if (c.prof_used == c.prof_events.size()) {
+        cudaEvent_t x, y;
+        CU(cudaEventCreate(&x));
+        CU(cudaEventCreate(&y));
+        c.prof_events.emplace_back(x, y);
+    }
+    ps.e0 = c.prof_events[c.prof_used].first;
+    ps.e1 = c.prof_events[c.prof_used].second;
+    ++c.prof_used;
+    CU(cudaEventRecord(ps.e0, st));
+    return DLESM_OK;
+}
+int prof_end(const ProfScope &ps, cudaStream_t st)
+{
+    if (ps.e1) CU(cudaEventRecord(ps.e1, st));
+    return DLESM_OK;
+}
+
+// push boxes: one per send-list entry of `ct` (src/parallel_comms_mod.f90:70-83), aimed at the
+// destination rank's counterparts of the `nout` output arrays
+template <class Seg, int NOUT>
+int make_push(const CommTables &ct, const void *const outs[NOUT], Seg *segs, int &nseg, k::PeerFlags &pf, const char *who)
+{
+    Context &c = ctx();
+    if (!ct.valid) {
+        set_error(DLESM_ERR_STATE, std::string(who) + ": halo push needs the comm tables (dlesm_dev_set_comms)");
+        return DLESM_ERR_STATE;
+    }
+    const Context::PeerView *pv[NOUT];
+    for (int q = 0; q < NOUT; ++q) {
+        auto it = c.peers.find(outs[q]);
+        if (it == c.peers.end()) {
+            set_error(DLESM_ERR_STATE, std::string(who) + ": halo push needs the output fields registered (dlesm_dev_peer_register)");
+            return DLESM_ERR_STATE;
+        }
+        pv[q] = &it->second;
+    }
+    const dlesm_comms &t = ct.t;
+    const int me0 = pstate().rank - 1;
+    const bool single = pstate().nranks == 1;
+    bool seen[64] = {false};
+    nseg = 0;
+    for (int sidx = 0; sidx < t.nsend; ++sidx) {
+        const int dest = single ? 0 : t.destination[sidx];
+        Seg &g = segs[nseg++];
+        g.i0 = t.isrcsend[sidx]; g.i1 = g.i0 + t.nxsend[sidx] - 1;
+        g.j0 = t.jsrcsend[sidx]; g.j1 = g.j0 + t.nysend[sidx] - 1;
+        g.ides = t.idessend[sidx]; g.jdes = t.jdessend[sidx];
+        if (dest < 0 || dest >= static_cast<int>(pv[0]->by_rank.size())) {
+            set_error(DLESM_ERR_STATE, std::string(who) + ": send list names a rank outside the communicator");
+            return DLESM_ERR_STATE;
+        }
+        g.dpitch = pv[0]->pitch_by_rank[dest];
+        for (int q = 0; q < NOUT; ++q) {
+            g.dst[q] = pv[q]->by_rank[dest];
+            if (!g.dst[q]) {
+                set_error(DLESM_ERR_STATE, std::string(who) + ": a neighbour's field is not mapped");
+                return DLESM_ERR_STATE;
+            }
+        }
+        if (dest != me0 && !seen[dest]) {
+            seen[dest] = true;
+            pf.remote[pf.n] = c.peer_flags[dest] + me0;
+            pf.local[pf.n] = c.flags + dest;
+            ++pf.n;
+        }
+    }
+    return DLESM_OK;
+}
+
+// The fused step.  `push_tables` non-null: halo push along that send list.
+int sw_step_fused_impl(const void *u, const void *v, const void *p, void *uold, void *vold, void *pold, void *unew,
+                       void *vnew, void *pnew, double dx, double dy, double tdt, double alpha, int first, int xs,
+                       int xe, int ys, int ye, const void *tm, int variant, const CommTables *push_tables)
 {
     SWEEP_PROLOGUE(unew)
     (void)b;
@@ -1131,89 +1388,50 @@ extern "C" int dlesm_sw_step_fused(const void *u, const void *v, const void *p, 
             return DLESM_ERR_ARGS;
         }
     }
+    Context &c = ctx();
     k::FusedArgs a;
     a.u = CD(u); a.v = CD(v); a.p = CD(p);
     a.uold = D(uold); a.vold = D(vold); a.pold = D(pold);
     a.unew = D(unew); a.vnew = D(vnew); a.pnew = D(pnew);
     a.tmask = static_cast<const int *>(tm);
+    a.mask8 = nullptr; a.mask8_pitch = 0;
     a.pitch = pitch; a.ny = ny_;
     a.b = k::Box{xs, xe, ys, ye};
-    a.sc.fsdx = 4.0 / dx; a.sc.fsdy = 4.0 / dy;
-    a.sc.tdts8 = tdt / 8.0; a.sc.tdtsdx = tdt / dx; a.sc.tdtsdy = tdt / dy;
-    a.sc.alpha = alpha; a.sc.first = first;
+    a.sc = k::make_scalars(dx, dy, tdt, alpha, first);
+    a.tiles = c.sweep_tiles;
     a.push.n = 0;
-    Context &c = ctx();
-    const bool push = (variant & DLESM_FUSED_PUSH) != 0;
-    variant &= ~DLESM_FUSED_PUSH;
+    if (tm && variant != 1 && pitch % 2 == 0) {
+        rc = mask8_of(tm, pitch, ny_, a.mask8, a.mask8_pitch);
+        if (rc != DLESM_OK) return rc;
+    }
+    const bool fma = c.arith == DLESM_ARITH_CONTRACTED;
     k::PeerFlags pf{};
-    if (push) {
-        // one push box per send-list entry (src/parallel_comms_mod.f90:70-83), aimed at the
-        // destination rank's counterparts of unew, vnew, pnew
-        if (!c.have_comms) {
-            set_error(DLESM_ERR_STATE, "sw_step_fused: halo push needs the comm tables (dlesm_dev_set_comms)");
-            return DLESM_ERR_STATE;
-        }
-        if (!k::fused_push_supported(a, variant)) {
-            set_error(DLESM_ERR_ARGS, "sw_step_fused: halo push needs a TMA variant (even pitch; pitch % 4 == 0 with a mask)");
+    if (push_tables) {
+        const bool ok = fma ? k::fma_on::fused_push_supported(a, variant) : k::fma_off::fused_push_supported(a, variant);
+        if (!ok) {
+            set_error(DLESM_ERR_ARGS, "sw_step_fused: halo push needs a TMA variant (even pitch)");
             return DLESM_ERR_ARGS;
         }
         const void *outs[3] = {unew, vnew, pnew};
-        const Context::PeerView *pv[3];
-        for (int q = 0; q < 3; ++q) {
-            auto it = c.peers.find(outs[q]);
-            if (it == c.peers.end()) {
-                set_error(DLESM_ERR_STATE, "sw_step_fused: halo push needs unew, vnew, pnew registered (dlesm_dev_peer_register)");
-                return DLESM_ERR_STATE;
-            }
-            pv[q] = &it->second;
-        }
-        const dlesm_comms &t = c.comms;
-        const int me0 = pstate().rank - 1;
-        const bool single = pstate().nranks == 1;
-        bool seen[64] = {false};
-        for (int sidx = 0; sidx < t.nsend; ++sidx) {
-            const int dest = single ? 0 : t.destination[sidx];
-            k::PushSeg &g = a.push.seg[a.push.n++];
-            g.i0 = t.isrcsend[sidx]; g.i1 = g.i0 + t.nxsend[sidx] - 1;
-            g.j0 = t.jsrcsend[sidx]; g.j1 = g.j0 + t.nysend[sidx] - 1;
-            g.ides = t.idessend[sidx]; g.jdes = t.jdessend[sidx];
-            g.dpitch = pv[0]->pitch_by_rank[dest];
-            for (int q = 0; q < 3; ++q) {
-                g.dst[q] = pv[q]->by_rank[dest];
-                if (!g.dst[q]) {
-                    set_error(DLESM_ERR_STATE, "sw_step_fused: a neighbour's field is not mapped");
-                    return DLESM_ERR_STATE;
-                }
-            }
-            if (dest != me0 && !seen[dest]) {
-                seen[dest] = true;
-                pf.remote[pf.n] = c.peer_flags[dest] + me0;
-                pf.local[pf.n] = c.flags + dest;
-                ++pf.n;
-            }
-        }
+        rc = make_push<k::PushSeg, 3>(*push_tables, outs, a.push.seg, a.push.n, pf, "sw_step_fused");
+        if (rc != DLESM_OK) return rc;
     }
-    cudaEvent_t e0 = nullptr, e1 = nullptr;
-    if (c.profile) {
-        if (c.prof_used == c.prof_events.size()) {
-            cudaEvent_t x, y;
-            CU(cudaEventCreate(&x));
-            CU(cudaEventCreate(&y));
-            c.prof_events.emplace_back(x, y);
-        }
-        e0 = c.prof_events[c.prof_used].first;
-        e1 = c.prof_events[c.prof_used].second;
-        ++c.prof_used;
-        CU(cudaEventRecord(e0, st));
-    }
-    cudaError_t e = k::sw_step_fused(a, variant, st);
-    if (e == cudaErrorNotSupported) {
+    ProfScope ps;
+    rc = prof_begin(ps, st);
+    if (rc != DLESM_OK) return rc;
+    cudaError_t e = fma ? k::fma_on::sw_step_fused(a, variant, st) : k::fma_off::sw_step_fused(a, variant, st);
+    if (e == cudaErrorNotSupported || e == cudaErrorInvalidValue) {
         set_error(DLESM_ERR_ARGS, "sw_step_fused: variant not available for this pitch / mask (see DESIGN.md)");
         return DLESM_ERR_ARGS;
     }
     if (e != cudaSuccess) return fail_cuda(e, "sw_step_fused");
-    if (c.profile) CU(cudaEventRecord(e1, st));
-    if (push && pf.n > 0) {
+    rc = prof_end(ps, st);
+    if (rc != DLESM_OK) return rc;
+    // the six arrays were written; with a push the halos of the new fields are filled as well
+    const int depth_new = push_tables ? 1 : 0;
+    mark_clean(unew, depth_new); mark_clean(vnew, depth_new); mark_clean(pnew, depth_new);
+    if (!first) { mark_written(uold); mark_written(vold); mark_written(pold); }
+    if (push_tables && pf.n > 0) {
         // neighbours must not start their next sweep before these pushes landed, nor push into
         // a buffer this rank is still reading: publish the epoch, wait for theirs
         ++c.push_epoch;
@@ -1222,10 +1440,10 @@ extern "C" int dlesm_sw_step_fused(const void *u, const void *v, const void *p, 
     return DLESM_OK;
 }
 
-extern "C" int dlesm_sw_step2_fused(const void *u, const void *v, const void *p, const void *uold, const void *vold,
-                                    const void *pold, void *u2, void *v2, void *p2, void *uold2, void *vold2,
-                                    void *pold2, double dx, double dy, double tdt, double alpha, int xs, int xe,
-                                    int ys, int ye, const void *tm, int variant)
+int sw_step2_fused_impl(const void *u, const void *v, const void *p, const void *uold, const void *vold,
+                        const void *pold, void *u2, void *v2, void *p2, void *uold2, void *vold2, void *pold2,
+                        double dx, double dy, double tdt, double alpha, int xs, int xe, int ys, int ye,
+                        const unsigned char *mask8, int mask8_pitch, int variant, const CommTables *push_tables)
 {
     SWEEP_PROLOGUE(u2)
     (void)b;
@@ -1240,103 +1458,110 @@ extern "C" int dlesm_sw_step2_fused(const void *u, const void *v, const void *p,
         }
     }
     const void *ins[] = {u, v, p, uold, vold, pold};
-    const void *outs[] = {u2, v2, p2, uold2, vold2, pold2};
+    const void *outs[6] = {u2, v2, p2, uold2, vold2, pold2};
     for (const void *a : ins)
         for (const void *o : outs)
             if (a == o) {
                 set_error(DLESM_ERR_ARGS, "sw_step2_fused: outputs must not alias inputs (neighbouring blocks re-read the ring)");
                 return DLESM_ERR_ARGS;
             }
+    Context &c = ctx();
     k::Fused2Args a;
     a.u = CD(u); a.v = CD(v); a.p = CD(p);
     a.uold = CD(uold); a.vold = CD(vold); a.pold = CD(pold);
     a.u2 = D(u2); a.v2 = D(v2); a.p2 = D(p2);
-    a.tmask = static_cast<const int *>(tm);
+    a.mask8 = mask8; a.mask8_pitch = mask8_pitch;
     a.uold2 = D(uold2); a.vold2 = D(vold2); a.pold2 = D(pold2);
     a.pitch = pitch; a.ny = ny_;
     a.b = k::Box{xs, xe, ys, ye};
-    a.sc.fsdx = 4.0 / dx; a.sc.fsdy = 4.0 / dy;
-    a.sc.tdts8 = tdt / 8.0; a.sc.tdtsdx = tdt / dx; a.sc.tdtsdy = tdt / dy;
-    a.sc.alpha = alpha; a.sc.first = 0;
-    if (!k::fused2_supported(a)) {
-        set_error(DLESM_ERR_ARGS, "sw_step2_fused: needs an even pitch (a multiple of 4 with a mask) and a box with two halo cells on every side (halo_width >= 2)");
+    a.sc = k::make_scalars(dx, dy, tdt, alpha, 0);
+    a.tiles = c.sweep_tiles;
+    const bool fma = c.arith == DLESM_ARITH_CONTRACTED;
+    if (!(fma ? k::fma_on::fused2_supported(a) : k::fma_off::fused2_supported(a))) {
+        set_error(DLESM_ERR_ARGS, "sw_step2_fused: needs an even pitch and a box with two halo cells on every side (halo_width >= 2)");
         return DLESM_ERR_ARGS;
     }
     a.push.n = 0;
-    Context &c = ctx();
-    const bool push = (variant & DLESM_FUSED_PUSH) != 0;
-    variant &= ~DLESM_FUSED_PUSH;
     k::PeerFlags pf{};
-    if (push) {
-        // one push box per send-list entry of the installed tables (which must be the depth-2
-        // ones), aimed at the destination rank's counterparts of the six outputs
-        if (!c.have_comms) {
-            set_error(DLESM_ERR_STATE, "sw_step2_fused: halo push needs the depth-2 comm tables (dlesm_dev_set_comms)");
-            return DLESM_ERR_STATE;
-        }
-        if (!k::fused2_push_supported(variant)) {
+    if (push_tables) {
+        // the tables must be the depth-2 ones
+        if (!k::fma_off::fused2_push_supported(variant)) {
             set_error(DLESM_ERR_ARGS, "sw_step2_fused: halo push needs the shuffle form of the sweep (variant 0 or 10..19)");
             return DLESM_ERR_ARGS;
         }
-        const Context::PeerView *pv[6];
-        for (int q = 0; q < 6; ++q) {
-            auto it = c.peers.find(outs[q]);
-            if (it == c.peers.end()) {
-                set_error(DLESM_ERR_STATE, "sw_step2_fused: halo push needs the six outputs registered (dlesm_dev_peer_register)");
-                return DLESM_ERR_STATE;
-            }
-            pv[q] = &it->second;
-        }
-        const dlesm_comms &t = c.comms;
-        const int me0 = pstate().rank - 1;
-        const bool single = pstate().nranks == 1;
-        bool seen[64] = {false};
-        for (int sidx = 0; sidx < t.nsend; ++sidx) {
-            const int dest = single ? 0 : t.destination[sidx];
-            k::PushSeg2 &g = a.push.seg[a.push.n++];
-            g.i0 = t.isrcsend[sidx]; g.i1 = g.i0 + t.nxsend[sidx] - 1;
-            g.j0 = t.jsrcsend[sidx]; g.j1 = g.j0 + t.nysend[sidx] - 1;
-            g.ides = t.idessend[sidx]; g.jdes = t.jdessend[sidx];
-            g.dpitch = pv[0]->pitch_by_rank[dest];
-            for (int q = 0; q < 6; ++q) {
-                g.dst[q] = pv[q]->by_rank[dest];
-                if (!g.dst[q]) {
-                    set_error(DLESM_ERR_STATE, "sw_step2_fused: a neighbour's field is not mapped");
-                    return DLESM_ERR_STATE;
-                }
-            }
-            if (dest != me0 && !seen[dest]) {
-                seen[dest] = true;
-                pf.remote[pf.n] = c.peer_flags[dest] + me0;
-                pf.local[pf.n] = c.flags + dest;
-                ++pf.n;
-            }
-        }
+        rc = make_push<k::PushSeg2, 6>(*push_tables, outs, a.push.seg, a.push.n, pf, "sw_step2_fused");
+        if (rc != DLESM_OK) return rc;
     }
-    cudaEvent_t e0 = nullptr, e1 = nullptr;
-    if (c.profile) {
-        if (c.prof_used == c.prof_events.size()) {
-            cudaEvent_t x, y;
-            CU(cudaEventCreate(&x));
-            CU(cudaEventCreate(&y));
-            c.prof_events.emplace_back(x, y);
-        }
-        e0 = c.prof_events[c.prof_used].first;
-        e1 = c.prof_events[c.prof_used].second;
-        ++c.prof_used;
-        CU(cudaEventRecord(e0, st));
-    }
-    cudaError_t e = k::sw_step2_fused(a, variant, st);
+    ProfScope ps;
+    rc = prof_begin(ps, st);
+    if (rc != DLESM_OK) return rc;
+    cudaError_t e = fma ? k::fma_on::sw_step2_fused(a, variant, st) : k::fma_off::sw_step2_fused(a, variant, st);
     if (e == cudaErrorNotSupported || e == cudaErrorInvalidValue) {
         set_error(DLESM_ERR_ARGS, "sw_step2_fused: variant not available (see DESIGN.md)");
         return DLESM_ERR_ARGS;
     }
     if (e != cudaSuccess) return fail_cuda(e, "sw_step2_fused");
-    if (c.profile) CU(cudaEventRecord(e1, st));
-    if (push && pf.n > 0) {
+    rc = prof_end(ps, st);
+    if (rc != DLESM_OK) return rc;
+    for (const void *o : outs) mark_clean(o, push_tables ? 2 : 0);
+    if (push_tables && pf.n > 0) {
         ++c.push_epoch;
         CU(k::peer_signal_wait(pf, c.push_epoch, c.push_err, st));
     }
+    return DLESM_OK;
+}
+}  // namespace
+
+extern "C" int dlesm_sw_step_fused(const void *u, const void *v, const void *p, void *uold, void *vold, void *pold,
+                                   void *unew, void *vnew, void *pnew, double dx, double dy, double tdt,
+                                   double alpha, int first, int xs, int xe, int ys, int ye, const void *tm,
+                                   int variant)
+{
+    clear_error();
+    const bool push = (variant & DLESM_FUSED_PUSH) != 0;
+    return sw_step_fused_impl(u, v, p, uold, vold, pold, unew, vnew, pnew, dx, dy, tdt, alpha, first, xs, xe, ys, ye,
+                              tm, variant & ~DLESM_FUSED_PUSH, push ? &ctx().installed : nullptr);
+}
+
+extern "C" int dlesm_sw_step2_fused(const void *u, const void *v, const void *p, const void *uold, const void *vold,
+                                    const void *pold, void *u2, void *v2, void *p2, void *uold2, void *vold2,
+                                    void *pold2, double dx, double dy, double tdt, double alpha, int xs, int xe,
+                                    int ys, int ye, const void *tm, int variant)
+{
+    clear_error();
+    const bool push = (variant & DLESM_FUSED_PUSH) != 0;
+    const unsigned char *m8 = nullptr;
+    int p8 = 0;
+    if (tm) {
+        int pitch, ny_;
+        int rc = pitch_of(u2, pitch, ny_);
+        if (rc == DLESM_OK) rc = mask8_of(tm, pitch, ny_, m8, p8);
+        if (rc != DLESM_OK) return rc;
+    }
+    return sw_step2_fused_impl(u, v, p, uold, vold, pold, u2, v2, p2, uold2, vold2, pold2, dx, dy, tdt, alpha, xs, xe,
+                               ys, ye, m8, p8, variant & ~DLESM_FUSED_PUSH, push ? &ctx().installed : nullptr);
+}
+
+extern "C" int dlesm_set_arith(int mode)
+{
+    clear_error();
+    if (mode != DLESM_ARITH_EXACT && mode != DLESM_ARITH_CONTRACTED) {
+        set_error(DLESM_ERR_ARGS, "dlesm_set_arith: DLESM_ARITH_EXACT or DLESM_ARITH_CONTRACTED");
+        return DLESM_ERR_ARGS;
+    }
+    ctx().arith = mode;
+    return DLESM_OK;
+}
+extern "C" int dlesm_get_arith(void) { return ctx().arith; }
+
+extern "C" int dlesm_dev_set_sweep_tiles(int ntilex, int ntiley)
+{
+    clear_error();
+    if (ntilex < 0 || ntiley < 0) {
+        set_error(DLESM_ERR_ARGS, "dlesm_dev_set_sweep_tiles: tile counts must be >= 0 (0 = library default)");
+        return DLESM_ERR_ARGS;
+    }
+    ctx().sweep_tiles = k::SweepTiles{ntilex, ntiley};
     return DLESM_OK;
 }
 
@@ -1470,6 +1695,8 @@ extern "C" int dlesm_grid_init(dlesm_grid_t *g, double dxarg, double dyarg, cons
         g->have_comms = true;
         rc = dlesm_dev_set_comms(&g->comms);  // module-level state, as in parallel_comms_mod
         if (rc != DLESM_OK) return rc;
+    } else {
+        dlesm_dev_set_comms(nullptr);         // one rank: map_comms finds no neighbour (stub build)
     }
     g->info.initialised = 1;
     return DLESM_OK;
@@ -1594,7 +1821,10 @@ extern "C" int dlesm_grid_device_array(dlesm_grid_t *g, int which, void **device
 extern "C" void dlesm_grid_free(dlesm_grid_t *g)
 {
     if (!g) return;
-    if (g->dev[0]) cudaFree(g->dev[0]);
+    if (g->dev[0]) {
+        release_mask8(g->dev[0]);
+        cudaFree(g->dev[0]);
+    }
     for (int q = 1; q < 17; ++q)
         if (g->dev[q]) dlesm_dev_field_free(g->dev[q]);
     delete g;
@@ -1608,8 +1838,85 @@ struct dlesm_field {
     FieldBounds fb;
     int nx = 0, ny = 0;
     int ntiles = 0;
+    std::vector<dlesm_region> tile_internal, tile_whole;   // tile(:)%internal / %whole (src/tile_mod.f90:36-42)
     void *dptr = nullptr;
 };
+
+namespace {
+// get_grid_dims (src/field_mod.f90:1473-1503): GOCEAN_OMP_GRID = "AxB"
+bool get_grid_dims(int &nx, int &ny)
+{
+    const char *e = std::getenv("GOCEAN_OMP_GRID");
+    if (!e) return false;
+    const char *x = std::strchr(e, 'x');
+    if (!x) {
+        std::fprintf(stderr, "\ndlesm get_grid_dims: failed to parse GOCEAN_OMP_GRID string: %s\n"
+                             "   -  will use defaults for dimensions of tiling grid\n", e);
+        return false;
+    }
+    char *end = nullptr;
+    const long a = std::strtol(e, &end, 10);
+    if (end == e || end != x || a < 1) return false;
+    const long b = std::strtol(x + 1, &end, 10);
+    if (end == x + 1 || b < 1) return false;
+    nx = static_cast<int>(a);
+    ny = static_cast<int>(b);
+    return true;
+}
+
+// do_tile (src/field_mod.f90:300-325).  The reference cuts the field's internal region into one tile
+// per OpenMP thread with go_decompose and keeps that decomposition for every later field (SAVEd
+// `decomp`, `tiling_initialised`).  Here a tile is the unit of work of one CTA column-strip march:
+// GOCEAN_OMP_GRID="AxB" gives the tile grid (A x-tiles, each cut into strips of the sweep's width; B
+// tiles = segments along j); without it the library's own choice stands (one x-tile, the segment
+// count the fused sweep picks for whole waves of CTAs).  The first tiled field installs the grid for
+// every sweep (module-level state, like the reference's), dlesm_dev_set_sweep_tiles overrides.
+int setup_tiles(dlesm_field *f)
+{
+    Context &c = ctx();
+    const dlesm_region &in = f->fb.internal;
+    if (!c.tiling_initialised) {
+        int a = 1, b = 0;
+        if (get_grid_dims(a, b)) c.sweep_tiles = k::SweepTiles{a, b};
+        c.tiling_initialised = true;
+    }
+    int ntx = c.sweep_tiles.nx > 0 ? c.sweep_tiles.nx : 1, nty = c.sweep_tiles.ny;
+    if (nty <= 0) {
+        // the default segment count of the one-step fused sweep over this box
+        k::FusedArgs a{};
+        a.pitch = f->nx - (f->nx % 2); a.ny = f->ny;   // geometry only
+        a.b = box_of(in);
+        a.tiles = k::SweepTiles{0, 0};
+        int grid[2] = {1, 1};
+        k::fma_off::fused_grid(a, 25, grid);
+        nty = grid[1] > 0 ? grid[1] : 1;
+    }
+    ntx = std::min(ntx, std::max(in.nx, 1));
+    nty = std::min(nty, std::max(in.ny, 1));
+    // tile boxes by go_decompose's remainder rule (src/parallel_mod.f90:211-223), in the field's
+    // own index space: internal = the tile's points, whole = one cell more on every side
+    f->ntiles = ntx * nty;
+    f->tile_internal.resize(f->ntiles);
+    f->tile_whole.resize(f->ntiles);
+    const int tw = in.nx / ntx, xr = in.nx % ntx, th = in.ny / nty, yr = in.ny % nty;
+    for (int b = 0; b < nty; ++b)
+        for (int a = 0; a < ntx; ++a) {
+            dlesm_region r;
+            r.xstart = in.xstart + a * tw + std::min(a, xr);
+            r.nx = tw + (a < xr ? 1 : 0);
+            r.xstop = r.xstart + r.nx - 1;
+            r.ystart = in.ystart + b * th + std::min(b, yr);
+            r.ny = th + (b < yr ? 1 : 0);
+            r.ystop = r.ystart + r.ny - 1;
+            f->tile_internal[b * ntx + a] = r;
+            dlesm_region w = r;
+            w.xstart -= 1; w.xstop += 1; w.ystart -= 1; w.ystop += 1;
+            w.nx += 2; w.ny += 2;
+            f->tile_whole[b * ntx + a] = w;
+        }
+    return DLESM_OK;
+}
+}  // namespace
 
 extern "C" dlesm_field_t *dlesm_r2d_field_create(dlesm_grid_t *g, int grid_points, int do_tile,
                                                  const double *init_global_data, int gnx, int gny)
@@ -1628,10 +1935,8 @@ extern "C" dlesm_field_t *dlesm_r2d_field_create(dlesm_grid_t *g, int grid_point
         delete f;
         return nullptr;
     }
-    // do_tile: OpenMP thread tiling of the host loops (src/field_mod.f90:300-325); the CUDA
-    // grid takes its place, so the request is accepted and ntiles stays 0
-    (void)do_tile;
-    f->ntiles = 0;
+    f->ntiles = 0;   // "We're not tiling this field so set ntiles to zero" (src/field_mod.f90:324)
+    if (do_tile && f->fb.internal.nx > 0 && f->fb.internal.ny > 0) setup_tiles(f);
     if (dlesm_dev_field_alloc(f->nx, f->ny, &f->dptr) != DLESM_OK) {
         delete f;
         return nullptr;
@@ -1678,6 +1983,38 @@ extern "C" int dlesm_field_get_info(const dlesm_field_t *f, dlesm_field_info *ou
     out->ntiles = f->ntiles;
     out->data_on_device = 1;
     out->device_ptr = f->dptr;
+    // halo_type%needs_update (src/halo_mod.f90:10-12) from the array's dirty flag
+    FieldRec r;
+    const bool dirty = lookup(f->dptr, r) != DLESM_OK || r.clean_depth < 1;
+    for (int q = 0; q < 4; ++q) out->halo[q].needs_update = dirty ? 1 : 0;
+    clear_error();
+    return DLESM_OK;
+}
+
+extern "C" int dlesm_field_tile(const dlesm_field_t *f, int itile1, dlesm_region *internal, dlesm_region *whole)
+{
+    clear_error();
+    if (!f || itile1 < 1 || itile1 > f->ntiles) {
+        set_error(DLESM_ERR_ARGS, "field tile index out of range (1..ntiles)");
+        return DLESM_ERR_ARGS;
+    }
+    if (internal) *internal = f->tile_internal[itile1 - 1];
+    if (whole) *whole = f->tile_whole[itile1 - 1];
+    return DLESM_OK;
+}
+
+extern "C" int dlesm_field_halo_is_dirty(const dlesm_field_t *f, int depth)
+{
+    FieldRec r;
+    if (!f || lookup(f->dptr, r) != DLESM_OK) {
+        clear_error();
+        return 1;
+    }
+    return r.clean_depth < (depth < 1 ? 1 : depth) ? 1 : 0;
+}
+extern "C" int dlesm_field_set_halo_dirty(dlesm_field_t *f)
+{
+    if (f) mark_written(f->dptr);
     return DLESM_OK;
 }
 
@@ -1741,13 +2078,14 @@ extern "C" int dlesm_fields_halo_exchange(dlesm_field_t *const *f, int nfields, 
     // depth, up to the halo width the grid was decomposed with.
     dlesm_grid *g = f[0]->grid;
     if (depth > 1 && (pstate().extensions & DLESM_EXT_HALO_DEPTH) && g->have_comms) {
+        // tables of that depth, used for this call only: the module-level (depth-1) state stays put
         dlesm_comms deep;
         int rc = build_comms(g->decomp, pstate().rank, pstate().nranks, g->pbc_x, g->pbc_y, depth, depth, deep);
         if (rc != DLESM_OK) return rc;
-        rc = dlesm_dev_set_comms(&deep);
-        if (rc == DLESM_OK) rc = dlesm_dev_halo_exchange(ptrs, nfields);
-        const int rc2 = dlesm_dev_set_comms(&g->comms);   // module-level state back to depth 1
-        return rc != DLESM_OK ? rc : rc2;
+        CommTables ct;
+        rc = build_tables(&deep, depth, ct);
+        if (rc != DLESM_OK) return rc;
+        return exchange_with(ptrs, nfields, ct);
     }
     return dlesm_dev_halo_exchange(ptrs, nfields);
 }
@@ -1763,8 +2101,10 @@ extern "C" int dlesm_field_apply_periodic_halos(dlesm_field_t *f)
     if (f->fb.num_halos <= 0) return DLESM_OK;
     const int *bcs = f->grid->info.boundary_conditions;
     double *fl[1] = {static_cast<double *>(f->dptr)};
-    CU(k::periodic_halos(fl, 1, f->nx, box_of(f->fb.internal), bcs[0] == DLESM_GO_BC_PERIODIC,
-                         bcs[1] == DLESM_GO_BC_PERIODIC, ctx().stream));
+    const bool px = bcs[0] == DLESM_GO_BC_PERIODIC, py = bcs[1] == DLESM_GO_BC_PERIODIC;
+    if ((pstate().extensions & DLESM_EXT_DIRTY_HALOS) && dlesm_field_halo_is_dirty(f, 1) == 0) return DLESM_OK;
+    CU(k::periodic_halos(fl, 1, f->nx, box_of(f->fb.internal), px, py, ctx().stream));
+    mark_clean(f->dptr, 1);   // every halo in the field's list (the periodic directions) is filled
     return DLESM_OK;
 }
 
@@ -1866,14 +2206,19 @@ struct dlesm_sw {
     const int *tmask_dev = nullptr;
     bool periodic_local = true;  // halos by local copies (1 rank) or by exchange (several)
     bool push = false;           // halos stored by the fused sweep itself (DLESM_HALO_PUSH)
-    bool registered = false;     // buffers are mapped by the neighbours (dlesm_dev_peer_register)
+    // halo push state of THIS object: the send list the sweeps push along (depth 1, or 2 with the
+    // two-step sweep) and the buffers the neighbours have mapped.  Nothing of it lives in the
+    // module-level comm state, so other fields' halo_exchange calls are unaffected.
+    CommTables push_tables;
+    std::vector<void *> registered;
     // two steps per sweep (dlesm_sw_set_two_step): second set of old fields (the two-step sweep
     // cannot filter in place), and whether u,v,p / uold,vold,pold currently hold deep halos
     bool two_step = false;
     int variant2 = 0;
     dlesm_field *old2[3] = {nullptr, nullptr, nullptr};
     bool deep_valid = false;
-    int *tmask2 = nullptr;       // the tmask with a PERIODIC ring two cells deep (two-step sweep, masked)
+    unsigned char *mask2 = nullptr;   // byte image of the tmask with a PERIODIC ring two cells deep
+    int mask2_pitch = 0;
 };
 
 extern "C" dlesm_sw_t *dlesm_sw_create(dlesm_grid_t *g, double dt, double alpha, int mode, int use_tmask)
@@ -1899,8 +2244,10 @@ extern "C" dlesm_sw_t *dlesm_sw_create(dlesm_grid_t *g, double dt, double alpha,
         DLESM_GO_T_POINTS, DLESM_GO_U_POINTS, DLESM_GO_V_POINTS, DLESM_GO_T_POINTS, DLESM_GO_U_POINTS,
         DLESM_GO_V_POINTS, DLESM_GO_F_POINTS, DLESM_GO_T_POINTS};
     const int nf = mode == DLESM_SW_FUSED ? DLESM_SW_CU : DLESM_SW_NFIELDS;  // cu,cv,z,h only un-fused
+    // an application built for tiling asks for tiled fields; here: whenever the knob is set
+    const int do_tile = std::getenv("GOCEAN_OMP_GRID") != nullptr;
     for (int q = 0; q < nf; ++q) {
-        s->f[q] = dlesm_r2d_field_create(g, pts[q], 0, nullptr, 0, 0);
+        s->f[q] = dlesm_r2d_field_create(g, pts[q], do_tile, nullptr, 0, 0);
         if (!s->f[q]) {
             dlesm_sw_free(s);
             return nullptr;
@@ -1926,16 +2273,24 @@ int sw_fill_halos(dlesm_sw *s, int first_field, int count)
         // every SW periodic field shares the T-point internal region
         CU(k::periodic_halos(fl, count, s->f[first_field]->nx, box_of(s->f[first_field]->fb.internal), true, true,
                              ctx().stream));
+        for (int q = 0; q < count; ++q) mark_clean(fl[q], 1);
         return DLESM_OK;
     }
     return dlesm_fields_halo_exchange(&s->f[first_field], count, 1);
 }
-}  // namespace
 
-namespace {
-// Halo push set-up of the model (collective): install the comm tables at the depth the sweeps
-// push (1, or 2 with the two-step sweep) and map the neighbours' counterparts of every buffer a
-// sweep stores into -- both rotating sets of u,v,p and, with the two-step sweep, of the old fields.
+// Collective.  Drops this object's registrations (the neighbours unmap its buffers and it unmaps theirs).
+int sw_release_peers(dlesm_sw *s)
+{
+    if (s->registered.empty()) return DLESM_OK;
+    int rc = peer_unregister_fields(s->registered.data(), static_cast<int>(s->registered.size()));
+    s->registered.clear();
+    return rc;
+}
+
+// Halo push set-up of the model (collective): build the send list at the depth the sweeps push
+// (1, or 2 with the two-step sweep) and map the neighbours' counterparts of every buffer a sweep
+// stores into -- both rotating sets of u,v,p and, with the two-step sweep, of the old fields.
 int sw_configure_push(dlesm_sw *s)
 {
     const int depth = s->two_step ? 2 : 1;
@@ -1946,7 +2301,7 @@ int sw_configure_push(dlesm_sw *s)
         rc = dlesm_map_comms(&g.dh, 1, 1, 1, 1, depth, depth, &t);   // wrap-around neighbours = this rank
     else
         rc = build_comms(g.decomp, pstate().rank, pstate().nranks, g.pbc_x, g.pbc_y, depth, depth, t);
-    if (rc == DLESM_OK) rc = dlesm_dev_set_comms(&t);
+    if (rc == DLESM_OK) rc = build_tables(&t, depth, s->push_tables);
     if (rc != DLESM_OK) return rc;
     void *bufs[12];
     int n = 0;
@@ -1956,10 +2311,10 @@ int sw_configure_push(dlesm_sw *s)
         for (int q = 0; q < 3; ++q) bufs[n++] = s->f[DLESM_SW_UOLD + q]->dptr;
         for (int q = 0; q < 3; ++q) bufs[n++] = s->old2[q]->dptr;
     }
-    rc = dlesm_dev_peer_unregister_all();    // the registered set is replaced (collective)
-    if (rc == DLESM_OK) rc = dlesm_dev_peer_register(bufs, n);   // collective
+    rc = sw_release_peers(s);                                   // the registered set is replaced (collective)
+    if (rc == DLESM_OK) rc = peer_register_with(bufs, n, s->push_tables);   // collective
     if (rc != DLESM_OK) return rc;
-    s->registered = true;
+    s->registered.assign(bufs, bufs + n);
     return DLESM_OK;
 }
 }  // namespace
@@ -1969,14 +2324,15 @@ extern "C" int dlesm_sw_set_halo_mode(dlesm_sw_t *s, int mode)
     clear_error();
     if (mode == DLESM_HALO_EXCHANGE) {
         s->push = false;
-        return DLESM_OK;
+        s->deep_valid = false;
+        return sw_release_peers(s);      // collective, like the call that mapped them
     }
     if (mode != DLESM_HALO_PUSH || s->mode != DLESM_SW_FUSED) {
         set_error(DLESM_ERR_ARGS, "sw_set_halo_mode: DLESM_HALO_PUSH needs the fused mode");
         return DLESM_ERR_ARGS;
     }
-    if (s->f[0]->nx % 2 != 0 || (s->tmask_dev && s->f[0]->nx % 4 != 0)) {
-        set_error(DLESM_ERR_ARGS, "sw_set_halo_mode: halo push needs a TMA-eligible pitch (DL_ESM_ALIGNMENT even; a multiple of 4 with a mask)");
+    if (s->f[0]->nx % 2 != 0) {
+        set_error(DLESM_ERR_ARGS, "sw_set_halo_mode: halo push needs a TMA-eligible pitch (DL_ESM_ALIGNMENT even)");
         return DLESM_ERR_ARGS;
     }
     s->push = true;
@@ -1994,13 +2350,13 @@ int sw_fill_deep_halos(dlesm_sw *s)
         double *dp[6];
         for (int q = 0; q < 6; ++q) dp[q] = static_cast<double *>(fl[q]->dptr);
         CU(k::periodic_halos_deep(dp, 6, fl[0]->nx, box_of(s->f[DLESM_SW_P]->fb.internal), 2, ctx().stream));
+        for (int q = 0; q < 6; ++q) mark_clean(dp[q], 2);
         return DLESM_OK;
     }
-    if (s->push) {
-        // the installed tables are already the depth-2 ones (sw_configure_push)
+    if (s->push && s->push_tables.valid && s->push_tables.depth == 2) {
         void *ptrs[6];
         for (int q = 0; q < 6; ++q) ptrs[q] = fl[q]->dptr;
-        return dlesm_dev_halo_exchange(ptrs, 6);
+        return exchange_with(ptrs, 6, s->push_tables);
     }
     return dlesm_fields_halo_exchange(fl, 6, 2);
 }
@@ -2011,16 +2367,13 @@ extern "C" int dlesm_sw_set_two_step(dlesm_sw_t *s, int on, int variant2)
     clear_error();
     if (!on) {
         s->two_step = false;
+        if (s->push) return sw_configure_push(s);   // back to the depth-1 send list
         return DLESM_OK;
     }
     const dlesm_region &in = s->f[DLESM_SW_P]->fb.internal;
     const int nx = s->f[0]->nx, ny = s->f[0]->ny;
     if (s->mode != DLESM_SW_FUSED) {
         set_error(DLESM_ERR_ARGS, "sw_set_two_step: needs the fused mode");
-        return DLESM_ERR_ARGS;
-    }
-    if (s->tmask_dev && nx % 4 != 0) {
-        set_error(DLESM_ERR_ARGS, "sw_set_two_step: with a tmask the pitch must be a multiple of 4 (DL_ESM_ALIGNMENT)");
         return DLESM_ERR_ARGS;
     }
     if (nx % 2 != 0 || in.xstart < 3 || in.ystart < 3 || in.xstop + 2 > nx || in.ystop + 2 > ny ||
@@ -2035,35 +2388,43 @@ extern "C" int dlesm_sw_set_two_step(dlesm_sw_t *s, int on, int variant2)
     static const int pts[3] = {DLESM_GO_U_POINTS, DLESM_GO_V_POINTS, DLESM_GO_T_POINTS};
     for (int q = 0; q < 3; ++q)
         if (!s->old2[q]) {
-            s->old2[q] = dlesm_r2d_field_create(s->grid, pts[q], 0, nullptr, 0, 0);
+            s->old2[q] = dlesm_r2d_field_create(s->grid, pts[q], s->f[0]->ntiles > 0, nullptr, 0, 0);
             if (!s->old2[q]) return last_status();
         }
-    if (s->tmask_dev && !s->tmask2) {
+    if (s->tmask_dev && !s->mask2) {
         // grid_init replicates the mask outward beyond the first halo ring (src/grid_mod.f90:400-431);
         // the two-step sweep reads the ring two cells deep, where the periodic model needs the
-        // wrapped mask.  Build it once: mask -> FP64 image -> depth-2 halo fill -> mask.
+        // wrapped mask.  Build it once: mask -> FP64 image -> depth-2 halo fill -> mask -> byte image.
         const size_t n = static_cast<size_t>(nx) * ny;
         dlesm_field *tmp = dlesm_r2d_field_create(s->grid, DLESM_GO_T_POINTS, 0, nullptr, 0, 0);
         if (!tmp) return last_status();
-        CU(cudaMalloc(&s->tmask2, n * sizeof(int)));
-        CU(cudaMemcpyAsync(s->tmask2, s->tmask_dev, n * sizeof(int), cudaMemcpyDeviceToDevice, ctx().stream));
-        CU(k::mask_convert(s->tmask2, static_cast<double *>(tmp->dptr), n, true, ctx().stream));
+        int *m32 = nullptr;
+        CU(cudaMalloc(&m32, n * sizeof(int)));
+        CU(cudaMemcpyAsync(m32, s->tmask_dev, n * sizeof(int), cudaMemcpyDeviceToDevice, ctx().stream));
+        CU(k::mask_convert(m32, static_cast<double *>(tmp->dptr), n, true, ctx().stream));
         int rc = DLESM_OK;
         if (s->periodic_local) {
             double *dp[1] = {static_cast<double *>(tmp->dptr)};
             CU(k::periodic_halos_deep(dp, 1, nx, box_of(in), 2, ctx().stream));
         } else {
+            mark_written(tmp->dptr);
             rc = dlesm_fields_halo_exchange(&tmp, 1, 2);
         }
-        if (rc == DLESM_OK) CU(k::mask_convert(s->tmask2, static_cast<double *>(tmp->dptr), n, false, ctx().stream));
+        if (rc == DLESM_OK) {
+            CU(k::mask_convert(m32, static_cast<double *>(tmp->dptr), n, false, ctx().stream));
+            s->mask2_pitch = (nx + 15) & ~15;
+            CU(cudaMalloc(&s->mask2, static_cast<size_t>(s->mask2_pitch) * ny));
+            CU(k::mask_to_bytes(m32, nx, ny, s->mask2, s->mask2_pitch, ctx().stream));
+        }
         CU(cudaStreamSynchronize(ctx().stream));
+        cudaFree(m32);
         dlesm_free_field(tmp);
         if (rc != DLESM_OK) return rc;
     }
     s->two_step = true;
     s->variant2 = variant2;
     s->deep_valid = false;
-    if (s->push) return sw_configure_push(s);   // tables two cells deep, the old fields mapped too
+    if (s->push) return sw_configure_push(s);   // send list two cells deep, the old fields mapped too
     return DLESM_OK;
 }
 
@@ -2119,12 +2480,12 @@ extern "C" int dlesm_sw_step(dlesm_sw_t *s, int nsteps)
             int rc = DLESM_OK;
             if (!s->deep_valid) rc = sw_fill_deep_halos(s);
             if (rc != DLESM_OK) return rc;
-            rc = dlesm_sw_step2_fused(f[DLESM_SW_U]->dptr, f[DLESM_SW_V]->dptr, f[DLESM_SW_P]->dptr,
-                                      f[DLESM_SW_UOLD]->dptr, f[DLESM_SW_VOLD]->dptr, f[DLESM_SW_POLD]->dptr,
-                                      f[DLESM_SW_UNEW]->dptr, f[DLESM_SW_VNEW]->dptr, f[DLESM_SW_PNEW]->dptr,
-                                      s->old2[0]->dptr, s->old2[1]->dptr, s->old2[2]->dptr, dx, dy, s->tdt, s->alpha,
-                                      rt.xstart, rt.xstop, rt.ystart, rt.ystop, s->tmask2,
-                                      s->variant2 | (s->push ? DLESM_FUSED_PUSH : 0));
+            rc = sw_step2_fused_impl(f[DLESM_SW_U]->dptr, f[DLESM_SW_V]->dptr, f[DLESM_SW_P]->dptr,
+                                     f[DLESM_SW_UOLD]->dptr, f[DLESM_SW_VOLD]->dptr, f[DLESM_SW_POLD]->dptr,
+                                     f[DLESM_SW_UNEW]->dptr, f[DLESM_SW_VNEW]->dptr, f[DLESM_SW_PNEW]->dptr,
+                                     s->old2[0]->dptr, s->old2[1]->dptr, s->old2[2]->dptr, dx, dy, s->tdt, s->alpha,
+                                     rt.xstart, rt.xstop, rt.ystart, rt.ystop, s->mask2, s->mask2_pitch, s->variant2,
+                                     s->push ? &s->push_tables : nullptr);
             if (rc != DLESM_OK) return rc;
             for (int q = 0; q < 3; ++q) {
                 std::swap(f[DLESM_SW_U + q]->dptr, f[DLESM_SW_UNEW + q]->dptr);
@@ -2143,10 +2504,10 @@ extern "C" int dlesm_sw_step(dlesm_sw_t *s, int nsteps)
         int rc;
 #define P(q) f[q]->dptr
         if (s->mode == DLESM_SW_FUSED) {
-            rc = dlesm_sw_step_fused(P(DLESM_SW_U), P(DLESM_SW_V), P(DLESM_SW_P), P(DLESM_SW_UOLD), P(DLESM_SW_VOLD),
-                                     P(DLESM_SW_POLD), P(DLESM_SW_UNEW), P(DLESM_SW_VNEW), P(DLESM_SW_PNEW), dx, dy,
-                                     s->tdt, s->alpha, first, rt.xstart, rt.xstop, rt.ystart, rt.ystop,
-                                     s->tmask_dev, s->variant | (s->push ? DLESM_FUSED_PUSH : 0));
+            rc = sw_step_fused_impl(P(DLESM_SW_U), P(DLESM_SW_V), P(DLESM_SW_P), P(DLESM_SW_UOLD), P(DLESM_SW_VOLD),
+                                    P(DLESM_SW_POLD), P(DLESM_SW_UNEW), P(DLESM_SW_VNEW), P(DLESM_SW_PNEW), dx, dy,
+                                    s->tdt, s->alpha, first, rt.xstart, rt.xstop, rt.ystart, rt.ystop,
+                                    s->tmask_dev, s->variant, s->push ? &s->push_tables : nullptr);
             if (rc != DLESM_OK) return rc;
             if (!s->push) {
                 rc = sw_fill_halos(s, DLESM_SW_UNEW, 3);
@@ -2311,14 +2672,71 @@ extern "C" int dlesm_sw_set_variant(dlesm_sw_t *s, int variant)
     s->variant = variant;
     return DLESM_OK;
 }
+// Collective when the object pushes halos on several ranks (its buffers are mapped by the
+// neighbours: they unmap, then a barrier, then the memory is freed) -- call it on every rank.
 extern "C" void dlesm_sw_free(dlesm_sw_t *s)
 {
     if (!s) return;
-    if (s->registered) dlesm_dev_peer_unregister_all();   // collective, like the set_halo_mode that mapped them
+    sw_release_peers(s);
     for (auto *fl : s->f)
         if (fl) dlesm_free_field(fl);
     for (auto *fl : s->old2)
         if (fl) dlesm_free_field(fl);
-    if (s->tmask2) cudaFree(s->tmask2);
+    if (s->mask2) cudaFree(s->mask2);
     delete s;
+}
+
+// Non-collective release for finalisers (a garbage collector must never enter a collective: ranks
+// would have to agree on its order).  Buffers the neighbours still have mapped are NOT freed --
+// they stay allocated until dlesm_dev_peer_unregister_all / process exit -- everything else is.
+extern "C" void dlesm_sw_free_local(dlesm_sw_t *s)
+{
+    if (!s) return;
+    const bool mapped = !s->registered.empty() && pstate().nranks > 1;
+    auto is_mapped = [&](void *p) {
+        return mapped && std::find(s->registered.begin(), s->registered.end(), p) != s->registered.end();
+    };
+    auto drop = [&](dlesm_field *fl) {
+        if (!fl) return;
+        if (is_mapped(fl->dptr)) {
+            std::fprintf(stderr, "dlesm: shallow-water object finalised while its buffers are mapped by the neighbours; "
+                                 "call free() on every rank instead -- leaking %p\n", fl->dptr);
+            delete fl;
+        } else {
+            dlesm_free_field(fl);
+        }
+    };
+    if (!mapped) sw_release_peers(s);   // one rank: local bookkeeping only
+    for (auto *fl : s->f) drop(fl);
+    for (auto *fl : s->old2) drop(fl);
+    if (s->mask2) cudaFree(s->mask2);
+    delete s;
+}
+
+// the launch grid (grid.x, grid.y) the one-step (two_step = 0) or two-step sweep of this model uses:
+// what the tile-grid knob (GOCEAN_OMP_GRID / dlesm_dev_set_sweep_tiles) changes
+extern "C" int dlesm_sw_launch_grid(dlesm_sw_t *s, int two_step, int grid[2])
+{
+    clear_error();
+    const dlesm_region &rt = s->f[DLESM_SW_P]->fb.internal;
+    const bool fma = ctx().arith == DLESM_ARITH_CONTRACTED;
+    if (two_step) {
+        k::Fused2Args a{};
+        a.pitch = s->f[0]->nx; a.ny = s->f[0]->ny;
+        a.b = box_of(rt);
+        a.tiles = ctx().sweep_tiles;
+        if (fma) k::fma_on::fused2_grid(a, s->variant2, grid);
+        else k::fma_off::fused2_grid(a, s->variant2, grid);
+    } else {
+        k::FusedArgs a{};
+        a.pitch = s->f[0]->nx; a.ny = s->f[0]->ny;
+        a.b = box_of(rt);
+        a.tiles = ctx().sweep_tiles;
+        a.tmask = s->tmask_dev;
+        static const unsigned char dummy = 0;
+        if (a.tmask) { a.mask8 = &dummy; a.mask8_pitch = 16; }   // geometry only
+        if (fma) k::fma_on::fused_grid(a, s->variant, grid);
+        else k::fma_off::fused_grid(a, s->variant, grid);
+    }
+    return DLESM_OK;
 }

@@ -84,8 +84,11 @@ extern "C" {
 
 /* last error message of the calling thread ("" if none) */
 const char *dlesm_last_error(void);
-/* library version string, e.g. "dlesm_b200 0.1 (sm_100a)" */
+/* library version string, e.g. "dlesm_b200 0.2 (sm_100a, ...) src <hash>" */
 const char *dlesm_version(void);
+/* hash of every source, header and compiler flag this library was built from (32 hex digits);
+ * dl_esm_inf_b200/build.py compares it with the sources on disk and rebuilds on mismatch */
+const char *dlesm_source_hash(void);
 
 /* ------------------------------------------------------------------------------------ */
 /* index boxes -- src/region_mod.f90:7-12, src/decomposition_mod.f90:44-50,              */
@@ -148,6 +151,12 @@ int dlesm_set_extensions(int flags);
  * decomposed with (the reference hard-wires depth 1: MAX_HALO_DEPTH, src/parallel_comms_mod.f90:48,
  * src/field_mod.f90:1226-1229). */
 #define DLESM_EXT_HALO_DEPTH 2
+/* bit 2: dirty-flag halos.  halo_type%needs_update exists in the reference but its set_dirty /
+ * is_dirty methods are commented out (src/halo_mod.f90:10-40) and every halo_exchange runs.  With
+ * this bit the library tracks, per device array, whether its halos are up to date (every entry point
+ * that writes an array marks it dirty; halo_exchange, the periodic fill and a pushing sweep mark it
+ * clean) and halo_exchange / apply_periodic_halos skip fields whose halos are clean: no launch. */
+#define DLESM_EXT_DIRTY_HALOS 4
 
 /* ------------------------------------------------------------------------------------ */
 /* HOST MIRROR: decomposition -- src/parallel_mod.f90:70-332, decomposition_mod.f90      */
@@ -282,6 +291,15 @@ typedef struct {
 dlesm_field_t *dlesm_r2d_field_create(dlesm_grid_t *g, int grid_points, int do_tile,
                                       const double *init_global_data, int gnx, int gny);
 int dlesm_field_get_info(const dlesm_field_t *f, dlesm_field_info *out);
+/* tile(itile)%internal / %whole (src/field_mod.f90:316-319, src/tile_mod.f90:36-42), 1 <= itile <= ntiles.
+ * r2d_field(..., do_tile=.true.) cuts the field's internal region into the tile grid the sweeps use:
+ * GOCEAN_OMP_GRID="AxB" (src/field_mod.f90:1473-1503) = A x-tiles (each cut into strips of the sweep's
+ * width) by B tiles (segments) along j, go_decompose's remainder rule; without it the library's choice. */
+int dlesm_field_tile(const dlesm_field_t *f, int itile1, dlesm_region *internal, dlesm_region *whole);
+/* halo_type%needs_update as a query / set_dirty (src/halo_mod.f90:18-40): is the halo out of date to
+ * `depth` cells?  (tracked always; acted upon under DLESM_EXT_DIRTY_HALOS) */
+int dlesm_field_halo_is_dirty(const dlesm_field_t *f, int depth);
+int dlesm_field_set_halo_dirty(dlesm_field_t *f);
 /* fld%grid (src/field_mod.f90:114) */
 dlesm_grid_t *dlesm_field_grid(const dlesm_field_t *f);
 /* set_field_bounds only (src/field_mod.f90:563-624): the regions and halo list a field of
@@ -359,7 +377,8 @@ int dlesm_dev_checksum(const void *field, int xstart, int xstop, int ystart, int
 int dlesm_dev_periodic_halos(void *field, int xstart, int xstop, int ystart, int ystop,
                              int periodic_x, int periodic_y);
 /* Install the comm tables computed by the (unchanged Fortran or mirrored) map_comms for this
- * rank; later dlesm_dev_halo_exchange calls use them. */
+ * rank; later dlesm_dev_halo_exchange calls use them (module-level state, like parallel_comms_mod's).
+ * NULL removes them (the state before any grid_init: halo_exchange is a no-op). */
 int dlesm_dev_set_comms(const dlesm_comms *tables);
 /* exchange_generic (src/parallel_comms_mod.f90:1501-1855) on device-resident fields: fused
  * pack kernel -> grouped NCCL send/recv (self-neighbours: on-device) -> fused unpack kernel */
@@ -412,9 +431,25 @@ int dlesm_time_smooth(const void *f, const void *fnew, void *fold, double alpha,
  * and all ranks stepping in lockstep. */
 #define DLESM_FUSED_PUSH 0x1000
 int dlesm_dev_peer_register(void *const *fields, int nfields);
-/* Collective: unmap every neighbour field mapped so far, then barrier.  Call before freeing
+/* Collective: drop the registration of these fields (the neighbours' mappings they hold are released,
+ * closed when no other registered field shares the allocation), then barrier.  Call before freeing
  * registered fields (importers must close a CUDA IPC mapping before the exporter frees). */
+int dlesm_dev_peer_unregister(void *const *fields, int nfields);
+/* Collective: the same for every field registered so far. */
 int dlesm_dev_peer_unregister_all(void);
+/* Arithmetic of the fused sweeps.  DLESM_ARITH_EXACT (default): one rounding per operation
+ * (-fmad=false), bit-identical to the reference's FMA-free Fortran loops.  DLESM_ARITH_CONTRACTED: the
+ * same kernels compiled with FMA contraction -- fewer FP64 instructions -- results within north_star's
+ * 1e-12 relative tolerance of the exact ones.  The environment variable DLESM_ARITH=fma selects the
+ * contracted form at start-up. */
+#define DLESM_ARITH_EXACT 0
+#define DLESM_ARITH_CONTRACTED 1
+int dlesm_set_arith(int mode);
+int dlesm_get_arith(void);
+/* The tile grid of the sweeps: ntilex x-tiles by ntiley segments (0 = the library's choice).  What
+ * r2d_field(..., do_tile) + GOCEAN_OMP_GRID="AxB" set (src/field_mod.f90:300-325); a Fortran build calls
+ * this from the field constructor. */
+int dlesm_dev_set_sweep_tiles(int ntilex, int ntiley);
 int dlesm_sw_step_fused(const void *u, const void *v, const void *p, void *uold, void *vold,
                         void *pold, void *unew, void *vnew, void *pnew, double dx, double dy,
                         double tdt, double alpha, int first, int xstart, int xstop, int ystart,
@@ -499,7 +534,13 @@ long long dlesm_kernel_launch_count(void);
  * fused-step launch; used by bench.py for the roofline figure) */
 int dlesm_profile_enable(int on);
 int dlesm_profile_read(double *ms_total, long long *nlaunches, int reset);
+/* Collective when the object pushes halos on several ranks (call it on every rank). */
 void dlesm_sw_free(dlesm_sw_t *s);
+/* Non-collective release for finalisers: frees everything except buffers the neighbours still have
+ * mapped (those leak until dlesm_dev_peer_unregister_all / process exit; a warning is printed). */
+void dlesm_sw_free_local(dlesm_sw_t *s);
+/* launch grid (grid.x, grid.y) of the model's one-step (two_step = 0) or two-step sweep */
+int dlesm_sw_launch_grid(dlesm_sw_t *s, int two_step, int grid[2]);
 
 /* ------------------------------------------------------------------------------------ */
 /* PSy LAYER: metadata-driven kernel dispatch -- kernel_mod / argument_mod                */

@@ -242,6 +242,7 @@ void orc_sw_step(double *fields[13], const orc_sw_params *prm, const orc_field_b
  * the serial fd_lib path (copy_field periodic halos, no exchange).
  * Returns wall seconds for `nsteps` timed steps (after `warmup` untimed ones);
  * checksums[3] = field_checksum of p,u,v after the last step (summed over workers). */
+void orc_sw_last_checksums_ld(double out[3]);
 double orc_sw_run_threads(int global_nx, int global_ny, int nthreads, int nsteps, int warmup,
                           double *checksums);
 

@@ -182,6 +182,8 @@ def lib():
     L.orc_sw_step.argtypes = [C.POINTER(_dp), C.POINTER(SwParams), FB, FB, FB, FB, _ip, C.c_int]
     L.orc_sw_run_threads.argtypes = [C.c_int] * 5 + [_dp]
     L.orc_sw_run_threads.restype = C.c_double
+    L.orc_sw_last_checksums_ld.argtypes = [_dp]
+    L.orc_sw_last_checksums_ld.restype = None
     _lib = L
     return L
 
@@ -417,3 +419,10 @@ def sw_run_threads(global_nx, global_ny, nthreads, nsteps, warmup=0):
     if secs < 0:
         raise RuntimeError("orc_sw_run_threads failed")
     return secs, tuple(cks)
+
+
+def sw_last_checksums_ld():
+    """(p, u, v) checksums of the last sw_run_threads call, accumulated in long double"""
+    cks = np.zeros(3)
+    lib().orc_sw_last_checksums_ld(_d(cks))
+    return tuple(cks)

@@ -60,3 +60,87 @@ def test_masked_points_are_not_advanced():
     assert np.array_equal(sw.f["u"][10:15, 20:25], u0[10:15, 20:25])      # U points touching land keep u
     assert not np.array_equal(sw.f["p"][2:8, 2:8], p0[2:8, 2:8])
     assert np.all(sw.f["cu"][10:15, 20:25] == 0.0) and np.all(sw.f["h"][10:14, 20:25] == 0.0)
+
+
+# ---------------------------------------------------------------------------------------------
+# the second opinion: the oracle against an independent restatement of the PUBLISHED benchmark
+# (NCAR shallow.f / Sadourny 1975) on the bare periodic core -- oracle/shallow_published.py
+# ---------------------------------------------------------------------------------------------
+def core(sw, name):
+    i = sw.fb["t"].internal
+    return sw.f[name][i.xstart - 1:i.xstop, i.ystart - 1:i.ystop]
+
+
+def perturbed_pair(n_x, n_y, seed, amp=0.05, **kw):
+    """oracle model + published model from the same state: the benchmark's analytic initial
+    condition with a random perturbation (so that nothing is steady or symmetric)"""
+    from oracle.shallow_published import PublishedShallow
+    sw = O.ShallowWater(n_x, n_y, **kw)
+    rng = np.random.default_rng(seed)
+    i = sw.fb["t"].internal
+    sl = (slice(i.xstart - 1, i.xstop), slice(i.ystart - 1, i.ystop))
+    for k, pts in (("u", "u"), ("v", "v"), ("p", "t")):
+        a = sw.f[k]
+        a[sl] = a[sl] * (1.0 + amp * rng.uniform(-1.0, 1.0, size=a[sl].shape))
+        O.lib().orc_apply_periodic_halos(O._d(a), sw.grid.nx, sw.fb[pts])
+    for x, y in (("u", "uold"), ("v", "vold"), ("p", "pold")):
+        O.copy_field(sw.f[x], sw.f[y])
+    ps = PublishedShallow(core(sw, "u"), core(sw, "v"), core(sw, "p"), dx=sw.grid.dx, dy=sw.grid.dy,
+                          dt=sw.dt, alpha=sw.alpha)
+    return sw, ps
+
+
+@pytest.mark.parametrize("n_x,n_y,seed", [(64, 64, 1), (50, 37, 2), (33, 129, 3)])
+def test_oracle_equals_published_scheme(n_x, n_y, seed):
+    """100 steps: every prognostic field of the oracle (fd_lib containers, halo copies, region
+    loops) equals the roll-based restatement of shallow.f -- same association order, no FMA on
+    either side, so bit for bit; includes the first-step rule (tdt doubles, no filter)"""
+    sw, ps = perturbed_pair(n_x, n_y, seed)
+    for step in range(100):
+        sw.step()
+        ps.step()
+        if step in (0, 1, 2, 49, 99):
+            assert sw.tdt == ps.tdt == 2 * sw.dt
+            for k in ("u", "v", "p", "uold", "vold", "pold"):
+                assert np.array_equal(core(sw, k), getattr(ps, k)), (k, step)
+
+
+def test_first_step_is_forward_euler_then_leapfrog_with_doubled_tdt():
+    """shallow.f: the first cycle advances from (uold = u) with tdt = dt and then sets
+    tdt = 2 dt; a model that skipped the doubling would take leapfrog steps of half length"""
+    from oracle.shallow_published import PublishedShallow
+    sw, ps = perturbed_pair(40, 40, 7)
+    u0, p0 = core(sw, "u").copy(), core(sw, "p").copy()
+    assert sw.tdt == sw.dt
+    sw.step()
+    assert sw.tdt == 2 * sw.dt
+    assert np.array_equal(core(sw, "uold"), u0) and np.array_equal(core(sw, "pold"), p0)   # no filter on step 1
+    # step 2 is a leapfrog step of 2 dt from the ORIGINAL state: redo it by hand with the published formulas
+    chk = PublishedShallow(core(sw, "u"), core(sw, "v"), core(sw, "p"), dt=sw.dt)
+    chk.uold, chk.vold, chk.pold = u0, ps.v.copy(), p0
+    chk.tdt, chk.ncycle = 2 * sw.dt, 1
+    chk.step()
+    sw.step()
+    assert np.array_equal(core(sw, "p"), chk.p) and np.array_equal(core(sw, "u"), chk.u)
+
+
+def drift(dt, nsteps, amp=0.05):
+    from oracle.shallow_published import invariants
+    sw, _ = perturbed_pair(96, 80, 11, amp=amp, dt=dt)
+    i0 = invariants(core(sw, "u"), core(sw, "v"), core(sw, "p"), sw.grid.dx, sw.grid.dy)
+    for _ in range(nsteps):
+        sw.step()
+    i1 = invariants(core(sw, "u"), core(sw, "v"), core(sw, "p"), sw.grid.dx, sw.grid.dy)
+    return [abs(a - b) / abs(b) for a, b in zip(i1, i0)]
+
+
+def test_sadourny_invariants_drift_bounds():
+    """Properties of the published scheme, independent of how either implementation is coded: over
+    100 steps of a strongly perturbed flow mass is conserved to rounding, potential enstrophy --
+    what Sadourny's scheme conserves in space -- to 1e-7, total energy to time-truncation order, and
+    the energy drift over the same model time shrinks faster than linearly when dt is halved
+    (measured here: 6.8e-5 -> 1.0e-5 -> 7.8e-7)"""
+    m, e, z = drift(90.0, 100)
+    assert m <= 1e-13 and e <= 2e-4 and z <= 1e-7
+    m2, e2, z2 = drift(45.0, 200)
+    assert m2 <= 1e-13 and z2 <= 1e-7 and e2 <= e / 3.0

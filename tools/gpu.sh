@@ -1,0 +1,52 @@
+#!/bin/bash
+# One parameterised GPU-box runner (replaces the one-off gpu_*.sh scripts of round 1).
+#   tools/gpu.sh tests            # every -m gpu test + smoke
+#   tools/gpu.sh bench [args..]   # python bench.py args..       (1 GPU)
+#   tools/gpu.sh benchn N [args]  # torchrun bench.py --gpus N args..
+#   tools/gpu.sh worker N         # tests/dist_worker.py on N GPUs
+#   tools/gpu.sh launches [args]  # ncu launch list of `bench.py args` (after a plain run exited 0)
+#   tools/gpu.sh ncu REGEX TAG [args]  # ncu --set full of kernels matching REGEX in `bench.py args`
+#   tools/gpu.sh micro [args]     # tools/microbench.py
+# Outputs land in gpurun_out/ (merged back by gpurun).  TAG env prefixes file names.
+set -u
+mkdir -p gpurun_out
+T=${TAG:-r02}
+what=${1:-tests}; shift || true
+trun() { n=$1; shift; timeout ${TMO:-900} python -m torch.distributed.run --nnodes=1 --nproc-per-node $n \
+         --master-addr 127.0.0.1 --master-port ${PORT:-29533} "$@"; }
+case $what in
+  tests)
+    timeout ${TMO:-1500} python -m pytest tests -m gpu -q "$@" > gpurun_out/${T}_pytest_gpu.log 2>&1
+    echo "pytest rc=$?" | tee -a gpurun_out/${T}_pytest_gpu.log; tail -4 gpurun_out/${T}_pytest_gpu.log
+    timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/${T}_smoke.log 2>&1
+    echo "smoke rc=$?"; tail -1 gpurun_out/${T}_smoke.log ;;
+  bench)
+    timeout ${TMO:-900} python bench.py "$@" > gpurun_out/${T}_bench.log 2>&1; echo "bench rc=$?"
+    grep '^{' gpurun_out/${T}_bench.log > gpurun_out/${T}_bench.json; tail -c 1500 gpurun_out/${T}_bench.log ;;
+  benchn)
+    n=$1; shift
+    trun $n bench.py --gpus $n "$@" > gpurun_out/${T}_bench_n$n.log 2>&1; echo "bench n=$n rc=$?"
+    grep '^{' gpurun_out/${T}_bench_n$n.log > gpurun_out/${T}_bench_n$n.json; tail -c 1500 gpurun_out/${T}_bench_n$n.log ;;
+  worker)
+    n=$1; shift
+    trun $n tests/dist_worker.py "$@" > gpurun_out/${T}_dist_worker_n$n.log 2>&1
+    echo "dist_worker rc=$?" | tee -a gpurun_out/${T}_dist_worker_n$n.log
+    grep -v "^\[W\|^W1\|OMP_NUM\|^\*\*\*" gpurun_out/${T}_dist_worker_n$n.log | tail -8 ;;
+  launches)
+    CMD="python bench.py --steps 6 --warmup 3 --e2e-steps 0 --no-cpu-baseline --no-parity $*"
+    $CMD > gpurun_out/${T}_plain.log 2>&1 &&
+    ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv \
+        --log-file gpurun_out/${T}_launches.csv $CMD > gpurun_out/${T}_ncu_launches.log 2>&1
+    echo "launch list rc=$?" ;;
+  ncu)
+    re=$1; tag=$2; shift 2
+    CMD="python bench.py --steps 8 --warmup 3 --e2e-steps 0 --no-cpu-baseline --no-parity $*"
+    $CMD > gpurun_out/${T}_${tag}_plain.log 2>&1 &&
+    timeout ${TMO:-900} ncu --set full --clock-control none --import-source on -k regex:$re -s ${SKIP:-2} -c 1 \
+        -o gpurun_out/${T}_${tag} -f $CMD > gpurun_out/${T}_${tag}_ncu.log 2>&1
+    echo "ncu $tag rc=$?" ;;
+  micro)
+    timeout ${TMO:-900} python tools/microbench.py "$@" > gpurun_out/${T}_micro.jsonl 2> gpurun_out/${T}_micro.err
+    echo "micro rc=$?"; tail -2 gpurun_out/${T}_micro.err ;;
+  *) echo "unknown action $what"; exit 2 ;;
+esac
