@@ -9,6 +9,19 @@ GO_OFFSET_SW, 16384^2 points PER GPU (weak scaling: the global domain grows with
 go_decompose tile grid 1x1, 1x2, 2x2, 2x4), DL_ESM_ALIGNMENT=64, synthetic classic "shallow"
 initial state.  One bench step = one model time step of the fused sweep + halo fill /
 exchange.  One JSON line on stdout (rank 0).
+
+Besides the timed K steps the line carries, all outside the timed region:
+  parity     a pre-flight parity leg on the SAME ranks and the same halo path as the timed leg: the
+             reference's distributed known answers (example/model.f90, tests/dist_mem/test_halos.f90,
+             test_gsum.f90, test_reduction.f90) and a 1024x1536 shallow-water domain (with and without
+             a tmask, one-step and two-step sweep), gathered to rank 1 and compared bit for bit with the
+             serial oracle; any mismatch ends the run with exit code 1
+  sustained  >= --sustain-s seconds of back-to-back steps with their own clocks record (the driver's
+             --steps 20 is a 40 ms burst, shorter than the board's power-management time constant)
+  config3    BASELINE configs[2]: 4096^2 with tmask land islands, value + roofline + an oracle
+             comparison of every field at full size (N=1)
+  cpu_baseline  and the assertion that the GPU checksums after the same number of steps agree with
+             the CPU arm's within 1e-12 at full size (N=1)
 """
 from __future__ import annotations
 
@@ -99,15 +112,21 @@ def measured_hbm_peak():
 # ---------------------------------------------------------------------------------------------
 # reference arm / cpu baseline: the oracle port of the reference's CPU formulation
 # ---------------------------------------------------------------------------------------------
+WORKLOAD = ("shallow-water C-grid step, %dx%d points per GPU (weak scaling over go_decompose tiles), double periodic, "
+            "GO_OFFSET_SW, FP64, DL_ESM_ALIGNMENT=%d, fused mode")
+
+
 def cpu_run(global_n, nthreads, steps, warmup):
+    """returns points/s, seconds, the reference-style checksums (double-precision sum(abs()) per
+    sub-domain + global_sum) and the same sums accumulated in long double"""
     from oracle import oracle as O
     secs, cks = O.sw_run_threads(global_n, global_n, nthreads, steps, warmup)
-    return global_n * global_n * steps / secs, secs, cks
+    return global_n * global_n * steps / secs, secs, cks, O.sw_last_checksums_ld()
 
 
 def pick_cpu_sample(nthreads, steps, warmup, budget_s):
     """largest square sample whose (steps+warmup) steps fit the time budget"""
-    rate, _, _ = cpu_run(1024, nthreads, 3, 1)          # calibration: points/s
+    rate = cpu_run(1024, nthreads, 3, 1)[0]              # calibration: points/s
     best = 1024
     for n in (2048, 4096, 8192, 16384):
         est = n * n * (steps + warmup) / rate * 1.3 + 13 * n * n * 8 / 4e9   # + first-touch init
@@ -126,23 +145,26 @@ def run_reference_arm(args):
         return 0        # rank 0 alone runs the CPU arm
     ncores = os.cpu_count() or 1
     n = pick_cpu_sample(ncores, args.steps, args.warmup, budget_s=90.0)
-    value, secs, cks = cpu_run(n, ncores, args.steps, args.warmup)
-    sample = ("%dx%d double-periodic sample of the 16384^2-per-GPU workload, %d timed steps, %d threads "
-              "(one go_decompose sub-domain each, exchange_generic-style pack/copy/unpack)"
-              % (n, n, args.steps, ncores))
+    value, secs, cks, cks_ld = cpu_run(n, ncores, args.steps, args.warmup)
+    sample = ("%dx%d double-periodic sample of the %d^2-per-GPU workload, %d timed steps, %d threads "
+              "(one go_decompose sub-domain each, exchange_generic-style pack/copy/unpack)%s"
+              % (n, n, args.size, args.steps, ncores,
+                 "; at --gpus %d the GPU arm's domain is %d such tiles: the CPU arm times ONE tile's worth of "
+                 "points on this host (throughput metric, same points/s unit)" % (args.gpus, args.gpus)
+                 if args.gpus > 1 else ""))
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1000.0 * secs / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
         "data": "synthetic",
-        "config": {"workload": "shallow-water C-grid step, 16384^2 points per GPU, double periodic, FP64 "
-                               "(CPU arm: bounded sample, see cpu_baseline.sample)",
+        "config": {"workload": WORKLOAD % (args.size, args.size, args.alignment),
+                   "reference_sample": sample,
                    "reference_build": "oracle port of the reference's Fortran loops (no Fortran/MPI toolchain "
                                       "in this image: oracle/_ref cannot be built)"},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": ncores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
-        "checksums_p_u_v": list(cks),
+        "checksums_p_u_v": list(cks), "checksums_p_u_v_long_double": list(cks_ld),
     }
     print(json.dumps(line), flush=True)
     return 0
@@ -151,6 +173,79 @@ def run_reference_arm(args):
 # ---------------------------------------------------------------------------------------------
 # our arm
 # ---------------------------------------------------------------------------------------------
+def config3_mask_for(grid, gx, gy, np):
+    """BASELINE config 3: land on 64x64 islands where mod(i,512) in [200,263] and mod(j,512) in
+    [300,363] (~1.6 % land), periodic; this tile's part over its whole extent incl. halos"""
+    sb = grid.subdomain
+    hw = sb.internal.xstart - 1
+    gi = (sb.glob.xstart - 1 - hw + np.arange(sb.glob.nx)) % gx + 1
+    gj = (sb.glob.ystart - 1 - hw + np.arange(sb.glob.ny)) % gy + 1
+    li = (gi % 512 >= 200) & (gi % 512 <= 263)
+    lj = (gj % 512 >= 300) & (gj % 512 <= 363)
+    return np.asfortranarray(np.where(li[:, None] & lj[None, :], 0, 1).astype(np.int32))
+
+
+def run_parity(args, fd, dist, torch, world, rank):
+    """Pre-flight parity leg, outside every timed region, on the ranks and the halo path of the timed
+    leg.  Cases and checks are those of tests/dist_worker.py (the reference's distributed tests +
+    the periodic shallow-water model against the serial oracle, fields gathered with
+    gather_inner_data and compared bit for bit)."""
+    tdir = os.path.join(ROOT, "tests")
+    if tdir not in sys.path:
+        sys.path.insert(0, tdir)
+    import dist_worker as DW
+    DW.COLLECT = True
+    t0 = time.time()
+    cases = []
+
+    def run(name, fn, *a, **k):
+        fn(*a, **k)
+        cases.append(name)
+
+    # the reference's own known answers on `world` ranks
+    run("example/model.f90:54-109", DW.case_example_model)
+    run("tests/dist_mem/test_gsum.f90:107-132", DW.case_gsum)
+    for shape in ((10, 4), (4, 10), (10, 10), (37, 23)):
+        run("tests/dist_mem/test_halos.f90:153-265 %dx%d" % shape, DW.case_halos, *shape)
+    run("test_halos.f90 64x48 DL_ESM_ALIGNMENT=64", DW.case_halos, 64, 48, alignment=64)
+    run("tests/dist_mem/test_reduction.f90:128-192", DW.case_reduction, 10)
+    run("parallel_utils_mod gather", DW.case_gather)
+    # the timed path against the serial oracle: 1024x1536, DL_ESM_ALIGNMENT=64
+    push = fd.HALO_PUSH if (world > 1 or args.halo == "push") and args.halo != "exchange" else None
+    hname = "halo push" if push is not None else ("periodic halo kernel" if world == 1 else "NCCL exchange")
+    nx, ny, A = 1024, 1536, args.alignment
+    for masked in (False, True):
+        tag = " + tmask" if masked else ""
+        run("shallow water %dx%d one-step sweep, %s%s" % (nx, ny, hname, tag), DW.case_shallow_water,
+            nx, ny, 7, A, fd.SW_FUSED, halo_mode=push, masked=masked)
+        run("shallow water %dx%d two-step sweep, %s%s" % (nx, ny, hname, tag), DW.case_shallow_water,
+            nx, ny, 8, A, fd.SW_FUSED, halo_mode=push, two_step=True, masked=masked)
+    if push is not None:
+        run("shallow water %dx%d one-step sweep, exchange path" % (nx, ny), DW.case_shallow_water,
+            nx, ny, 5, A, fd.SW_FUSED)
+    run("shallow water %dx%d two-step sweep, %s, contracted arithmetic (1e-12)" % (nx, ny, hname),
+        DW.case_shallow_water, nx, ny, 8, A, fd.SW_FUSED, halo_mode=push, two_step=True, arith=fd.ARITH_CONTRACTED)
+    run("shallow water %dx%d one-step sweep, %s, contracted arithmetic (1e-12)" % (nx, ny, hname),
+        DW.case_shallow_water, nx, ny, 7, A, fd.SW_FUSED, halo_mode=push, arith=fd.ARITH_CONTRACTED)
+    fd.dev_sync()
+    nfail, ncheck = len(DW.FAILURES), DW.NCHECK
+    if dist is not None:
+        t = torch.tensor([nfail, ncheck], dtype=torch.int64, device="cuda")
+        dist.all_reduce(t)
+        nfail, ncheck = int(t[0].item()), int(t[1].item())
+    for msg in DW.FAILURES[:10]:
+        print("PARITY MISMATCH " + msg, file=sys.stderr, flush=True)
+    # leave the library as the timed legs expect it
+    fd.gocean_initialise(rank + 1, world)
+    fd.set_arith(fd.ARITH_EXACT)
+    os.environ["DL_ESM_ALIGNMENT"] = str(args.alignment)
+    return {"checked": True, "ranks": world, "cases": len(cases), "checks": ncheck, "mismatches": nfail,
+            "seconds": time.time() - t0, "halo_path": hname,
+            "oracle": "serial CPU oracle (oracle/), itself pinned on the reference's known answers and on the "
+                      "published shallow.f scheme (tests/test_oracle_golden.py, tests/test_oracle_sw.py)",
+            "case_list": cases}
+
+
 def run_ours(args):
     os.environ["DL_ESM_ALIGNMENT"] = str(args.alignment)
     rank, world, local_rank = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
@@ -176,7 +271,6 @@ def run_ours(args):
             idt = torch.frombuffer(bytearray(fd.comm_unique_id()), dtype=torch.uint8).cuda()
         dist.broadcast(idt, 0)
         fd.gocean_initialise(rank + 1, world, device=local_rank, comm_id=bytes(idt.cpu().numpy().tobytes()))
-        fd.set_extensions(fd.EXT_PERIODIC_DISTMEM)   # periodic wrap across ranks (SURVEY F4 extension)
 
     def barrier():
         fd.dev_sync()
@@ -184,45 +278,61 @@ def run_ours(args):
             dist.barrier()
             torch.cuda.synchronize()
 
+    def max_over_ranks(x):
+        if dist is None:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- parity first: a bench line of a wrong kernel is worth nothing ----
+    parity = {"checked": False, "mismatches": None, "why": "--no-parity"}
+    if not args.no_parity:
+        parity = run_parity(args, fd, dist, torch, world, rank)
+        if parity["mismatches"]:
+            if rank == 0:
+                print(json.dumps({"metric": METRIC, "value": None, "parity": parity,
+                                  "error": "parity leg found mismatches: no number is reported"}), flush=True)
+            return 1
+
     sampler = ClockSampler(local_rank)
     sampler.start()
+    peak, peak_src = measured_hbm_peak()
+    ext_base = fd.EXT_PERIODIC_DISTMEM if world > 1 else 0   # periodic wrap across ranks (SURVEY F4 extension)
 
-    def timed(two_step, run=True):
+    def timed(two_step, run=True, size=None, tmask=None, scaling=None, steps=None, sustain_s=None, arith=None):
         """one timed run of K steps: the one-step sweep (96 B/point per step) or the two-step sweep
         (temporal blocking: 96 B/point per TWO steps, tiles with halo width 2)"""
-        # weak scaling: args.size^2 points per GPU; strong: args.size^2 points in total (configs[3]
-        # names both).  The tile grid is go_decompose's own choice either way.
-        n = args.size
+        # weak scaling: size^2 points per GPU; strong: size^2 points in total (configs[3] names both).
+        # The tile grid is go_decompose's own choice either way.
+        n = size or args.size
+        tmask = args.tmask if tmask is None else tmask
+        scaling = scaling or args.scaling
+        steps = steps or args.steps
+        sustain_s = args.sustain_s if sustain_s is None else sustain_s
+        fd.gocean_initialise(rank + 1, world)               # go_decompose's SAVEd halo width back to 1
+        fd.set_arith(fd.ARITH_CONTRACTED if (arith or args.arith) == "fma" else fd.ARITH_EXACT)
         probe = fd.go_decompose(n, n)                       # tile grid for `world` ranks on a square domain
-        if args.scaling == "strong":
+        if scaling == "strong":
             gx, gy = n, n
         else:
             gx, gy = n * probe.nx, n * probe.ny
         bcs = (fd.GO_BC_PERIODIC, fd.GO_BC_PERIODIC, fd.GO_BC_NONE)
         grid = fd.grid_type(fd.GO_ARAKAWA_C, bcs, fd.GO_OFFSET_SW)
         if two_step:
-            fd.set_extensions(fd.EXT_PERIODIC_DISTMEM | fd.EXT_HALO_DEPTH if world > 1 else 0)
+            fd.set_extensions(ext_base | (fd.EXT_HALO_DEPTH if world > 1 else 0))
             grid.decompose(gx, gy, halo_width=2)      # the two-step sweep needs two halo cells
         else:
+            fd.set_extensions(ext_base)
             grid.decompose(gx, gy)
-        tm = None
-        if args.tmask:
-            # BASELINE config 3: land on 64x64 islands where mod(i,512) in [200,263] and mod(j,512) in
-            # [300,363] (~1.6 % land), periodic; this tile's part over its whole extent incl. halos
-            sb = grid.subdomain
-            hw = sb.internal.xstart - 1
-            gi = (sb.glob.xstart - 1 - hw + np.arange(sb.glob.nx)) % gx + 1
-            gj = (sb.glob.ystart - 1 - hw + np.arange(sb.glob.ny)) % gy + 1
-            li = (gi % 512 >= 200) & (gi % 512 <= 263)
-            lj = (gj % 512 >= 300) & (gj % 512 <= 363)
-            tm = np.asfortranarray(np.where(li[:, None] & lj[None, :], 0, 1).astype(np.int32))
+        tm = config3_mask_for(grid, gx, gy, np) if tmask else None
         fd.grid_init(grid, 1.0e5, 1.0e5, tm)
         sub = grid.subdomain
         local_points = sub.internal.nx * sub.internal.ny
         total_points = gx * gy
 
         sw = fd.shallow_water(grid, dt=90.0, alpha=0.001, mode=fd.SW_FUSED if args.mode == "fused" else fd.SW_UNFUSED,
-                              use_tmask=bool(args.tmask))
+                              use_tmask=bool(tmask))
         sw.set_variant(args.variant)
         if two_step:
             sw.set_two_step(True, args.variant2)
@@ -236,68 +346,79 @@ def run_ours(args):
             return dict(sw=sw, grid=grid, total_points=total_points)
         mass0 = fd.field_checksum(sw.field("p"))
 
-        sw.step(max(args.warmup, 3))
-        L.dlesm_profile_enable(1)
-        L.dlesm_profile_read(None, None, 1)
-        barrier()
-        launches0 = fd.kernel_launch_count()
-        t_wall0 = time.time()
-        L.dlesm_event_record(0)
-        sw.step(args.steps)
-        L.dlesm_event_record(1)
-        ms = C.c_double(0.0)
-        assert L.dlesm_event_elapsed_ms(0, 1, C.byref(ms)) == 0
-        barrier()
-        t_wall1 = time.time()
-        launches = fd.kernel_launch_count() - launches0
-        kms, kn = C.c_double(0.0), C.c_longlong(0)
-        L.dlesm_profile_read(C.byref(kms), C.byref(kn), 1)
-        L.dlesm_profile_enable(0)
-        clocks = sampler.summary(t_wall0, t_wall1)
+        def region(nsteps):
+            """nsteps back-to-back model steps bracketed by barrier + sync; device time (CUDA events on the
+            library's stream), max over ranks; the dominant kernel timed by its own event pairs"""
+            L.dlesm_profile_enable(1)
+            L.dlesm_profile_read(None, None, 1)
+            barrier()
+            launches0 = fd.kernel_launch_count()
+            w0 = time.time()
+            L.dlesm_event_record(0)
+            sw.step(nsteps)
+            L.dlesm_event_record(1)
+            ms = C.c_double(0.0)
+            assert L.dlesm_event_elapsed_ms(0, 1, C.byref(ms)) == 0
+            barrier()
+            w1 = time.time()
+            launches = fd.kernel_launch_count() - launches0
+            kms, kn = C.c_double(0.0), C.c_longlong(0)
+            L.dlesm_profile_read(C.byref(kms), C.byref(kn), 1)
+            L.dlesm_profile_enable(0)
+            el = max_over_ranks(ms.value)
+            return dict(elapsed_ms=el, launches=int(launches), kernel_ms_total=kms.value, kernel_launches=kn.value,
+                        clocks=sampler.summary(w0, w1), value=total_points * nsteps / (el * 1e-3), steps=nsteps)
 
-        elapsed_ms = ms.value
-        if dist is not None:
-            t = torch.tensor([elapsed_ms], dtype=torch.float64, device="cuda")
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            elapsed_ms = float(t.item())
-        value = total_points * args.steps / (elapsed_ms * 1e-3)
-
-        # parity guards on the timed state: mass conservation and finite checksums
-        cks = sw.checksums()
-        mass1 = cks[0]
-        assert all(np.isfinite(c) for c in cks), cks
-        assert abs(mass1 - mass0) <= 1e-11 * abs(mass0), (mass0, mass1)
-
-        # ---- roofline of the dominant kernel (fused sweep), timed live with CUDA events ----
-        peak, peak_src = measured_hbm_peak()
-        roofline = None
-        if kn.value > 0:
-            k_ms = kms.value / kn.value
-            steps_per_launch = args.steps / kn.value          # 2 with --two-step (temporal blocking)
-            achieved = BYTES_PER_POINT * local_points * steps_per_launch / (k_ms * 1e-3) / 1e9
-            roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                        "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                        "kernel": ("two-step fused shallow-water sweep (variant2 %d)" % args.variant2) if two_step
-                              else ("fused shallow-water sweep (variant %d)" % args.variant),
-                        "kernel_ms": k_ms, "kernel_share_of_step": kms.value / elapsed_ms,
-                        "algorithmic_bytes_per_launch": BYTES_PER_POINT * local_points * steps_per_launch,
-                        "steps_per_launch": steps_per_launch,
-                        "frac_of_nominal_8TBs": achieved / 8000.0}
-            if two_step:
-                # a two-step launch moves the state through HBM once for two steps: its own DRAM minimum
-                # is 96 B/point per LAUNCH, so `frac` (algorithmic bytes of both steps / time) exceeds 1;
-                # the kernel itself is bound by the FP64 pipe under the power cap, not by HBM
-                roofline["frac_of_hbm_on_kernel_dram_minimum"] = achieved / steps_per_launch / peak
-                roofline["note"] = ("temporal blocking: 2 model steps per launch for one pass over the state "
-                                    "(96 B/point per launch); frac > 1 against the per-step byte model means the "
-                                    "intermediate state never reached HBM; ncu: FP64 pipe is the busiest unit")
-            prof = os.path.join(ROOT, "profiles", "fused_traffic.json")
+        def roofline_of(r):
+            """the dominant kernel (fused sweep) against the measured HBM copy bandwidth.  Bytes per launch =
+            the DRAM minimum of one launch: 96 B x the points it sweeps (6 reads + 6 writes of FP64,
+            SURVEY 8(d)) -- ONE pass over the state whether the launch advances one model step or two."""
+            if r["kernel_launches"] <= 0:
+                return None
+            k_ms = r["kernel_ms_total"] / r["kernel_launches"]
+            spl = r["steps"] / r["kernel_launches"]           # model steps per launch: 2 with temporal blocking
+            bytes_launch = BYTES_PER_POINT * local_points + (local_points if tmask else 0)   # + 1 B/pt byte mask
+            achieved = bytes_launch / (k_ms * 1e-3) / 1e9
+            rf = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                  "traffic": None, "peak_source": peak_src,
+                  "kernel": ("two-step fused shallow-water sweep fused2s_tma_kernel (variant2 %d)" % args.variant2)
+                  if two_step else ("fused shallow-water sweep fused_tma_kernel (variant %d)" % args.variant),
+                  "kernel_ms": k_ms, "kernel_share_of_step": r["kernel_ms_total"] / r["elapsed_ms"],
+                  "algorithmic_bytes_per_launch": bytes_launch, "steps_per_launch": spl,
+                  "frac_of_nominal_8TBs": achieved / 8000.0,
+                  "effective_bytes_speedup": spl,
+                  "effective_GBs_on_the_per_step_byte_model": achieved * spl,
+                  "note": ("temporal blocking: one pass over the state (96 B/point) advances TWO model steps; "
+                           "`frac` is that pass against the measured HBM copy bandwidth, "
+                           "`effective_bytes_speedup` the factor the per-step byte model is beaten by")
+                  if spl > 1.5 else "one pass over the state (96 B/point) per model step"}
             try:
-                with open(prof) as fh:
-                    roofline["traffic"] = json.load(fh).get(
-                        "dram_bytes_per_launch_two_step" if two_step else "dram_bytes_per_launch")
+                with open(os.path.join(ROOT, "profiles", "fused_traffic.json")) as fh:
+                    tj = json.load(fh)
+                key = ("dram_bytes_per_launch_two_step" if two_step else "dram_bytes_per_launch") + ("_masked" if tmask else "")
+                if n == 16384 and world == 1:
+                    rf["traffic"] = tj.get(key)
             except Exception:
                 pass
+            return rf
+
+        sw.step(max(args.warmup, 3))
+        R = region(steps)
+        R["roofline"] = roofline_of(R)
+        # parity guards on the timed state: mass conservation and finite checksums
+        cks = sw.checksums()
+        assert all(np.isfinite(c) for c in cks), cks
+        assert abs(cks[0] - mass0) <= 1e-11 * abs(mass0), (mass0, cks[0])
+        sustained = None
+        if sustain_s > 0:
+            ms_step = R["elapsed_ms"] / steps
+            ns = max(2, int(sustain_s * 1e3 / ms_step))
+            ns += ns & 1
+            S = region(ns)
+            rf = roofline_of(S)
+            sustained = {"value": S["value"], "ms_per_step": S["elapsed_ms"] / ns, "steps": ns,
+                         "seconds": S["elapsed_ms"] * 1e-3, "clocks": S["clocks"],
+                         "roofline_frac": rf["frac"] if rf else None, "kernel_ms": rf["kernel_ms"] if rf else None}
 
         # ---- halo traffic of one step against NVLink (north_star: "halo traffic also as a fraction of
         # NVLink bandwidth"): the map_comms send/recv lists of this rank x the three new fields ----
@@ -311,16 +432,35 @@ def run_ours(args):
                        if cm.destination[q] != rank) * per_step
             recv = sum(cm.nxrecv[q] * cm.nyrecv[q] for q in range(cm.nrecv)
                        if cm.source[q] != rank) * per_step
-            step_s = elapsed_ms * 1e-3 / args.steps
+            step_s = R["elapsed_ms"] * 1e-3 / steps
             halo_traffic = {"sent_bytes_per_rank_per_step": sent, "recv_bytes_per_rank_per_step": recv,
                             "messages_per_rank_per_step": int(cm.nsend),
                             "nvlink_peak_GBs_both_directions": 1800.0,
                             "nvlink_frac_of_step": (sent + recv) / step_s / 1.8e12,
-                            "step_minus_sweep_us": (elapsed_ms - kms.value) / args.steps * 1e3}
+                            "step_minus_sweep_us": (R["elapsed_ms"] - R["kernel_ms_total"]) / steps * 1e3}
 
-        return dict(value=value, elapsed_ms=elapsed_ms, roofline=roofline, clocks=clocks, launches=int(launches),
-                    cks=cks, halo_traffic=halo_traffic, halo=halo, grid=grid, sw=sw, probe=probe, sub=sub, gx=gx,
-                    gy=gy, local_points=local_points, total_points=total_points, two_step=two_step)
+        R.update(cks=cks, halo_traffic=halo_traffic, halo=halo, grid=grid, sw=sw, probe=probe, sub=sub, gx=gx,
+                 gy=gy, local_points=local_points, total_points=total_points, two_step=two_step,
+                 sustained=sustained, n=n, tmask=bool(tmask), arith=(arith or args.arith))
+        return R
+
+    def halo_text(r):
+        if r["two_step"] and r["halo"] == "push":
+            return ("push: the two-step sweep stores the neighbours' halo cells of its six outputs, two cells "
+                    "deep, over NVLink peer memory; flag hand-shake per sweep")
+        if r["two_step"]:
+            return ("periodic halo kernel, two cells deep, every second step" if world == 1 else
+                    "halo_exchange(depth 2) of six fields every second step: pack -> NCCL send/recv -> unpack")
+        if r["halo"] == "push":
+            return ("push: the fused sweep stores the neighbours' halo cells over NVLink peer memory, "
+                    "flag hand-shake per step")
+        return "periodic halo kernel" if world == 1 else "pack -> NCCL send/recv -> unpack"
+
+    def sub_record(r):
+        return {"value": r["value"], "ms_per_step": r["elapsed_ms"] / r["steps"], "steps": r["steps"],
+                "roofline": r["roofline"], "clocks": r["clocks"], "gpu_launches": r["launches"],
+                "halo": halo_text(r), "halo_traffic": r["halo_traffic"], "checksums_p_u_v": list(r["cks"]),
+                "sustained": r["sustained"], "arithmetic": r["arith"]}
 
     sweep = "two" if args.two_step else args.sweep
     if args.mode != "fused":
@@ -344,72 +484,139 @@ def run_ours(args):
         two["sw"].free()
         two["sw"] = None
         main = two
+    # the other arithmetic of the headline sweep, for the record (same process, same box)
+    other = None
+    if args.both_arith and main is not None and args.mode == "fused":
+        other = timed(main["two_step"], arith="exact" if args.arith == "fma" else "fma")
+        other["sw"].free()
+        other["sw"] = None
+
+    # ---- BASELINE configs[2] (N=1): 4096^2, tmask land islands, DL_ESM_ALIGNMENT=64; full-size oracle check ----
+    config3 = None
+    if world == 1 and not args.no_config3 and args.mode == "fused":
+        config3 = run_config3(args, fd, timed, sub_record, np)
+
     sampler.stop_flag = True
 
-    # ---- cpu baseline (rank 0, N=1 only): bounded sample on the box's host cores ----
+    # ---- cpu baseline (rank 0, N=1 only): bounded sample on the box's host cores; its checksums are the
+    # full-size parity check of the GPU path ----
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         ncores = os.cpu_count() or 1
         ncpu = pick_cpu_sample(ncores, 6, 1, budget_s=20.0)
-        cval, csecs, _ = cpu_run(ncpu, ncores, 6, 1)
+        cval, csecs, ccks, ccks_ld = cpu_run(ncpu, ncores, 6, 1)
         cpu = {"value": cval, "unit": UNIT, "cores": ncores, "kind": "port",
                "sample": "%dx%d double-periodic sample, 6 timed steps, %d threads (oracle port of the "
-                         "reference's un-fused loops + exchange_generic-style halo exchange)" % (ncpu, ncpu, ncores)}
-        c1, _, _ = cpu_run(1024, 1, 6, 1)
-        cpu["serial_fd_lib_1core_1024sq"] = c1
+                         "reference's un-fused loops + exchange_generic-style halo exchange)" % (ncpu, ncpu, ncores),
+               "checksums_p_u_v_after_7_steps": list(ccks), "checksums_p_u_v_long_double": list(ccks_ld)}
+        cpu["serial_fd_lib_1core_1024sq"] = cpu_run(1024, 1, 6, 1)[0]
+        # the GPU path from the same initial state, same number of steps (1 warm-up + 6 timed), same size
+        full = {}
+        for label, two_step in (("one_step_sweep", False), ("two_step_sweep", True)):
+            r = timed(two_step, run=False, size=ncpu, tmask=False, scaling="weak", arith="exact")
+            r["sw"].step(7)
+            got = r["sw"].checksums()
+            r["sw"].free()
+            rel = [abs(a - b) / abs(b) for a, b in zip(got, ccks_ld)]
+            full[label] = {"checksums_p_u_v": list(got), "max_rel_diff_vs_cpu_long_double": max(rel)}
+            if max(rel) > 1e-12:
+                parity["mismatches"] = (parity.get("mismatches") or 0) + 1
+        parity["full_size"] = {"size": ncpu, "steps": 7, "tolerance": 1e-12,
+                               "what": "GPU checksums (p, u, v) after 7 steps from the classic initial state vs the "
+                                       "CPU arm's (long-double accumulation of the same sums) at %dx%d" % (ncpu, ncpu),
+                               **full}
 
+    rc = 0
     if rank == 0:
-        peak, _ = measured_hbm_peak()
         R = main
         sub, probe, grid = R["sub"], R["probe"], R["grid"]
-
-        def halo_text(r):
-            if r["two_step"] and r["halo"] == "push":
-                return ("push: the two-step sweep stores the neighbours' halo cells of its six outputs, two cells "
-                        "deep, over NVLink peer memory; flag hand-shake per sweep")
-            if r["two_step"]:
-                return ("periodic halo kernel, two cells deep, every second step" if world == 1 else
-                        "halo_exchange(depth 2) of six fields every second step: pack -> NCCL send/recv -> unpack")
-            if r["halo"] == "push":
-                return ("push: the fused sweep stores the neighbours' halo cells over NVLink peer memory, "
-                        "flag hand-shake per step")
-            return "periodic halo kernel" if world == 1 else "pack -> NCCL send/recv -> unpack"
-
         line = {
             "metric": METRIC, "value": R["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": R["elapsed_ms"] / args.steps, "higher_is_better": True,
             "scaling": args.scaling, "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": "shallow-water C-grid step %dx%d per GPU (global %dx%d, tiles %dx%d), "
-                                   "double periodic, GO_OFFSET_SW, FP64, DL_ESM_ALIGNMENT=%d, mode=%s%s"
-                                   % (sub.internal.nx, sub.internal.ny, R["gx"], R["gy"], probe.nx, probe.ny,
-                                      args.alignment, args.mode,
+            "config": {"workload": WORKLOAD % (args.size, args.size, args.alignment) if args.scaling == "weak" and
+                                   args.mode == "fused" and not args.tmask else
+                                   "shallow-water C-grid step %dx%d per GPU (%s scaling), double periodic, GO_OFFSET_SW, "
+                                   "FP64, DL_ESM_ALIGNMENT=%d, mode=%s%s"
+                                   % (sub.internal.nx, sub.internal.ny, args.scaling, args.alignment, args.mode,
                                       ", tmask with 64x64 land islands (1.6 % land)" if args.tmask else ""),
+                       "tile": "%dx%d per GPU, global %dx%d, tiles %dx%d" % (sub.internal.nx, sub.internal.ny, R["gx"],
+                                                                          R["gy"], probe.nx, probe.ny),
                        "l2": "inputs larger than L2 (%d fields x %.2f GB per GPU)"
                              % (12 if R["two_step"] else 9, grid.nx * grid.ny * 8 / 1e9),
                        "fused_variant": args.variant,
+                       "arithmetic": "contracted (FMA; within 1e-12 of the oracle)" if R["arith"] == "fma" else
+                                     "exact (one rounding per operation; bit-identical to the oracle)",
                        "sweep": ("two model steps per sweep (temporal blocking, halo width 2, variant2 %d): the "
-                                 "intermediate state never reaches HBM; bit-identical to stepping one at a time"
-                                 % args.variant2) if R["two_step"] else "one model step per sweep",
+                                 "intermediate state never reaches HBM" % args.variant2)
+                                if R["two_step"] else "one model step per sweep",
                        "parallelism": "tile-per-GPU %dx%d" % (probe.nx, probe.ny),
                        "halo": halo_text(R)},
             "clocks": R["clocks"], "gpu_launches": R["launches"], "roofline": R["roofline"], "cpu_baseline": cpu,
             "e2e": e2e, "halo_traffic": R["halo_traffic"], "checksums_p_u_v": list(R["cks"]),
-            "hbm_frac_of_measured_whole_step": (BYTES_PER_POINT * R["local_points"] * args.steps /
-                                                (R["elapsed_ms"] * 1e-3) / 1e9) / peak,
+            "sustained": R["sustained"], "parity": parity,
         }
         if R["two_step"] and one is not None:
             # the one-step formulation (the reference's: every step reads and writes the state once),
             # measured in the same process just before
-            line["one_step"] = {"value": one["value"], "ms_per_step": one["elapsed_ms"] / args.steps,
-                                "roofline": one["roofline"], "clocks": one["clocks"],
-                                "gpu_launches": one["launches"], "halo": halo_text(one),
-                                "halo_traffic": one["halo_traffic"], "checksums_p_u_v": list(one["cks"])}
+            line["one_step"] = sub_record(one)
+        if other is not None:
+            line["other_arithmetic"] = sub_record(other)
+        if config3 is not None:
+            line["config3"] = config3
         print(json.dumps(line), flush=True)
+        if parity.get("mismatches"):
+            print("PARITY MISMATCH at full size: see parity.full_size / config3.parity", file=sys.stderr, flush=True)
+            rc = 1
     if dist is not None:
         dist.barrier()
         fd.gocean_finalise()
         dist.destroy_process_group()
-    return 0
+    return rc
+
+
+def run_config3(args, fd, timed, sub_record, np):
+    """BASELINE configs[2]: "shallow-water step 4096^2 with tmask land points and DL_ESM_ALIGNMENT=64
+    padding" -- both sweeps timed like the headline, and every prognostic field after 5 steps compared
+    bit for bit with the serial oracle at full size."""
+    from oracle import oracle as O
+    n, out = 4096, {}
+    for label, two_step in (("one_step", False), ("two_step", True)):
+        r = timed(two_step, size=n, tmask=True, scaling="weak", steps=max(args.steps, 20),
+                  sustain_s=min(args.sustain_s, 1.0))
+        r["sw"].free()
+        r["sw"] = None
+        out[label] = sub_record(r)
+    # oracle comparison at full size (outside any timed region)
+    t0 = time.time()
+    i = np.arange(1, n + 1)[:, None]
+    j = np.arange(1, n + 1)[None, :]
+    land = ((i % 512 >= 200) & (i % 512 <= 263)) & ((j % 512 >= 300) & (j % 512 <= 363))
+    gmask = np.where(land, 0, 1).astype(np.int32)
+    osw = O.ShallowWater(n, n, alignment=args.alignment, tmask=np.asfortranarray(np.pad(gmask, 1, mode="wrap")))
+    for _ in range(5):
+        osw.step()
+    oi = osw.fb["t"].internal
+    osl = (slice(oi.xstart - 1, oi.xstop), slice(oi.ystart - 1, oi.ystop))
+    par = {"size": n, "steps": 5, "fields": 6, "mismatches": 0, "what": "u,v,p,uold,vold,pold after 5 steps vs the "
+           "serial oracle, bit for bit, 4096x4096 with the config-3 tmask"}
+    for label, two_step in (("one_step", False), ("two_step", True)):
+        r = timed(two_step, run=False, size=n, tmask=True, scaling="weak", arith="exact")
+        sw = r["sw"]
+        sw.step(5)
+        ii = sw.field("p").internal
+        gsl = (slice(ii.xstart - 1, ii.xstop), slice(ii.ystart - 1, ii.ystop))
+        bad = 0
+        for name in ("u", "v", "p", "uold", "vold", "pold"):
+            if not np.array_equal(sw.field(name).get_data()[gsl], osw.f[name][osl]):
+                bad += 1
+        par[label + "_fields_differing"] = bad
+        par["mismatches"] += bad
+        sw.free()
+    par["seconds"] = time.time() - t0
+    out["parity"] = par
+    out["workload"] = "shallow-water C-grid step 4096x4096, tmask with 64x64 land islands (1.6 % land), DL_ESM_ALIGNMENT=64"
+    return out
 
 
 def run_e2e(args, fd, L, sw, grid, total_points, dist, torch):
@@ -547,6 +754,14 @@ def main():
                     help="two model steps per sweep (temporal blocking; tile decomposed with halo_width=2)")
     ap.add_argument("--variant2", type=int, default=0, help="kernel variant of the two-step sweep")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="skip the pre-flight parity leg (profiling runs)")
+    ap.add_argument("--no-config3", action="store_true", help="skip the config-3 (4096^2 + tmask) sub-record")
+    ap.add_argument("--sustain-s", type=float, default=3.0,
+                    help="seconds of back-to-back steps of the sustained leg (0 = none)")
+    ap.add_argument("--arith", choices=["exact", "fma"], default="exact",
+                    help="arithmetic of the fused sweeps: exact = one rounding per operation (bit-identical to the "
+                         "oracle), fma = contracted (within 1e-12)")
+    ap.add_argument("--both-arith", action="store_true", help="also time the headline sweep with the other arithmetic")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference_arm(args)
