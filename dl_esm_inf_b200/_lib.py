@@ -174,6 +174,7 @@ SIGNATURES = {
     "dlesm_sw_set_state": (_I, [_V, _PD, _PD, _PD]),
     "dlesm_sw_step": (_I, [_V, _I]),
     "dlesm_sw_step_host": (_I, [_V, C.POINTER(_PD), C.POINTER(_PD), _I]),
+    "dlesm_sw_step_host_n": (_I, [_V, C.POINTER(_PD), C.POINTER(_PD), _I, _I]),
     "dlesm_sw_field": (_V, [_V, _I]),
     "dlesm_sw_set_variant": (_I, [_V, _I]),
     "dlesm_sw_set_halo_mode": (_I, [_V, _I]),

@@ -471,10 +471,12 @@ class shallow_water:
     def step(self, nsteps=1):
         _chk(_lib.lib().dlesm_sw_step(self._h, nsteps))
 
-    def step_host(self, host_in, host_out=None, band_rows=0):
-        """One step with HOST state: host_in = (u, v, p, uold, vold, pold) Fortran-ordered
-        (nx, ny) float64 arrays (or raw addresses of such buffers); results land in host_out
-        (default: in place).  Upload, sweep and download are pipelined in row bands."""
+    def step_host(self, host_in, host_out=None, band_rows=0, nsteps=1):
+        """nsteps (1 or 2) model steps with HOST state: host_in = (u, v, p, uold, vold, pold)
+        Fortran-ordered (nx, ny) float64 arrays (or raw addresses of such buffers); results land in
+        host_out (default: in place).  Upload, sweep and download are pipelined in row bands;
+        nsteps=2 sends the bands through the two-step sweep (set_two_step), halving the PCIe
+        bytes per model step."""
         if host_out is None:
             host_out = host_in
         PD = C.POINTER(C.c_double)
@@ -487,7 +489,7 @@ class shallow_water:
 
         ins = (PD * 6)(*[ptr(a) for a in host_in])
         outs = (PD * 6)(*[ptr(a) for a in host_out])
-        _chk(_lib.lib().dlesm_sw_step_host(self._h, ins, outs, int(band_rows)))
+        _chk(_lib.lib().dlesm_sw_step_host_n(self._h, ins, outs, int(band_rows), int(nsteps)))
 
     def checksums(self):
         return tuple(field_checksum(self.field(n)) for n in ("p", "u", "v"))

@@ -2662,6 +2662,126 @@ extern "C" int dlesm_sw_step_host(dlesm_sw_t *s, const double *const host_in[6],
     return DLESM_OK;
 }
 
+// Two model steps per PCIe round trip: the bands go through the two-step sweep (temporal blocking,
+// tile with two halo cells), so each row of each field crosses the bus once per direction for
+// TWO steps -- half the bytes per model step of dlesm_sw_step_host.  nsteps = 1 is that call.
+// Needs dlesm_sw_set_two_step(on), the exchange halo mode and a model past its first step (the
+// forward start-up step has no two-step form); host arrays carry the two-cell halo ring in and out.
+extern "C" int dlesm_sw_step_host_n(dlesm_sw_t *s, const double *const host_in[6], double *const host_out[6],
+                                    int band_rows, int nsteps)
+{
+    if (nsteps == 1) return dlesm_sw_step_host(s, host_in, host_out, band_rows);
+    clear_error();
+    if (!s || nsteps != 2 || !s->two_step || s->push || s->ncycle == 0) {
+        set_error(DLESM_ERR_ARGS, "sw_step_host_n: nsteps is 1 or 2; 2 needs set_two_step(on), the exchange halo mode "
+                                  "and a model past its first step");
+        return DLESM_ERR_ARGS;
+    }
+    int rc = ensure_device();
+    if (rc != DLESM_OK) return rc;
+    Context &c = ctx();
+    dlesm_grid &g = *s->grid;
+    dlesm_field **f = s->f;
+    const dlesm_region &rt = f[DLESM_SW_P]->fb.internal;
+    const int nx = f[0]->nx, ny = f[0]->ny;
+    const size_t row_bytes = static_cast<size_t>(nx) * sizeof(double);
+    if (band_rows <= 0) band_rows = std::max(64, ((rt.ny / 128) + 31) / 32 * 32);
+    const int nbands = (rt.ny + band_rows - 1) / band_rows;
+    while (c.band_events.size() < static_cast<size_t>(2 * nbands + 2)) {
+        cudaEvent_t e;
+        CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        c.band_events.push_back(e);
+    }
+    cudaEvent_t e_start = c.band_events[2 * nbands];
+    CU(cudaEventRecord(e_start, c.stream));
+    CU(cudaStreamWaitEvent(c.s_h2d, e_start, 0));
+    CU(cudaStreamWaitEvent(c.s_d2h, e_start, 0));
+    dlesm_field *in_f[6], *out_f[6];
+    for (int q = 0; q < 6; ++q) in_f[q] = f[DLESM_SW_U + q];                    // u,v,p,uold,vold,pold
+    for (int q = 0; q < 3; ++q) { out_f[q] = f[DLESM_SW_UNEW + q]; out_f[3 + q] = s->old2[q]; }
+    int up_next = 1;
+    for (int b = 0; b < nbands; ++b) {
+        const int j0 = rt.ystart + b * band_rows;
+        const int j1 = std::min(rt.ystop, j0 + band_rows - 1);
+        // rows the two-step sweep of [j0, j1] reads: j0-2 .. j1+2 of u,v,p; j0-1 .. j1+1 of the old fields
+        const int up_to = (b == nbands - 1) ? ny : std::min(ny, j1 + 2);
+        if (up_to >= up_next) {
+            const size_t off = static_cast<size_t>(up_next - 1) * nx;
+            const size_t bytes = static_cast<size_t>(up_to - up_next + 1) * row_bytes;
+            for (int q = 0; q < 6; ++q)
+                CU(cudaMemcpyAsync(static_cast<double *>(in_f[q]->dptr) + off, host_in[q] + off, bytes,
+                                   cudaMemcpyHostToDevice, c.s_h2d));
+            up_next = up_to + 1;
+        }
+        cudaEvent_t e_up = c.band_events[2 * b], e_done = c.band_events[2 * b + 1];
+        CU(cudaEventRecord(e_up, c.s_h2d));
+        CU(cudaStreamWaitEvent(c.stream, e_up, 0));
+        rc = sw_step2_fused_impl(in_f[0]->dptr, in_f[1]->dptr, in_f[2]->dptr, in_f[3]->dptr, in_f[4]->dptr,
+                                 in_f[5]->dptr, out_f[0]->dptr, out_f[1]->dptr, out_f[2]->dptr, out_f[3]->dptr,
+                                 out_f[4]->dptr, out_f[5]->dptr, g.info.dx, g.info.dy, s->tdt, s->alpha, rt.xstart,
+                                 rt.xstop, j0, j1, s->mask2, s->mask2_pitch, s->variant2, nullptr);
+        if (rc != DLESM_OK) return rc;
+        CU(cudaEventRecord(e_done, c.stream));
+        CU(cudaStreamWaitEvent(c.s_d2h, e_done, 0));
+        const size_t off = static_cast<size_t>(j0 - 1) * nx;
+        const size_t bytes = static_cast<size_t>(j1 - j0 + 1) * row_bytes;
+        for (int q = 0; q < 6; ++q)
+            CU(cudaMemcpyAsync(host_out[q] + off, static_cast<const double *>(out_f[q]->dptr) + off, bytes,
+                               cudaMemcpyDeviceToHost, c.s_d2h));
+    }
+    for (int q = 0; q < 3; ++q) {
+        std::swap(f[DLESM_SW_U + q]->dptr, f[DLESM_SW_UNEW + q]->dptr);
+        std::swap(f[DLESM_SW_UOLD + q]->dptr, s->old2[q]->dptr);
+    }
+    rc = sw_fill_deep_halos(s);            // two-cell ring of all six fields (wrapped copies / depth-2 exchange)
+    if (rc != DLESM_OK) return rc;
+    s->deep_valid = true;
+    s->ncycle += 2;
+    // ring -> host: 2 + 2 halo rows are contiguous; the 2 + 2 halo columns are gathered on the
+    // device, shipped as one block and scattered by the host
+    const size_t col_n = 2 * static_cast<size_t>(ny);
+    rc = ensure_scratch(12 * col_n);
+    if (rc != DLESM_OK) return rc;
+    if (c.ring_host_n < 12 * col_n) {
+        if (c.ring_host) cudaFreeHost(c.ring_host);
+        c.ring_host = nullptr;
+        c.ring_host_n = 0;
+        CU(cudaMallocHost(&c.ring_host, 12 * col_n * sizeof(double)));
+        c.ring_host_n = 12 * col_n;
+    }
+    const int xw = rt.xstart - 2, xe = rt.xstop + 1;      // first column of the west / east halo pair
+    for (int q = 0; q < 6; ++q) {
+        const double *d = static_cast<const double *>(f[DLESM_SW_U + q]->dptr);
+        CU(k::gather_box(d, nx, k::Box{xw, xw + 1, 1, ny}, c.scratch + (2 * q) * col_n, c.stream));
+        CU(k::gather_box(d, nx, k::Box{xe, xe + 1, 1, ny}, c.scratch + (2 * q + 1) * col_n, c.stream));
+    }
+    CU(cudaMemcpyAsync(c.ring_host, c.scratch, 12 * col_n * sizeof(double), cudaMemcpyDeviceToHost, c.stream));
+    cudaEvent_t e_dl = c.band_events[2 * nbands + 1];
+    CU(cudaEventRecord(e_dl, c.s_d2h));
+    CU(cudaStreamWaitEvent(c.stream, e_dl, 0));
+    for (int q = 0; q < 6; ++q) {
+        const double *d = static_cast<const double *>(f[DLESM_SW_U + q]->dptr);
+        const int rows[2] = {rt.ystart - 2, rt.ystop + 1};
+        for (int r : rows) {
+            const size_t off = static_cast<size_t>(r - 1) * nx;
+            CU(cudaMemcpyAsync(host_out[q] + off, d + off, 2 * row_bytes, cudaMemcpyDeviceToHost, c.stream));
+        }
+    }
+    CU(cudaStreamSynchronize(c.stream));
+    for (int q = 0; q < 6; ++q) {
+        double *h = host_out[q];
+        const double *w = c.ring_host + (2 * q) * col_n, *e = c.ring_host + (2 * q + 1) * col_n;
+        for (int j = rt.ystart - 2; j <= rt.ystop + 2; ++j) {
+            double *row = h + static_cast<size_t>(j - 1) * nx;
+            row[xw - 1] = w[2 * (j - 1)];
+            row[xw] = w[2 * (j - 1) + 1];
+            row[xe - 1] = e[2 * (j - 1)];
+            row[xe] = e[2 * (j - 1) + 1];
+        }
+    }
+    return DLESM_OK;
+}
+
 extern "C" dlesm_field_t *dlesm_sw_field(dlesm_sw_t *s, int which)
 {
     if (which < 0 || which >= DLESM_SW_NFIELDS) return nullptr;

@@ -508,6 +508,12 @@ int dlesm_sw_step(dlesm_sw_t *s, int nsteps);
  * band_rows <= 0 selects the default.  Fused mode only. */
 int dlesm_sw_step_host(dlesm_sw_t *s, const double *const host_in[6], double *const host_out[6],
                        int band_rows);
+/* nsteps model steps per PCIe round trip.  nsteps = 1 is dlesm_sw_step_host.  nsteps = 2 streams the
+ * bands through the two-step sweep (dlesm_sw_set_two_step(on), tile decomposed with halo_width 2,
+ * exchange halo mode, model past its first step): each row crosses the bus once per direction for
+ * two steps.  Host arrays carry a valid two-cell halo ring of all six fields in, and get it back. */
+int dlesm_sw_step_host_n(dlesm_sw_t *s, const double *const host_in[6], double *const host_out[6],
+                         int band_rows, int nsteps);
 dlesm_field_t *dlesm_sw_field(dlesm_sw_t *s, int which);
 int dlesm_sw_set_variant(dlesm_sw_t *s, int variant);
 /* How the halos of unew, vnew, pnew get filled after the fused sweep:

@@ -745,6 +745,52 @@ def test_two_step_sweep_matches_oracle(variant2, n_x, n_y, align, nsteps, monkey
         _lib.lib().dlesm_reset_saved_state()
 
 
+@pytest.mark.parametrize("n_x,n_y,align,band_rows,masked", [
+    (64, 64, 2, 0, False), (130, 77, 64, 10, False), (300, 523, 64, 97, True), (1024, 1024, 64, 0, False),
+    (96, 40, 64, 1000, False)])
+@pytest.mark.parametrize("in_place", [True, False])
+def test_step_host_two_steps_per_round_trip_matches_oracle(n_x, n_y, align, band_rows, masked, in_place,
+                                                          monkeypatch):
+    """dlesm_sw_step_host_n(nsteps=2): the bands go through the two-step sweep, each row crosses the
+    bus once per direction for two model steps; host results (internal points and the two-cell halo
+    ring) and the device state == the oracle stepping one step at a time, bit for bit"""
+    try:
+        tm = periodic_island_mask(n_x + 2, n_y + 2, 12345) if masked else None
+        osw, sw = sw_pair_hw2(n_x, n_y, align, monkeypatch, tmask=tm)
+        sw.set_two_step(True)
+        names = ("u", "v", "p", "uold", "vold", "pold")
+        with pytest.raises(fd.GoceanStop):          # the forward start-up step has no two-step form
+            sw.step_host([sw.field(n).get_data() for n in names], nsteps=2)
+        osw.step()
+        sw.step(1)
+        host = [sw.field(n).get_data() for n in names]
+        oi, ii = osw.fb["t"].internal, sw.field("p").internal
+        core = (slice(oi.xstart - 1, oi.xstop), slice(oi.ystart - 1, oi.ystop))
+        ring2 = (slice(ii.xstart - 3, ii.xstop + 2), slice(ii.ystart - 3, ii.ystop + 2))
+        # the old fields' ring must be valid on the way in (two-step reads them one cell out)
+        for q in (3, 4, 5):
+            host[q][ring2] = np.pad(osw.f[names[q]][core], 2, mode="wrap")
+        for trip in range(3):
+            osw.step(); osw.step()
+            if in_place:
+                sw.step_host(host, band_rows=band_rows, nsteps=2)
+            else:
+                out = [np.full_like(a, np.nan) for a in host]
+                sw.step_host(host, out, band_rows=band_rows, nsteps=2)
+                for n, a, o in zip(names, host, out):
+                    assert not np.isnan(o[ring2]).any(), n
+                    a[ring2] = o[ring2]
+            for n, a in zip(names, host):
+                assert np.array_equal(a[ring2], np.pad(osw.f[n][core], 2, mode="wrap")), (n, trip)
+        assert_internal_equal(osw, sw, halo=1)
+        osw.step(); osw.step(); osw.step()
+        sw.step(3)                                   # a device-resident run continues from it
+        assert_internal_equal(osw, sw, halo=1)
+        sw.free()
+    finally:
+        _lib.lib().dlesm_reset_saved_state()
+
+
 @pytest.mark.parametrize("order", ["two_step_first", "push_first"])
 @pytest.mark.parametrize("n_x,n_y,align,nsteps", [(64, 64, 2, 7), (130, 77, 64, 6), (300, 523, 64, 8),
                                                   (1024, 1024, 64, 9)])
