@@ -153,6 +153,7 @@ SIGNATURES = {
     "dlesm_dev_periodic_halos": (_I, [_V, _I, _I, _I, _I, _I, _I]),
     "dlesm_dev_set_comms": (_I, [C.POINTER(Comms)]),
     "dlesm_dev_halo_exchange": (_I, [C.POINTER(_V), _I]),
+    "dlesm_host_halo_exchange": (_I, [_PD, _I, _I]),
     "dlesm_dev_peer_register": (_I, [C.POINTER(_V), _I]),
     "dlesm_dev_peer_unregister": (_I, [C.POINTER(_V), _I]),
     "dlesm_dev_peer_unregister_all": (_I, []),

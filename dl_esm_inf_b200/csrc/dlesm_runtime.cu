@@ -896,6 +896,52 @@ extern "C" int dlesm_dev_halo_exchange(void *const *fields, int nfields)
     return exchange_with(fields, nfields, ctx().installed);
 }
 
+// fld%halo_exchange(depth) of a field whose values live in HOST memory (data_on_device false) in a
+// build whose parallel_utils_mod has no MPI (src/field_mod.f90:1231-1256 would end in post_receive):
+// the send patches of the installed tables go up to a staging array of the same shape, the device
+// exchange runs, the receive patches come back.  Only the patches cross the bus.
+extern "C" int dlesm_host_halo_exchange(double *host, int nx, int ny)
+{
+    clear_error();
+    Context &c = ctx();
+    const CommTables &ct = c.installed;
+    if (!ct.valid || (ct.t.nsend == 0 && ct.t.nrecv == 0)) return DLESM_OK;   // one rank: a no-op, as in the reference
+    if (!host || nx < 1 || ny < 1) {
+        set_error(DLESM_ERR_ARGS, "host_halo_exchange: null array or empty shape");
+        return DLESM_ERR_ARGS;
+    }
+    int rc = ensure_device();
+    if (rc != DLESM_OK) return rc;
+    static void *stage = nullptr;          // one staging array, re-used while the shape stays
+    static int stage_nx = 0, stage_ny = 0;
+    if (stage && (stage_nx != nx || stage_ny != ny)) {
+        rc = dlesm_dev_field_free(stage);
+        stage = nullptr;
+        if (rc != DLESM_OK) return rc;
+    }
+    if (!stage) {
+        rc = dlesm_dev_field_alloc(nx, ny, &stage);
+        if (rc != DLESM_OK) return rc;
+        stage_nx = nx; stage_ny = ny;
+    }
+    const dlesm_comms &t = ct.t;
+    for (int q = 0; q < t.nsend; ++q)
+        if (t.nxsend[q] > 0 && t.nysend[q] > 0) {
+            rc = hook_copy(stage, host, true, t.isrcsend[q], t.jsrcsend[q], t.nxsend[q], t.nysend[q], false);
+            if (rc != DLESM_OK) return rc;
+        }
+    void *ptrs[1] = {stage};
+    rc = exchange_with(ptrs, 1, ct);
+    if (rc != DLESM_OK) return rc;
+    for (int q = 0; q < t.nrecv; ++q)
+        if (t.nxrecv[q] > 0 && t.nyrecv[q] > 0) {
+            rc = hook_copy(stage, host, false, t.idesrecv[q], t.jdesrecv[q], t.nxrecv[q], t.nyrecv[q], false);
+            if (rc != DLESM_OK) return rc;
+        }
+    CU(cudaStreamSynchronize(c.stream));
+    return DLESM_OK;
+}
+
 // ---------------------------------------------------------------------------------------
 // Halo push set-up.  Collective over all ranks; every rank passes its fields in the same order.
 // Each field's allocation is exported with cudaIpcGetMemHandle, the handles travel through one

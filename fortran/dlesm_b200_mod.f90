@@ -167,6 +167,19 @@ module dlesm_b200_mod
        integer(c_int), value :: nfields
        integer(c_int) :: ierr
      end function
+     ! fld%halo_exchange of a host-resident field: patches up, device exchange, patches back
+     function dlesm_host_halo_exchange(host, nx, ny) bind(C, name="dlesm_host_halo_exchange") result(ierr)
+       import :: c_int, c_ptr
+       type(c_ptr), value :: host
+       integer(c_int), value :: nx, ny
+       integer(c_int) :: ierr
+     end function
+     ! do_tile + GOCEAN_OMP_GRID="AxB" (src/field_mod.f90:300-325) -> block grid of the device sweeps
+     function dlesm_dev_set_sweep_tiles(ntilex, ntiley) bind(C, name="dlesm_dev_set_sweep_tiles") result(ierr)
+       import :: c_int
+       integer(c_int), value :: ntilex, ntiley
+       integer(c_int) :: ierr
+     end function
 
      ! ---- grid upload (fills the 17 *_device slots of src/grid_mod.f90:104-150)
      function dlesm_dev_grid_upload(nx, ny, tmask, metrics, device_ptrs) &
@@ -308,23 +321,25 @@ module dlesm_b200_mod
 
 contains
 
-  !> Turn a non-zero status into the reference's only error path, gocean_stop
-  !! (src/gocean_mod.F90:50-57), with the library's message.
+  !> Turn a non-zero status into the reference's only error path: gocean_stop
+  !! (src/gocean_mod.F90:50-57) is parallel_abort(msg), and in a B200 build parallel_abort is
+  !! dlesm_parallel_abort (fortran/parallel_utils_nccl_mod.f90).  Called directly: this module
+  !! must not `use gocean_mod` (gocean_mod -> parallel_mod -> parallel_utils_mod -> this module).
   subroutine dlesm_check(ierr, where)
-    use gocean_mod, only: gocean_stop
     integer(c_int), intent(in) :: ierr
     character(len=*), intent(in) :: where
     character(kind=c_char), dimension(:), pointer :: cmsg
-    character(len=256) :: msg
-    integer :: i
+    character(len=320) :: msg
+    integer :: i, n
     if (ierr == DLESM_OK) return
-    msg = ' '
+    msg = where//': '
+    n = len_trim(msg) + 1
     call c_f_pointer(dlesm_last_error(), cmsg, (/ 256 /))
     do i = 1, 256
-       if (cmsg(i) == c_null_char) exit
-       msg(i:i) = cmsg(i)
+       if (cmsg(i) == c_null_char .or. n + i > len(msg) - 1) exit
+       msg(n+i:n+i) = cmsg(i)
     end do
-    call gocean_stop(where//': '//trim(msg))
+    call dlesm_parallel_abort(trim(msg)//c_null_char)
   end subroutine dlesm_check
 
 end module dlesm_b200_mod

@@ -7,7 +7,7 @@
 module shallow_psy_mod
   use iso_c_binding
   use kind_params_mod, only: go_wp
-  use field_mod, only: r2d_field
+  use field_mod, only: r2d_field, copy_field
   use parallel_utils_mod, only: get_num_ranks
   use field_device_mod
   use dlesm_b200_mod
@@ -105,7 +105,7 @@ contains
        call dlesm_check(dlesm_time_smooth(p%device_ptr, pnew%device_ptr, pold%device_ptr, real(alpha, c_double), &
             b(p,1), b(p,2), b(p,3), b(p,4), tm, 2_c_int), 'smooth p')     ! GO_T_POINTS
     end if
-    call dev_copy_field(unew, u);  call dev_copy_field(vnew, v);  call dev_copy_field(pnew, p)
+    call copy_field(unew, u);  call copy_field(vnew, v);  call copy_field(pnew, p)   ! device-resident: one D2D pass each
   end subroutine sw_step_unfused
 
   !> internal-region bound k of a field as c_int (1 xstart, 2 xstop, 3 ystart, 4 ystop)
@@ -133,7 +133,7 @@ contains
   subroutine fill_halos_1(f)
     type(r2d_field), intent(inout) :: f
     if (get_num_ranks() > 1) then
-       call dev_halo_exchange(f)
+       call f%halo_exchange(1)
     else
        call dev_periodic_halos(f)
     end if

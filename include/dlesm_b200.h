@@ -383,6 +383,10 @@ int dlesm_dev_set_comms(const dlesm_comms *tables);
 /* exchange_generic (src/parallel_comms_mod.f90:1501-1855) on device-resident fields: fused
  * pack kernel -> grouped NCCL send/recv (self-neighbours: on-device) -> fused unpack kernel */
 int dlesm_dev_halo_exchange(void *const *fields, int nfields);
+/* fld%halo_exchange(depth) (src/field_mod.f90:1231-1256) for a field whose values are in HOST memory
+ * (data_on_device false): send patches up to a staging array, device exchange, receive patches back.
+ * host = fld%data (nx*ny, column-major).  A no-op on one rank, like the reference. */
+int dlesm_host_halo_exchange(double *host, int nx, int ny);
 /* Upload grid arrays once (grid_mod would call this at the end of grid_init): tmask int32
  * (nx,ny) and 16 FP64 metric arrays in the DLESM_GRID_* order (NULL entries are skipped);
  * device_ptrs[17] receives the 17 *_device values of src/grid_mod.f90:104-150. */

@@ -115,3 +115,50 @@ def test_periodic_with_several_ranks_is_refused_like_the_reference():
     finally:
         fd.set_extensions(0)
         fd.gocean_initialise(1, 1)
+
+
+def test_fortran_bindings_name_only_exported_symbols():
+    """every bind(C, name=...) of fortran/*.f90 is an entry point the shared library exports (no Fortran
+    compiler here: this is the link-time check a build would make)"""
+    import glob
+    import re
+    L = _lib.lib()
+    names = set()
+    for path in glob.glob(os.path.join(ROOT, "fortran", "*.f90")):
+        names |= set(re.findall(r'name="(dlesm_\w+)"', open(path).read()))
+    assert len(names) >= 40
+    missing = [n for n in sorted(names) if not hasattr(L, n)]
+    assert not missing, missing
+
+
+def test_field_mod_and_grid_mod_patches_apply_to_the_reference(tmp_path):
+    """fortran/patches/*.patch turn the reference's field_mod / grid_mod into the B200 build (public
+    generics dispatching on data_on_device).  Where the reference tree is present (the build container)
+    they must apply cleanly; every dlesm_* name they call must be declared in dlesm_b200_mod.f90."""
+    import re
+    import shutil
+    import subprocess
+    mod = open(os.path.join(ROOT, "fortran", "dlesm_b200_mod.f90")).read()
+    declared = set(re.findall(r'name="(dlesm_\w+)"', mod)) | {"dlesm_check", "dlesm_comms"}
+    for name in ("field_mod", "grid_mod"):
+        patch = os.path.join(ROOT, "fortran", "patches", name + ".f90.patch")
+        added = [l[1:] for l in open(patch) if l.startswith("+") and not l.startswith("+++")]
+        called = set(re.findall(r"\b(dlesm_\w+)", " ".join(a.split("!")[0] for a in added)))
+        assert called and called <= declared | {"dlesm_b200_mod"}, called - declared
+    ref = "/root/reference/finite_difference/src"
+    if not os.path.isdir(ref):
+        pytest.skip("reference tree not present on this box")
+    work = tmp_path / "finite_difference" / "src"
+    work.mkdir(parents=True)
+    for name in ("field_mod", "grid_mod"):
+        shutil.copy(os.path.join(ref, name + ".f90"), work / (name + ".f90"))
+        patch = os.path.join(ROOT, "fortran", "patches", name + ".f90.patch")
+        p = subprocess.run(["patch", "-p1", "-d", str(tmp_path), "-i", patch], capture_output=True, text=True)
+        assert p.returncode == 0, p.stdout + p.stderr
+        out = (work / (name + ".f90")).read_text()
+        assert "use dlesm_b200_mod" in out
+    fm = (work / "field_mod.f90").read_text()
+    # fld%halo_exchange no longer reaches exchange_generic (-> post_receive, which the NCCL variant of
+    # parallel_utils_mod does not have)
+    body = fm[fm.index("subroutine halo_exchange(self, depth)"):fm.index("end subroutine halo_exchange")]
+    assert "call exchange_generic" not in body and "dlesm_dev_halo_exchange" in body and "dlesm_host_halo_exchange" in body
