@@ -657,7 +657,7 @@ def run_e2e(args, fd, L, sw, grid, total_points, dist, torch, per_trip=1):
     nx, ny = grid.nx, grid.ny
     nbytes = nx * ny * 8
     if per_trip == 2:
-        sw.step(2)                                    # past the forward start-up step; deep halos valid
+        sw.step(3)                # the forward start-up step, then one pair: two-cell halos of all six fields valid
     flds = [sw.field(nm) for nm in names]
     host = []
     for f in flds:

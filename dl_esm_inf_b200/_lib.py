@@ -188,6 +188,17 @@ SIGNATURES = {
     "dlesm_sw_free": (None, [_V]),
     "dlesm_sw_free_local": (None, [_V]),
     "dlesm_sw_launch_grid": (_I, [_V, _I, _PI]),
+    "dlesm_tileset_create": (_V, [_I, _PI, _I, _I, _I, _I, _I, _I, _I]),
+    "dlesm_tileset_ntiles": (_I, [_V]),
+    "dlesm_tileset_grid": (_V, [_V, _I]),
+    "dlesm_tileset_tile_id": (_I, [_V, _I]),
+    "dlesm_tileset_decomp": (_V, [_V]),
+    "dlesm_tileset_free": (None, [_V]),
+    "dlesm_tileset_plan": (_I, [_V, _I, _I, _I, _I, _I, C.POINTER(C.c_longlong), _I, _PI, C.POINTER(C.c_longlong)]),
+    "dlesm_tileset_halo_exchange": (_I, [_V, C.POINTER(_V), _I, _I]),
+    "dlesm_tileset_gather_inner_data": (_I, [_V, C.POINTER(_V), _PD]),
+    "dlesm_tileset_sw_step": (_I, [_V, C.POINTER(_V), _I]),
+    "dlesm_tileset_sw_sync_state": (_I, [_V, C.POINTER(_V)]),
     "dlesm_kernel_create": (_V, [C.c_char_p, C.c_char_p, C.POINTER(GoArg), _I, _I, _I]),
     "dlesm_kernel_generated_source": (C.c_char_p, [_V]),
     "dlesm_kernel_launch": (_I, [_V, C.POINTER(_V), _I, _PD, _I, _PI, _I]),

@@ -177,7 +177,10 @@ def iprocmap(decomp: decomposition_type, ia, ja, nranks=None):
 class grid_type:
     """grid_type(grid_name, boundary_conditions, grid_offsets) -- src/grid_mod.f90:75-157, 217-304"""
 
-    def __init__(self, grid_name, boundary_conditions, grid_offsets=None):
+    def __init__(self, grid_name=None, boundary_conditions=None, grid_offsets=None, _handle=None):
+        if _handle is not None:              # a tile of a tile set: the set owns the handle
+            self._h, self._borrowed = _handle, True
+            return
         bcs = (C.c_int * 3)(*boundary_conditions)
         self._h = _chk_ptr(_lib.lib().dlesm_grid_create(grid_name, bcs, _opt(grid_offsets)))
 
@@ -246,7 +249,7 @@ class grid_type:
         raise AttributeError(item)
 
     def __del__(self):
-        if getattr(self, "_h", None):
+        if getattr(self, "_h", None) and not getattr(self, "_borrowed", False):
             _lib.lib().dlesm_grid_free(self._h)
             self._h = None
 
@@ -514,6 +517,101 @@ class shallow_water:
                 self._h = None
         except Exception:
             pass
+
+
+# --- several sub-domains per rank (extension; src/decomposition_mod.f90:64-67, --------------------
+# --- src/parallel_mod.f90:141-152, the \TODO of src/parallel_comms_mod.f90:295) -----------------
+class tileset:
+    """go_decompose(ndomains > nranks): this rank owns proc_subdomains(:, rank).  One ordinary grid per
+    owned sub-domain (`grids`; grid_init each, create fields / models on them as usual) and ONE halo
+    exchange over all of them: same-rank neighbours by device copies, the others packed per peer rank."""
+
+    def __init__(self, grid_name, boundary_conditions, grid_offsets, domainx, domainy, ndomains=None,
+                 ndomainx=None, ndomainy=None, halo_width=None):
+        bcs = (C.c_int * 3)(*boundary_conditions)
+        L = _lib.lib()
+        self._h = _chk_ptr(L.dlesm_tileset_create(grid_name, bcs, _opt(grid_offsets), domainx, domainy,
+                                                  _opt(ndomains), _opt(ndomainx), _opt(ndomainy), _opt(halo_width)))
+        self.ntiles = L.dlesm_tileset_ntiles(self._h)
+        self.grids = [grid_type(_handle=L.dlesm_tileset_grid(self._h, k)) for k in range(self.ntiles)]
+        self.tile_ids = [L.dlesm_tileset_tile_id(self._h, k) for k in range(self.ntiles)]
+        self.decomp = decomposition_type(L.dlesm_tileset_decomp(self._h), False)
+
+    def _handles(self, fields_by_tile):
+        """[[field q of tile k for k in tiles] for q in fields] -> flat field-major handle array"""
+        flat = [f._h for per_tile in fields_by_tile for f in per_tile]
+        return (C.c_void_p * len(flat))(*flat)
+
+    def halo_exchange(self, fields_by_tile, depth=1):
+        """fields_by_tile[q][k] = field q on tile k; collective"""
+        assert all(len(per_tile) == self.ntiles for per_tile in fields_by_tile)
+        _chk(_lib.lib().dlesm_tileset_halo_exchange(self._h, self._handles(fields_by_tile), len(fields_by_tile), depth))
+
+    def gather_inner_data(self, fields):
+        """one field per tile -> the global array on rank 1 (None elsewhere); collective"""
+        d = self.decomp
+        out = np.zeros((d.global_nx, d.global_ny), order="F")
+        _chk(_lib.lib().dlesm_tileset_gather_inner_data(self._h, self._handles([fields]), _dp(out)))
+        return out if on_master() else None
+
+    def free(self):
+        if self._h:
+            _lib.lib().dlesm_tileset_free(self._h)
+            self._h = None
+            for g in self.grids:
+                g._h = None
+
+
+def tileset_plan(decomp: decomposition_type, irank, nranks, pbc=(False, False), depth=1):
+    """host only: rank `irank`'s exchange plan over its tiles, as an (n, 14) integer array
+    (kind, peer0, src_tile, dst_tile, si0, sj0, di0, dj0, nx, ny, offset, dst_id, src_id, dir) + totals"""
+    rows = np.zeros((512, 14), dtype=np.int64)
+    n = C.c_int(0)
+    tot = (C.c_longlong * 2)()
+    _chk(_lib.lib().dlesm_tileset_plan(decomp._h, irank, nranks, int(pbc[0]), int(pbc[1]), depth,
+                                       rows.ctypes.data_as(C.POINTER(C.c_longlong)), 512, C.byref(n), tot))
+    return rows[:n.value].copy(), (tot[0], tot[1])
+
+
+class shallow_water_tiles:
+    """the shallow-water model over a tile set: one fused-mode model per owned tile, stepped together
+    (one sweep per tile, then one exchange of unew, vnew, pnew over all tiles)"""
+
+    def __init__(self, ts: tileset, dt=90.0, alpha=0.001, use_tmask=False):
+        self.ts = ts
+        self.models = [shallow_water(g, dt=dt, alpha=alpha, mode=SW_FUSED, use_tmask=use_tmask) for g in ts.grids]
+
+    def _handles(self):
+        return (C.c_void_p * len(self.models))(*[m._h for m in self.models])
+
+    def init_device(self):
+        for m in self.models:
+            m.init_device()
+        _chk(_lib.lib().dlesm_tileset_sw_sync_state(self.ts._h, self._handles()))
+
+    def set_state(self, states):
+        """states[k] = (u, v, p) local arrays of tile k (internal points; halos are exchanged here)"""
+        for m, (u, v, p) in zip(self.models, states):
+            m.set_state(u, v, p)
+        _chk(_lib.lib().dlesm_tileset_sw_sync_state(self.ts._h, self._handles()))
+
+    def step(self, nsteps=1):
+        _chk(_lib.lib().dlesm_tileset_sw_step(self.ts._h, self._handles(), nsteps))
+
+    def fields(self, name):
+        return [m.field(name) for m in self.models]
+
+    def gather(self, name):
+        return self.ts.gather_inner_data(self.fields(name))
+
+    def checksums(self):
+        """global sums over every tile of every rank"""
+        return tuple(sum(field_checksum(f) for f in self.fields(n)) for n in ("p", "u", "v"))
+
+    def free(self):
+        for m in self.models:
+            m.free()
+        self.models = []
 
 
 # --- kernel_mod / argument_mod: metadata-driven kernel dispatch (the PSy layer) ---------------

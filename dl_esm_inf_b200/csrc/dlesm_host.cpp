@@ -322,6 +322,95 @@ int build_comms(const Decomposition &d, int irank1, int nranks, bool pbc_x, bool
 }
 
 // ---------------------------------------------------------------------------
+// several sub-domains per rank: one exchange plan over the tiles a rank owns
+// ---------------------------------------------------------------------------
+int build_tileset_plan(const Decomposition &d, int rank1, int nranks, bool pbc_x, bool pbc_y, int depth,
+                       TilesetPlan &out)
+{
+    out = TilesetPlan{};
+    if (d.nranks != nranks || d.domperrank < 1 || rank1 < 1 || rank1 > nranks) {
+        set_error(DLESM_ERR_ARGS, "tile set: the decomposition was built for another number of ranks");
+        return DLESM_ERR_ARGS;
+    }
+    // tile id -> (owner rank, index in the owner's list)
+    std::vector<int> owner0(d.ndomains + 1, -1), local(d.ndomains + 1, -1);
+    for (int r = 0; r < nranks; ++r) {
+        int k = 0;
+        for (int s = 0; s < d.domperrank; ++s) {
+            const int id = d.proc_subdomains[static_cast<size_t>(r) * d.domperrank + s];
+            if (id < 1) continue;
+            owner0[id] = r;
+            local[id] = k++;
+            if (r == rank1 - 1) out.owned.push_back(id);
+        }
+    }
+    if (out.owned.empty()) {
+        set_error(DLESM_ERR_ARGS, "tile set: this rank owns no sub-domain");
+        return DLESM_ERR_ARGS;
+    }
+    std::vector<TileSeg> copies, sends, recvs;
+    for (size_t k = 0; k < out.owned.size(); ++k) {
+        const int id = out.owned[k];
+        dlesm_comms t;
+        int rc = build_comms(d, id, d.ndomains, pbc_x, pbc_y, depth, depth, t);
+        if (rc != DLESM_OK) return rc;
+        const dlesm_region &in = d.subdomains[id - 1].internal;
+        for (int s = 0; s < t.nsend; ++s) {
+            if (t.nxsend[s] <= 0 || t.nysend[s] <= 0) continue;
+            // a same-rank copy reads while other copies write: sends must read internal points only
+            if (t.isrcsend[s] < in.xstart || t.isrcsend[s] + t.nxsend[s] - 1 > in.xstop ||
+                t.jsrcsend[s] < in.ystart || t.jsrcsend[s] + t.nysend[s] - 1 > in.ystop) {
+                set_error(DLESM_ERR_ARGS, "tile set: a send patch reaches outside the internal region");
+                return DLESM_ERR_ARGS;
+            }
+            TileSeg g;
+            const int dst = t.destination[s] + 1;
+            g.peer0 = owner0[dst];
+            g.src_tile = static_cast<int>(k);
+            g.si0 = t.isrcsend[s]; g.sj0 = t.jsrcsend[s];
+            g.di0 = t.idessend[s]; g.dj0 = t.jdessend[s];
+            g.nx = t.nxsend[s]; g.ny = t.nysend[s];
+            g.dst_id = dst; g.src_id = id; g.dir = t.dirsend[s];
+            if (g.peer0 == rank1 - 1) {
+                g.kind = 0;
+                g.dst_tile = local[dst];
+                copies.push_back(g);
+            } else {
+                g.kind = 1;
+                sends.push_back(g);
+            }
+        }
+        for (int r = 0; r < t.nrecv; ++r) {
+            if (t.nxrecv[r] <= 0 || t.nyrecv[r] <= 0) continue;
+            const int src = t.source[r] + 1;
+            if (owner0[src] == rank1 - 1) continue;   // arrives as the sender's same-rank copy
+            TileSeg g;
+            g.kind = 2;
+            g.peer0 = owner0[src];
+            g.dst_tile = static_cast<int>(k);
+            g.di0 = t.idesrecv[r]; g.dj0 = t.jdesrecv[r];
+            g.nx = t.nxrecv[r]; g.ny = t.nyrecv[r];
+            g.dst_id = id; g.src_id = src; g.dir = t.dirrecv[r];   // received with the sender's tag
+            recvs.push_back(g);
+        }
+    }
+    auto by_key = [](const TileSeg &a, const TileSeg &b) {
+        if (a.peer0 != b.peer0) return a.peer0 < b.peer0;
+        if (a.dst_id != b.dst_id) return a.dst_id < b.dst_id;
+        if (a.src_id != b.src_id) return a.src_id < b.src_id;
+        return a.dir < b.dir;
+    };
+    std::sort(sends.begin(), sends.end(), by_key);
+    std::sort(recvs.begin(), recvs.end(), by_key);
+    for (TileSeg &g : sends) { g.offset = out.send_total; out.send_total += static_cast<long long>(g.nx) * g.ny; }
+    for (TileSeg &g : recvs) { g.offset = out.recv_total; out.recv_total += static_cast<long long>(g.nx) * g.ny; }
+    out.segs = copies;
+    out.segs.insert(out.segs.end(), sends.begin(), sends.end());
+    out.segs.insert(out.segs.end(), recvs.begin(), recvs.end());
+    return DLESM_OK;
+}
+
+// ---------------------------------------------------------------------------
 // grid sizing -- src/grid_mod.f90:344-385
 // ---------------------------------------------------------------------------
 int parse_alignment(const char *env, int &alignment)

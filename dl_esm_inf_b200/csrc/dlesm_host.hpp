@@ -50,6 +50,29 @@ int owner_of(const Decomposition &d, int nranks, int ia, int ja);
 int build_comms(const Decomposition &d, int irank1, int nranks, bool pbc_x, bool pbc_y,
                 int depth_x, int depth_y, dlesm_comms &out);
 
+// ---- several sub-domains per rank (extension F3; the reference carries proc_subdomains,
+// src/decomposition_mod.f90:64-67, and marks map_comms "\TODO support multiple subdomains per
+// rank", src/parallel_comms_mod.f90:295) ----
+// One halo exchange over every tile this rank owns.  Tables are map_comms' own, built per tile with
+// the tile id in the place of the rank; a message whose two ends live on this rank becomes a device
+// copy, the others are packed per peer RANK in the order (destination tile, source tile, direction)
+// that both ends can compute.
+struct TileSeg {
+    int kind = 0;                   // 0 same-rank copy, 1 send (pack), 2 receive (unpack)
+    int peer0 = 0;                  // 0-based rank at the other end (this rank for kind 0)
+    int src_tile = -1, dst_tile = -1;   // 0-based indices into this rank's tile list (-1: the buffer)
+    int si0 = 0, sj0 = 0, di0 = 0, dj0 = 0, nx = 0, ny = 0;   // 1-based corners in the tiles' local arrays
+    long long offset = 0;           // element offset of the patch in the send / receive buffer, one field
+    int dst_id = 0, src_id = 0, dir = 0;   // the ordering key (1-based tile ids, direction tag)
+};
+struct TilesetPlan {
+    std::vector<int> owned;         // 1-based ids of this rank's tiles, proc_subdomains(:, rank)
+    std::vector<TileSeg> segs;      // copies, then sends grouped by peer, then receives grouped by peer
+    long long send_total = 0, recv_total = 0;
+};
+int build_tileset_plan(const Decomposition &d, int rank1, int nranks, bool pbc_x, bool pbc_y, int depth,
+                       TilesetPlan &out);
+
 // ---- grid sizing (src/grid_mod.f90:344-385) ----
 int parse_alignment(const char *envval, int &alignment);
 struct GridDims {

@@ -5,6 +5,7 @@
 // no tensor cores.  Compiled with -fmad=false so that each arithmetic operation rounds once,
 // like the reference's Fortran loops built without FMA (compiler_setup/gnu.sh:7-8) and like
 // the CPU oracle: stencil results are bit-identical, not merely within 1e-12.
+#include <algorithm>
 #include "dlesm_kernels.cuh"
 
 #include <atomic>
@@ -458,6 +459,33 @@ cudaError_t gather_box(const double *f, int pitch, Box b, double *packed, cudaSt
     const int w = b.xe - b.xs + 1, h = b.ye - b.ys + 1;
     if (w <= 0 || h <= 0) return cudaSuccess;
     patch_kernel<<<kSMs * 4, 256, 0, s>>>(f, pitch, b.xs, b.ys, packed, w, 1, 1, w, h);
+    count_launch();
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------
+// Tile-set exchange: every same-rank halo copy, pack or unpack of one phase in one launch.
+// Patches are halo strips (a few KB to a few hundred KB): blockIdx.y picks the copy, blockIdx.x
+// strides over its elements; rows of the wide (north / south) strips are read and written coalesced.
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) tile_ops_kernel(const __grid_constant__ TileOpBatch b)
+{
+    const TileOp &o = b.op[blockIdx.y];
+    const long long n = static_cast<long long>(o.nx) * o.ny;
+    for (long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; t < n;
+         t += static_cast<long long>(gridDim.x) * blockDim.x) {
+        const int jj = static_cast<int>(t / o.nx), ii = static_cast<int>(t - static_cast<long long>(jj) * o.nx);
+        o.dst[static_cast<size_t>(jj) * o.dpitch + ii] = o.src[static_cast<size_t>(jj) * o.spitch + ii];
+    }
+}
+
+cudaError_t tile_ops(const TileOpBatch &b, cudaStream_t s)
+{
+    if (b.n <= 0) return cudaSuccess;
+    long long nmax = 1;
+    for (int q = 0; q < b.n; ++q) nmax = std::max(nmax, static_cast<long long>(b.op[q].nx) * b.op[q].ny);
+    const unsigned bx = static_cast<unsigned>(std::min<long long>((nmax + 255) / 256, 32));
+    tile_ops_kernel<<<dim3(bx, b.n), 256, 0, s>>>(b);
     count_launch();
     return cudaGetLastError();
 }

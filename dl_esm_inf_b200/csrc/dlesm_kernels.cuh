@@ -68,6 +68,21 @@ cudaError_t scatter_global(double *f, int pitch, Box box, const double *global, 
                            int dy, cudaStream_t s);
 cudaError_t gather_box(const double *f, int pitch, Box box, double *packed, cudaStream_t s);
 
+// Tile-set exchange (several sub-domains per rank): a batch of rectangular copies, each between two
+// arrays of its own pitch -- tile to tile, tile to send buffer, receive buffer to tile.  Pointers
+// address the first element of the patch.  One launch per batch, blockIdx.y = copy.
+struct TileOp {
+    const double *src;
+    double *dst;
+    int spitch, dpitch, nx, ny;
+};
+constexpr int kTileOpsPerLaunch = 96;
+struct TileOpBatch {
+    TileOp op[kTileOpsPerLaunch];
+    int n;
+};
+cudaError_t tile_ops(const TileOpBatch &b, cudaStream_t s);
+
 // ---- shallow-water sweeps, un-fused (one launch per reference-style kernel) ----
 cudaError_t compute_cu(double *cu, const double *p, const double *u, int pitch, Box b,
                        const int *tmask, cudaStream_t s);

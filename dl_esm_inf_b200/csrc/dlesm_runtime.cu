@@ -1648,6 +1648,7 @@ struct dlesm_grid {
     bool have_comms = false;
     bool pbc_x = false, pbc_y = false;
     void *dev[17] = {nullptr};
+    int tile_id = 0;                  // > 0: one of several sub-domains of this rank (dlesm_tileset), 1-based id
 };
 
 extern "C" dlesm_grid_t *dlesm_grid_create(int grid_name, const int bcs[3], int grid_offsets)
@@ -1707,7 +1708,8 @@ extern "C" int dlesm_grid_init(dlesm_grid_t *g, double dxarg, double dyarg, cons
     const dlesm_subdomain &sub = g->info.subdomain;
     const bool px = g->info.boundary_conditions[0] == DLESM_GO_BC_PERIODIC;
     const bool py = g->info.boundary_conditions[1] == DLESM_GO_BC_PERIODIC;
-    const bool dist = pstate().nranks > 1;
+    // a tile of a tile set gets its halos from the set's own exchange plan (periodic wrap included)
+    const bool dist = pstate().nranks > 1 && g->tile_id == 0;
     const bool ext = (pstate().extensions & DLESM_EXT_PERIODIC_DISTMEM) != 0;
     if (dist && (px || py) && !ext) {
         // src/grid_mod.f90:437-442 and :559-564
@@ -1741,7 +1743,7 @@ extern "C" int dlesm_grid_init(dlesm_grid_t *g, double dxarg, double dyarg, cons
         g->have_comms = true;
         rc = dlesm_dev_set_comms(&g->comms);  // module-level state, as in parallel_comms_mod
         if (rc != DLESM_OK) return rc;
-    } else {
+    } else if (g->tile_id == 0) {
         dlesm_dev_set_comms(nullptr);         // one rank: map_comms finds no neighbour (stub build)
     }
     g->info.initialised = 1;
@@ -2265,6 +2267,7 @@ struct dlesm_sw {
     bool deep_valid = false;
     unsigned char *mask2 = nullptr;   // byte image of the tmask with a PERIODIC ring two cells deep
     int mask2_pitch = 0;
+    bool tiled = false;               // model of one tile of a tile set: halos come from dlesm_tileset_*
 };
 
 extern "C" dlesm_sw_t *dlesm_sw_create(dlesm_grid_t *g, double dt, double alpha, int mode, int use_tmask)
@@ -2284,7 +2287,8 @@ extern "C" dlesm_sw_t *dlesm_sw_create(dlesm_grid_t *g, double dt, double alpha,
     s->dt = s->tdt = dt;
     s->alpha = alpha;
     s->mode = mode;
-    s->periodic_local = pstate().nranks == 1;
+    s->tiled = g->tile_id > 0;
+    s->periodic_local = pstate().nranks == 1 && !s->tiled;
     static const int pts[DLESM_SW_NFIELDS] = {
         DLESM_GO_U_POINTS, DLESM_GO_V_POINTS, DLESM_GO_T_POINTS, DLESM_GO_U_POINTS, DLESM_GO_V_POINTS,
         DLESM_GO_T_POINTS, DLESM_GO_U_POINTS, DLESM_GO_V_POINTS, DLESM_GO_T_POINTS, DLESM_GO_U_POINTS,
@@ -2313,6 +2317,7 @@ extern "C" dlesm_sw_t *dlesm_sw_create(dlesm_grid_t *g, double dt, double alpha,
 namespace {
 int sw_fill_halos(dlesm_sw *s, int first_field, int count)
 {
+    if (s->tiled) return DLESM_OK;   // deferred: the tile set exchanges every tile's fields at once
     if (s->periodic_local) {
         double *fl[k::kMaxExchangeFields];
         for (int q = 0; q < count; ++q) fl[q] = static_cast<double *>(s->f[first_field + q]->dptr);
@@ -2515,6 +2520,10 @@ extern "C" int dlesm_sw_set_state(dlesm_sw_t *s, const double *u, const double *
 extern "C" int dlesm_sw_step(dlesm_sw_t *s, int nsteps)
 {
     clear_error();
+    if (s->tiled) {
+        set_error(DLESM_ERR_STATE, "sw_step: this model is one tile of a tile set; step the set (dlesm_tileset_sw_step)");
+        return DLESM_ERR_STATE;
+    }
     dlesm_grid &g = *s->grid;
     const double dx = g.info.dx, dy = g.info.dy;
     for (int it = 0; it < nsteps; ++it) {
@@ -2905,4 +2914,353 @@ extern "C" int dlesm_sw_launch_grid(dlesm_sw_t *s, int two_step, int grid[2])
         else k::fma_off::fused_grid(a, s->variant, grid);
     }
     return DLESM_OK;
+}
+
+// =========================================================================================
+// Several sub-domains per rank (SURVEY F3 extension).  The reference carries the bookkeeping
+// (decomposition_type%proc_subdomains, src/decomposition_mod.f90:64-67; go_decompose(ndomains > nranks),
+// src/parallel_mod.f90:141-152) and stops at map_comms ("\TODO support multiple subdomains per rank",
+// src/parallel_comms_mod.f90:295).  Here: a tile set owns one ordinary grid per sub-domain of this rank;
+// fields and models are created on those grids as usual; ONE exchange fills the halos of every tile --
+// same-rank neighbours by device copies, the others packed per peer rank (build_tileset_plan).
+// =========================================================================================
+struct dlesm_tileset {
+    dlesm_grid *parent = nullptr;          // name, offset, BCs and the decomposition
+    std::vector<dlesm_grid *> tiles;       // one grid per owned sub-domain, in proc_subdomains order
+    std::vector<TilesetPlan> plans;        // index = depth - 1, built on first use
+    bool pbc_x = false, pbc_y = false;
+};
+
+extern "C" dlesm_tileset_t *dlesm_tileset_create(int grid_name, const int bcs[3], int grid_offsets, int domainx,
+                                                 int domainy, int ndomains, int ndomainx, int ndomainy,
+                                                 int halo_width)
+{
+    clear_error();
+    dlesm_grid *parent = dlesm_grid_create(grid_name, bcs, grid_offsets);
+    if (!parent) return nullptr;
+    int rc = go_decompose(domainx, domainy, ndomains, ndomainx, ndomainy, halo_width, pstate().nranks, parent->decomp);
+    if (rc != DLESM_OK) {
+        delete parent;
+        return nullptr;
+    }
+    const Decomposition &d = parent->decomp;
+    if (d.ndomains % pstate().nranks != 0) {
+        set_error(DLESM_ERR_ARGS, "tile set: the number of sub-domains must be a multiple of the number of ranks");
+        delete parent;
+        return nullptr;
+    }
+    auto *ts = new dlesm_tileset;
+    ts->parent = parent;
+    ts->pbc_x = bcs[0] == DLESM_GO_BC_PERIODIC;
+    ts->pbc_y = bcs[1] == DLESM_GO_BC_PERIODIC;
+    parent->info.global_nx = d.global_nx;
+    parent->info.global_ny = d.global_ny;
+    const int me = pstate().rank;
+    for (int s = 0; s < d.domperrank; ++s) {
+        const int id = d.proc_subdomains[static_cast<size_t>(me - 1) * d.domperrank + s];
+        if (id < 1) continue;
+        auto *g = new dlesm_grid;
+        g->info = parent->info;
+        g->decomp = d;
+        g->info.subdomain = d.subdomains[id - 1];
+        g->decomposed = true;
+        g->tile_id = id;
+        ts->tiles.push_back(g);
+    }
+    parent->info.subdomain = ts->tiles.empty() ? dlesm_subdomain{} : ts->tiles[0]->info.subdomain;
+    parent->decomposed = true;
+    return ts;
+}
+
+extern "C" int dlesm_tileset_ntiles(const dlesm_tileset_t *ts) { return static_cast<int>(ts->tiles.size()); }
+extern "C" dlesm_grid_t *dlesm_tileset_grid(dlesm_tileset_t *ts, int k)
+{
+    if (k < 0 || k >= static_cast<int>(ts->tiles.size())) return nullptr;
+    return ts->tiles[k];
+}
+extern "C" int dlesm_tileset_tile_id(const dlesm_tileset_t *ts, int k)
+{
+    if (k < 0 || k >= static_cast<int>(ts->tiles.size())) return -1;
+    return ts->tiles[k]->tile_id;
+}
+extern "C" const dlesm_decomp_t *dlesm_tileset_decomp(const dlesm_tileset_t *ts) { return &ts->parent->dh; }
+
+extern "C" void dlesm_tileset_free(dlesm_tileset_t *ts)
+{
+    if (!ts) return;
+    for (auto *g : ts->tiles) dlesm_grid_free(g);
+    dlesm_grid_free(ts->parent);
+    delete ts;
+}
+
+// the plan as rows of 14 integers (CPU-testable: no device involved):
+// kind, peer0, src_tile, dst_tile, si0, sj0, di0, dj0, nx, ny, offset, dst_id, src_id, dir
+extern "C" int dlesm_tileset_plan(const dlesm_decomp_t *d, int rank1, int nranks, int pbc_x, int pbc_y, int depth,
+                                  long long *rows, int max_rows, int *nrows, long long totals[2])
+{
+    clear_error();
+    TilesetPlan plan;
+    int rc = build_tileset_plan(d->d, rank1, nranks, pbc_x != 0, pbc_y != 0, depth, plan);
+    if (rc != DLESM_OK) return rc;
+    *nrows = static_cast<int>(plan.segs.size());
+    totals[0] = plan.send_total;
+    totals[1] = plan.recv_total;
+    if (*nrows > max_rows) {
+        set_error(DLESM_ERR_ARGS, "tileset_plan: more rows than the caller's array holds");
+        return DLESM_ERR_ARGS;
+    }
+    for (int q = 0; q < *nrows; ++q) {
+        const TileSeg &g = plan.segs[q];
+        const long long v[14] = {g.kind, g.peer0, g.src_tile, g.dst_tile, g.si0, g.sj0, g.di0, g.dj0,
+                                 g.nx, g.ny, g.offset, g.dst_id, g.src_id, g.dir};
+        std::copy(v, v + 14, rows + static_cast<size_t>(q) * 14);
+    }
+    return DLESM_OK;
+}
+
+namespace {
+int tileset_plan_for(dlesm_tileset *ts, int depth, const TilesetPlan *&out)
+{
+    if (depth < 1 || depth > ts->parent->decomp.hwidth) {
+        set_error(DLESM_ERR_HALO_DEPTH, "tile set: halo depth exceeds the halo width of the decomposition");
+        return DLESM_ERR_HALO_DEPTH;
+    }
+    if (static_cast<int>(ts->plans.size()) < depth) ts->plans.resize(depth);
+    TilesetPlan &p = ts->plans[depth - 1];
+    if (p.owned.empty()) {
+        int rc = build_tileset_plan(ts->parent->decomp, pstate().rank, pstate().nranks, ts->pbc_x, ts->pbc_y, depth, p);
+        if (rc != DLESM_OK) return rc;
+    }
+    out = &p;
+    return DLESM_OK;
+}
+
+// fields[q * ntiles + k] = device array of field q on tile k
+int tileset_exchange(dlesm_tileset *ts, void *const *fields, int nfields, int depth)
+{
+    const TilesetPlan *pp;
+    int rc = tileset_plan_for(ts, depth, pp);
+    if (rc != DLESM_OK) return rc;
+    const TilesetPlan &plan = *pp;
+    const int nt = static_cast<int>(ts->tiles.size());
+    if (nfields < 1 || nfields > k::kMaxExchangeFields) {
+        set_error(DLESM_ERR_ARGS, "tile set exchange: between 1 and 8 fields per call");
+        return DLESM_ERR_ARGS;
+    }
+    rc = ensure_device();
+    if (rc != DLESM_OK) return rc;
+    Context &c = ctx();
+    std::vector<int> pitch(nt);
+    for (int k = 0; k < nt; ++k)
+        for (int q = 0; q < nfields; ++q) {
+            FieldRec r;
+            rc = lookup(fields[q * nt + k], r);
+            if (rc != DLESM_OK) return rc;
+            if (r.nx != ts->tiles[k]->info.nx || r.ny != ts->tiles[k]->info.ny) {
+                set_error(DLESM_ERR_ARGS, "tile set exchange: a field does not have its tile's shape");
+                return DLESM_ERR_ARGS;
+            }
+            pitch[k] = r.nx;
+        }
+    rc = ensure_xbuf(static_cast<size_t>(std::max(plan.send_total, plan.recv_total)) * nfields + 1);
+    if (rc != DLESM_OK) return rc;
+    bool remote = false;
+    for (const TileSeg &g : plan.segs) remote = remote || g.kind != 0;
+    if (remote && !c.comm_ready) {
+        set_error(DLESM_ERR_STATE, "tile set exchange: communicator not initialised (dlesm_comm_init)");
+        return DLESM_ERR_STATE;
+    }
+    auto at = [&](int q, int k, int i0, int j0) {
+        return static_cast<double *>(fields[q * nt + k]) + (static_cast<size_t>(j0) - 1) * pitch[k] + (i0 - 1);
+    };
+    k::TileOpBatch batch;
+    batch.n = 0;
+    auto flush = [&]() -> int {
+        if (batch.n > 0) CU(k::tile_ops(batch, c.stream));
+        batch.n = 0;
+        return DLESM_OK;
+    };
+    auto add = [&](const double *src, int sp, double *dst, int dp, int nx, int ny) -> int {
+        if (batch.n == k::kTileOpsPerLaunch) {
+            int r2 = flush();
+            if (r2 != DLESM_OK) return r2;
+        }
+        batch.op[batch.n++] = k::TileOp{src, dst, sp, dp, nx, ny};
+        return DLESM_OK;
+    };
+    // phase 1: same-rank halos directly, everything that leaves the rank into the send buffer
+    // (segment-major, field-minor: both ends agree on it)
+    for (const TileSeg &g : plan.segs) {
+        for (int q = 0; q < nfields && rc == DLESM_OK; ++q) {
+            if (g.kind == 0)
+                rc = add(at(q, g.src_tile, g.si0, g.sj0), pitch[g.src_tile], at(q, g.dst_tile, g.di0, g.dj0),
+                         pitch[g.dst_tile], g.nx, g.ny);
+            else if (g.kind == 1)
+                rc = add(at(q, g.src_tile, g.si0, g.sj0), pitch[g.src_tile],
+                         c.sendbuf + g.offset * nfields + static_cast<long long>(q) * g.nx * g.ny, g.nx, g.nx, g.ny);
+        }
+        if (rc != DLESM_OK) return rc;
+    }
+    rc = flush();
+    if (rc != DLESM_OK) return rc;
+    if (remote) {
+        // one message per peer rank and direction of travel, whatever the number of tile pairs behind it
+        std::map<int, std::pair<long long, long long>> so, ro;   // peer -> (first offset, elements), one field
+        for (const TileSeg &g : plan.segs) {
+            if (g.kind == 0) continue;
+            auto &m = g.kind == 1 ? so : ro;
+            auto it = m.find(g.peer0);
+            const long long n = static_cast<long long>(g.nx) * g.ny;
+            if (it == m.end()) m[g.peer0] = {g.offset, n};
+            else it->second.second += n;
+        }
+        NC(ncclGroupStart());
+        for (const auto &kv : so)
+            NC(ncclSend(c.sendbuf + kv.second.first * nfields, static_cast<size_t>(kv.second.second) * nfields,
+                        ncclDouble, kv.first, c.comm, c.stream));
+        for (const auto &kv : ro)
+            NC(ncclRecv(c.recvbuf + kv.second.first * nfields, static_cast<size_t>(kv.second.second) * nfields,
+                        ncclDouble, kv.first, c.comm, c.stream));
+        NC(ncclGroupEnd());
+        for (const TileSeg &g : plan.segs) {
+            if (g.kind != 2) continue;
+            for (int q = 0; q < nfields && rc == DLESM_OK; ++q)
+                rc = add(c.recvbuf + g.offset * nfields + static_cast<long long>(q) * g.nx * g.ny, g.nx,
+                         at(q, g.dst_tile, g.di0, g.dj0), pitch[g.dst_tile], g.nx, g.ny);
+            if (rc != DLESM_OK) return rc;
+        }
+        rc = flush();
+        if (rc != DLESM_OK) return rc;
+    }
+    for (int q = 0; q < nfields * nt; ++q) mark_clean(fields[q], depth);
+    return DLESM_OK;
+}
+}  // namespace
+
+// halo_exchange(depth) of `nfields` fields on every tile of the set; fields[q * ntiles + k] = field q of tile k
+extern "C" int dlesm_tileset_halo_exchange(dlesm_tileset_t *ts, dlesm_field_t *const *fields, int nfields, int depth)
+{
+    clear_error();
+    const int nt = static_cast<int>(ts->tiles.size());
+    std::vector<void *> ptrs(static_cast<size_t>(nfields) * nt);
+    for (size_t q = 0; q < ptrs.size(); ++q) {
+        if (fields[q]->grid != ts->tiles[q % nt]) {
+            set_error(DLESM_ERR_ARGS, "tile set exchange: fields must be listed field-major, one per tile, on the set's grids");
+            return DLESM_ERR_ARGS;
+        }
+        ptrs[q] = fields[q]->dptr;
+    }
+    return tileset_exchange(ts, ptrs.data(), nfields, depth);
+}
+
+// gather_inner_data (src/field_mod.f90:1311-1391) of one field per tile into the global array on rank 1
+extern "C" int dlesm_tileset_gather_inner_data(dlesm_tileset_t *ts, dlesm_field_t *const *fields, double *global_data)
+{
+    clear_error();
+    Context &c = ctx();
+    int rc = ensure_device();
+    if (rc != DLESM_OK) return rc;
+    const Decomposition &d = ts->parent->decomp;
+    const int nt = static_cast<int>(ts->tiles.size());
+    const int nranks = pstate().nranks, me = pstate().rank;
+    const int hw = d.hwidth;
+    const size_t slot = static_cast<size_t>(d.max_width - 2 * hw) * (d.max_height - 2 * hw);   // one tile
+    const size_t per_rank = slot * d.domperrank;
+    rc = ensure_scratch(per_rank * (me == 1 ? nranks : 1));
+    if (rc != DLESM_OK) return rc;
+    for (int k = 0; k < nt; ++k)
+        CU(k::gather_box(static_cast<const double *>(fields[k]->dptr), fields[k]->nx,
+                         box_of(ts->tiles[k]->info.subdomain.internal), c.scratch + slot * k, c.stream));
+    if (nranks > 1) {
+        if (!c.comm_ready) {
+            set_error(DLESM_ERR_STATE, "tile set gather: communicator not initialised (dlesm_comm_init)");
+            return DLESM_ERR_STATE;
+        }
+        NC(ncclGroupStart());
+        if (me == 1) {
+            for (int r = 1; r < nranks; ++r)
+                NC(ncclRecv(c.scratch + per_rank * r, per_rank, ncclDouble, r, c.comm, c.stream));
+        } else {
+            NC(ncclSend(c.scratch, per_rank, ncclDouble, 0, c.comm, c.stream));
+        }
+        NC(ncclGroupEnd());
+    }
+    if (me != 1) {
+        CU(cudaStreamSynchronize(c.stream));
+        return DLESM_OK;
+    }
+    std::vector<double> recv(per_rank * nranks);
+    CU(cudaMemcpyAsync(recv.data(), c.scratch, recv.size() * sizeof(double), cudaMemcpyDeviceToHost, c.stream));
+    CU(cudaStreamSynchronize(c.stream));
+    for (int r = 0; r < nranks; ++r)
+        for (int s = 0; s < d.domperrank; ++s) {
+            const int id = d.proc_subdomains[static_cast<size_t>(r) * d.domperrank + s];
+            if (id < 1) continue;
+            // T-point internal region of the tile == its piece of the global domain; the packed box of
+            // any staggering has the field's own internal extents, which for interior tiles equal it
+            const dlesm_region &gr = d.subdomains[id - 1].global;
+            const dlesm_region &in = d.subdomains[id - 1].internal;
+            size_t q = per_rank * r + slot * s;
+            for (int jj = 0; jj < in.ny; ++jj)
+                for (int ji = 0; ji < in.nx; ++ji)
+                    global_data[(static_cast<size_t>(gr.ystart) - 1 + jj) * d.global_nx + (gr.xstart - 1 + ji)] = recv[q++];
+        }
+    return DLESM_OK;
+}
+
+// nsteps steps of the fused shallow-water model on every tile: per step one sweep per tile, then
+// ONE exchange of unew, vnew, pnew over all tiles, then the buffer rotation.
+extern "C" int dlesm_tileset_sw_step(dlesm_tileset_t *ts, dlesm_sw_t *const *sws, int nsteps)
+{
+    clear_error();
+    const int nt = static_cast<int>(ts->tiles.size());
+    for (int k = 0; k < nt; ++k)
+        if (!sws[k] || sws[k]->grid != ts->tiles[k] || sws[k]->mode != DLESM_SW_FUSED ||
+            sws[k]->ncycle != sws[0]->ncycle) {
+            set_error(DLESM_ERR_ARGS, "tileset_sw_step: one fused-mode model per tile, in tile order, all at the same step");
+            return DLESM_ERR_ARGS;
+        }
+    int rc = ensure_device();
+    if (rc != DLESM_OK) return rc;
+    std::vector<void *> ptrs(static_cast<size_t>(3) * nt);
+    for (int it = 0; it < nsteps; ++it) {
+        for (int k = 0; k < nt; ++k) {
+            dlesm_sw *s = sws[k];
+            dlesm_field **f = s->f;
+            const dlesm_region &rt = f[DLESM_SW_P]->fb.internal;
+            const int first = s->ncycle == 0;
+            rc = sw_step_fused_impl(f[DLESM_SW_U]->dptr, f[DLESM_SW_V]->dptr, f[DLESM_SW_P]->dptr,
+                                    f[DLESM_SW_UOLD]->dptr, f[DLESM_SW_VOLD]->dptr, f[DLESM_SW_POLD]->dptr,
+                                    f[DLESM_SW_UNEW]->dptr, f[DLESM_SW_VNEW]->dptr, f[DLESM_SW_PNEW]->dptr,
+                                    s->grid->info.dx, s->grid->info.dy, s->tdt, s->alpha, first, rt.xstart, rt.xstop,
+                                    rt.ystart, rt.ystop, s->tmask_dev, s->variant, nullptr);
+            if (rc != DLESM_OK) return rc;
+            for (int q = 0; q < 3; ++q) ptrs[static_cast<size_t>(q) * nt + k] = f[DLESM_SW_UNEW + q]->dptr;
+        }
+        rc = tileset_exchange(ts, ptrs.data(), 3, 1);
+        if (rc != DLESM_OK) return rc;
+        for (int k = 0; k < nt; ++k) {
+            dlesm_sw *s = sws[k];
+            for (int q = 0; q < 3; ++q) std::swap(s->f[DLESM_SW_U + q]->dptr, s->f[DLESM_SW_UNEW + q]->dptr);
+            if (s->ncycle == 0) s->tdt = s->tdt + s->tdt;
+            ++s->ncycle;
+            s->deep_valid = false;
+        }
+    }
+    return DLESM_OK;
+}
+
+// halos of u, v, p after dlesm_sw_init_device / dlesm_sw_set_state on every tile, and the old fields from them
+extern "C" int dlesm_tileset_sw_sync_state(dlesm_tileset_t *ts, dlesm_sw_t *const *sws)
+{
+    clear_error();
+    const int nt = static_cast<int>(ts->tiles.size());
+    std::vector<void *> ptrs(static_cast<size_t>(3) * nt);
+    for (int k = 0; k < nt; ++k)
+        for (int q = 0; q < 3; ++q) ptrs[static_cast<size_t>(q) * nt + k] = sws[k]->f[DLESM_SW_U + q]->dptr;
+    int rc = tileset_exchange(ts, ptrs.data(), 3, 1);
+    for (int k = 0; k < nt && rc == DLESM_OK; ++k)
+        for (int q = 0; q < 3 && rc == DLESM_OK; ++q)
+            rc = dlesm_copy_field(sws[k]->f[DLESM_SW_U + q], sws[k]->f[DLESM_SW_UOLD + q]);
+    return rc;
 }

@@ -519,6 +519,39 @@ int dlesm_sw_step_host(dlesm_sw_t *s, const double *const host_in[6], double *co
 int dlesm_sw_step_host_n(dlesm_sw_t *s, const double *const host_in[6], double *const host_out[6],
                          int band_rows, int nsteps);
 dlesm_field_t *dlesm_sw_field(dlesm_sw_t *s, int which);
+/* ------------------------------------------------------------------------------------ */
+/* Several sub-domains per rank (extension).  The reference carries the bookkeeping --     */
+/* decomposition_type%proc_subdomains (src/decomposition_mod.f90:64-67), go_decompose with  */
+/* ndomains > nranks (src/parallel_mod.f90:141-152) -- and stops at map_comms ("\TODO      */
+/* support multiple subdomains per rank", src/parallel_comms_mod.f90:295).                  */
+/* A tile set owns one ordinary grid per sub-domain of this rank (grid_init each with its   */
+/* local T-mask, create fields / models on them as usual); one exchange fills the halos of  */
+/* every tile: same-rank neighbours by device copies, the others packed per peer rank.      */
+/* Periodic wrap is part of the plan (no DLESM_EXT_PERIODIC_DISTMEM needed).                */
+/* ------------------------------------------------------------------------------------ */
+typedef struct dlesm_tileset dlesm_tileset_t;
+dlesm_tileset_t *dlesm_tileset_create(int grid_name, const int boundary_conditions[3], int grid_offsets,
+                                      int domainx, int domainy, int ndomains, int ndomainx, int ndomainy,
+                                      int halo_width);
+int dlesm_tileset_ntiles(const dlesm_tileset_t *ts);            /* tiles of THIS rank (domperrank) */
+dlesm_grid_t *dlesm_tileset_grid(dlesm_tileset_t *ts, int k);   /* 0-based; owned by the set */
+int dlesm_tileset_tile_id(const dlesm_tileset_t *ts, int k);    /* 1-based sub-domain id, proc_subdomains(k+1, rank) */
+const dlesm_decomp_t *dlesm_tileset_decomp(const dlesm_tileset_t *ts);
+void dlesm_tileset_free(dlesm_tileset_t *ts);
+/* host only: this rank's exchange plan, rows of 14 integers
+ * (kind 0 copy / 1 send / 2 receive, peer rank (0-based), src tile, dst tile, si0, sj0, di0, dj0, nx, ny,
+ *  buffer offset, destination tile id, source tile id, direction tag); totals = send / receive elements */
+int dlesm_tileset_plan(const dlesm_decomp_t *d, int rank1, int nranks, int pbc_x, int pbc_y, int depth,
+                       long long *rows, int max_rows, int *nrows, long long totals[2]);
+/* fields[q * ntiles + k] = field q on tile k; collective over the ranks */
+int dlesm_tileset_halo_exchange(dlesm_tileset_t *ts, dlesm_field_t *const *fields, int nfields, int depth);
+/* fields[k] = one field per tile -> global array (global_nx * global_ny) on rank 1; collective */
+int dlesm_tileset_gather_inner_data(dlesm_tileset_t *ts, dlesm_field_t *const *fields, double *global_data);
+/* shallow-water models created on the set's grids (fused mode): step them together */
+int dlesm_tileset_sw_step(dlesm_tileset_t *ts, dlesm_sw_t *const *sws, int nsteps);
+/* after dlesm_sw_init_device / dlesm_sw_set_state on every tile: halos of u,v,p, then the old fields */
+int dlesm_tileset_sw_sync_state(dlesm_tileset_t *ts, dlesm_sw_t *const *sws);
+
 int dlesm_sw_set_variant(dlesm_sw_t *s, int variant);
 /* How the halos of unew, vnew, pnew get filled after the fused sweep:
  * DLESM_HALO_EXCHANGE (default): periodic copies on one rank, pack -> NCCL -> unpack on several;

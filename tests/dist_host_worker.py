@@ -234,6 +234,79 @@ def case_depth_periodic(nx, ny, depth=2):
     fd.gocean_initialise(RANK + 1, WORLD)            # go_decompose's SAVEd halo width back to 1
 
 
+def case_tileset(nx, ny, tiles_per_rank, periodic, depth=1):
+    """extension F3: several sub-domains per rank (src/decomposition_mod.f90:64-67; the \\TODO of
+    src/parallel_comms_mod.f90:295).  Each rank owns proc_subdomains(:, rank); its exchange plan
+    (dlesm_tileset_plan) turns same-rank neighbours into copies and groups the rest per peer RANK.
+    Driven over gloo with numpy for the copy kernel.  Known answer: every halo cell that lies inside
+    the (periodic: wrapped) global domain holds the global field's value at its position."""
+    from dl_esm_inf_b200.api import tileset_plan
+    os.environ.pop("DL_ESM_ALIGNMENT", None)
+    ndom = tiles_per_rank * WORLD
+    d = fd.go_decompose(nx, ny, ndomains=ndom, halo_width=depth)
+    ok(d.domperrank == tiles_per_rank, "domperrank")
+    owned = [d.proc_subdomains(s, RANK + 1) for s in range(1, tiles_per_rank + 1)]
+    ok(owned == list(range(RANK * tiles_per_rank + 1, (RANK + 1) * tiles_per_rank + 1)),
+       "proc_subdomains(:, rank) as go_decompose fills it (src/parallel_mod.f90:141-152)")
+    rows, (send_total, recv_total) = tileset_plan(d, RANK + 1, WORLD, pbc=(periodic, periodic), depth=depth)
+    subs = d.subdomains
+    G = np.asfortranarray(np.random.default_rng(5 + nx * 3 + ny).uniform(-1, 1, size=(nx, ny)))
+    arrs = []
+    for tid in owned:
+        sb = subs[tid - 1]
+        li = sb.internal
+        a = np.full((sb.glob.nx, sb.glob.ny), -7.0, order="F")     # the tile's full extent incl. halos
+        gi = sb.glob.xstart + np.arange(li.nx) - 1
+        gj = sb.glob.ystart + np.arange(li.ny) - 1
+        a[li.xstart - 1:li.xstop, li.ystart - 1:li.ystop] = G[np.ix_(gi, gj)]
+        arrs.append(a)
+    before = [a.copy() for a in arrs]
+    sendbuf, recvbuf = np.zeros(send_total), np.zeros(recv_total)
+    peers_s, peers_r = {}, {}
+    for kind, peer, st, dt_, si0, sj0, di0, dj0, w, h, off, dst_id, src_id, dirn in rows.tolist():
+        if kind == 0:       # same-rank neighbour: a copy that never leaves the device
+            ok(peer == RANK, "copy segments stay on this rank")
+            arrs[dt_][di0 - 1:di0 - 1 + w, dj0 - 1:dj0 - 1 + h] = before[st][si0 - 1:si0 - 1 + w, sj0 - 1:sj0 - 1 + h]
+        elif kind == 1:
+            sendbuf[off:off + w * h] = before[st][si0 - 1:si0 - 1 + w, sj0 - 1:sj0 - 1 + h].flatten(order="F")
+            lo, n = peers_s.get(peer, (off, 0))
+            peers_s[peer] = (min(lo, off), n + w * h)
+        else:
+            lo, n = peers_r.get(peer, (off, 0))
+            peers_r[peer] = (min(lo, off), n + w * h)
+    ok(set(peers_s) == set(peers_r), "a rank sends to exactly the ranks it receives from")
+    ops, views = [], []
+    for peer, (lo, n) in sorted(peers_s.items()):
+        ops.append(dist.P2POp(dist.isend, torch.from_numpy(sendbuf[lo:lo + n].copy()), peer))
+    for peer, (lo, n) in sorted(peers_r.items()):
+        t = torch.zeros(n, dtype=torch.float64)
+        views.append((lo, n, t))
+        ops.append(dist.P2POp(dist.irecv, t, peer))
+    if ops:
+        for w_ in dist.batch_isend_irecv(ops):
+            w_.wait()
+    for lo, n, t in views:
+        recvbuf[lo:lo + n] = t.numpy()
+    for kind, peer, st, dt_, si0, sj0, di0, dj0, w, h, off, dst_id, src_id, dirn in rows.tolist():
+        if kind == 2:
+            arrs[dt_][di0 - 1:di0 - 1 + w, dj0 - 1:dj0 - 1 + h] = recvbuf[off:off + w * h].reshape((w, h), order="F")
+    for tid, a in zip(owned, arrs):
+        sb = subs[tid - 1]
+        li = sb.internal
+        for ji in range(li.xstart - depth, li.xstop + depth + 1):
+            for jj in range(li.ystart - depth, li.ystop + depth + 1):
+                gx, gy = sb.glob.xstart + ji - li.xstart, sb.glob.ystart + jj - li.ystart
+                if periodic:
+                    want = G[(gx - 1) % nx, (gy - 1) % ny]
+                elif 1 <= gx <= nx and 1 <= gy <= ny:
+                    want = G[gx - 1, gy - 1]
+                else:
+                    want = -7.0
+                ok(a[ji - 1, jj - 1] == want, "tile %d cell (%d,%d) after the tile-set exchange (%dx%d, %d tiles "
+                   "per rank, periodic=%s, depth %d)" % (tid, ji, jj, nx, ny, tiles_per_rank, periodic, depth))
+    fd.gocean_initialise(RANK + 1, WORLD)            # go_decompose's SAVEd halo width back to 1
+
+
 def main():
     dist.init_process_group("gloo")
     fd.gocean_initialise(RANK + 1, WORLD)            # host only: no device, no NCCL
@@ -255,6 +328,12 @@ def main():
     case_depth(40, 36, 3)
     for shape in ((16, 24), (37, 23), (64, 48)):
         case_depth_periodic(*shape)
+    for tpr in (2, 3):
+        case_tileset(48, 36, tpr, False)
+        case_tileset(48, 36, tpr, True)
+    case_tileset(37, 61, 2, True)
+    case_tileset(64, 48, 2, True, depth=2)
+    case_tileset(40, 40, 4, False, depth=2)
     dist.barrier()
     if RANK == 0:
         print("HOST DIST OK %d checks on %d ranks" % (NCHECK, WORLD), flush=True)

@@ -383,6 +383,79 @@ def case_shallow_water(n_x, n_y, nsteps, alignment, mode, halo_mode=None, two_st
         fd.gocean_initialise(RANK + 1, WORLD)       # resets go_decompose's SAVEd halo width to 1
 
 
+def case_tileset(n_x, n_y, tiles_per_rank, nsteps, alignment, masked=False):
+    """extension F3: `tiles_per_rank` sub-domains per rank (go_decompose(ndomains > nranks),
+    src/parallel_mod.f90:141-152; proc_subdomains, src/decomposition_mod.f90:64-67).  The periodic
+    shallow-water model on the tile set == the serial oracle on the undivided domain, bit for bit;
+    plus the halo known answer (every halo cell = the periodic global field at the wrapped position)."""
+    os.environ["DL_ESM_ALIGNMENT"] = str(alignment)
+    gmask = island_mask(n_x, n_y) if masked else None
+    osw = O.ShallowWater(n_x, n_y, alignment=1,
+                         tmask=np.asfortranarray(np.pad(gmask, 1, mode="wrap")) if masked else None)
+    oi = osw.fb["t"].internal
+    core = (slice(oi.xstart - 1, oi.xstop), slice(oi.ystart - 1, oi.ystop))
+    init = {k: np.asfortranarray(osw.f[k][core]) for k in ("u", "v", "p")}
+    for _ in range(nsteps):
+        osw.step()
+    ts = fd.tileset(fd.GO_ARAKAWA_C, BCS_PER, fd.GO_OFFSET_SW, n_x, n_y, ndomains=tiles_per_rank * WORLD)
+    ok(ts.ntiles == tiles_per_rank and ts.tile_ids[0] == RANK * tiles_per_rank + 1, "tiles owned by this rank")
+
+    def local(k, G, halo=0, fill=0.0):
+        g = ts.grids[k]
+        sb, li = g.subdomain, g.subdomain.internal
+        a = np.full((g.nx, g.ny), fill, order="F")
+        ji = np.arange(li.xstart - halo, li.xstop + halo + 1)
+        jj = np.arange(li.ystart - halo, li.ystop + halo + 1)
+        gi = (sb.glob.xstart + (ji - li.xstart) - 1) % n_x
+        gj = (sb.glob.ystart + (jj - li.ystart) - 1) % n_y
+        a[np.ix_(ji - 1, jj - 1)] = G[np.ix_(gi, gj)]
+        return a
+
+    for k, g in enumerate(ts.grids):
+        tm = None
+        if masked:
+            sb = g.subdomain
+            mi = (sb.glob.xstart - 2 + np.arange(sb.glob.nx)) % n_x
+            mj = (sb.glob.ystart - 2 + np.arange(sb.glob.ny)) % n_y
+            tm = np.asfortranarray(gmask[np.ix_(mi, mj)])
+        fd.grid_init(g, 1.0e5, 1.0e5, tm)
+    # halo known answer on two fields at once
+    G = np.asfortranarray(np.random.default_rng(n_x * 13 + n_y).uniform(-1, 1, size=(n_x, n_y)))
+    fa = [fd.r2d_field(g, fd.GO_T_POINTS) for g in ts.grids]
+    fb = [fd.r2d_field(g, fd.GO_V_POINTS) for g in ts.grids]
+    for k in range(ts.ntiles):
+        fa[k].set_data(local(k, G, fill=-7.0))
+        fb[k].set_data(local(k, -G, fill=-7.0))
+    ts.halo_exchange([fa, fb])
+    for k in range(ts.ntiles):
+        li = ts.grids[k].subdomain.internal
+        sl = (slice(li.xstart - 2, li.xstop + 1), slice(li.ystart - 2, li.ystop + 1))
+        ok(np.array_equal(fa[k].get_data()[sl], local(k, G, halo=1)[sl]), "tile-set halo exchange, field 1 tile %d" % k)
+        ok(np.array_equal(fb[k].get_data()[sl], local(k, -G, halo=1)[sl]), "tile-set halo exchange, field 2 tile %d" % k)
+    out = ts.gather_inner_data(fa)
+    if RANK == 0:
+        ok(np.array_equal(out, G), "tile-set gather_inner_data")
+    for f in fa + fb:
+        f.free()
+    # the model
+    swt = fd.shallow_water_tiles(ts, use_tmask=masked)
+    swt.set_state([tuple(local(k, init[n]) for n in ("u", "v", "p")) for k in range(ts.ntiles)])
+    swt.step(nsteps)
+    fd.dev_sync()
+    for name in ("u", "v", "p", "uold", "vold", "pold"):
+        out = swt.gather(name)
+        if RANK == 0:
+            want = osw.f[name][core]
+            ok(np.array_equal(out, want), "tile-set shallow water %dx%d, %d tiles per rank, field %s: %d cells differ"
+               % (n_x, n_y, tiles_per_rank, name, int((out != want).sum())))
+    for a, b in zip(swt.checksums(), osw.checksums()):
+        ok(abs(a - b) <= 1e-12 * abs(b), "tile-set checksum %r vs oracle %r" % (a, b))
+    swt.free()
+    ts.free()
+    os.environ.pop("DL_ESM_ALIGNMENT", None)
+    fd.gocean_initialise(RANK + 1, WORLD)
+
+
 def main():
     bring_up()
     case_example_model()
@@ -426,6 +499,11 @@ def main():
     for shape in ((300, 523, 8, 64), (1024, 1024, 9, 64)):
         case_shallow_water(*shape, fd.SW_FUSED, halo_mode=fd.HALO_PUSH, two_step=True, arith=fd.ARITH_CONTRACTED)
         case_shallow_water(*shape, fd.SW_FUSED, halo_mode=fd.HALO_PUSH, arith=fd.ARITH_CONTRACTED)
+    # several sub-domains per rank (extension F3): 2 and 3 tiles per rank, with and without land
+    case_tileset(64, 96, 2, 5, 2)
+    case_tileset(130, 77, 3, 4, 64)
+    case_tileset(300, 523, 2, 6, 64, masked=True)
+    case_tileset(1024, 1024, 2, 5, 64)
     dist.barrier()
     fd.gocean_finalise()
     if RANK == 0:

@@ -767,8 +767,9 @@ def test_step_host_two_steps_per_round_trip_matches_oracle(n_x, n_y, align, band
         oi, ii = osw.fb["t"].internal, sw.field("p").internal
         core = (slice(oi.xstart - 1, oi.xstop), slice(oi.ystart - 1, oi.ystop))
         ring2 = (slice(ii.xstart - 3, ii.xstop + 2), slice(ii.ystart - 3, ii.ystop + 2))
-        # the old fields' ring must be valid on the way in (two-step reads them one cell out)
-        for q in (3, 4, 5):
+        # the two-cell ring of all six fields must be valid on the way in (a one-step sweep leaves
+        # only u,v,p with a one-cell ring)
+        for q in range(6):
             host[q][ring2] = np.pad(osw.f[names[q]][core], 2, mode="wrap")
         for trip in range(3):
             osw.step(); osw.step()
@@ -1106,3 +1107,100 @@ def test_dirty_flag_halos_in_the_exchange_engine(monkeypatch):
     finally:
         fd.set_extensions(0)
         assert L.dlesm_dev_set_comms(None) == 0
+
+
+# ---------------------------------------------------------------------------------------------
+# several sub-domains per rank (extension F3: src/decomposition_mod.f90:64-67, the \TODO of
+# src/parallel_comms_mod.f90:295).  One GPU here = one rank owning every tile; tests/dist_worker.py
+# runs 2 tiles per rank across GPUs.
+# ---------------------------------------------------------------------------------------------
+def tile_local(ts, k, G, halo=0, fill=0.0):
+    """tile k's local array holding its piece of the periodic global field G (internal points, plus
+    `halo` wrapped cells around them)"""
+    g = ts.grids[k]
+    sb, li = g.subdomain, g.subdomain.internal
+    nx, ny = G.shape
+    a = np.full((g.nx, g.ny), fill, order="F")
+    ji = np.arange(li.xstart - halo, li.xstop + halo + 1)
+    jj = np.arange(li.ystart - halo, li.ystop + halo + 1)
+    gi = (sb.glob.xstart + (ji - li.xstart) - 1) % nx
+    gj = (sb.glob.ystart + (jj - li.ystart) - 1) % ny
+    a[np.ix_(ji - 1, jj - 1)] = G[np.ix_(gi, gj)]
+    return a
+
+
+@pytest.mark.parametrize("n_x,n_y,ntiles,align,depth", [(48, 36, 4, None, 1), (130, 77, 6, 64, 1), (64, 96, 4, 2, 2),
+                                                        (37, 61, 2, None, 1), (96, 40, 1, 64, 1)])
+def test_tileset_halo_exchange_periodic(n_x, n_y, ntiles, align, depth, monkeypatch):
+    """every halo cell of every tile, corners included, holds the periodic global field at the wrapped
+    position after ONE exchange over the tile set (same-rank neighbours: device copies)"""
+    if align:
+        monkeypatch.setenv("DL_ESM_ALIGNMENT", str(align))
+    try:
+        ts = fd.tileset(fd.GO_ARAKAWA_C, BCS_PER, fd.GO_OFFSET_SW, n_x, n_y, ndomains=ntiles, halo_width=depth)
+        assert ts.ntiles == ntiles and ts.tile_ids == list(range(1, ntiles + 1))
+        G = np.asfortranarray(np.random.default_rng(n_x + n_y).uniform(-1, 1, size=(n_x, n_y)))
+        H = -G
+        fa, fb = [], []
+        for k, g in enumerate(ts.grids):
+            fd.grid_init(g, 1.0e5, 1.0e5)
+            f1, f2 = fd.r2d_field(g, fd.GO_T_POINTS), fd.r2d_field(g, fd.GO_U_POINTS)
+            f1.set_data(tile_local(ts, k, G, fill=-7.0))
+            f2.set_data(tile_local(ts, k, H, fill=-7.0))
+            fa.append(f1); fb.append(f2)
+        n0 = fd.kernel_launch_count()
+        ts.halo_exchange([fa, fb], depth=depth)
+        assert fd.kernel_launch_count() - n0 == 1            # every copy of both fields in one launch
+        for k in range(ntiles):
+            li = ts.grids[k].subdomain.internal
+            sl = (slice(li.xstart - 1 - depth, li.xstop + depth), slice(li.ystart - 1 - depth, li.ystop + depth))
+            assert np.array_equal(fa[k].get_data()[sl], tile_local(ts, k, G, halo=depth)[sl]), k
+            assert np.array_equal(fb[k].get_data()[sl], tile_local(ts, k, H, halo=depth)[sl]), k
+        # gather_inner_data over the tile set gives the global field back
+        assert np.array_equal(ts.gather_inner_data(fa), G)
+        for f in fa + fb:
+            f.free()
+        ts.free()
+    finally:
+        _lib.lib().dlesm_reset_saved_state()
+
+
+@pytest.mark.parametrize("n_x,n_y,ntiles,align,masked", [(64, 64, 4, 2, False), (130, 77, 2, 64, False),
+                                                         (300, 523, 6, 64, True), (1024, 1024, 4, 64, False),
+                                                         (257, 300, 3, 2, True)])
+def test_tileset_shallow_water_matches_serial_oracle(n_x, n_y, ntiles, align, masked, monkeypatch):
+    """the periodic shallow-water model on `ntiles` sub-domains of one rank (fused sweep per tile, one
+    exchange per step) == the serial oracle on the undivided domain, bit for bit, every prognostic field"""
+    monkeypatch.setenv("DL_ESM_ALIGNMENT", str(align))
+    try:
+        gm = periodic_island_mask(n_x + 2, n_y + 2, 12345) if masked else None
+        osw = O.ShallowWater(n_x, n_y, alignment=align, tmask=gm)
+        oi = osw.fb["t"].internal
+        core = (slice(oi.xstart - 1, oi.xstop), slice(oi.ystart - 1, oi.ystop))
+        init = {n: np.asfortranarray(osw.f[n][core]) for n in ("u", "v", "p")}
+        ts = fd.tileset(fd.GO_ARAKAWA_C, BCS_PER, fd.GO_OFFSET_SW, n_x, n_y, ndomains=ntiles)
+        for k, g in enumerate(ts.grids):
+            tm = None
+            if masked:      # this tile's part of the mask over its whole extent (halo cells wrap)
+                sb = g.subdomain
+                mi = (sb.glob.xstart - 2 + np.arange(sb.glob.nx)) % n_x
+                mj = (sb.glob.ystart - 2 + np.arange(sb.glob.ny)) % n_y
+                tm = np.asfortranarray(gm[1:-1, 1:-1][np.ix_(mi, mj)])
+            fd.grid_init(g, 1.0e5, 1.0e5, tm)
+        swt = fd.shallow_water_tiles(ts, use_tmask=masked)
+        swt.set_state([tuple(tile_local(ts, k, init[n]) for n in ("u", "v", "p")) for k in range(ntiles)])
+        for _ in range(5):
+            osw.step()
+        swt.step(2)
+        swt.step(3)
+        for name in ("u", "v", "p", "uold", "vold", "pold"):
+            got = swt.gather(name)
+            assert np.array_equal(got, osw.f[name][core]), (name, int((got != osw.f[name][core]).sum()))
+        for a, b in zip(swt.checksums(), osw.checksums()):
+            assert abs(a - b) <= RTOL * abs(b)
+        with pytest.raises(fd.GoceanStop):      # a tile's model is stepped through the set
+            swt.models[0].step(1)
+        swt.free()
+        ts.free()
+    finally:
+        _lib.lib().dlesm_reset_saved_state()
