@@ -154,6 +154,7 @@ SIGNATURES = {
     "dlesm_dev_set_comms": (_I, [C.POINTER(Comms)]),
     "dlesm_dev_halo_exchange": (_I, [C.POINTER(_V), _I]),
     "dlesm_host_halo_exchange": (_I, [_PD, _I, _I]),
+    "dlesm_dev_set_exchange_mode": (_I, [_I]),
     "dlesm_dev_peer_register": (_I, [C.POINTER(_V), _I]),
     "dlesm_dev_peer_unregister": (_I, [C.POINTER(_V), _I]),
     "dlesm_dev_peer_unregister_all": (_I, []),

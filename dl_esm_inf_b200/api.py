@@ -412,6 +412,15 @@ def make_region(xstart, xstop, ystart, ystop) -> Region:
     return Region(xstop - xstart + 1, ystop - ystart + 1, xstart, xstop, ystart, ystop)
 
 
+EXCHANGE_DIRECT, EXCHANGE_NCCL = 0, 1
+
+
+def set_exchange_mode(mode):
+    """EXCHANGE_DIRECT (default): halo patches go straight into the neighbours' receive slots over NVLink
+    peer memory; EXCHANGE_NCCL: pack -> ncclSend/ncclRecv -> unpack.  Same on every rank."""
+    _chk(_lib.lib().dlesm_dev_set_exchange_mode(int(mode)))
+
+
 def dev_sync():
     _chk(_lib.lib().dlesm_dev_sync())
 

@@ -158,12 +158,19 @@ __device__ inline double block_sum_256(double v)
     return r;  // valid in warp 0
 }
 
-__global__ void __launch_bounds__(256) abs_sum_rows_kernel(const double *__restrict__ f, int pitch,
-                                                           Box b, double *__restrict__ partials)
+// One launch: every block leaves its partial, takes a ticket, and the block that draws the last
+// ticket folds all partials in index order (so the sum does not depend on which block that is) and
+// stores the result on the device and, when asked, straight into mapped pinned host memory -- the
+// caller then needs a stream synchronise, no copy.  Blocks beyond the row count leave 0.0: the
+// fold tree is the one of a kChecksumBlocks-wide launch whatever the field's height.
+__global__ void __launch_bounds__(256) abs_sum_fold_kernel(const double *__restrict__ f, int pitch, Box b,
+                                                           double *__restrict__ partials, int npartials,
+                                                           unsigned *ticket, double *__restrict__ result,
+                                                           double *host_result)
 {
     const int w = b.xe - b.xs + 1;
     double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
-    for (int j = b.ys + blockIdx.x; j <= b.ye; j += gridDim.x) {
+    for (int j = b.ys + blockIdx.x; j <= b.ye; j += npartials) {
         const double *row = f + idx(pitch, b.xs, j);
         int i = threadIdx.x;
         for (; i + 768 < w; i += 1024) {
@@ -174,25 +181,31 @@ __global__ void __launch_bounds__(256) abs_sum_rows_kernel(const double *__restr
         for (; i < w; i += 256) a0 += fabs(__ldcs(row + i));
     }
     const double r = block_sum_256((a0 + a1) + (a2 + a3));
-    if (threadIdx.x == 0) partials[blockIdx.x] = r;
-}
-
-__global__ void __launch_bounds__(256) fold_partials_kernel(const double *__restrict__ partials,
-                                                            int n, double *__restrict__ result)
-{
+    __shared__ bool last;
+    if (threadIdx.x == 0) {
+        partials[blockIdx.x] = r;
+        __threadfence();
+        last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (!last) return;
+    __threadfence();
     double a = 0.0;
-    for (int t = threadIdx.x; t < n; t += 256) a += partials[t];
-    const double r = block_sum_256(a);
-    if (threadIdx.x == 0) *result = r;
+    for (int t = threadIdx.x; t < npartials; t += 256) a += t < static_cast<int>(gridDim.x) ? __ldcg(partials + t) : 0.0;
+    const double tot = block_sum_256(a);
+    if (threadIdx.x == 0) {
+        *result = tot;
+        if (host_result) *host_result = tot;
+        *ticket = 0u;
+    }
 }
 
-cudaError_t checksum(const double *f, int pitch, Box b, double *partials, double *result,
-                     cudaStream_t s)
+cudaError_t checksum(const double *f, int pitch, Box b, double *partials, unsigned *ticket, double *result,
+                     double *host_result, cudaStream_t s)
 {
-    if (b.xe < b.xs || b.ye < b.ys) return cudaMemsetAsync(result, 0, sizeof(double), s);
-    abs_sum_rows_kernel<<<kChecksumBlocks, 256, 0, s>>>(f, pitch, b, partials);
-    fold_partials_kernel<<<1, 256, 0, s>>>(partials, kChecksumBlocks, result);
-    count_launch();
+    const int rows = b.ye - b.ys + 1;
+    const int blocks = rows < 1 || b.xe < b.xs ? 1 : (rows < kChecksumBlocks ? rows : kChecksumBlocks);
+    abs_sum_fold_kernel<<<blocks, 256, 0, s>>>(f, pitch, b, partials, kChecksumBlocks, ticket, result, host_result);
     count_launch();
     return cudaGetLastError();
 }
@@ -403,6 +416,91 @@ cudaError_t pack(const PackPlan &plan, double *buffer, cudaStream_t s) { return 
 cudaError_t unpack(const PackPlan &plan, const double *buffer, cudaStream_t s)
 {
     return pack_launch(plan, const_cast<double *>(buffer), false, s);
+}
+
+// ---------------------------------------------------------------------------------------
+// Direct halo exchange over peer memory (see XPlan in the header).  blockIdx.y = segment * nfields
+// + field as in pack_kernel; the packed layout inside a slot is the same (field-major inside a
+// segment, j outer / i inner inside a field), so what lands in the neighbour's slot is byte for
+// byte what NCCL would have delivered.
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) xdirect_send_kernel(const __grid_constant__ XPlan plan, unsigned *ticket)
+{
+    const int sidx = blockIdx.y / plan.nfields, kf = blockIdx.y - sidx * plan.nfields;
+    const XSegment &sg = plan.seg[sidx];
+    const long long n = static_cast<long long>(sg.nx) * sg.ny;
+    double *buf = sg.buf + static_cast<long long>(kf) * n;
+    const double *f = plan.fields[kf];
+    for (long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; t < n;
+         t += static_cast<long long>(gridDim.x) * blockDim.x) {
+        const int jj = static_cast<int>(t / sg.nx), ii = static_cast<int>(t - static_cast<long long>(jj) * sg.nx);
+        buf[t] = f[idx(plan.pitch, sg.i0 + ii, sg.j0 + jj)];
+    }
+    // every thread's peer stores ordered before the ticket; the last block publishes
+    __threadfence_system();
+    __syncthreads();
+    __shared__ bool last;
+    if (threadIdx.x == 0) last = atomicAdd(ticket, 1u) == gridDim.x * gridDim.y - 1;
+    __syncthreads();
+    if (!last) return;
+    if (threadIdx.x < plan.npeers) {
+        __threadfence_system();
+        asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(plan.flag[threadIdx.x]), "l"(plan.count[threadIdx.x])
+                     : "memory");
+    }
+    if (threadIdx.x == 0) *ticket = 0u;
+}
+
+__global__ void __launch_bounds__(256) xdirect_recv_kernel(const __grid_constant__ XPlan plan, int *err)
+{
+    if (threadIdx.x < plan.npeers) {
+        const long long t0 = clock64();
+        for (;;) {
+            unsigned long long v;
+            asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(plan.flag[threadIdx.x]) : "memory");
+            if (v >= plan.count[threadIdx.x]) break;
+            if (clock64() - t0 > 40000000000LL) {   // ~20 s: the ranks are out of step -- fatal, as in the halo push
+                atomicExch(err, 1);
+                __threadfence_system();
+                __trap();
+            }
+            __nanosleep(100);
+        }
+    }
+    __syncthreads();
+    const int sidx = blockIdx.y / plan.nfields, kf = blockIdx.y - sidx * plan.nfields;
+    const XSegment &sg = plan.seg[sidx];
+    const long long n = static_cast<long long>(sg.nx) * sg.ny;
+    const double *buf = sg.buf + static_cast<long long>(kf) * n;
+    double *f = plan.fields[kf];
+    for (long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; t < n;
+         t += static_cast<long long>(gridDim.x) * blockDim.x) {
+        const int jj = static_cast<int>(t / sg.nx), ii = static_cast<int>(t - static_cast<long long>(jj) * sg.nx);
+        f[idx(plan.pitch, sg.i0 + ii, sg.j0 + jj)] = __ldcg(buf + t);   // written by a peer: not through L1
+    }
+}
+
+static dim3 xdirect_grid(const XPlan &plan)
+{
+    long long nmax = 1;
+    for (int q = 0; q < plan.nseg; ++q)
+        nmax = std::max(nmax, static_cast<long long>(plan.seg[q].nx) * plan.seg[q].ny);
+    return dim3(nmax / 256 + 1 < 32 ? static_cast<unsigned>(nmax / 256 + 1) : 32u,
+                static_cast<unsigned>(plan.nseg * plan.nfields));
+}
+cudaError_t xdirect_send(const XPlan &plan, unsigned *ticket, cudaStream_t s)
+{
+    if (plan.nseg <= 0 || plan.nfields <= 0) return cudaSuccess;
+    xdirect_send_kernel<<<xdirect_grid(plan), 256, 0, s>>>(plan, ticket);
+    count_launch();
+    return cudaGetLastError();
+}
+cudaError_t xdirect_recv(const XPlan &plan, int *err, cudaStream_t s)
+{
+    if (plan.nseg <= 0 || plan.nfields <= 0) return cudaSuccess;
+    xdirect_recv_kernel<<<xdirect_grid(plan), 256, 0, s>>>(plan, err);
+    count_launch();
+    return cudaGetLastError();
 }
 
 // ---------------------------------------------------------------------------------------

@@ -54,10 +54,11 @@ inline SwScalars make_scalars(double dx, double dy, double tdt, double alpha, in
 cudaError_t copy_field(const double *in, double *out, size_t n, cudaStream_t s);
 cudaError_t set_field(double *f, size_t n, double val, cudaStream_t s);
 cudaError_t copy_patch(double *f, int pitch, Box src, Box dst, double *scratch, cudaStream_t s);
-// partials: >= kChecksumBlocks doubles of scratch; result: 1 double (device)
+// partials: >= kChecksumBlocks doubles of scratch; ticket: one zeroed unsigned (left zero again);
+// result: 1 double (device); host_result: mapped pinned double or null.  One launch.
 constexpr int kChecksumBlocks = 1184;  // 148 SMs x 8
-cudaError_t checksum(const double *f, int pitch, Box b, double *partials, double *result,
-                     cudaStream_t s);
+cudaError_t checksum(const double *f, int pitch, Box b, double *partials, unsigned *ticket, double *result,
+                     double *host_result, cudaStream_t s);
 cudaError_t periodic_halos(double *const *fields, int nfields, int pitch, Box internal,
                            bool periodic_x, bool periodic_y, cudaStream_t s);
 cudaError_t pack(const PackPlan &plan, double *buffer, cudaStream_t s);
@@ -67,6 +68,27 @@ cudaError_t broadcast_y(double *out, int nx, int ny, const double *yvec, cudaStr
 cudaError_t scatter_global(double *f, int pitch, Box box, const double *global, int gnx, int dx,
                            int dy, cudaStream_t s);
 cudaError_t gather_box(const double *f, int pitch, Box box, double *packed, cudaStream_t s);
+
+// Direct halo exchange (exchange_generic over NVLink peer memory instead of pack -> NCCL -> unpack).
+// Every rank owns two receive buffers (used alternately per neighbour pair) divided into one slot
+// per direction tag, mapped by all its peers.  Launch 1 packs every send patch of every field
+// STRAIGHT INTO THE NEIGHBOUR'S slot (contiguous remote stores), and the block that finishes last
+// publishes the pair's exchange count into each neighbour's flag array (release, system scope).
+// Launch 2 waits (acquire) for the neighbours' counts and unpacks this rank's own slots.
+struct XSegment {
+    int i0, j0, nx, ny;      // patch in the local fields
+    double *buf;             // send: the neighbour's slot (peer memory); receive: this rank's slot
+};
+struct XPlan {
+    int nseg, nfields, pitch;
+    XSegment seg[kMaxSegments];
+    double *fields[kMaxExchangeFields];
+    int npeers;
+    unsigned long long *flag[kMaxSegments];     // send: neighbour's flag cell for this rank; receive: own cell for the neighbour
+    unsigned long long count[kMaxSegments];     // the pair's exchange count this launch publishes / waits for
+};
+cudaError_t xdirect_send(const XPlan &plan, unsigned *ticket, cudaStream_t s);
+cudaError_t xdirect_recv(const XPlan &plan, int *err, cudaStream_t s);
 
 // Tile-set exchange (several sub-domains per rank): a batch of rectangular copies, each between two
 // arrays of its own pitch -- tile to tile, tile to send buffer, receive buffer to tile.  Pointers

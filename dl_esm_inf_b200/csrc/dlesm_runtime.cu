@@ -63,7 +63,8 @@ struct Context {
     size_t ring_host_n = 0;
     double *partials = nullptr;   // checksum partials + result
     double *result = nullptr;
-    double *host_result = nullptr;  // pinned
+    double *host_result = nullptr;  // pinned (and, under UVA, writable by kernels: the checksum lands here)
+    unsigned *ticket = nullptr;     // last-block ticket of the one-launch checksum
     double *scratch = nullptr;      // patch scratch
     size_t scratch_n = 0;
     double *sendbuf = nullptr, *recvbuf = nullptr;
@@ -85,6 +86,17 @@ struct Context {
     std::vector<void *> flag_mappings;                // flag-array mappings, closed at finalise
     unsigned long long push_epoch = 0;
     int *push_err = nullptr;                          // device flag: a neighbour wait timed out
+    // direct halo exchange over peer memory (DLESM_EXCHANGE_DIRECT): one allocation per rank --
+    // [flag cells | ticket | err | receive buffer 0 | receive buffer 1] -- mapped by every rank
+    struct XDirect {
+        bool ready = false;
+        char *base = nullptr;
+        size_t slot_cap = 0;                          // elements per direction slot
+        std::vector<char *> peer_base;                // the same allocation on rank r (own for r = me)
+        std::vector<unsigned long long> count;        // exchanges done with rank r (equal on both ends)
+        std::vector<void *> mappings;
+    } xd;
+    int exchange_mode = -1;                           // -1: from DLESM_EXCHANGE at first use
     // arithmetic of the fused sweeps (dlesm_set_arith) and the tile-grid knob (GOCEAN_OMP_GRID)
     int arith = DLESM_ARITH_EXACT;
     k::SweepTiles sweep_tiles{0, 0};
@@ -249,8 +261,10 @@ extern "C" int dlesm_device_init(int device)
     CU(cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&c.s_h2d, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&c.s_d2h, cudaStreamNonBlocking));
-    CU(cudaMalloc(&c.partials, (k::kChecksumBlocks + 8) * sizeof(double)));
+    CU(cudaMalloc(&c.partials, (k::kChecksumBlocks + 16) * sizeof(double)));
     c.result = c.partials + k::kChecksumBlocks;
+    c.ticket = reinterpret_cast<unsigned *>(c.partials + k::kChecksumBlocks + 8);
+    CU(cudaMemset(c.ticket, 0, sizeof(unsigned)));
     CU(cudaMallocHost(&c.host_result, 8 * sizeof(double)));
     c.device = device;
     c.device_ready = true;
@@ -285,6 +299,17 @@ extern "C" int dlesm_parallel_finalise(void)
 {
     Context &c = ctx();
     if (c.device_ready) cudaStreamSynchronize(c.stream);
+    if (c.xd.ready) {
+        // importers close before the exporter frees: unmap, meet, then free
+        for (void *m : c.xd.mappings) cudaIpcCloseMemHandle(m);
+        c.xd.mappings.clear();
+        if (c.comm_ready && pstate().nranks > 1) {
+            double one = 1.0;
+            dlesm_global_sum(&one);
+        }
+        cudaFree(c.xd.base);
+        c.xd = Context::XDirect{};
+    }
     if (c.comm_ready) {
         ncclCommDestroy(c.comm);
         c.comm = nullptr;
@@ -644,8 +669,9 @@ extern "C" int dlesm_dev_checksum(const void *f, int xs, int xe, int ys, int ye,
         return DLESM_ERR_ARGS;
     }
     Context &c = ctx();
-    CU(k::checksum(static_cast<const double *>(f), r.nx, k::Box{xs, xe, ys, ye}, c.partials, c.result, c.stream));
-    CU(cudaMemcpyAsync(c.host_result, c.result, sizeof(double), cudaMemcpyDeviceToHost, c.stream));
+    // one launch; the folding block stores the sum straight into pinned host memory
+    CU(k::checksum(static_cast<const double *>(f), r.nx, k::Box{xs, xe, ys, ye}, c.partials, c.ticket, c.result,
+                   c.host_result, c.stream));
     CU(cudaStreamSynchronize(c.stream));
     *val = c.host_result[0];
     return DLESM_OK;
@@ -773,6 +799,8 @@ int build_tables(const dlesm_comms *t, int depth, CommTables &out)
 
 // exchange_generic on device-resident fields with the given tables.  With DLESM_EXT_DIRTY_HALOS
 // fields whose halos are already up to date to the tables' depth are left out (all clean: no launch).
+int xdirect_exchange(void *const *fields, int nfields, int pitch, const CommTables &ct, bool &done);
+
 int exchange_with(void *const *fields_in, int nfields_in, const CommTables &ct)
 {
     Context &c = ctx();
@@ -815,6 +843,16 @@ int exchange_with(void *const *fields_in, int nfields_in, const CommTables &ct)
             set_error(DLESM_ERR_ARGS, "halo_exchange: a receive patch of the installed tables lies outside the field (tables of another grid?)");
             return DLESM_ERR_ARGS;
         }
+    {
+        // default path: the send patches go straight into the neighbours' receive slots over NVLink
+        bool done = false;
+        rc = xdirect_exchange(fields, nfields, r0.nx, ct, done);
+        if (rc != DLESM_OK) return rc;
+        if (done) {
+            for (int q = 0; q < nfields; ++q) mark_clean(fields[q], ct.depth);
+            return DLESM_OK;
+        }
+    }
     const long long tot = std::max(ct.send_total, ct.recv_total) * nfields;
     rc = ensure_xbuf(static_cast<size_t>(tot) + 1);
     if (rc != DLESM_OK) return rc;
@@ -1153,6 +1191,134 @@ int peer_unregister_fields(void *const *fields, int nfields)
     return barrier_all();
 }
 }  // namespace
+
+namespace {
+constexpr size_t kXdFlagsBytes = 4096;     // flag cells [kMaxRanks] at 0, ticket at 1024, err at 1032
+
+// Collective, once per process (at the first direct exchange, which every rank reaches together):
+// allocate this rank's flag cells + two receive buffers as ONE allocation and map every rank's.
+int xdirect_setup()
+{
+    Context &c = ctx();
+    Context::XDirect &xd = c.xd;
+    const int nranks = pstate().nranks, me0 = pstate().rank - 1;
+    if (nranks > kMaxRanks) {
+        set_error(DLESM_ERR_ARGS, "direct exchange: too many ranks");
+        return DLESM_ERR_ARGS;
+    }
+    size_t mb = 64;
+    if (const char *e = std::getenv("DLESM_XDIRECT_MB")) mb = std::max(1L, std::atol(e));
+    xd.slot_cap = mb * (1u << 20) / sizeof(double) / 8;                // 8 direction slots per buffer
+    const size_t bytes = kXdFlagsBytes + 2 * 8 * xd.slot_cap * sizeof(double);
+    CU(cudaMalloc(&xd.base, bytes));
+    CU(cudaMemset(xd.base, 0, kXdFlagsBytes));
+    xd.peer_base.assign(nranks, nullptr);
+    xd.count.assign(nranks, 0);
+    xd.peer_base[me0] = xd.base;
+    if (nranks > 1) {
+        IpcEntry mine;
+        int rc = make_entry(xd.base, 0, 0, mine);
+        if (rc != DLESM_OK) return rc;
+        std::vector<IpcEntry> all(nranks);
+        rc = ensure_scratch((sizeof(IpcEntry) * (nranks + 1) + 7) / 8);
+        if (rc != DLESM_OK) return rc;
+        char *dsend = reinterpret_cast<char *>(c.scratch), *drecv = dsend + sizeof(IpcEntry);
+        CU(cudaMemcpyAsync(dsend, &mine, sizeof(IpcEntry), cudaMemcpyHostToDevice, c.stream));
+        NC(ncclAllGather(dsend, drecv, sizeof(IpcEntry), ncclChar, c.comm, c.stream));
+        CU(cudaMemcpyAsync(all.data(), drecv, sizeof(IpcEntry) * nranks, cudaMemcpyDeviceToHost, c.stream));
+        CU(cudaStreamSynchronize(c.stream));
+        for (int r = 0; r < nranks; ++r) {
+            if (r == me0) continue;
+            void *b = nullptr;
+            CU(cudaIpcOpenMemHandle(&b, all[r].handle, cudaIpcMemLazyEnablePeerAccess));
+            xd.mappings.push_back(b);
+            xd.peer_base[r] = static_cast<char *>(b) + all[r].offset;
+        }
+        int rc2 = barrier_all();     // nobody stores into a buffer before everybody has mapped
+        if (rc2 != DLESM_OK) return rc2;
+    }
+    xd.ready = true;
+    return DLESM_OK;
+}
+
+// exchange_generic (src/parallel_comms_mod.f90:1501-1855) with the neighbours' memory as the wire.
+// done = false: not taken (mode NCCL) -- the caller falls through to pack -> NCCL -> unpack.
+int xdirect_exchange(void *const *fields, int nfields, int pitch, const CommTables &ct, bool &done)
+{
+    Context &c = ctx();
+    done = false;
+    if (c.exchange_mode < 0) {
+        const char *e = std::getenv("DLESM_EXCHANGE");
+        c.exchange_mode = (e && std::strcmp(e, "nccl") == 0) ? DLESM_EXCHANGE_NCCL : DLESM_EXCHANGE_DIRECT;
+    }
+    if (c.exchange_mode != DLESM_EXCHANGE_DIRECT) return DLESM_OK;
+    const int me0 = pstate().rank - 1;
+    bool remote = false;
+    for (const auto &g : ct.groups) remote = remote || g.peer0 != me0;
+    if (remote && !c.comm_ready) {
+        set_error(DLESM_ERR_STATE, "halo_exchange: communicator not initialised (dlesm_comm_init)");
+        return DLESM_ERR_STATE;
+    }
+    if (!c.xd.ready) {
+        int rc = xdirect_setup();
+        if (rc != DLESM_OK) return rc;
+    }
+    Context::XDirect &xd = c.xd;
+    const dlesm_comms &t = ct.t;
+    k::XPlan sp{}, rp{};
+    sp.nfields = rp.nfields = nfields;
+    sp.pitch = rp.pitch = pitch;
+    for (int q = 0; q < nfields; ++q) sp.fields[q] = rp.fields[q] = static_cast<double *>(fields[q]);
+    auto slot = [&](char *base, unsigned long long cnt, int dir) {
+        return reinterpret_cast<double *>(base + kXdFlagsBytes) + ((cnt & 1) * 8 + (dir - 1)) * xd.slot_cap;
+    };
+    for (const auto &g : ct.groups) {
+        if (g.sends.empty() && g.recvs.empty()) continue;
+        if (g.peer0 < 0 || g.peer0 >= static_cast<int>(xd.peer_base.size()) || !xd.peer_base[g.peer0]) {
+            set_error(DLESM_ERR_STATE, "direct exchange: neighbour rank not mapped");
+            return DLESM_ERR_STATE;
+        }
+        const unsigned long long cnt = ++xd.count[g.peer0];
+        for (int s : g.sends) {
+            if (t.dirsend[s] < 1 || t.dirsend[s] > 8 ||
+                static_cast<size_t>(t.nxsend[s]) * t.nysend[s] * nfields > xd.slot_cap) {
+                set_error(DLESM_ERR_ARGS, "direct exchange: a message exceeds its slot (raise DLESM_XDIRECT_MB or set DLESM_EXCHANGE=nccl on every rank)");
+                return DLESM_ERR_ARGS;
+            }
+            k::XSegment &sg = sp.seg[sp.nseg++];
+            sg.i0 = t.isrcsend[s]; sg.j0 = t.jsrcsend[s]; sg.nx = t.nxsend[s]; sg.ny = t.nysend[s];
+            sg.buf = slot(xd.peer_base[g.peer0], cnt, t.dirsend[s]);
+        }
+        for (int r : g.recvs) {
+            k::XSegment &sg = rp.seg[rp.nseg++];
+            sg.i0 = t.idesrecv[r]; sg.j0 = t.jdesrecv[r]; sg.nx = t.nxrecv[r]; sg.ny = t.nyrecv[r];
+            sg.buf = slot(xd.base, cnt, t.dirrecv[r]);
+        }
+        // publish into the neighbour's cell for this rank; wait on this rank's cell for the neighbour
+        sp.flag[sp.npeers] = reinterpret_cast<unsigned long long *>(xd.peer_base[g.peer0]) + me0;
+        sp.count[sp.npeers++] = cnt;
+        rp.flag[rp.npeers] = reinterpret_cast<unsigned long long *>(xd.base) + g.peer0;
+        rp.count[rp.npeers++] = cnt;
+    }
+    unsigned *ticket = reinterpret_cast<unsigned *>(xd.base + 1024);
+    int *err = reinterpret_cast<int *>(xd.base + 1032);
+    CU(k::xdirect_send(sp, ticket, c.stream));
+    CU(k::xdirect_recv(rp, err, c.stream));
+    done = true;
+    return DLESM_OK;
+}
+}  // namespace
+
+extern "C" int dlesm_dev_set_exchange_mode(int mode)
+{
+    clear_error();
+    if (mode != DLESM_EXCHANGE_DIRECT && mode != DLESM_EXCHANGE_NCCL) {
+        set_error(DLESM_ERR_ARGS, "set_exchange_mode: DLESM_EXCHANGE_DIRECT or DLESM_EXCHANGE_NCCL");
+        return DLESM_ERR_ARGS;
+    }
+    ctx().exchange_mode = mode;
+    return DLESM_OK;
+}
 
 // Collective.  Drops the registration of these fields: the neighbours' mappings they hold are
 // released (closed when no other registered field uses the same allocation), then a barrier, after
@@ -2229,9 +2395,22 @@ extern "C" int dlesm_field_checksum(dlesm_field_t *f, double *val)
 {
     clear_error();
     const dlesm_region &in = f->fb.internal;
-    int rc = dlesm_dev_checksum(f->dptr, in.xstart, in.xstop, in.ystart, in.ystop, val);
+    if (pstate().nranks == 1) return dlesm_dev_checksum(f->dptr, in.xstart, in.xstop, in.ystart, in.ystop, val);
+    // several ranks: local sum -> all-reduce -> host, chained on the stream with one synchronise
+    Context &c = ctx();
+    int rc = ensure_device();
     if (rc != DLESM_OK) return rc;
-    return dlesm_global_sum(val);
+    if (!c.comm_ready) {
+        set_error(DLESM_ERR_STATE, "field_checksum: communicator not initialised (dlesm_comm_init)");
+        return DLESM_ERR_STATE;
+    }
+    CU(k::checksum(static_cast<const double *>(f->dptr), f->nx, box_of(in), c.partials, c.ticket, c.result, nullptr,
+                   c.stream));
+    NC(ncclAllReduce(c.result, c.result + 2, 1, ncclDouble, ncclSum, c.comm, c.stream));
+    CU(cudaMemcpyAsync(c.host_result + 2, c.result + 2, sizeof(double), cudaMemcpyDeviceToHost, c.stream));
+    CU(cudaStreamSynchronize(c.stream));
+    *val = c.host_result[2];
+    return DLESM_OK;
 }
 extern "C" int dlesm_free_field(dlesm_field_t *f)
 {

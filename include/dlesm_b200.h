@@ -383,6 +383,14 @@ int dlesm_dev_set_comms(const dlesm_comms *tables);
 /* exchange_generic (src/parallel_comms_mod.f90:1501-1855) on device-resident fields: fused
  * pack kernel -> grouped NCCL send/recv (self-neighbours: on-device) -> fused unpack kernel */
 int dlesm_dev_halo_exchange(void *const *fields, int nfields);
+/* How dlesm_dev_halo_exchange moves the patches between ranks.  DIRECT (default): one kernel packs every
+ * send patch straight into the neighbour's receive slot over NVLink peer memory and publishes a flag, a
+ * second waits for the neighbours' flags and unpacks -- two launches, no library call.  NCCL: pack kernel,
+ * grouped ncclSend/ncclRecv, unpack kernel.  Same result, bit for bit.  The mode must be the same on every
+ * rank; the environment variable DLESM_EXCHANGE=nccl|direct sets the initial value. */
+#define DLESM_EXCHANGE_DIRECT 0
+#define DLESM_EXCHANGE_NCCL 1
+int dlesm_dev_set_exchange_mode(int mode);
 /* fld%halo_exchange(depth) (src/field_mod.f90:1231-1256) for a field whose values are in HOST memory
  * (data_on_device false): send patches up to a staging array, device exchange, receive patches back.
  * host = fld%data (nx*ny, column-major).  A no-op on one rank, like the reference. */

@@ -465,6 +465,15 @@ def main():
     case_halos(10, 10, alignment=8)
     case_halos(64, 48, alignment=64)
     case_reduction(10)
+    # the same exchanges through pack -> ncclSend/ncclRecv -> unpack (the default above is the direct
+    # path: patches stored straight into the neighbours' receive slots over NVLink + flag hand-shake)
+    fd.set_exchange_mode(fd.EXCHANGE_NCCL)
+    for shape in ((10, 4), (4, 10), (10, 10), (37, 23)):
+        case_halos(*shape)
+    case_halos(64, 48, alignment=64)
+    case_shallow_water(130, 77, 4, 64, fd.SW_UNFUSED)
+    case_shallow_water(300, 523, 8, 64, fd.SW_FUSED, two_step=True)
+    fd.set_exchange_mode(fd.EXCHANGE_DIRECT)
     for mode in (fd.SW_UNFUSED, fd.SW_FUSED):
         case_shallow_water(64, 96, 5, 2, mode)
         case_shallow_water(130, 77, 4, 64, mode)

@@ -253,11 +253,14 @@ def test_only_x_or_only_y_periodic_halos():
         assert np.array_equal(f.get_data(), want)
 
 
-def test_exchange_engine_with_self_neighbours():
-    """One rank, wrap-around neighbours = itself: the device pack -> (on-device) deliver ->
-    unpack path of halo_exchange must reproduce the serial periodic fill bit for bit,
-    corners included, for one field and for several grouped fields."""
+@pytest.mark.parametrize("mode", ["direct", "nccl"])
+def test_exchange_engine_with_self_neighbours(mode):
+    """One rank, wrap-around neighbours = itself: halo_exchange must reproduce the serial periodic fill
+    bit for bit, corners included, for one field and for several grouped fields -- by the direct path
+    (patches stored straight into the receiver's slots + flag hand-shake, two launches) and by the
+    pack -> (on-device) deliver -> unpack path of the NCCL mode."""
     L = _lib.lib()
+    fd.set_exchange_mode(fd.EXCHANGE_DIRECT if mode == "direct" else fd.EXCHANGE_NCCL)
     g = make_grid(40, 27, offset=fd.GO_OFFSET_SW, bcs=BCS_PER, tmask=None)
     tables = fd.map_comms(g.decomp, 1, 1, pbc=(True, True))
     assert tables.nsend == 8 and tables.nrecv == 8
@@ -272,11 +275,27 @@ def test_exchange_engine_with_self_neighbours():
         of.data[:, :] = src
         of.apply_periodic_halos()
         wants.append(of.data)
+    n0 = fd.kernel_launch_count()
     flds[0].halo_exchange(1)
+    assert fd.kernel_launch_count() - n0 == 2          # send + receive, or pack + unpack
     assert np.array_equal(flds[0].get_data(), wants[0])
     fd.halo_exchange_fields(flds[1:])
     assert np.array_equal(flds[1].get_data(), wants[1])
     assert np.array_equal(flds[2].get_data(), wants[2])
+    # again and again: the receive buffers alternate per exchange, the pair counts keep in step
+    for it in range(5):
+        for k, f in enumerate(flds):
+            src = rnd((g.nx, g.ny), 400 + 10 * it + k)
+            f.set_data(src)
+            of = O.Field(og, (O.GO_U_POINTS, O.GO_V_POINTS, O.GO_T_POINTS)[k])
+            of.data[:, :] = src
+            of.apply_periodic_halos()
+            wants[k] = of.data
+        fd.halo_exchange_fields(flds)
+        for k, f in enumerate(flds):
+            assert np.array_equal(f.get_data(), wants[k]), (it, k)
+    fd.dev_sync()
+    fd.set_exchange_mode(fd.EXCHANGE_DIRECT)
     empty = fd.Comms()
     assert L.dlesm_dev_set_comms(C.byref(empty)) == 0   # leave the module state clean
 

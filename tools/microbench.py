@@ -178,12 +178,17 @@ def main():
                     fl = [fd.r2d_field(g2, fd.GO_T_POINTS) for _ in range(nf)]
                     for f in fl:
                         fd.set_field(f, float(rank + 1))
-                    us = timed(lambda: fd.halo_exchange_fields(fl, depth), reps)
-                    emit(op="halo_exchange", local_tile="%dx%d" % (n, n), n_gpus=world, depth=depth, fields=nf,
-                         tiles="%dx%d" % (probe.nx, probe.ny), us_per_call=us, rank1_bytes_sent=sent * nf,
-                         rank1_bytes_received=recv * nf, messages=c.nsend,
-                         nvlink_frac_of_900GBs_per_dir=max(sent, recv) * nf / (us * 1e-6) / 900e9,
-                         how="pack kernel -> grouped ncclSend/ncclRecv -> unpack kernel")
+                    for mode, how in ((fd.EXCHANGE_DIRECT, "direct: send kernel stores the patches into the neighbours' "
+                                       "receive slots over NVLink + flag, receive kernel waits and unpacks"),
+                                      (fd.EXCHANGE_NCCL, "pack kernel -> grouped ncclSend/ncclRecv -> unpack kernel")):
+                        fd.set_exchange_mode(mode)
+                        us = timed(lambda: fd.halo_exchange_fields(fl, depth), reps)
+                        emit(op="halo_exchange", local_tile="%dx%d" % (n, n), n_gpus=world, depth=depth, fields=nf,
+                             tiles="%dx%d" % (probe.nx, probe.ny), us_per_call=us, rank1_bytes_sent=sent * nf,
+                             rank1_bytes_received=recv * nf, messages=c.nsend,
+                             nvlink_frac_of_900GBs_per_dir=max(sent, recv) * nf / (us * 1e-6) / 900e9,
+                             mode="direct" if mode == fd.EXCHANGE_DIRECT else "nccl", how=how)
+                    fd.set_exchange_mode(fd.EXCHANGE_DIRECT)
                     for f in fl:
                         f.free()
                 fd.set_extensions(0)
