@@ -510,6 +510,22 @@ def run_ours(args):
     if world == 1 and not args.no_config3 and args.mode == "fused":
         config3 = run_config3(args, fd, timed, sub_record, np)
 
+    # ---- BASELINE configs[3] "(strong/weak)": the same --size^2 domain split over the N GPUs ----
+    strong = None
+    if world > 1 and args.scaling == "weak" and not args.no_strong and args.mode == "fused":
+        strong = {}
+        for label, two_step in (("two_step", True), ("one_step", False)):
+            r = timed(two_step, scaling="strong", steps=max(args.steps, 40), sustain_s=0.0)
+            r["sw"].free()
+            r["sw"] = None
+            strong[label] = sub_record(r)
+            strong[label]["tile"] = "%dx%d per GPU, global %dx%d" % (r["sub"].internal.nx, r["sub"].internal.ny,
+                                                                   r["gx"], r["gy"])
+    # ---- BASELINE configs[4]: halo_exchange + field_checksum microbench on small and large local tiles ----
+    config5 = None
+    if not args.no_config5:
+        config5 = run_config5(args, fd, L, C, world, rank, max_over_ranks, barrier)
+
     sampler.stop_flag = True
 
     # ---- cpu baseline (rank 0, N=1 only): bounded sample on the box's host cores; its checksums are the
@@ -578,6 +594,10 @@ def run_ours(args):
             line["other_arithmetic"] = sub_record(other)
         if config3 is not None:
             line["config3"] = config3
+        if strong is not None:
+            line["strong"] = strong
+        if config5 is not None:
+            line["config5"] = config5
         print(json.dumps(line), flush=True)
         if parity.get("mismatches"):
             print("PARITY MISMATCH at full size: see parity.full_size / config3.parity", file=sys.stderr, flush=True)
@@ -587,6 +607,63 @@ def run_ours(args):
         fd.gocean_finalise()
         dist.destroy_process_group()
     return rc
+
+
+def run_config5(args, fd, L, C, world, rank, max_over_ranks, barrier):
+    """BASELINE configs[4]: "Halo-exchange + field_checksum microbench (width-1/2 halos, 2048^2-32768^2 local
+    tiles, NE offset, external BCs -- the reference's dist-mem set-up)".  CUDA events on the library's stream,
+    20 calls after 3 warm-up calls, max over ranks.  halo_exchange (N > 1) in both modes: direct (patches
+    stored into the neighbours' receive slots over NVLink + flag hand-shake) and NCCL."""
+    out = []
+    reps = 20
+
+    def timed_us(fn):
+        for _ in range(3):
+            fn()
+        fd.dev_sync()
+        barrier()
+        L.dlesm_event_record(6)
+        for _ in range(reps):
+            fn()
+        L.dlesm_event_record(7)
+        ms = C.c_double(0.0)
+        assert L.dlesm_event_elapsed_ms(6, 7, C.byref(ms)) == 0
+        fd.dev_sync()
+        return max_over_ranks(ms.value) / reps * 1e3
+
+    bcs = (fd.GO_BC_EXTERNAL, fd.GO_BC_EXTERNAL, fd.GO_BC_NONE)
+    for n in (2048, 4096, 16384):
+        fd.gocean_initialise(rank + 1, world)
+        probe = fd.go_decompose(n, n)
+        for depth in ((1, 2) if world > 1 else (1,)):
+            fd.gocean_initialise(rank + 1, world)              # go_decompose's SAVEd halo width back to 1
+            fd.set_extensions(fd.EXT_HALO_DEPTH)
+            g = fd.grid_type(fd.GO_ARAKAWA_C, bcs, fd.GO_OFFSET_NE)
+            g.decompose(n * probe.nx, n * probe.ny, halo_width=depth)
+            fd.grid_init(g, 1.0, 1.0)
+            f = fd.r2d_field(g, fd.GO_T_POINTS)
+            fd.set_field(f, 1.0)
+            rec = {"local_tile": "%dx%d" % (n, n), "halo_width": depth}
+            if depth == 1:
+                i = f.internal
+                us = timed_us(lambda: fd.field_checksum(f))
+                rec["field_checksum_us"] = us
+                rec["field_checksum_GBs"] = 8.0 * i.nx * i.ny / (us * 1e-6) / 1e9
+                want = float(i.nx * i.ny) * world
+                got = fd.field_checksum(f)
+                assert abs(got - want) <= 1e-12 * want, (got, want)      # known answer: N ranks x points x 1.0
+            if world > 1:
+                c = g.comms if depth == 1 else fd.map_comms(g.decomp, halo_depths=(depth, depth))
+                rec["halo_bytes_sent_rank1"] = sum(c.nxsend[q] * c.nysend[q] for q in range(c.nsend)) * 8
+                for mode, name in ((fd.EXCHANGE_DIRECT, "direct"), (fd.EXCHANGE_NCCL, "nccl")):
+                    fd.set_exchange_mode(mode)
+                    rec["halo_exchange_%s_us" % name] = timed_us(lambda: f.halo_exchange(depth))
+                fd.set_exchange_mode(fd.EXCHANGE_DIRECT)
+            out.append(rec)
+            f.free()
+            fd.set_extensions(0)
+    fd.gocean_initialise(rank + 1, world)
+    return out
 
 
 def run_config3(args, fd, timed, sub_record, np):
@@ -789,6 +866,8 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-parity", action="store_true", help="skip the pre-flight parity leg (profiling runs)")
     ap.add_argument("--no-config3", action="store_true", help="skip the config-3 (4096^2 + tmask) sub-record")
+    ap.add_argument("--no-strong", action="store_true", help="skip the strong-scaling sub-record (N > 1)")
+    ap.add_argument("--no-config5", action="store_true", help="skip the halo_exchange / field_checksum microbench")
     ap.add_argument("--sustain-s", type=float, default=3.0,
                     help="seconds of back-to-back steps of the sustained leg (0 = none)")
     ap.add_argument("--arith", choices=["exact", "fma"], default="exact",

@@ -5,7 +5,12 @@
 #include <cuda_runtime.h>
 #include <nccl.h>
 
+#include <sys/mman.h>
+#include <sys/syscall.h>
+#include <unistd.h>
+
 #include <algorithm>
+#include <cctype>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -554,15 +559,68 @@ extern "C" int dlesm_dev_sync(void)
     return DLESM_OK;
 }
 
+namespace {
+// NUMA node of the GPU this process drives (sysfs), -1 if unknown
+int gpu_numa_node()
+{
+    char bus[32] = {0};
+    if (cudaDeviceGetPCIBusId(bus, sizeof(bus), ctx().device) != cudaSuccess) return -1;
+    for (char *p = bus; *p; ++p) *p = static_cast<char>(std::tolower(*p));
+    const std::string path = std::string("/sys/bus/pci/devices/") + bus + "/numa_node";
+    FILE *f = std::fopen(path.c_str(), "r");
+    if (!f) return -1;
+    int node = -1;
+    if (std::fscanf(f, "%d", &node) != 1) node = -1;
+    std::fclose(f);
+    return node;
+}
+std::map<void *, size_t> &numa_allocs()
+{
+    static std::map<void *, size_t> m;
+    return m;
+}
+}  // namespace
+
+// Pinned host memory for the host-state step and the hooks.  With several GPUs per node every rank
+// would otherwise pin and stream from whichever node its launcher thread ran on (the round-1 scaling
+// run: all eight ranks on NUMA node 0); here the pages are placed on the GPU's own node first
+// (mmap + mbind(MPOL_PREFERRED) + first touch) and then registered.  Falls back to cudaMallocHost when
+// the node is unknown or DLESM_HOST_NUMA=0.
 extern "C" int dlesm_host_alloc(size_t bytes, void **host_ptr)
 {
     int rc = ensure_device();
     if (rc != DLESM_OK) return rc;
+    const char *e = std::getenv("DLESM_HOST_NUMA");
+    const int node = (e && std::atoi(e) == 0) ? -1 : gpu_numa_node();
+    if (node >= 0 && node < 1024 && bytes > 0) {
+        void *p = mmap(nullptr, bytes, PROT_READ | PROT_WRITE, MAP_PRIVATE | MAP_ANONYMOUS, -1, 0);
+        if (p != MAP_FAILED) {
+            unsigned long mask[16] = {0};
+            mask[node / (8 * sizeof(unsigned long))] |= 1UL << (node % (8 * sizeof(unsigned long)));
+            // MPOL_PREFERRED = 1: place on `node` when the cpuset allows it, anywhere otherwise
+            syscall(SYS_mbind, p, bytes, 1, mask, sizeof(mask) * 8, 0);
+            madvise(p, bytes, MADV_HUGEPAGE);
+            if (cudaHostRegister(p, bytes, cudaHostRegisterPortable) == cudaSuccess) {
+                numa_allocs()[p] = bytes;
+                *host_ptr = p;
+                return DLESM_OK;
+            }
+            cudaGetLastError();
+            munmap(p, bytes);
+        }
+    }
     CU(cudaMallocHost(host_ptr, bytes));
     return DLESM_OK;
 }
 extern "C" int dlesm_host_free(void *host_ptr)
 {
+    auto it = numa_allocs().find(host_ptr);
+    if (it != numa_allocs().end()) {
+        CU(cudaHostUnregister(host_ptr));
+        munmap(host_ptr, it->second);
+        numa_allocs().erase(it);
+        return DLESM_OK;
+    }
     CU(cudaFreeHost(host_ptr));
     return DLESM_OK;
 }

@@ -33,18 +33,24 @@ case $what in
     echo "dist_worker rc=$?" | tee -a gpurun_out/${T}_dist_worker_n$n.log
     grep -v "^\[W\|^W1\|OMP_NUM\|^\*\*\*" gpurun_out/${T}_dist_worker_n$n.log | tail -8 ;;
   launches)
-    CMD="python bench.py --steps 6 --warmup 3 --e2e-steps 0 --no-cpu-baseline --no-parity $*"
+    CMD="python bench.py --steps 6 --warmup 3 --e2e-steps 0 --no-cpu-baseline --no-parity --no-config5 --no-strong $*"
     $CMD > gpurun_out/${T}_plain.log 2>&1 &&
     ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv \
         --log-file gpurun_out/${T}_launches.csv $CMD > gpurun_out/${T}_ncu_launches.log 2>&1
     echo "launch list rc=$?" ;;
   ncu)
     re=$1; tag=$2; shift 2
-    CMD="python bench.py --steps 8 --warmup 3 --e2e-steps 0 --no-cpu-baseline --no-parity $*"
+    CMD="python bench.py --steps 8 --warmup 3 --e2e-steps 0 --no-cpu-baseline --no-parity --no-config5 --no-strong $*"
     $CMD > gpurun_out/${T}_${tag}_plain.log 2>&1 &&
     timeout ${TMO:-900} ncu --set full --clock-control none --import-source on -k regex:$re -s ${SKIP:-2} -c 1 \
         -o gpurun_out/${T}_${tag} -f $CMD > gpurun_out/${T}_${tag}_ncu.log 2>&1
     echo "ncu $tag rc=$?" ;;
+  probe)
+    { nvidia-smi topo -m; echo; cat /sys/devices/system/node/online; grep -H . /sys/devices/system/node/node*/cpulist
+      for d in /sys/bus/pci/devices/*; do c=$(cat $d/class 2>/dev/null); case $c in 0x0302*|0x0300*) echo "$d numa=$(cat $d/numa_node) $(cat $d/vendor)";; esac; done
+      cat /sys/fs/cgroup/cpuset.cpus.effective /sys/fs/cgroup/cpuset.mems.effective 2>/dev/null; nproc; free -g | head -2
+      grep -i "Mems_allowed_list\|Cpus_allowed_list" /proc/self/status; } > gpurun_out/${T}_probe.txt 2>&1
+    echo "probe rc=$?" ;;
   micro)
     timeout ${TMO:-900} python tools/microbench.py "$@" > gpurun_out/${T}_micro.jsonl 2> gpurun_out/${T}_micro.err
     echo "micro rc=$?"; tail -2 gpurun_out/${T}_micro.err ;;
