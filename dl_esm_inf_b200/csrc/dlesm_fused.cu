@@ -1154,11 +1154,33 @@ fused2w_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_consta
 
 // every segment recomputes two rows of the intermediate state and re-reads four raw rows, so
 // segments are longer than the one-step sweep's; DLESM_SEG_ROWS2 overrides
+// CTAs of `kern` one SM holds (registers and shared memory decide; __launch_bounds__' MINB is only a
+// floor): the wave size the segment height is rounded to.  A 4096^2 tile is 2.7 waves of 444 CTAs:
+// sized for 296 slots it ran 4 waves of 98-row segments instead of 3 of 108 (+20 % time).
+int resident_ctas(const void *kern, int threads, int smem, int floor_per_sm)
+{
+    static std::mutex mu;
+    static std::map<const void *, int> cache;
+    std::lock_guard<std::mutex> lock(mu);
+    auto it = cache.find(kern);
+    if (it != cache.end()) return it->second;
+    int per_sm = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, smem) != cudaSuccess || per_sm < 1) {
+        cudaGetLastError();
+        per_sm = floor_per_sm;
+    }
+    int sms = 148;
+    int dev = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    cache[kern] = per_sm * sms;
+    return cache[kern];
+}
+
 template <class Cfg, int RY, int MINB>
-void tma2_geometry(const Fused2Args &a, TileMap &tm, dim3 &grid)
+void tma2_geometry(const Fused2Args &a, TileMap &tm, dim3 &grid, int slots = 148 * MINB)
 {
     static const int target = env_rows("DLESM_SEG_ROWS2", 124);
-    make_tile_map(a.b, a.tiles, a.b.xs, Cfg::OUT, 148 * MINB, RY, target, 4, tm, grid);
+    make_tile_map(a.b, a.tiles, a.b.xs, Cfg::OUT, slots, RY, target, 4, tm, grid);
 }
 
 template <class Cfg, int RY, int MINB, bool M, class Kern>
@@ -1178,14 +1200,15 @@ cudaError_t launch_tma2_generic(const Fused2Args &a, cudaStream_t s, Kern kern)
     Tma2Params prm;
     prm.u2 = a.u2; prm.v2 = a.v2; prm.p2 = a.p2;
     prm.uold2 = a.uold2; prm.vold2 = a.vold2; prm.pold2 = a.pold2;
-    dim3 grid;
-    tma2_geometry<Cfg, RY, MINB>(a, prm.tm, grid);
-    prm.pitch = a.pitch; prm.b = a.b; prm.sc = a.sc;
-    prm.push = a.push;
     // per KERNEL, not per instantiation of this launcher: kernels that differ only in a template
     // argument of their own (PIPE) share this function
     cudaError_t e = allow_smem(reinterpret_cast<const void *>(kern), Cfg::SMEM_BYTES);
     if (e != cudaSuccess) return e;
+    dim3 grid;
+    tma2_geometry<Cfg, RY, MINB>(a, prm.tm, grid,
+                                 resident_ctas(reinterpret_cast<const void *>(kern), Cfg::THREADS, Cfg::SMEM_BYTES, MINB));
+    prm.pitch = a.pitch; prm.b = a.b; prm.sc = a.sc;
+    prm.push = a.push;
     kern<<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, s>>>(mu, mv, mp, muo, mvo, mpo, mm, prm);
     return cudaGetLastError();
 }
@@ -1204,7 +1227,10 @@ void grid_tma2s(const Fused2Args &a, int grid[2])
 {
     TileMap tm;
     dim3 g;
-    tma2_geometry<Tma2sCfg<TX, RY, STAGES, false>, RY, MINB>(a, tm, g);
+    using Cfg = Tma2sCfg<TX, RY, STAGES, false>;
+    const void *kern = reinterpret_cast<const void *>(fused2s_tma_kernel<TX, RY, STAGES, MINB, false, PIPE>);
+    allow_smem(kern, Cfg::SMEM_BYTES);
+    tma2_geometry<Cfg, RY, MINB>(a, tm, g, resident_ctas(kern, Cfg::THREADS, Cfg::SMEM_BYTES, MINB));
     grid[0] = static_cast<int>(g.x);
     grid[1] = static_cast<int>(g.y);
 }

@@ -55,10 +55,11 @@ cudaError_t copy_field(const double *in, double *out, size_t n, cudaStream_t s);
 cudaError_t set_field(double *f, size_t n, double val, cudaStream_t s);
 cudaError_t copy_patch(double *f, int pitch, Box src, Box dst, double *scratch, cudaStream_t s);
 // partials: >= kChecksumBlocks doubles of scratch; ticket: one zeroed unsigned (left zero again);
-// result: 1 double (device); host_result: mapped pinned double or null.  One launch.
+// result: 1 double (device); host_result: null, or two mapped pinned words -- the sum, then `seq` (written
+// after it, system fence between: a host that sees seq sees the sum).  One launch.
 constexpr int kChecksumBlocks = 1184;  // 148 SMs x 8
 cudaError_t checksum(const double *f, int pitch, Box b, double *partials, unsigned *ticket, double *result,
-                     double *host_result, cudaStream_t s);
+                     double *host_result, unsigned long long seq, cudaStream_t s);
 cudaError_t periodic_halos(double *const *fields, int nfields, int pitch, Box internal,
                            bool periodic_x, bool periodic_y, cudaStream_t s);
 cudaError_t pack(const PackPlan &plan, double *buffer, cudaStream_t s);

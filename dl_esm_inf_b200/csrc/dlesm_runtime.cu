@@ -271,6 +271,7 @@ extern "C" int dlesm_device_init(int device)
     c.ticket = reinterpret_cast<unsigned *>(c.partials + k::kChecksumBlocks + 8);
     CU(cudaMemset(c.ticket, 0, sizeof(unsigned)));
     CU(cudaMallocHost(&c.host_result, 8 * sizeof(double)));
+    std::memset(c.host_result, 0, 8 * sizeof(double));
     c.device = device;
     c.device_ready = true;
     if (const char *ar = std::getenv("DLESM_ARITH"))
@@ -728,10 +729,24 @@ extern "C" int dlesm_dev_checksum(const void *f, int xs, int xe, int ys, int ye,
     }
     Context &c = ctx();
     // one launch; the folding block stores the sum straight into pinned host memory
+    static unsigned long long seq = 0;
+    ++seq;
     CU(k::checksum(static_cast<const double *>(f), r.nx, k::Box{xs, xe, ys, ye}, c.partials, c.ticket, c.result,
-                   c.host_result, c.stream));
-    CU(cudaStreamSynchronize(c.stream));
-    *val = c.host_result[0];
+                   c.host_result + 4, seq, c.stream));
+    // poll the sequence word instead of cudaStreamSynchronize (a driver round trip of several us); the
+    // stream is queried now and then so that a failed launch ends the wait with its error
+    volatile unsigned long long *flag = reinterpret_cast<volatile unsigned long long *>(c.host_result + 5);
+    for (unsigned spin = 1; *flag != seq; ++spin) {
+        if ((spin & 0xfffff) == 0) {
+            cudaError_t q = cudaStreamQuery(c.stream);
+            if (q != cudaSuccess && q != cudaErrorNotReady) return fail_cuda(q, "field_checksum");
+            if (q == cudaSuccess && *flag != seq) {
+                set_error(DLESM_ERR_CUDA, "field_checksum: the kernel finished without publishing its result");
+                return DLESM_ERR_CUDA;
+            }
+        }
+    }
+    *val = c.host_result[4];
     return DLESM_OK;
 }
 
@@ -2462,7 +2477,7 @@ extern "C" int dlesm_field_checksum(dlesm_field_t *f, double *val)
         set_error(DLESM_ERR_STATE, "field_checksum: communicator not initialised (dlesm_comm_init)");
         return DLESM_ERR_STATE;
     }
-    CU(k::checksum(static_cast<const double *>(f->dptr), f->nx, box_of(in), c.partials, c.ticket, c.result, nullptr,
+    CU(k::checksum(static_cast<const double *>(f->dptr), f->nx, box_of(in), c.partials, c.ticket, c.result, nullptr, 0,
                    c.stream));
     NC(ncclAllReduce(c.result, c.result + 2, 1, ncclDouble, ncclSum, c.comm, c.stream));
     CU(cudaMemcpyAsync(c.host_result + 2, c.result + 2, sizeof(double), cudaMemcpyDeviceToHost, c.stream));

@@ -45,6 +45,15 @@ case $what in
     timeout ${TMO:-900} ncu --set full --clock-control none --import-source on -k regex:$re -s ${SKIP:-2} -c 1 \
         -o gpurun_out/${T}_${tag} -f $CMD > gpurun_out/${T}_${tag}_ncu.log 2>&1
     echo "ncu $tag rc=$?" ;;
+  nvlink)
+    # NVLink counters of the push sweep on rank 0 of an N-rank run (N = $1)
+    n=$1; shift
+    ncu --query-metrics 2>/dev/null | grep -i "nvl" > gpurun_out/${T}_nvl_metrics.txt
+    export TAG=$T NCU_METRICS=${NCU_METRICS:-nvltx__bytes.sum,nvlrx__bytes.sum,gpu__time_duration.sum}
+    TMO=${TMO:-240} timeout ${TMO:-240} python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 \
+        --master-port ${PORT:-29544} --no-python tools/ncu_rank0.sh bench.py --gpus $n --steps 8 --warmup 3 --e2e-steps 0 \
+        --no-cpu-baseline --no-parity --no-config5 --no-strong --no-config3 --sustain-s 0 "$@" > gpurun_out/${T}_nvlink.log 2>&1
+    echo "nvlink rc=$?"; wc -l gpurun_out/${T}_nvl_metrics.txt ;;
   probe)
     { nvidia-smi topo -m; echo; cat /sys/devices/system/node/online; grep -H . /sys/devices/system/node/node*/cpulist
       for d in /sys/bus/pci/devices/*; do c=$(cat $d/class 2>/dev/null); case $c in 0x0302*|0x0300*) echo "$d numa=$(cat $d/numa_node) $(cat $d/vendor)";; esac; done
