@@ -482,6 +482,12 @@ def run_ours(args):
             # through the two-step sweep); the one-step-per-trip figure stays beside it
             src2 = timed(True, run=False, halo="exchange")
             e2 = run_e2e(args, fd, L, src2["sw"], src2["grid"], src2["total_points"], dist, torch, per_trip=2)
+            if world == 1 and not args.no_deep_trips:
+                # for the record, not the headline: more model steps per round trip (skewed passes of the
+                # two-step sweep over the row bands); the bus is crossed once per direction per CALL
+                e2["more_steps_per_round_trip"] = [
+                    run_e2e(args, fd, L, src2["sw"], src2["grid"], src2["total_points"], dist, torch, per_trip=k)
+                    for k in (4, 8)]
             src2["sw"].free()
             for k in ("pcie_GBs_per_direction_both_busy_measured",):
                 if k in e2e:
@@ -733,7 +739,8 @@ def run_e2e(args, fd, L, sw, grid, total_points, dist, torch, per_trip=1):
     names = ("u", "v", "p", "uold", "vold", "pold")
     nx, ny = grid.nx, grid.ny
     nbytes = nx * ny * 8
-    if per_trip == 2:
+    if per_trip >= 2 and sw.ncycle_hint == 0:
+        sw.ncycle_hint = 3
         sw.step(3)                # the forward start-up step, then one pair: two-cell halos of all six fields valid
     flds = [sw.field(nm) for nm in names]
     host = []
@@ -790,7 +797,9 @@ def run_e2e(args, fd, L, sw, grid, total_points, dist, torch, per_trip=1):
            "what": ("per round trip: dlesm_sw_step_host_n with HOST (pinned) buffers: u,v,p,uold,vold,pold "
                     "host->device, %s, the six results device->host, pipelined in row bands (upload / sweep / "
                     "download overlapped, both PCIe directions busy)"
-                    % ("TWO model steps in one pass of the two-step sweep" if per_trip == 2 else "one model step"))}
+                    % ("one model step" if per_trip == 1 else "TWO model steps in one pass of the two-step sweep"
+                       if per_trip == 2 else "%d model steps in %d skewed passes of the two-step sweep"
+                       % (per_trip, per_trip // 2)))}
     if per_trip == 1:
         el_hooks = timed(step_hooks, 1, 4)
         out["hooks_serial"] = {"value": total_points / (el_hooks * 1e-3), "ms_per_step": el_hooks,
@@ -866,6 +875,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-parity", action="store_true", help="skip the pre-flight parity leg (profiling runs)")
     ap.add_argument("--no-config3", action="store_true", help="skip the config-3 (4096^2 + tmask) sub-record")
+    ap.add_argument("--no-deep-trips", action="store_true", help="skip the 4 / 8 steps-per-round-trip e2e sub-records")
     ap.add_argument("--no-strong", action="store_true", help="skip the strong-scaling sub-record (N > 1)")
     ap.add_argument("--no-config5", action="store_true", help="skip the halo_exchange / field_checksum microbench")
     ap.add_argument("--sustain-s", type=float, default=3.0,

@@ -453,6 +453,7 @@ class shallow_water:
     def __init__(self, grid: grid_type, dt=90.0, alpha=0.001, mode=SW_FUSED, use_tmask=False):
         self.grid = grid
         self.mode = mode
+        self.ncycle_hint = 0      # callers' scratch (bench.py notes whether the start-up steps were taken)
         self._h = _chk_ptr(_lib.lib().dlesm_sw_create(grid._h, dt, alpha, mode, int(use_tmask)))
 
     def field(self, name) -> r2d_field:
@@ -484,7 +485,7 @@ class shallow_water:
         _chk(_lib.lib().dlesm_sw_step(self._h, nsteps))
 
     def step_host(self, host_in, host_out=None, band_rows=0, nsteps=1):
-        """nsteps (1 or 2) model steps with HOST state: host_in = (u, v, p, uold, vold, pold)
+        """nsteps (1, 2, or on one rank any even number) model steps with HOST state: host_in = (u, v, p, uold, vold, pold)
         Fortran-ordered (nx, ny) float64 arrays (or raw addresses of such buffers); results land in
         host_out (default: in place).  Upload, sweep and download are pipelined in row bands;
         nsteps=2 sends the bands through the two-step sweep (set_two_step), halving the PCIe

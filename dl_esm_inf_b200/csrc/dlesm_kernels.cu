@@ -337,6 +337,39 @@ cudaError_t periodic_halos_deep(double *const *fields, int nfields, int pitch, B
     return cudaGetLastError();
 }
 
+// east / west halo columns, `depth` deep, of rows j0..j1 only (periodic in x): what a row band of the
+// multi-pass host step needs before the next pass reads it, while other bands are still in flight
+__global__ void __launch_bounds__(256) periodic_x_rows_kernel(DeepHaloArgs a)
+{
+    const int w = a.in.xe - a.in.xs + 1, h = a.in.ye - a.in.ys + 1, d = a.depth;
+    const long long per_field = 2LL * d * h;
+    const long long total = per_field * a.nfields;
+    for (long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; t < total;
+         t += static_cast<long long>(gridDim.x) * blockDim.x) {
+        const int kf = static_cast<int>(t / per_field);
+        const long long c = t - kf * per_field;
+        const int jj = static_cast<int>(c / (2 * d)), ii = static_cast<int>(c - static_cast<long long>(jj) * 2 * d);
+        const int dj = a.in.ys + jj;
+        const int di = ii < d ? a.in.xs - d + ii : a.in.xe + 1 + (ii - d);
+        const int si = di < a.in.xs ? di + w : di - w;
+        double *f = a.f[kf];
+        f[idx(a.pitch, di, dj)] = f[idx(a.pitch, si, dj)];
+    }
+}
+cudaError_t periodic_x_rows(double *const *fields, int nfields, int pitch, Box rows, int depth, cudaStream_t s)
+{
+    if (nfields <= 0 || depth <= 0 || rows.ye < rows.ys) return cudaSuccess;
+    if (nfields > kMaxExchangeFields || depth > rows.xe - rows.xs + 1) return cudaErrorInvalidValue;
+    DeepHaloArgs a;
+    for (int q = 0; q < nfields; ++q) a.f[q] = fields[q];
+    a.nfields = nfields; a.pitch = pitch; a.depth = depth; a.in = rows;
+    const long long total = static_cast<long long>(nfields) * 2LL * depth * (rows.ye - rows.ys + 1);
+    const unsigned blocks = total / 256 + 1 < kSMs ? static_cast<unsigned>(total / 256 + 1) : kSMs;
+    periodic_x_rows_kernel<<<blocks, 256, 0, s>>>(a);
+    count_launch();
+    return cudaGetLastError();
+}
+
 // tmask <-> FP64 image of it, so that the mask can ride the FP64 halo machinery once (the
 // two-step sweep needs the periodic mask two cells deep; grid_init replicates it outward instead)
 __global__ void __launch_bounds__(256) mask_convert_kernel(int *__restrict__ m, double *__restrict__ d, size_t n,
@@ -483,6 +516,88 @@ __global__ void __launch_bounds__(256) xdirect_recv_kernel(const __grid_constant
         const int jj = static_cast<int>(t / sg.nx), ii = static_cast<int>(t - static_cast<long long>(jj) * sg.nx);
         f[idx(plan.pitch, sg.i0 + ii, sg.j0 + jj)] = __ldcg(buf + t);   // written by a peer: not through L1
     }
+}
+
+// Both phases in ONE launch.  The grid is small enough to be co-resident (<= 2 CTAs per SM), so CTAs that
+// have finished their share of the sends may spin on the neighbours' flags while others still send: the
+// flags this rank publishes depend only on its own sends, never on a neighbour's.
+constexpr int kXChunk = 4096;   // elements per work item
+__device__ __forceinline__ void xdirect_items(const XPlan &plan, bool send)
+{
+    int base = 0;
+    for (int sidx = 0; sidx < plan.nseg; ++sidx) {
+        const XSegment &sg = plan.seg[sidx];
+        const int n = sg.nx * sg.ny;
+        const int chunks = (n + kXChunk - 1) / kXChunk;
+        const int items = chunks * plan.nfields;
+        // first work item of this segment that belongs to this CTA
+        int w = (static_cast<int>(blockIdx.x) - base % static_cast<int>(gridDim.x) + static_cast<int>(gridDim.x)) %
+                static_cast<int>(gridDim.x);
+        for (; w < items; w += gridDim.x) {
+            const int kf = w / chunks, ch = w - kf * chunks;
+            double *buf = sg.buf + static_cast<long long>(kf) * n;
+            double *f = plan.fields[kf];
+            const int hi = min(n, (ch + 1) * kXChunk);
+            for (int t = ch * kXChunk + threadIdx.x; t < hi; t += blockDim.x) {
+                const int jj = t / sg.nx, ii = t - jj * sg.nx;
+                const size_t q = idx(plan.pitch, sg.i0 + ii, sg.j0 + jj);
+                if (send) buf[t] = f[q];
+                else f[q] = __ldcg(buf + t);
+            }
+        }
+        base += items;
+    }
+}
+
+__global__ void __launch_bounds__(256) xdirect_fused_kernel(const __grid_constant__ XPlan sp,
+                                                            const __grid_constant__ XPlan rp, unsigned *ticket, int *err)
+{
+    xdirect_items(sp, true);
+    __threadfence_system();
+    __syncthreads();
+    __shared__ bool last;
+    if (threadIdx.x == 0) last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (last) {
+        if (threadIdx.x < sp.npeers) {
+            __threadfence_system();
+            asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(sp.flag[threadIdx.x]), "l"(sp.count[threadIdx.x])
+                         : "memory");
+        }
+        if (threadIdx.x == 0) *ticket = 0u;
+    }
+    if (threadIdx.x < rp.npeers) {
+        const long long t0 = clock64();
+        for (;;) {
+            unsigned long long v;
+            asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(rp.flag[threadIdx.x]) : "memory");
+            if (v >= rp.count[threadIdx.x]) break;
+            if (clock64() - t0 > 40000000000LL) {
+                atomicExch(err, 1);
+                __threadfence_system();
+                __trap();
+            }
+            __nanosleep(40);
+        }
+    }
+    __syncthreads();
+    xdirect_items(rp, false);
+}
+
+cudaError_t xdirect_exchange(const XPlan &sp, const XPlan &rp, unsigned *ticket, int *err, cudaStream_t s)
+{
+    if (sp.nfields <= 0 || (sp.nseg <= 0 && rp.nseg <= 0)) return cudaSuccess;
+    long long items = 0;
+    for (int q = 0; q < sp.nseg; ++q)
+        items += static_cast<long long>((sp.seg[q].nx * sp.seg[q].ny + kXChunk - 1) / kXChunk) * sp.nfields;
+    long long ritems = 0;
+    for (int q = 0; q < rp.nseg; ++q)
+        ritems += static_cast<long long>((rp.seg[q].nx * rp.seg[q].ny + kXChunk - 1) / kXChunk) * rp.nfields;
+    items = std::max(items, ritems);
+    const unsigned blocks = static_cast<unsigned>(std::max(1LL, std::min<long long>(items, kSMs * 2)));
+    xdirect_fused_kernel<<<blocks, 256, 0, s>>>(sp, rp, ticket, err);
+    count_launch();
+    return cudaGetLastError();
 }
 
 static dim3 xdirect_grid(const XPlan &plan)

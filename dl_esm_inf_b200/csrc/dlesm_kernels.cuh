@@ -88,6 +88,8 @@ struct XPlan {
     unsigned long long *flag[kMaxSegments];     // send: neighbour's flag cell for this rank; receive: own cell for the neighbour
     unsigned long long count[kMaxSegments];     // the pair's exchange count this launch publishes / waits for
 };
+// send + publish + wait + unpack in one co-resident launch (the default); the two-launch form follows
+cudaError_t xdirect_exchange(const XPlan &send, const XPlan &recv, unsigned *ticket, int *err, cudaStream_t s);
 cudaError_t xdirect_send(const XPlan &plan, unsigned *ticket, cudaStream_t s);
 cudaError_t xdirect_recv(const XPlan &plan, int *err, cudaStream_t s);
 
@@ -233,6 +235,8 @@ DLESM_FUSED_API(fma_on)
 // periodic halo fill to `depth` cells on one rank (wrapped source index; corners included)
 cudaError_t periodic_halos_deep(double *const *fields, int nfields, int pitch, Box internal, int depth,
                                 cudaStream_t s);
+// east / west halo columns of rows box.ys..box.ye only (box.xs..box.xe = the internal columns)
+cudaError_t periodic_x_rows(double *const *fields, int nfields, int pitch, Box rows, int depth, cudaStream_t s);
 
 // m[t] -> d[t] (to_double) or d[t] -> m[t]: the tmask rides the FP64 halo machinery once
 cudaError_t mask_convert(int *m, double *d, size_t n, bool to_double, cudaStream_t s);

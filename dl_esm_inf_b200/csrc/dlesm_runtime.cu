@@ -1375,8 +1375,13 @@ int xdirect_exchange(void *const *fields, int nfields, int pitch, const CommTabl
     }
     unsigned *ticket = reinterpret_cast<unsigned *>(xd.base + 1024);
     int *err = reinterpret_cast<int *>(xd.base + 1032);
-    CU(k::xdirect_send(sp, ticket, c.stream));
-    CU(k::xdirect_recv(rp, err, c.stream));
+    static const bool two_launches = std::getenv("DLESM_XDIRECT_TWO_LAUNCHES") != nullptr;
+    if (two_launches) {
+        CU(k::xdirect_send(sp, ticket, c.stream));
+        CU(k::xdirect_recv(rp, err, c.stream));
+    } else {
+        CU(k::xdirect_exchange(sp, rp, ticket, err, c.stream));
+    }
     done = true;
     return DLESM_OK;
 }
@@ -2969,6 +2974,150 @@ extern "C" int dlesm_sw_step_host(dlesm_sw_t *s, const double *const host_in[6],
     return DLESM_OK;
 }
 
+namespace {
+// 2 * npass model steps per PCIe round trip on one rank (periodic wrap is local).  The bands of pass 1
+// follow the upload as in the two-step form; pass p+1 of band b needs pass p of bands b-1, b, b+1, so it
+// runs two bands behind -- skewed, on the same stream, while later bands are still uploading -- and the
+// last pass's bands download as they finish.  Only the first and last band of a pass wait for the whole
+// previous pass (they read the wrapped halo rows).  Both PCIe directions stay busy; each row crosses the
+// bus once per direction for 2 * npass steps.  Outputs ping-pong between the two buffer sets; a band's
+// east / west halo columns are filled right after its sweep (periodic_x_rows), the north / south rows
+// when a pass is complete.
+int sw_step_host_passes(dlesm_sw *s, const double *const host_in[6], double *const host_out[6], int band_rows,
+                        int npass)
+{
+    int rc = ensure_device();
+    if (rc != DLESM_OK) return rc;
+    Context &c = ctx();
+    dlesm_grid &g = *s->grid;
+    dlesm_field **f = s->f;
+    const dlesm_region &rt = f[DLESM_SW_P]->fb.internal;
+    const int nx = f[0]->nx, ny = f[0]->ny;
+    const size_t row_bytes = static_cast<size_t>(nx) * sizeof(double);
+    if (band_rows <= 0) band_rows = std::max(64, ((rt.ny / 128) + 31) / 32 * 32);
+    band_rows = std::max(band_rows, 4);
+    const int nbands = (rt.ny + band_rows - 1) / band_rows;
+    if (rt.ny - (nbands - 1) * band_rows < 2 && nbands > 1) {
+        set_error(DLESM_ERR_ARGS, "sw_step_host_n: the last row band must hold at least two rows (change band_rows)");
+        return DLESM_ERR_ARGS;
+    }
+    while (c.band_events.size() < static_cast<size_t>(2 * nbands + 2)) {
+        cudaEvent_t e;
+        CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        c.band_events.push_back(e);
+    }
+    cudaEvent_t e_start = c.band_events[2 * nbands];
+    CU(cudaEventRecord(e_start, c.stream));
+    CU(cudaStreamWaitEvent(c.s_h2d, e_start, 0));
+    CU(cudaStreamWaitEvent(c.s_d2h, e_start, 0));
+    // set 0 = the model's current fields (uploaded into), set 1 = the spare ones; pass p reads set p % 2
+    double *set[2][6];
+    for (int q = 0; q < 6; ++q) set[0][q] = static_cast<double *>(f[DLESM_SW_U + q]->dptr);
+    for (int q = 0; q < 3; ++q) {
+        set[1][q] = static_cast<double *>(f[DLESM_SW_UNEW + q]->dptr);
+        set[1][3 + q] = static_cast<double *>(s->old2[q]->dptr);
+    }
+    auto band_j0 = [&](int b) { return rt.ystart + b * band_rows; };
+    auto band_j1 = [&](int b) { return std::min(rt.ystop, band_j0(b) + band_rows - 1); };
+    std::vector<std::vector<char>> done(npass, std::vector<char>(nbands, 0));
+    std::vector<int> ndone(npass, 0);
+    std::vector<char> filled(npass, 0);
+    auto issue = [&](int p, int b) -> int {
+        double **in = set[p % 2], **out = set[(p + 1) % 2];
+        const int j0 = band_j0(b), j1 = band_j1(b);
+        int r2 = sw_step2_fused_impl(in[0], in[1], in[2], in[3], in[4], in[5], out[0], out[1], out[2], out[3], out[4],
+                                     out[5], g.info.dx, g.info.dy, s->tdt, s->alpha, rt.xstart, rt.xstop, j0, j1,
+                                     s->mask2, s->mask2_pitch, s->variant2, nullptr);
+        if (r2 != DLESM_OK) return r2;
+        CU(k::periodic_x_rows(out, 6, nx, k::Box{rt.xstart, rt.xstop, j0, j1}, 2, c.stream));
+        if (p == npass - 1) {
+            cudaEvent_t e_done = c.band_events[2 * b + 1];
+            CU(cudaEventRecord(e_done, c.stream));
+            CU(cudaStreamWaitEvent(c.s_d2h, e_done, 0));
+            const size_t off = static_cast<size_t>(j0 - 1) * nx;
+            const size_t bytes = static_cast<size_t>(j1 - j0 + 1) * row_bytes;
+            for (int q = 0; q < 6; ++q)
+                CU(cudaMemcpyAsync(host_out[q] + off, out[q] + off, bytes, cudaMemcpyDeviceToHost, c.s_d2h));
+        }
+        done[p][b] = 1;
+        ++ndone[p];
+        return DLESM_OK;
+    };
+    auto ready = [&](int p, int b) {
+        if (done[p][b] || !done[p - 1][b]) return false;
+        const bool south = b > 0 ? done[p - 1][b - 1] != 0 : filled[p - 1] != 0;
+        const bool north = b < nbands - 1 ? done[p - 1][b + 1] != 0 : filled[p - 1] != 0;
+        return south && north;
+    };
+    auto advance = [&]() -> int {     // everything the finished work makes ready, in pass order
+        for (bool progress = true; progress;) {
+            progress = false;
+            for (int p = 0; p < npass; ++p) {
+                if (ndone[p] == nbands && !filled[p]) {
+                    // north / south halo rows (and the corners) of this pass's outputs
+                    CU(k::periodic_halos_deep(set[(p + 1) % 2], 6, nx, box_of(rt), 2, c.stream));
+                    filled[p] = 1;
+                    progress = true;
+                }
+                if (p == 0) continue;
+                for (int b = 0; b < nbands; ++b)
+                    if (ready(p, b)) {
+                        int r2 = issue(p, b);
+                        if (r2 != DLESM_OK) return r2;
+                        progress = true;
+                    }
+            }
+        }
+        return DLESM_OK;
+    };
+    int up_next = 1;
+    for (int b = 0; b < nbands; ++b) {
+        const int j1 = band_j1(b);
+        const int up_to = (b == nbands - 1) ? ny : std::min(ny, j1 + 2);
+        if (up_to >= up_next) {
+            const size_t off = static_cast<size_t>(up_next - 1) * nx;
+            const size_t bytes = static_cast<size_t>(up_to - up_next + 1) * row_bytes;
+            for (int q = 0; q < 6; ++q)
+                CU(cudaMemcpyAsync(set[0][q] + off, host_in[q] + off, bytes, cudaMemcpyHostToDevice, c.s_h2d));
+            up_next = up_to + 1;
+        }
+        cudaEvent_t e_up = c.band_events[2 * b];
+        CU(cudaEventRecord(e_up, c.s_h2d));
+        CU(cudaStreamWaitEvent(c.stream, e_up, 0));
+        rc = issue(0, b);
+        if (rc == DLESM_OK) rc = advance();
+        if (rc != DLESM_OK) return rc;
+    }
+    rc = advance();
+    if (rc != DLESM_OK) return rc;
+    if (ndone[npass - 1] != nbands || !filled[npass - 1]) {
+        set_error(DLESM_ERR_STATE, "sw_step_host_n: the band schedule did not complete");
+        return DLESM_ERR_STATE;
+    }
+    double **fin = set[npass % 2];
+    // the two + two halo rows, full width, once every band's download has landed
+    cudaEvent_t e_dl = c.band_events[2 * nbands + 1];
+    CU(cudaEventRecord(e_dl, c.s_d2h));
+    CU(cudaStreamWaitEvent(c.stream, e_dl, 0));
+    for (int q = 0; q < 6; ++q) {
+        const int rows[2] = {rt.ystart - 2, rt.ystop + 1};
+        for (int r : rows) {
+            const size_t off = static_cast<size_t>(r - 1) * nx;
+            CU(cudaMemcpyAsync(host_out[q] + off, fin[q] + off, 2 * row_bytes, cudaMemcpyDeviceToHost, c.stream));
+        }
+    }
+    CU(cudaStreamSynchronize(c.stream));
+    if (npass % 2 == 1)
+        for (int q = 0; q < 3; ++q) {
+            std::swap(f[DLESM_SW_U + q]->dptr, f[DLESM_SW_UNEW + q]->dptr);
+            std::swap(f[DLESM_SW_UOLD + q]->dptr, s->old2[q]->dptr);
+        }
+    s->deep_valid = true;
+    s->ncycle += 2 * npass;
+    return DLESM_OK;
+}
+}  // namespace
+
 // Two model steps per PCIe round trip: the bands go through the two-step sweep (temporal blocking,
 // tile with two halo cells), so each row of each field crosses the bus once per direction for
 // TWO steps -- half the bytes per model step of dlesm_sw_step_host.  nsteps = 1 is that call.
@@ -2979,9 +3128,11 @@ extern "C" int dlesm_sw_step_host_n(dlesm_sw_t *s, const double *const host_in[6
 {
     if (nsteps == 1) return dlesm_sw_step_host(s, host_in, host_out, band_rows);
     clear_error();
+    if (s && nsteps >= 4 && nsteps % 2 == 0 && s->two_step && !s->push && s->ncycle > 0 && s->periodic_local)
+        return sw_step_host_passes(s, host_in, host_out, band_rows, nsteps / 2);
     if (!s || nsteps != 2 || !s->two_step || s->push || s->ncycle == 0) {
-        set_error(DLESM_ERR_ARGS, "sw_step_host_n: nsteps is 1 or 2; 2 needs set_two_step(on), the exchange halo mode "
-                                  "and a model past its first step");
+        set_error(DLESM_ERR_ARGS, "sw_step_host_n: nsteps is 1, 2 or (one rank) an even number; more than 1 needs "
+                                  "set_two_step(on), the exchange halo mode and a model past its first step");
         return DLESM_ERR_ARGS;
     }
     int rc = ensure_device();

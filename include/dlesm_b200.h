@@ -523,7 +523,10 @@ int dlesm_sw_step_host(dlesm_sw_t *s, const double *const host_in[6], double *co
 /* nsteps model steps per PCIe round trip.  nsteps = 1 is dlesm_sw_step_host.  nsteps = 2 streams the
  * bands through the two-step sweep (dlesm_sw_set_two_step(on), tile decomposed with halo_width 2,
  * exchange halo mode, model past its first step): each row crosses the bus once per direction for
- * two steps.  Host arrays carry a valid two-cell halo ring of all six fields in, and get it back. */
+ * two steps.  On one rank nsteps may be any even number: nsteps / 2 skewed passes of the two-step sweep over the
+ * bands (pass p+1 runs two bands behind pass p while later bands still upload; the last pass's bands download
+ * as they finish), one bus crossing per direction per CALL.  Host arrays carry a valid two-cell halo ring of all
+ * six fields in, and get it back. */
 int dlesm_sw_step_host_n(dlesm_sw_t *s, const double *const host_in[6], double *const host_out[6],
                          int band_rows, int nsteps);
 dlesm_field_t *dlesm_sw_field(dlesm_sw_t *s, int which);

@@ -257,7 +257,7 @@ def test_only_x_or_only_y_periodic_halos():
 def test_exchange_engine_with_self_neighbours(mode):
     """One rank, wrap-around neighbours = itself: halo_exchange must reproduce the serial periodic fill
     bit for bit, corners included, for one field and for several grouped fields -- by the direct path
-    (patches stored straight into the receiver's slots + flag hand-shake, two launches) and by the
+    (patches stored straight into the receiver's slots + flag hand-shake + unpack, ONE launch) and by the
     pack -> (on-device) deliver -> unpack path of the NCCL mode."""
     L = _lib.lib()
     fd.set_exchange_mode(fd.EXCHANGE_DIRECT if mode == "direct" else fd.EXCHANGE_NCCL)
@@ -277,7 +277,7 @@ def test_exchange_engine_with_self_neighbours(mode):
         wants.append(of.data)
     n0 = fd.kernel_launch_count()
     flds[0].halo_exchange(1)
-    assert fd.kernel_launch_count() - n0 == 2          # send + receive, or pack + unpack
+    assert fd.kernel_launch_count() - n0 == (1 if mode == "direct" else 2)   # one fused launch, or pack + unpack
     assert np.array_equal(flds[0].get_data(), wants[0])
     fd.halo_exchange_fields(flds[1:])
     assert np.array_equal(flds[1].get_data(), wants[1])
@@ -768,11 +768,13 @@ def test_two_step_sweep_matches_oracle(variant2, n_x, n_y, align, nsteps, monkey
     (64, 64, 2, 0, False), (130, 77, 64, 10, False), (300, 523, 64, 97, True), (1024, 1024, 64, 0, False),
     (96, 40, 64, 1000, False)])
 @pytest.mark.parametrize("in_place", [True, False])
-def test_step_host_two_steps_per_round_trip_matches_oracle(n_x, n_y, align, band_rows, masked, in_place,
+@pytest.mark.parametrize("per_trip", [2, 4, 6])
+def test_step_host_two_steps_per_round_trip_matches_oracle(n_x, n_y, align, band_rows, masked, in_place, per_trip,
                                                           monkeypatch):
-    """dlesm_sw_step_host_n(nsteps=2): the bands go through the two-step sweep, each row crosses the
-    bus once per direction for two model steps; host results (internal points and the two-cell halo
-    ring) and the device state == the oracle stepping one step at a time, bit for bit"""
+    """dlesm_sw_step_host_n(nsteps = 2, 4, 6): the bands go through the two-step sweep -- for 4 and 6 steps
+    through two and three skewed passes of it, later passes running two bands behind the upload -- and
+    each row crosses the bus once per direction per call; host results (internal points and the two-cell
+    halo ring) and the device state == the oracle stepping one step at a time, bit for bit"""
     try:
         tm = periodic_island_mask(n_x + 2, n_y + 2, 12345) if masked else None
         osw, sw = sw_pair_hw2(n_x, n_y, align, monkeypatch, tmask=tm)
@@ -791,12 +793,13 @@ def test_step_host_two_steps_per_round_trip_matches_oracle(n_x, n_y, align, band
         for q in range(6):
             host[q][ring2] = np.pad(osw.f[names[q]][core], 2, mode="wrap")
         for trip in range(3):
-            osw.step(); osw.step()
+            for _ in range(per_trip):
+                osw.step()
             if in_place:
-                sw.step_host(host, band_rows=band_rows, nsteps=2)
+                sw.step_host(host, band_rows=band_rows, nsteps=per_trip)
             else:
                 out = [np.full_like(a, np.nan) for a in host]
-                sw.step_host(host, out, band_rows=band_rows, nsteps=2)
+                sw.step_host(host, out, band_rows=band_rows, nsteps=per_trip)
                 for n, a, o in zip(names, host, out):
                     assert not np.isnan(o[ring2]).any(), n
                     a[ring2] = o[ring2]
