@@ -84,6 +84,25 @@ class ClockSampler(threading.Thread):
                 pass
             time.sleep(self.period)
 
+    def nvlink_kib(self):
+        """cumulative NVLink payload / raw traffic of this GPU, all links: (data_tx, data_rx, raw_tx, raw_rx)
+        in KiB (NVML_FI_DEV_NVLINK_THROUGHPUT_*), or None where the driver does not report them"""
+        if not self.ok:
+            return None
+        try:
+            nv = self.nv
+            ids = [nv.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_TX, nv.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_RX,
+                   nv.NVML_FI_DEV_NVLINK_THROUGHPUT_RAW_TX, nv.NVML_FI_DEV_NVLINK_THROUGHPUT_RAW_RX]
+            vals = nv.nvmlDeviceGetFieldValues(self.h, ids)
+            out = []
+            for v in vals:
+                if v.nvmlReturn != 0:
+                    return None
+                out.append(int(v.value.ullVal))
+            return out
+        except Exception:
+            return None
+
     def summary(self, t0, t1):
         if not self.ok:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvml unavailable"]}
@@ -353,6 +372,7 @@ def run_ours(args):
             L.dlesm_profile_enable(1)
             L.dlesm_profile_read(None, None, 1)
             barrier()
+            nvl0 = sampler.nvlink_kib() if world > 1 else None
             launches0 = fd.kernel_launch_count()
             w0 = time.time()
             L.dlesm_event_record(0)
@@ -367,7 +387,13 @@ def run_ours(args):
             L.dlesm_profile_read(C.byref(kms), C.byref(kn), 1)
             L.dlesm_profile_enable(0)
             el = max_over_ranks(ms.value)
-            return dict(elapsed_ms=el, launches=int(launches), kernel_ms_total=kms.value, kernel_launches=kn.value,
+            nvl1 = sampler.nvlink_kib() if world > 1 else None
+            nvl = None
+            if nvl0 and nvl1:
+                # the counters tick at their own pace: this is a lower bound on the region's traffic unless
+                # the region is long (the sustained leg); reported per step beside the algorithmic figure
+                nvl = [(b - a) * 1024.0 / nsteps for a, b in zip(nvl0, nvl1)]
+            return dict(nvlink_bytes_per_step=nvl, elapsed_ms=el, launches=int(launches), kernel_ms_total=kms.value, kernel_launches=kn.value,
                         clocks=sampler.summary(w0, w1), value=total_points * nsteps / (el * 1e-3), steps=nsteps)
 
         def roofline_of(r):
@@ -438,6 +464,11 @@ def run_ours(args):
                             "messages_per_rank_per_step": int(cm.nsend),
                             "nvlink_peak_GBs_both_directions": 1800.0,
                             "nvlink_frac_of_step": (sent + recv) / step_s / 1.8e12,
+                            "nvml_nvlink_bytes_per_step_data_tx_rx_raw_tx_rx": (S if sustain_s > 0 else R).get(
+                                "nvlink_bytes_per_step"),
+                            "nvml_note": "NVML NVLINK_THROUGHPUT counters of this rank's GPU (all links) over the "
+                                         "%s leg, per model step: data = payload, raw = with protocol overhead"
+                                         % ("sustained" if sustain_s > 0 else "timed"),
                             "step_minus_sweep_us": (R["elapsed_ms"] - R["kernel_ms_total"]) / steps * 1e3}
 
         R.update(cks=cks, halo_traffic=halo_traffic, halo=halo, grid=grid, sw=sw, probe=probe, sub=sub, gx=gx,
