@@ -30,7 +30,9 @@
 #include <cstdlib>
 #include <map>
 #include <mutex>
+#include <string>
 #include <tuple>
+#include <vector>
 #include <type_traits>
 
 #include "dlesm_kernels.cuh"
@@ -246,6 +248,9 @@ __device__ __forceinline__ void tile_of_block(const TileMap &t, const Box &b, in
     j1 = min(j0 + t.th + (by < t.yextra ? 1 : 0) - 1, b.ye);
 }
 
+// tile_list != null: a 1-D launch over a subset of the tile grid -- blockIdx.x indexes the list, an entry
+// is by * list_gx + bx of the natural 2-D grid (masked runs: all-wet tiles go through the unmasked
+// kernel, the tiles that see land through the masked one)
 struct TmaStepParams {
     double *unew, *vnew, *pnew, *uold, *vold, *pold;
     int pitch;
@@ -253,7 +258,19 @@ struct TmaStepParams {
     TileMap tm;
     SwScalars sc;
     PushPlan push;
+    const int *tile_list;
+    int list_gx;
 };
+__device__ __forceinline__ void block_tile(const int *tile_list, int list_gx, int &bx, int &by)
+{
+    bx = blockIdx.x;
+    by = blockIdx.y;
+    if (tile_list) {
+        const int t = tile_list[blockIdx.x];
+        by = t / list_gx;
+        bx = t - by * list_gx;
+    }
+}
 
 // edge outputs of row j, column i -> the neighbours' halo cells (rare: only threads whose
 // column/segment meets a push box get here)
@@ -324,7 +341,9 @@ fused_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_constant
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     int i_first, i_last, j0, j1;   // first output column of this strip, last column of its x-tile, rows
-    tile_of_block(prm.tm, prm.b, blockIdx.x, blockIdx.y, TX, i_first, i_last, j0, j1);
+    int bx_, by_;
+    block_tile(prm.tile_list, prm.list_gx, bx_, by_);
+    tile_of_block(prm.tm, prm.b, bx_, by_, TX, i_first, i_last, j0, j1);
     const int nsteps = (j1 - j0 + 1) + 2;            // raw rows j0-1 .. j1+1
     const int nchunks = (nsteps + RY - 1) / RY;
 
@@ -579,6 +598,101 @@ void make_tile_map(const Box &b, SweepTiles tiles, int x0, int out_cols, int slo
     grid = dim3(static_cast<unsigned>(tm.strips * ntx), static_cast<unsigned>(nty));
 }
 
+// ---------------------------------------------------------------------------------------
+// Masked runs: which tiles of the launch grid see land at all?  A tile whose mask cells are all wet
+// within `margin` cells of its outputs computes exactly what the unmasked march computes (every
+// select of the masked rule passes), so it goes through the UNMASKED kernel -- full speed, small
+// code -- and only the tiles near land run the masked kernel.  The classification is done once per
+// (mask image, geometry) on the device and cached; the runtime calls forget_mask when it frees an image.
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) classify_tiles_kernel(const unsigned char *__restrict__ m8, int pitch8, int nx,
+                                                             int ny, TileMap tm, Box b, int out_cols, int margin,
+                                                             unsigned char *__restrict__ all_wet)
+{
+    int i_first, i_last, j0, j1;
+    tile_of_block(tm, b, blockIdx.x, blockIdx.y, out_cols, i_first, i_last, j0, j1);
+    const int i_hi = min(i_first + out_cols - 1, i_last);
+    const int ilo = max(1, i_first - margin), ihi = min(nx, i_hi + margin);
+    const int jlo = max(1, j0 - margin), jhi = min(ny, j1 + margin);
+    const int w = ihi - ilo + 1, h = jhi - jlo + 1;
+    int wet = 1;
+    for (int t = threadIdx.x; t < w * h && wet; t += blockDim.x) {
+        const int jj = t / w, ii = t - jj * w;
+        wet = m8[static_cast<size_t>(jlo - 1 + jj) * pitch8 + (ilo - 1 + ii)] == 1;
+    }
+    wet = __syncthreads_and(wet);
+    if (threadIdx.x == 0) all_wet[blockIdx.y * gridDim.x + blockIdx.x] = static_cast<unsigned char>(wet);
+}
+
+struct TileLists {
+    int *wet = nullptr, *land = nullptr;   // device arrays of tile ids in natural (row-major) order
+    int nwet = 0, nland = 0;
+    const void *mask = nullptr;
+};
+std::mutex &tile_mu()
+{
+    static std::mutex m;
+    return m;
+}
+std::map<std::string, TileLists> &tile_cache()
+{
+    static std::map<std::string, TileLists> c;
+    return c;
+}
+cudaError_t tile_lists(const unsigned char *m8, int pitch8, int nx, int ny, const TileMap &tm, const Box &b, int out_cols,
+                       int margin, dim3 grid, cudaStream_t s, TileLists &out)
+{
+    struct Key {
+        const void *m;
+        int v[16];
+    } key{m8, {pitch8, nx, ny, tm.strips, tm.x0, tm.tw, tm.xextra, tm.th, tm.yextra, b.xs, b.xe, b.ys, b.ye, out_cols,
+               margin, static_cast<int>(grid.x)}};
+    const std::string k(reinterpret_cast<const char *>(&key), sizeof(key));
+    std::lock_guard<std::mutex> lock(tile_mu());
+    auto it = tile_cache().find(k);
+    if (it != tile_cache().end()) {
+        out = it->second;
+        return cudaSuccess;
+    }
+    const int n = static_cast<int>(grid.x * grid.y);
+    unsigned char *flags = nullptr;
+    cudaError_t e = cudaMalloc(&flags, n);
+    if (e != cudaSuccess) return e;
+    classify_tiles_kernel<<<grid, 256, 0, s>>>(m8, pitch8, nx, ny, tm, b, out_cols, margin, flags);
+    std::vector<unsigned char> h(n);
+    e = cudaMemcpyAsync(h.data(), flags, n, cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+    cudaFree(flags);
+    if (e != cudaSuccess) return e;
+    std::vector<int> wet, land;
+    for (int t = 0; t < n; ++t) (h[t] ? wet : land).push_back(t);
+    TileLists tl;
+    tl.mask = m8;
+    tl.nwet = static_cast<int>(wet.size());
+    tl.nland = static_cast<int>(land.size());
+    if (tl.nwet) {
+        e = cudaMalloc(&tl.wet, wet.size() * sizeof(int));
+        if (e == cudaSuccess) e = cudaMemcpyAsync(tl.wet, wet.data(), wet.size() * sizeof(int), cudaMemcpyHostToDevice, s);
+    }
+    if (e == cudaSuccess && tl.nland) {
+        e = cudaMalloc(&tl.land, land.size() * sizeof(int));
+        if (e == cudaSuccess) e = cudaMemcpyAsync(tl.land, land.data(), land.size() * sizeof(int), cudaMemcpyHostToDevice, s);
+    }
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+    if (e != cudaSuccess) return e;
+    tile_cache()[k] = tl;
+    out = tl;
+    return cudaSuccess;
+}
+bool split_masked_launches()
+{
+    static const bool on = [] {
+        const char *e = std::getenv("DLESM_MASK_SPLIT");
+        return !(e && std::atoi(e) == 0);
+    }();
+    return on;
+}
+
 template <int TX, int RY, int STAGES, int MINB, bool ALN>
 void tma_geometry(const FusedArgs &a, TileMap &tm, dim3 &grid)
 {
@@ -593,8 +707,9 @@ void tma_geometry(const FusedArgs &a, TileMap &tm, dim3 &grid)
     make_tile_map(a.b, a.tiles, x0, TX, 148 * MINB, RY, target, 2, tm, grid);
 }
 
+// one instantiation of the one-step kernel over `grid` (2-D natural grid, or 1-D over prm.tile_list)
 template <int TX, int RY, int STAGES, int MINB, bool M, bool FIRST, bool ALN>
-cudaError_t launch_tma_mf(const FusedArgs &a, cudaStream_t s)
+cudaError_t launch_tma_kernel(const FusedArgs &a, const TmaStepParams &prm, dim3 grid, cudaStream_t s)
 {
     using Cfg = TmaCfg<TX, RY, STAGES, M, ALN>;
     CUtensorMap mu, mv, mp, muo, mvo, mpo, mm;
@@ -609,6 +724,16 @@ cudaError_t launch_tma_mf(const FusedArgs &a, cudaStream_t s)
     } else {
         mm = mp;  // unused by the unmasked kernel
     }
+    auto kern = fused_tma_kernel<TX, RY, STAGES, MINB, M, FIRST, ALN>;
+    cudaError_t e = allow_smem(reinterpret_cast<const void *>(kern), Cfg::SMEM_BYTES);
+    if (e != cudaSuccess) return e;
+    kern<<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, s>>>(mu, mv, mp, muo, mvo, mpo, mm, prm);
+    return cudaGetLastError();
+}
+
+template <int TX, int RY, int STAGES, int MINB, bool M, bool FIRST, bool ALN>
+cudaError_t launch_tma_mf(const FusedArgs &a, cudaStream_t s)
+{
     TmaStepParams prm;
     prm.unew = a.unew; prm.vnew = a.vnew; prm.pnew = a.pnew;
     prm.uold = a.uold; prm.vold = a.vold; prm.pold = a.pold;
@@ -616,11 +741,25 @@ cudaError_t launch_tma_mf(const FusedArgs &a, cudaStream_t s)
     tma_geometry<TX, RY, STAGES, MINB, ALN>(a, prm.tm, grid);
     prm.pitch = a.pitch; prm.b = a.b; prm.sc = a.sc;
     prm.push = a.push;
-    auto kern = fused_tma_kernel<TX, RY, STAGES, MINB, M, FIRST, ALN>;
-    cudaError_t e = allow_smem(reinterpret_cast<const void *>(kern), Cfg::SMEM_BYTES);
-    if (e != cudaSuccess) return e;
-    kern<<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, s>>>(mu, mv, mp, muo, mvo, mpo, mm, prm);
-    return cudaGetLastError();
+    prm.tile_list = nullptr;
+    prm.list_gx = static_cast<int>(grid.x);
+    if (M && split_masked_launches() && a.mask8 && a.mask8_pitch % 16 == 0) {
+        // all-wet tiles through the unmasked kernel, the rest through the masked one (same bits)
+        TileLists tl;
+        cudaError_t e = tile_lists(a.mask8, a.mask8_pitch, a.pitch, a.ny, prm.tm, a.b, TX, 3, grid, s, tl);
+        if (e != cudaSuccess) return e;
+        if (tl.nwet) {
+            prm.tile_list = tl.wet;
+            e = launch_tma_kernel<TX, RY, STAGES, MINB, false, FIRST, ALN>(a, prm, dim3(tl.nwet), s);
+            if (e != cudaSuccess) return e;
+        }
+        if (tl.nland) {
+            prm.tile_list = tl.land;
+            e = launch_tma_kernel<TX, RY, STAGES, MINB, true, FIRST, ALN>(a, prm, dim3(tl.nland), s);
+        }
+        return e;
+    }
+    return launch_tma_kernel<TX, RY, STAGES, MINB, M, FIRST, ALN>(a, prm, grid, s);
 }
 
 template <int TX, int RY, int STAGES, int MINB, bool ALN>
@@ -665,6 +804,8 @@ struct Tma2Params {
     TileMap tm;
     SwScalars sc;
     PushPlan2 push;
+    const int *tile_list;   // see TmaStepParams
+    int list_gx;
 };
 
 // edge outputs of row j, column i -> the neighbours' halo cells, two cells deep (rare path)
@@ -806,7 +947,9 @@ fused2s_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_consta
     // ~100k single-cell NVLink stores into the first waves: 2x2 tiles, 4.8 -> 7.0 ms per launch.  Natural
     // order spreads them over the sweep.)
     int i_first, i_last, j0, j1;   // first output column of this CTA, last column of its x-tile, rows
-    tile_of_block(prm.tm, prm.b, blockIdx.x, blockIdx.y, Cfg::OUT, i_first, i_last, j0, j1);
+    int bx_, by_;
+    block_tile(prm.tile_list, prm.list_gx, bx_, by_);
+    tile_of_block(prm.tm, prm.b, bx_, by_, Cfg::OUT, i_first, i_last, j0, j1);
     const int nsteps = (j1 - j0 + 1) + 4;            // raw rows j0-2 .. j1+2
     const int nchunks = (nsteps + RY - 1) / RY;
     // lane column (both stages): i_first + 30*warp + lane - 2
@@ -1057,7 +1200,9 @@ fused2w_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_consta
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     int i_first, i_last, j0, j1;
-    tile_of_block(prm.tm, prm.b, blockIdx.x, blockIdx.y, Cfg::OUT, i_first, i_last, j0, j1);
+    int bx_, by_;
+    block_tile(prm.tile_list, prm.list_gx, bx_, by_);
+    tile_of_block(prm.tm, prm.b, bx_, by_, Cfg::OUT, i_first, i_last, j0, j1);
     const int nsteps = (j1 - j0 + 1) + 4;            // raw rows j0-2 .. j1+2
     const int nchunks = (nsteps + RY - 1) / RY;
 
@@ -1183,8 +1328,9 @@ void tma2_geometry(const Fused2Args &a, TileMap &tm, dim3 &grid, int slots = 148
     make_tile_map(a.b, a.tiles, a.b.xs, Cfg::OUT, slots, RY, target, 4, tm, grid);
 }
 
-template <class Cfg, int RY, int MINB, bool M, class Kern>
-cudaError_t launch_tma2_generic(const Fused2Args &a, cudaStream_t s, Kern kern)
+// one kernel of the two-step family over `grid` (2-D natural grid, or 1-D over prm.tile_list)
+template <class Cfg, int RY, bool M, class Kern>
+cudaError_t launch_tma2_kernel(const Fused2Args &a, const Tma2Params &prm, dim3 grid, cudaStream_t s, Kern kern)
 {
     CUtensorMap mu, mv, mp, muo, mvo, mpo, mm;
     if (!get_map(a.u, 8, a.pitch, a.ny, Cfg::BW, RY, mu) || !get_map(a.v, 8, a.pitch, a.ny, Cfg::BW, RY, mv) ||
@@ -1197,6 +1343,13 @@ cudaError_t launch_tma2_generic(const Fused2Args &a, cudaStream_t s, Kern kern)
     } else {
         mm = mp;  // unused by the unmasked kernels
     }
+    kern<<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, s>>>(mu, mv, mp, muo, mvo, mpo, mm, prm);
+    return cudaGetLastError();
+}
+
+template <class Cfg, int RY, int MINB, bool M, class Kern>
+cudaError_t launch_tma2_generic(const Fused2Args &a, cudaStream_t s, Kern kern)
+{
     Tma2Params prm;
     prm.u2 = a.u2; prm.v2 = a.v2; prm.p2 = a.p2;
     prm.uold2 = a.uold2; prm.vold2 = a.vold2; prm.pold2 = a.pold2;
@@ -1209,13 +1362,50 @@ cudaError_t launch_tma2_generic(const Fused2Args &a, cudaStream_t s, Kern kern)
                                  resident_ctas(reinterpret_cast<const void *>(kern), Cfg::THREADS, Cfg::SMEM_BYTES, MINB));
     prm.pitch = a.pitch; prm.b = a.b; prm.sc = a.sc;
     prm.push = a.push;
-    kern<<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, s>>>(mu, mv, mp, muo, mvo, mpo, mm, prm);
-    return cudaGetLastError();
+    prm.tile_list = nullptr;
+    prm.list_gx = static_cast<int>(grid.x);
+    return launch_tma2_kernel<Cfg, RY, M>(a, prm, grid, s, kern);
+}
+
+// masked two-step sweep: all-wet tiles through the unmasked kernel `kern_wet`, tiles that see land through
+// the masked kernel `kern_land` (same geometry, same bits)
+template <class CfgWet, class CfgLand, int RY, int MINB, class KernWet, class KernLand>
+cudaError_t launch_tma2_split(const Fused2Args &a, cudaStream_t s, KernWet kern_wet, KernLand kern_land)
+{
+    Tma2Params prm;
+    prm.u2 = a.u2; prm.v2 = a.v2; prm.p2 = a.p2;
+    prm.uold2 = a.uold2; prm.vold2 = a.vold2; prm.pold2 = a.pold2;
+    cudaError_t e = allow_smem(reinterpret_cast<const void *>(kern_wet), CfgWet::SMEM_BYTES);
+    if (e == cudaSuccess) e = allow_smem(reinterpret_cast<const void *>(kern_land), CfgLand::SMEM_BYTES);
+    if (e != cudaSuccess) return e;
+    dim3 grid;
+    tma2_geometry<CfgWet, RY, MINB>(a, prm.tm, grid, resident_ctas(reinterpret_cast<const void *>(kern_wet),
+                                                                  CfgWet::THREADS, CfgWet::SMEM_BYTES, MINB));
+    prm.pitch = a.pitch; prm.b = a.b; prm.sc = a.sc;
+    prm.push = a.push;
+    prm.list_gx = static_cast<int>(grid.x);
+    TileLists tl;
+    e = tile_lists(a.mask8, a.mask8_pitch, a.pitch, a.ny, prm.tm, a.b, CfgWet::OUT, 4, grid, s, tl);
+    if (e != cudaSuccess) return e;
+    if (tl.nwet) {
+        prm.tile_list = tl.wet;
+        e = launch_tma2_kernel<CfgWet, RY, false>(a, prm, dim3(tl.nwet), s, kern_wet);
+        if (e != cudaSuccess) return e;
+    }
+    if (tl.nland) {
+        prm.tile_list = tl.land;
+        e = launch_tma2_kernel<CfgLand, RY, true>(a, prm, dim3(tl.nland), s, kern_land);
+    }
+    return e;
 }
 
 template <int TX, int RY, int STAGES, int MINB, bool PIPE>
 cudaError_t launch_tma2s(const Fused2Args &a, cudaStream_t s)
 {
+    if (a.mask8 && a.mask8_pitch % 16 == 0 && split_masked_launches())
+        return launch_tma2_split<Tma2sCfg<TX, RY, STAGES, false>, Tma2sCfg<TX, RY, STAGES, true>, RY, MINB>(
+            a, s, fused2s_tma_kernel<TX, RY, STAGES, MINB, false, PIPE>,
+            fused2s_tma_kernel<TX, RY, STAGES, MINB, true, PIPE>);
     if (a.mask8)
         return launch_tma2_generic<Tma2sCfg<TX, RY, STAGES, true>, RY, MINB, true>(
             a, s, fused2s_tma_kernel<TX, RY, STAGES, MINB, true, PIPE>);
@@ -1302,6 +1492,22 @@ cudaError_t sw_step2_fused(const Fused2Args &a, int variant, cudaStream_t s)
             return e;
         }
     return cudaErrorInvalidValue;
+}
+
+// the runtime frees (or rebuilds) a byte mask image: drop the tile classifications made for it
+void forget_mask(const unsigned char *m8)
+{
+    std::lock_guard<std::mutex> lock(tile_mu());
+    auto &c = tile_cache();
+    for (auto it = c.begin(); it != c.end();) {
+        if (it->second.mask == m8) {
+            cudaFree(it->second.wet);
+            cudaFree(it->second.land);
+            it = c.erase(it);
+        } else {
+            ++it;
+        }
+    }
 }
 
 void fused2_grid(const Fused2Args &a, int variant, int grid[2])

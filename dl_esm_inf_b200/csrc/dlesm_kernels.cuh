@@ -227,6 +227,8 @@ struct Fused2Args {
     /* launch geometry the sweep would use (grid.x, grid.y) -- for the tiling knob's tests */        \
     void fused_grid(const FusedArgs &a, int variant, int grid[2]);                                   \
     void fused2_grid(const Fused2Args &a, int variant, int grid[2]);                                 \
+    /* a byte mask image is about to be freed: drop what was cached for it */                        \
+    void forget_mask(const unsigned char *m8);                                                       \
     }
 DLESM_FUSED_API(fma_off)
 DLESM_FUSED_API(fma_on)

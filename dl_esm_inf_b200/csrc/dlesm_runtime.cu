@@ -1580,6 +1580,8 @@ void release_mask8(const void *tmask)
     auto it = c.mask8.find(tmask);
     if (it == c.mask8.end()) return;
     if (c.device_ready) cudaStreamSynchronize(c.stream);
+    k::fma_off::forget_mask(it->second.p);
+    k::fma_on::forget_mask(it->second.p);
     cudaFree(it->second.p);
     c.mask8.erase(it);
 }
@@ -3260,7 +3262,11 @@ extern "C" void dlesm_sw_free(dlesm_sw_t *s)
         if (fl) dlesm_free_field(fl);
     for (auto *fl : s->old2)
         if (fl) dlesm_free_field(fl);
-    if (s->mask2) cudaFree(s->mask2);
+    if (s->mask2) {
+        k::fma_off::forget_mask(s->mask2);
+        k::fma_on::forget_mask(s->mask2);
+        cudaFree(s->mask2);
+    }
     delete s;
 }
 
@@ -3287,7 +3293,11 @@ extern "C" void dlesm_sw_free_local(dlesm_sw_t *s)
     if (!mapped) sw_release_peers(s);   // one rank: local bookkeeping only
     for (auto *fl : s->f) drop(fl);
     for (auto *fl : s->old2) drop(fl);
-    if (s->mask2) cudaFree(s->mask2);
+    if (s->mask2) {
+        k::fma_off::forget_mask(s->mask2);
+        k::fma_on::forget_mask(s->mask2);
+        cudaFree(s->mask2);
+    }
     delete s;
 }
 
