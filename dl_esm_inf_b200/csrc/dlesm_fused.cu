@@ -258,9 +258,40 @@ struct TmaStepParams {
     TileMap tm;
     SwScalars sc;
     PushPlan push;
+    PushSync sync;
     const int *tile_list;
     int list_gx;
 };
+// start of an edge tile of a push sweep: wait for the neighbours' previous sweep (see PushSync); call
+// before a CTA-wide barrier that precedes the first load
+__device__ __forceinline__ void sync_wait_neighbours(const PushSync &sy, bool edge)
+{
+    if (edge && static_cast<int>(threadIdx.x) < sy.n_wait) {
+        const long long t0 = clock64();
+        for (;;) {
+            unsigned long long v;
+            asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(sy.local[threadIdx.x]) : "memory");
+            if (v >= sy.wait_epoch) break;
+            if (clock64() - t0 > 40000000000LL) {   // ~20 s: the ranks are out of step -- fatal
+                atomicExch(sy.err, 1);
+                __threadfence_system();
+                __trap();
+            }
+            __nanosleep(100);
+        }
+    }
+}
+// end of a push sweep, called by ONE thread per CTA after a barrier that follows every thread's
+// __threadfence_system(): the CTA that draws the last ticket publishes this rank's epoch
+__device__ __forceinline__ void sync_publish_if_last(const PushSync &sy)
+{
+    if (atomicAdd(sy.ticket, 1u) == gridDim.x * gridDim.y - 1) {
+        __threadfence_system();
+        for (int q = 0; q < sy.n; ++q)
+            asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(sy.remote[q]), "l"(sy.epoch) : "memory");
+        *sy.ticket = 0u;
+    }
+}
 __device__ __forceinline__ void block_tile(const int *tile_list, int list_gx, int &bx, int &by)
 {
     bx = blockIdx.x;
@@ -356,6 +387,9 @@ fused_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_constant
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
+    // an edge tile reads halo cells the neighbours push and pushes into theirs: their previous sweep first
+    sync_wait_neighbours(prm.sync, i_first - 2 < prm.b.xs || min(i_first + TX - 1, i_last) + 2 > prm.b.xe ||
+                                       j0 - 2 < prm.b.ys || j1 + 2 > prm.b.ye);
     __syncthreads();
 
     if (warp == TX / 32) {
@@ -472,6 +506,15 @@ fused_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_constant
         t_hi -= RY;
         __syncwarp();
         if (lane == 0) mbar_arrive(&empty[s]);
+    }
+    if (prm.sync.n > 0) {
+        // every thread's peer stores are ordered before the ticket; the last CTA of a publishing launch
+        // tells the neighbours that this rank's sweep is complete
+        __threadfence_system();
+        if (prm.sync.publish) {
+            asm volatile("bar.sync 1, %0;" ::"r"(TX) : "memory");   // the consumer threads (the producer warp has left)
+            if (tid == 0) sync_publish_if_last(prm.sync);
+        }
     }
 }
 
@@ -763,9 +806,12 @@ cudaError_t launch_tma_mf(const FusedArgs &a, cudaStream_t s)
     tma_geometry<TX, RY, STAGES, MINB, ALN>(a, prm.tm, grid);
     prm.pitch = a.pitch; prm.b = a.b; prm.sc = a.sc;
     prm.push = a.push;
+    prm.sync = a.sync;
     prm.tile_list = nullptr;
     prm.list_gx = static_cast<int>(grid.x);
-    if (M && split_masked_launches() && a.mask8 && a.mask8_pitch % 16 == 0) {
+    // (with remote neighbours the two launches of a split run would both have to take tickets: the masked
+    // kernel alone runs there)
+    if (M && split_masked_launches() && a.mask8 && a.mask8_pitch % 16 == 0 && a.sync.n == 0 && a.sync.n_wait == 0) {
         // all-wet tiles through the unmasked kernel, the rest through the masked one (same bits)
         TileLists tl;
         cudaError_t e = tile_lists(a.mask8, a.mask8_pitch, a.pitch, a.ny, prm.tm, a.b, TX, 3, grid, s, tl);
@@ -839,6 +885,7 @@ struct Tma2Params {
     TileMap tm;
     SwScalars sc;
     PushPlan2 push;
+    PushSync sync;
     const int *tile_list;   // see TmaStepParams
     int list_gx;
 };
@@ -1006,6 +1053,12 @@ fused2s_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_consta
         tma_load_2d(st + Cfg::OFF_OLD + 2 * Cfg::AO, &tm_po, x_old, y_old, &full[s]);
         if (M) tma_load_2d(st + Cfg::OFF_MASK, &tm_mask, x_msk, y_raw, &full[s]);
     };
+    // an edge tile reads halo cells the neighbours push and pushes into theirs: their previous sweep first
+    if (prm.sync.n_wait > 0) {
+        sync_wait_neighbours(prm.sync, i_first - 3 < prm.b.xs || min(i_first + Cfg::OUT - 1, i_last) + 3 > prm.b.xe ||
+                                           j0 - 3 < prm.b.ys || j1 + 3 > prm.b.ye);
+        __syncthreads();
+    }
     // No producer warp here: the per-chunk barrier between the two stages already tells thread 0
     // that every warp is done with a ring stage, so it refills the stage right after it.  (A
     // fifth warp would also cap the kernel at 168 registers: 10 warps on 4 schedulers.)
@@ -1193,6 +1246,13 @@ fused2s_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_consta
             if (tid == 0 && c + STAGES < nchunks) issue(c + STAGES);
         }
         stage_b(nchunks - 1);
+    }
+    if (prm.sync.n > 0) {
+        __threadfence_system();
+        if (prm.sync.publish) {
+            __syncthreads();
+            if (tid == 0) sync_publish_if_last(prm.sync);
+        }
     }
 }
 
@@ -1397,6 +1457,7 @@ cudaError_t launch_tma2_generic(const Fused2Args &a, cudaStream_t s, Kern kern)
                                  resident_ctas(reinterpret_cast<const void *>(kern), Cfg::THREADS, Cfg::SMEM_BYTES, MINB));
     prm.pitch = a.pitch; prm.b = a.b; prm.sc = a.sc;
     prm.push = a.push;
+    prm.sync = a.sync;
     prm.tile_list = nullptr;
     prm.list_gx = static_cast<int>(grid.x);
     return launch_tma2_kernel<Cfg, RY, M>(a, prm, grid, s, kern);
@@ -1418,6 +1479,7 @@ cudaError_t launch_tma2_split(const Fused2Args &a, cudaStream_t s, KernWet kern_
                                                                   CfgWet::THREADS, CfgWet::SMEM_BYTES, MINB));
     prm.pitch = a.pitch; prm.b = a.b; prm.sc = a.sc;
     prm.push = a.push;
+    prm.sync = a.sync;       // n == 0 here: see the caller
     prm.list_gx = static_cast<int>(grid.x);
     TileLists tl;
     e = tile_lists(a.mask8, a.mask8_pitch, a.pitch, a.ny, prm.tm, a.b, CfgWet::OUT, 4, grid, s, tl);
@@ -1450,7 +1512,9 @@ cudaError_t launch_tma2_split(const Fused2Args &a, cudaStream_t s, KernWet kern_
 template <int TX, int RY, int STAGES, int MINB, bool PIPE>
 cudaError_t launch_tma2s(const Fused2Args &a, cudaStream_t s)
 {
-    if (a.mask8 && a.mask8_pitch % 16 == 0 && split_masked_launches())
+    // (with remote neighbours the two launches of a split run would both have to take tickets: the masked
+    // kernel alone runs there)
+    if (a.mask8 && a.mask8_pitch % 16 == 0 && split_masked_launches() && a.sync.n == 0 && a.sync.n_wait == 0)
         return launch_tma2_split<Tma2sCfg<TX, RY, STAGES, false>, Tma2sCfg<TX, RY, STAGES, true>, RY, MINB>(
             a, s, fused2s_tma_kernel<TX, RY, STAGES, MINB, false, PIPE>,
             fused2s_tma_kernel<TX, RY, STAGES, MINB, true, PIPE>);

@@ -716,12 +716,14 @@ cudaError_t tile_ops(const TileOpBatch &b, cudaStream_t s)
 // bounded (~20 s of SM clocks): on time-out *err is set and the kernel TRAPS -- the run ends with
 // a CUDA error on the next call instead of hanging the GPU or sweeping over stale halos.
 // ---------------------------------------------------------------------------------------
-__global__ void peer_signal_wait_kernel(PeerFlags pf, unsigned long long epoch, int *err)
+__global__ void peer_signal_wait_kernel(PeerFlags pf, unsigned long long epoch, int *err, int publish)
 {
     const int q = threadIdx.x;
     if (q >= pf.n) return;
-    __threadfence_system();
-    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(pf.remote[q]), "l"(epoch) : "memory");
+    if (publish) {
+        __threadfence_system();
+        asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(pf.remote[q]), "l"(epoch) : "memory");
+    }
     const long long t0 = clock64();
     for (;;) {
         unsigned long long v;
@@ -739,10 +741,10 @@ __global__ void peer_signal_wait_kernel(PeerFlags pf, unsigned long long epoch, 
         __nanosleep(200);
     }
 }
-cudaError_t peer_signal_wait(const PeerFlags &pf, unsigned long long epoch, int *err, cudaStream_t s)
+cudaError_t peer_signal_wait(const PeerFlags &pf, unsigned long long epoch, int *err, cudaStream_t s, bool publish)
 {
     if (pf.n <= 0) return cudaSuccess;
-    peer_signal_wait_kernel<<<1, 32, 0, s>>>(pf, epoch, err);
+    peer_signal_wait_kernel<<<1, 32, 0, s>>>(pf, epoch, err, publish ? 1 : 0);
     count_launch();
     return cudaGetLastError();
 }

@@ -155,7 +155,26 @@ struct PeerFlags {
     unsigned long long *remote[kMaxPush];
     const unsigned long long *local[kMaxPush];
 };
-cudaError_t peer_signal_wait(const PeerFlags &pf, unsigned long long epoch, int *err, cudaStream_t s);
+cudaError_t peer_signal_wait(const PeerFlags &pf, unsigned long long epoch, int *err, cudaStream_t s,
+                             bool publish = true);
+
+// The same hand-shake folded into a push sweep (no launch of its own).  Wait half: CTAs whose tile
+// reads halo cells or pushes (the edge tiles) wait at their start until each of the `n_wait` neighbours of
+// the PREVIOUS push sweep has published `wait_epoch` -- that sweep is complete there, so its pushes into
+// this rank's halos have landed (RAW) and it no longer reads the buffer this sweep pushes into (WAR);
+// interior tiles start at once and absorb the skew between ranks.  Publish half: when the last CTA of a
+// launch with `publish` set finishes (ticket), it stores `epoch` into the flag cells of this sweep's `n`
+// neighbours.  n_wait = n = 0: no remote neighbour, nothing happens.
+struct PushSync {
+    int n_wait;
+    int n;
+    int publish;
+    const unsigned long long *local[kMaxPush];   // n_wait cells of this rank's flag array
+    unsigned long long *remote[kMaxPush];        // n cells, one in each neighbour's flag array
+    unsigned long long wait_epoch, epoch;
+    unsigned *ticket;
+    int *err;
+};
 
 // ---- the fused step ----
 // Tile grid of a sweep: the CUDA analogue of the reference's OpenMP tile grid (GOCEAN_OMP_GRID="AxB",
@@ -177,6 +196,7 @@ struct FusedArgs {
     SwScalars sc;
     SweepTiles tiles;
     PushPlan push;      // push.n == 0: halos of the new fields are left to the caller
+    PushSync sync;      // sync.n == 0: no in-kernel hand-shake
 };
 
 // ---- two model steps in one sweep (temporal blocking): 96 B / point per TWO steps ----
@@ -208,6 +228,7 @@ struct Fused2Args {
     SwScalars sc;
     SweepTiles tiles;
     PushPlan2 push;     // push.n == 0: halos of the outputs are left to the caller
+    PushSync sync;      // sync.n == 0: no in-kernel hand-shake
 };
 
 // The fused sweeps exist twice: namespace fma_off is compiled with -fmad=false (one rounding per

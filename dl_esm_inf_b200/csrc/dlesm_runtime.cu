@@ -91,6 +91,11 @@ struct Context {
     std::vector<void *> flag_mappings;                // flag-array mappings, closed at finalise
     unsigned long long push_epoch = 0;
     int *push_err = nullptr;                          // device flag: a neighbour wait timed out
+    unsigned *push_ticket = nullptr;                  // CTA ticket of a push sweep that publishes its own epoch
+    // a push sweep whose hand-shake is deferred published `push_epoch` itself; nobody has waited for the
+    // neighbours of THAT sweep yet.  The next push sweep's edge tiles do (PushSync), or push_settle().
+    bool push_pending = false;
+    k::PeerFlags pending_pf{};
     // direct halo exchange over peer memory (DLESM_EXCHANGE_DIRECT): one allocation per rank --
     // [flag cells | ticket | err | receive buffer 0 | receive buffer 1] -- mapped by every rank
     struct XDirect {
@@ -1184,6 +1189,8 @@ int peer_register_with(void *const *fields, int nfields, const CommTables &ct)
         CU(cudaMemset(c.flags, 0, kMaxRanks * sizeof(unsigned long long)));
         CU(cudaMalloc(&c.push_err, sizeof(int)));
         CU(cudaMemset(c.push_err, 0, sizeof(int)));
+        CU(cudaMalloc(&c.push_ticket, sizeof(unsigned)));
+        CU(cudaMemset(c.push_ticket, 0, sizeof(unsigned)));
         c.peer_flags.assign(nranks, nullptr);
         c.peer_flags[me0] = c.flags;
     }
@@ -1664,9 +1671,50 @@ int make_push(const CommTables &ct, const void *const outs[NOUT], Seg *segs, int
 }
 
 // The fused step.  `push_tables` non-null: halo push along that send list.
+// The hand-shake of a push sweep rides in the sweep itself (k::PushSync): its edge tiles wait for the
+// neighbours of the previous, still unsettled push sweep, its last CTA publishes the new epoch.
+void push_sync_fill(Context &c, const k::PeerFlags &pf, k::PushSync &sy)
+{
+    sy = k::PushSync{};
+    if (pf.n <= 0) return;
+    if (c.push_pending) {
+        sy.n_wait = c.pending_pf.n;
+        for (int q = 0; q < sy.n_wait; ++q) sy.local[q] = c.pending_pf.local[q];
+        sy.wait_epoch = c.push_epoch;
+    }
+    sy.n = pf.n;
+    for (int q = 0; q < pf.n; ++q) sy.remote[q] = pf.remote[q];
+    sy.publish = 1;
+    sy.epoch = c.push_epoch + 1;
+    sy.ticket = c.push_ticket;
+    sy.err = c.push_err;
+}
+// after the launch: the sweep publishes push_epoch + 1.  `deferred`: the caller sweeps again (or settles)
+// before anything else reads the pushed halos; otherwise wait for the neighbours right here.
+int push_sync_done(Context &c, const k::PeerFlags &pf, bool deferred, cudaStream_t st)
+{
+    if (pf.n <= 0) return DLESM_OK;
+    ++c.push_epoch;
+    c.pending_pf = pf;
+    c.push_pending = true;
+    if (deferred) return DLESM_OK;
+    c.push_pending = false;
+    CU(k::peer_signal_wait(pf, c.push_epoch, c.push_err, st, /*publish=*/false));
+    return DLESM_OK;
+}
+int push_settle()
+{
+    Context &c = ctx();
+    if (!c.push_pending) return DLESM_OK;
+    c.push_pending = false;
+    CU(k::peer_signal_wait(c.pending_pf, c.push_epoch, c.push_err, c.stream, /*publish=*/false));
+    return DLESM_OK;
+}
+
 int sw_step_fused_impl(const void *u, const void *v, const void *p, void *uold, void *vold, void *pold, void *unew,
                        void *vnew, void *pnew, double dx, double dy, double tdt, double alpha, int first, int xs,
-                       int xe, int ys, int ye, const void *tm, int variant, const CommTables *push_tables)
+                       int xe, int ys, int ye, const void *tm, int variant, const CommTables *push_tables,
+                       bool deferred = false)
 {
     SWEEP_PROLOGUE(unew)
     (void)b;
@@ -1708,6 +1756,7 @@ int sw_step_fused_impl(const void *u, const void *v, const void *p, void *uold, 
         rc = make_push<k::PushSeg, 3>(*push_tables, outs, a.push.seg, a.push.n, pf, "sw_step_fused");
         if (rc != DLESM_OK) return rc;
     }
+    push_sync_fill(c, pf, a.sync);
     ProfScope ps;
     rc = prof_begin(ps, st);
     if (rc != DLESM_OK) return rc;
@@ -1723,19 +1772,16 @@ int sw_step_fused_impl(const void *u, const void *v, const void *p, void *uold, 
     const int depth_new = push_tables ? 1 : 0;
     mark_clean(unew, depth_new); mark_clean(vnew, depth_new); mark_clean(pnew, depth_new);
     if (!first) { mark_written(uold); mark_written(vold); mark_written(pold); }
-    if (push_tables && pf.n > 0) {
-        // neighbours must not start their next sweep before these pushes landed, nor push into
-        // a buffer this rank is still reading: publish the epoch, wait for theirs
-        ++c.push_epoch;
-        CU(k::peer_signal_wait(pf, c.push_epoch, c.push_err, st));
-    }
-    return DLESM_OK;
+    // neighbours must not start their next sweep before these pushes landed, nor push into a buffer this
+    // rank is still reading: the sweep published its epoch, someone waits for theirs
+    return push_sync_done(c, pf, deferred, st);
 }
 
 int sw_step2_fused_impl(const void *u, const void *v, const void *p, const void *uold, const void *vold,
                         const void *pold, void *u2, void *v2, void *p2, void *uold2, void *vold2, void *pold2,
                         double dx, double dy, double tdt, double alpha, int xs, int xe, int ys, int ye,
-                        const unsigned char *mask8, int mask8_pitch, int variant, const CommTables *push_tables)
+                        const unsigned char *mask8, int mask8_pitch, int variant, const CommTables *push_tables,
+                        bool deferred = false)
 {
     SWEEP_PROLOGUE(u2)
     (void)b;
@@ -1784,6 +1830,7 @@ int sw_step2_fused_impl(const void *u, const void *v, const void *p, const void 
         rc = make_push<k::PushSeg2, 6>(*push_tables, outs, a.push.seg, a.push.n, pf, "sw_step2_fused");
         if (rc != DLESM_OK) return rc;
     }
+    push_sync_fill(c, pf, a.sync);
     ProfScope ps;
     rc = prof_begin(ps, st);
     if (rc != DLESM_OK) return rc;
@@ -1796,11 +1843,7 @@ int sw_step2_fused_impl(const void *u, const void *v, const void *p, const void 
     rc = prof_end(ps, st);
     if (rc != DLESM_OK) return rc;
     for (const void *o : outs) mark_clean(o, push_tables ? 2 : 0);
-    if (push_tables && pf.n > 0) {
-        ++c.push_epoch;
-        CU(k::peer_signal_wait(pf, c.push_epoch, c.push_err, st));
-    }
-    return DLESM_OK;
+    return push_sync_done(c, pf, deferred, st);
 }
 }  // namespace
 
@@ -2792,14 +2835,17 @@ extern "C" int dlesm_sw_step(dlesm_sw_t *s, int nsteps)
             // two steps in one sweep: 96 B / point for both
             const dlesm_region &rt = f[DLESM_SW_P]->fb.internal;
             int rc = DLESM_OK;
-            if (!s->deep_valid) rc = sw_fill_deep_halos(s);
+            if (!s->deep_valid) {
+                rc = push_settle();
+                if (rc == DLESM_OK) rc = sw_fill_deep_halos(s);
+            }
             if (rc != DLESM_OK) return rc;
             rc = sw_step2_fused_impl(f[DLESM_SW_U]->dptr, f[DLESM_SW_V]->dptr, f[DLESM_SW_P]->dptr,
                                      f[DLESM_SW_UOLD]->dptr, f[DLESM_SW_VOLD]->dptr, f[DLESM_SW_POLD]->dptr,
                                      f[DLESM_SW_UNEW]->dptr, f[DLESM_SW_VNEW]->dptr, f[DLESM_SW_PNEW]->dptr,
                                      s->old2[0]->dptr, s->old2[1]->dptr, s->old2[2]->dptr, dx, dy, s->tdt, s->alpha,
                                      rt.xstart, rt.xstop, rt.ystart, rt.ystop, s->mask2, s->mask2_pitch, s->variant2,
-                                     s->push ? &s->push_tables : nullptr);
+                                     s->push ? &s->push_tables : nullptr, /*deferred=*/true);
             if (rc != DLESM_OK) return rc;
             for (int q = 0; q < 3; ++q) {
                 std::swap(f[DLESM_SW_U + q]->dptr, f[DLESM_SW_UNEW + q]->dptr);
@@ -2821,7 +2867,8 @@ extern "C" int dlesm_sw_step(dlesm_sw_t *s, int nsteps)
             rc = sw_step_fused_impl(P(DLESM_SW_U), P(DLESM_SW_V), P(DLESM_SW_P), P(DLESM_SW_UOLD), P(DLESM_SW_VOLD),
                                     P(DLESM_SW_POLD), P(DLESM_SW_UNEW), P(DLESM_SW_VNEW), P(DLESM_SW_PNEW), dx, dy,
                                     s->tdt, s->alpha, first, rt.xstart, rt.xstop, rt.ystart, rt.ystop,
-                                    s->tmask_dev, s->variant, s->push ? &s->push_tables : nullptr);
+                                    s->tmask_dev, s->variant, s->push ? &s->push_tables : nullptr,
+                                    /*deferred=*/true);
             if (rc != DLESM_OK) return rc;
             if (!s->push) {
                 rc = sw_fill_halos(s, DLESM_SW_UNEW, 3);
@@ -2853,7 +2900,8 @@ extern "C" int dlesm_sw_step(dlesm_sw_t *s, int nsteps)
         if (first) s->tdt = s->tdt + s->tdt;
         ++s->ncycle;
     }
-    return DLESM_OK;
+    // the last push sweep published its epoch; the neighbours' must be in before the caller reads halos
+    return push_settle();
 }
 
 // One model time step driven with HOST state (the `e2e` path of bench.py): instead of
