@@ -297,6 +297,14 @@ def run_ours(args):
             dist.barrier()
             torch.cuda.synchronize()
 
+    def gather_ranks(obj):
+        """every rank's value on every rank (small Python objects; outside the timed regions)"""
+        if dist is None:
+            return [obj]
+        out = [None] * world
+        dist.all_gather_object(out, obj)
+        return out
+
     def max_over_ranks(x):
         if dist is None:
             return x
@@ -393,8 +401,16 @@ def run_ours(args):
                 # the counters tick at their own pace: this is a lower bound on the region's traffic unless
                 # the region is long (the sustained leg); reported per step beside the algorithmic figure
                 nvl = [(b - a) * 1024.0 / nsteps for a, b in zip(nvl0, nvl1)]
+            clocks = sampler.summary(w0, w1)
+            # what each rank saw: its own sweep time (with the in-sweep hand-shake a rank that waits for a
+            # slower neighbour shows the wait here) and its own GPU's clocks -- a slow GPU explains itself
+            per_rank = None
+            if world > 1:
+                per_rank = gather_ranks({"rank": rank + 1, "kernel_ms": kms.value / max(1, kn.value),
+                                         "elapsed_ms_per_step": ms.value / nsteps, "sm_mhz": clocks.get("sm_mhz"),
+                                         "reasons": clocks.get("reasons")})
             return dict(nvlink_bytes_per_step=nvl, elapsed_ms=el, launches=int(launches), kernel_ms_total=kms.value, kernel_launches=kn.value,
-                        clocks=sampler.summary(w0, w1), value=total_points * nsteps / (el * 1e-3), steps=nsteps)
+                        clocks=clocks, value=total_points * nsteps / (el * 1e-3), steps=nsteps, per_rank=per_rank)
 
         def roofline_of(r):
             """the dominant kernel (fused sweep) against the measured HBM copy bandwidth.  Bytes per launch =
@@ -469,7 +485,8 @@ def run_ours(args):
                             "nvml_note": "NVML NVLINK_THROUGHPUT counters of this rank's GPU (all links) over the "
                                          "%s leg, per model step: data = payload, raw = with protocol overhead"
                                          % ("sustained" if sustain_s > 0 else "timed"),
-                            "step_minus_sweep_us": (R["elapsed_ms"] - R["kernel_ms_total"]) / steps * 1e3}
+                            "step_minus_sweep_us": (R["elapsed_ms"] - R["kernel_ms_total"]) / steps * 1e3,
+                            "per_rank": R.get("per_rank")}
 
         R.update(cks=cks, halo_traffic=halo_traffic, halo=halo, grid=grid, sw=sw, probe=probe, sub=sub, gx=gx,
                  gy=gy, local_points=local_points, total_points=total_points, two_step=two_step,
@@ -653,6 +670,7 @@ def run_config5(args, fd, L, C, world, rank, max_over_ranks, barrier):
     stored into the neighbours' receive slots over NVLink + flag hand-shake) and NCCL."""
     out = []
     reps = 20
+    host_issue_us = [0.0]
 
     def timed_us(fn):
         for _ in range(3):
@@ -660,8 +678,10 @@ def run_config5(args, fd, L, C, world, rank, max_over_ranks, barrier):
         fd.dev_sync()
         barrier()
         L.dlesm_event_record(6)
+        h0 = time.perf_counter()
         for _ in range(reps):
             fn()
+        host_issue_us[0] = (time.perf_counter() - h0) / reps * 1e6   # host time to ISSUE a call (no sync)
         L.dlesm_event_record(7)
         ms = C.c_double(0.0)
         assert L.dlesm_event_elapsed_ms(6, 7, C.byref(ms)) == 0
@@ -695,6 +715,7 @@ def run_config5(args, fd, L, C, world, rank, max_over_ranks, barrier):
                 for mode, name in ((fd.EXCHANGE_DIRECT, "direct"), (fd.EXCHANGE_NCCL, "nccl")):
                     fd.set_exchange_mode(mode)
                     rec["halo_exchange_%s_us" % name] = timed_us(lambda: f.halo_exchange(depth))
+                    rec["halo_exchange_%s_host_issue_us" % name] = host_issue_us[0]
                 fd.set_exchange_mode(fd.EXCHANGE_DIRECT)
             out.append(rec)
             f.free()

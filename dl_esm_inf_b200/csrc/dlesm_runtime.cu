@@ -1673,10 +1673,20 @@ int make_push(const CommTables &ct, const void *const outs[NOUT], Seg *segs, int
 // The fused step.  `push_tables` non-null: halo push along that send list.
 // The hand-shake of a push sweep rides in the sweep itself (k::PushSync): its edge tiles wait for the
 // neighbours of the previous, still unsettled push sweep, its last CTA publishes the new epoch.
+// DLESM_PUSH_SYNC=kernel keeps round 1's form for A/B runs: a one-warp kernel after every push sweep
+// publishes the epoch and waits for the neighbours'.  Must agree across ranks.
+bool push_sync_in_sweep()
+{
+    static const bool in_sweep = [] {
+        const char *e = std::getenv("DLESM_PUSH_SYNC");
+        return !(e && std::strcmp(e, "kernel") == 0);
+    }();
+    return in_sweep;
+}
 void push_sync_fill(Context &c, const k::PeerFlags &pf, k::PushSync &sy)
 {
     sy = k::PushSync{};
-    if (pf.n <= 0) return;
+    if (pf.n <= 0 || !push_sync_in_sweep()) return;
     if (c.push_pending) {
         sy.n_wait = c.pending_pf.n;
         for (int q = 0; q < sy.n_wait; ++q) sy.local[q] = c.pending_pf.local[q];
@@ -1695,6 +1705,10 @@ int push_sync_done(Context &c, const k::PeerFlags &pf, bool deferred, cudaStream
 {
     if (pf.n <= 0) return DLESM_OK;
     ++c.push_epoch;
+    if (!push_sync_in_sweep()) {
+        CU(k::peer_signal_wait(pf, c.push_epoch, c.push_err, st, /*publish=*/true));
+        return DLESM_OK;
+    }
     c.pending_pf = pf;
     c.push_pending = true;
     if (deferred) return DLESM_OK;
