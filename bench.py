@@ -379,8 +379,11 @@ def run_ours(args):
             library's stream), max over ranks; the dominant kernel timed by its own event pairs"""
             L.dlesm_profile_enable(1)
             L.dlesm_profile_read(None, None, 1)
-            barrier()
+            # (the NVML counter reads take milliseconds and serialise across the ranks' processes: they stay
+            # OUTSIDE the barriers -- taken between the barrier and the first event they started the ranks up
+            # to 34 ms apart at N=4, which the max over ranks then charged to the steps)
             nvl0 = sampler.nvlink_kib() if world > 1 else None
+            barrier()
             launches0 = fd.kernel_launch_count()
             w0 = time.time()
             L.dlesm_event_record(0)

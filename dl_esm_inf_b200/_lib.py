@@ -186,6 +186,8 @@ SIGNATURES = {
     "dlesm_kernel_launch_count": (C.c_longlong, []),
     "dlesm_profile_enable": (_I, [_I]),
     "dlesm_profile_read": (_I, [_PD, C.POINTER(C.c_longlong), _I]),
+    "dlesm_debug_cta_trace_begin": (_I, [_I]),
+    "dlesm_debug_cta_trace_end": (_I, [C.POINTER(C.c_longlong), _I]),
     "dlesm_sw_free": (None, [_V]),
     "dlesm_sw_free_local": (None, [_V]),
     "dlesm_sw_launch_grid": (_I, [_V, _I, _PI]),

@@ -292,6 +292,28 @@ __device__ __forceinline__ void sync_publish_if_last(const PushSync &sy)
         *sy.ticket = 0u;
     }
 }
+// diagnostics (dlesm_debug_cta_trace_begin/end): when set, thread 0 of every CTA of the TMA sweeps records
+// its timeline -- slot 0 start, 1 end, 2 SM id, 3 after the neighbour wait (globaltimer, ns)
+__device__ long long *g_cta_trace = nullptr;
+__device__ __forceinline__ long long global_ns()
+{
+    long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __forceinline__ void cta_trace(int slot)
+{
+    long long *tr = g_cta_trace;
+    if (tr && threadIdx.x == 0) {
+        long long *e = tr + 4 * (static_cast<long long>(blockIdx.y) * gridDim.x + blockIdx.x);
+        e[slot] = global_ns();
+        if (slot == 0) {
+            unsigned sm;
+            asm volatile("mov.u32 %0, %smid;" : "=r"(sm));
+            e[2] = sm;
+        }
+    }
+}
 __device__ __forceinline__ void block_tile(const int *tile_list, int list_gx, int &bx, int &by)
 {
     bx = blockIdx.x;
@@ -387,9 +409,11 @@ fused_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_constant
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
+    cta_trace(0);
     // an edge tile reads halo cells the neighbours push and pushes into theirs: their previous sweep first
     sync_wait_neighbours(prm.sync, i_first - 2 < prm.b.xs || min(i_first + TX - 1, i_last) + 2 > prm.b.xe ||
                                        j0 - 2 < prm.b.ys || j1 + 2 > prm.b.ye);
+    cta_trace(3);
     __syncthreads();
 
     if (warp == TX / 32) {
@@ -518,6 +542,7 @@ fused_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_constant
             if (tid == 0) sync_publish_if_last(prm.sync);
         }
     }
+    cta_trace(1);
 }
 
 // ---- tensor-map cache ----
@@ -1056,11 +1081,13 @@ fused2s_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_consta
         if (M) tma_load_2d(st + Cfg::OFF_MASK, &tm_mask, x_msk, y_raw, &full[s]);
     };
     // an edge tile reads halo cells the neighbours push and pushes into theirs: their previous sweep first
+    cta_trace(0);
     if (prm.sync.n_wait > 0) {
         sync_wait_neighbours(prm.sync, i_first - 3 < prm.b.xs || min(i_first + Cfg::OUT - 1, i_last) + 3 > prm.b.xe ||
                                            j0 - 3 < prm.b.ys || j1 + 3 > prm.b.ye);
         __syncthreads();
     }
+    cta_trace(3);
     // No producer warp here: the per-chunk barrier between the two stages already tells thread 0
     // that every warp is done with a ring stage, so it refills the stage right after it.  (A
     // fifth warp would also cap the kernel at 168 registers: 10 warps on 4 schedulers.)
@@ -1098,15 +1125,38 @@ fused2s_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_consta
     long long qo = (static_cast<long long>(j0) - 5) * prm.pitch + (i - 1);
     const long long pitch = prm.pitch;
     int t_lo = active ? 4 : (1 << 30), t_hi = nsteps;
-    // push boxes this lane's column and this CTA's rows can meet (0 for almost every thread)
+    // push boxes this lane's column and this CTA's rows can meet (0 for almost every thread).  With a staging
+    // strip the narrow boxes (x edges, corners) are deferred to the end of the CTA: `pmask` keeps the wide
+    // ones (north / south rows), `dmask` (CTA-uniform) the deferred ones this CTA's columns and rows meet.
     unsigned pmask = 0;
+    // deferred boxes this CTA's columns and rows meet (CTA-uniform; recomputed in the epilogue rather than
+    // carried through the march: the masked form has no register to spare)
+    auto deferred_boxes = [&]() {
+        unsigned d = 0;
+        if (prm.push.strip) {
+            const int i_end = min(i_first + Cfg::OUT - 1, i_last);   // last output column of this CTA
+            for (int q = 0; q < prm.push.n; ++q) {
+                const PushSeg2 &g = prm.push.seg[q];
+                if (g.i1 - g.i0 < 2 && g.j1 >= j0 && g.j0 <= j1 && g.i1 >= i_first && g.i0 <= i_end) d |= 1u << q;
+            }
+        }
+        return d;
+    };
     if (active)
         for (int q = 0; q < prm.push.n; ++q) {
             const PushSeg2 &g = prm.push.seg[q];
-            if (i >= g.i0 && i <= g.i1 && g.j1 >= j0 && g.j0 <= j1) pmask |= 1u << q;
+            if (!(prm.push.strip && g.i1 - g.i0 < 2) && i >= g.i0 && i <= g.i1 && g.j1 >= j0 && g.j0 <= j1)
+                pmask |= 1u << q;
         }
     const int pfirst = pmask ? __ffs(pmask) - 1 : 0;
     const unsigned prest = pmask & (pmask - 1);
+    // this lane's slot in the staging strip (doubles): the two columns at either x edge of the tile
+    int qs = -1;
+    if (active && deferred_boxes()) {
+        const int h = prm.b.ye - prm.b.ys + 1;
+        if (i - prm.b.xs < 2) qs = (j0 - prm.b.ys) * 12 + (i - prm.b.xs);
+        else if (prm.b.xe - i < 2) qs = (h + (j0 - prm.b.ys)) * 12 + (i - (prm.b.xe - 1));
+    }
     int jrow = j0 - 4;
 
     // state handed from stage A of a chunk to stage B of the same chunk
@@ -1200,6 +1250,14 @@ fused2s_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_consta
                     __stcs(prm.uold2 + qo, o.uold);
                     __stcs(prm.vold2 + qo, o.vold);
                     __stcs(prm.pold2 + qo, o.pold);
+                    if (qs >= 0) {
+                        // x-edge lane: outputs of this row into the local staging strip (this lane stores
+                        // rows j0.. in order: r - t_lo counts them within the chunk)
+                        double *e = prm.push.strip + qs;
+                        e[0] = o.unew; e[2] = o.vnew; e[4] = o.pnew;
+                        e[6] = o.uold; e[8] = o.vold; e[10] = o.pold;
+                        qs += 12;
+                    }
                     if (pmask) {
                         // first box inline (an x-edge column meets it on every row; a call would save and
                         // restore ~150 live registers each time), the rest -- corners -- out of line
@@ -1249,13 +1307,39 @@ fused2s_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_consta
         }
         stage_b(nchunks - 1);
     }
+    const unsigned dmask = deferred_boxes();
+    if (dmask) {
+        // deferred boxes: every thread of the CTA copies its share of the staged rows to the neighbours
+        __syncthreads();
+        const double *strip = prm.push.strip;
+        const long long h = prm.b.ye - prm.b.ys + 1;
+        const int i_end = min(i_first + Cfg::OUT - 1, i_last);
+        for (unsigned m = dmask; m; m &= m - 1) {
+            const PushSeg2 &g = prm.push.seg[__ffs(m) - 1];
+            const int c0 = max(g.i0, i_first), c1 = min(g.i1, i_end);
+            const int r0 = max(g.j0, j0), r1 = min(g.j1, j1);
+            const int nc = c1 - c0 + 1, total = (r1 - r0 + 1) * 6 * nc;
+            for (int e = tid; e < total; e += TX) {
+                const int c = e % nc, f = (e / nc) % 6, r = e / (6 * nc);
+                const int col = c0 + c, row = r0 + r;
+                const long long srow = (col - prm.b.xs < 2) ? (row - prm.b.ys) : (h + (row - prm.b.ys));
+                const int cell = (col - prm.b.xs < 2) ? (col - prm.b.xs) : (col - (prm.b.xe - 1));
+                const double v = __ldcg(strip + srow * 12 + f * 2 + cell);
+                if (g.dpitch == 0)   // packed: the neighbour's slot for this direction, [row][field][column]
+                    g.dst[0][(static_cast<long long>(row - g.j0) * 6 + f) * (g.i1 - g.i0 + 1) + (col - g.i0)] = v;
+                else
+                    g.dst[f][idx(g.dpitch, g.ides + (col - g.i0), g.jdes + (row - g.j0))] = v;
+            }
+        }
+    }
     if (prm.sync.n > 0) {
-        if (pmask) __threadfence_system();   // only the threads that pushed (see the one-step sweep)
+        if (pmask || dmask) __threadfence_system();   // only the threads that pushed (see the one-step sweep)
         if (prm.sync.publish) {
             __syncthreads();
             if (tid == 0) sync_publish_if_last(prm.sync);
         }
     }
+    cta_trace(1);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -1592,6 +1676,8 @@ bool fused2_supported(const Fused2Args &a)
 }
 
 bool fused2_push_supported(int variant) { return variant == 0 || (variant >= 10 && variant < 20); }
+
+cudaError_t set_cta_trace(long long *buf) { return cudaMemcpyToSymbol(g_cta_trace, &buf, sizeof(buf)); }
 
 cudaError_t sw_step2_fused(const Fused2Args &a, int variant, cudaStream_t s)
 {

@@ -741,6 +741,51 @@ __global__ void peer_signal_wait_kernel(PeerFlags pf, unsigned long long epoch, 
         __nanosleep(200);
     }
 }
+__global__ void __launch_bounds__(256) peer_wait_scatter_kernel(const __grid_constant__ PeerFlags pf, unsigned long long epoch,
+                                                                int *err, int publish, const __grid_constant__ StripScatter sp)
+{
+    const int q = threadIdx.x;
+    if (q < pf.n) {
+        if (publish && blockIdx.x == 0) {
+            __threadfence_system();
+            asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(pf.remote[q]), "l"(epoch) : "memory");
+        }
+        const long long t0 = clock64();
+        for (;;) {
+            unsigned long long v;
+            asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(pf.local[q]) : "memory");
+            if (v >= epoch) break;
+            if (clock64() - t0 > 40000000000LL) {   // fatal, like peer_signal_wait_kernel
+                atomicExch(err, 1);
+                __threadfence_system();
+                __trap();
+            }
+            __nanosleep(200);
+        }
+    }
+    __syncthreads();
+    // the slots were written by other GPUs (or by this one's sweep): read them past L1
+    for (int b = 0; b < sp.n; ++b) {
+        const StripScatter::Item &it = sp.item[b];
+        const int total = it.nx * it.ny * 6;
+        for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < total; e += gridDim.x * blockDim.x) {
+            const int c = e % it.nx, f = (e / it.nx) % 6, r = e / (6 * it.nx);
+            sp.dst[f][idx(sp.pitch, it.ides + c, it.jdes + r)] = __ldcg(it.slot + e);
+        }
+    }
+}
+cudaError_t peer_wait_scatter(const PeerFlags &pf, unsigned long long epoch, int *err, bool publish,
+                              const StripScatter &sp, cudaStream_t s)
+{
+    if (sp.n <= 0) return pf.n > 0 ? peer_signal_wait(pf, epoch, err, s, publish) : cudaSuccess;
+    long long total = 0;
+    for (int b = 0; b < sp.n; ++b) total += static_cast<long long>(sp.item[b].nx) * sp.item[b].ny * 6;
+    const unsigned blocks = static_cast<unsigned>(std::max(1LL, std::min<long long>((total + 2047) / 2048, kSMs)));
+    peer_wait_scatter_kernel<<<blocks, 256, 0, s>>>(pf, epoch, err, publish ? 1 : 0, sp);
+    count_launch();
+    return cudaGetLastError();
+}
+
 cudaError_t peer_signal_wait(const PeerFlags &pf, unsigned long long epoch, int *err, cudaStream_t s, bool publish)
 {
     if (pf.n <= 0) return cudaSuccess;

@@ -157,6 +157,20 @@ struct PeerFlags {
 };
 cudaError_t peer_signal_wait(const PeerFlags &pf, unsigned long long epoch, int *err, cudaStream_t s,
                              bool publish = true);
+// The receiving end of the two-step sweep's packed x-edge / corner strips (PushPlan2): after the
+// hand-shake (every CTA waits for the neighbours' epoch itself) the rows a neighbour left in this rank's
+// slot -- [row][field 0..5][column] doubles -- go into the halo columns of the six output arrays.
+struct StripScatter {
+    int n;
+    int pitch;
+    struct Item {
+        int ides, jdes, nx, ny;
+        const double *slot;
+    } item[8];
+    double *dst[6];
+};
+cudaError_t peer_wait_scatter(const PeerFlags &pf, unsigned long long epoch, int *err, bool publish,
+                              const StripScatter &sp, cudaStream_t s);
 
 // The same hand-shake folded into a push sweep (no launch of its own).  Wait half: CTAs whose tile
 // reads halo cells or pushes (the edge tiles) wait at their start until each of the `n_wait` neighbours of
@@ -213,9 +227,16 @@ struct PushSeg2 {
     int pad_;
     double *dst[6];
 };
+// `strip` non-null: boxes at most two columns wide (the east / west edges and the corners) are DEFERRED --
+// the lanes on the tile's two x-edge column pairs store their outputs into this LOCAL staging strip
+// ([side 0 = west, 1 = east][row - b.ys][field 0..5][cell 0..1] doubles) on every row, and when a CTA
+// has finished its segment all its threads copy the rows of those boxes to the neighbours in one burst.
+// (CTA timelines with remote x neighbours: the per-row peer stores made an edge CTA of the two-step sweep
+// 3.5x longer and slowed the CTAs sharing its SM; profiles/r02q_cta_trace_n4.jsonl.)
 struct PushPlan2 {
     int n;
     int pad_;
+    double *strip;
     PushSeg2 seg[kMaxPush];
 };
 struct Fused2Args {
@@ -250,6 +271,9 @@ struct Fused2Args {
     void fused2_grid(const Fused2Args &a, int variant, int grid[2]);                                 \
     /* a byte mask image is about to be freed: drop what was cached for it */                        \
     void forget_mask(const unsigned char *m8);                                                       \
+    /* diagnostics: CTA (by * gridDim.x + bx) of the TMA sweeps records globaltimer at its start,    \
+       after the neighbour wait and at its end, and its SM id: 4 long long each; null = off */       \
+    cudaError_t set_cta_trace(long long *buf);                                                       \
     }
 DLESM_FUSED_API(fma_off)
 DLESM_FUSED_API(fma_on)

@@ -92,6 +92,8 @@ struct Context {
     unsigned long long push_epoch = 0;
     int *push_err = nullptr;                          // device flag: a neighbour wait timed out
     unsigned *push_ticket = nullptr;                  // CTA ticket of a push sweep that publishes its own epoch
+    double *push_strip = nullptr;                     // local staging strip of the two-step sweep's deferred x-edge push
+    size_t push_strip_cap = 0;
     // a push sweep whose hand-shake is deferred published `push_epoch` itself; nobody has waited for the
     // neighbours of THAT sweep yet.  The next push sweep's edge tiles do (PushSync), or push_settle().
     bool push_pending = false;
@@ -102,6 +104,9 @@ struct Context {
         bool ready = false;
         char *base = nullptr;
         size_t slot_cap = 0;                          // elements per direction slot
+        // second region of the same allocation: 2 x 8 direction slots for the packed x-edge / corner
+        // strips of the two-step halo push (k::PushPlan2), buffers alternating with the push epoch
+        size_t pslot_cap = 0;
         std::vector<char *> peer_base;                // the same allocation on rank r (own for r = me)
         std::vector<unsigned long long> count;        // exchanges done with rank r (equal on both ends)
         std::vector<void *> mappings;
@@ -1161,6 +1166,14 @@ void neighbours_of(const CommTables &ct, std::vector<char> &is_nb)
         if (g.peer0 >= 0 && g.peer0 < static_cast<int>(is_nb.size())) is_nb[g.peer0] = 1;
 }
 
+int xdirect_setup();
+// slot of the packed push strip for direction tag `dir` (1..8) in the allocation at `base`
+double *push_slot(char *base, unsigned long long epoch, int dir)
+{
+    const Context::XDirect &xd = ctx().xd;
+    return reinterpret_cast<double *>(base + 4096) + 2 * 8 * xd.slot_cap + ((epoch & 1) * 8 + (dir - 1)) * xd.pslot_cap;
+}
+
 int peer_register_with(void *const *fields, int nfields, const CommTables &ct)
 {
     Context &c = ctx();
@@ -1193,6 +1206,11 @@ int peer_register_with(void *const *fields, int nfields, const CommTables &ct)
         CU(cudaMemset(c.push_ticket, 0, sizeof(unsigned)));
         c.peer_flags.assign(nranks, nullptr);
         c.peer_flags[me0] = c.flags;
+    }
+    // the slots of the packed push strips live in the direct exchange's allocation (collective, once)
+    if (!c.xd.ready && (nranks == 1 || c.comm_ready)) {
+        rc = xdirect_setup();
+        if (rc != DLESM_OK) return rc;
     }
     if (nranks == 1) {
         for (int q = 0; q < nfields; ++q) {
@@ -1273,7 +1291,7 @@ int peer_unregister_fields(void *const *fields, int nfields)
 }  // namespace
 
 namespace {
-constexpr size_t kXdFlagsBytes = 4096;     // flag cells [kMaxRanks] at 0, ticket at 1024, err at 1032
+constexpr size_t kXdFlagsBytes = 4096;     // flag cells [kMaxRanks] at 0, ticket at 1024, err at 1032 (push_slot assumes 4096)
 
 // Collective, once per process (at the first direct exchange, which every rank reaches together):
 // allocate this rank's flag cells + two receive buffers as ONE allocation and map every rank's.
@@ -1289,7 +1307,8 @@ int xdirect_setup()
     size_t mb = 64;
     if (const char *e = std::getenv("DLESM_XDIRECT_MB")) mb = std::max(1L, std::atol(e));
     xd.slot_cap = mb * (1u << 20) / sizeof(double) / 8;                // 8 direction slots per buffer
-    const size_t bytes = kXdFlagsBytes + 2 * 8 * xd.slot_cap * sizeof(double);
+    xd.pslot_cap = xd.slot_cap;
+    const size_t bytes = kXdFlagsBytes + 2 * 8 * (xd.slot_cap + xd.pslot_cap) * sizeof(double);
     CU(cudaMalloc(&xd.base, bytes));
     CU(cudaMemset(xd.base, 0, kXdFlagsBytes));
     xd.peer_base.assign(nranks, nullptr);
@@ -1620,8 +1639,12 @@ int prof_end(const ProfScope &ps, cudaStream_t st)
 
 // push boxes: one per send-list entry of `ct` (src/parallel_comms_mod.f90:70-83), aimed at the
 // destination rank's counterparts of the `nout` output arrays
+// `strips` (two-step sweep only): a box at most two columns wide is aimed at the packed slot of its
+// direction tag in the neighbour's exchange allocation (dpitch = 0 marks it; dst[0] = the slot for the
+// epoch the sweep will publish), which the neighbour scatters into its halo columns after the hand-shake
 template <class Seg, int NOUT>
-int make_push(const CommTables &ct, const void *const outs[NOUT], Seg *segs, int &nseg, k::PeerFlags &pf, const char *who)
+int make_push(const CommTables &ct, const void *const outs[NOUT], Seg *segs, int &nseg, k::PeerFlags &pf, const char *who,
+              bool strips = false)
 {
     Context &c = ctx();
     if (!ct.valid) {
@@ -1653,12 +1676,19 @@ int make_push(const CommTables &ct, const void *const outs[NOUT], Seg *segs, int
             return DLESM_ERR_STATE;
         }
         g.dpitch = pv[0]->pitch_by_rank[dest];
+        const bool packed = strips && g.i1 - g.i0 < 2 && c.xd.ready && t.dirsend[sidx] >= 1 && t.dirsend[sidx] <= 8 &&
+                            dest < static_cast<int>(c.xd.peer_base.size()) && c.xd.peer_base[dest] &&
+                            static_cast<size_t>(t.nxsend[sidx]) * t.nysend[sidx] * NOUT <= c.xd.pslot_cap;
         for (int q = 0; q < NOUT; ++q) {
             g.dst[q] = pv[q]->by_rank[dest];
             if (!g.dst[q]) {
                 set_error(DLESM_ERR_STATE, std::string(who) + ": a neighbour's field is not mapped");
                 return DLESM_ERR_STATE;
             }
+        }
+        if (packed) {
+            g.dpitch = 0;
+            g.dst[0] = push_slot(c.xd.peer_base[dest], c.push_epoch + 1, t.dirsend[sidx]);
         }
         if (dest != me0 && !seen[dest]) {
             seen[dest] = true;
@@ -1834,15 +1864,61 @@ int sw_step2_fused_impl(const void *u, const void *v, const void *p, const void 
         return DLESM_ERR_ARGS;
     }
     a.push.n = 0;
+    a.push.strip = nullptr;
     k::PeerFlags pf{};
+    k::StripScatter sp{};
+    bool strips = false;
     if (push_tables) {
         // the tables must be the depth-2 ones
         if (!k::fma_off::fused2_push_supported(variant)) {
             set_error(DLESM_ERR_ARGS, "sw_step2_fused: halo push needs the shuffle form of the sweep (variant 0 or 10..19)");
             return DLESM_ERR_ARGS;
         }
-        rc = make_push<k::PushSeg2, 6>(*push_tables, outs, a.push.seg, a.push.n, pf, "sw_step2_fused");
+        // x-edge and corner boxes (at most two columns wide) leave through a local staging strip in ONE
+        // burst per CTA into the packed slot of their direction in the neighbour's exchange allocation, and
+        // the neighbour scatters them into its halo columns after the hand-shake (k::PushPlan2,
+        // k::StripScatter): a peer store per row and field touched a new remote page every time and made the
+        // edge CTAs 3.5x longer.  DLESM_PUSH_DEFER=0 (on every rank) keeps the per-row peer stores for A/B runs.
+        static const bool defer = [] {
+            const char *e = std::getenv("DLESM_PUSH_DEFER");
+            return !(e && std::strcmp(e, "0") == 0);
+        }();
+        strips = defer && c.xd.ready;
+        rc = make_push<k::PushSeg2, 6>(*push_tables, outs, a.push.seg, a.push.n, pf, "sw_step2_fused", strips);
         if (rc != DLESM_OK) return rc;
+        if (strips) {
+            for (int q = 0; q < a.push.n; ++q) {
+                const k::PushSeg2 &g = a.push.seg[q];
+                if (g.i1 - g.i0 < 2 && !((g.i0 >= xs && g.i1 <= xs + 1) || (g.i0 >= xe - 1 && g.i1 <= xe))) {
+                    set_error(DLESM_ERR_STATE, "sw_step2_fused: a narrow push box away from the tile's x edges");
+                    return DLESM_ERR_STATE;
+                }
+            }
+            const size_t need = static_cast<size_t>(2) * (ye - ys + 1) * 12;
+            if (c.push_strip_cap < need) {
+                if (c.push_strip) {
+                    CU(cudaStreamSynchronize(st));
+                    CU(cudaFree(c.push_strip));
+                    c.push_strip = nullptr;
+                    c.push_strip_cap = 0;
+                }
+                CU(cudaMalloc(&c.push_strip, need * sizeof(double)));
+                c.push_strip_cap = need;
+            }
+            a.push.strip = c.push_strip;
+            // the receiving end: this rank's narrow receive boxes, from the slots of their direction tags
+            const dlesm_comms &t = push_tables->t;
+            sp.pitch = a.pitch;
+            for (int q = 0; q < 6; ++q) sp.dst[q] = const_cast<double *>(static_cast<const double *>(outs[q]));
+            for (int r = 0; r < t.nrecv && sp.n < 8; ++r) {
+                if (t.nxrecv[r] > 2 || t.dirrecv[r] < 1 || t.dirrecv[r] > 8 ||
+                    static_cast<size_t>(t.nxrecv[r]) * t.nyrecv[r] * 6 > c.xd.pslot_cap)
+                    continue;
+                k::StripScatter::Item &it = sp.item[sp.n++];
+                it.ides = t.idesrecv[r]; it.jdes = t.jdesrecv[r]; it.nx = t.nxrecv[r]; it.ny = t.nyrecv[r];
+                it.slot = push_slot(c.xd.base, c.push_epoch + 1, t.dirrecv[r]);
+            }
+        }
     }
     push_sync_fill(c, pf, a.sync);
     ProfScope ps;
@@ -1857,6 +1933,15 @@ int sw_step2_fused_impl(const void *u, const void *v, const void *p, const void 
     rc = prof_end(ps, st);
     if (rc != DLESM_OK) return rc;
     for (const void *o : outs) mark_clean(o, push_tables ? 2 : 0);
+    if (sp.n > 0) {
+        // hand-shake and scatter in one small launch: wait for the neighbours' epoch (the sweep's last CTA
+        // published this rank's; with DLESM_PUSH_SYNC=kernel this launch does), then move the strips they
+        // left here into the halo columns
+        ++c.push_epoch;
+        c.push_pending = false;
+        CU(k::peer_wait_scatter(pf, c.push_epoch, c.push_err, !push_sync_in_sweep(), sp, st));
+        return DLESM_OK;
+    }
     return push_sync_done(c, pf, deferred, st);
 }
 }  // namespace
@@ -1933,6 +2018,51 @@ extern "C" int dlesm_profile_read(double *ms_total, long long *nlaunches, int re
     if (ms_total) *ms_total = tot;
     if (nlaunches) *nlaunches = static_cast<long long>(c.prof_used);
     if (reset) c.prof_used = 0;
+    return DLESM_OK;
+}
+
+// Diagnostics: per-CTA timeline of the TMA sweeps launched between begin and end (each launch overwrites
+// the entries of its own CTAs: trace ONE launch shape at a time).  4 long long per CTA
+// (by * gridDim.x + bx): start ns, end ns, SM id, ns after the neighbour wait.
+namespace {
+long long *g_trace_buf = nullptr;
+int g_trace_cap = 0;
+}  // namespace
+extern "C" int dlesm_debug_cta_trace_begin(int max_ctas)
+{
+    clear_error();
+    int rc = ensure_device();
+    if (rc != DLESM_OK) return rc;
+    if (max_ctas <= 0) {
+        set_error(DLESM_ERR_ARGS, "dlesm_debug_cta_trace_begin: max_ctas must be positive");
+        return DLESM_ERR_ARGS;
+    }
+    if (g_trace_buf) cudaFree(g_trace_buf);
+    g_trace_buf = nullptr;
+    CU(cudaMalloc(&g_trace_buf, static_cast<size_t>(max_ctas) * 4 * sizeof(long long)));
+    CU(cudaMemset(g_trace_buf, 0, static_cast<size_t>(max_ctas) * 4 * sizeof(long long)));
+    g_trace_cap = max_ctas;
+    CU(k::fma_off::set_cta_trace(g_trace_buf));
+    CU(k::fma_on::set_cta_trace(g_trace_buf));
+    return DLESM_OK;
+}
+extern "C" int dlesm_debug_cta_trace_end(long long *out, int max_ctas)
+{
+    clear_error();
+    if (!g_trace_buf) {
+        set_error(DLESM_ERR_STATE, "dlesm_debug_cta_trace_end: no trace in progress");
+        return DLESM_ERR_STATE;
+    }
+    Context &c = ctx();
+    CU(cudaStreamSynchronize(c.stream));
+    CU(k::fma_off::set_cta_trace(nullptr));
+    CU(k::fma_on::set_cta_trace(nullptr));
+    if (out)
+        CU(cudaMemcpy(out, g_trace_buf, static_cast<size_t>(std::min(max_ctas, g_trace_cap)) * 4 * sizeof(long long),
+                      cudaMemcpyDeviceToHost));
+    cudaFree(g_trace_buf);
+    g_trace_buf = nullptr;
+    g_trace_cap = 0;
     return DLESM_OK;
 }
 

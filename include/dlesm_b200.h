@@ -588,6 +588,11 @@ long long dlesm_kernel_launch_count(void);
  * fused-step launch; used by bench.py for the roofline figure) */
 int dlesm_profile_enable(int on);
 int dlesm_profile_read(double *ms_total, long long *nlaunches, int reset);
+/* Diagnostics: per-CTA timeline of the fused TMA sweeps launched between begin and end.  `out` gets 4
+ * long long per CTA (index by * grid.x + bx of dlesm_sw_launch_grid): start ns, end ns, SM id, ns after
+ * the wait for the neighbours' previous sweep (halo push).  Later launches overwrite earlier ones. */
+int dlesm_debug_cta_trace_begin(int max_ctas);
+int dlesm_debug_cta_trace_end(long long *out, int max_ctas);
 /* Collective when the object pushes halos on several ranks (call it on every rank). */
 void dlesm_sw_free(dlesm_sw_t *s);
 /* Non-collective release for finalisers: frees everything except buffers the neighbours still have

@@ -64,6 +64,7 @@ int main(int argc, char **argv)
     CK(cudaEventCreate(&e0));
     CK(cudaEventCreate(&e1));
     const int rows = 124;
+    if (argc > 1) goto both_busy;
     printf("where mode W F work ctas fence us_per_launch ns_per_store_instr_per_cta Mstores_per_s\n");
     for (int where = 0; where < (have_peer ? 2 : 1); ++where)
         for (int mode = 0; mode < 2; ++mode)
@@ -143,6 +144,44 @@ int main(int argc, char **argv)
                         printf("busy %d %d %d %d | %.1f %.1f | %.3f %.3f\n", mode, W, F, ctas, idle * 1000 / 20, busy * 1000 / 20,
                                alone / creps, with / creps);
                     }
+    }
+both_busy:
+    // ---- source AND destination busy: both devices stream copies; the probe CTAs run beside the source's copy
+    if (have_peer && argc > 1) {
+        cudaStream_t s0, s1b, sp;
+        double2 *src0, *dst0;
+        const size_t nbytes = static_cast<size_t>(pitch) * ny * 8;
+        CK(cudaSetDevice(0));
+        CK(cudaStreamCreateWithFlags(&s0, cudaStreamNonBlocking));
+        CK(cudaStreamCreateWithFlags(&sp, cudaStreamNonBlocking));
+        CK(cudaMalloc(&src0, nbytes));
+        CK(cudaMalloc(&dst0, nbytes));
+        CK(cudaSetDevice(1));
+        CK(cudaStreamCreate(&s1b));
+        if (!busy_src) { CK(cudaMalloc(&busy_src, nbytes)); CK(cudaMalloc(&busy_dst, nbytes)); }
+        CK(cudaSetDevice(0));
+        printf("both-busy: where mode W F ctas burst | probe_us (20 launches back to back beside a streaming copy on the source; dest also copying)\n");
+        for (int where = 0; where < 2; ++where)
+            for (int mode = 0; mode < 2; ++mode)
+                for (int W : {1, 2})
+                    for (int F : {3, 6})
+                        for (int ctas : {66, 132}) {
+                            const Arrs &d = where ? rem : loc;
+                            CK(cudaSetDevice(1));
+                            for (int it = 0; it < 8; ++it) busy_copy<<<148 * 16, 256, 0, s1b>>>(busy_dst, busy_src, nbytes / 16);
+                            CK(cudaSetDevice(0));
+                            // the source's copy leaves room for the probe CTAs: 148 x 6 CTAs of 256 threads
+                            for (int it = 0; it < 8; ++it) busy_copy<<<148 * 6, 256, 0, s0>>>(dst0, src0, nbytes / 16);
+                            CK(cudaEventRecord(e0, sp));
+                            for (int it = 0; it < 20; ++it) probe<<<ctas, 32, 0, sp>>>(d, pitch, rows, W, F, mode, 100, 1, sink);
+                            CK(cudaEventRecord(e1, sp));
+                            CK(cudaEventSynchronize(e1));
+                            float ms; CK(cudaEventElapsedTime(&ms, e0, e1));
+                            const bool overlapped = cudaStreamQuery(s0) == cudaErrorNotReady;
+                            CK(cudaDeviceSynchronize());
+                            CK(cudaSetDevice(1)); CK(cudaDeviceSynchronize()); CK(cudaSetDevice(0));
+                            printf("bothbusy %s %d %d %d %d | %.1f overlapped=%d\n", where ? "remote" : "local", mode, W, F, ctas, ms * 1000 / 20, overlapped ? 1 : 0);
+                        }
     }
     return 0;
 }
