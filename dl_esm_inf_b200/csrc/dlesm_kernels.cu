@@ -553,10 +553,15 @@ __global__ void __launch_bounds__(256) xdirect_fused_kernel(const __grid_constan
                                                             const __grid_constant__ XPlan rp, unsigned *ticket, int *err)
 {
     xdirect_items(sp, true);
-    __threadfence_system();
+    // one system fence per CTA, by the thread that takes the ticket: the barrier orders the other threads'
+    // peer stores before it and the fence is cumulative (the grid-sync pattern); a fence in every thread
+    // made every warp wait for its own acknowledgements first
     __syncthreads();
     __shared__ bool last;
-    if (threadIdx.x == 0) last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+    if (threadIdx.x == 0) {
+        __threadfence_system();
+        last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+    }
     __syncthreads();
     if (last) {
         if (threadIdx.x < sp.npeers) {
