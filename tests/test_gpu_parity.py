@@ -845,6 +845,57 @@ def test_two_step_sweep_with_halo_push(order, n_x, n_y, align, nsteps, monkeypat
         _lib.lib().dlesm_reset_saved_state()
 
 
+@pytest.mark.parametrize("n_x,n_y,align,nsteps", [(4, 37, 2, 6), (7, 5, 2, 7), (130, 4, 64, 6), (5, 300, 2, 5)])
+def test_two_step_halo_push_on_narrow_tiles(n_x, n_y, align, nsteps, monkeypatch):
+    """packed x-edge strips (local staging strip -> the neighbour's slot -> scatter) on tiles whose two edge
+    column pairs touch or overlap, and on tiles shorter than a chunk: every field, halos two cells deep"""
+    try:
+        osw, sw = sw_pair_hw2(n_x, n_y, align, monkeypatch)
+        sw.set_two_step(True)
+        sw.set_halo_mode(fd.HALO_PUSH)
+        for _ in range(nsteps):
+            osw.step()
+        sw.step(nsteps)
+        assert_internal_equal(osw, sw, halo=0)
+        oi = osw.fb["t"].internal
+        ii = sw.field("p").internal
+        if nsteps % 2 == 1:    # the last sweep was a two-step sweep: its six outputs carry depth-2 halos
+            for n in ("u", "v", "p"):
+                want = np.pad(osw.f[n][oi.xstart - 1:oi.xstop, oi.ystart - 1:oi.ystop], 2, mode="wrap")
+                got = sw.field(n).get_data()[ii.xstart - 3:ii.xstop + 2, ii.ystart - 3:ii.ystop + 2]
+                assert np.array_equal(got, want), n
+    finally:
+        _lib.lib().dlesm_reset_saved_state()
+
+
+def test_cta_trace_records_every_cta_of_a_sweep(monkeypatch):
+    """dlesm_debug_cta_trace_begin/end: one entry per CTA of the launch grid, start <= after-wait <= end, SM id in range"""
+    import ctypes as C
+    try:
+        osw, sw = sw_pair_hw2(300, 523, 64, monkeypatch)
+        sw.set_two_step(True)
+        sw.set_halo_mode(fd.HALO_PUSH)
+        sw.step(3)
+        L = _lib.lib()
+        g = sw.launch_grid(two_step=True)
+        ncta = int(g[0]) * int(g[1])
+        assert ncta > 0
+        assert L.dlesm_debug_cta_trace_end(None, 0) != 0          # no trace in progress
+        assert L.dlesm_debug_cta_trace_begin(0) != 0
+        assert L.dlesm_debug_cta_trace_begin(ncta) == 0
+        sw.step(2)
+        buf = (C.c_longlong * (4 * ncta))()
+        assert L.dlesm_debug_cta_trace_end(buf, ncta) == 0
+        t = np.frombuffer(buf, dtype=np.int64).reshape(ncta, 4)
+        assert (t[:, 0] > 0).all() and (t[:, 0] <= t[:, 3]).all() and (t[:, 3] <= t[:, 1]).all()
+        assert (t[:, 2] >= 0).all() and (t[:, 2] < 200).all()
+        for _ in range(5):
+            osw.step()
+        assert_internal_equal(osw, sw, halo=1)                    # tracing changes nothing
+    finally:
+        _lib.lib().dlesm_reset_saved_state()
+
+
 @pytest.mark.parametrize("push", [False, True])
 @pytest.mark.parametrize("variant2", [0, 17])
 @pytest.mark.parametrize("n_x,n_y,align,seed,nsteps", [(96, 80, 4, None, 7), (66, 40, 2, None, 6), (70, 51, 64, 12345, 6),
