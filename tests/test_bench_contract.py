@@ -20,7 +20,7 @@ def _latest(pattern):
 
 
 def test_our_arm_line_has_every_contract_key():
-    d = json.load(open(_latest("r01z_bench_n1.json")))
+    d = json.load(open(_latest("r02z_bench_n1.json")))
     for k in ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling",
               "vs_baseline", "dtype", "data", "config", "clocks", "e2e", "gpu_launches", "roofline", "cpu_baseline"):
         assert k in d, k
@@ -49,10 +49,31 @@ def test_our_arm_line_has_every_contract_key():
     assert abs(d["value"] - pts / (d["ms_per_step"] * 1e-3)) <= 1e-6 * d["value"]
     # the two formulations advanced the same model: identical checksums
     assert d["checksums_p_u_v"] == d["one_step"]["checksums_p_u_v"]
+    # round 2: frac is a fraction of a roofline again (one pass over the state per launch), the temporal-blocking
+    # gain is a separate field; parity ran in the driver's run and found nothing; sustained leg and config 3 present
+    assert 0.5 < r["frac"] <= 1.2 and r["effective_bytes_speedup"] == 2.0
+    p = d["parity"]
+    assert p["checked"] is True and p["mismatches"] == 0 and p["cases"] >= 10
+    for leg in ("one_step_sweep", "two_step_sweep"):      # asserted 16384^2 checksums vs the CPU arm
+        assert p["full_size"][leg]["max_rel_diff_vs_cpu_long_double"] <= p["full_size"]["tolerance"] == 1e-12
+    assert d["sustained"]["seconds"] >= 2.5 and d["sustained"]["value"] <= d["value"] * 1.05
+    assert d["config3"]["parity"]["mismatches"] == 0
+    assert d["e2e"]["model_steps_per_round_trip"] == 2
+
+
+def test_both_arms_name_the_same_workload():
+    ours = json.load(open(_latest("r02z_bench_n1.json")))
+    ref = json.load(open(_latest("r02z_bench_reference_arm.json")))
+    assert ours["config"]["workload"] == ref["config"]["workload"]
+    assert ours["metric"] == ref["metric"] and ours["unit"] == ref["unit"]
+    assert "reference_sample" in ref["config"]
+    # the CPU arm's checksums after its steps agree with the long-double sums it prints
+    for a, b in zip(ref["checksums_p_u_v"], ref["checksums_p_u_v_long_double"]):
+        assert abs(a - b) <= 1e-12 * abs(b)
 
 
 def test_reference_arm_line():
-    d = json.load(open(_latest("r01o_bench_reference_arm.json")))
+    d = json.load(open(_latest("r02z_bench_reference_arm.json")))
     assert d["impl"] == "reference" and d["gpu_launches"] == 0
     assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["e2e"]["d2h_bytes_per_step"] == 0
     assert d["e2e"]["value"] == d["value"] == d["cpu_baseline"]["value"]
