@@ -521,7 +521,11 @@ __global__ void __launch_bounds__(256) xdirect_recv_kernel(const __grid_constant
 // Both phases in ONE launch.  The grid is small enough to be co-resident (<= 2 CTAs per SM), so CTAs that
 // have finished their share of the sends may spin on the neighbours' flags while others still send: the
 // flags this rank publishes depend only on its own sends, never on a neighbour's.
-constexpr int kXChunk = 4096;   // elements per work item
+// An east / west patch is one element per ROW of the field: every load of the pack is its own DRAM page, ~1.5 us
+// of latency.  Work items are therefore small (1024 elements: a 16384-row edge spreads over 16 CTAs, not 4) and a
+// thread keeps four loads in flight before it stores (with 4096-element items a thread walked 16 dependent
+// load -> peer-store pairs: 16-25 us per exchange whatever its size, profiles/r02w_bench_n8.json config5).
+constexpr int kXChunk = 1024;   // elements per work item
 __device__ __forceinline__ void xdirect_items(const XPlan &plan, bool send)
 {
     int base = 0;
@@ -538,11 +542,26 @@ __device__ __forceinline__ void xdirect_items(const XPlan &plan, bool send)
             double *buf = sg.buf + static_cast<long long>(kf) * n;
             double *f = plan.fields[kf];
             const int hi = min(n, (ch + 1) * kXChunk);
-            for (int t = ch * kXChunk + threadIdx.x; t < hi; t += blockDim.x) {
-                const int jj = t / sg.nx, ii = t - jj * sg.nx;
-                const size_t q = idx(plan.pitch, sg.i0 + ii, sg.j0 + jj);
-                if (send) buf[t] = f[q];
-                else f[q] = __ldcg(buf + t);
+            for (int t0 = ch * kXChunk + threadIdx.x; t0 < hi; t0 += 4 * blockDim.x) {
+                double v[4];
+                size_t q[4];
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const int t = t0 + k * blockDim.x;
+                    if (t < hi) {
+                        const int jj = t / sg.nx, ii = t - jj * sg.nx;
+                        q[k] = idx(plan.pitch, sg.i0 + ii, sg.j0 + jj);
+                        v[k] = send ? f[q[k]] : __ldcg(buf + t);
+                    }
+                }
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const int t = t0 + k * blockDim.x;
+                    if (t < hi) {
+                        if (send) buf[t] = v[k];
+                        else f[q[k]] = v[k];
+                    }
+                }
             }
         }
         base += items;
