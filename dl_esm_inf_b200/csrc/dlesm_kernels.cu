@@ -166,7 +166,8 @@ __device__ inline double block_sum_256(double v)
 __global__ void __launch_bounds__(256) abs_sum_fold_kernel(const double *__restrict__ f, int pitch, Box b,
                                                            double *__restrict__ partials, int npartials,
                                                            unsigned *ticket, double *__restrict__ result,
-                                                           double *host_result, unsigned long long seq)
+                                                           double *host_result, unsigned long long seq,
+                                                           const __grid_constant__ GlobalSumPlan gs)
 {
     const int w = b.xe - b.xs + 1;
     double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
@@ -192,7 +193,40 @@ __global__ void __launch_bounds__(256) abs_sum_fold_kernel(const double *__restr
     __threadfence();
     double a = 0.0;
     for (int t = threadIdx.x; t < npartials; t += 256) a += t < static_cast<int>(gridDim.x) ? __ldcg(partials + t) : 0.0;
-    const double tot = block_sum_256(a);
+    double tot = block_sum_256(a);
+    if (gs.nranks > 1) {
+        // global sum over the ranks, through peer memory
+        __shared__ double vals[kGsumMaxRanks];
+        if (threadIdx.x == 0) vals[0] = tot;
+        __syncthreads();
+        const double mine = vals[0];
+        __syncthreads();
+        const int t = threadIdx.x;
+        if (t < gs.nranks) {
+            gs.peer_cell[t][0] = mine;
+            __threadfence_system();
+            asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(gs.peer_cell[t] + 1), "l"(gs.seq) : "memory");
+            const double *cell = gs.own_cells + 2 * t;
+            const long long t0 = clock64();
+            for (;;) {
+                unsigned long long v;
+                asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(cell + 1) : "memory");
+                if (v >= gs.seq) break;
+                if (clock64() - t0 > 40000000000LL) {   // ~20 s: a rank never reached this checksum -- fatal
+                    atomicExch(gs.err, 1);
+                    __threadfence_system();
+                    __trap();
+                }
+                __nanosleep(40);
+            }
+            vals[t] = __ldcg(cell);
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            tot = 0.0;
+            for (int r = 0; r < gs.nranks; ++r) tot += vals[r];
+        }
+    }
     if (threadIdx.x == 0) {
         *result = tot;
         if (host_result) {
@@ -206,11 +240,13 @@ __global__ void __launch_bounds__(256) abs_sum_fold_kernel(const double *__restr
 }
 
 cudaError_t checksum(const double *f, int pitch, Box b, double *partials, unsigned *ticket, double *result,
-                     double *host_result, unsigned long long seq, cudaStream_t s)
+                     double *host_result, unsigned long long seq, cudaStream_t s, const GlobalSumPlan *gs)
 {
     const int rows = b.ye - b.ys + 1;
     const int blocks = rows < 1 || b.xe < b.xs ? 1 : (rows < kChecksumBlocks ? rows : kChecksumBlocks);
-    abs_sum_fold_kernel<<<blocks, 256, 0, s>>>(f, pitch, b, partials, kChecksumBlocks, ticket, result, host_result, seq);
+    GlobalSumPlan none{};
+    abs_sum_fold_kernel<<<blocks, 256, 0, s>>>(f, pitch, b, partials, kChecksumBlocks, ticket, result, host_result, seq,
+                                               gs ? *gs : none);
     count_launch();
     return cudaGetLastError();
 }

@@ -58,8 +58,21 @@ cudaError_t copy_patch(double *f, int pitch, Box src, Box dst, double *scratch, 
 // result: 1 double (device); host_result: null, or two mapped pinned words -- the sum, then `seq` (written
 // after it, system fence between: a host that sees seq sees the sum).  One launch.
 constexpr int kChecksumBlocks = 1184;  // 148 SMs x 8
+// `gs` non-null (several ranks): the global sum rides in the same launch -- the folding block stores this
+// rank's sum and the call's sequence number into every rank's cell for this rank (peer memory, two buffers
+// alternating with the sequence), waits for every rank's cell here, adds them in rank order (the same bits
+// on every rank) and publishes THAT to the host.  No collective library call, no second launch.
+constexpr int kGsumMaxRanks = 64;
+struct GlobalSumPlan {
+    int nranks, me;
+    unsigned long long seq;        // this call's number, equal on every rank
+    int *err;
+    // cell of rank `me` in rank r's table, and this rank's own table: cells of {double value; u64 seq}
+    double *peer_cell[kGsumMaxRanks];
+    const double *own_cells;
+};
 cudaError_t checksum(const double *f, int pitch, Box b, double *partials, unsigned *ticket, double *result,
-                     double *host_result, unsigned long long seq, cudaStream_t s);
+                     double *host_result, unsigned long long seq, cudaStream_t s, const GlobalSumPlan *gs = nullptr);
 cudaError_t periodic_halos(double *const *fields, int nfields, int pitch, Box internal,
                            bool periodic_x, bool periodic_y, cudaStream_t s);
 cudaError_t pack(const PackPlan &plan, double *buffer, cudaStream_t s);

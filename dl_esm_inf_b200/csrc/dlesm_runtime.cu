@@ -1174,6 +1174,10 @@ double *push_slot(char *base, unsigned long long epoch, int dir)
     return reinterpret_cast<double *>(base + 4096) + 2 * 8 * xd.slot_cap + ((epoch & 1) * 8 + (dir - 1)) * xd.pslot_cap;
 }
 
+// global-sum cells of the allocation at `base`: bytes 2048..4095 of its flag page, two tables (alternating
+// with the call's sequence number) of 64 cells {double value; u64 seq}
+double *gsum_cells(char *base, unsigned long long seq) { return reinterpret_cast<double *>(base + 2048 + (seq & 1) * 1024); }
+
 int peer_register_with(void *const *fields, int nfields, const CommTables &ct)
 {
     Context &c = ctx();
@@ -2670,6 +2674,42 @@ extern "C" int dlesm_field_checksum(dlesm_field_t *f, double *val)
     if (!c.comm_ready) {
         set_error(DLESM_ERR_STATE, "field_checksum: communicator not initialised (dlesm_comm_init)");
         return DLESM_ERR_STATE;
+    }
+    const int nranks = pstate().nranks, me0 = pstate().rank - 1;
+    if (c.exchange_mode < 0) {
+        const char *e = std::getenv("DLESM_EXCHANGE");
+        c.exchange_mode = (e && std::strcmp(e, "nccl") == 0) ? DLESM_EXCHANGE_NCCL : DLESM_EXCHANGE_DIRECT;
+    }
+    if (nranks <= k::kGsumMaxRanks && c.exchange_mode != DLESM_EXCHANGE_NCCL) {
+        // ONE launch: local sum, global sum through the ranks' peer-mapped cells (rank order: the same bits
+        // everywhere), result into pinned host memory which the host polls
+        if (!c.xd.ready) {
+            rc = xdirect_setup();      // collective; every rank reaches its first checksum together
+            if (rc != DLESM_OK) return rc;
+        }
+        static unsigned long long gseq = 0;
+        ++gseq;
+        k::GlobalSumPlan gs{};
+        gs.nranks = nranks; gs.me = me0; gs.seq = gseq;
+        gs.err = reinterpret_cast<int *>(c.xd.base + 1032);
+        for (int r = 0; r < nranks; ++r)
+            gs.peer_cell[r] = gsum_cells(c.xd.peer_base[r], gseq) + 2 * me0;
+        gs.own_cells = gsum_cells(c.xd.base, gseq);
+        CU(k::checksum(static_cast<const double *>(f->dptr), f->nx, box_of(in), c.partials, c.ticket, c.result,
+                       c.host_result + 6, gseq, c.stream, &gs));
+        volatile unsigned long long *flag = reinterpret_cast<volatile unsigned long long *>(c.host_result + 7);
+        for (unsigned spin = 1; *flag != gseq; ++spin) {
+            if ((spin & 0xfffff) == 0) {
+                cudaError_t q = cudaStreamQuery(c.stream);
+                if (q != cudaSuccess && q != cudaErrorNotReady) return fail_cuda(q, "field_checksum");
+                if (q == cudaSuccess && *flag != gseq) {
+                    set_error(DLESM_ERR_CUDA, "field_checksum: the kernel finished without publishing its result");
+                    return DLESM_ERR_CUDA;
+                }
+            }
+        }
+        *val = c.host_result[6];
+        return DLESM_OK;
     }
     CU(k::checksum(static_cast<const double *>(f->dptr), f->nx, box_of(in), c.partials, c.ticket, c.result, nullptr, 0,
                    c.stream));
