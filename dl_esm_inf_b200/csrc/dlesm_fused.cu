@@ -301,11 +301,13 @@ __device__ __forceinline__ long long global_ns()
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
     return t;
 }
-__device__ __forceinline__ void cta_trace(int slot)
+// `tile`: by * (x-tiles of the natural grid) + bx -- the same entry whether the tile ran in the natural 2-D
+// launch or in one of the two list launches of a split masked sweep
+__device__ __forceinline__ void cta_trace(int slot, int tile)
 {
     long long *tr = g_cta_trace;
     if (tr && threadIdx.x == 0) {
-        long long *e = tr + 4 * (static_cast<long long>(blockIdx.y) * gridDim.x + blockIdx.x);
+        long long *e = tr + 4 * static_cast<long long>(tile);
         e[slot] = global_ns();
         if (slot == 0) {
             unsigned sm;
@@ -409,11 +411,11 @@ fused_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_constant
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
-    cta_trace(0);
+    cta_trace(0, by_ * prm.list_gx + bx_);
     // an edge tile reads halo cells the neighbours push and pushes into theirs: their previous sweep first
     sync_wait_neighbours(prm.sync, i_first - 2 < prm.b.xs || min(i_first + TX - 1, i_last) + 2 > prm.b.xe ||
                                        j0 - 2 < prm.b.ys || j1 + 2 > prm.b.ye);
-    cta_trace(3);
+    cta_trace(3, by_ * prm.list_gx + bx_);
     __syncthreads();
 
     if (warp == TX / 32) {
@@ -542,7 +544,7 @@ fused_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_constant
             if (tid == 0) sync_publish_if_last(prm.sync);
         }
     }
-    cta_trace(1);
+    cta_trace(1, by_ * prm.list_gx + bx_);
 }
 
 // ---- tensor-map cache ----
@@ -604,6 +606,12 @@ cudaError_t allow_smem(const void *kern, int bytes)
     auto it = done.find(kern);
     if (it != done.end() && it->second >= bytes) return cudaSuccess;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    // every sweep kernel asks for the SAME shared-memory carve-out (all of it): left to the driver, the masked
+    // kernel (two CTAs per SM) and the unmasked one (three) got different carve-outs, an SM cannot hold both at
+    // once, and the two launches of a split masked sweep ran one after the other -- the second started when the
+    // first one's CTAs had all finished (CTA timelines, profiles/r03e_cta_trace_masked_4096_steady.jsonl)
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     if (e == cudaSuccess) done[kern] = bytes;
     return e;
 }
@@ -851,14 +859,18 @@ cudaError_t launch_tma_mf(const FusedArgs &a, cudaStream_t s)
             if (e == cudaSuccess) e = cudaStreamWaitEvent(ss.s, ss.fork, 0);
             if (e != cudaSuccess) return e;
         }
+        // the land tiles are the slow ones (masked march, fewer CTAs per SM): they go FIRST, on the launching
+        // stream, so that they start at once; the wet-tile launch follows on the side stream and fills the slots
+        // around them.  (The other way round the wet launch took every slot and the land tiles ran as a tail of
+        // their own: 4096^2 config 3, 380 us per two-step launch against 305 unmasked.)
         if (tl.nland) {
             prm.tile_list = tl.land;
-            e = launch_tma_kernel<TX, RY, STAGES, MINB, true, FIRST, ALN>(a, prm, dim3(tl.nland), both ? ss.s : s);
+            e = launch_tma_kernel<TX, RY, STAGES, MINB, true, FIRST, ALN>(a, prm, dim3(tl.nland), s);
             if (e != cudaSuccess) return e;
         }
         if (tl.nwet) {
             prm.tile_list = tl.wet;
-            e = launch_tma_kernel<TX, RY, STAGES, MINB, false, FIRST, ALN>(a, prm, dim3(tl.nwet), s);
+            e = launch_tma_kernel<TX, RY, STAGES, MINB, false, FIRST, ALN>(a, prm, dim3(tl.nwet), both ? ss.s : s);
             if (e != cudaSuccess) return e;
         }
         if (both) {
@@ -1081,13 +1093,13 @@ fused2s_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_consta
         if (M) tma_load_2d(st + Cfg::OFF_MASK, &tm_mask, x_msk, y_raw, &full[s]);
     };
     // an edge tile reads halo cells the neighbours push and pushes into theirs: their previous sweep first
-    cta_trace(0);
+    cta_trace(0, by_ * prm.list_gx + bx_);
     if (prm.sync.n_wait > 0) {
         sync_wait_neighbours(prm.sync, i_first - 3 < prm.b.xs || min(i_first + Cfg::OUT - 1, i_last) + 3 > prm.b.xe ||
                                            j0 - 3 < prm.b.ys || j1 + 3 > prm.b.ye);
         __syncthreads();
     }
-    cta_trace(3);
+    cta_trace(3, by_ * prm.list_gx + bx_);
     // No producer warp here: the per-chunk barrier between the two stages already tells thread 0
     // that every warp is done with a ring stage, so it refills the stage right after it.  (A
     // fifth warp would also cap the kernel at 168 registers: 10 warps on 4 schedulers.)
@@ -1339,7 +1351,7 @@ fused2s_tma_kernel(const __grid_constant__ CUtensorMap tm_u, const __grid_consta
             if (tid == 0) sync_publish_if_last(prm.sync);
         }
     }
-    cta_trace(1);
+    cta_trace(1, by_ * prm.list_gx + bx_);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -1561,8 +1573,8 @@ cudaError_t launch_tma2_split(const Fused2Args &a, cudaStream_t s, KernWet kern_
     if (e == cudaSuccess) e = allow_smem(reinterpret_cast<const void *>(kern_land), CfgLand::SMEM_BYTES);
     if (e != cudaSuccess) return e;
     dim3 grid;
-    tma2_geometry<CfgWet, RY, MINB>(a, prm.tm, grid, resident_ctas(reinterpret_cast<const void *>(kern_wet),
-                                                                  CfgWet::THREADS, CfgWet::SMEM_BYTES, MINB));
+    const int slots = resident_ctas(reinterpret_cast<const void *>(kern_wet), CfgWet::THREADS, CfgWet::SMEM_BYTES, MINB);
+    tma2_geometry<CfgWet, RY, MINB>(a, prm.tm, grid, slots);
     prm.pitch = a.pitch; prm.b = a.b; prm.sc = a.sc;
     prm.push = a.push;
     prm.sync = a.sync;       // n == 0 here: see the caller
@@ -1578,14 +1590,15 @@ cudaError_t launch_tma2_split(const Fused2Args &a, cudaStream_t s, KernWet kern_
         if (e == cudaSuccess) e = cudaStreamWaitEvent(ss.s, ss.fork, 0);
         if (e != cudaSuccess) return e;
     }
+    // land tiles first, on the launching stream; the wet tiles on the side stream (see launch_tma_mf)
     if (tl.nland) {
         prm.tile_list = tl.land;
-        e = launch_tma2_kernel<CfgLand, RY, true>(a, prm, dim3(tl.nland), both ? ss.s : s, kern_land);
+        e = launch_tma2_kernel<CfgLand, RY, true>(a, prm, dim3(tl.nland), s, kern_land);
         if (e != cudaSuccess) return e;
     }
     if (tl.nwet) {
         prm.tile_list = tl.wet;
-        e = launch_tma2_kernel<CfgWet, RY, false>(a, prm, dim3(tl.nwet), s, kern_wet);
+        e = launch_tma2_kernel<CfgWet, RY, false>(a, prm, dim3(tl.nwet), both ? ss.s : s, kern_wet);
         if (e != cudaSuccess) return e;
     }
     if (both) {

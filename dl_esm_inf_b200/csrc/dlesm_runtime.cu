@@ -326,6 +326,11 @@ extern "C" int dlesm_parallel_finalise(void)
         cudaFree(c.xd.base);
         c.xd = Context::XDirect{};
     }
+    if (c.push_strip) {
+        cudaFree(c.push_strip);
+        c.push_strip = nullptr;
+        c.push_strip_cap = 0;
+    }
     if (c.comm_ready) {
         ncclCommDestroy(c.comm);
         c.comm = nullptr;

@@ -29,7 +29,11 @@ def main():
     ap.add_argument("--sweep", choices=["one", "two"], default="two")
     ap.add_argument("--halo", choices=["push", "exchange"], default="push")
     ap.add_argument("--warm", type=int, default=9)
+    ap.add_argument("--launches", type=int, default=1,
+                    help="sweeps enqueued back to back while tracing; every launch overwrites the table, so the LAST "
+                         "one is what is reported (the host is ahead of the device by then: steady state)")
     ap.add_argument("--dump", default="")
+    ap.add_argument("--tmask", action="store_true", help="BASELINE config 3's land islands (bench.config3_mask_for)")
     args = ap.parse_args()
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     local = int(os.environ.get("LOCAL_RANK", 0))
@@ -66,8 +70,12 @@ def main():
     else:
         fd.set_extensions(ext)
         grid.decompose(gx, gy)
-    fd.grid_init(grid, 1.0e5, 1.0e5)
-    sw = fd.shallow_water(grid, dt=90.0, alpha=0.001, mode=fd.SW_FUSED)
+    tm = None
+    if args.tmask:
+        import bench
+        tm = bench.config3_mask_for(grid, gx, gy, np)
+    fd.grid_init(grid, 1.0e5, 1.0e5, tm)
+    sw = fd.shallow_water(grid, dt=90.0, alpha=0.001, mode=fd.SW_FUSED, use_tmask=bool(args.tmask))
     if two:
         sw.set_two_step(True, 0)
     sw.init_device()
@@ -80,7 +88,7 @@ def main():
     if dist is not None:
         dist.barrier()
     assert L.dlesm_debug_cta_trace_begin(ncta) == 0
-    sw.step(2 if two else 1)
+    sw.step((2 if two else 1) * args.launches)
     buf = (C.c_longlong * (4 * ncta))()
     assert L.dlesm_debug_cta_trace_end(buf, ncta) == 0
     t = np.frombuffer(buf, dtype=np.int64).reshape(ncta, 4).copy()
@@ -113,6 +121,14 @@ def main():
     rec["last_start_us"] = float(s_us.max())
     rec["tail_ctas"] = [{"bx": int(bx[q]), "by": int(by[q]), "class": names[cls[q]], "start_us": float(s_us[q]),
                          "dur_us": float(dur[q])} for q in order[-6:]]
+    # slow CTAs (the land tiles of a split masked sweep): how many, how long, when they start and end
+    med = float(np.median(dur))
+    slow = dur > 1.3 * med
+    rec["slow_ctas"] = {"n": int(slow.sum()), "dur_us_p50": float(np.median(dur[slow])) if slow.any() else None,
+                        "start_us_p10_p50_p90": [float(np.percentile(s_us[slow], q)) for q in (10, 50, 90)] if slow.any() else None,
+                        "end_us_p50_max": [float(np.percentile(e_us[slow], 50)), float(e_us[slow].max())] if slow.any() else None}
+    rec["fast_ctas"] = {"n": int((~slow).sum()), "dur_us_p50": float(np.median(dur[~slow])),
+                        "end_us_p50_max": [float(np.percentile(e_us[~slow], 50)), float(e_us[~slow].max())]}
     # occupancy profile: CTAs running at 10 points of the span
     span = rec["span_us"]
     rec["running_at_tenths"] = [int(((s_us <= f * span) & (e_us > f * span)).sum()) for f in np.linspace(0.05, 0.95, 10)]
