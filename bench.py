@@ -692,7 +692,7 @@ def run_config5(args, fd, L, C, world, rank, max_over_ranks, barrier):
         return max_over_ranks(ms.value) / reps * 1e3
 
     bcs = (fd.GO_BC_EXTERNAL, fd.GO_BC_EXTERNAL, fd.GO_BC_NONE)
-    for n in (2048, 4096, 16384):
+    for n in ((2048, 4096, 8192, 16384, 32768) if args.config5_full else (2048, 4096, 8192, 16384)):
         fd.gocean_initialise(rank + 1, world)
         probe = fd.go_decompose(n, n)
         for depth in ((1, 2) if world > 1 else (1,)):
@@ -933,6 +933,7 @@ def main():
     ap.add_argument("--no-deep-trips", action="store_true", help="skip the 4 / 8 steps-per-round-trip e2e sub-records")
     ap.add_argument("--no-strong", action="store_true", help="skip the strong-scaling sub-record (N > 1)")
     ap.add_argument("--no-config5", action="store_true", help="skip the halo_exchange / field_checksum microbench")
+    ap.add_argument("--config5-full", action="store_true", help="config 5 up to 32768^2 local tiles (8.6 GB per field)")
     ap.add_argument("--sustain-s", type=float, default=3.0,
                     help="seconds of back-to-back steps of the sustained leg (0 = none)")
     ap.add_argument("--arith", choices=["exact", "fma"], default="exact",

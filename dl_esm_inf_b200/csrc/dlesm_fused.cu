@@ -610,7 +610,11 @@ cudaError_t allow_smem(const void *kern, int bytes)
     // kernel (two CTAs per SM) and the unmasked one (three) got different carve-outs, an SM cannot hold both at
     // once, and the two launches of a split masked sweep ran one after the other -- the second started when the
     // first one's CTAs had all finished (CTA timelines, profiles/r03e_cta_trace_masked_4096_steady.jsonl)
-    if (e == cudaSuccess)
+    static const bool same_carveout = [] {
+        const char *v = std::getenv("DLESM_SAME_CARVEOUT");   // 0: leave the carve-out to the driver (A/B runs)
+        return !(v && std::atoi(v) == 0);
+    }();
+    if (e == cudaSuccess && same_carveout)
         e = cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     if (e == cudaSuccess) done[kern] = bytes;
     return e;
