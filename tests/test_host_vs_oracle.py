@@ -221,3 +221,38 @@ def _product_bounds(g, pts):
         return g.field_bounds(pts)
     except fd.GoceanStop as e:
         return e.code
+
+
+@pytest.mark.parametrize("dx_,dy_,nranks", [(64, 48, 1), (64, 48, 2), (40, 90, 3), (64, 48, 4), (96, 50, 6), (128, 96, 8),
+                                             (99, 99, 9), (64, 300, 12), (256, 256, 16)])
+@pytest.mark.parametrize("depth", [1, 2])
+def test_direction_tags_address_one_slot_per_message(dx_, dy_, nranks, depth):
+    """What the direct exchange and the packed push strips of the two-step sweep rely on: with
+    periodic tables of any depth, every send entry of rank r meets EXACTLY ONE receive entry on its destination
+    with source r, the same direction tag and the same size -- so the tag names a slot both ends agree on -- and
+    no two messages into one rank carry the same tag (a slot is never shared).  Narrow boxes (at most `depth`
+    columns wide: what leaves as a packed strip) sit on the tile's two x-edge column pairs."""
+    fd.gocean_initialise(1, nranks)
+    fd.set_extensions(fd.EXT_PERIODIC_DISTMEM | fd.EXT_HALO_DEPTH)
+    try:
+        d = fd.go_decompose(dx_, dy_, halo_width=depth)
+        tabs = {r: fd.map_comms(d, r, nranks, pbc=(True, True), halo_depths=(depth, depth)) for r in range(1, nranks + 1)}
+        for r, t in tabs.items():
+            sub = d.subdomains[r - 1].internal if hasattr(d, "subdomains") else None
+            tags_in = [t.dirrecv[q] for q in range(t.nrecv)]
+            assert len(set(tags_in)) == len(tags_in), (r, tags_in)          # one message per tag into a rank
+            assert all(1 <= g <= 8 for g in tags_in)
+            for s in range(t.nsend):
+                dest = t.destination[s] + 1 if nranks > 1 else 1     # the tables hold 0-based ranks
+                td = tabs[dest]
+                hits = [q for q in range(td.nrecv)
+                        if (td.source[q] == r - 1 or nranks == 1) and td.dirrecv[q] == t.dirsend[s]]
+                assert len(hits) == 1, (r, s, dest, hits)
+                q = hits[0]
+                assert (td.nxrecv[q], td.nyrecv[q]) == (t.nxsend[s], t.nysend[s])
+                if sub is not None and t.nxsend[s] <= depth and sub.nx >= 2 * depth:
+                    i0 = t.isrcsend[s]
+                    assert i0 == sub.xstart or i0 + t.nxsend[s] - 1 == sub.xstop, (r, s, i0)
+    finally:
+        fd.set_extensions(0)
+        fd.gocean_initialise(1, 1)
