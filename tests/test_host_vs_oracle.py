@@ -324,3 +324,56 @@ def test_go_decompose_and_map_comms_match_oracle_on_random_cases():
     check()
     O.reset_saved_state()
     fd.gocean_initialise(1, 1)
+
+
+def test_field_bounds_match_oracle_on_random_grids(monkeypatch):
+    """property test: grid sizing (DL_ESM_ALIGNMENT padding, src/grid_mod.f90:368-385) and set_field_bounds for
+    every point type, offset and boundary-condition mix (src/field_mod.f90:563-1122, incl. the gocean_stop
+    branches and the periodic halo lists) equal the oracle on random domains"""
+    from hypothesis import given, settings, strategies as st, HealthCheck
+
+    bc = st.sampled_from([fd.GO_BC_EXTERNAL, fd.GO_BC_PERIODIC])
+
+    @settings(max_examples=80, deadline=None, suppress_health_check=list(HealthCheck))
+    @given(nx_=st.integers(2, 150), ny_=st.integers(2, 150), offset=st.sampled_from([fd.GO_OFFSET_NE, fd.GO_OFFSET_SW]),
+           bcx=bc, bcy=bc, align=st.sampled_from([1, 2, 8, 64]))
+    def check(nx_, ny_, offset, bcx, bcy, align):
+        monkeypatch.setenv("DL_ESM_ALIGNMENT", str(align))
+        O.reset_saved_state()
+        fd.gocean_initialise(1, 1)
+        bcs = (bcx, bcy, fd.GO_BC_NONE)
+        og = O.Grid(O.GO_ARAKAWA_C, bcs, offset)
+        og.decompose(nx_, ny_, rank=1, nranks=1)
+        g = fd.grid_type(fd.GO_ARAKAWA_C, bcs, offset)
+        g.decompose(nx_, ny_)
+        try:
+            og.init(1.0, 2.0, tmask=None, alignment=align)
+            want_err = None
+        except O.OracleStop as e:
+            want_err = e.code
+        try:
+            fd.grid_init(g, 1.0, 2.0)
+            got_err = None
+        except fd.GoceanStop as e:
+            got_err = e.code
+        assert got_err == want_err, (nx_, ny_, offset, bcx, bcy, align)
+        if want_err is not None:
+            return
+        assert (g.nx, g.ny) == (og.nx, og.ny) and g.nx % align == 0
+        for pts in (fd.GO_U_POINTS, fd.GO_V_POINTS, fd.GO_T_POINTS, fd.GO_F_POINTS, fd.GO_ALL_POINTS):
+            try:
+                want, werr = O.field_bounds(og, pts), None
+            except O.OracleStop as e:
+                want, werr = None, e.code
+            fb = _product_bounds(g, pts)
+            if werr is not None:
+                assert fb == werr, (nx_, ny_, offset, bcx, bcy, pts)
+                continue
+            assert not isinstance(fb, int), (nx_, ny_, offset, bcx, bcy, pts, fb)
+            assert region_eq(fb.internal, want.internal) and region_eq(fb.whole, want.whole)
+            assert fb.num_halos == want.num_halos
+            for k in range(max(want.num_halos, 0)):
+                assert box_eq(fb.halo[k].source, want.halo[k].source) and box_eq(fb.halo[k].dest, want.halo[k].dest)
+
+    check()
+    fd.gocean_initialise(1, 1)
