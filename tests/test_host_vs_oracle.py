@@ -377,3 +377,47 @@ def test_field_bounds_match_oracle_on_random_grids(monkeypatch):
 
     check()
     fd.gocean_initialise(1, 1)
+
+
+def test_comm_plans_pair_up_across_ranks_on_random_cases():
+    """property test of the NCCL-mode message plan (dlesm_comm_plan_build) without any communicator: for random
+    domains, rank counts (up to 16), periodicity and depth, what rank a plans to send to rank b is exactly what b
+    plans to receive from a -- the same number of messages, the same element count, segment by segment in the
+    order both ends derive from the direction tags"""
+    from hypothesis import given, settings, strategies as st, HealthCheck
+    from dl_esm_inf_b200.api import comm_plan
+
+    @settings(max_examples=60, deadline=None, suppress_health_check=list(HealthCheck))
+    @given(dx_=st.integers(8, 300), dy_=st.integers(8, 300), nranks=st.integers(2, 16), depth=st.integers(1, 2),
+           periodic=st.booleans())
+    def check(dx_, dy_, nranks, depth, periodic):
+        fd.gocean_initialise(1, nranks)
+        fd.set_extensions((fd.EXT_PERIODIC_DISTMEM if periodic else 0) | fd.EXT_HALO_DEPTH)
+        try:
+            d = fd.go_decompose(dx_, dy_, halo_width=depth)
+            subs = d.subdomains
+            if any(subs[k].internal.nx < depth or subs[k].internal.ny < depth for k in range(nranks)):
+                return                      # a tile thinner than the halo it has to send
+            plans = {}
+            for r in range(1, nranks + 1):
+                c = fd.map_comms(d, r, nranks, pbc=(periodic, periodic), halo_depths=(depth, depth))
+                plans[r] = (c, comm_plan(c, r))
+            for a, (ca, pa) in plans.items():
+                for k in range(pa.npeers):
+                    b = pa.peer[k] + 1
+                    if b == a:
+                        continue
+                    cb, pb = plans[b]
+                    back = [q for q in range(pb.npeers) if pb.peer[q] + 1 == a]
+                    assert len(back) == 1, (a, b)
+                    q = back[0]
+                    assert pa.nsend[k] == pb.nrecv[q] and pa.send_n[k] == pb.recv_n[q], (a, b)
+                    for m in range(pa.nsend[k]):
+                        s, rcv = pa.send_slot[k][m], pb.recv_slot[q][m]
+                        assert ca.nxsend[s] * ca.nysend[s] == cb.nxrecv[rcv] * cb.nyrecv[rcv], (a, b, m)
+                        assert ca.dirsend[s] == cb.dirrecv[rcv], (a, b, m)
+        finally:
+            fd.set_extensions(0)
+
+    check()
+    fd.gocean_initialise(1, 1)
