@@ -421,3 +421,53 @@ def test_comm_plans_pair_up_across_ranks_on_random_cases():
 
     check()
     fd.gocean_initialise(1, 1)
+
+
+def test_periodic_tables_reproduce_the_global_field_on_random_cases():
+    """property test: an exchange SIMULATED in one process from the product's map_comms tables of every rank
+    (send boxes copied into the destination rank's array at the table's (ides, jdes)) leaves in every halo cell
+    within `depth` of the internal region -- corners included -- the value of the periodic global field at the
+    wrapped position.  Random domains, 1..16 ranks, depth 1..3: the index arithmetic of the wrap-around
+    (DLESM_EXT_PERIODIC_DISTMEM) and deep-halo (DLESM_EXT_HALO_DEPTH) tables, at rank counts no test box has."""
+    from hypothesis import given, settings, strategies as st, HealthCheck
+
+    @settings(max_examples=60, deadline=None, suppress_health_check=list(HealthCheck))
+    @given(dx_=st.integers(6, 120), dy_=st.integers(6, 120), nranks=st.integers(1, 16), depth=st.integers(1, 3),
+           seed=st.integers(0, 10 ** 6))
+    def check(dx_, dy_, nranks, depth, seed):
+        fd.gocean_initialise(1, nranks)
+        fd.set_extensions(fd.EXT_PERIODIC_DISTMEM | fd.EXT_HALO_DEPTH)
+        try:
+            d = fd.go_decompose(dx_, dy_, halo_width=depth)
+            subs = [d.subdomains[k] for k in range(nranks)]
+            if any(sd.internal.nx < depth or sd.internal.ny < depth for sd in subs):
+                return
+            G = np.random.default_rng(seed).uniform(-1, 1, size=(dx_, dy_))
+            arrs = []
+            for sd in subs:
+                li = sd.internal
+                a = np.full((sd.glob.nx, sd.glob.ny), -7.0)
+                gi = sd.glob.xstart + np.arange(li.nx) - 1
+                gj = sd.glob.ystart + np.arange(li.ny) - 1
+                a[li.xstart - 1:li.xstop, li.ystart - 1:li.ystop] = G[np.ix_(gi, gj)]
+                arrs.append(a)
+            tabs = [fd.map_comms(d, r, nranks, pbc=(True, True), halo_depths=(depth, depth)) for r in range(1, nranks + 1)]
+            # all sources are internal cells, all destinations halo cells: the order of the copies does not matter
+            for r, t in enumerate(tabs):
+                for s in range(t.nsend):
+                    dest = t.destination[s] if nranks > 1 else 0
+                    i0, j0, nx, ny = t.isrcsend[s] - 1, t.jsrcsend[s] - 1, t.nxsend[s], t.nysend[s]
+                    di, dj = t.idessend[s] - 1, t.jdessend[s] - 1
+                    arrs[dest][di:di + nx, dj:dj + ny] = arrs[r][i0:i0 + nx, j0:j0 + ny]
+            for sd, a in zip(subs, arrs):
+                li = sd.internal
+                ji = np.arange(li.xstart - depth, li.xstop + depth + 1)
+                jj = np.arange(li.ystart - depth, li.ystop + depth + 1)
+                wi = (sd.glob.xstart + (ji - li.xstart) - 1) % dx_
+                wj = (sd.glob.ystart + (jj - li.ystart) - 1) % dy_
+                assert np.array_equal(a[np.ix_(ji - 1, jj - 1)], G[np.ix_(wi, wj)]), (dx_, dy_, nranks, depth)
+        finally:
+            fd.set_extensions(0)
+
+    check()
+    fd.gocean_initialise(1, 1)
