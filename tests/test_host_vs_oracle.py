@@ -471,3 +471,80 @@ def test_periodic_tables_reproduce_the_global_field_on_random_cases():
 
     check()
     fd.gocean_initialise(1, 1)
+
+
+def test_tileset_plans_reproduce_the_global_field_on_random_cases():
+    """property test of the several-sub-domains-per-rank plan (dlesm_tileset_plan, extension F3): the plans of
+    EVERY rank, executed in one process (same-rank copies; per-peer buffers handed from the sender's plan to the
+    receiver's), fill every halo cell inside the -- periodic: wrapped -- domain with the global field's value.
+    Random domains, 1..6 ranks x 1..4 tiles, depth 1..2."""
+    from hypothesis import given, settings, strategies as st, HealthCheck
+    from dl_esm_inf_b200.api import tileset_plan
+
+    @settings(max_examples=50, deadline=None, suppress_health_check=list(HealthCheck))
+    @given(nx=st.integers(12, 96), ny=st.integers(12, 96), world=st.integers(1, 6), tpr=st.integers(1, 4),
+           periodic=st.booleans(), depth=st.integers(1, 2), seed=st.integers(0, 10 ** 6))
+    def check(nx, ny, world, tpr, periodic, depth, seed):
+        fd.gocean_initialise(1, world)
+        d = fd.go_decompose(nx, ny, ndomains=tpr * world, halo_width=depth)
+        subs = d.subdomains
+        if any(subs[k].internal.nx < depth or subs[k].internal.ny < depth for k in range(tpr * world)):
+            return
+        G = np.random.default_rng(seed).uniform(-1, 1, size=(nx, ny))
+        arrs, plans, sendbufs, recvbufs = {}, {}, {}, {}
+        for r in range(world):
+            owned = [d.proc_subdomains(s, r + 1) for s in range(1, tpr + 1)]
+            local = []
+            for tid in owned:
+                sb = subs[tid - 1]
+                li = sb.internal
+                a = np.full((sb.glob.nx, sb.glob.ny), -7.0, order="F")
+                gi = sb.glob.xstart + np.arange(li.nx) - 1
+                gj = sb.glob.ystart + np.arange(li.ny) - 1
+                a[li.xstart - 1:li.xstop, li.ystart - 1:li.ystop] = G[np.ix_(gi, gj)]
+                local.append(a)
+            arrs[r] = (owned, local)
+            rows, (stot, rtot) = tileset_plan(d, r + 1, world, pbc=(periodic, periodic), depth=depth)
+            plans[r] = rows.tolist()
+            sendbufs[r], recvbufs[r] = np.zeros(stot), np.zeros(rtot)
+        region_s, region_r = {}, {}
+        for r in range(world):
+            before = [a.copy() for a in arrs[r][1]]
+            for kind, peer, st_, dt_, si0, sj0, di0, dj0, w, h, off, dst_id, src_id, dirn in plans[r]:
+                if kind == 0:
+                    assert peer == r
+                    arrs[r][1][dt_][di0 - 1:di0 - 1 + w, dj0 - 1:dj0 - 1 + h] = before[st_][si0 - 1:si0 - 1 + w, sj0 - 1:sj0 - 1 + h]
+                elif kind == 1:
+                    sendbufs[r][off:off + w * h] = before[st_][si0 - 1:si0 - 1 + w, sj0 - 1:sj0 - 1 + h].flatten(order="F")
+                    lo, n = region_s.get((r, peer), (off, 0))
+                    region_s[(r, peer)] = (min(lo, off), n + w * h)
+                else:
+                    lo, n = region_r.get((r, peer), (off, 0))
+                    region_r[(r, peer)] = (min(lo, off), n + w * h)
+        assert {(a, b) for a, b in region_s} == {(b, a) for a, b in region_r}
+        for (a, b), (lo, n) in region_s.items():
+            rlo, rn = region_r[(b, a)]
+            assert rn == n, (a, b)
+            recvbufs[b][rlo:rlo + n] = sendbufs[a][lo:lo + n]
+        for r in range(world):
+            for kind, peer, st_, dt_, si0, sj0, di0, dj0, w, h, off, dst_id, src_id, dirn in plans[r]:
+                if kind == 2:
+                    arrs[r][1][dt_][di0 - 1:di0 - 1 + w, dj0 - 1:dj0 - 1 + h] = recvbufs[r][off:off + w * h].reshape((w, h), order="F")
+        for r in range(world):
+            for tid, a in zip(*arrs[r]):
+                sb = subs[tid - 1]
+                li = sb.internal
+                ji = np.arange(li.xstart - depth, li.xstop + depth + 1)
+                jj = np.arange(li.ystart - depth, li.ystop + depth + 1)
+                gx = sb.glob.xstart + ji - li.xstart
+                gy = sb.glob.ystart + jj - li.ystart
+                if periodic:
+                    want = G[np.ix_((gx - 1) % nx, (gy - 1) % ny)]
+                else:
+                    inx, iny = (gx >= 1) & (gx <= nx), (gy >= 1) & (gy <= ny)
+                    want = np.full((len(ji), len(jj)), -7.0)
+                    want[np.ix_(inx, iny)] = G[np.ix_(gx[inx] - 1, gy[iny] - 1)]
+                assert np.array_equal(a[np.ix_(ji - 1, jj - 1)], want), (nx, ny, world, tpr, periodic, depth, tid)
+
+    check()
+    fd.gocean_initialise(1, 1)
