@@ -105,6 +105,25 @@ def test_oracle_equals_published_scheme(n_x, n_y, seed):
                 assert np.array_equal(core(sw, k), getattr(ps, k)), (k, step)
 
 
+def test_oracle_equals_published_scheme_on_random_cases():
+    """property test: the same comparison on random (small) domain shapes, perturbation amplitudes and seeds,
+    12 steps each -- thin domains (3 points across) exercise the wrap of every neighbour index"""
+    from hypothesis import given, settings, strategies as st, HealthCheck
+
+    @settings(max_examples=40, deadline=None, suppress_health_check=list(HealthCheck))
+    @given(n_x=st.integers(3, 40), n_y=st.integers(3, 40), seed=st.integers(0, 10 ** 6),
+           amp=st.sampled_from([0.0, 0.01, 0.2]))
+    def check(n_x, n_y, seed, amp):
+        sw, ps = perturbed_pair(n_x, n_y, seed, amp=amp)
+        for _ in range(12):
+            sw.step()
+            ps.step()
+        for k in ("u", "v", "p", "uold", "vold", "pold"):
+            assert np.array_equal(core(sw, k), getattr(ps, k)), (k, n_x, n_y, seed, amp)
+
+    check()
+
+
 def test_first_step_is_forward_euler_then_leapfrog_with_doubled_tdt():
     """shallow.f: the first cycle advances from (uold = u) with tdt = dt and then sets
     tdt = 2 dt; a model that skipped the doubling would take leapfrog steps of half length"""
