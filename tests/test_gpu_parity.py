@@ -234,6 +234,46 @@ def test_copy_patch_and_periodic_halos():
     assert np.array_equal(f.get_data(), want)
 
 
+def test_copy_patch_checksum_on_random_boxes(monkeypatch):
+    """property test (derandomised): copy_field over random source / destination boxes of one field -- disjoint,
+    overlapping, one row or one column, shifted by a single cell -- keeps Fortran's array-assignment semantics
+    (RHS first, src/field_mod.f90:1179-1187) like the oracle, on random allocations and alignments; the checksum
+    of the internal region stays within 1e-12 of the long-double oracle"""
+    from hypothesis import given, settings, strategies as st, HealthCheck
+
+    @settings(max_examples=40, derandomize=True, deadline=None, suppress_health_check=list(HealthCheck), database=None)
+    @given(n_x=st.integers(3, 90), n_y=st.integers(3, 90), align=st.sampled_from([None, 2, 8, 64]),
+           data=st.data())
+    def check(n_x, n_y, align, data):
+        if align:
+            monkeypatch.setenv("DL_ESM_ALIGNMENT", str(align))
+        else:
+            monkeypatch.delenv("DL_ESM_ALIGNMENT", raising=False)
+        g = make_grid(n_x, n_y, offset=fd.GO_OFFSET_SW, bcs=BCS_PER, tmask=None)
+        f = fd.r2d_field(g, fd.GO_T_POINTS)
+        try:
+            src = rnd((g.nx, g.ny), n_x * 131 + n_y)
+            f.set_data(src)
+            want = src.copy(order="F")
+            for _ in range(3):
+                w = data.draw(st.integers(1, g.nx))
+                h = data.draw(st.integers(1, g.ny))
+                sx = data.draw(st.integers(1, g.nx - w + 1))
+                sy = data.draw(st.integers(1, g.ny - h + 1))
+                dx_ = data.draw(st.integers(1, g.nx - w + 1))
+                dy_ = data.draw(st.integers(1, g.ny - h + 1))
+                fd.copy_field(f, fd.make_region(sx, sx + w - 1, sy, sy + h - 1), fd.make_region(dx_, dx_ + w - 1, dy_, dy_ + h - 1))
+                O.copy_patch(want, O.make_region(sx, sx + w - 1, sy, sy + h - 1), O.make_region(dx_, dx_ + w - 1, dy_, dy_ + h - 1))
+                assert np.array_equal(f.get_data(), want), (n_x, n_y, align, (sx, sy, dx_, dy_, w, h))
+            i = f.internal
+            ref = float(np.sum(np.abs(want[i.xstart - 1:i.xstop, i.ystart - 1:i.ystop]).astype(np.longdouble)))
+            assert abs(fd.field_checksum(f) - ref) <= 1e-12 * max(ref, 1e-300)
+        finally:
+            f.free()
+
+    check()
+
+
 def test_only_x_or_only_y_periodic_halos():
     L = _lib.lib()
     for px, py in ((1, 0), (0, 1)):
