@@ -1360,3 +1360,41 @@ def test_tileset_shallow_water_matches_serial_oracle(n_x, n_y, ntiles, align, ma
         ts.free()
     finally:
         _lib.lib().dlesm_reset_saved_state()
+
+
+def test_tileset_shallow_water_on_random_shapes(monkeypatch):
+    """property test (derandomised): the periodic model over 1..8 sub-domains of one rank on random domain shapes
+    and alignments == the serial oracle on the undivided domain, bit for bit"""
+    from hypothesis import given, settings, strategies as st, HealthCheck
+
+    @settings(max_examples=24, derandomize=True, deadline=None, suppress_health_check=list(HealthCheck), database=None)
+    @given(n_x=st.integers(16, 140), n_y=st.integers(16, 140), ntiles=st.integers(1, 8),
+           align=st.sampled_from([2, 8, 64]), nsteps=st.integers(1, 5))
+    def check(n_x, n_y, ntiles, align, nsteps):
+        monkeypatch.setenv("DL_ESM_ALIGNMENT", str(align))
+        swt = ts = None
+        try:
+            osw = O.ShallowWater(n_x, n_y, alignment=align)
+            oi = osw.fb["t"].internal
+            core = (slice(oi.xstart - 1, oi.xstop), slice(oi.ystart - 1, oi.ystop))
+            init = {n: np.asfortranarray(osw.f[n][core]) for n in ("u", "v", "p")}
+            ts = fd.tileset(fd.GO_ARAKAWA_C, BCS_PER, fd.GO_OFFSET_SW, n_x, n_y, ndomains=ntiles)
+            for g in ts.grids:
+                fd.grid_init(g, 1.0e5, 1.0e5)
+            swt = fd.shallow_water_tiles(ts)
+            swt.set_state([tuple(tile_local(ts, k, init[n]) for n in ("u", "v", "p")) for k in range(ntiles)])
+            for _ in range(nsteps):
+                osw.step()
+            swt.step(nsteps)
+            for name in ("u", "v", "p", "uold", "vold", "pold"):
+                got = swt.gather(name)
+                assert np.array_equal(got, osw.f[name][core]), (name, n_x, n_y, ntiles, align, nsteps)
+        finally:
+            if swt is not None:
+                swt.free()
+            if ts is not None:
+                ts.free()
+            _lib.lib().dlesm_reset_saved_state()
+            fd.gocean_initialise(1, 1, device=0)
+
+    check()
