@@ -1398,3 +1398,51 @@ def test_tileset_shallow_water_on_random_shapes(monkeypatch):
             fd.gocean_initialise(1, 1, device=0)
 
     check()
+
+
+def test_step_host_on_random_shapes_and_bands(monkeypatch):
+    """property test (derandomised): the host-state step (dlesm_sw_step_host_n: row bands streamed through the
+    two-step sweep, 2..8 model steps per round trip in skewed passes) on random domain shapes, band heights from
+    one chunk to more than the tile, alignments, in place or not -- host results incl. the two-cell ring == the
+    oracle stepping one at a time, bit for bit"""
+    from hypothesis import given, settings, strategies as st, HealthCheck
+
+    names = ("u", "v", "p", "uold", "vold", "pold")
+
+    @settings(max_examples=24, derandomize=True, deadline=None, suppress_health_check=list(HealthCheck), database=None)
+    @given(n_x=st.integers(8, 160), n_y=st.integers(8, 260), align=st.sampled_from([2, 8, 64]),
+           band_rows=st.sampled_from([0, 4, 7, 16, 33, 64, 1000]), per_trip=st.sampled_from([2, 4, 6, 8]),
+           in_place=st.booleans())
+    def check(n_x, n_y, align, band_rows, per_trip, in_place):
+        sw = None
+        try:
+            osw, sw = sw_pair_hw2(n_x, n_y, align, monkeypatch)
+            sw.set_two_step(True)
+            osw.step()
+            sw.step(1)
+            host = [sw.field(n).get_data() for n in names]
+            oi, ii = osw.fb["t"].internal, sw.field("p").internal
+            core = (slice(oi.xstart - 1, oi.xstop), slice(oi.ystart - 1, oi.ystop))
+            ring2 = (slice(ii.xstart - 3, ii.xstop + 2), slice(ii.ystart - 3, ii.ystop + 2))
+            for q in range(6):
+                host[q][ring2] = np.pad(osw.f[names[q]][core], 2, mode="wrap")
+            for trip in range(2):
+                for _ in range(per_trip):
+                    osw.step()
+                if in_place:
+                    sw.step_host(host, band_rows=band_rows, nsteps=per_trip)
+                else:
+                    out = [np.full_like(a, np.nan) for a in host]
+                    sw.step_host(host, out, band_rows=band_rows, nsteps=per_trip)
+                    for a, o in zip(host, out):
+                        a[ring2] = o[ring2]
+                for n, a in zip(names, host):
+                    assert np.array_equal(a[ring2], np.pad(osw.f[n][core], 2, mode="wrap")), (
+                        n, trip, n_x, n_y, align, band_rows, per_trip, in_place)
+        finally:
+            if sw is not None:
+                sw.free()
+            _lib.lib().dlesm_reset_saved_state()
+            fd.gocean_initialise(1, 1, device=0)
+
+    check()
