@@ -1446,3 +1446,48 @@ def test_step_host_on_random_shapes_and_bands(monkeypatch):
             fd.gocean_initialise(1, 1, device=0)
 
     check()
+
+
+def test_tile_grid_knob_on_random_shapes(monkeypatch):
+    """property test (derandomised): any tile grid A x B (what GOCEAN_OMP_GRID / do_tile select,
+    src/field_mod.f90:1473-1503 -- tiles with go_decompose's remainder rule, more tiles than rows or columns
+    included) on random domain shapes gives the same bits as the library's own choice: one- and two-step
+    sweeps, halos by exchange or pushed, all wet or 3 % land"""
+    from hypothesis import given, settings, strategies as st, HealthCheck
+
+    @settings(max_examples=40, derandomize=True, deadline=None, suppress_health_check=list(HealthCheck), database=None)
+    @given(n_x=st.integers(4, 300), n_y=st.integers(4, 200), align=st.sampled_from([2, 64]), ntx=st.integers(0, 7),
+           nty=st.integers(0, 90), two_step=st.booleans(), push=st.booleans(),
+           mask_seed=st.one_of(st.none(), st.integers(1, 10 ** 6)), nsteps=st.integers(2, 5))
+    def check(n_x, n_y, align, ntx, nty, two_step, push, mask_seed, nsteps):
+        sw = None
+        try:
+            tm = periodic_island_mask(n_x + 2, n_y + 2, mask_seed) if mask_seed is not None else None
+            if two_step:
+                osw, sw = sw_pair_hw2(n_x, n_y, align, monkeypatch, tmask=tm)
+                sw.set_two_step(True)
+            else:
+                osw, sw = sw_pair(n_x, n_y, fd.SW_FUSED, alignment=align, tmask=tm, monkeypatch=monkeypatch)
+            if push:
+                sw.set_halo_mode(fd.HALO_PUSH)
+            fd.set_sweep_tiles(ntx, nty)
+            for _ in range(nsteps):
+                osw.step()
+            sw.step(nsteps)
+            if two_step:
+                assert_internal_equal(osw, sw, halo=1)
+            else:
+                assert_state_equal(osw, sw, internal_only=("uold", "vold", "pold"))
+        except AssertionError as e:
+            raise AssertionError("%s [n_x=%d n_y=%d align=%d tiles=%dx%d two_step=%s push=%s mask_seed=%s nsteps=%d]"
+                                 % (e, n_x, n_y, align, ntx, nty, two_step, push, mask_seed, nsteps))
+        finally:
+            fd.set_sweep_tiles(0, 0)
+            if sw is not None:
+                sw.free()
+            empty = fd.Comms()
+            _lib.lib().dlesm_dev_set_comms(C.byref(empty))
+            _lib.lib().dlesm_reset_saved_state()
+            fd.gocean_initialise(1, 1, device=0)
+
+    check()
