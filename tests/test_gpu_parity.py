@@ -1491,3 +1491,63 @@ def test_tile_grid_knob_on_random_shapes(monkeypatch):
             fd.gocean_initialise(1, 1, device=0)
 
     check()
+
+
+def test_exchange_engine_on_random_shapes(monkeypatch):
+    """property test (derandomised): halo_exchange of 1..3 fields with the wrap-around neighbours being the rank
+    itself, both engines (direct: patches stored into the receive slots + flags + unpack in one launch; NCCL mode:
+    pack / deliver / unpack), depth 1 or 2, random domain shapes incl. edges longer than one work item -- every cell
+    within `depth` of the internal region holds the wrapped value, everything else is untouched"""
+    from hypothesis import given, settings, strategies as st, HealthCheck
+    L = _lib.lib()
+
+    @settings(max_examples=30, derandomize=True, deadline=None, suppress_health_check=list(HealthCheck), database=None)
+    @given(shape=st.one_of(st.tuples(st.integers(4, 200), st.integers(4, 200)),
+                           st.tuples(st.integers(1500, 4000), st.integers(4, 12)),
+                           st.tuples(st.integers(4, 12), st.integers(1500, 4000))),
+           align=st.sampled_from([None, 2, 64]), depth=st.integers(1, 2), nfields=st.integers(1, 3),
+           mode=st.sampled_from(["direct", "nccl"]))
+    def check(shape, align, depth, nfields, mode):
+        n_x, n_y = shape
+        if align:
+            monkeypatch.setenv("DL_ESM_ALIGNMENT", str(align))
+        else:
+            monkeypatch.delenv("DL_ESM_ALIGNMENT", raising=False)
+        flds = []
+        try:
+            fd.set_extensions(fd.EXT_HALO_DEPTH)
+            fd.set_exchange_mode(fd.EXCHANGE_DIRECT if mode == "direct" else fd.EXCHANGE_NCCL)
+            g = fd.grid_type(fd.GO_ARAKAWA_C, BCS_PER, fd.GO_OFFSET_SW)
+            g.decompose(n_x, n_y, halo_width=depth)
+            fd.grid_init(g, 1.0, 1.0)
+            tables = fd.map_comms(g.decomp, 1, 1, pbc=(True, True), halo_depths=(depth, depth))
+            assert L.dlesm_dev_set_comms(C.byref(tables)) == 0
+            wants = []
+            for k in range(nfields):
+                f = fd.r2d_field(g, fd.GO_T_POINTS)
+                src = rnd((g.nx, g.ny), 7 * n_x + n_y + k)
+                f.set_data(src)
+                i = f.internal
+                want = src.copy(order="F")
+                core = src[i.xstart - 1:i.xstop, i.ystart - 1:i.ystop]
+                want[i.xstart - 1 - depth:i.xstop + depth, i.ystart - 1 - depth:i.ystop + depth] = np.pad(core, depth, mode="wrap")
+                flds.append(f); wants.append(want)
+            for rep in range(2):        # twice: the receive buffers alternate
+                if nfields == 1:
+                    flds[0].halo_exchange(depth)
+                else:
+                    fd.halo_exchange_fields(flds, depth)
+                for k, f in enumerate(flds):
+                    assert np.array_equal(f.get_data(), wants[k]), (shape, align, depth, nfields, mode, rep, k)
+        finally:
+            for f in flds:
+                f.free()
+            fd.dev_sync()
+            fd.set_exchange_mode(fd.EXCHANGE_DIRECT)
+            fd.set_extensions(0)
+            empty = fd.Comms()
+            L.dlesm_dev_set_comms(C.byref(empty))
+            L.dlesm_reset_saved_state()
+            fd.gocean_initialise(1, 1, device=0)
+
+    check()
