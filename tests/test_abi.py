@@ -162,3 +162,121 @@ def test_field_mod_and_grid_mod_patches_apply_to_the_reference(tmp_path):
     # parallel_utils_mod does not have)
     body = fm[fm.index("subroutine halo_exchange(self, depth)"):fm.index("end subroutine halo_exchange")]
     assert "call exchange_generic" not in body and "dlesm_dev_halo_exchange" in body and "dlesm_host_halo_exchange" in body
+
+
+def _c_prototypes():
+    import re
+    hdr = open(os.path.join(ROOT, "include", "dlesm_b200.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    hdr = re.sub(r"//[^\n]*", "", hdr)
+    protos = {}
+    for m in re.finditer(r"\b([A-Za-z_][\w \*]*?)\b(dlesm_\w+)\s*\(([^;{}]*?)\)\s*;", hdr):
+        ret, name, args = m.group(1).strip(), m.group(2), m.group(3).strip()
+        if "typedef" in ret:
+            continue
+        protos[name] = (ret, [] if args in ("void", "") else [a.strip() for a in args.split(",")])
+    return protos, hdr
+
+
+def _c_kind(a):
+    """(base type, levels of indirection) of a C parameter declaration"""
+    import re
+    a = re.sub(r"\b(const|restrict|__restrict__)\b", "", a).strip()
+    arr = "[" in a
+    a = re.sub(r"\[[^\]]*\]", "", a)
+    stars = a.count("*") + (1 if arr else 0)
+    toks = a.replace("*", " ").split()
+    return (" ".join(toks[:-1]) if len(toks) > 1 else toks[0]), stars
+
+
+def test_fortran_interfaces_match_the_c_prototypes():
+    """the check a Fortran compiler + linker cannot make and this image cannot run at all: every
+    bind(C) interface of fortran/*.f90 against the prototype of include/dlesm_b200.h -- the same number of
+    arguments, by value where C takes a scalar and by reference where it takes a pointer, c_int / c_double /
+    c_long_long / c_size_t / c_ptr against int / double / long long / size_t / pointers, and the result type"""
+    import glob
+    import re
+    protos, _ = _c_prototypes()
+    scal = {"integer(c_int)": "int", "integer(c_long_long)": "long long", "real(c_double)": "double",
+            "integer(c_size_t)": "size_t", "logical(c_bool)": "bool"}
+    bad, n = [], 0
+    for path in sorted(glob.glob(os.path.join(ROOT, "fortran", "*.f90"))):
+        txt = re.sub(r"&\s*\n\s*&?", " ", open(path).read())
+        pat = (r'(function|subroutine)\s+(\w+)\s*\(([^)]*)\)\s*bind\(C,\s*name="(\w+)"\)'
+               r'(?:\s*result\((\w+)\))?(.*?)end\s+(?:function|subroutine)')
+        for kind, _fname, args, cname, res, body in re.findall(pat, txt, flags=re.S | re.I):
+            n += 1
+            args = [a.strip() for a in args.split(",") if a.strip()]
+            decl = {}
+            for line in body.split("\n"):
+                line = line.split("!")[0].strip()
+                if "::" not in line:
+                    continue
+                lhs, rhs = line.split("::", 1)
+                for v in re.split(r",(?![^()]*\))", rhs):
+                    vn = re.match(r"\s*(\w+)", v)
+                    if vn:
+                        decl[vn.group(1).lower()] = lhs.strip().lower()
+            if cname not in protos:
+                bad.append((cname, "no prototype in the header"))
+                continue
+            ret, cargs = protos[cname]
+            if len(cargs) != len(args):
+                bad.append((cname, "argument count: Fortran %d, C %d" % (len(args), len(cargs))))
+                continue
+            for a, ca in zip(args, cargs):
+                lhs = decl.get(a.lower())
+                if lhs is None:
+                    bad.append((cname, "dummy argument %s has no declaration" % a))
+                    continue
+                base, stars = _c_kind(ca)
+                byval = "value" in lhs
+                head = lhs.split(",")[0].strip()
+                if head in scal:
+                    ok = base == scal[head] and stars == (0 if byval else 1)
+                elif head == "type(c_ptr)":
+                    ok = stars == (1 if byval else 2) or (byval and "(*" in ca)
+                elif head == "type(c_funptr)":
+                    ok = byval
+                elif head.startswith("character"):
+                    ok = stars == 1 and base in ("char", "void")
+                elif head.startswith("type(dlesm_"):
+                    ok = stars == 1 and base == head[5:-1]
+                else:
+                    ok = False
+                if not ok:
+                    bad.append((cname, "argument %s: Fortran '%s' against C '%s'" % (a, lhs, ca)))
+            if kind.lower() == "subroutine":
+                if ret != "void":
+                    bad.append((cname, "a subroutine, but C returns " + ret))
+            else:
+                rl = decl.get((res or "").lower(), "").split(",")[0].strip()
+                rb, rs = _c_kind(ret + " x")
+                if rl in scal and not (rb == scal[rl] and rs == 0):
+                    bad.append((cname, "result '%s' against C '%s'" % (rl, ret)))
+                if rl == "type(c_ptr)" and rs < 1:
+                    bad.append((cname, "result c_ptr against C '%s'" % ret))
+    assert n >= 40
+    assert not bad, bad
+
+
+def test_fortran_dlesm_comms_mirrors_the_c_struct():
+    """member order of the interoperable derived type == the C struct's == the ctypes mirror's"""
+    import re
+    _, hdr = _c_prototypes()
+    body = re.search(r"typedef struct(?:\s+\w+)?\s*\{([^{}]*?)\}\s*dlesm_comms;", hdr, flags=re.S)
+    assert body is not None
+    cnames = []
+    for decl in body.group(1).split(";"):
+        decl = decl.strip()
+        if not decl:
+            continue
+        decl = re.sub(r"^\s*int\s+", "", decl)
+        cnames += [re.sub(r"\[.*?\]", "", v).strip() for v in decl.split(",")]
+    ftxt = open(os.path.join(ROOT, "fortran", "dlesm_b200_mod.f90")).read()
+    fbody = re.search(r"type,\s*bind\(C\)\s*::\s*dlesm_comms(.*?)end type", ftxt, flags=re.S | re.I).group(1)
+    fnames = []
+    for line in fbody.split("\n"):
+        if "::" in line:
+            fnames += [v.strip() for v in line.split("::", 1)[1].split("!")[0].split(",") if v.strip()]
+    assert fnames == cnames == [n for n, _ in _lib.Comms._fields_], (fnames, cnames)
