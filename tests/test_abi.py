@@ -280,3 +280,46 @@ def test_fortran_dlesm_comms_mirrors_the_c_struct():
         if "::" in line:
             fnames += [v.strip() for v in line.split("::", 1)[1].split("!")[0].split(",") if v.strip()]
     assert fnames == cnames == [n for n, _ in _lib.Comms._fields_], (fnames, cnames)
+
+
+def test_fortran_calls_pass_as_many_arguments_as_the_interfaces_take():
+    """every reference to a dlesm_* interface in fortran/*.f90 and in the lines the patches ADD to the
+    reference's field_mod / grid_mod passes exactly the number of arguments its interface declares"""
+    import glob
+    import re
+    arity = {}
+    for path in glob.glob(os.path.join(ROOT, "fortran", "*.f90")):
+        txt = re.sub(r"&\s*\n\s*&?", " ", open(path).read())
+        for fname, args in re.findall(r'(?:function|subroutine)\s+(\w+)\s*\(([^)]*)\)\s*bind\(C', txt, flags=re.I):
+            arity[fname.lower()] = len([a for a in args.split(",") if a.strip()])
+    assert len(arity) >= 40
+    bad, total = [], 0
+    files = glob.glob(os.path.join(ROOT, "fortran", "*.f90")) + glob.glob(os.path.join(ROOT, "fortran", "patches", "*.patch"))
+    for path in files:
+        txt = open(path).read()
+        if path.endswith(".patch"):
+            txt = "\n".join(l[1:] for l in txt.split("\n") if l.startswith("+") and not l.startswith("+++"))
+        txt = "\n".join("" if l.lstrip().startswith("!") else l.split("!")[0] for l in txt.split("\n"))
+        txt = re.sub(r"&\s*\n\s*&?", " ", txt)
+        for m in re.finditer(r"\b(dlesm_\w+)\s*\(", txt):
+            name = m.group(1).lower()
+            if name not in arity:
+                continue
+            i, depth, commas, nonblank = m.end(), 1, 0, False
+            while i < len(txt) and depth:
+                c = txt[i]
+                if c == "(":
+                    depth += 1
+                elif c == ")":
+                    depth -= 1
+                elif c == "," and depth == 1:
+                    commas += 1
+                elif not c.isspace():
+                    nonblank = True
+                i += 1
+            total += 1
+            n = commas + 1 if nonblank else 0
+            if n != arity[name]:
+                bad.append((os.path.basename(path), name, n, arity[name]))
+    assert total >= 60
+    assert not bad, bad
