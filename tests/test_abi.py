@@ -131,6 +131,66 @@ def test_fortran_bindings_name_only_exported_symbols():
     assert not missing, missing
 
 
+def _fortran_block_errors(txt):
+    """the structural check a Fortran front end makes first: every module / interface / type / subroutine /
+    function / do / if-then / select / associate is closed by the matching END, in order (free form, comments
+    and continuation lines removed).  Calibrated on the reference's 17 source files: no false positive."""
+    import re
+    lines = ["" if l.lstrip().startswith("!") else l.split("!")[0].rstrip() for l in txt.split("\n")]
+    joined = re.sub(r"&\s*\n\s*&?", " ", "\n".join(lines))
+    stack, errs = [], []
+    for ln, l in enumerate(joined.split("\n"), 1):
+        t = l.strip().lower()
+        if not t:
+            continue
+        t = re.sub(r"^\d+\s+", "", t)
+        t = re.sub(r"^\w+\s*:\s*(?=(do|if|select)\b)", "", t)
+        m = re.match(r"end\s*(module|subroutine|function|interface|type|do|if|select|program|associate|block)\b", t)
+        if m:
+            if not stack:
+                errs.append((ln, "end %s with nothing open" % m.group(1)))
+            else:
+                top = stack.pop()
+                if top != m.group(1):
+                    errs.append((ln, "end %s closes %s" % (m.group(1), top)))
+            continue
+        if re.match(r"end\s*$", t):
+            if stack:
+                stack.pop()
+            continue
+        if re.match(r"module\s+(?!procedure)\w+", t):
+            stack.append("module")
+        elif re.match(r"program\s+\w+", t):
+            stack.append("program")
+        elif re.match(r"(abstract\s+)?interface\b", t):
+            stack.append("interface")
+        elif re.match(r"type\s*(,[^:]*)?(::)?\s*\w+\s*$", t) and not re.match(r"type\s*\(", t):
+            stack.append("type")
+        elif re.match(r"((pure|elemental|recursive|impure)\s+)*subroutine\s+\w+", t):
+            stack.append("subroutine")
+        elif re.match(r"((pure|elemental|recursive|impure)\s+)*([\w\(\)=\*, ]+\s+)?function\s+\w+\s*\(", t):
+            stack.append("function")
+        elif re.match(r"do\b(\s+\w+\s*=|\s+while|\s*$|\s+concurrent)", t):
+            stack.append("do")
+        elif re.match(r"if\s*\(.*\)\s*then\s*$", t):
+            stack.append("if")
+        elif re.match(r"select\s+(case|type)\b", t):
+            stack.append("select")
+        elif re.match(r"associate\s*\(", t):
+            stack.append("associate")
+    errs += [(0, "unclosed %s" % k) for k in stack]
+    return errs
+
+
+def test_fortran_sources_are_structurally_balanced():
+    import glob
+    for path in sorted(glob.glob(os.path.join(ROOT, "fortran", "*.f90"))):
+        assert _fortran_block_errors(open(path).read()) == [], path
+    # the checker itself: an unclosed block and a crossed END are seen
+    assert _fortran_block_errors("module m\ncontains\nsubroutine s()\nif (a) then\nend subroutine s\nend module m\n")
+    assert _fortran_block_errors("subroutine s()\ndo i = 1, 2\nend subroutine\n")
+
+
 def test_field_mod_and_grid_mod_patches_apply_to_the_reference(tmp_path):
     """fortran/patches/*.patch turn the reference's field_mod / grid_mod into the B200 build (public
     generics dispatching on data_on_device).  Where the reference tree is present (the build container)
@@ -157,6 +217,7 @@ def test_field_mod_and_grid_mod_patches_apply_to_the_reference(tmp_path):
         assert p.returncode == 0, p.stdout + p.stderr
         out = (work / (name + ".f90")).read_text()
         assert "use dlesm_b200_mod" in out
+        assert _fortran_block_errors(out) == [], name      # the patched module still closes every block
     fm = (work / "field_mod.f90").read_text()
     # fld%halo_exchange no longer reaches exchange_generic (-> post_receive, which the NCCL variant of
     # parallel_utils_mod does not have)
