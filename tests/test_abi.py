@@ -384,3 +384,24 @@ def test_fortran_calls_pass_as_many_arguments_as_the_interfaces_take():
                 bad.append((os.path.basename(path), name, n, arity[name]))
     assert total >= 60
     assert not bad, bad
+
+
+def test_fortran_use_statements_name_existing_modules():
+    """every `use X` of fortran/*.f90 names a module of the shim or of the reference's src/ (where the
+    reference tree is present) or an intrinsic one"""
+    import glob
+    import re
+    ref = "/root/reference/finite_difference/src"
+    if not os.path.isdir(ref):
+        pytest.skip("reference tree not present on this box")
+    files = glob.glob(os.path.join(ROOT, "fortran", "*.f90"))
+    srcs = files + glob.glob(ref + "/*.f90") + glob.glob(ref + "/*.F90") + glob.glob(ref + "/parallel/*.f90")
+    mods = {"iso_c_binding", "iso_fortran_env"}
+    for p in srcs:
+        mods |= {m.lower() for m in re.findall(r"^\s*module\s+(?!procedure)(\w+)", open(p).read(), flags=re.I | re.M)}
+    used = 0
+    for p in files:
+        for m in re.findall(r"^\s*use\s*(?:,\s*intrinsic\s*::\s*)?(\w+)", open(p).read(), flags=re.I | re.M):
+            used += 1
+            assert m.lower() in mods, (os.path.basename(p), m)
+    assert used >= 5
