@@ -148,6 +148,7 @@ SIGNATURES = {
     "dlesm_event_elapsed_ms": (_I, [_I, _I, _PD]),
     "dlesm_dev_copy_field": (_I, [_V, _V]),
     "dlesm_dev_copy_patch": (_I, [_V] + [_I] * 8),
+    "dlesm_dev_copy_patch_static": (_I, [_V] + [_I] * 10 + [_V, _I]),
     "dlesm_dev_set_field": (_I, [_V, _D]),
     "dlesm_dev_checksum": (_I, [_V, _I, _I, _I, _I, _PD]),
     "dlesm_dev_periodic_halos": (_I, [_V, _I, _I, _I, _I, _I, _I]),

@@ -43,6 +43,7 @@ UNITS = [
     ("dlesm_fused_fma", "dlesm_fused.cu", ["-fmad=true", "-DDLESM_CONTRACTED=1"]),
     ("dlesm_runtime", "dlesm_runtime.cu", ["-fmad=false"]),
     ("dlesm_psy", "dlesm_psy.cu", ["-fmad=false"]),
+    ("dlesm_static_scratch", "dlesm_static_scratch.cu", ["-fmad=false"]),
 ]
 MARKER = b"DLESM_SRC_HASH="
 

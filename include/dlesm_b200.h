@@ -368,6 +368,30 @@ int dlesm_dev_copy_field(const void *field_in, void *field_out);                
 int dlesm_dev_copy_patch(void *field, int sxstart, int sxstop, int systart, int systop,
                          int dxstart, int dxstop, int dystart, int dystop);       /* :1179 */
 int dlesm_dev_set_field(void *field, double val);                                 /* :1191 */
+/* dlesm_dev_copy_patch for callers that cannot allocate device memory.  No counterpart in the
+ * reference (it has no device code); same result as dlesm_dev_copy_patch, i.e. :1179-1187 with the
+ * right-hand side read first.  Meant for hosts where a cudaMalloc inside the library is not an
+ * option: the application's own pool already owns all of the GPU's memory (the call would fail), the
+ * time-step loop must not take the device-wide synchronisation an allocation implies, or the memory
+ * budget is fixed up front.  An overlapping copy is therefore staged through an area that is part of
+ * the library image -- DLESM_STATIC_SCRATCH_DOUBLES doubles (2 MiB) on every GPU that loads the
+ * library, held until the process exits -- and the entry point calls no cudaMalloc / cudaFree and
+ * does not touch the library's context.
+ *   field        device memory of the caller, nx x ny doubles, column-major (need not come from
+ *                dlesm_dev_field_alloc); boxes are 1-based inclusive, inside the allocation
+ *   stream       a cudaStream_t of the CURRENT device (NULL = default stream); blocking != 0 waits
+ *                for it before returning
+ * Limit: overlapping patches of more than DLESM_STATIC_SCRATCH_DOUBLES cells return
+ * DLESM_ERR_ARGS (split the copy); disjoint patches are copied directly and have no limit.
+ * Sharing: there is ONE staging area per GPU.  It keeps the previous call's contents, which is
+ * harmless (every cell read is written first by the same call; nothing needs to start at zero), but
+ * calls that can run at the same time on one GPU -- other streams, other threads -- race on it.
+ * Set-up: the first call on each device looks up the area's device address; make that call during
+ * initialisation, before any stream capture on that device. */
+#define DLESM_STATIC_SCRATCH_DOUBLES 262144
+int dlesm_dev_copy_patch_static(void *field, int nx, int ny, int sxstart, int sxstop, int systart,
+                                int systop, int dxstart, int dxstop, int dystart, int dystop,
+                                void *stream, int blocking);
 /* local SUM(ABS(field(xstart:xstop, ystart:ystop))) -- :1289-1302; deterministic two-pass
  * tree (no atomics).  Follow with dlesm_global_sum for :1305. */
 int dlesm_dev_checksum(const void *field, int xstart, int xstop, int ystart, int ystop,
