@@ -262,6 +262,13 @@ struct TmaStepParams {
     const int *tile_list;
     int list_gx;
 };
+// bound of the neighbour wait in SM clock cycles (0 = unbounded); set_wait_limit, read on the slow path only
+__device__ long long g_wait_limit = 0;
+__device__ __forceinline__ bool wait_expired(long long t0)
+{
+    const long long lim = *reinterpret_cast<volatile long long *>(&g_wait_limit);
+    return lim > 0 && clock64() - t0 > lim;
+}
 // start of an edge tile of a push sweep: wait for the neighbours' previous sweep (see PushSync); call
 // before a CTA-wide barrier that precedes the first load
 __device__ __forceinline__ void sync_wait_neighbours(const PushSync &sy, bool edge)
@@ -272,7 +279,7 @@ __device__ __forceinline__ void sync_wait_neighbours(const PushSync &sy, bool ed
             unsigned long long v;
             asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(sy.local[threadIdx.x]) : "memory");
             if (v >= sy.wait_epoch) break;
-            if (clock64() - t0 > 40000000000LL) {   // ~20 s: the ranks are out of step -- fatal
+            if (wait_expired(t0)) {   // DLESM_WAIT_TIMEOUT_S: the ranks are out of step -- fatal
                 atomicExch(sy.err, 1);
                 __threadfence_system();
                 __trap();
@@ -1695,6 +1702,7 @@ bool fused2_supported(const Fused2Args &a)
 bool fused2_push_supported(int variant) { return variant == 0 || (variant >= 10 && variant < 20); }
 
 cudaError_t set_cta_trace(long long *buf) { return cudaMemcpyToSymbol(g_cta_trace, &buf, sizeof(buf)); }
+cudaError_t set_wait_limit(long long cycles) { return cudaMemcpyToSymbol(g_wait_limit, &cycles, sizeof(cycles)); }
 
 cudaError_t sw_step2_fused(const Fused2Args &a, int variant, cudaStream_t s)
 {

@@ -25,6 +25,16 @@ __host__ __device__ inline size_t idx(int pitch, int i, int j)
 inline unsigned cdiv(long long a, long long b) { return static_cast<unsigned>((a + b - 1) / b); }
 }  // namespace
 
+// Bound of every in-kernel wait for another rank, in SM clock cycles; 0 = wait for ever (like an MPI wait).
+// Set once per device by set_wait_limit (DLESM_WAIT_TIMEOUT_S, dlesm_runtime.cu); read on the slow path only.
+__device__ long long g_wait_limit = 0;
+__device__ __forceinline__ bool wait_expired(long long t0)
+{
+    const long long lim = *reinterpret_cast<volatile long long *>(&g_wait_limit);
+    return lim > 0 && clock64() - t0 > lim;
+}
+cudaError_t set_wait_limit(long long cycles) { return cudaMemcpyToSymbol(g_wait_limit, &cycles, sizeof(cycles)); }
+
 long long launch_count() { return g_launches.load(); }
 void note_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
@@ -212,7 +222,7 @@ __global__ void __launch_bounds__(256) abs_sum_fold_kernel(const double *__restr
                 unsigned long long v;
                 asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(cell + 1) : "memory");
                 if (v >= gs.seq) break;
-                if (clock64() - t0 > 40000000000LL) {   // ~20 s: a rank never reached this checksum -- fatal
+                if (wait_expired(t0)) {   // DLESM_WAIT_TIMEOUT_S: a rank never reached this checksum -- fatal
                     atomicExch(gs.err, 1);
                     __threadfence_system();
                     __trap();
@@ -533,7 +543,7 @@ __global__ void __launch_bounds__(256) xdirect_recv_kernel(const __grid_constant
             unsigned long long v;
             asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(plan.flag[threadIdx.x]) : "memory");
             if (v >= plan.count[threadIdx.x]) break;
-            if (clock64() - t0 > 40000000000LL) {   // ~20 s: the ranks are out of step -- fatal, as in the halo push
+            if (wait_expired(t0)) {   // DLESM_WAIT_TIMEOUT_S: the ranks are out of step -- fatal, as in the halo push
                 atomicExch(err, 1);
                 __threadfence_system();
                 __trap();
@@ -632,7 +642,7 @@ __global__ void __launch_bounds__(256) xdirect_fused_kernel(const __grid_constan
             unsigned long long v;
             asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(rp.flag[threadIdx.x]) : "memory");
             if (v >= rp.count[threadIdx.x]) break;
-            if (clock64() - t0 > 40000000000LL) {
+            if (wait_expired(t0)) {
                 atomicExch(err, 1);
                 __threadfence_system();
                 __trap();
@@ -773,7 +783,7 @@ cudaError_t tile_ops(const TileOpBatch &b, cudaStream_t s)
 // the sweep's peer stores are complete when this kernel starts, so a system-scope release of
 // the epoch into each neighbour's flag array publishes them; then wait (acquire) until every
 // neighbour has published the same epoch into ours.  One thread per neighbour.  The wait is
-// bounded (~20 s of SM clocks): on time-out *err is set and the kernel TRAPS -- the run ends with
+// bounded (DLESM_WAIT_TIMEOUT_S, default 300 s; 0 = unbounded): on time-out *err is set and the kernel TRAPS -- the run ends with
 // a CUDA error on the next call instead of hanging the GPU or sweeping over stale halos.
 // ---------------------------------------------------------------------------------------
 __global__ void peer_signal_wait_kernel(PeerFlags pf, unsigned long long epoch, int *err, int publish)
@@ -789,8 +799,8 @@ __global__ void peer_signal_wait_kernel(PeerFlags pf, unsigned long long epoch, 
         unsigned long long v;
         asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(pf.local[q]) : "memory");
         if (v >= epoch) break;
-        if (clock64() - t0 > 40000000000LL) {
-            // ~20 s of SM clocks without the neighbour's epoch: the ranks are out of step.  Carrying
+        if (wait_expired(t0)) {
+            // DLESM_WAIT_TIMEOUT_S without the neighbour's epoch: the ranks are out of step.  Carrying
             // on would sweep over halos that were never pushed, so the time-out is FATAL: the flag is
             // set for dlesm_dev_sync's message and the kernel traps, which fails every later CUDA
             // call of this process (checksum, get_data, gather ... all return DLESM_ERR_CUDA).
@@ -815,7 +825,7 @@ __global__ void __launch_bounds__(256) peer_wait_scatter_kernel(const __grid_con
             unsigned long long v;
             asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(pf.local[q]) : "memory");
             if (v >= epoch) break;
-            if (clock64() - t0 > 40000000000LL) {   // fatal, like peer_signal_wait_kernel
+            if (wait_expired(t0)) {   // fatal, like peer_signal_wait_kernel
                 atomicExch(err, 1);
                 __threadfence_system();
                 __trap();

@@ -287,6 +287,8 @@ struct Fused2Args {
     /* diagnostics: CTA (by * gridDim.x + bx) of the TMA sweeps records globaltimer at its start,    \
        after the neighbour wait and at its end, and its SM id: 4 long long each; null = off */       \
     cudaError_t set_cta_trace(long long *buf);                                                       \
+    /* bound of the in-kernel neighbour wait, SM clock cycles; 0 = unbounded */                      \
+    cudaError_t set_wait_limit(long long cycles);                                                    \
     }
 DLESM_FUSED_API(fma_off)
 DLESM_FUSED_API(fma_on)
@@ -306,6 +308,10 @@ cudaError_t mask_to_bytes(const int *m, int pitch, int ny, unsigned char *m8, in
 // classic initial conditions, synthetic (device sin/cos)
 cudaError_t sw_init(double *u, double *v, double *p, int pitch, Box b, int gx0, int gy0, int M,
                     int N, double dx, double dy, cudaStream_t s);
+
+// bound of every in-kernel wait for another rank (exchange, global sum, push hand-shake), SM clock cycles;
+// 0 = unbounded.  Once per device.
+cudaError_t set_wait_limit(long long cycles);
 
 long long launch_count();
 void note_launch(int n = 1);

@@ -9,6 +9,7 @@
 #include <sys/syscall.h>
 #include <unistd.h>
 
+#include <atomic>
 #include <algorithm>
 #include <cctype>
 #include <cstdio>
@@ -70,6 +71,7 @@ struct Context {
     double *result = nullptr;
     double *host_result = nullptr;  // pinned (and, under UVA, writable by kernels: the checksum lands here)
     unsigned *ticket = nullptr;     // last-block ticket of the one-launch checksum
+    std::atomic<unsigned long long> checksum_seq{0}, gsum_seq{0};   // sequence numbers the host polls for
     double *scratch = nullptr;      // patch scratch
     size_t scratch_n = 0;
     double *sendbuf = nullptr, *recvbuf = nullptr;
@@ -224,6 +226,7 @@ k::Box box_of(const dlesm_region &r) { return k::Box{r.xstart, r.xstop, r.ystart
 namespace dlesm {
 int internal_ensure_device() { return ensure_device(); }
 cudaStream_t internal_stream() { return ctx().stream; }
+void internal_mark_written(const void *device_ptr) { mark_written(device_ptr); }
 int internal_pitch_of(const void *device_ptr, int &pitch, int &ny)
 {
     FieldRec r;
@@ -282,6 +285,29 @@ extern "C" int dlesm_device_init(int device)
     CU(cudaMemset(c.ticket, 0, sizeof(unsigned)));
     CU(cudaMallocHost(&c.host_result, 8 * sizeof(double)));
     std::memset(c.host_result, 0, 8 * sizeof(double));
+    {
+        // How long a kernel waits for another rank before it gives up (exchange, global sum, halo push
+        // hand-shake): DLESM_WAIT_TIMEOUT_S seconds, default 300, 0 = for ever like an MPI wait.  A rank that
+        // is merely late (output on rank 0, an NVRTC compile, a debugger) must not end the job; a lost rank
+        // must not hang it for good.  Expiry is fatal by design: carrying on would compute on stale halos.
+        double secs = 300.0;
+        if (const char *e = std::getenv("DLESM_WAIT_TIMEOUT_S")) {
+            char *end = nullptr;
+            const double v = std::strtod(e, &end);
+            if (end == e || v < 0.0) {
+                set_error(DLESM_ERR_ARGS, "DLESM_WAIT_TIMEOUT_S: expected a number of seconds >= 0 (0 = wait for ever)");
+                return DLESM_ERR_ARGS;
+            }
+            secs = v;
+        }
+        int khz = 0;
+        CU(cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, device));
+        const double cyc = secs * 1000.0 * (khz > 0 ? khz : 2000000);
+        const long long cycles = secs == 0.0 ? 0 : (cyc < 1.0 ? 1 : (cyc > 9.0e18 ? 9000000000000000000LL : static_cast<long long>(cyc)));
+        CU(k::set_wait_limit(cycles));
+        CU(k::fma_off::set_wait_limit(cycles));
+        CU(k::fma_on::set_wait_limit(cycles));
+    }
     c.device = device;
     c.device_ready = true;
     if (const char *ar = std::getenv("DLESM_ARITH"))
@@ -744,18 +770,19 @@ extern "C" int dlesm_dev_checksum(const void *f, int xs, int xe, int ys, int ye,
     }
     Context &c = ctx();
     // one launch; the folding block stores the sum straight into pinned host memory
-    static unsigned long long seq = 0;
-    ++seq;
+    const unsigned long long seq = ++c.checksum_seq;
     CU(k::checksum(static_cast<const double *>(f), r.nx, k::Box{xs, xe, ys, ye}, c.partials, c.ticket, c.result,
                    c.host_result + 4, seq, c.stream));
     // poll the sequence word instead of cudaStreamSynchronize (a driver round trip of several us); the
     // stream is queried now and then so that a failed launch ends the wait with its error
-    volatile unsigned long long *flag = reinterpret_cast<volatile unsigned long long *>(c.host_result + 5);
-    for (unsigned spin = 1; *flag != seq; ++spin) {
+    // acquire: the value next to the sequence word is read only after the word (weakly ordered hosts too)
+    const unsigned long long *flag = reinterpret_cast<const unsigned long long *>(c.host_result + 5);
+    auto published = [flag]() { return __atomic_load_n(flag, __ATOMIC_ACQUIRE); };
+    for (unsigned spin = 1; published() != seq; ++spin) {
         if ((spin & 0xfffff) == 0) {
             cudaError_t q = cudaStreamQuery(c.stream);
             if (q != cudaSuccess && q != cudaErrorNotReady) return fail_cuda(q, "field_checksum");
-            if (q == cudaSuccess && *flag != seq) {
+            if (q == cudaSuccess && published() != seq) {
                 set_error(DLESM_ERR_CUDA, "field_checksum: the kernel finished without publishing its result");
                 return DLESM_ERR_CUDA;
             }
@@ -1380,19 +1407,26 @@ int xdirect_exchange(void *const *fields, int nfields, int pitch, const CommTabl
     auto slot = [&](char *base, unsigned long long cnt, int dir) {
         return reinterpret_cast<double *>(base + kXdFlagsBytes) + ((cnt & 1) * 8 + (dir - 1)) * xd.slot_cap;
     };
+    // validate every group before any pair count moves: a refusal must leave this rank's counts (and with
+    // them the slot parity) in step with its neighbours'
     for (const auto &g : ct.groups) {
         if (g.sends.empty() && g.recvs.empty()) continue;
         if (g.peer0 < 0 || g.peer0 >= static_cast<int>(xd.peer_base.size()) || !xd.peer_base[g.peer0]) {
             set_error(DLESM_ERR_STATE, "direct exchange: neighbour rank not mapped");
             return DLESM_ERR_STATE;
         }
-        const unsigned long long cnt = ++xd.count[g.peer0];
         for (int s : g.sends) {
             if (t.dirsend[s] < 1 || t.dirsend[s] > 8 ||
                 static_cast<size_t>(t.nxsend[s]) * t.nysend[s] * nfields > xd.slot_cap) {
                 set_error(DLESM_ERR_ARGS, "direct exchange: a message exceeds its slot (raise DLESM_XDIRECT_MB or set DLESM_EXCHANGE=nccl on every rank)");
                 return DLESM_ERR_ARGS;
             }
+        }
+    }
+    for (const auto &g : ct.groups) {
+        if (g.sends.empty() && g.recvs.empty()) continue;
+        const unsigned long long cnt = ++xd.count[g.peer0];
+        for (int s : g.sends) {
             k::XSegment &sg = sp.seg[sp.nseg++];
             sg.i0 = t.isrcsend[s]; sg.j0 = t.jsrcsend[s]; sg.nx = t.nxsend[s]; sg.ny = t.nysend[s];
             sg.buf = slot(xd.peer_base[g.peer0], cnt, t.dirsend[s]);
@@ -2692,8 +2726,7 @@ extern "C" int dlesm_field_checksum(dlesm_field_t *f, double *val)
             rc = xdirect_setup();      // collective; every rank reaches its first checksum together
             if (rc != DLESM_OK) return rc;
         }
-        static unsigned long long gseq = 0;
-        ++gseq;
+        const unsigned long long gseq = ++c.gsum_seq;
         k::GlobalSumPlan gs{};
         gs.nranks = nranks; gs.me = me0; gs.seq = gseq;
         gs.err = reinterpret_cast<int *>(c.xd.base + 1032);
@@ -2702,12 +2735,13 @@ extern "C" int dlesm_field_checksum(dlesm_field_t *f, double *val)
         gs.own_cells = gsum_cells(c.xd.base, gseq);
         CU(k::checksum(static_cast<const double *>(f->dptr), f->nx, box_of(in), c.partials, c.ticket, c.result,
                        c.host_result + 6, gseq, c.stream, &gs));
-        volatile unsigned long long *flag = reinterpret_cast<volatile unsigned long long *>(c.host_result + 7);
-        for (unsigned spin = 1; *flag != gseq; ++spin) {
+        const unsigned long long *flag = reinterpret_cast<const unsigned long long *>(c.host_result + 7);
+        auto published = [flag]() { return __atomic_load_n(flag, __ATOMIC_ACQUIRE); };
+        for (unsigned spin = 1; published() != gseq; ++spin) {
             if ((spin & 0xfffff) == 0) {
                 cudaError_t q = cudaStreamQuery(c.stream);
                 if (q != cudaSuccess && q != cudaErrorNotReady) return fail_cuda(q, "field_checksum");
-                if (q == cudaSuccess && *flag != gseq) {
+                if (q == cudaSuccess && published() != gseq) {
                     set_error(DLESM_ERR_CUDA, "field_checksum: the kernel finished without publishing its result");
                     return DLESM_ERR_CUDA;
                 }
@@ -2980,6 +3014,8 @@ extern "C" int dlesm_sw_init_device(dlesm_sw_t *s)
                   static_cast<double *>(s->f[DLESM_SW_P]->dptr), n, box_of(in), sub.global.xstart,
                   sub.global.ystart, s->grid->info.global_nx, s->grid->info.global_ny, s->grid->info.dx,
                   s->grid->info.dy, ctx().stream));
+    // the internal regions were just overwritten: whatever the halos held is stale (dirty-flag halos)
+    for (int q = 0; q < 3; ++q) mark_written(s->f[DLESM_SW_U + q]->dptr);
     int rc = sw_fill_halos(s, DLESM_SW_U, 3);
     if (rc != DLESM_OK) return rc;
     for (int q = 0; q < 3; ++q) {

@@ -1551,3 +1551,76 @@ def test_exchange_engine_on_random_shapes(monkeypatch):
             fd.gocean_initialise(1, 1, device=0)
 
     check()
+
+
+def test_dirty_flag_halos_after_generated_kernels_and_reinitialisation():
+    """every writer has to mark its outputs dirty, or DLESM_EXT_DIRTY_HALOS skips a fill that is needed: a PSy-layer
+    sweep (metadata GO_WRITE) and dlesm_sw_init_device both overwrite the internal region of fields whose halos
+    were clean"""
+    from dl_esm_inf_b200.api import GO_CT, GO_INTERNAL_PTS, GO_WRITE, field_arg, kernel_type
+    g = make_grid(40, 30, offset=fd.GO_OFFSET_SW, bcs=BCS_PER, tmask=None, dx=1.0e5, dy=1.0e5)
+    f = fd.r2d_field(g, fd.GO_T_POINTS)
+    kern = kernel_type("ramp", "__device__ void ramp_code(int ji, int jj, dlesm_field o) { o(ji, jj) = ji + 100.0 * jj; }",
+                       [field_arg(GO_WRITE, GO_CT)], GO_INTERNAL_PTS, fd.GO_OFFSET_SW)
+    sw = fd.shallow_water(g, mode=fd.SW_FUSED)
+    try:
+        fd.set_extensions(fd.EXT_DIRTY_HALOS)
+        fd.set_field(f, -3.0)
+        f.apply_periodic_halos()
+        assert not f.halo_is_dirty()
+        kern([f])
+        assert f.halo_is_dirty()                                   # the sweep wrote f
+        f.apply_periodic_halos()                                   # ... so this fill must run
+        got = f.get_data()
+        i = f.internal
+        want = np.full((g.nx, g.ny), -3.0, order="F")
+        ii, jj = np.meshgrid(np.arange(1, g.nx + 1), np.arange(1, g.ny + 1), indexing="ij")
+        ramp = ii + 100.0 * jj
+        want[i.xstart - 1:i.xstop, i.ystart - 1:i.ystop] = ramp[i.xstart - 1:i.xstop, i.ystart - 1:i.ystop]
+        # halo cells equal the wrapped internal cells
+        assert np.array_equal(got[i.xstart - 2, i.ystart - 1:i.ystop], got[i.xstop - 1, i.ystart - 1:i.ystop])
+        assert np.array_equal(got[i.xstop, i.ystart - 1:i.ystop], got[i.xstart - 1, i.ystart - 1:i.ystop])
+        assert np.array_equal(got[i.xstart - 1:i.xstop, i.ystart - 2], got[i.xstart - 1:i.xstop, i.ystop - 1])
+        assert np.array_equal(got[i.xstart - 1:i.xstop, i.ystop], got[i.xstart - 1:i.xstop, i.ystart - 1])
+        assert np.array_equal(got[i.xstart - 1:i.xstop, i.ystart - 1:i.ystop], want[i.xstart - 1:i.xstop, i.ystart - 1:i.ystop])
+        # re-initialisation of the model state over clean halos
+        sw.init_device()
+        first = [sw.field(n).get_data().copy() for n in ("u", "v", "p")]
+        for n in ("u", "v", "p"):
+            fld = sw.field(n)
+            fd.set_field(fld, 7.0)
+            fld.apply_periodic_halos()
+            assert not fld.halo_is_dirty()
+        sw.init_device()
+        for n, a in zip(("u", "v", "p"), first):
+            fld = sw.field(n)
+            w = fld.whole                                          # internal region + its halos (not the padding)
+            sl = (slice(w.xstart - 1, w.xstop), slice(w.ystart - 1, w.ystop))
+            assert np.array_equal(fld.get_data()[sl], a[sl]), n
+    finally:
+        fd.set_extensions(0)
+        kern.free()
+
+
+def test_wait_timeout_knob_is_read_at_device_init():
+    """DLESM_WAIT_TIMEOUT_S: the bound of the in-kernel waits for other ranks is an
+    environment knob, 0 = unbounded; a value that is not a number >= 0 is refused at dlesm_device_init.  Each value
+    in a process of its own (the knob is read once)."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    prog = ("import dl_esm_inf_b200 as fd, numpy as np\n"
+            "fd.gocean_initialise(1, 1, device=0)\n"
+            "g = fd.grid_type(fd.GO_ARAKAWA_C, (fd.GO_BC_PERIODIC, fd.GO_BC_PERIODIC, fd.GO_BC_NONE), fd.GO_OFFSET_SW)\n"
+            "g.decompose(16, 16); fd.grid_init(g, 1.0, 1.0, None)\n"
+            "f = fd.r2d_field(g, fd.GO_T_POINTS); fd.set_field(f, 2.0)\n"
+            "f.halo_exchange(1)\n"
+            "print('sum', fd.field_checksum(f))\n")
+    for val, ok in (("0", True), ("7.5", True), ("-1", False), ("soon", False)):
+        env = dict(os.environ, DLESM_WAIT_TIMEOUT_S=val)
+        res = subprocess.run([sys.executable, "-c", prog], env=env, cwd=root, capture_output=True, text=True, timeout=300)
+        if ok:
+            assert res.returncode == 0 and "sum 512.0" in res.stdout, (val, res.stdout, res.stderr[-600:])
+        else:
+            assert res.returncode != 0 and "DLESM_WAIT_TIMEOUT_S" in (res.stdout + res.stderr), (val, res.stderr[-600:])
