@@ -342,4 +342,27 @@ contains
     call dlesm_parallel_abort(trim(msg)//c_null_char)
   end subroutine dlesm_check
 
+  !> What r2d_field%read_from_device_c points at.  The pointer component's abstract interface
+  !! (read_from_device_c_interface, src/field_mod.f90:66-72) has all-value interoperable dummies
+  !! but is NOT bind(C), and BIND is a characteristic of a procedure: a bind(C) procedure is not a
+  !! valid target for that pointer.  These two wrappers have exactly the reference's interface (no
+  !! bind(C)) and forward to the C entry points.
+  subroutine dlesm_read_from_device_hook(from, to, startx, starty, nx, ny, blocking)
+    type(c_ptr), intent(in), value :: from
+    type(c_ptr), intent(in), value :: to
+    integer(c_int), intent(in), value :: startx, starty, nx, ny
+    logical(c_bool), intent(in), value :: blocking
+    call dlesm_read_from_device_c(from, to, startx, starty, nx, ny, blocking)
+  end subroutine dlesm_read_from_device_hook
+
+  !> What r2d_field%write_to_device_c points at (write_to_device_c_interface,
+  !! src/field_mod.f90:87-93); see dlesm_read_from_device_hook.
+  subroutine dlesm_write_to_device_hook(from, to, startx, starty, nx, ny, blocking)
+    type(c_ptr), intent(in), value :: from
+    type(c_ptr), intent(in), value :: to
+    integer(c_int), intent(in), value :: startx, starty, nx, ny
+    logical(c_bool), intent(in), value :: blocking
+    call dlesm_write_to_device_c(from, to, startx, starty, nx, ny, blocking)
+  end subroutine dlesm_write_to_device_hook
+
 end module dlesm_b200_mod

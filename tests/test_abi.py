@@ -199,7 +199,10 @@ def test_field_mod_and_grid_mod_patches_apply_to_the_reference(tmp_path):
     import shutil
     import subprocess
     mod = open(os.path.join(ROOT, "fortran", "dlesm_b200_mod.f90")).read()
-    declared = set(re.findall(r'name="(dlesm_\w+)"', mod)) | {"dlesm_check", "dlesm_comms"}
+    declared = set(re.findall(r'name="(dlesm_\w+)"', mod)) | {"dlesm_comms"}
+    # ... and the module procedures of its `contains` part (dlesm_check, the two hook wrappers)
+    declared |= set(re.findall(r"^\s*(?:subroutine|function)\s+(dlesm_\w+)", mod[mod.index("\ncontains"):], flags=re.M | re.I))
+    assert {"dlesm_check", "dlesm_read_from_device_hook", "dlesm_write_to_device_hook"} <= declared
     for name in ("field_mod", "grid_mod"):
         patch = os.path.join(ROOT, "fortran", "patches", name + ".f90.patch")
         added = [l[1:] for l in open(patch) if l.startswith("+") and not l.startswith("+++")]
@@ -384,6 +387,46 @@ def test_fortran_calls_pass_as_many_arguments_as_the_interfaces_take():
                 bad.append((os.path.basename(path), name, n, arity[name]))
     assert total >= 60
     assert not bad, bad
+
+
+def test_procedure_pointer_targets_have_the_pointer_interface_characteristics():
+    """every `ptr => proc` the patches add to field_mod must name a module procedure of fortran/*.f90 that is NOT
+    bind(C) (the reference's abstract interfaces, src/field_mod.f90:66-72,87-93, are not: BIND is a procedure
+    characteristic, F2008 12.3.1 / 7.2.2.4) and whose dummy list and declarations equal the abstract interface's"""
+    import glob
+    import re
+    patch = open(os.path.join(ROOT, "fortran", "patches", "field_mod.f90.patch")).read()
+    added = "\n".join(l[1:] for l in patch.split("\n") if l.startswith("+") and not l.startswith("+++"))
+    targets = dict(re.findall(r"self%(\w+)\s*=>\s*(\w+)", added))
+    assert set(targets) == {"read_from_device_c", "write_to_device_c"}
+    shim = "\n".join(open(p).read() for p in glob.glob(os.path.join(ROOT, "fortran", "*.f90")))
+    shim = re.sub(r"&\s*\n\s*&?", " ", shim)
+    # the abstract interface, as the reference has it (both hooks share it)
+    want_args = ["from", "to", "startx", "starty", "nx", "ny", "blocking"]
+    want_decls = {"type(c_ptr), intent(in), value :: from", "type(c_ptr), intent(in), value :: to",
+                  "integer(c_int), intent(in), value :: startx, starty, nx, ny",
+                  "logical(c_bool), intent(in), value :: blocking"}
+    ref = "/root/reference/finite_difference/src/field_mod.f90"
+    if os.path.exists(ref):          # calibrate on the reference itself where it is present
+        rt = open(ref).read()
+        for comp, iface in (("read_from_device_c", "read_from_device_c_interface"),
+                            ("write_to_device_c", "write_to_device_c_interface")):
+            m = re.search(r"subroutine\s+%s\s*\(([^)]*)\)([^\n]*)\n(.*?)end subroutine" % iface, rt, flags=re.S | re.I)
+            assert m and "bind" not in m.group(2).lower()
+            assert [a.strip() for a in m.group(1).split(",")] == want_args
+            decl = {" ".join(l.split()) for l in m.group(3).split("\n") if "::" in l}
+            assert decl == want_decls, decl
+            assert re.search(r"procedure\s*\(\s*%s\s*\)\s*,\s*(?:nopass\s*,\s*pointer|pointer\s*,\s*nopass)\s*::\s*%s\b" % (iface, comp), rt, flags=re.I)
+    for comp, proc in targets.items():
+        m = re.search(r"^[ \t]*subroutine\s+%s\s*\(([^)]*)\)([^\n]*)\n(.*?)end subroutine" % proc, shim, flags=re.S | re.I | re.M)
+        assert m, "%s => %s: no such procedure in fortran/*.f90" % (comp, proc)
+        assert "bind" not in m.group(2).lower(), "%s is bind(C); the pointer's interface is not" % proc
+        assert [a.strip() for a in m.group(1).split(",")] == want_args
+        decl = {" ".join(l.split()) for l in m.group(3).split("\n") if "::" in l}
+        assert decl == want_decls, (proc, decl)
+        # and it forwards to the C entry point of the same direction
+        assert re.search(r"call\s+dlesm_%s\s*\(\s*from\s*,\s*to\s*,\s*startx\s*,\s*starty\s*,\s*nx\s*,\s*ny\s*,\s*blocking\s*\)" % comp,
+                         m.group(3), flags=re.I)
 
 
 def test_fortran_use_statements_name_existing_modules():
