@@ -929,7 +929,13 @@ int exchange_with(void *const *fields_in, int nfields_in, const CommTables &ct)
     void *fields[k::kMaxExchangeFields];
     int nfields = 0;
     FieldRec r0{};
-    const bool skip_clean = (pstate().extensions & DLESM_EXT_DIRTY_HALOS) != 0;
+    // The skip is a per-rank decision, but an exchange with another rank is a contract between two: both sides
+    // must agree on the field list (packed layout, slot parity) and on launching at all.  A one-sided write
+    // (a hook or set_field on one rank) would break that, so fields are only skipped when every neighbour of the
+    // installed tables is this rank itself; with remote neighbours every listed field is exchanged.
+    bool remote_peer = false;
+    for (const auto &g : ct.groups) remote_peer = remote_peer || g.peer0 != pstate().rank - 1;
+    const bool skip_clean = (pstate().extensions & DLESM_EXT_DIRTY_HALOS) != 0 && !remote_peer;
     for (int q = 0; q < nfields_in; ++q) {
         FieldRec rq;
         rc = lookup(fields_in[q], rq);

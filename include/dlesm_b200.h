@@ -155,7 +155,10 @@ int dlesm_set_extensions(int flags);
  * is_dirty methods are commented out (src/halo_mod.f90:10-40) and every halo_exchange runs.  With
  * this bit the library tracks, per device array, whether its halos are up to date (every entry point
  * that writes an array marks it dirty; halo_exchange, the periodic fill and a pushing sweep mark it
- * clean) and halo_exchange / apply_periodic_halos skip fields whose halos are clean: no launch. */
+ * clean) and halo_exchange / apply_periodic_halos skip fields whose halos are clean: no launch.
+ * An exchange that involves another rank is never shortened: the skip would be one rank's decision
+ * about a message both sides must agree on, so it applies to self-neighbour (one-rank periodic)
+ * exchanges and periodic fills only. */
 #define DLESM_EXT_DIRTY_HALOS 4
 
 /* ------------------------------------------------------------------------------------ */
