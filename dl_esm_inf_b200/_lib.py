@@ -163,6 +163,7 @@ SIGNATURES = {
     "dlesm_get_arith": (_I, []),
     "dlesm_dev_set_sweep_tiles": (_I, [_I, _I]),
     "dlesm_dev_grid_upload": (_I, [_I, _I, _PI, C.POINTER(_PD), C.POINTER(_V)]),
+    "dlesm_dev_grid_release": (_I, [C.POINTER(_V)]),
     "dlesm_compute_cu": (_I, [_V, _V, _V, _I, _I, _I, _I, _V]),
     "dlesm_compute_cv": (_I, [_V, _V, _V, _I, _I, _I, _I, _V]),
     "dlesm_compute_z": (_I, [_V, _V, _V, _V, _D, _D, _I, _I, _I, _I, _V]),

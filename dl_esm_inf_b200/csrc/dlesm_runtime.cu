@@ -1520,6 +1520,32 @@ extern "C" int dlesm_dev_grid_upload(int nx, int ny, const int *tmask, const dou
     return DLESM_OK;
 }
 
+// Release what dlesm_dev_grid_upload handed out (grid_mod keeps the 17 values in its *_device slots): the
+// tmask copy and every metric array that is not NULL; the slots are set to NULL.  Call before a second
+// grid_init of the same grid and when the grid is dropped -- the reference has no grid finaliser, so
+// nothing else will.
+extern "C" int dlesm_dev_grid_release(void *device_ptrs[17])
+{
+    clear_error();
+    if (!device_ptrs) return DLESM_OK;
+    int rc = ensure_device();
+    if (rc != DLESM_OK) return rc;
+    CU(cudaStreamSynchronize(ctx().stream));   // no sweep may still be reading the arrays
+    int first = DLESM_OK;
+    if (device_ptrs[0]) {
+        cudaError_t e = cudaFree(device_ptrs[0]);
+        if (e != cudaSuccess) first = fail_cuda(e, "grid release: tmask");
+        device_ptrs[0] = nullptr;
+    }
+    for (int q = 1; q < 17; ++q) {
+        if (!device_ptrs[q]) continue;
+        rc = dlesm_dev_field_free(device_ptrs[q]);
+        if (rc != DLESM_OK && first == DLESM_OK) first = rc;
+        device_ptrs[q] = nullptr;
+    }
+    return first;
+}
+
 // =========================================================================================
 // device layer: stencils
 // =========================================================================================

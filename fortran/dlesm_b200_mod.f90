@@ -191,6 +191,12 @@ module dlesm_b200_mod
        type(c_ptr), dimension(17), intent(out) :: device_ptrs
        integer(c_int) :: ierr
      end function
+     !> frees the 17 values dlesm_dev_grid_upload returned (null entries skipped) and nulls them
+     function dlesm_dev_grid_release(device_ptrs) bind(C, name="dlesm_dev_grid_release") result(ierr)
+       import :: c_int, c_ptr
+       type(c_ptr), dimension(17), intent(inout) :: device_ptrs
+       integer(c_int) :: ierr
+     end function
 
      ! ---- shallow-water stencils: one launcher per kernel + the fused step (SURVEY a-S)
      function dlesm_compute_cu(cu, p, u, xstart, xstop, ystart, ystop, tmask) &

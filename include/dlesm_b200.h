@@ -427,6 +427,11 @@ int dlesm_host_halo_exchange(double *host, int nx, int ny);
  * device_ptrs[17] receives the 17 *_device values of src/grid_mod.f90:104-150. */
 int dlesm_dev_grid_upload(int nx, int ny, const int *tmask, const double *const metrics[16],
                           void *device_ptrs[17]);
+/* Free what dlesm_dev_grid_upload returned (NULL entries are skipped) and set the 17 slots to NULL.
+ * The reference's grid_mod has no finaliser and grid_init may run again on the same grid
+ * (src/grid_mod.f90:104-150 only declares the slots): the patched grid_init calls this before it
+ * uploads again, and an application calls it when it drops a grid. */
+int dlesm_dev_grid_release(void *device_ptrs[17]);
 
 /* ------------------------------------------------------------------------------------ */
 /* DEVICE LAYER: shallow-water stencils (SURVEY.md a-S).  One launcher per kernel of the  */

@@ -353,6 +353,39 @@ def test_grid_device_arrays():
     assert g.device_array("tmask") == g.tmask_device != 0
 
 
+def test_grid_upload_and_release_as_the_patched_grid_init_calls_them():
+    """fortran/patches/grid_mod.f90.patch: grid_init -> dlesm_dev_grid_release(old slots) -> dlesm_dev_grid_upload.
+    The 17 device copies hold the host arrays bit for bit, NULL metrics are skipped, a release nulls the slots and
+    returns the memory (a second grid_init must not leak 17 arrays), a release of empty slots is a no-op"""
+    L = _lib.lib()
+    nx, ny = 72, 19
+    tm = np.asfortranarray(np.random.default_rng(5).integers(-1, 2, size=(nx, ny)).astype(np.int32))
+    host = [rnd((nx, ny), 40 + q) for q in range(16)]
+    metrics = (C.POINTER(C.c_double) * 16)(*[h.ctypes.data_as(C.POINTER(C.c_double)) for h in host])
+    metrics[3] = None                                              # a metric the application does not have
+    dev = (C.c_void_p * 17)()
+    assert L.dlesm_dev_grid_release(dev) == 0                      # constructor state: all C_NULL_PTR
+    for round_ in range(3):                                        # grid_init three times on one grid
+        assert L.dlesm_dev_grid_release(dev) == 0
+        assert all(not dev[q] for q in range(17))
+        assert L.dlesm_dev_grid_upload(nx, ny, tm.ctypes.data_as(C.POINTER(C.c_int)), metrics, dev) == 0, L.dlesm_last_error()
+        assert dev[0] and not dev[4] and all(dev[q + 1] for q in range(16) if q != 3)
+        for q in (0, 8, 15):
+            back = np.zeros((nx, ny), order="F")
+            L.dlesm_read_from_device_c(dev[q + 1], back.ctypes.data, 1, 1, nx, ny, True)
+            assert np.array_equal(back, host[q]), q
+        # the device copies are ordinary library fields: the checksum of one equals the host sum
+        v = C.c_double()
+        assert L.dlesm_dev_checksum(dev[1], 1, nx, 1, ny, C.byref(v)) == 0
+        ref = float(np.sum(np.abs(host[0]).astype(np.longdouble)))
+        assert abs(v.value - ref) <= RTOL * ref
+    ptr = dev[1]
+    assert L.dlesm_dev_grid_release(dev) == 0
+    assert all(not dev[q] for q in range(17))
+    # released arrays are gone from the registry: the library refuses the stale pointer
+    assert L.dlesm_dev_set_field(C.c_void_p(ptr), 0.0) == -23      # DLESM_ERR_UNKNOWN_PTR
+
+
 # ---------------------------------------------------------------------------------------------
 # shallow water: every un-fused kernel, then whole steps, fused variants, masks
 # ---------------------------------------------------------------------------------------------
