@@ -158,6 +158,15 @@ def pick_cpu_sample(nthreads, steps, warmup, budget_s):
     return best
 
 
+def arm_config(args, workload=None):
+    """the `config` object of BOTH arms, key for key and value for value (the driver compares them): what is
+    measured and how L2 is kept out of it.  Everything that belongs to one arm only goes to `config_notes`."""
+    return {"workload": workload or WORKLOAD % (args.size, args.size, args.alignment),
+            "l2": "GPU arm: inputs larger than L2, never flushed (each of the 9-12 resident fields is %.2f GB per GPU); "
+                  "CPU arm: a bounded sample of the same workload, see cpu_baseline.sample"
+                  % (args.size * args.size * 8 / 1e9)}
+
+
 def run_reference_arm(args):
     rank = env_int("RANK", 0)
     if rank != 0:
@@ -176,10 +185,10 @@ def run_reference_arm(args):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1000.0 * secs / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
         "data": "synthetic",
-        "config": {"workload": WORKLOAD % (args.size, args.size, args.alignment),
-                   "reference_sample": sample,
-                   "reference_build": "oracle port of the reference's Fortran loops (no Fortran/MPI toolchain "
-                                      "in this image: oracle/_ref cannot be built)"},
+        "config": arm_config(args),
+        "config_notes": {"reference_sample": sample,
+                         "reference_build": "oracle port of the reference's Fortran loops (no Fortran/MPI toolchain "
+                                            "in this image: oracle/_ref cannot be built)"},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": ncores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -621,12 +630,12 @@ def run_ours(args):
             "metric": METRIC, "value": R["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": R["elapsed_ms"] / args.steps, "higher_is_better": True,
             "scaling": args.scaling, "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": WORKLOAD % (args.size, args.size, args.alignment) if args.scaling == "weak" and
-                                   args.mode == "fused" and not args.tmask else
-                                   "shallow-water C-grid step %dx%d per GPU (%s scaling), double periodic, GO_OFFSET_SW, "
-                                   "FP64, DL_ESM_ALIGNMENT=%d, mode=%s%s"
-                                   % (sub.internal.nx, sub.internal.ny, args.scaling, args.alignment, args.mode,
-                                      ", tmask with 64x64 land islands (1.6 % land)" if args.tmask else ""),
+            "config": arm_config(args, None if args.scaling == "weak" and args.mode == "fused" and not args.tmask else
+                                 "shallow-water C-grid step %dx%d per GPU (%s scaling), double periodic, GO_OFFSET_SW, "
+                                 "FP64, DL_ESM_ALIGNMENT=%d, mode=%s%s"
+                                 % (sub.internal.nx, sub.internal.ny, args.scaling, args.alignment, args.mode,
+                                    ", tmask with 64x64 land islands (1.6 % land)" if args.tmask else "")),
+            "config_notes": {
                        "tile": "%dx%d per GPU, global %dx%d, tiles %dx%d" % (sub.internal.nx, sub.internal.ny, R["gx"],
                                                                           R["gy"], probe.nx, probe.ny),
                        "l2": "inputs larger than L2 (%d fields x %.2f GB per GPU)"
@@ -642,6 +651,28 @@ def run_ours(args):
             "clocks": R["clocks"], "gpu_launches": R["launches"], "roofline": R["roofline"], "cpu_baseline": cpu,
             "e2e": e2e, "halo_traffic": R["halo_traffic"], "checksums_p_u_v": list(R["cks"]),
             "sustained": R["sustained"], "parity": parity,
+        }
+
+        def pick(d, *path):
+            for k in path:
+                d = d.get(k) if isinstance(d, dict) else None
+            return d
+        # the figures a reviewer looks for first, at the top level at every N (the sub-records below carry the detail)
+        line["summary"] = {
+            "parity": {"ranks": parity.get("ranks"), "cases": parity.get("cases"), "checks": parity.get("checks"),
+                       "mismatches": parity.get("mismatches"), "full_size_checked": "full_size" in parity},
+            "sustained_value": pick(R, "sustained", "value"), "sustained_frac": pick(R, "sustained", "roofline_frac"),
+            "burst_frac": pick(R, "roofline", "frac"),
+            "one_step_value": one["value"] if (R["two_step"] and one is not None) else None,
+            "one_step_frac": pick(one, "roofline", "frac") if (R["two_step"] and one is not None) else None,
+            "strong_two_step": pick(strong, "two_step", "value"), "strong_one_step": pick(strong, "one_step", "value"),
+            "strong_two_step_frac": pick(strong, "two_step", "roofline", "frac"),
+            "config3_two_step_frac": pick(config3, "two_step", "roofline", "frac"),
+            "config3_one_step_frac": pick(config3, "one_step", "roofline", "frac"),
+            "config3_mismatches": pick(config3, "parity", "mismatches"),
+            "e2e_value": pick(e2e, "value"), "e2e_frac_of_pcie": pick(e2e, "frac_of_pcie"),
+            "stencil_parity_note": "stencils are compared with the project's oracle (pinned on the published shallow.f; "
+                                   "the reference ships no stencil): vs oracle, unpinned by the reference",
         }
         if R["two_step"] and one is not None:
             # the one-step formulation (the reference's: every step reads and writes the state once),

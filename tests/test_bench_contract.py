@@ -72,6 +72,24 @@ def test_both_arms_name_the_same_workload():
         assert abs(a - b) <= 1e-12 * abs(b)
 
 
+def test_round3_lines_share_one_config_and_carry_a_summary():
+    """round 3: both arms print the same `config` object (arm-specific text lives in `config_notes`) and our
+    line carries a compact top-level `summary` (parity, sustained and per-config roofline fractions)"""
+    ours = json.load(open(_latest("round3*_bench_n1.json")))
+    ref = json.load(open(_latest("round3*_bench_reference_arm.json")))
+    if "summary" not in ours:
+        pytest.skip("latest committed line predates the summary")
+    assert ours["config"] == ref["config"] and set(ours["config"]) == {"workload", "l2"}
+    assert "reference_sample" in ref["config_notes"] and "halo" in ours["config_notes"]
+    sm = ours["summary"]
+    assert sm["parity"]["mismatches"] == 0 and sm["parity"]["checks"] >= 100 and sm["parity"]["full_size_checked"]
+    assert sm["sustained_value"] == ours["sustained"]["value"] <= ours["value"] * 1.05
+    assert abs(sm["burst_frac"] - ours["roofline"]["frac"]) < 1e-12
+    assert sm["config3_mismatches"] == 0 and 0.5 < sm["config3_two_step_frac"] < 1.2
+    assert sm["e2e_value"] == ours["e2e"]["value"]
+    assert "unpinned" in sm["stencil_parity_note"]
+
+
 def test_reference_arm_line():
     d = json.load(open(_latest("r02z_bench_reference_arm.json")))
     assert d["impl"] == "reference" and d["gpu_launches"] == 0
